@@ -1,0 +1,184 @@
+// common.cuh -- internal types of libb200amg (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <string>
+#include "../../include/b200amg.h"
+
+// ---------------------------------------------------------------- errors
+void b200_set_error(const char *fmt, ...);
+
+#define CUDA_TRY(expr)                                                              \
+   do {                                                                             \
+      cudaError_t _e = (expr);                                                      \
+      if (_e != cudaSuccess) {                                                      \
+         b200_set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(_e),         \
+                        __FILE__, __LINE__, cudaGetErrorString(_e));                \
+         return B200_ERR_CUDA;                                                      \
+      }                                                                             \
+   } while (0)
+
+#define NCCL_TRY(expr)                                                              \
+   do {                                                                             \
+      ncclResult_t _r = (expr);                                                     \
+      if (_r != ncclSuccess) {                                                      \
+         b200_set_error("NCCL error at %s:%d: %s", __FILE__, __LINE__,              \
+                        ncclGetErrorString(_r));                                    \
+         return B200_ERR_NCCL;                                                      \
+      }                                                                             \
+   } while (0)
+
+#define B200_TRY(expr)                                                              \
+   do { int _s = (expr); if (_s != B200_OK) return _s; } while (0)
+
+#define ARG_CHECK(cond)                                                             \
+   do {                                                                             \
+      if (!(cond)) {                                                                \
+         b200_set_error("bad argument: %s (%s:%d)", #cond, __FILE__, __LINE__);     \
+         return B200_ERR_ARG;                                                       \
+      }                                                                             \
+   } while (0)
+
+// ---------------------------------------------------------------- context
+constexpr int B200_NUM_SMS      = 148;   // B200: 2 dies x 74 SMs
+constexpr int B200_MAX_RED      = 4;     // fused reductions per kernel
+constexpr int B200_MAX_PARTIALS = 8192;  // per-block partial sums kept per reduction slot
+
+struct b200_ctx {
+   int          device   = 0;
+   int          rank     = 0;
+   int          nranks   = 1;
+   cudaStream_t stream   = nullptr;   // compute stream (all kernels)
+   cudaStream_t cstream  = nullptr;   // halo / collective stream
+   cudaEvent_t  ev_pack  = nullptr;   // pack done   (compute -> comm)
+   cudaEvent_t  ev_halo  = nullptr;   // halo landed (comm -> compute)
+   cudaEvent_t  ev_t0 = nullptr, ev_t1 = nullptr;
+   ncclComm_t   comm     = nullptr;
+   long long    launches = 0;
+   // reduction scratch: partials[slot][block], finished-block counter, results
+   double      *d_partials = nullptr;
+   unsigned    *d_counter  = nullptr;
+   double      *d_scalars  = nullptr;  // device-resident scalars (dots, alpha, beta, ...)
+   double      *h_scalars  = nullptr;  // pinned mirror
+   // L2 flush scratch
+   char        *d_flush = nullptr;
+   size_t       flush_bytes = 0;
+   // pinned staging for host-vector entry points
+   double      *h_stage = nullptr;
+   size_t       h_stage_n = 0;
+   bool         capturing = false;
+};
+
+constexpr int B200_NUM_SCALARS = 64;
+
+#define LAUNCH(ctx, kern, grid, block, smem, ...)                                   \
+   do {                                                                             \
+      kern<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                \
+      (ctx)->launches++;                                                            \
+   } while (0)
+
+#define CHECK_LAUNCH()  CUDA_TRY(cudaGetLastError())
+
+// ---------------------------------------------------------------- matrices
+// One CSR block in HBM.  Two layouts are kept:
+//   layout 0 (CSR-vector): rp/ci/va as given; `lanes` lanes of a warp cooperate on a row
+//   layout 1 (sliced ELL, slice height 32): slice s holds rows 32s..32s+31, entry k of
+//            lane l at sl_off[s] + k*32 + l  -> every warp load is one contiguous
+//            128 B (ci) / 256 B (va) segment; padded entries have va = 0.
+struct DMat {
+   int        n_rows = 0, n_cols = 0;
+   long long  nnz = 0;
+   int       *rp = nullptr;    // [n_rows+1]
+   int       *ci = nullptr;    // [nnz]
+   double    *va = nullptr;    // [nnz]
+   int        layout = 0;
+   int        lanes  = 4;
+   int        n_slices = 0;
+   long long  sell_entries = 0;
+   long long *sl_off = nullptr;  // [n_slices+1]
+   int       *sl_ci  = nullptr;
+   double    *sl_va  = nullptr;
+   int        max_row = 0;
+   double     avg_row = 0.0;
+};
+
+// view passed by value to kernels
+struct MatView {
+   int              n_rows;
+   const int       *rp;
+   const int       *ci;
+   const double    *va;
+   const long long *sl_off;
+   const int       *sl_ci;
+   const double    *sl_va;
+};
+
+static inline MatView view_of(const DMat &m)
+{
+   MatView v;
+   v.n_rows = m.n_rows; v.rp = m.rp; v.ci = m.ci; v.va = m.va;
+   v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va;
+   return v;
+}
+
+struct HostCsr {
+   int n_rows = 0, n_cols = 0;
+   std::vector<int>    i, j;
+   std::vector<double> a;
+};
+
+struct b200_parcsr {
+   b200_ctx *ctx = nullptr;
+   int n_rows = 0, n_cols_diag = 0, n_cols_offd = 0;
+   DMat diag, offd;
+   // explicit transposes (restriction) -- built on first MatvecT
+   bool hasT = false;
+   DMat diagT, offdT;
+   // strict lower triangle of diag + the diagonal (two-stage GS) -- built on demand
+   bool hasL = false;
+   DMat lower;
+   double *d_diagonal = nullptr;
+   bool zero_diagonal = false;
+   // host copies kept for derived operators
+   HostCsr h_diag, h_offd;
+   // halo plan (hypre_ParCSRCommPkg)
+   int num_sends = 0, num_recvs = 0;
+   std::vector<int> send_procs, send_map_starts, recv_procs, recv_vec_starts;
+   int     n_send_elmts = 0;
+   int    *d_send_map  = nullptr;  // [n_send_elmts] local rows to pack
+   double *d_send_buf  = nullptr;  // [n_send_elmts]
+   double *d_ghost     = nullptr;  // [n_cols_offd]   x_tmp of the reference
+   // rows with at least one offd entry (processed after the halo landed)
+   int     n_bnd = 0;
+   int    *d_bnd_rows = nullptr;
+   // for MatvecT (job 2): contributions for ghost columns / received contributions
+   double *d_ghost_out = nullptr;  // [n_cols_offd]
+   double *d_recv_buf  = nullptr;  // [n_send_elmts]
+   // deterministic unpack plan for job 2: CSR of (local row -> positions in recv buf)
+   int    *d_unpack_rp = nullptr, *d_unpack_pos = nullptr;
+   int     n_unpack_rows = 0;
+   int    *d_unpack_rows = nullptr;
+};
+
+// ---------------------------------------------------------------- helpers
+template <class T>
+static inline int dev_upload(T **dst, const T *src, size_t n)
+{
+   *dst = nullptr;
+   if (n == 0) { return B200_OK; }
+   CUDA_TRY(cudaMalloc((void **)dst, n * sizeof(T)));
+   CUDA_TRY(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+   return B200_OK;
+}
+
+int  dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell);
+void dmat_free(DMat *m);
+void host_transpose(const HostCsr &a, HostCsr *t);
+
+// internal launchers shared between translation units (all on ctx->stream)
+int halo_start(b200_parcsr *A, const double *x);   // pack + post exchange on cstream
+int halo_finish(b200_parcsr *A);                   // make compute stream wait for ghosts

@@ -1,0 +1,215 @@
+// ctx.cu -- context, device memory, BLAS-1 kernels.
+#include "common.cuh"
+#include "vecops.cuh"
+#include <cstdarg>
+
+static thread_local char g_err[1024] = "";
+
+void b200_set_error(const char *fmt, ...)
+{
+   va_list ap;
+   va_start(ap, fmt);
+   vsnprintf(g_err, sizeof(g_err), fmt, ap);
+   va_end(ap);
+}
+
+extern "C" const char *b200_last_error(void) { return g_err; }
+extern "C" int b200_version(void) { return 100; }
+
+static int ctx_init_common(b200_ctx *c, int device)
+{
+   int ndev = 0;
+   cudaError_t e = cudaGetDeviceCount(&ndev);
+   if (e != cudaSuccess || ndev == 0)
+   {
+      b200_set_error("no CUDA device available (%s): this library has no CPU fallback",
+                     e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+      return B200_ERR_CUDA;
+   }
+   ARG_CHECK(device >= 0 && device < ndev);
+   c->device = device;
+   CUDA_TRY(cudaSetDevice(device));
+   CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+   CUDA_TRY(cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking));
+   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_pack, cudaEventDisableTiming));
+   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+   CUDA_TRY(cudaEventCreate(&c->ev_t0));
+   CUDA_TRY(cudaEventCreate(&c->ev_t1));
+   CUDA_TRY(cudaMalloc((void **)&c->d_partials, sizeof(double) * B200_MAX_RED * B200_MAX_PARTIALS));
+   CUDA_TRY(cudaMalloc((void **)&c->d_counter, sizeof(unsigned)));
+   CUDA_TRY(cudaMemset(c->d_counter, 0, sizeof(unsigned)));
+   CUDA_TRY(cudaMalloc((void **)&c->d_scalars, sizeof(double) * B200_NUM_SCALARS));
+   CUDA_TRY(cudaMemset(c->d_scalars, 0, sizeof(double) * B200_NUM_SCALARS));
+   CUDA_TRY(cudaMallocHost((void **)&c->h_scalars, sizeof(double) * B200_NUM_SCALARS));
+   return B200_OK;
+}
+
+extern "C" int b200_ctx_create(int device, b200_ctx **ctx)
+{
+   ARG_CHECK(ctx != nullptr);
+   b200_ctx *c = new b200_ctx();
+   int s = ctx_init_common(c, device);
+   if (s != B200_OK) { delete c; *ctx = nullptr; return s; }
+   *ctx = c;
+   return B200_OK;
+}
+
+extern "C" int b200_nccl_unique_id(char uid[128])
+{
+   ncclUniqueId id;
+   static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+   NCCL_TRY(ncclGetUniqueId(&id));
+   memcpy(uid, &id, 128);
+   return B200_OK;
+}
+
+extern "C" int b200_ctx_create_dist(int device, int rank, int nranks, const char uid[128], b200_ctx **ctx)
+{
+   ARG_CHECK(ctx != nullptr && nranks >= 1 && rank >= 0 && rank < nranks);
+   b200_ctx *c = new b200_ctx();
+   int s = ctx_init_common(c, device);
+   if (s != B200_OK) { delete c; *ctx = nullptr; return s; }
+   c->rank = rank; c->nranks = nranks;
+   if (nranks > 1)
+   {
+      ncclUniqueId id;
+      memcpy(&id, uid, 128);
+      NCCL_TRY(ncclCommInitRank(&c->comm, nranks, id, rank));
+   }
+   *ctx = c;
+   return B200_OK;
+}
+
+extern "C" int b200_ctx_destroy(b200_ctx *c)
+{
+   if (!c) { return B200_OK; }
+   cudaSetDevice(c->device);
+   cudaDeviceSynchronize();
+   if (c->comm) { ncclCommDestroy(c->comm); }
+   cudaFree(c->d_partials); cudaFree(c->d_counter); cudaFree(c->d_scalars);
+   cudaFreeHost(c->h_scalars);
+   if (c->d_flush) { cudaFree(c->d_flush); }
+   if (c->h_stage) { cudaFreeHost(c->h_stage); }
+   cudaEventDestroy(c->ev_pack); cudaEventDestroy(c->ev_halo);
+   cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);
+   cudaStreamDestroy(c->stream); cudaStreamDestroy(c->cstream);
+   delete c;
+   return B200_OK;
+}
+
+extern "C" int b200_ctx_sync(b200_ctx *c)
+{
+   ARG_CHECK(c != nullptr);
+   CUDA_TRY(cudaStreamSynchronize(c->cstream));
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   return B200_OK;
+}
+
+extern "C" int b200_ctx_rank(const b200_ctx *c, int *rank, int *nranks)
+{
+   ARG_CHECK(c != nullptr);
+   if (rank) { *rank = c->rank; }
+   if (nranks) { *nranks = c->nranks; }
+   return B200_OK;
+}
+
+extern "C" long long b200_ctx_launch_count(const b200_ctx *c) { return c ? c->launches : -1; }
+
+extern "C" int b200_timer_start(b200_ctx *c)
+{
+   ARG_CHECK(c != nullptr);
+   CUDA_TRY(cudaEventRecord(c->ev_t0, c->stream));
+   return B200_OK;
+}
+
+extern "C" int b200_timer_stop(b200_ctx *c, float *ms)
+{
+   ARG_CHECK(c != nullptr && ms != nullptr);
+   CUDA_TRY(cudaEventRecord(c->ev_t1, c->stream));
+   CUDA_TRY(cudaEventSynchronize(c->ev_t1));
+   CUDA_TRY(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+   return B200_OK;
+}
+
+extern "C" int b200_flush_l2(b200_ctx *c)
+{
+   ARG_CHECK(c != nullptr);
+   if (!c->d_flush)
+   {
+      c->flush_bytes = (size_t)256 << 20;   // 256 MiB > 126 MB L2
+      CUDA_TRY(cudaMalloc((void **)&c->d_flush, c->flush_bytes));
+   }
+   CUDA_TRY(cudaMemsetAsync(c->d_flush, 1, c->flush_bytes, c->stream));
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- memory
+extern "C" int b200_dev_alloc(b200_ctx *c, long long n, double **dev)
+{
+   ARG_CHECK(c != nullptr && dev != nullptr && n >= 0);
+   *dev = nullptr;
+   CUDA_TRY(cudaMalloc((void **)dev, sizeof(double) * (size_t)(n > 0 ? n : 1)));
+   CUDA_TRY(cudaMemsetAsync(*dev, 0, sizeof(double) * (size_t)(n > 0 ? n : 1), c->stream));
+   return B200_OK;
+}
+
+extern "C" int b200_dev_free(b200_ctx *c, double *dev)
+{
+   ARG_CHECK(c != nullptr);
+   if (dev) { CUDA_TRY(cudaStreamSynchronize(c->stream)); CUDA_TRY(cudaFree(dev)); }
+   return B200_OK;
+}
+
+extern "C" int b200_h2d(b200_ctx *c, double *dev, const double *host, long long n)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   if (n == 0) { return B200_OK; }
+   CUDA_TRY(cudaMemcpyAsync(dev, host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   return B200_OK;
+}
+
+extern "C" int b200_d2h(b200_ctx *c, double *host, const double *dev, long long n)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   if (n == 0) { return B200_OK; }
+   CUDA_TRY(cudaMemcpyAsync(host, dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- BLAS-1
+extern "C" int b200_vec_fill(b200_ctx *c, int n, double a, double *y)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   return vec_fill(c, n, a, y);
+}
+extern "C" int b200_vec_copy(b200_ctx *c, int n, const double *x, double *y)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   if (n == 0 || x == y) { return B200_OK; }
+   CUDA_TRY(cudaMemcpyAsync(y, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
+   return B200_OK;
+}
+extern "C" int b200_vec_scale(b200_ctx *c, int n, double a, double *y)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   // hypre_SeqVectorScale: alpha == 1 is a no-op, alpha == 0 fills (src/seq_mv/vector.c:652-689)
+   if (a == 1.0) { return B200_OK; }
+   if (a == 0.0) { return vec_fill(c, n, 0.0, y); }
+   return vec_scale(c, n, a, y);
+}
+extern "C" int b200_vec_axpy(b200_ctx *c, int n, double a, const double *x, double *y)
+{
+   ARG_CHECK(c != nullptr && n >= 0);
+   return vec_axpy(c, n, a, x, y);
+}
+extern "C" int b200_vec_dot(b200_ctx *c, int n, const double *x, const double *y, double *result_h)
+{
+   ARG_CHECK(c != nullptr && n >= 0 && result_h != nullptr);
+   B200_TRY(vec_dot(c, n, x, y, c->d_scalars + 0));
+   B200_TRY(scalars_allreduce(c, c->d_scalars + 0, 1));
+   B200_TRY(scalars_to_host(c, 0, 1));
+   *result_h = c->h_scalars[0];
+   return B200_OK;
+}

@@ -1,0 +1,328 @@
+// ops.cu -- SpMV, residual, smoothers and transfer operators as epilogues of the
+// fused row kernels (spmv.cuh).
+#include "ops.cuh"
+#include "vecops.cuh"
+
+// ---------------------------------------------------------------- epilogues
+// y = alpha*t + beta*b           hypre_CSRMatrixMatvecOutOfPlaceHost (src/seq_mv/csr_matvec.c:683-847)
+struct EpiMatvec {
+   static constexpr int NRED = 0;
+   double alpha, beta; const double *b; double *y;
+   __device__ void operator()(int r, double t, double *) const
+   {
+      double v = alpha * t;
+      if (beta != 0.0) { v = fma(beta, b[r], v); }
+      y[r] = v;
+   }
+};
+// y = t, red0 += y*x             PCG: s = A p and <s,p> (src/krylov/pcg.c:577-580)
+struct EpiMatvecDot {
+   static constexpr int NRED = 1;
+   const double *x; double *y;
+   __device__ void operator()(int r, double t, double *red) const
+   {
+      y[r] = t;
+      red[0] = fma(t, x[r], red[0]);
+   }
+};
+// u_out = u_in + (w*(f - t)) / l1     hypre_BoomerAMGRelax7Jacobi (src/parcsr_ls/par_relax.c:1177-1254)
+struct EpiJacobi {
+   static constexpr int NRED = 0;
+   double w; const double *f; const double *l1; const double *u_in; double *u_out;
+   __device__ void operator()(int r, double t, double *) const
+   {
+      u_out[r] = u_in[r] + (w * (f[r] - t)) / l1[r];
+   }
+};
+// Chebyshev first step (src/parcsr_ls/par_cheby.c:275-283,318-341):
+//   r = ds.*(f - t)  [scale]  |  r = f - t ;  tmp = ds.*(c*r) | c*r
+struct EpiChebyFirst {
+   static constexpr int NRED = 0;
+   int scale; double c; const double *f; const double *ds; double *rv; double *tmp;
+   __device__ void operator()(int r, double t, double *) const
+   {
+      double res = f[r] - t;
+      if (scale) { res = ds[r] * res; }
+      rv[r] = res;
+      double u1 = res * c;
+      tmp[r] = scale ? ds[r] * u1 : u1;
+   }
+};
+// Chebyshev inner step (par_cheby.c:284-297,344-371): u_i = c_i*r + ds.*t ; then either
+//   out = ds.*u_i (next SpMV input)   or   u += ds.*u_i (last step)
+struct EpiChebyStep {
+   static constexpr int NRED = 0;
+   int scale; int last; double c; const double *ds; const double *rv; double *out; double *u;
+   __device__ void operator()(int r, double t, double *) const
+   {
+      double ui = scale ? c * rv[r] + ds[r] * t : c * rv[r] + t;
+      double su = scale ? ds[r] * ui : ui;
+      if (last) { u[r] = u[r] + su; }
+      else      { out[r] = su; }
+   }
+};
+// two-stage GS first stage (par_relax.c:1546-1557): z0 = (w*(f - t))/d
+struct EpiGsFirst {
+   static constexpr int NRED = 0;
+   double w; const double *f; const double *d; double *z;
+   __device__ void operator()(int r, double t, double *) const { z[r] = (w * (f[r] - t)) / d[r]; }
+};
+// inner stage over the strict lower triangle (par_relax.c:1562-1585): z' = t/d ; u += mult*z'
+// (first inner stage also applies the pending u += z0)
+struct EpiGsInner {
+   static constexpr int NRED = 0;
+   int first; double mult; const double *d; const double *z_in; double *z_out; double *u;
+   __device__ void operator()(int r, double t, double *) const
+   {
+      double zn = t / d[r];
+      double uu = u[r];
+      if (first) { uu = uu + z_in[r]; }
+      u[r] = uu + mult * zn;
+      z_out[r] = zn;
+   }
+};
+
+// zero-initial-guess / alpha == 0 elementwise variants (A*0 == 0: same arithmetic, no SpMV)
+struct FScaleCopy { static constexpr int NRED = 0; double beta; const double *b; double *y;
+   __device__ void operator()(int i, double *) const { y[i] = beta * b[i]; } };
+struct FZero { static constexpr int NRED = 0; double w; const double *f; const double *l1; double *u;
+   __device__ void operator()(int i, double *) const { u[i] = (w * f[i]) / l1[i]; } };
+struct FChebyFirst0 { static constexpr int NRED = 0; int scale; double c; const double *f; const double *ds;
+   double *rv; double *tmp;
+   __device__ void operator()(int i, double *) const
+   {
+      double res = f[i];
+      if (scale) { res = ds[i] * res; }
+      rv[i] = res;
+      double u1 = res * c;
+      tmp[i] = scale ? ds[i] * u1 : u1;
+   } };
+struct FGsFirst0 { static constexpr int NRED = 0; double w; const double *f; const double *d; double *z;
+   __device__ void operator()(int i, double *) const { z[i] = (w * f[i]) / d[i]; } };
+
+// ---------------------------------------------------------------- operators
+int op_matvec(b200_parcsr *A, double alpha, const double *x, double beta, const double *b, double *y)
+{
+   if (alpha == 0.0)
+   {
+      // y = beta*b (csr_matvec.c:130-160)
+      if (beta == 0.0) { return vec_fill(A->ctx, A->n_rows, 0.0, y); }
+      FScaleCopy f{beta, b, y};
+      return run_ewise(A->ctx, A->n_rows, f, nullptr);
+   }
+   EpiMatvec e{alpha, beta, b, y};
+   return run_rows(A, A->diag, A->offd, true, x, e, nullptr);
+}
+
+int op_matvec_dot(b200_parcsr *A, const double *x, double *y, double *d_out)
+{
+   EpiMatvecDot e{x, y};
+   return run_rows(A, A->diag, A->offd, true, x, e, d_out);
+}
+
+struct FScaleInPlace { static constexpr int NRED = 0; double beta; double *y;
+   __device__ void operator()(int i, double *) const { y[i] = beta * y[i]; } };
+
+// hypre_ParCSRMatrixMatvecTHost (src/parcsr_mv/par_csr_matvec.c:287-514):
+//   y_tmp = offd^T x -> owners (job 2)  ||  y = alpha diag^T x + beta y  ; y[send_map] += y_buf
+int op_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, double *y)
+{
+   B200_TRY(parcsr_ensure_T(A));
+   b200_ctx *c = A->ctx;
+   const bool comm = c->nranks > 1 && (A->num_sends + A->num_recvs) > 0;
+   if (comm && A->n_cols_offd > 0)
+   {
+      EpiMatvec eo{1.0, 0.0, nullptr, A->d_ghost_out};
+      B200_TRY(run_rows(A, A->offdT, A->offdT, false, x, eo, nullptr));
+   }
+   if (comm) { B200_TRY(halo_reverse_start(A)); }
+   EpiMatvec e{alpha, beta, y, y};
+   B200_TRY(run_rows(A, A->diagT, A->offdT, false, x, e, nullptr));
+   if (comm) { B200_TRY(halo_reverse_finish_add(A, alpha, y)); }
+   return B200_OK;
+}
+
+int op_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
+                const double *u_in, double *u_out, int zero_guess)
+{
+   if (zero_guess)
+   {
+      // Vtemp = w*f ; u = 0 + Vtemp./l1 (par_relax.c:1221-1228,1238-1246)
+      FZero fz{w, f, l1, u_out};
+      return run_ewise(A->ctx, A->n_rows, fz, nullptr);
+   }
+   EpiJacobi e{w, f, l1, u_in, u_out};
+   return run_rows(A, A->diag, A->offd, true, u_in, e, nullptr);
+}
+
+int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *coefs_h, int order,
+             int scale, double *u, double *v, double *r, double *tmp, int zero_guess)
+{
+   if (order > 4) { order = 4; }
+   if (order < 1) { order = 1; }
+   const int k = order - 1;   // cheby_order (par_cheby.c:262)
+   b200_ctx *c = A->ctx;
+   const int n = A->n_rows;
+   if (zero_guess)
+   {
+      FChebyFirst0 f0{scale, coefs_h[k], f, ds, r, tmp};
+      B200_TRY(run_ewise(c, n, f0, nullptr));
+   }
+   else
+   {
+      EpiChebyFirst e{scale, coefs_h[k], f, ds, r, tmp};
+      B200_TRY(run_rows(A, A->diag, A->offd, true, u, e, nullptr));
+   }
+   if (k == 0)
+   {
+      // u = orig_u + ds.*u1  (tmp already holds ds.*u1)
+      return zero_guess ? b200_vec_copy(c, n, tmp, u) : vec_axpy(c, n, 1.0, tmp, u);
+   }
+   double *in = tmp, *out = v;
+   for (int i = k - 1; i >= 0; i--)
+   {
+      EpiChebyStep e{scale, i == 0 ? 1 : 0, coefs_h[i], ds, r, out, u};
+      if (i == 0 && zero_guess)
+      {
+         // u == 0: write instead of accumulate (same value: 0 + x == x)
+         B200_TRY(vec_fill(c, n, 0.0, u));
+      }
+      B200_TRY(run_rows(A, A->diag, A->offd, true, in, e, nullptr));
+      double *t = in; in = out; out = t;
+   }
+   return B200_OK;
+}
+
+int op_gs2(b200_parcsr *A, const double *f, double w, int inner, double *u, double *z, double *tmp,
+           int zero_guess)
+{
+   B200_TRY(parcsr_ensure_L(A));
+   if (A->zero_diagonal)
+   {
+      b200_set_error("two-stage Gauss-Seidel: zero diagonal entry (reference: hypre_error_in_arg(1), par_relax.c:1538-1544)");
+      return B200_ERR_NUMERIC;
+   }
+   b200_ctx *c = A->ctx;
+   const int n = A->n_rows;
+   const double *d = A->d_diagonal;
+   if (zero_guess)
+   {
+      FGsFirst0 f0{w, f, d, z};
+      B200_TRY(run_ewise(c, n, f0, nullptr));
+      B200_TRY(vec_fill(c, n, 0.0, u));
+   }
+   else
+   {
+      EpiGsFirst e{w, f, d, z};
+      B200_TRY(run_rows(A, A->diag, A->offd, true, u, e, nullptr));
+   }
+   if (inner <= 0) { return vec_axpy(c, n, 1.0, z, u); }
+   double mult = -1.0;
+   double *zin = z, *zout = tmp;
+   for (int k = 0; k < inner; k++)
+   {
+      EpiGsInner e{k == 0 ? 1 : 0, mult, d, zin, zout, u};
+      B200_TRY(run_rows(A, A->lower, A->lower, false, zin, e, nullptr));
+      mult = -mult;
+      double *t = zin; zin = zout; zout = t;
+   }
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- dense coarse solve
+// u[i] = sum_j Ainv[i][j] * f_all[j]; one warp per row.
+__global__ void dense_matvec_kernel(int n_rows, int n_cols, const double *__restrict__ M,
+                                    const double *__restrict__ f, double *__restrict__ u)
+{
+   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+   const int lane = threadIdx.x & 31;
+   if (row >= n_rows) { return; }
+   double t = 0.0;
+   for (int j = lane; j < n_cols; j += 32) { t = fma(M[(size_t)row * n_cols + j], f[j], t); }
+#pragma unroll
+   for (int o = 16; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o); }
+   if (lane == 0) { u[row] = t; }
+}
+
+int op_dense_matvec(b200_ctx *ctx, int n_rows, int n_cols, const double *M, const double *f_all, double *u)
+{
+   if (n_rows == 0) { return B200_OK; }
+   int grid = (n_rows + 7) / 8;
+   LAUNCH(ctx, dense_matvec_kernel, grid, 256, 0, n_rows, n_cols, M, f_all, u);
+   CHECK_LAUNCH();
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- C ABI
+extern "C" int b200_parcsr_matvec(b200_parcsr *A, double alpha, const double *x, double beta,
+                                  const double *b, double *y)
+{
+   ARG_CHECK(A != nullptr && y != nullptr && (x != nullptr || A->n_cols_diag == 0));
+   ARG_CHECK(beta == 0.0 || b != nullptr);
+   ARG_CHECK(x != y);
+   return op_matvec(A, alpha, x, beta, b, y);
+}
+
+extern "C" int b200_parcsr_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, double *y)
+{
+   ARG_CHECK(A != nullptr && y != nullptr && x != y);
+   return op_matvecT(A, alpha, x, beta, y);
+}
+
+extern "C" int b200_relax_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
+                                   double *u, double *tmp, int zero_guess)
+{
+   ARG_CHECK(A != nullptr && f != nullptr && l1 != nullptr && u != nullptr && tmp != nullptr);
+   if (zero_guess) { return op_l1jacobi(A, f, l1, w, u, u, 1); }
+   B200_TRY(op_l1jacobi(A, f, l1, w, u, tmp, 0));
+   return b200_vec_copy(A->ctx, A->n_rows, tmp, u);
+}
+
+extern "C" int b200_relax_cheby(b200_parcsr *A, const double *f, const double *ds, const double *coefs_h,
+                                int order, int scale, double *u, double *v, double *r, double *tmp,
+                                int zero_guess)
+{
+   ARG_CHECK(A != nullptr && f != nullptr && coefs_h != nullptr && u != nullptr && v != nullptr &&
+             r != nullptr && tmp != nullptr);
+   ARG_CHECK(!scale || ds != nullptr);
+   return op_cheby(A, f, ds, coefs_h, order, scale, u, v, r, tmp, zero_guess);
+}
+
+extern "C" int b200_relax_2stage_gs(b200_parcsr *A, const double *f, double w, int inner,
+                                    double *u, double *z, double *tmp, int zero_guess)
+{
+   ARG_CHECK(A != nullptr && f != nullptr && u != nullptr && z != nullptr && tmp != nullptr && inner >= 1);
+   return op_gs2(A, f, w, inner, u, z, tmp, zero_guess);
+}
+
+static int ensure_stage(b200_ctx *c, size_t n)
+{
+   if (c->h_stage_n >= n) { return B200_OK; }
+   if (c->h_stage) { CUDA_TRY(cudaFreeHost(c->h_stage)); c->h_stage = nullptr; c->h_stage_n = 0; }
+   CUDA_TRY(cudaMallocHost((void **)&c->h_stage, sizeof(double) * n));
+   c->h_stage_n = n;
+   return B200_OK;
+}
+
+// host-vector SpMV: what HYPRE_ParCSRMatrixMatvec costs end to end for host-resident
+// hypre vectors (H2D x [, b], kernel, D2H y).
+extern "C" int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const double *x_h, double beta,
+                                       const double *b_h, double *y_h)
+{
+   ARG_CHECK(A != nullptr && x_h != nullptr && y_h != nullptr && (beta == 0.0 || b_h != nullptr));
+   b200_ctx *c = A->ctx;
+   static thread_local double *dx = nullptr, *dy = nullptr;
+   static thread_local long long cap_x = 0, cap_y = 0;
+   if (cap_x < A->n_cols_diag) { if (dx) { cudaFree(dx); } B200_TRY(b200_dev_alloc(c, A->n_cols_diag, &dx)); cap_x = A->n_cols_diag; }
+   if (cap_y < A->n_rows) { if (dy) { cudaFree(dy); } B200_TRY(b200_dev_alloc(c, A->n_rows, &dy)); cap_y = A->n_rows; }
+   (void)ensure_stage;
+   CUDA_TRY(cudaMemcpyAsync(dx, x_h, sizeof(double) * (size_t)A->n_cols_diag, cudaMemcpyHostToDevice, c->stream));
+   if (beta != 0.0)
+   {
+      CUDA_TRY(cudaMemcpyAsync(dy, b_h, sizeof(double) * (size_t)A->n_rows, cudaMemcpyHostToDevice, c->stream));
+   }
+   B200_TRY(op_matvec(A, alpha, dx, beta, dy, dy));
+   CUDA_TRY(cudaMemcpyAsync(y_h, dy, sizeof(double) * (size_t)A->n_rows, cudaMemcpyDeviceToHost, c->stream));
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   return B200_OK;
+}

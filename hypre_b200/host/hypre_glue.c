@@ -1,0 +1,462 @@
+/* hypre_glue.c -- the reference-side binding of the B200 solve phase.
+ *
+ * This file is what a hypre maintainer would add to the library: it reads
+ * hypre's own host objects (hypre_ParCSRMatrix, hypre_ParAMGData, hypre_PCGData)
+ * after the reference's host setup, uploads them once through the C ABI of
+ * include/b200amg.h, and routes the solve-phase entry points to the device:
+ *
+ *   hypre_PCGSolve               (src/krylov/pcg.c:317)            -> b200_pcg_solve_host
+ *   HYPRE_ParCSRMatrixMatvec     (src/parcsr_mv/HYPRE_parcsr_matrix.c) -> b200_parcsr_matvec_host
+ *   hypre_BoomerAMGSetup/Destroy (mirror invalidation)
+ *
+ * It is built as libHYPRE_b200.so and placed BEFORE the reference library in
+ * the link/load order, so these definitions interpose the reference's symbols
+ * (ELF symbol interposition; the reference library is compiled -fPIC without
+ * -Bsymbolic).  Calls that are not on the supported device path are rejected
+ * loudly (HYPRE_ERROR_GENERIC) -- there is no CPU fallback for the solve --
+ * except for Krylov solves whose operator table is not ParCSR (struct/sstruct
+ * interfaces), which were never on this path and go to the reference untouched.
+ *
+ * Compiled against the reference's own headers (-I/root/reference/src/...);
+ * no reference source is copied.
+ */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+
+#include "_hypre_parcsr_ls.h"
+#include "_hypre_parcsr_mv.h"
+#include "_hypre_utilities.h"
+#include "krylov.h"
+#include "b200amg.h"
+
+/* ------------------------------------------------------------------ state */
+static b200_ctx *g_ctx = NULL;
+static int g_verbose = -1;
+
+typedef struct mirror_s {
+   void            *key;      /* hypre_ParAMGData* or hypre_ParCSRMatrix* */
+   b200_amg        *amg;
+   b200_parcsr     *A;        /* level-0 operator (owned by amg when amg != NULL) */
+   struct mirror_s *next;
+} mirror_t;
+static mirror_t *g_mirrors = NULL;
+
+static int verbose(void)
+{
+   if (g_verbose < 0) { const char *e = getenv("HYPRE_B200_VERBOSE"); g_verbose = e ? atoi(e) : 0; }
+   return g_verbose;
+}
+
+static b200_ctx *glue_ctx(void)
+{
+   if (!g_ctx)
+   {
+      int dev = 0;
+      const char *e = getenv("HYPRE_B200_DEVICE");
+      if (!e) { e = getenv("LOCAL_RANK"); }
+      if (e) { dev = atoi(e); }
+      if (b200_ctx_create(dev, &g_ctx) != B200_OK)
+      {
+         fprintf(stderr, "hypre_b200: cannot create device context: %s\n", b200_last_error());
+         g_ctx = NULL;
+      }
+   }
+   return g_ctx;
+}
+
+b200_ctx *hypre_b200_context(void) { return glue_ctx(); }
+
+static mirror_t *mirror_find(void *key)
+{
+   mirror_t *m;
+   for (m = g_mirrors; m; m = m->next) { if (m->key == key) { return m; } }
+   return NULL;
+}
+
+static void mirror_drop(void *key)
+{
+   mirror_t **pp = &g_mirrors;
+   while (*pp)
+   {
+      if ((*pp)->key == key)
+      {
+         mirror_t *m = *pp;
+         *pp = m->next;
+         if (m->amg) { b200_amg_destroy(m->amg); }
+         else if (m->A) { b200_parcsr_destroy(m->A); }
+         free(m);
+         return;
+      }
+      pp = &(*pp)->next;
+   }
+}
+
+void hypre_b200_reset(void)
+{
+   while (g_mirrors) { mirror_drop(g_mirrors->key); }
+   if (g_ctx) { b200_ctx_destroy(g_ctx); g_ctx = NULL; }
+}
+
+#define GLUE_FAIL(msg)                                                              \
+   do {                                                                             \
+      char _b[1200];                                                                \
+      snprintf(_b, sizeof(_b), "hypre_b200: %s (%s)", msg, b200_last_error());      \
+      fprintf(stderr, "%s\n", _b);                                                  \
+      hypre_error_w_msg(HYPRE_ERROR_GENERIC, _b);                                   \
+   } while (0)
+
+/* --------------------------------------------------------------- uploads */
+/* hypre_ParCSRMatrix -> b200_parcsr (diag, offd, halo plan of the CommPkg) */
+static b200_parcsr *upload_parcsr(hypre_ParCSRMatrix *A)
+{
+   hypre_CSRMatrix     *diag = hypre_ParCSRMatrixDiag(A);
+   hypre_CSRMatrix     *offd = hypre_ParCSRMatrixOffd(A);
+   hypre_ParCSRCommPkg *pkg;
+   b200_parcsr         *dA = NULL;
+   HYPRE_Int            n_offd = hypre_CSRMatrixNumCols(offd);
+   int ns = 0, nr = 0;
+   const int *sp = NULL, *sms = NULL, *sme = NULL, *rp = NULL, *rvs = NULL;
+
+   if (!hypre_ParCSRMatrixCommPkg(A)) { hypre_MatvecCommPkgCreate(A); }
+   pkg = hypre_ParCSRMatrixCommPkg(A);
+   if (pkg)
+   {
+      ns  = hypre_ParCSRCommPkgNumSends(pkg);
+      nr  = hypre_ParCSRCommPkgNumRecvs(pkg);
+      sp  = hypre_ParCSRCommPkgSendProcs(pkg);
+      sms = hypre_ParCSRCommPkgSendMapStarts(pkg);
+      sme = hypre_ParCSRCommPkgSendMapElmts(pkg);
+      rp  = hypre_ParCSRCommPkgRecvProcs(pkg);
+      rvs = hypre_ParCSRCommPkgRecvVecStarts(pkg);
+   }
+   if (b200_parcsr_create(glue_ctx(), hypre_CSRMatrixNumRows(diag), hypre_CSRMatrixNumCols(diag),
+                          hypre_CSRMatrixI(diag), hypre_CSRMatrixJ(diag), hypre_CSRMatrixData(diag),
+                          n_offd, hypre_CSRMatrixI(offd), hypre_CSRMatrixJ(offd), hypre_CSRMatrixData(offd),
+                          ns, sp, sms, sme, nr, rp, rvs, &dA) != B200_OK)
+   {
+      return NULL;
+   }
+   return dA;
+}
+
+/* hypre_ParAMGData (after the reference's host setup) -> b200_amg */
+static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
+{
+   b200_ctx  *ctx = glue_ctx();
+   b200_amg  *amg = NULL;
+   HYPRE_Int  nl = hypre_ParAMGDataNumLevels(amg_data);
+   hypre_ParCSRMatrix **A_array = hypre_ParAMGDataAArray(amg_data);
+   hypre_ParCSRMatrix **P_array = hypre_ParAMGDataPArray(amg_data);
+   HYPRE_Int *grt = hypre_ParAMGDataGridRelaxType(amg_data);
+   HYPRE_Int *ngs = hypre_ParAMGDataNumGridSweeps(amg_data);
+   hypre_Vector **l1 = hypre_ParAMGDataL1Norms(amg_data);
+   hypre_Vector **ds = hypre_ParAMGDataChebyDS(amg_data);
+   HYPRE_Real **coefs = hypre_ParAMGDataChebyCoefs(amg_data);
+   int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0;
+
+   if (!ctx) { return NULL; }
+   /* options with no device implementation are rejected, never silently run on the CPU */
+   if (hypre_ParAMGDataBlockMode(amg_data) || hypre_ParAMGDataSmoothNumLevels(amg_data) > 0 ||
+       hypre_ParAMGDataAdditive(amg_data) >= 0 || hypre_ParAMGDataMultAdditive(amg_data) >= 0 ||
+       hypre_ParAMGDataSimple(amg_data) >= 0 || hypre_ParAMGDataRestriction(amg_data) ||
+       hypre_ParAMGDataRelaxOrder(amg_data) != 0 || hypre_ParAMGDataGridRelaxPoints(amg_data) != NULL ||
+       hypre_ParAMGDataParticipate(amg_data) || hypre_ParAMGDataPartialCycleCoarsestLevel(amg_data) >= 0)
+   {
+      b200_ctx_sync(ctx);
+      fprintf(stderr, "hypre_b200: BoomerAMG option outside the device path (block mode, complex "
+              "smoothers, additive cycles, AIR restriction, CF relaxation order, sequential coarse solve)\n");
+      return NULL;
+   }
+   for (k = 0; k < 4; k++) { relax_type[k] = grt[k]; num_sweeps[k] = ngs[k]; }
+   if (nl == 1)
+   {
+      relax_type[0] = hypre_ParAMGDataUserRelaxType(amg_data);
+      if (relax_type[0] == -1) { relax_type[0] = 6; }
+   }
+   if (relax_type[3] == 19) { relax_type[3] = 9; }
+
+   if (b200_amg_create(ctx, nl, &amg) != B200_OK) { return NULL; }
+   for (l = 0; l < nl; l++)
+   {
+      b200_parcsr *dA = upload_parcsr(A_array[l]);
+      b200_parcsr *dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+      if (!dA || (l < nl - 1 && !dP) || b200_amg_set_level(amg, l, dA, dP) != B200_OK)
+      {
+         if (dA) { b200_parcsr_destroy(dA); }
+         if (dP) { b200_parcsr_destroy(dP); }
+         b200_amg_destroy(amg);
+         return NULL;
+      }
+   }
+   if (b200_amg_set_cycle(amg, relax_type, num_sweeps, hypre_ParAMGDataCycleType(amg_data),
+                          hypre_ParAMGDataFCycle(amg_data)) != B200_OK) { b200_amg_destroy(amg); return NULL; }
+   for (k = 0; k < 4; k++) { if (relax_type[k] == 16) { uses_cheby = 1; } }
+   for (l = 0; l < nl; l++)
+   {
+      const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) : NULL;
+      if (b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d) != B200_OK)
+      {
+         b200_amg_destroy(amg); return NULL;
+      }
+      if (uses_cheby && coefs && coefs[l])
+      {
+         const double *dsd = (ds && ds[l]) ? hypre_VectorData(ds[l]) : NULL;
+         if (b200_amg_set_level_cheby(amg, l, dsd, coefs[l], hypre_ParAMGDataChebyOrder(amg_data),
+                                      hypre_ParAMGDataChebyScale(amg_data)) != B200_OK)
+         {
+            b200_amg_destroy(amg); return NULL;
+         }
+      }
+   }
+   if (relax_type[3] == 9 && nl > 1)
+   {
+      hypre_ParCSRMatrix *Ac = A_array[nl - 1];
+      HYPRE_Int N = (HYPRE_Int) hypre_ParCSRMatrixGlobalNumRows(Ac);
+      HYPRE_Int np;
+      if (!hypre_ParAMGDataGSSetup(amg_data)) { hypre_GaussElimSetup(amg_data, nl - 1, grt[3]); }
+      hypre_MPI_Comm_size(hypre_ParCSRMatrixComm(Ac), &np);
+      if (b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data),
+                                    (int) hypre_ParCSRMatrixFirstRowIndex(Ac),
+                                    np > 1 ? hypre_ParAMGDataCommInfo(amg_data) : NULL) != B200_OK)
+      {
+         b200_amg_destroy(amg); return NULL;
+      }
+   }
+   if (b200_amg_finalize(amg) != B200_OK) { b200_amg_destroy(amg); return NULL; }
+   if (verbose())
+   {
+      double bytes = 0.0;
+      b200_amg_cycle_bytes(amg, &bytes);
+      fprintf(stderr, "hypre_b200: uploaded %d-level hierarchy, %.3f MB algorithmic bytes per cycle\n",
+              (int) nl, bytes * 1e-6);
+   }
+   return amg;
+}
+
+/* --------------------------------------------------------- interposition */
+typedef HYPRE_Int (*pcg_solve_fn)(void *, void *, void *, void *);
+typedef HYPRE_Int (*amg_setup_fn)(void *, hypre_ParCSRMatrix *, hypre_ParVector *, hypre_ParVector *);
+typedef HYPRE_Int (*amg_destroy_fn)(void *);
+typedef HYPRE_Int (*mat_destroy_fn)(hypre_ParCSRMatrix *);
+
+static void *next_sym(const char *name)
+{
+   void *p = dlsym(RTLD_NEXT, name);
+   if (!p) { fprintf(stderr, "hypre_b200: reference symbol %s not found\n", name); abort(); }
+   return p;
+}
+
+/* A new setup invalidates the device mirror of that solver's hierarchy. */
+HYPRE_Int hypre_BoomerAMGSetup(void *amg_vdata, hypre_ParCSRMatrix *A, hypre_ParVector *f, hypre_ParVector *u)
+{
+   static amg_setup_fn next = NULL;
+   if (!next) { next = (amg_setup_fn) next_sym("hypre_BoomerAMGSetup"); }
+   mirror_drop(amg_vdata);
+   return next(amg_vdata, A, f, u);
+}
+
+HYPRE_Int hypre_BoomerAMGDestroy(void *amg_vdata)
+{
+   static amg_destroy_fn next = NULL;
+   if (!next) { next = (amg_destroy_fn) next_sym("hypre_BoomerAMGDestroy"); }
+   mirror_drop(amg_vdata);
+   return next(amg_vdata);
+}
+
+HYPRE_Int hypre_ParCSRMatrixDestroy(hypre_ParCSRMatrix *A)
+{
+   static mat_destroy_fn next = NULL;
+   if (!next) { next = (mat_destroy_fn) next_sym("hypre_ParCSRMatrixDestroy"); }
+   if (A) { mirror_drop(A); }
+   return next(A);
+}
+
+static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
+{
+   mirror_t *m = mirror_find(amg_data);
+   if (m) { return m; }
+   {
+      b200_amg *amg = upload_amg(amg_data);
+      if (!amg) { return NULL; }
+      m = (mirror_t *) calloc(1, sizeof(mirror_t));
+      m->key = amg_data; m->amg = amg;
+      b200_amg_level_matrix(amg, 0, &m->A);
+      m->next = g_mirrors; g_mirrors = m;
+   }
+   return m;
+}
+
+static mirror_t *mirror_for_matrix(hypre_ParCSRMatrix *A)
+{
+   mirror_t *m = mirror_find(A);
+   if (m) { return m; }
+   {
+      b200_parcsr *dA = glue_ctx() ? upload_parcsr(A) : NULL;
+      if (!dA) { return NULL; }
+      m = (mirror_t *) calloc(1, sizeof(mirror_t));
+      m->key = A; m->A = dA;
+      m->next = g_mirrors; g_mirrors = m;
+   }
+   return m;
+}
+
+/* hypre_PCGSolve (src/krylov/pcg.c:317-1008) for the ParCSR operator table. */
+HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
+{
+   static pcg_solve_fn next = NULL;
+   hypre_PCGData      *pcg = (hypre_PCGData *) pcg_vdata;
+   hypre_PCGFunctions *fn  = pcg->functions;
+   hypre_ParCSRMatrix *pA  = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector    *pb  = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
+   HYPRE_Int (*precond)(void *, void *, void *, void *) = fn->precond;
+   mirror_t *m = NULL;
+   b200_amg *amg = NULL;
+   b200_pcg_params prm;
+   b200_pcg_result res;
+   HYPRE_Int my_id, num_procs, i;
+   int status;
+
+   if (!next) { next = (pcg_solve_fn) next_sym("hypre_PCGSolve"); }
+   /* other interfaces (struct, sstruct, ...) were never on this path */
+   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(pcg_vdata, A, b, x); }
+
+   memset(&prm, 0, sizeof(prm));
+   if (pcg->rel_change || pcg->recompute_residual || pcg->recompute_residual_p || pcg->stop_crit ||
+       pcg->flex || pcg->rtol != 0.0 || pcg->cf_tol > 0.0 || pcg->atolf > 0.0 ||
+       hypre_ParVectorNumVectors(pb) > 1)
+   {
+      GLUE_FAIL("PCG option outside the device path (rel_change / recompute_residual / stop_crit / flex / rtol / cf_tol / atolf / multivector)");
+      return hypre_error_flag;
+   }
+   if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_BoomerAMGSolve ||
+       precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_BoomerAMGSolve)
+   {
+      hypre_ParAMGData *amg_data = (hypre_ParAMGData *) pcg->precond_data;
+      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) != 1)
+      {
+         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 and max_iter 1");
+         return hypre_error_flag;
+      }
+      if (hypre_ParAMGDataAArray(amg_data) == NULL || hypre_ParAMGDataAArray(amg_data)[0] != pA)
+      {
+         GLUE_FAIL("BoomerAMG was not set up for this matrix");
+         return hypre_error_flag;
+      }
+      m = mirror_for_amg(amg_data);
+      if (!m) { GLUE_FAIL("hierarchy upload failed"); return hypre_error_flag; }
+      amg = m->amg;
+   }
+   else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_ParCSRDiagScale)
+   {
+      prm.diag_scale = 1;
+      m = mirror_for_matrix(pA);
+   }
+   else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_ParKrylovIdentity)
+   {
+      m = mirror_for_matrix(pA);
+   }
+   else
+   {
+      GLUE_FAIL("preconditioner has no device implementation (BoomerAMG, diagonal scaling, identity are supported)");
+      return hypre_error_flag;
+   }
+   if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
+
+   prm.tol = pcg->tol; prm.a_tol = pcg->a_tol; prm.max_iter = pcg->max_iter;
+   prm.two_norm = pcg->two_norm; prm.skip_break = pcg->skip_break;
+   pcg->converged = 0;
+   (*(fn->CommInfo))(A, &my_id, &num_procs);
+
+   status = b200_pcg_solve_host(glue_ctx(), m->A, amg, &prm,
+                                hypre_VectorData(hypre_ParVectorLocalVector(pb)),
+                                hypre_VectorData(hypre_ParVectorLocalVector(px)), &res,
+                                (pcg->logging > 0 || pcg->print_level > 0) ? pcg->norms : NULL,
+                                (pcg->logging > 0 || pcg->print_level > 0) ? pcg->rel_norms : NULL);
+   if (status != B200_OK) { GLUE_FAIL("device PCG failed"); return hypre_error_flag; }
+
+   /* the reference's printed table (pcg.c:405-409,536-560,772-792,983-986) */
+   if (pcg->print_level > 1 && my_id == 0)
+   {
+      hypre_printf(pcg->two_norm ? "<b,b>: %e\n" : "<C*b,b>: %e\n", res.bi_prod);
+      if (res.error_flag != 1 && res.bi_prod > 0.0)
+      {
+         hypre_printf("\n\n");
+         if (pcg->two_norm)
+         {
+            hypre_printf("Iters       ||r||_2     conv.rate  ||r||_2/||b||_2\n");
+            hypre_printf("-----    ------------   ---------  ------------ \n");
+         }
+         else
+         {
+            hypre_printf("Iters       ||r||_C     conv.rate  ||r||_C/||b||_C\n");
+            hypre_printf("-----    ------------    ---------  ------------ \n");
+         }
+         for (i = 1; i <= res.num_iterations; i++)
+         {
+            hypre_printf("% 5d    %e    %f    %e\n", i, pcg->norms[i], pcg->norms[i] / pcg->norms[i - 1],
+                         pcg->rel_norms[i]);
+         }
+         hypre_printf("\n\n");
+      }
+   }
+   if (res.error_flag == 1)
+   {
+      if (pcg->print_level > 0 || pcg->logging > 0)
+      {
+         hypre_printf("\n\nERROR detected by Hypre ...  BEGIN\n");
+         hypre_printf("ERROR -- hypre_PCGSolve: INFs and/or NaNs detected in input.\n");
+         hypre_printf("Returning error flag += 101.  Program not terminated.\n");
+         hypre_printf("ERROR detected by Hypre ...  END\n\n\n");
+      }
+      hypre_error(HYPRE_ERROR_GENERIC);
+      return hypre_error_flag;
+   }
+   if (res.error_flag & 256) { hypre_error_w_msg(HYPRE_ERROR_CONV, "PCG (B200 path): breakdown or max iterations reached"); }
+   pcg->converged = res.converged;
+   pcg->num_iterations = res.num_iterations;
+   pcg->rel_residual_norm = res.rel_residual_norm;
+   hypre_ParVectorAllZeros(px) = 0;
+   return hypre_error_flag;
+}
+
+/* Public SpMV y = alpha*A*x + beta*y (src/parcsr_mv/HYPRE_parcsr_matrix.c), the call
+ * `ij -solver -1 -nmv N` times (src/test/ij.c:4262-4296).  The matrix is mirrored on the
+ * first call; library-internal hypre_ParCSRMatrixMatvec calls (host setup) are untouched. */
+HYPRE_Int HYPRE_ParCSRMatrixMatvec(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HYPRE_ParVector x,
+                                   HYPRE_Complex beta, HYPRE_ParVector y)
+{
+   hypre_ParCSRMatrix *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector    *px = (hypre_ParVector *) x, *py = (hypre_ParVector *) y;
+   mirror_t *m;
+   if (hypre_ParVectorNumVectors(px) > 1)
+   {
+      GLUE_FAIL("multivector SpMV is outside the device path");
+      return hypre_error_flag;
+   }
+   m = mirror_for_matrix(pA);
+   if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
+   if (b200_parcsr_matvec_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)), beta,
+                               hypre_VectorData(hypre_ParVectorLocalVector(py)),
+                               hypre_VectorData(hypre_ParVectorLocalVector(py))) != B200_OK)
+   {
+      GLUE_FAIL("device SpMV failed");
+   }
+   hypre_ParVectorAllZeros(py) = 0;
+   return hypre_error_flag;
+}
+
+/* handles for tests / bench (python ctypes) */
+b200_amg *hypre_b200_amg_mirror(void *amg_vdata)
+{
+   mirror_t *m = mirror_for_amg((hypre_ParAMGData *) amg_vdata);
+   return m ? m->amg : NULL;
+}
+b200_parcsr *hypre_b200_matrix_mirror(void *parcsr)
+{
+   mirror_t *m = mirror_for_matrix((hypre_ParCSRMatrix *) parcsr);
+   return m ? m->A : NULL;
+}

@@ -1,0 +1,213 @@
+/* b200amg.h -- C ABI of the B200 (sm_100a) BoomerAMG-PCG solve phase.
+ *
+ * Plain C types only: opaque handles, host pointers (suffix _h / "host"),
+ * DEVICE pointers (double* documented as "dev"), ints and doubles.  Every
+ * function returns B200_OK (0) or a negative B200_ERR_* code; the text of the
+ * last error is available from b200_last_error().  There is NO CPU fallback in
+ * this library: without a CUDA device every entry point that computes fails
+ * with B200_ERR_CUDA.
+ *
+ * Each entry point names the reference (hypre 2.32.0, paths under src/) routine
+ * whose solve-phase work it replaces.  Index type = int (HYPRE_Int), values =
+ * double (HYPRE_Real), see src/utilities/HYPRE_utilities.h:35-61,105,131.
+ */
+#ifndef B200AMG_H
+#define B200AMG_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK               0
+#define B200_ERR_CUDA        -1
+#define B200_ERR_ARG         -2
+#define B200_ERR_NCCL        -3
+#define B200_ERR_UNSUPPORTED -4
+#define B200_ERR_NUMERIC     -5   /* zero diagonal, NaN/Inf input, ... */
+
+typedef struct b200_ctx    b200_ctx;     /* device + streams + (optional) NCCL communicator */
+typedef struct b200_parcsr b200_parcsr;  /* device mirror of hypre_ParCSRMatrix             */
+typedef struct b200_amg    b200_amg;     /* device mirror of hypre_ParAMGData (solve part)  */
+
+const char *b200_last_error(void);
+int  b200_version(void);
+
+/* ------------------------------------------------------------------ context
+ * One context per process = one GPU (the reference binds one MPI rank to one
+ * device: src/utilities/device_utils.c:3008-3068; compute stream =
+ * hypre_HandleComputeStream, src/utilities/device_utils.h:252-269).
+ * b200_ctx_create_dist joins an NCCL communicator (replaces the MPI_Comm of
+ * hypre_ParCSRMatrixComm for the solve phase); uid = 128-byte ncclUniqueId
+ * produced by b200_nccl_unique_id on rank 0 and broadcast by the caller. */
+int b200_ctx_create(int device, b200_ctx **ctx);
+int b200_nccl_unique_id(char uid[128]);
+int b200_ctx_create_dist(int device, int rank, int nranks, const char uid[128], b200_ctx **ctx);
+int b200_ctx_destroy(b200_ctx *ctx);
+int b200_ctx_sync(b200_ctx *ctx);
+int b200_ctx_rank(const b200_ctx *ctx, int *rank, int *nranks);
+/* number of kernels this library launched on ctx since creation */
+long long b200_ctx_launch_count(const b200_ctx *ctx);
+/* CUDA-event timing on the library's own compute stream (ms) */
+int b200_timer_start(b200_ctx *ctx);
+int b200_timer_stop(b200_ctx *ctx, float *ms);
+/* write `bytes` of scratch (evicts L2 between timed iterations) */
+int b200_flush_l2(b200_ctx *ctx);
+
+/* ------------------------------------------------------------ device memory
+ * hypre_TAlloc/hypre_TFree/hypre_TMemcpy(…, HYPRE_MEMORY_DEVICE)
+ * (src/utilities/memory.c:817-842) for vectors of doubles. */
+int b200_dev_alloc(b200_ctx *ctx, long long n, double **dev);
+int b200_dev_free(b200_ctx *ctx, double *dev);
+int b200_h2d(b200_ctx *ctx, double *dev, const double *host, long long n);
+int b200_d2h(b200_ctx *ctx, double *host, const double *dev, long long n);
+
+/* ------------------------------------------------------------ BLAS-1 (dev)
+ * hypre_SeqVectorSetConstantValues / Copy / Scale / Axpy / InnerProd
+ * (src/seq_mv/vector.c:350-386,435-460,652-689,722-749,1069-1097) and
+ * hypre_ParVectorInnerProd = local dot + Allreduce (src/parcsr_mv/par_vector.c:513-533). */
+int b200_vec_fill(b200_ctx *ctx, int n, double a, double *y);
+int b200_vec_copy(b200_ctx *ctx, int n, const double *x, double *y);
+int b200_vec_scale(b200_ctx *ctx, int n, double a, double *y);
+int b200_vec_axpy(b200_ctx *ctx, int n, double a, const double *x, double *y);
+int b200_vec_dot(b200_ctx *ctx, int n, const double *x, const double *y, double *result_h);
+
+/* ------------------------------------------------------------------ ParCSR
+ * Device mirror of hypre_ParCSRMatrix (src/parcsr_mv/par_csr_matrix.h:27-84):
+ * diag (n_rows x n_cols_diag) and offd (n_rows x n_cols_offd, compressed
+ * columns) CSR blocks, plus the halo plan of hypre_ParCSRCommPkg
+ * (src/parcsr_mv/par_csr_communication.h:51-75).  All arrays are HOST arrays
+ * and are copied; offd_* and the comm arrays may be NULL when n_cols_offd == 0
+ * / num_sends == num_recvs == 0 (single rank). */
+int b200_parcsr_create(b200_ctx *ctx,
+                       int n_rows, int n_cols_diag,
+                       const int *diag_i, const int *diag_j, const double *diag_a,
+                       int n_cols_offd,
+                       const int *offd_i, const int *offd_j, const double *offd_a,
+                       int num_sends, const int *send_procs, const int *send_map_starts,
+                       const int *send_map_elmts,
+                       int num_recvs, const int *recv_procs, const int *recv_vec_starts,
+                       b200_parcsr **A);
+int b200_parcsr_destroy(b200_parcsr *A);
+int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *nnz,
+                     int *layout /* 0 = CSR-vector, 1 = sliced-ELL */, int *lanes_per_row);
+/* force the storage layout chosen for the diag block (tests/bench): -1 auto */
+int b200_set_layout_override(int layout, int lanes_per_row);
+
+/* y = alpha*A*x + beta*b   (dev pointers; y may alias b, must not alias x)
+ * hypre_ParCSRMatrixMatvecOutOfPlace (src/parcsr_mv/par_csr_matvec.c:20-265)
+ * over hypre_CSRMatrixMatvecOutOfPlace (src/seq_mv/csr_matvec.c:21-891). */
+int b200_parcsr_matvec(b200_parcsr *A, double alpha, const double *x,
+                       double beta, const double *b, double *y);
+/* y = alpha*A^T*x + beta*y
+ * hypre_ParCSRMatrixMatvecT (src/parcsr_mv/par_csr_matvec.c:287-546); the
+ * explicit transpose is built once on first use (the reference transposes on
+ * every call on its GPU path, src/seq_mv/csr_spmv_device.c:424-427). */
+int b200_parcsr_matvecT(b200_parcsr *A, double alpha, const double *x,
+                        double beta, double *y);
+/* Same as b200_parcsr_matvec with HOST vectors: copies x (and b) to the device,
+ * runs the kernel, copies y back.  This is the call the reference-facing
+ * HYPRE_ParCSRMatrixMatvec binding makes for host-resident hypre vectors. */
+int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const double *x_h,
+                            double beta, const double *b_h, double *y_h);
+
+/* --------------------------------------------------------------- smoothers
+ * One sweep each, dev pointers.  `tmp` arguments are caller-provided work
+ * vectors of length n_rows.  zero_guess != 0 promises u == 0 on entry (the
+ * reference's hypre_ParVectorAllZeros flag, src/parcsr_mv/par_vector.h:24-44). */
+
+/* relax_type 18 (and 7): u += w*(f - A u) ./ l1
+ * hypre_BoomerAMGRelax7Jacobi (src/parcsr_ls/par_relax.c:1177-1254). */
+int b200_relax_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
+                        double *u, double *tmp, int zero_guess);
+/* relax_type 16: hypre_ParCSRRelax_Cheby_SolveHost (src/parcsr_ls/par_cheby.c:224-385).
+ * coefs_h = HOST array of order+1 coefficients... only the first `order` are used
+ * exactly as the reference does (cheby_order = order-1). */
+int b200_relax_cheby(b200_parcsr *A, const double *f, const double *ds, const double *coefs_h,
+                     int order, int scale, double *u, double *v, double *r, double *tmp,
+                     int zero_guess);
+/* relax_type 11 (inner=1) / 12 (inner=2):
+ * hypre_BoomerAMGRelaxTwoStageGaussSeidelHost (src/parcsr_ls/par_relax.c:1505-1588).
+ * Returns B200_ERR_NUMERIC if a diagonal entry is zero (reference: hypre_error_in_arg(1)). */
+int b200_relax_2stage_gs(b200_parcsr *A, const double *f, double w, int inner,
+                         double *u, double *z, double *tmp, int zero_guess);
+
+/* --------------------------------------------------------------- hierarchy
+ * Device mirror of the solve-phase fields of hypre_ParAMGData
+ * (src/parcsr_ls/par_amg.h:20-300).  The hierarchy is produced by the
+ * reference's host setup and uploaded once. */
+int b200_amg_create(b200_ctx *ctx, int num_levels, b200_amg **amg);
+int b200_amg_destroy(b200_amg *amg);
+/* A_array[level]; P_array[level] (NULL on the coarsest level).  The amg object
+ * takes ownership of A and P. */
+int b200_amg_set_level(b200_amg *amg, int level, b200_parcsr *A, b200_parcsr *P);
+/* grid_relax_type[1..3], num_grid_sweeps[1..3] (index = cycle_param: 1 down,
+ * 2 up, 3 coarsest), cycle_type (1 = V, 2 = W), fcycle */
+int b200_amg_set_cycle(b200_amg *amg, const int relax_type[4], const int num_sweeps[4],
+                       int cycle_type, int fcycle);
+/* per-level smoother data (HOST arrays, copied):
+ * l1_norms[level] (relax 18/7: l1 row norms; 11/12: the diagonal), relax_weight[level] */
+int b200_amg_set_level_relax(b200_amg *amg, int level, double relax_weight,
+                             const double *l1_norms_h);
+/* cheby_ds[level], cheby_coefs[level], cheby_order, cheby_scale
+ * (src/parcsr_ls/par_cheby.c:57-206) */
+int b200_amg_set_level_cheby(b200_amg *amg, int level, const double *ds_h,
+                             const double *coefs_h, int order, int scale);
+/* coarsest level, relax_type 9: the replicated dense N x N matrix A_mat (row
+ * major) of hypre_GaussElimSetup (src/parcsr_ls/par_gauss_elim.c:32-454), this
+ * rank's first row and the per-rank row counts for the gather. */
+int b200_amg_set_coarse_dense(b200_amg *amg, int n_global, const double *A_mat_h,
+                              int first_row, const int *rows_per_rank_h);
+/* finalise: allocates F/U/work vectors, builds transposes and the launch plan */
+int b200_amg_finalize(b200_amg *amg);
+/* one multigrid cycle u <- u + B(f - A u)   (dev pointers, level-0 size)
+ * hypre_BoomerAMGCycle (src/parcsr_ls/par_cycle.c:22-803).  zero_guess as above. */
+int b200_amg_cycle(b200_amg *amg, const double *f, double *u, int zero_guess);
+/* algorithmic HBM bytes of one cycle, from the uploaded level sizes */
+int b200_amg_cycle_bytes(const b200_amg *amg, double *bytes);
+/* borrowed handle to A_array[level] / P_array[level] (owned by amg) */
+int b200_amg_level_matrix(const b200_amg *amg, int level, b200_parcsr **A);
+int b200_amg_level_interp(const b200_amg *amg, int level, b200_parcsr **P);
+int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *nnz_A,
+                        long long *nnz_P);
+/* stand-alone AMG iteration (ij -solver 0): hypre_BoomerAMGSolve
+ * (src/parcsr_ls/par_amg_solve.c:21-424) with converge_type 0. */
+int b200_amg_solve(b200_amg *amg, const double *b, double *x, double tol, int min_iter,
+                   int max_iter, int *num_iterations, double *rel_resid_norm);
+
+/* --------------------------------------------------------------------- PCG
+ * hypre_PCGSolve (src/krylov/pcg.c:317-1008) with the ParCSR operator table
+ * (src/parcsr_ls/par_krylov_func.c:14-330).  amg == NULL -> no preconditioner
+ * (identity), amg != NULL -> one b200_amg_cycle per iteration
+ * (HYPRE_BoomerAMGSolve with tol 0, max_iter 1).  b, x are dev pointers;
+ * norms_h / rel_norms_h (HOST, length max_iter+1, may be NULL) receive the
+ * history the reference logs (pcg.c:767-771). */
+typedef struct {
+   double tol;        /* r_tol  */
+   double a_tol;      /* absolute tolerance */
+   int    max_iter;
+   int    two_norm;
+   int    skip_break; /* pcg.c:581-629 */
+   int    diag_scale; /* 1: preconditioner = diagonal scaling (HYPRE_ParCSRDiagScale) when amg == NULL */
+} b200_pcg_params;
+
+typedef struct {
+   int    num_iterations;
+   int    converged;
+   int    error_flag;      /* HYPRE_ERROR_CONV (256) semantics: 0 or 256 */
+   double rel_residual_norm;
+   double bi_prod;
+} b200_pcg_result;
+
+int b200_pcg_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_pcg_params *prm,
+                   const double *b, double *x, b200_pcg_result *res,
+                   double *norms_h, double *rel_norms_h);
+/* same with HOST b/x: H2D of b and x, device solve, D2H of x (end-to-end call
+ * made by the hypre_PCGSolve binding for host-resident hypre vectors) */
+int b200_pcg_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_pcg_params *prm,
+                        const double *b_h, double *x_h, b200_pcg_result *res,
+                        double *norms_h, double *rel_norms_h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AMG_H */
