@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py -- AMG-PCG solve throughput (DOF*iterations/s) of the B200 solve phase.
+
+Workload (BASELINE.json configs[2], the largest AMG-PCG case that fits one GPU):
+    ij -laplacian -n 256 256 256 -solver 1 -rlx 16   (7-pt Laplacian, 16.8M DOF,
+    HMIS + ext+i, Chebyshev smoother, PCG to 1e-8, rhs = ones, x0 = 0)
+One "step" = one complete HYPRE_PCGSolve.  The AMG setup runs once, outside the timed
+region, in the reference's host code (north star) and the hierarchy is uploaded once.
+
+    value : device-resident solve (b, x in HBM; CUDA events on the library's stream)
+    e2e   : HYPRE_ParCSRPCGSolve through the interposed C API with HOST vectors
+            (pinned): H2D of b and x0 and D2H of x inside the timed region, wall clock
+    --impl reference : the reference's own CPU hypre_PCGSolve (oracle/_ref) on the host
+            cores, each step a bounded sample (PCG capped at --ref-iters iterations)
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (generator, args, relax_type, ij command line)
+    "lap7_256_cheby": ("laplacian", (256, 256, 256), 16, "ij -laplacian -n 256 256 256 -solver 1 -rlx 16"),
+    "lap7_256_l1jac": ("laplacian", (256, 256, 256), 18, "ij -laplacian -n 256 256 256 -solver 1 -rlx 18"),
+    "lap7_100_l1jac": ("laplacian", (100, 100, 100), 18, "ij -laplacian -n 100 100 100 -solver 1 -rlx 18"),
+    "lap27_128_gs11": ("laplacian_27pt", (128, 128, 128), 11, "ij -27pt -n 128 128 128 -solver 1 -rlx 11"),
+    "lap7_64_cheby": ("laplacian", (64, 64, 64), 16, "ij -laplacian -n 64 64 64 -solver 1 -rlx 16"),
+}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device=0):
+        self.rows, self.proc, self.device = [], None, device
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for k, nm in enumerate(names):
+                    if r[2 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_problem(H, name, nscale=None):
+    gen, dims, rlx, cmd = WORKLOADS[name]
+    if nscale:
+        dims = tuple(nscale for _ in dims)
+        cmd = cmd + " [scaled to n=%d]" % nscale
+    A = getattr(H, gen)(*dims)
+    b = A.vector(1.0)
+    x = A.vector(0.0)
+    amg = H.BoomerAMG(relax_type=rlx)
+    pcg = H.ParCSRPCG(tol=1e-8, max_iter=100, two_norm=1, print_level=0, logging=1)
+    pcg.SetPrecond(amg)
+    t0 = time.perf_counter()
+    pcg.Setup(A, b, x)        # reference host setup (coarsening, interpolation, RAP)
+    return dict(A=A, b=b, x=x, amg=amg, pcg=pcg, rlx=rlx, cmd=cmd, setup_s=time.perf_counter() - t0)
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU hypre_PCGSolve on the host cores."""
+    if rank != 0:
+        return
+    from hypre_b200 import hypre as H
+    H.set_device_path(False)
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
+    P = build_problem(H, args.workload, args.n)
+    n = P["A"].global_rows
+    P["pcg"].SetMaxIter(args.ref_iters)
+    xs = P["x"].numpy()
+    times, iters = [], 0
+    for s in range(args.warmup + args.steps):
+        xs[:] = 0.0
+        P["x"].set_all_zeros_flag(0)
+        H.clear_errors()
+        t0 = time.perf_counter()
+        P["pcg"].Solve(P["A"], P["b"], P["x"])
+        dt = time.perf_counter() - t0
+        iters = P["pcg"].num_iterations
+        if s >= args.warmup:
+            times.append(dt)
+    tot = sum(times)
+    value = n * iters * len(times) / tot
+    sample = "%s, PCG capped at %d iterations per step, %d OpenMP threads" % (P["cmd"], args.ref_iters, ncores)
+    out = {
+        "impl": "reference", "metric": "AMG-PCG solve DOF*iterations/s", "value": value, "unit": "DOF*it/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "l2": "inputs larger than L2"},
+        "cpu_baseline": {"value": value, "unit": "DOF*it/s", "cores": ncores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "DOF*it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "setup_s": P["setup_s"],
+    }
+    print(json.dumps(out))
+
+
+def run_b200(args, rank, world):
+    from hypre_b200 import capi, hypre as H
+    L = capi.lib()
+    if world > 1:
+        raise SystemExit("multi-GPU bench path not wired in this build (see DESIGN.md, section multi-GPU)")
+    ncores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
+    P = build_problem(H, args.workload, args.n)
+    A, b, x, amg, pcg = P["A"], P["b"], P["x"], P["amg"], P["pcg"]
+    n = A.global_rows
+    HL = H.lib()
+    ctx = C.c_void_p(HL.hypre_b200_context())
+    if not ctx:
+        raise capi.B200Error("no CUDA device: " + L.b200_last_error().decode())
+    t0 = time.perf_counter()
+    damg = amg.device_mirror()          # one-time upload of the hierarchy
+    upload_s = time.perf_counter() - t0
+    dA = C.c_void_p()
+    capi.check(L.b200_amg_level_matrix(damg, 0, C.byref(dA)))
+    cyc_bytes = C.c_double()
+    capi.check(L.b200_amg_cycle_bytes(damg, C.byref(cyc_bytes)))
+    nnz0 = C.c_longlong(); nrows = C.c_int(); layout = C.c_int(); lanes = C.c_int()
+    capi.check(L.b200_parcsr_info(dA, C.byref(nrows), None, C.byref(nnz0), C.byref(layout), C.byref(lanes)))
+    nnz0 = nnz0.value
+
+    # ---------------- value: device-resident solve, CUDA events on the library's stream
+    db = capi.DeviceVector(ctx, n, b.numpy())
+    dx = capi.DeviceVector(ctx, n)
+    prm = capi.PcgParams(tol=1e-8, a_tol=0.0, max_iter=100, two_norm=1, skip_break=0, diag_scale=0)
+    res = capi.PcgResult()
+    norms = np.zeros(101); rel = np.zeros(101)
+
+    def dev_solve():
+        capi.check(L.b200_vec_fill(ctx, n, 0.0, dx.ptr))
+        capi.check(L.b200_pcg_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
+                                    capi.ptr(norms), capi.ptr(rel)))
+    for _ in range(args.warmup):
+        dev_solve()
+    sampler = ClockSampler()
+    sampler.start()
+    l0 = L.b200_ctx_launch_count(ctx)
+    ms = C.c_float()
+    capi.check(L.b200_ctx_sync(ctx))
+    capi.check(L.b200_timer_start(ctx))
+    for _ in range(args.steps):
+        dev_solve()
+    capi.check(L.b200_timer_stop(ctx, C.byref(ms)))
+    capi.check(L.b200_ctx_sync(ctx))
+    launches = L.b200_ctx_launch_count(ctx) - l0
+    iters = res.num_iterations
+    dev_s = ms.value * 1e-3
+    value = n * iters * args.steps / dev_s
+
+    # ---------------- e2e: HYPRE_ParCSRPCGSolve with host vectors (pinned once, like a user would)
+    bh, xh = b.numpy(), x.numpy()
+    L.b200_host_pin(capi.ptr(bh), bh.nbytes)
+    L.b200_host_pin(capi.ptr(xh), xh.nbytes)
+    H.set_device_path(True)
+
+    def api_solve():
+        xh[:] = 0.0
+        H.clear_errors()
+        pcg.Solve(A, b, x)
+    for _ in range(max(1, args.warmup)):
+        api_solve()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        api_solve()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    e2e_iters = pcg.num_iterations
+    e2e_value = n * e2e_iters * args.steps / e2e_s
+    api_rel = pcg.rel_norms()
+
+    # ---------------- roofline: the level-0 SpMV of the PCG loop (s = A p), timed live
+    peak, peak_src = measured_peaks()
+    dp = capi.DeviceVector(ctx, n, np.sin(np.arange(n)) * 1e-3 + 1.0)
+    ds_ = capi.DeviceVector(ctx, n)
+    reps = 20
+    for _ in range(3):
+        capi.check(L.b200_parcsr_matvec(dA, 1.0, dp.ptr, 0.0, None, ds_.ptr))
+    capi.check(L.b200_timer_start(ctx))
+    for _ in range(reps):
+        capi.check(L.b200_parcsr_matvec(dA, 1.0, dp.ptr, 0.0, None, ds_.ptr))
+    capi.check(L.b200_timer_stop(ctx, C.byref(ms)))
+    spmv_ms = ms.value / reps
+    spmv_bytes = 12.0 * nnz0 + 4.0 * (n + 1) + 8.0 * n + 8.0 * n
+    spmv_gbs = spmv_bytes / (spmv_ms * 1e-3) / 1e9
+    # whole-iteration view: algorithmic bytes of one PCG iteration / time of one iteration
+    iter_bytes = cyc_bytes.value + spmv_bytes + 8.0 * n * (4 + 2 + 3)   # update (4 streams+..), dot, direction
+    iter_gbs = iter_bytes * iters * args.steps / dev_s / 1e9
+
+    # ---------------- cpu_baseline: the reference's CPU PCG on this box, bounded sample
+    cpu = None
+    if not args.no_cpu_baseline:
+        H.set_device_path(False)
+        pcg.SetMaxIter(args.ref_iters)
+        xh[:] = 0.0
+        H.clear_errors()
+        t0 = time.perf_counter()
+        pcg.Solve(A, b, x)
+        dt = time.perf_counter() - t0
+        cpu = {"value": n * pcg.num_iterations / dt, "unit": "DOF*it/s", "cores": ncores, "kind": "reference",
+               "sample": "%s capped at %d PCG iterations, 1 solve, %d OpenMP threads (oracle/_ref/libHYPRE_ref.so)"
+                         % (P["cmd"], args.ref_iters, ncores)}
+        H.clear_errors()
+        H.set_device_path(True)
+
+    out = {
+        "metric": "AMG-PCG solve DOF*iterations/s", "value": value, "unit": "DOF*it/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "levels": amg.num_levels,
+                   "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration)" % (iter_bytes / 1e9),
+                   "final_rel_residual": float(rel[iters]), "level0_layout": "sliced-ELL" if layout.value == 1 else
+                   "CSR-vector/%d" % lanes.value},
+        "e2e": {"value": e2e_value, "unit": "DOF*it/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 8 * n,
+                "iterations_per_step": e2e_iters, "ms_per_step": 1e3 * e2e_s / args.steps,
+                "final_rel_residual": float(api_rel[-1]) if len(api_rel) else None},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "rows_kernel (level-0 SpMV y=A*x, %.1f MB algorithmic)" % (spmv_bytes / 1e6),
+                     "achieved": spmv_gbs, "peak": peak, "unit": "GB/s", "frac": spmv_gbs / peak, "traffic": None,
+                     "peak_source": peak_src, "frac_of_8000": spmv_gbs / 8000.0, "ms_per_launch": spmv_ms,
+                     "pcg_iteration_gbs": iter_gbs, "pcg_iteration_frac": iter_gbs / peak,
+                     "pcg_iteration_bytes": iter_bytes},
+        "cpu_baseline": cpu, "clocks": clocks,
+        "setup_s": P["setup_s"], "upload_s": upload_s,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="lap7_256_cheby", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=None, help="override the grid edge (scaled-down smoke runs)")
+    ap.add_argument("--ref-iters", type=int, default=3, help="PCG iterations per reference step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_b200(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -71,7 +71,16 @@ struct b200_ctx {
    double      *h_stage = nullptr;
    size_t       h_stage_n = 0;
    bool         capturing = false;
+   // cached device work vectors (PCG p/s/r, host-entry b/x, ...): grown on demand, never
+   // freed before the context dies, so repeated solves do not pay cudaMalloc/cudaFree
+   static constexpr int NUM_WS = 12;
+   double      *ws[NUM_WS] = {nullptr};
+   size_t       ws_n[NUM_WS] = {0};
 };
+
+enum { WS_PCG_P = 0, WS_PCG_S, WS_PCG_R, WS_HOST_B, WS_HOST_X, WS_HOST_Y, WS_AMG_R };
+// device work vector `slot` with at least n doubles
+int ctx_workspace(b200_ctx *c, int slot, size_t n, double **out);
 
 constexpr int B200_NUM_SCALARS = 64;
 

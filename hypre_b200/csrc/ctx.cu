@@ -90,6 +90,7 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    cudaFreeHost(c->h_scalars);
    if (c->d_flush) { cudaFree(c->d_flush); }
    if (c->h_stage) { cudaFreeHost(c->h_stage); }
+   for (int k = 0; k < b200_ctx::NUM_WS; k++) { if (c->ws[k]) { cudaFree(c->ws[k]); } }
    cudaEventDestroy(c->ev_pack); cudaEventDestroy(c->ev_halo);
    cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);
    cudaStreamDestroy(c->stream); cudaStreamDestroy(c->cstream);
@@ -144,6 +145,33 @@ extern "C" int b200_flush_l2(b200_ctx *c)
 }
 
 // ---------------------------------------------------------------- memory
+int ctx_workspace(b200_ctx *c, int slot, size_t n, double **out)
+{
+   if (n == 0) { n = 1; }
+   if (c->ws_n[slot] < n)
+   {
+      if (c->ws[slot]) { CUDA_TRY(cudaStreamSynchronize(c->stream)); CUDA_TRY(cudaFree(c->ws[slot])); c->ws[slot] = nullptr; c->ws_n[slot] = 0; }
+      CUDA_TRY(cudaMalloc((void **)&c->ws[slot], sizeof(double) * n));
+      c->ws_n[slot] = n;
+   }
+   *out = c->ws[slot];
+   return B200_OK;
+}
+
+// page-lock a host array the caller owns (hypre vectors are plain malloc memory) so that
+// the H2D/D2H copies of the host-vector entry points run at full PCIe speed
+extern "C" int b200_host_pin(void *host, long long bytes)
+{
+   ARG_CHECK(host != nullptr && bytes > 0);
+   CUDA_TRY(cudaHostRegister(host, (size_t)bytes, cudaHostRegisterDefault));
+   return B200_OK;
+}
+extern "C" int b200_host_unpin(void *host)
+{
+   ARG_CHECK(host != nullptr);
+   CUDA_TRY(cudaHostUnregister(host));
+   return B200_OK;
+}
 extern "C" int b200_dev_alloc(b200_ctx *c, long long n, double **dev)
 {
    ARG_CHECK(c != nullptr && dev != nullptr && n >= 0);

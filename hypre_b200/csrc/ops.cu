@@ -295,15 +295,6 @@ extern "C" int b200_relax_2stage_gs(b200_parcsr *A, const double *f, double w, i
    return op_gs2(A, f, w, inner, u, z, tmp, zero_guess);
 }
 
-static int ensure_stage(b200_ctx *c, size_t n)
-{
-   if (c->h_stage_n >= n) { return B200_OK; }
-   if (c->h_stage) { CUDA_TRY(cudaFreeHost(c->h_stage)); c->h_stage = nullptr; c->h_stage_n = 0; }
-   CUDA_TRY(cudaMallocHost((void **)&c->h_stage, sizeof(double) * n));
-   c->h_stage_n = n;
-   return B200_OK;
-}
-
 // host-vector SpMV: what HYPRE_ParCSRMatrixMatvec costs end to end for host-resident
 // hypre vectors (H2D x [, b], kernel, D2H y).
 extern "C" int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const double *x_h, double beta,
@@ -311,11 +302,9 @@ extern "C" int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const doubl
 {
    ARG_CHECK(A != nullptr && x_h != nullptr && y_h != nullptr && (beta == 0.0 || b_h != nullptr));
    b200_ctx *c = A->ctx;
-   static thread_local double *dx = nullptr, *dy = nullptr;
-   static thread_local long long cap_x = 0, cap_y = 0;
-   if (cap_x < A->n_cols_diag) { if (dx) { cudaFree(dx); } B200_TRY(b200_dev_alloc(c, A->n_cols_diag, &dx)); cap_x = A->n_cols_diag; }
-   if (cap_y < A->n_rows) { if (dy) { cudaFree(dy); } B200_TRY(b200_dev_alloc(c, A->n_rows, &dy)); cap_y = A->n_rows; }
-   (void)ensure_stage;
+   double *dx = nullptr, *dy = nullptr;
+   B200_TRY(ctx_workspace(c, WS_HOST_X, A->n_cols_diag, &dx));
+   B200_TRY(ctx_workspace(c, WS_HOST_Y, A->n_rows, &dy));
    CUDA_TRY(cudaMemcpyAsync(dx, x_h, sizeof(double) * (size_t)A->n_cols_diag, cudaMemcpyHostToDevice, c->stream));
    if (beta != 0.0)
    {

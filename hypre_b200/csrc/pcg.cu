@@ -93,9 +93,9 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
    memset(res, 0, sizeof(*res));
 
    double *p = nullptr, *s = nullptr, *r = nullptr;
-   B200_TRY(b200_dev_alloc(c, n, &p));
-   B200_TRY(b200_dev_alloc(c, n, &s));
-   B200_TRY(b200_dev_alloc(c, n, &r));
+   B200_TRY(ctx_workspace(c, WS_PCG_P, n, &p));
+   B200_TRY(ctx_workspace(c, WS_PCG_S, n, &s));
+   B200_TRY(ctx_workspace(c, WS_PCG_R, n, &r));
    int status = B200_OK;
    int i = 0;
    double bi_prod = 0.0, i_prod = 0.0, i_prod_0 = 0.0, gamma = 0.0, gamma_old = 0.0, eps = 0.0;
@@ -209,7 +209,6 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
 done:
 #undef PCG_TRY
    cudaStreamSynchronize(c->stream);
-   b200_dev_free(c, p); b200_dev_free(c, s); b200_dev_free(c, r);
    return status;
 }
 
@@ -220,12 +219,10 @@ extern "C" int b200_pcg_solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg, c
    ARG_CHECK(c != nullptr && A != nullptr && b_h != nullptr && x_h != nullptr);
    const int n = A->n_rows;
    double *b = nullptr, *x = nullptr;
-   B200_TRY(b200_dev_alloc(c, n, &b));
-   B200_TRY(b200_dev_alloc(c, n, &x));
-   int s = b200_h2d(c, b, b_h, n);
-   if (s == B200_OK) { s = b200_h2d(c, x, x_h, n); }
-   if (s == B200_OK) { s = b200_pcg_solve(c, A, amg, prm, b, x, res, norms_h, rel_norms_h); }
-   if (s == B200_OK) { s = b200_d2h(c, x_h, x, n); }
-   b200_dev_free(c, b); b200_dev_free(c, x);
-   return s;
+   B200_TRY(ctx_workspace(c, WS_HOST_B, n, &b));
+   B200_TRY(ctx_workspace(c, WS_HOST_X, n, &x));
+   CUDA_TRY(cudaMemcpyAsync(b, b_h, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+   CUDA_TRY(cudaMemcpyAsync(x, x_h, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+   B200_TRY(b200_pcg_solve(c, A, amg, prm, b, x, res, norms_h, rel_norms_h));
+   return b200_d2h(c, x_h, x, n);
 }

@@ -36,6 +36,12 @@
 /* ------------------------------------------------------------------ state */
 static b200_ctx *g_ctx = NULL;
 static int g_verbose = -1;
+/* test hook: 0 routes every interposed entry point to the reference (in-process A/B
+ * comparison on the same hierarchy); the product default is 1 and nothing in the
+ * product path ever clears it */
+static int g_enabled = 1;
+void hypre_b200_set_enabled(int enabled) { g_enabled = enabled; }
+int  hypre_b200_get_enabled(void) { return g_enabled; }
 
 typedef struct mirror_s {
    void            *key;      /* hypre_ParAMGData* or hypre_ParCSRMatrix* */
@@ -321,6 +327,7 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
    int status;
 
    if (!next) { next = (pcg_solve_fn) next_sym("hypre_PCGSolve"); }
+   if (!g_enabled) { return next(pcg_vdata, A, b, x); }
    /* other interfaces (struct, sstruct, ...) were never on this path */
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(pcg_vdata, A, b, x); }
 
@@ -432,6 +439,13 @@ HYPRE_Int HYPRE_ParCSRMatrixMatvec(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HY
    hypre_ParCSRMatrix *pA = (hypre_ParCSRMatrix *) A;
    hypre_ParVector    *px = (hypre_ParVector *) x, *py = (hypre_ParVector *) y;
    mirror_t *m;
+   if (!g_enabled)
+   {
+      typedef HYPRE_Int (*mv_fn)(HYPRE_Complex, HYPRE_ParCSRMatrix, HYPRE_ParVector, HYPRE_Complex, HYPRE_ParVector);
+      static mv_fn next = NULL;
+      if (!next) { next = (mv_fn) next_sym("HYPRE_ParCSRMatrixMatvec"); }
+      return next(alpha, A, x, beta, y);
+   }
    if (hypre_ParVectorNumVectors(px) > 1)
    {
       GLUE_FAIL("multivector SpMV is outside the device path");

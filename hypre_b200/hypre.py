@@ -1,0 +1,334 @@
+"""Python mirror of the part of the HYPRE C API that src/test/ij.c uses for
+`-solver 1` (AMG-PCG), `-solver 0` (AMG) and `-solver -1` (SpMV), bound with ctypes
+to libHYPRE_b200.so (the B200 binding layered over the reference's host library).
+
+Names and argument meaning follow the reference (HYPRE_parcsr_ls.h / HYPRE_krylov.h):
+``BoomerAMG.SetRelaxType(18)`` is ``HYPRE_BoomerAMGSetRelaxType(solver, 18)`` and so on.
+``set_device_path(False)`` routes the interposed entry points to the reference's own CPU
+implementation in the same process (test / cpu_baseline use only).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import LIB_HYPRE_B200, capi
+
+_lib = None
+COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    capi.lib()   # libb200amg.so first: fail loudly if the CUDA library is missing
+    if not os.path.exists(LIB_HYPRE_B200):
+        raise capi.B200Error("%s is missing (built from hypre_b200/host with the reference headers)"
+                             % LIB_HYPRE_B200)
+    L = C.CDLL(LIB_HYPRE_B200, mode=C.RTLD_GLOBAL)
+    vp, i, d = C.c_void_p, C.c_int, C.c_double
+    for name in ("GenerateLaplacian", "GenerateLaplacian27pt", "GenerateRotate7pt", "hb_vector_create",
+                 "hb_vector_create_cols", "hb_amg_A", "hb_amg_P", "hb_amg_F", "hb_amg_U", "hb_amg_Vtemp",
+                 "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_precond_data",
+                 "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
+        getattr(L, name).restype = vp
+    for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
+                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms"):
+        getattr(L, name).restype = C.POINTER(d)
+    L.hb_amg_relax_weight.restype = d
+    L.hb_amg_omega.restype = d
+    L.hb_matrix_global_rows.restype = C.c_longlong
+    L.GenerateLaplacian.argtypes = [i, i, i, i, i, i, i, i, i, i, vp]
+    L.GenerateLaplacian27pt.argtypes = [i, i, i, i, i, i, i, i, i, i, vp]
+    L.GenerateRotate7pt.argtypes = [i, i, i, i, i, i, i, d, d]
+    L.hb_vector_create.argtypes = [vp, d]
+    L.hb_vector_create_cols.argtypes = [vp, d]
+    for name in ("hb_vector_destroy", "hb_vector_data", "hb_vector_size", "hb_amg_num_levels", "hb_amg_Vtemp",
+                 "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
+                 "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
+                 "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
+                 "HYPRE_ParCSRPCGDestroy"):
+        getattr(L, name).argtypes = [vp]
+    for name in ("hb_amg_A", "hb_amg_P", "hb_amg_F", "hb_amg_U", "hb_amg_l1", "hb_amg_cheby_ds",
+                 "hb_amg_cheby_coefs", "hb_amg_relax_weight", "hb_amg_omega", "hb_vector_set_all_zeros"):
+        getattr(L, name).argtypes = [vp, i]
+    L.hb_amg_params.argtypes = [vp, vp]
+    L.hb_amg_coarse_dense.argtypes = [vp, C.POINTER(i)]
+    L.hb_matrix_blocks.argtypes = [vp] + [vp] * 9
+    L.hypre_b200_set_enabled.argtypes = [i]
+    L.HYPRE_ParCSRMatrixMatvec.argtypes = [d, vp, vp, d, vp]
+    L.hypre_ParCSRMatrixMatvecOutOfPlace.argtypes = [d, vp, vp, d, vp, vp]
+    L.hypre_ParCSRMatrixMatvecT.argtypes = [d, vp, vp, d, vp]
+    L.hypre_BoomerAMGRelax.argtypes = [vp, vp, vp, i, i, d, d, vp, vp, vp, vp]
+    L.hypre_ParCSRRelax_Cheby_Solve.argtypes = [vp, vp, vp, vp, i, i, i, vp, vp, vp, vp, vp]
+    L.hypre_BoomerAMGCycle.argtypes = [vp, vp, vp]
+    L.HYPRE_BoomerAMGSolve.argtypes = [vp, vp, vp, vp]
+    L.HYPRE_BoomerAMGSetup.argtypes = [vp, vp, vp, vp]
+    L.HYPRE_Initialize()
+    _lib = L
+    return L
+
+
+def set_device_path(enabled):
+    """False: interposed entry points call the reference (CPU).  Tests / cpu_baseline only."""
+    lib().hypre_b200_set_enabled(1 if enabled else 0)
+
+
+def error_flag():
+    return lib().hb_error_flag()
+
+
+def clear_errors():
+    lib().hb_clear_errors()
+
+
+# ------------------------------------------------------------------ matrices / vectors
+class ParCSRMatrix:
+    def __init__(self, handle, own=True):
+        self.h, self.own = C.c_void_p(handle), own
+
+    def blocks(self):
+        """(diag, offd) as scipy CSR views of hypre's own arrays (copied)."""
+        import scipy.sparse as sp
+        L = lib()
+        n, nc, no = C.c_int(), C.c_int(), C.c_int()
+        di, dj, oi, oj = (C.POINTER(C.c_int)() for _ in range(4))
+        da, oa = C.POINTER(C.c_double)(), C.POINTER(C.c_double)()
+        L.hb_matrix_blocks(self.h, C.byref(n), C.byref(nc), C.byref(di), C.byref(dj), C.byref(da),
+                           C.byref(no), C.byref(oi), C.byref(oj), C.byref(oa))
+        n, nc, no = n.value, nc.value, no.value
+        ii = np.ctypeslib.as_array(di, (n + 1,)).copy() if n else np.zeros(1, np.int32)
+        nnz = int(ii[-1])
+        jj = np.ctypeslib.as_array(dj, (max(nnz, 1),))[:nnz].copy()
+        aa = np.ctypeslib.as_array(da, (max(nnz, 1),))[:nnz].copy()
+        diag = sp.csr_matrix((aa, jj, ii), shape=(n, nc))
+        offd = sp.csr_matrix((n, no))
+        if no > 0:
+            oii = np.ctypeslib.as_array(oi, (n + 1,)).copy()
+            onz = int(oii[-1])
+            offd = sp.csr_matrix((np.ctypeslib.as_array(oa, (max(onz, 1),))[:onz].copy(),
+                                  np.ctypeslib.as_array(oj, (max(onz, 1),))[:onz].copy(), oii), shape=(n, no))
+        return diag, offd
+
+    @property
+    def global_rows(self):
+        return int(lib().hb_matrix_global_rows(self.h))
+
+    def vector(self, value=0.0, cols=False):
+        fn = lib().hb_vector_create_cols if cols else lib().hb_vector_create
+        return ParVector(fn(self.h, float(value)))
+
+    def device_mirror(self):
+        m = lib().hypre_b200_matrix_mirror(self.h)
+        if not m:
+            raise capi.B200Error("matrix upload failed: " + capi.lib().b200_last_error().decode())
+        return C.c_void_p(m)
+
+    def destroy(self):
+        if self.own and self.h:
+            lib().HYPRE_ParCSRMatrixDestroy(self.h)
+            self.h = None
+
+
+class ParVector:
+    def __init__(self, handle, own=True):
+        self.h, self.own = C.c_void_p(handle), own
+
+    @property
+    def size(self):
+        return lib().hb_vector_size(self.h)
+
+    def numpy(self):
+        """numpy view of hypre's own host array (no copy)."""
+        n = self.size
+        if n == 0:
+            return np.zeros(0)
+        return np.ctypeslib.as_array(lib().hb_vector_data(self.h), (n,))
+
+    def set_all_zeros_flag(self, flag):
+        lib().hb_vector_set_all_zeros(self.h, int(flag))
+
+    def destroy(self):
+        if self.own and self.h:
+            lib().hb_vector_destroy(self.h)
+            self.h = None
+
+
+def laplacian(nx, ny, nz, c=(1.0, 1.0, 1.0)):
+    """ij -laplacian -n nx ny nz [-c cx cy cz]   (BuildParLaplacian, src/test/ij.c:9559-9790)."""
+    cx, cy, cz = c
+    v = np.zeros(4)
+    v[1], v[2], v[3] = -cx, -cy, -cz
+    v[0] = (2.0 * cx if nx > 1 else 0.0) + (2.0 * cy if ny > 1 else 0.0) + (2.0 * cz if nz > 1 else 0.0)
+    return ParCSRMatrix(lib().GenerateLaplacian(COMM_WORLD, nx, ny, nz, 1, 1, 1, 0, 0, 0, capi.ptr(v)))
+
+
+def laplacian_27pt(nx, ny, nz):
+    """ij -27pt -n nx ny nz   (BuildParLaplacian27pt, src/test/ij.c:10984-10996)."""
+    v = np.array([26.0, -1.0])
+    if nx == 1 or ny == 1 or nz == 1:
+        v[0] = 8.0
+    if nx * ny == 1 or nx * nz == 1 or ny * nz == 1:
+        v[0] = 2.0
+    return ParCSRMatrix(lib().GenerateLaplacian27pt(COMM_WORLD, nx, ny, nz, 1, 1, 1, 0, 0, 0, capi.ptr(v)))
+
+
+def rotate_7pt(nx, ny, alpha, eps):
+    """ij -rotate -n nx ny -alpha a -eps e   (BuildParRotate7pt, src/test/ij.c:11184-11240)."""
+    return ParCSRMatrix(lib().GenerateRotate7pt(COMM_WORLD, nx, ny, 1, 1, 0, 0, float(alpha), float(eps)))
+
+
+# ------------------------------------------------------------------ solvers
+class _Solver:
+    _prefix = ""
+
+    def __getattr__(self, name):
+        # solver.SetXxx(args) -> HYPRE_<prefix>SetXxx(handle, args)
+        if name.startswith(("Set", "Get")):
+            fn = getattr(lib(), self._prefix + name)
+
+            def call(*args):
+                conv = [C.c_double(a) if isinstance(a, float) else a for a in args]
+                return fn(self.h, *conv)
+            return call
+        raise AttributeError(name)
+
+
+class BoomerAMG(_Solver):
+    """HYPRE_BoomerAMG* (src/parcsr_ls/HYPRE_parcsr_amg.c) with the defaults ij.c passes."""
+    _prefix = "HYPRE_BoomerAMG"
+
+    def __init__(self, relax_type=18, as_precond=True, **opts):
+        self.h = C.c_void_p()
+        lib().HYPRE_BoomerAMGCreate(C.byref(self.h))
+        # ij.c defaults (src/test/ij.c:248-302): HMIS, ext+i, Pmax 4, relax_order 0, max coarse 9
+        self.SetCoarsenType(10)
+        self.SetInterpType(6)
+        self.SetPMaxElmts(4)
+        self.SetRelaxOrder(0)
+        self.SetMaxCoarseSize(9)
+        self.SetMinCoarseSize(0)
+        self.SetMaxRowSum(1.0)          # ij.c: max_row_sum = 1. (library default 0.9)
+        self.SetStrongThreshold(0.25)
+        self.SetMaxLevels(25)
+        self.SetMeasureType(0)
+        self.SetNumSweeps(1)
+        self.SetTruncFactor(0.0)
+        self.SetAggNumLevels(0)
+        self.SetPrintLevel(0)
+        self.SetChebyOrder(2)
+        self.SetChebyEigEst(10)
+        self.SetChebyVariant(0)
+        self.SetChebyScale(1)
+        self.SetChebyFraction(0.3)
+        if relax_type is not None and relax_type >= 0:
+            self.SetRelaxType(relax_type)
+        if as_precond:
+            self.SetTol(0.0)       # ij.c:5037 pc_tol = 0
+            self.SetMaxIter(1)     # ij.c:5055 precon_cycles = 1
+        for k, v in opts.items():
+            getattr(self, "Set" + k)(v)
+
+    def Setup(self, A, b, x):
+        return lib().HYPRE_BoomerAMGSetup(self.h, A.h, b.h, x.h)
+
+    def Solve(self, A, b, x):
+        return lib().HYPRE_BoomerAMGSolve(self.h, A.h, b.h, x.h)
+
+    def device_mirror(self):
+        m = lib().hypre_b200_amg_mirror(self.h)
+        if not m:
+            raise capi.B200Error("hierarchy upload failed: " + capi.lib().b200_last_error().decode())
+        return C.c_void_p(m)
+
+    # hierarchy access (reference's host objects)
+    @property
+    def num_levels(self):
+        return lib().hb_amg_num_levels(self.h)
+
+    def A(self, level):
+        return ParCSRMatrix(lib().hb_amg_A(self.h, level), own=False)
+
+    def P(self, level):
+        return ParCSRMatrix(lib().hb_amg_P(self.h, level), own=False)
+
+    def params(self):
+        out = np.zeros(14, dtype=np.int32)
+        lib().hb_amg_params(self.h, capi.ptr(out))
+        return {"relax_type": out[0:4].tolist(), "num_sweeps": out[4:8].tolist(), "cycle_type": int(out[8]),
+                "fcycle": int(out[9]), "cheby_order": int(out[10]), "cheby_scale": int(out[11]),
+                "cheby_variant": int(out[12]), "relax_order": int(out[13])}
+
+    def level_array(self, which, level, n):
+        p = getattr(lib(), "hb_amg_" + which)(self.h, level)
+        return np.ctypeslib.as_array(p, (n,)).copy() if p else None
+
+    def relax_weight(self, level):
+        return lib().hb_amg_relax_weight(self.h, level)
+
+    def coarse_dense(self):
+        n = C.c_int()
+        p = lib().hb_amg_coarse_dense(self.h, C.byref(n))
+        if not p or n.value == 0:
+            return None
+        return np.ctypeslib.as_array(p, (n.value * n.value,)).copy().reshape(n.value, n.value)
+
+    def destroy(self):
+        if self.h:
+            lib().HYPRE_BoomerAMGDestroy(self.h)
+            self.h = None
+
+
+class ParCSRPCG(_Solver):
+    """HYPRE_ParCSRPCG* / HYPRE_PCG* (src/parcsr_ls/HYPRE_parcsr_pcg.c, src/krylov/HYPRE_pcg.c)."""
+    _prefix = "HYPRE_PCG"
+
+    def __init__(self, tol=1e-8, max_iter=100, two_norm=1, print_level=0, logging=1):
+        self.h = C.c_void_p()
+        lib().HYPRE_ParCSRPCGCreate(COMM_WORLD, C.byref(self.h))
+        self.SetMaxIter(max_iter)
+        self.SetTol(float(tol))
+        self.SetTwoNorm(two_norm)
+        self.SetPrintLevel(print_level)
+        self.SetLogging(logging)
+        self.max_iter = max_iter
+        self.precond = None
+
+    def SetPrecond(self, amg):
+        L = lib()
+        self.precond = amg
+        return L.HYPRE_PCGSetPrecond(self.h, L.HYPRE_BoomerAMGSolve, L.HYPRE_BoomerAMGSetup, amg.h)
+
+    def SetDiagScalePrecond(self):
+        L = lib()
+        return L.HYPRE_PCGSetPrecond(self.h, L.HYPRE_ParCSRDiagScale, L.HYPRE_ParCSRDiagScaleSetup, None)
+
+    def Setup(self, A, b, x):
+        return lib().HYPRE_ParCSRPCGSetup(self.h, A.h, b.h, x.h)
+
+    def Solve(self, A, b, x):
+        return lib().HYPRE_ParCSRPCGSolve(self.h, A.h, b.h, x.h)
+
+    @property
+    def num_iterations(self):
+        n = C.c_int()
+        lib().HYPRE_PCGGetNumIterations(self.h, C.byref(n))
+        return n.value
+
+    @property
+    def final_rel_norm(self):
+        v = C.c_double()
+        lib().HYPRE_PCGGetFinalRelativeResidualNorm(self.h, C.byref(v))
+        return v.value
+
+    def rel_norms(self):
+        """per-iteration ||r||/||b|| (pcg.c:767-771), entries 1..num_iterations."""
+        p = lib().hb_pcg_rel_norms(self.h)
+        n = self.num_iterations
+        return np.ctypeslib.as_array(p, (self.max_iter + 1,))[1:n + 1].copy()
+
+    def destroy(self):
+        if self.h:
+            lib().HYPRE_ParCSRPCGDestroy(self.h)
+            self.h = None

@@ -60,6 +60,10 @@ int b200_dev_alloc(b200_ctx *ctx, long long n, double **dev);
 int b200_dev_free(b200_ctx *ctx, double *dev);
 int b200_h2d(b200_ctx *ctx, double *dev, const double *host, long long n);
 int b200_d2h(b200_ctx *ctx, double *host, const double *dev, long long n);
+/* page-lock / unlock a caller-owned host array (cudaHostRegister) so host-vector entry
+ * points copy at full PCIe speed; hypre allocates its vectors with plain malloc */
+int b200_host_pin(void *host, long long bytes);
+int b200_host_unpin(void *host);
 
 /* ------------------------------------------------------------ BLAS-1 (dev)
  * hypre_SeqVectorSetConstantValues / Copy / Scale / Axpy / InnerProd
@@ -172,7 +176,8 @@ int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *
 /* stand-alone AMG iteration (ij -solver 0): hypre_BoomerAMGSolve
  * (src/parcsr_ls/par_amg_solve.c:21-424) with converge_type 0. */
 int b200_amg_solve(b200_amg *amg, const double *b, double *x, double tol, int min_iter,
-                   int max_iter, int *num_iterations, double *rel_resid_norm);
+                   int max_iter, int *num_iterations, double *rel_resid_norm,
+                   double *resid_norms_h /* HOST, max_iter+1 entries ||r_k||_2, may be NULL */);
 
 /* --------------------------------------------------------------------- PCG
  * hypre_PCGSolve (src/krylov/pcg.c:317-1008) with the ParCSR operator table

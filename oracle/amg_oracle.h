@@ -1,0 +1,45 @@
+/* amg_oracle.h -- TEST INFRASTRUCTURE: plain-C CPU restatement of the reference's
+ * BoomerAMG-PCG solve phase (hypre 2.32.0).  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline leg may use it; it is never part of the product path.
+ * Parity pinned: tests/test_oracle.py checks it against the compiled reference
+ * (oracle/_ref/libHYPRE_ref.so) and against the golden PCG histories of BASELINE.md.
+ */
+#ifndef AMG_ORACLE_H
+#define AMG_ORACLE_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orc_amg orc_amg;
+
+void orc_csr_matvec(int n_rows, const int *ia, const int *ja, const double *a, double alpha,
+                    const double *x, double beta, const double *b, double *y);
+void orc_csr_matvecT(int n_rows, int n_cols, const int *ia, const int *ja, const double *a, double alpha,
+                     const double *x, double beta, double *y);
+void orc_relax_l1jacobi(int n, const int *ia, const int *ja, const double *a, const double *f,
+                        const double *l1, double w, double *u, double *vtemp, int all_zeros);
+void orc_relax_cheby(int n, const int *ia, const int *ja, const double *a, const double *f,
+                     const double *ds, const double *coefs, int order, int scale, double *u,
+                     double *v, double *r, double *orig_u, double *tmp);
+int  orc_relax_gs2(int n, const int *ia, const int *ja, const double *a, const double *f, double w,
+                   int inner, double *u, double *vtemp);
+int  orc_gselim(double *A, double *x, int n);
+
+orc_amg *orc_amg_create(int num_levels);
+void orc_amg_destroy(orc_amg *h);
+/* arrays are borrowed (must outlive the object); P may be NULL on the last level */
+void orc_amg_set_level(orc_amg *h, int level, int n, const int *Ai, const int *Aj, const double *Aa,
+                       int n_coarse, const int *Pi, const int *Pj, const double *Pa,
+                       const double *l1, const double *ds, const double *coefs, double relax_weight);
+void orc_amg_set_cycle(orc_amg *h, const int relax_type[4], const int num_sweeps[4], int cycle_type,
+                       int fcycle, int cheby_order, int cheby_scale);
+void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat);
+int  orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros);
+/* returns the iteration count; rel_norms[1..iters] = ||r||/||b|| (two_norm) */
+int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, int two_norm,
+             double *norms, double *rel_norms, int *converged);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,187 @@
+"""Test-only helpers: ctypes binding of oracle/_ref/liboracle.so (the plain-C restatement)
+and problem builders shared by the CPU and GPU tests."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+from hypre_b200 import LIB_ORACLE, ROOT, capi
+
+GOLDEN = os.path.join(ROOT, "tests", "golden", "pcg_histories.json")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(LIB_ORACLE)
+        vp, i, d = C.c_void_p, C.c_int, C.c_double
+        L.orc_csr_matvec.argtypes = [i, vp, vp, vp, d, vp, d, vp, vp]
+        L.orc_csr_matvecT.argtypes = [i, i, vp, vp, vp, d, vp, d, vp]
+        L.orc_relax_l1jacobi.argtypes = [i, vp, vp, vp, vp, vp, d, vp, vp, i]
+        L.orc_relax_cheby.argtypes = [i, vp, vp, vp, vp, vp, vp, i, i, vp, vp, vp, vp, vp]
+        L.orc_relax_gs2.argtypes = [i, vp, vp, vp, vp, d, i, vp, vp]
+        L.orc_gselim.argtypes = [vp, vp, i]
+        L.orc_amg_create.restype = vp
+        L.orc_amg_create.argtypes = [i]
+        L.orc_amg_destroy.argtypes = [vp]
+        L.orc_amg_set_level.argtypes = [vp, i, i, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, d]
+        L.orc_amg_set_cycle.argtypes = [vp, vp, vp, i, i, i, i]
+        L.orc_amg_set_coarse_dense.argtypes = [vp, i, vp]
+        L.orc_amg_cycle.argtypes = [vp, vp, vp, i]
+        L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
+        _lib = L
+    return _lib
+
+
+p = capi.ptr
+
+
+def csr_arrays(A):
+    A = A.tocsr()
+    return (np.ascontiguousarray(A.indptr, dtype=np.int32), np.ascontiguousarray(A.indices, dtype=np.int32),
+            np.ascontiguousarray(A.data, dtype=np.float64))
+
+
+def matvec(A, alpha, x, beta, b):
+    ii, jj, aa = csr_arrays(A)
+    y = np.zeros(A.shape[0])
+    bb = np.ascontiguousarray(b, dtype=np.float64) if b is not None else None
+    lib().orc_csr_matvec(A.shape[0], p(ii), p(jj), p(aa), alpha, p(np.ascontiguousarray(x)), beta, p(bb), p(y))
+    return y
+
+
+def matvecT(A, alpha, x, beta, y):
+    ii, jj, aa = csr_arrays(A)
+    out = np.array(y, dtype=np.float64, copy=True)
+    lib().orc_csr_matvecT(A.shape[0], A.shape[1], p(ii), p(jj), p(aa), alpha, p(np.ascontiguousarray(x)), beta, p(out))
+    return out
+
+
+def relax_l1jacobi(A, f, l1, w, u, all_zeros):
+    ii, jj, aa = csr_arrays(A)
+    u = np.array(u, dtype=np.float64, copy=True)
+    vt = np.zeros_like(u)
+    lib().orc_relax_l1jacobi(A.shape[0], p(ii), p(jj), p(aa), p(f), p(l1), w, p(u), p(vt), int(all_zeros))
+    return u
+
+
+def relax_cheby(A, f, ds, coefs, order, scale, u):
+    ii, jj, aa = csr_arrays(A)
+    u = np.array(u, dtype=np.float64, copy=True)
+    n = u.size
+    w = [np.zeros(n) for _ in range(4)]
+    lib().orc_relax_cheby(n, p(ii), p(jj), p(aa), p(f), p(ds), p(np.ascontiguousarray(coefs)), order, scale,
+                          p(u), p(w[0]), p(w[1]), p(w[2]), p(w[3]))
+    return u
+
+
+def relax_gs2(A, f, w, inner, u):
+    ii, jj, aa = csr_arrays(A)
+    u = np.array(u, dtype=np.float64, copy=True)
+    vt = np.zeros_like(u)
+    err = lib().orc_relax_gs2(u.size, p(ii), p(jj), p(aa), p(f), w, inner, p(u), p(vt))
+    return u, err
+
+
+class OracleAMG:
+    """orc_amg built from the reference's hierarchy (hypre_b200.hypre.BoomerAMG after Setup)."""
+
+    def __init__(self, amg):
+        L = lib()
+        self.keep = []
+        nl = amg.num_levels
+        prm = amg.params()
+        self.h = C.c_void_p(L.orc_amg_create(nl))
+        self.n = []
+        for l in range(nl):
+            Ad, _ = amg.A(l).blocks()
+            n = Ad.shape[0]
+            self.n.append(n)
+            Ai, Aj, Aa = csr_arrays(Ad)
+            if l < nl - 1:
+                Pd, _ = amg.P(l).blocks()
+                Pi, Pj, Pa = csr_arrays(Pd)
+                nc = Pd.shape[1]
+            else:
+                Pi = Pj = Pa = None
+                nc = 0
+            l1 = amg.level_array("l1", l, n)
+            ds = amg.level_array("cheby_ds", l, n)
+            coefs = amg.level_array("cheby_coefs", l, prm["cheby_order"] + 1) if 16 in prm["relax_type"] else None
+            self.keep.append((Ai, Aj, Aa, Pi, Pj, Pa, l1, ds, coefs))
+            L.orc_amg_set_level(self.h, l, n, p(Ai), p(Aj), p(Aa), nc, p(Pi), p(Pj), p(Pa), p(l1), p(ds), p(coefs),
+                                amg.relax_weight(l))
+        rt = np.array(prm["relax_type"], dtype=np.int32)
+        if rt[3] == 19:
+            rt[3] = 9
+        ns = np.array(prm["num_sweeps"], dtype=np.int32)
+        L.orc_amg_set_cycle(self.h, p(rt), p(ns), prm["cycle_type"], prm["fcycle"], prm["cheby_order"],
+                            prm["cheby_scale"])
+        dense = amg.coarse_dense()
+        if dense is not None:
+            dense = np.ascontiguousarray(dense)
+            L.orc_amg_set_coarse_dense(self.h, dense.shape[0], p(dense))
+
+    def cycle(self, f, u, all_zeros):
+        u = np.array(u, dtype=np.float64, copy=True)
+        lib().orc_amg_cycle(self.h, p(np.ascontiguousarray(f)), p(u), int(all_zeros))
+        return u
+
+    def pcg(self, b, x0, tol=1e-8, max_iter=100, two_norm=1):
+        x = np.array(x0, dtype=np.float64, copy=True)
+        norms = np.zeros(max_iter + 1)
+        rel = np.zeros(max_iter + 1)
+        conv = C.c_int()
+        it = lib().orc_pcg(self.h, p(np.ascontiguousarray(b)), p(x), tol, max_iter, two_norm, p(norms), p(rel),
+                           C.byref(conv))
+        return x, it, rel[1:it + 1].copy(), conv.value
+
+    def destroy(self):
+        if self.h:
+            lib().orc_amg_destroy(self.h)
+            self.h = None
+
+
+def golden():
+    return json.load(open(GOLDEN))
+
+
+# the scaled-down versions of BASELINE.json's configs used across the tests
+CASES = {
+    "lap7_32_rlx18": dict(gen="laplacian", dims=(32, 32, 32), rlx=18),
+    "lap7_100_rlx18": dict(gen="laplacian", dims=(100, 100, 100), rlx=18),
+    "lap7_64_rlx16": dict(gen="laplacian", dims=(64, 64, 64), rlx=16),
+    "lap27_48_rlx11": dict(gen="laplacian_27pt", dims=(48, 48, 48), rlx=11),
+    "lap27_48_rlx12": dict(gen="laplacian_27pt", dims=(48, 48, 48), rlx=12),
+    "rot_512_rlx18_agg1": dict(gen="rotate_7pt", dims=(512, 512, 45.0, 0.001), rlx=18, opts={"AggNumLevels": 1}),
+    "lap7_24_rlx16": dict(gen="laplacian", dims=(24, 24, 24), rlx=16),
+    "lap27_20_rlx11": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=11),
+    "lap27_20_rlx12": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=12),
+}
+
+IJ_ARGS = {
+    "lap7_32_rlx18": "-laplacian -n 32 32 32 -solver 1 -rlx 18",
+    "lap7_100_rlx18": "-laplacian -n 100 100 100 -solver 1 -rlx 18",
+    "lap7_64_rlx16": "-laplacian -n 64 64 64 -solver 1 -rlx 16",
+    "lap27_48_rlx11": "-27pt -n 48 48 48 -solver 1 -rlx 11",
+    "lap27_48_rlx12": "-27pt -n 48 48 48 -solver 1 -rlx 12",
+    "rot_512_rlx18_agg1": "-rotate -n 512 512 -alpha 45 -eps 0.001 -solver 1 -rlx 18 -agg_nl 1",
+    "lap7_24_rlx16": "-laplacian -n 24 24 24 -solver 1 -rlx 16",
+    "lap27_20_rlx11": "-27pt -n 20 20 20 -solver 1 -rlx 11",
+    "lap27_20_rlx12": "-27pt -n 20 20 20 -solver 1 -rlx 12",
+}
+
+
+def build_case(H, name, setup=True):
+    c = CASES[name]
+    A = getattr(H, c["gen"])(*c["dims"])
+    b = A.vector(1.0)
+    x = A.vector(0.0)
+    amg = H.BoomerAMG(relax_type=c["rlx"], **c.get("opts", {}))
+    pcg = H.ParCSRPCG(tol=1e-8, max_iter=100)
+    pcg.SetPrecond(amg)
+    if setup:
+        pcg.Setup(A, b, x)
+    return A, b, x, amg, pcg
