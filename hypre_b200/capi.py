@@ -76,6 +76,12 @@ def lib():
         "b200_parcsr_destroy": (i, [vp]),
         "b200_parcsr_info": (i, [vp, c_int_p, c_int_p, C.POINTER(ll), c_int_p, c_int_p]),
         "b200_set_layout_override": (i, [i, i]),
+        "b200_rowpart_create": (i, [i, i, i, i, vp, vp, vp, vp, vp, c_void_pp]),
+        "b200_rowpart_destroy": (i, [vp]),
+        "b200_rowpart_sizes": (i, [vp] + [c_int_p] * 8),
+        "b200_rowpart_int_array": (i, [vp, i, C.POINTER(c_int_p), c_int_p]),
+        "b200_rowpart_real_array": (i, [vp, i, C.POINTER(c_dbl_p), c_int_p]),
+        "b200_parcsr_create_from_rowpart": (i, [vp, vp, c_void_pp]),
         "b200_parcsr_matvec": (i, [vp, d, vp, d, vp, vp]),
         "b200_parcsr_matvecT": (i, [vp, d, vp, d, vp]),
         "b200_parcsr_matvec_host": (i, [vp, d, vp, d, vp, vp]),
@@ -162,3 +168,58 @@ def parcsr_from_scipy(ctx, A):
     check(lib().b200_parcsr_create(ctx, A.shape[0], A.shape[1], ptr(ii), ptr(jj), ptr(aa),
                                    0, None, None, None, 0, None, None, None, 0, None, None, C.byref(h)))
     return h
+
+
+class RowPart:
+    """b200_rowpart: this rank's ParCSR blocks + halo plan of a replicated global CSR matrix
+    (host only -- usable without a GPU)."""
+    INT_NAMES = ["diag_i", "diag_j", "offd_i", "offd_j", "col_map_offd", "send_procs", "send_map_starts",
+                 "send_map_elmts", "recv_procs", "recv_vec_starts"]
+
+    def __init__(self, rank, nranks, A, row_starts, col_starts):
+        A = A.tocsr()
+        ii = np.ascontiguousarray(A.indptr, dtype=np.int32)
+        jj = np.ascontiguousarray(A.indices, dtype=np.int32)
+        aa = np.ascontiguousarray(A.data, dtype=np.float64)
+        rs = np.ascontiguousarray(row_starts, dtype=np.int32)
+        cs = np.ascontiguousarray(col_starts, dtype=np.int32)
+        self.h = C.c_void_p()
+        check(lib().b200_rowpart_create(rank, nranks, A.shape[0], A.shape[1], ptr(ii), ptr(jj), ptr(aa),
+                                        ptr(rs), ptr(cs), C.byref(self.h)))
+        for k, name in enumerate(self.INT_NAMES):
+            p, n = c_int_p(), C.c_int()
+            check(lib().b200_rowpart_int_array(self.h, k, C.byref(p), C.byref(n)))
+            setattr(self, name, np.ctypeslib.as_array(p, (n.value,)).copy() if n.value else np.zeros(0, np.int32))
+        for k, name in enumerate(["diag_a", "offd_a"]):
+            p, n = c_dbl_p(), C.c_int()
+            check(lib().b200_rowpart_real_array(self.h, k, C.byref(p), C.byref(n)))
+            setattr(self, name, np.ctypeslib.as_array(p, (n.value,)).copy() if n.value else np.zeros(0))
+        s = [C.c_int() for _ in range(8)]
+        check(lib().b200_rowpart_sizes(self.h, *[C.byref(v) for v in s]))
+        (self.n_rows, self.n_cols_diag, self.n_cols_offd, self.nnz_diag, self.nnz_offd, self.num_sends,
+         self.n_send_elmts, self.num_recvs) = [v.value for v in s]
+
+    def blocks(self):
+        import scipy.sparse as sp
+        diag = sp.csr_matrix((self.diag_a, self.diag_j, self.diag_i), shape=(self.n_rows, self.n_cols_diag))
+        offd = sp.csr_matrix((self.offd_a, self.offd_j, self.offd_i), shape=(self.n_rows, self.n_cols_offd))
+        return diag, offd
+
+    def device(self, ctx):
+        h = C.c_void_p()
+        check(lib().b200_parcsr_create_from_rowpart(ctx, self.h, C.byref(h)))
+        return h
+
+    def destroy(self):
+        if self.h:
+            lib().b200_rowpart_destroy(self.h)
+            self.h = None
+
+
+def even_starts(n, nranks):
+    """hypre_GeneratePartitioning: the first n % nranks ranks get one extra row."""
+    size, rest = divmod(n, nranks)
+    st = np.zeros(nranks + 1, dtype=np.int32)
+    for r in range(nranks):
+        st[r + 1] = st[r] + size + (1 if r < rest else 0)
+    return st

@@ -43,10 +43,16 @@ static int g_enabled = 1;
 void hypre_b200_set_enabled(int enabled) { g_enabled = enabled; }
 int  hypre_b200_get_enabled(void) { return g_enabled; }
 
+/* distributed mode (one process per GPU, no MPI on the box): every process holds the SAME
+ * single-rank hypre objects; process `g_rank` mirrors rows [first_row, first_row + n_local)
+ * of every level on its GPU (hypre's 1-D row partition) and the solve runs over NCCL. */
+static int g_rank = 0, g_nranks = 1;
+
 typedef struct mirror_s {
    void            *key;      /* hypre_ParAMGData* or hypre_ParCSRMatrix* */
    b200_amg        *amg;
    b200_parcsr     *A;        /* level-0 operator (owned by amg when amg != NULL) */
+   int              first_row, first_col;   /* this rank's offset into the global host vectors */
    struct mirror_s *next;
 } mirror_t;
 static mirror_t *g_mirrors = NULL;
@@ -75,6 +81,23 @@ static b200_ctx *glue_ctx(void)
 }
 
 b200_ctx *hypre_b200_context(void) { return glue_ctx(); }
+
+/* Join an NCCL communicator of `nranks` processes (uid from b200_nccl_unique_id on rank 0,
+ * broadcast by the caller).  Must be called before anything is mirrored. */
+int hypre_b200_init_dist(int device, int rank, int nranks, const char *uid)
+{
+   if (g_ctx || g_mirrors) { fprintf(stderr, "hypre_b200_init_dist: context already exists\n"); return -1; }
+   if (b200_ctx_create_dist(device, rank, nranks, uid, &g_ctx) != B200_OK)
+   {
+      fprintf(stderr, "hypre_b200: cannot create distributed context: %s\n", b200_last_error());
+      g_ctx = NULL;
+      return -1;
+   }
+   g_rank = rank; g_nranks = nranks;
+   return 0;
+}
+int hypre_b200_rank(void) { return g_rank; }
+int hypre_b200_nranks(void) { return g_nranks; }
 
 static mirror_t *mirror_find(void *key)
 {
@@ -149,6 +172,35 @@ static b200_parcsr *upload_parcsr(hypre_ParCSRMatrix *A)
    return dA;
 }
 
+/* hypre_GeneratePartitioning (src/parcsr_mv/par_csr_matrix.c / utilities): n rows over P ranks,
+ * the first n % P ranks get one extra row */
+static void even_starts(int n, int P, int *starts)
+{
+   int size = n / P, rest = n - size * P, i;
+   starts[0] = 0;
+   for (i = 0; i < P; i++) { starts[i + 1] = starts[i] + size + (i < rest ? 1 : 0); }
+}
+
+/* rows [rs[g_rank], rs[g_rank+1]) of a single-rank hypre_ParCSRMatrix -> b200_parcsr with the
+ * halo plan of that partition (b200_rowpart_create = GenerateDiagAndOffd + MatvecCommPkgCreate) */
+static b200_parcsr *upload_parcsr_rows(hypre_ParCSRMatrix *A, const int *rs, const int *cs)
+{
+   hypre_CSRMatrix *diag = hypre_ParCSRMatrixDiag(A);
+   b200_rowpart    *part = NULL;
+   b200_parcsr     *dA = NULL;
+   if (hypre_CSRMatrixNumCols(hypre_ParCSRMatrixOffd(A)) != 0)
+   {
+      fprintf(stderr, "hypre_b200: distributed mode expects single-rank (replicated) hypre matrices\n");
+      return NULL;
+   }
+   if (b200_rowpart_create(g_rank, g_nranks, hypre_CSRMatrixNumRows(diag), hypre_CSRMatrixNumCols(diag),
+                           hypre_CSRMatrixI(diag), hypre_CSRMatrixJ(diag), hypre_CSRMatrixData(diag),
+                           rs, cs, &part) != B200_OK) { return NULL; }
+   if (b200_parcsr_create_from_rowpart(glue_ctx(), part, &dA) != B200_OK) { dA = NULL; }
+   b200_rowpart_destroy(part);
+   return dA;
+}
+
 /* hypre_ParAMGData (after the reference's host setup) -> b200_amg */
 static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
 {
@@ -163,6 +215,8 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
    hypre_Vector **ds = hypre_ParAMGDataChebyDS(amg_data);
    HYPRE_Real **coefs = hypre_ParAMGDataChebyCoefs(amg_data);
    int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0;
+   int *starts = NULL;   /* distributed mode: (nl+1) x (g_nranks+1) row starts per level */
+#define STARTS(l) (starts + (size_t)(l) * (g_nranks + 1))
 
    if (!ctx) { return NULL; }
    /* options with no device implementation are rejected, never silently run on the CPU */
@@ -185,16 +239,55 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
    }
    if (relax_type[3] == 19) { relax_type[3] = 9; }
 
-   if (b200_amg_create(ctx, nl, &amg) != B200_OK) { return NULL; }
+   if (g_nranks > 1)
+   {
+      /* Row partition of every level.  Level 0: hypre's even split.  Level l+1 inherits the
+       * partition of level l: coarse point c belongs to the rank that owns its fine point
+       * (C points keep their relative order, so the ranges stay contiguous) -- the layout the
+       * reference's parallel coarsening produces (coarse rows stay with their owners). */
+      hypre_IntArray **cfm = hypre_ParAMGDataCFMarkerArray(amg_data);
+      starts = (int *) calloc((size_t)(nl + 1) * (g_nranks + 1), sizeof(int));
+      even_starts((int) hypre_ParCSRMatrixGlobalNumRows(A_array[0]), g_nranks, STARTS(0));
+      for (l = 0; l < nl - 1; l++)
+      {
+         int nf = (int) hypre_ParCSRMatrixGlobalNumRows(A_array[l]);
+         int nc = (int) hypre_ParCSRMatrixGlobalNumRows(A_array[l + 1]);
+         int ok = 0;
+         if (cfm && cfm[l] && hypre_IntArraySize(cfm[l]) == nf)
+         {
+            const HYPRE_Int *m = hypre_IntArrayData(cfm[l]);
+            int i, r = 0, cnt = 0;
+            for (i = 0; i < nf; i++)
+            {
+               while (r < g_nranks && i == STARTS(l)[r]) { STARTS(l + 1)[r++] = cnt; }
+               if (m[i] > 0) { cnt++; }
+            }
+            while (r <= g_nranks) { STARTS(l + 1)[r++] = cnt; }
+            ok = (cnt == nc);
+         }
+         if (!ok) { even_starts(nc, g_nranks, STARTS(l + 1)); }
+      }
+   }
+   if (b200_amg_create(ctx, nl, &amg) != B200_OK) { free(starts); return NULL; }
    for (l = 0; l < nl; l++)
    {
-      b200_parcsr *dA = upload_parcsr(A_array[l]);
-      b200_parcsr *dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+      b200_parcsr *dA, *dP;
+      if (g_nranks > 1)
+      {
+         dA = upload_parcsr_rows(A_array[l], STARTS(l), STARTS(l));
+         dP = (l < nl - 1) ? upload_parcsr_rows(P_array[l], STARTS(l), STARTS(l + 1)) : NULL;
+      }
+      else
+      {
+         dA = upload_parcsr(A_array[l]);
+         dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+      }
       if (!dA || (l < nl - 1 && !dP) || b200_amg_set_level(amg, l, dA, dP) != B200_OK)
       {
          if (dA) { b200_parcsr_destroy(dA); }
          if (dP) { b200_parcsr_destroy(dP); }
          b200_amg_destroy(amg);
+         free(starts);
          return NULL;
       }
    }
@@ -203,18 +296,19 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
    for (k = 0; k < 4; k++) { if (relax_type[k] == 16) { uses_cheby = 1; } }
    for (l = 0; l < nl; l++)
    {
-      const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) : NULL;
+      const int off = starts ? STARTS(l)[g_rank] : 0;   /* this rank's slice of the level vectors */
+      const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) + off : NULL;
       if (b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d) != B200_OK)
       {
-         b200_amg_destroy(amg); return NULL;
+         b200_amg_destroy(amg); free(starts); return NULL;
       }
       if (uses_cheby && coefs && coefs[l])
       {
-         const double *dsd = (ds && ds[l]) ? hypre_VectorData(ds[l]) : NULL;
+         const double *dsd = (ds && ds[l]) ? hypre_VectorData(ds[l]) + off : NULL;
          if (b200_amg_set_level_cheby(amg, l, dsd, coefs[l], hypre_ParAMGDataChebyOrder(amg_data),
                                       hypre_ParAMGDataChebyScale(amg_data)) != B200_OK)
          {
-            b200_amg_destroy(amg); return NULL;
+            b200_amg_destroy(amg); free(starts); return NULL;
          }
       }
    }
@@ -223,15 +317,26 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
       hypre_ParCSRMatrix *Ac = A_array[nl - 1];
       HYPRE_Int N = (HYPRE_Int) hypre_ParCSRMatrixGlobalNumRows(Ac);
       HYPRE_Int np;
+      int status;
       if (!hypre_ParAMGDataGSSetup(amg_data)) { hypre_GaussElimSetup(amg_data, nl - 1, grt[3]); }
       hypre_MPI_Comm_size(hypre_ParCSRMatrixComm(Ac), &np);
-      if (b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data),
-                                    (int) hypre_ParCSRMatrixFirstRowIndex(Ac),
-                                    np > 1 ? hypre_ParAMGDataCommInfo(amg_data) : NULL) != B200_OK)
+      if (starts)
       {
-         b200_amg_destroy(amg); return NULL;
+         int *rows = (int *) calloc((size_t) g_nranks, sizeof(int)), r;
+         for (r = 0; r < g_nranks; r++) { rows[r] = STARTS(nl - 1)[r + 1] - STARTS(nl - 1)[r]; }
+         status = b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data), STARTS(nl - 1)[g_rank], rows);
+         free(rows);
       }
+      else
+      {
+         status = b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data),
+                                            (int) hypre_ParCSRMatrixFirstRowIndex(Ac),
+                                            np > 1 ? hypre_ParAMGDataCommInfo(amg_data) : NULL);
+      }
+      if (status != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
    }
+   free(starts);
+#undef STARTS
    if (b200_amg_finalize(amg) != B200_OK) { b200_amg_destroy(amg); return NULL; }
    if (verbose())
    {
@@ -291,6 +396,13 @@ static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
       m = (mirror_t *) calloc(1, sizeof(mirror_t));
       m->key = amg_data; m->amg = amg;
       b200_amg_level_matrix(amg, 0, &m->A);
+      if (g_nranks > 1)
+      {
+         int *st = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+         even_starts((int) hypre_ParCSRMatrixGlobalNumRows(hypre_ParAMGDataAArray(amg_data)[0]), g_nranks, st);
+         m->first_row = m->first_col = st[g_rank];
+         free(st);
+      }
       m->next = g_mirrors; g_mirrors = m;
    }
    return m;
@@ -301,10 +413,22 @@ static mirror_t *mirror_for_matrix(hypre_ParCSRMatrix *A)
    mirror_t *m = mirror_find(A);
    if (m) { return m; }
    {
-      b200_parcsr *dA = glue_ctx() ? upload_parcsr(A) : NULL;
+      b200_parcsr *dA = NULL;
+      int first_row = 0, first_col = 0;
+      if (glue_ctx() && g_nranks > 1)
+      {
+         int *rs = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+         int *cs = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+         even_starts((int) hypre_ParCSRMatrixGlobalNumRows(A), g_nranks, rs);
+         even_starts((int) hypre_ParCSRMatrixGlobalNumCols(A), g_nranks, cs);
+         dA = upload_parcsr_rows(A, rs, cs);
+         first_row = rs[g_rank]; first_col = cs[g_rank];
+         free(rs); free(cs);
+      }
+      else if (glue_ctx()) { dA = upload_parcsr(A); }
       if (!dA) { return NULL; }
       m = (mirror_t *) calloc(1, sizeof(mirror_t));
-      m->key = A; m->A = dA;
+      m->key = A; m->A = dA; m->first_row = first_row; m->first_col = first_col;
       m->next = g_mirrors; g_mirrors = m;
    }
    return m;
@@ -378,15 +502,16 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
    pcg->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
 
+   /* distributed mode: this rank's slice of the replicated host vectors (offset 0 otherwise) */
    status = b200_pcg_solve_host(glue_ctx(), m->A, amg, &prm,
-                                hypre_VectorData(hypre_ParVectorLocalVector(pb)),
-                                hypre_VectorData(hypre_ParVectorLocalVector(px)), &res,
+                                hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res,
                                 (pcg->logging > 0 || pcg->print_level > 0) ? pcg->norms : NULL,
                                 (pcg->logging > 0 || pcg->print_level > 0) ? pcg->rel_norms : NULL);
    if (status != B200_OK) { GLUE_FAIL("device PCG failed"); return hypre_error_flag; }
 
    /* the reference's printed table (pcg.c:405-409,536-560,772-792,983-986) */
-   if (pcg->print_level > 1 && my_id == 0)
+   if (pcg->print_level > 1 && my_id == 0 && g_rank == 0)
    {
       hypre_printf(pcg->two_norm ? "<b,b>: %e\n" : "<C*b,b>: %e\n", res.bi_prod);
       if (res.error_flag != 1 && res.bi_prod > 0.0)
@@ -453,9 +578,9 @@ HYPRE_Int HYPRE_ParCSRMatrixMatvec(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HY
    }
    m = mirror_for_matrix(pA);
    if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
-   if (b200_parcsr_matvec_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)), beta,
-                               hypre_VectorData(hypre_ParVectorLocalVector(py)),
-                               hypre_VectorData(hypre_ParVectorLocalVector(py))) != B200_OK)
+   if (b200_parcsr_matvec_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_col, beta,
+                               hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row,
+                               hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row) != B200_OK)
    {
       GLUE_FAIL("device SpMV failed");
    }
@@ -473,4 +598,10 @@ b200_parcsr *hypre_b200_matrix_mirror(void *parcsr)
 {
    mirror_t *m = mirror_for_matrix((hypre_ParCSRMatrix *) parcsr);
    return m ? m->A : NULL;
+}
+/* this rank's first row of the level-0 operator mirrored for `key` (amg data or matrix) */
+int hypre_b200_first_row(void *key)
+{
+   mirror_t *m = mirror_find(key);
+   return m ? m->first_row : -1;
 }

@@ -97,6 +97,27 @@ int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *
 /* force the storage layout chosen for the diag block (tests/bench): -1 auto */
 int b200_set_layout_override(int layout, int lanes_per_row);
 
+/* ------------------------------------------------------- row partitioning (host)
+ * Splits a replicated GLOBAL CSR matrix into this rank's ParCSR blocks and halo plan --
+ * what hypre_CSRMatrixToParCSRMatrix / GenerateDiagAndOffd
+ * (src/parcsr_mv/par_csr_matrix.c:1812-2230) and hypre_MatvecCommPkgCreate
+ * (src/parcsr_mv/par_csr_communication.c:1163-1200) produce, derived locally because every
+ * rank sees the whole matrix (no MPI exists on the GPU box).  row_starts / col_starts have
+ * nranks+1 entries.  Pure host code (works without a GPU). */
+typedef struct b200_rowpart b200_rowpart;
+int b200_rowpart_create(int rank, int nranks, int n_rows, int n_cols,
+                        const int *gi, const int *gj, const double *ga,
+                        const int *row_starts, const int *col_starts, b200_rowpart **part);
+int b200_rowpart_destroy(b200_rowpart *part);
+int b200_rowpart_sizes(const b200_rowpart *part, int *n_rows, int *n_cols_diag, int *n_cols_offd,
+                       int *nnz_diag, int *nnz_offd, int *num_sends, int *n_send_elmts, int *num_recvs);
+/* which: 0 diag_i, 1 diag_j, 2 offd_i, 3 offd_j, 4 col_map_offd, 5 send_procs,
+ * 6 send_map_starts, 7 send_map_elmts, 8 recv_procs, 9 recv_vec_starts (borrowed pointers) */
+int b200_rowpart_int_array(const b200_rowpart *part, int which, const int **data, int *len);
+/* which: 0 diag values, 1 offd values */
+int b200_rowpart_real_array(const b200_rowpart *part, int which, const double **data, int *len);
+int b200_parcsr_create_from_rowpart(b200_ctx *ctx, const b200_rowpart *part, b200_parcsr **A);
+
 /* y = alpha*A*x + beta*b   (dev pointers; y may alias b, must not alias x)
  * hypre_ParCSRMatrixMatvecOutOfPlace (src/parcsr_mv/par_csr_matvec.c:20-265)
  * over hypre_CSRMatrixMatvecOutOfPlace (src/seq_mv/csr_matvec.c:21-891). */

@@ -131,3 +131,186 @@ def test_two_stage_gs_zero_diagonal_is_an_error(ctx):
     u, err = O.relax_gs2(A, np.ones(3), 1.0, 1, np.zeros(3))
     assert err != 0
     L.b200_parcsr_destroy(h)
+
+
+# ------------------------------------------------------------------ multigrid cycle
+CYCLE_CASES = ["lap7_32_rlx18", "lap7_24_rlx16", "lap27_20_rlx11", "lap27_20_rlx12"]
+
+
+@pytest.mark.parametrize("name", CYCLE_CASES)
+def test_amg_cycle_matches_oracle(H, ctx, cases, name):
+    """hypre_BoomerAMGCycle: one V(1,1) cycle from a zero and from a non-zero initial guess"""
+    L = capi.lib()
+    A, b, x, amg, pcg = cases(name)
+    damg = amg.device_mirror()
+    orc = O.OracleAMG(amg)
+    n = A.global_rows
+    rng = np.random.default_rng(30)
+    f = rng.standard_normal(n)
+    for zg in (1, 0):
+        u0 = np.zeros(n) if zg else rng.standard_normal(n)
+        df, du = dvec(ctx, f), dvec(ctx, u0)
+        capi.check(L.b200_amg_cycle(damg, df.ptr, du.ptr, zg))
+        uref = orc.cycle(f, u0, zg)
+        assert vec_err(du.get(), uref) < 1e-10, (name, zg)
+        df.free(); du.free()
+    orc.destroy()
+
+
+def test_amg_cycle_matches_reference_in_process(H, ctx, cases):
+    """the same hierarchy through the reference's own hypre_BoomerAMGSolve (1 cycle, tol 0)"""
+    L = capi.lib()
+    A, b, x, amg, pcg = cases("lap7_32_rlx18")
+    n = A.global_rows
+    rng = np.random.default_rng(31)
+    f = A.vector(0.0); u = A.vector(0.0)
+    f.numpy()[:] = rng.standard_normal(n)
+    H.set_device_path(False)
+    try:
+        u.set_all_zeros_flag(0)
+        amg.Solve(A, f, u)
+    finally:
+        H.set_device_path(True)
+    damg = amg.device_mirror()
+    df, du = dvec(ctx, f.numpy()), capi.DeviceVector(ctx, n)
+    capi.check(L.b200_amg_cycle(damg, df.ptr, du.ptr, 0))
+    assert vec_err(du.get(), u.numpy()) < 1e-10
+    df.free(); du.free()
+
+
+def test_amg_solve_standalone_matches_reference(H, ctx, cases):
+    """ij -solver 0: residual history of the stand-alone AMG iteration (par_amg_solve.c:257-336)"""
+    L = capi.lib()
+    A = H.laplacian(20, 20, 20)
+    b = A.vector(1.0); x = A.vector(0.0)
+    amg = H.BoomerAMG(relax_type=18, as_precond=False)
+    amg.SetTol(1e-8); amg.SetMaxIter(30); amg.SetLogging(1)
+    H.set_device_path(False)
+    try:
+        amg.Setup(A, b, x)
+        amg.Solve(A, b, x)
+        it_ref = C.c_int(); rel_ref = C.c_double()
+        H.lib().HYPRE_BoomerAMGGetNumIterations(amg.h, C.byref(it_ref))
+        H.lib().HYPRE_BoomerAMGGetFinalRelativeResidualNorm(amg.h, C.byref(rel_ref))
+    finally:
+        H.set_device_path(True)
+    damg = amg.device_mirror()
+    n = A.global_rows
+    db, dx = dvec(ctx, b.numpy()), capi.DeviceVector(ctx, n)
+    it = C.c_int(); rel = C.c_double(); hist = np.zeros(31)
+    capi.check(L.b200_amg_solve(damg, db.ptr, dx.ptr, 1e-8, 0, 30, C.byref(it), C.byref(rel), capi.ptr(hist)))
+    assert it.value == it_ref.value
+    assert abs(rel.value - rel_ref.value) <= NORM_TOL * rel_ref.value
+    assert vec_err(dx.get(), x.numpy()) < 1e-9
+    amg.destroy(); A.destroy()
+
+
+# ------------------------------------------------------------------ PCG
+PCG_CASES = ["lap7_32_rlx18", "lap7_24_rlx16", "lap27_20_rlx11", "lap27_20_rlx12", "lap7_64_rlx16",
+             "lap27_48_rlx11", "lap27_48_rlx12", "rot_512_rlx18_agg1", "lap7_100_rlx18"]
+
+
+@pytest.mark.parametrize("name", PCG_CASES)
+def test_pcg_matches_oracle_and_golden(H, ctx, cases, name):
+    """HYPRE_ParCSRPCGSolve through the interposed API: iteration count identical, per-iteration
+    ||r||/||b|| within 1e-9 of the oracle and within print precision of the reference's ij output"""
+    A, b, x, amg, pcg = cases(name)
+    g = O.golden()[name]
+    x.numpy()[:] = 0.0
+    H.clear_errors()
+    pcg.Solve(A, b, x)
+    assert H.error_flag() == 0
+    it, rel = pcg.num_iterations, pcg.rel_norms()
+    orc = O.OracleAMG(amg)
+    xo, ito, relo, conv = orc.pcg(b.numpy(), np.zeros(A.global_rows))
+    orc.destroy()
+    assert it == ito == g["iterations"]
+    np.testing.assert_allclose(rel, relo, rtol=NORM_TOL)
+    np.testing.assert_allclose(rel, g["rel_norms"], rtol=2e-6)
+    assert abs(pcg.final_rel_norm - relo[-1]) <= NORM_TOL * relo[-1]
+    assert vec_err(x.numpy(), xo) < 1e-8
+
+
+@pytest.mark.parametrize("precond", ["diag", "none"])
+def test_pcg_diag_scale_and_identity_match_reference(H, ctx, precond):
+    """ij -solver 2 (DS-PCG) and unpreconditioned CG against the reference in-process"""
+    A = H.laplacian(24, 20, 16)
+    b = A.vector(1.0); x = A.vector(0.0)
+    pcg = H.ParCSRPCG(tol=1e-8, max_iter=500)
+    if precond == "diag":
+        pcg.SetDiagScalePrecond()
+    pcg.Setup(A, b, x)
+    out = {}
+    for dev in (False, True):
+        H.set_device_path(dev)
+        x.numpy()[:] = 0.0
+        H.clear_errors()
+        pcg.Solve(A, b, x)
+        out[dev] = (pcg.num_iterations, pcg.rel_norms(), x.numpy().copy())
+    H.set_device_path(True)
+    assert out[True][0] == out[False][0]
+    np.testing.assert_allclose(out[True][1], out[False][1], rtol=NORM_TOL)
+    assert vec_err(out[True][2], out[False][2]) < 1e-8
+    pcg.destroy(); A.destroy()
+
+
+def test_pcg_max_iter_sets_conv_error_and_zero_rhs(H, ctx, cases):
+    """pcg.c:988-993 (HYPRE_ERROR_CONV = 256 when max_iter is hit) and pcg.c:472-485 (b = 0 -> x = b)"""
+    A, b, x, amg, pcg = cases("lap7_32_rlx18")
+    pcg.SetMaxIter(3)
+    x.numpy()[:] = 0.0
+    H.clear_errors()
+    pcg.Solve(A, b, x)
+    assert pcg.num_iterations == 3 and (H.error_flag() & 256)
+    H.clear_errors()
+    pcg.SetMaxIter(100)
+    z = A.vector(0.0)
+    x.numpy()[:] = 1.0
+    pcg.Solve(A, z, x)
+    assert H.error_flag() == 0 and pcg.num_iterations == 0 and np.all(x.numpy() == 0.0)
+    z.destroy()
+
+
+def test_host_spmv_entry_matches_reference(H, ctx):
+    """HYPRE_ParCSRMatrixMatvec (ij -solver -1 -nmv N, ij.c:4262-4296) with host vectors"""
+    A = H.laplacian_27pt(30, 28, 26)
+    x = A.vector(0.0, cols=True); y = A.vector(0.0)
+    n = A.global_rows
+    x.numpy()[:] = np.sin(np.arange(n)) * 1e-3 + 1.0
+    out = {}
+    for dev in (False, True):
+        H.set_device_path(dev)
+        y.numpy()[:] = 0.5
+        H.lib().HYPRE_ParCSRMatrixMatvec(2.0, A.h, x.h, -1.0, y.h)
+        out[dev] = y.numpy().copy()
+    H.set_device_path(True)
+    Ad = A.blocks()[0]
+    scale = np.abs(Ad).dot(np.abs(x.numpy())) * 2.0 + 0.5
+    assert np.max(np.abs(out[True] - out[False]) / scale) < 1e-12
+    A.destroy()
+
+
+# ------------------------------------------------------------------ the unchanged ij driver
+def _ij(binary, args):
+    env = dict(os.environ)
+    r = subprocess.run([binary] + args.split(), capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    it = int(re.search(r"Iterations = (\d+)", r.stdout).group(1))
+    rel = float(re.search(r"Final Relative Residual Norm = (\S+)", r.stdout).group(1))
+    hist = [float(m.group(1)) for m in re.finditer(r"^\s*\d+\s+\S+\s+\S+\s+(\S+)\s*$", r.stdout, re.M)]
+    return it, rel, hist, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("name", ["lap7_32_rlx18", "lap7_24_rlx16", "lap27_20_rlx11"])
+def test_unchanged_ij_driver_on_the_device_path(built, name):
+    """the reference's own src/test/ij.c, compiled unmodified and linked on the binding (ij_b200),
+    against the same driver on the reference library (ij_ref): same iterations, same printed norms"""
+    args = O.IJ_ARGS[name]
+    it_d, rel_d, hist_d, out_d = _ij(IJ_B200, args)
+    it_r, rel_r, hist_r, _ = _ij(IJ_REF, args)
+    g = O.golden()[name]
+    assert it_d == it_r == g["iterations"]
+    assert abs(rel_d - rel_r) <= 2e-6 * rel_r
+    assert len(hist_d) == len(hist_r) == it_d
+    np.testing.assert_allclose(hist_d, hist_r, rtol=2e-6)
+    assert "hypre_b200:" not in out_d or "uploaded" in out_d
