@@ -148,17 +148,69 @@ def run_reference(args, rank):
     print(json.dumps(out))
 
 
+class Ranks:
+    """torch.distributed plumbing for N > 1 (one process per GPU, NCCL); no-ops for N = 1."""
+
+    def __init__(self, rank, world):
+        self.rank, self.world = rank, world
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            self.torch, self.dist = torch, dist
+            torch.cuda.set_device(self.local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def bcast_bytes(self, data):
+        if self.world == 1:
+            return data
+        t = self.torch.tensor(list(data), dtype=self.torch.uint8, device="cuda")
+        self.dist.broadcast(t, 0)
+        return bytes(t.cpu().tolist())
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def max(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
 def run_b200(args, rank, world):
+    ncores = os.cpu_count() or 1
+    # every rank runs the (replicated) reference host setup: share the cores
+    os.environ.setdefault("OMP_NUM_THREADS", str(max(1, ncores // world)))
+    R = Ranks(rank, world)       # N > 1: imports torch first so that its bundled NCCL is the one loaded
     from hypre_b200 import capi, hypre as H
     L = capi.lib()
+    HL = H.lib()
     if world > 1:
-        raise SystemExit("multi-GPU bench path not wired in this build (see DESIGN.md, section multi-GPU)")
-    ncores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
+        uid = C.create_string_buffer(128)
+        if rank == 0:
+            capi.check(L.b200_nccl_unique_id(uid))
+        uid = C.create_string_buffer(R.bcast_bytes(uid.raw), 128)
+        if HL.hypre_b200_init_dist(R.local, rank, world, uid) != 0:
+            raise capi.B200Error("hypre_b200_init_dist failed: " + L.b200_last_error().decode())
     P = build_problem(H, args.workload, args.n)
     A, b, x, amg, pcg = P["A"], P["b"], P["x"], P["amg"], P["pcg"]
-    n = A.global_rows
-    HL = H.lib()
+    n_global = A.global_rows
     ctx = C.c_void_p(HL.hypre_b200_context())
     if not ctx:
         raise capi.B200Error("no CUDA device: " + L.b200_last_error().decode())
@@ -172,9 +224,11 @@ def run_b200(args, rank, world):
     nnz0 = C.c_longlong(); nrows = C.c_int(); layout = C.c_int(); lanes = C.c_int()
     capi.check(L.b200_parcsr_info(dA, C.byref(nrows), None, C.byref(nnz0), C.byref(layout), C.byref(lanes)))
     nnz0 = nnz0.value
+    n = nrows.value                                        # this rank's rows (== n_global for N = 1)
+    first = HL.hypre_b200_first_row(amg.h) if world > 1 else 0
 
     # ---------------- value: device-resident solve, CUDA events on the library's stream
-    db = capi.DeviceVector(ctx, n, b.numpy())
+    db = capi.DeviceVector(ctx, n, b.numpy()[first:first + n])
     dx = capi.DeviceVector(ctx, n)
     prm = capi.PcgParams(tol=1e-8, a_tol=0.0, max_iter=100, two_norm=1, skip_break=0, diag_scale=0)
     res = capi.PcgResult()
@@ -186,20 +240,22 @@ def run_b200(args, rank, world):
                                     capi.ptr(norms), capi.ptr(rel)))
     for _ in range(args.warmup):
         dev_solve()
-    sampler = ClockSampler()
+    sampler = ClockSampler(R.local)
     sampler.start()
     l0 = L.b200_ctx_launch_count(ctx)
     ms = C.c_float()
     capi.check(L.b200_ctx_sync(ctx))
+    R.barrier()
     capi.check(L.b200_timer_start(ctx))
     for _ in range(args.steps):
         dev_solve()
     capi.check(L.b200_timer_stop(ctx, C.byref(ms)))
     capi.check(L.b200_ctx_sync(ctx))
+    R.barrier()
     launches = L.b200_ctx_launch_count(ctx) - l0
     iters = res.num_iterations
-    dev_s = ms.value * 1e-3
-    value = n * iters * args.steps / dev_s
+    dev_s = R.max(ms.value * 1e-3)                         # max over ranks
+    value = n_global * iters * args.steps / dev_s
 
     # ---------------- e2e: HYPRE_ParCSRPCGSolve with host vectors (pinned once, like a user would)
     bh, xh = b.numpy(), x.numpy()
@@ -213,14 +269,22 @@ def run_b200(args, rank, world):
         pcg.Solve(A, b, x)
     for _ in range(max(1, args.warmup)):
         api_solve()
+    R.barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         api_solve()
-    e2e_s = time.perf_counter() - t0
+    R.barrier()
+    e2e_s = R.max(time.perf_counter() - t0)
     clocks = sampler.stop()
     e2e_iters = pcg.num_iterations
-    e2e_value = n * e2e_iters * args.steps / e2e_s
+    e2e_value = n_global * e2e_iters * args.steps / e2e_s
     api_rel = pcg.rel_norms()
+    if world > 1:
+        return finish_multi(args, R, P, dict(value=value, dev_s=dev_s, iters=iters, launches=launches,
+                                             e2e_value=e2e_value, e2e_s=e2e_s, e2e_iters=e2e_iters, rel=rel,
+                                             api_rel=api_rel, clocks=clocks, n_global=n_global, n_local=n,
+                                             cyc_bytes=cyc_bytes.value, nnz0=nnz0, upload_s=upload_s,
+                                             levels=amg.num_levels))
 
     # ---------------- roofline: the level-0 SpMV of the PCG loop (s = A p), timed live
     peak, peak_src = measured_peaks()
@@ -277,6 +341,37 @@ def run_b200(args, rank, world):
         "setup_s": P["setup_s"], "upload_s": upload_s,
     }
     print(json.dumps(out))
+
+
+def finish_multi(args, R, P, m):
+    """N > 1: whole-job numbers (max-over-ranks time), per-rank algorithmic bytes summed over ranks."""
+    n = m["n_local"]
+    spmv_bytes = 12.0 * m["nnz0"] + 4.0 * (n + 1) + 16.0 * n
+    iter_bytes = R.sum(m["cyc_bytes"] + spmv_bytes + 8.0 * n * 9)
+    launches = R.sum(m["launches"])
+    if R.rank == 0:
+        peak, peak_src = measured_peaks()
+        iter_gbs = iter_bytes * m["iters"] * args.steps / m["dev_s"] / 1e9
+        out = {
+            "metric": "AMG-PCG solve DOF*iterations/s", "value": m["value"], "unit": "DOF*it/s", "n_gpus": R.world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * m["dev_s"] / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": P["cmd"], "dof": m["n_global"], "iterations_per_step": m["iters"],
+                       "levels": m["levels"], "partition": "1-D row blocks, %d ranks, halo over NCCL/NVLink" % R.world,
+                       "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration, all ranks)" % (iter_bytes / 1e9),
+                       "final_rel_residual": float(m["rel"][m["iters"]])},
+            "e2e": {"value": m["e2e_value"], "unit": "DOF*it/s", "h2d_bytes_per_step": 16 * m["n_global"],
+                    "d2h_bytes_per_step": 8 * m["n_global"], "iterations_per_step": m["e2e_iters"],
+                    "ms_per_step": 1e3 * m["e2e_s"] / args.steps,
+                    "final_rel_residual": float(m["api_rel"][-1]) if len(m["api_rel"]) else None},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "whole PCG iteration, all ranks (per-kernel roofline is reported at N=1)",
+                         "achieved": iter_gbs, "peak": peak * R.world, "unit": "GB/s", "frac": iter_gbs / (peak * R.world),
+                         "traffic": None, "peak_source": peak_src + " x n_gpus", "pcg_iteration_bytes": iter_bytes},
+            "cpu_baseline": None, "clocks": m["clocks"], "setup_s": P["setup_s"], "upload_s": m["upload_s"],
+        }
+        print(json.dumps(out))
+    R.close()
 
 
 def main():

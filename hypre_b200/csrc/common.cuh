@@ -57,7 +57,9 @@ struct b200_ctx {
    cudaEvent_t  ev_pack  = nullptr;   // pack done   (compute -> comm)
    cudaEvent_t  ev_halo  = nullptr;   // halo landed (comm -> compute)
    cudaEvent_t  ev_t0 = nullptr, ev_t1 = nullptr;
-   ncclComm_t   comm     = nullptr;
+   ncclComm_t   comm     = nullptr;   // collectives (dots, coarse gather) on `stream`
+   ncclComm_t   hcomm    = nullptr;   // halo point-to-point on `cstream` (own communicator: the two
+                                      // streams run concurrently and must not share one)
    long long    launches = 0;
    // reduction scratch: partials[slot][block], finished-block counter, results
    double      *d_partials = nullptr;

@@ -75,6 +75,7 @@ extern "C" int b200_ctx_create_dist(int device, int rank, int nranks, const char
       ncclUniqueId id;
       memcpy(&id, uid, 128);
       NCCL_TRY(ncclCommInitRank(&c->comm, nranks, id, rank));
+      NCCL_TRY(ncclCommSplit(c->comm, 0, rank, &c->hcomm, nullptr));
    }
    *ctx = c;
    return B200_OK;
@@ -85,6 +86,7 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    if (!c) { return B200_OK; }
    cudaSetDevice(c->device);
    cudaDeviceSynchronize();
+   if (c->hcomm) { ncclCommDestroy(c->hcomm); }
    if (c->comm) { ncclCommDestroy(c->comm); }
    cudaFree(c->d_partials); cudaFree(c->d_counter); cudaFree(c->d_scalars);
    cudaFreeHost(c->h_scalars);

@@ -305,12 +305,12 @@ int halo_start(b200_parcsr *A, const double *x)
    for (int i = 0; i < A->num_recvs; i++)
    {
       int cnt = A->recv_vec_starts[i + 1] - A->recv_vec_starts[i];
-      NCCL_TRY(ncclRecv(A->d_ghost + A->recv_vec_starts[i], (size_t)cnt, ncclDouble, A->recv_procs[i], c->comm, c->cstream));
+      NCCL_TRY(ncclRecv(A->d_ghost + A->recv_vec_starts[i], (size_t)cnt, ncclDouble, A->recv_procs[i], c->hcomm, c->cstream));
    }
    for (int i = 0; i < A->num_sends; i++)
    {
       int cnt = A->send_map_starts[i + 1] - A->send_map_starts[i];
-      NCCL_TRY(ncclSend(A->d_send_buf + A->send_map_starts[i], (size_t)cnt, ncclDouble, A->send_procs[i], c->comm, c->cstream));
+      NCCL_TRY(ncclSend(A->d_send_buf + A->send_map_starts[i], (size_t)cnt, ncclDouble, A->send_procs[i], c->hcomm, c->cstream));
    }
    NCCL_TRY(ncclGroupEnd());
    CUDA_TRY(cudaEventRecord(c->ev_halo, c->cstream));
@@ -354,12 +354,12 @@ int halo_reverse_start(b200_parcsr *A)
    for (int i = 0; i < A->num_sends; i++)
    {
       int cnt = A->send_map_starts[i + 1] - A->send_map_starts[i];
-      NCCL_TRY(ncclRecv(A->d_recv_buf + A->send_map_starts[i], (size_t)cnt, ncclDouble, A->send_procs[i], c->comm, c->cstream));
+      NCCL_TRY(ncclRecv(A->d_recv_buf + A->send_map_starts[i], (size_t)cnt, ncclDouble, A->send_procs[i], c->hcomm, c->cstream));
    }
    for (int i = 0; i < A->num_recvs; i++)
    {
       int cnt = A->recv_vec_starts[i + 1] - A->recv_vec_starts[i];
-      NCCL_TRY(ncclSend(A->d_ghost_out + A->recv_vec_starts[i], (size_t)cnt, ncclDouble, A->recv_procs[i], c->comm, c->cstream));
+      NCCL_TRY(ncclSend(A->d_ghost_out + A->recv_vec_starts[i], (size_t)cnt, ncclDouble, A->recv_procs[i], c->hcomm, c->cstream));
    }
    NCCL_TRY(ncclGroupEnd());
    CUDA_TRY(cudaEventRecord(c->ev_halo, c->cstream));
