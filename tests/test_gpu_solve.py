@@ -200,7 +200,9 @@ def test_amg_solve_standalone_matches_reference(H, ctx, cases):
     it = C.c_int(); rel = C.c_double(); hist = np.zeros(31)
     capi.check(L.b200_amg_solve(damg, db.ptr, dx.ptr, 1e-8, 0, 30, C.byref(it), C.byref(rel), capi.ptr(hist)))
     assert it.value == it_ref.value
-    assert abs(rel.value - rel_ref.value) <= NORM_TOL * rel_ref.value
+    # the stand-alone iteration recomputes r = b - A x, so at ||r||/||b|| ~ 5e-9 nine digits cancel:
+    # the norm itself is only defined to ~eps/5e-9; tolerance = 1e-9 relative + 5 ulp of ||b||/||b||
+    assert abs(rel.value - rel_ref.value) <= NORM_TOL * rel_ref.value + 5e-16
     assert vec_err(dx.get(), x.numpy()) < 1e-9
     amg.destroy(); A.destroy()
 
