@@ -1,6 +1,7 @@
 // amg.cu -- device multigrid cycle (hypre_BoomerAMGCycle, src/parcsr_ls/par_cycle.c:22-803).
 #include "ops.cuh"
 #include "vecops.cuh"
+#include "p2p.cuh"
 #include <cmath>
 
 struct AmgLevel {
@@ -264,7 +265,8 @@ static int coarse_dense_solve(b200_amg *a, const double *f, double *u)
          CUDA_TRY(cudaMemcpyAsync(a->d_fall + a->coarse_first_row, f, sizeof(double) * (size_t)n_local,
                                   cudaMemcpyDeviceToDevice, c->stream));
       }
-      NCCL_TRY(ncclAllReduce(a->d_fall, a->d_fall, (size_t)a->coarse_n, ncclDouble, ncclSum, c->comm, c->stream));
+      if (c->use_p2p && a->coarse_n <= 256) { B200_TRY(p2p_allreduce(c, a->d_fall, a->coarse_n)); }
+      else { NCCL_TRY(ncclAllReduce(a->d_fall, a->d_fall, (size_t)a->coarse_n, ncclDouble, ncclSum, c->comm, c->stream)); }
       return op_dense_matvec(c, n_local, a->coarse_n, a->d_Ainv, a->d_fall, u);
    }
    return op_dense_matvec(c, n_local, a->coarse_n, a->d_Ainv, f, u);

@@ -3,6 +3,7 @@
 // ||b - A x|| / ||b|| < tol.  The residual SpMV and its norm are one launch.
 #include "ops.cuh"
 #include "vecops.cuh"
+#include "p2p.cuh"
 #include <cmath>
 
 // r = b - t ; red0 += r*r
@@ -44,6 +45,7 @@ extern "C" int b200_amg_solve(b200_amg *amg, const double *b, double *x, double 
    double resid = 1.0, rhs_norm = 0.0, rel = 1.0;
    int status = B200_OK, cycles = 0;
    const bool track = tol > 0.0 || resid_norms_h != nullptr;
+   B200_TRY(ctx_rendezvous(c));
    if (track)
    {
       status = residual_norm(A, b, x, r, &resid);

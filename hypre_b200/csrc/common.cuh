@@ -61,6 +61,16 @@ struct b200_ctx {
    ncclComm_t   hcomm    = nullptr;   // halo point-to-point on `cstream` (own communicator: the two
                                       // streams run concurrently and must not share one)
    long long    launches = 0;
+   // peer-memory exchange (p2p.cuh): this rank's arena, the IPC-mapped arenas of all ranks
+   int          use_p2p = 0;
+   char        *arena = nullptr;
+   size_t       arena_bytes = 0, arena_used = 0;
+   std::vector<char *> peer_arena;
+   char       **d_peer_arena = nullptr;
+   size_t       ar_vals_off = 0, ar_flag_off = 0;
+   unsigned long long *d_ar_seq = nullptr;
+   int         *d_err = nullptr;      // set by a kernel whose bounded spin expired
+   int         *h_err = nullptr;      // pinned mirror
    // reduction scratch: partials[slot][block], finished-block counter, results
    double      *d_partials = nullptr;
    unsigned    *d_counter  = nullptr;
@@ -73,6 +83,7 @@ struct b200_ctx {
    double      *h_stage = nullptr;
    size_t       h_stage_n = 0;
    bool         capturing = false;
+   int         *d_stop = nullptr;     // device stop word checked by every kernel (see RedCtx::stop)
    // cached device work vectors (PCG p/s/r, host-entry b/x, ...): grown on demand, never
    // freed before the context dies, so repeated solves do not pay cudaMalloc/cudaFree
    static constexpr int NUM_WS = 12;
@@ -142,8 +153,13 @@ struct HostCsr {
    std::vector<double> a;
 };
 
+struct b200_p2p_chan;
+
 struct b200_parcsr {
    b200_ctx *ctx = nullptr;
+   // peer-memory channels (N > 1): forward = ghost values of x (job 1), reverse = contributions
+   // to the owners for A^T x (job 2); nullptr -> NCCL send/recv path
+   b200_p2p_chan *ch_fwd = nullptr, *ch_rev = nullptr;
    int n_rows = 0, n_cols_diag = 0, n_cols_offd = 0;
    DMat diag, offd;
    // explicit transposes (restriction) -- built on first MatvecT
@@ -171,6 +187,7 @@ struct b200_parcsr {
    double *d_recv_buf  = nullptr;  // [n_send_elmts]
    // deterministic unpack plan for job 2: CSR of (local row -> positions in recv buf)
    int    *d_unpack_rp = nullptr, *d_unpack_pos = nullptr;
+   int    *d_unpack_rp_dense = nullptr;   // [n_cols_diag+1]: the same lists indexed by local row (fused kernel)
    int     n_unpack_rows = 0;
    int    *d_unpack_rows = nullptr;
 };

@@ -1,6 +1,7 @@
 // ctx.cu -- context, device memory, BLAS-1 kernels.
 #include "common.cuh"
 #include "vecops.cuh"
+#include "p2p.cuh"
 #include <cstdarg>
 
 static thread_local char g_err[1024] = "";
@@ -41,6 +42,8 @@ static int ctx_init_common(b200_ctx *c, int device)
    CUDA_TRY(cudaMalloc((void **)&c->d_scalars, sizeof(double) * B200_NUM_SCALARS));
    CUDA_TRY(cudaMemset(c->d_scalars, 0, sizeof(double) * B200_NUM_SCALARS));
    CUDA_TRY(cudaMallocHost((void **)&c->h_scalars, sizeof(double) * B200_NUM_SCALARS));
+   CUDA_TRY(cudaMalloc((void **)&c->d_stop, sizeof(int)));
+   CUDA_TRY(cudaMemset(c->d_stop, 0, sizeof(int)));
    return B200_OK;
 }
 
@@ -76,6 +79,10 @@ extern "C" int b200_ctx_create_dist(int device, int rank, int nranks, const char
       memcpy(&id, uid, 128);
       NCCL_TRY(ncclCommInitRank(&c->comm, nranks, id, rank));
       NCCL_TRY(ncclCommSplit(c->comm, 0, rank, &c->hcomm, nullptr));
+      CUDA_TRY(cudaMallocHost((void **)&c->h_err, sizeof(int)));
+      *c->h_err = 0;
+      s = p2p_bootstrap(c);
+      if (s != B200_OK) { *ctx = nullptr; return s; }
    }
    *ctx = c;
    return B200_OK;
@@ -86,10 +93,12 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    if (!c) { return B200_OK; }
    cudaSetDevice(c->device);
    cudaDeviceSynchronize();
+   p2p_shutdown(c);
+   if (c->h_err) { cudaFreeHost(c->h_err); }
    if (c->hcomm) { ncclCommDestroy(c->hcomm); }
    if (c->comm) { ncclCommDestroy(c->comm); }
    cudaFree(c->d_partials); cudaFree(c->d_counter); cudaFree(c->d_scalars);
-   cudaFreeHost(c->h_scalars);
+   cudaFreeHost(c->h_scalars); cudaFree(c->d_stop);
    if (c->d_flush) { cudaFree(c->d_flush); }
    if (c->h_stage) { cudaFreeHost(c->h_stage); }
    for (int k = 0; k < b200_ctx::NUM_WS; k++) { if (c->ws[k]) { cudaFree(c->ws[k]); } }

@@ -1,5 +1,6 @@
 // matrix.cu -- upload of CSR blocks into the HBM layouts, ParCSR mirror, halo.
 #include "common.cuh"
+#include "p2p.cuh"
 #include <algorithm>
 #include <numeric>
 
@@ -177,6 +178,13 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
          s = dev_upload(&A->d_unpack_rows, rows.data(), rows.size());
          if (s == B200_OK) { s = dev_upload(&A->d_unpack_rp, rp.data(), rp.size()); }
          if (s == B200_OK) { s = dev_upload(&A->d_unpack_pos, order.data(), order.size()); }
+         if (s == B200_OK)
+         {
+            std::vector<int> dense((size_t)n_cols_diag + 1, 0);
+            for (int k = 0; k < A->n_send_elmts; k++) { dense[(size_t)send_map_elmts[k] + 1]++; }
+            for (int r = 0; r < n_cols_diag; r++) { dense[(size_t)r + 1] += dense[(size_t)r]; }
+            s = dev_upload(&A->d_unpack_rp_dense, dense.data(), dense.size());
+         }
       }
    }
    if (s == B200_OK && num_recvs > 0)
@@ -199,6 +207,26 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
       b200_parcsr_destroy(A);
       return s;
    }
+   if (ctx->use_p2p && (num_sends + num_recvs) > 0)
+   {
+      if (A->d_unpack_rp_dense == nullptr)
+      {
+         // this rank receives no contributions for A^T x: the fused kernel still reads a per-row list
+         std::vector<int> dense((size_t)n_cols_diag + 1, 0);
+         s = dev_upload(&A->d_unpack_rp_dense, dense.data(), dense.size());
+         if (s != B200_OK) { b200_parcsr_destroy(A); return s; }
+      }
+      // forward: I write x[send_map] into the ghost vectors of send_procs, recv_procs write into mine;
+      // reverse (A^T x): roles swapped, segments = the same starts
+      const int *sms = num_sends > 0 ? A->send_map_starts.data() : nullptr;
+      const int *rvs = num_recvs > 0 ? A->recv_vec_starts.data() : nullptr;
+      s = p2p_chan_create(ctx, num_sends, A->send_procs.data(), sms, num_recvs, A->recv_procs.data(), rvs, &A->ch_fwd);
+      if (s == B200_OK)
+      {
+         s = p2p_chan_create(ctx, num_recvs, A->recv_procs.data(), rvs, num_sends, A->send_procs.data(), sms, &A->ch_rev);
+      }
+      if (s != B200_OK) { b200_parcsr_destroy(A); return s; }
+   }
    *out = A;
    return B200_OK;
 }
@@ -207,12 +235,13 @@ extern "C" int b200_parcsr_destroy(b200_parcsr *A)
 {
    if (!A) { return B200_OK; }
    if (A->ctx) { cudaSetDevice(A->ctx->device); cudaStreamSynchronize(A->ctx->stream); cudaStreamSynchronize(A->ctx->cstream); }
+   p2p_chan_destroy(A->ch_fwd); p2p_chan_destroy(A->ch_rev);
    dmat_free(&A->diag); dmat_free(&A->offd);
    dmat_free(&A->diagT); dmat_free(&A->offdT); dmat_free(&A->lower);
    cudaFree(A->d_diagonal);
    cudaFree(A->d_send_map); cudaFree(A->d_send_buf); cudaFree(A->d_recv_buf);
    cudaFree(A->d_ghost); cudaFree(A->d_ghost_out); cudaFree(A->d_bnd_rows);
-   cudaFree(A->d_unpack_rp); cudaFree(A->d_unpack_pos); cudaFree(A->d_unpack_rows);
+   cudaFree(A->d_unpack_rp); cudaFree(A->d_unpack_pos); cudaFree(A->d_unpack_rows); cudaFree(A->d_unpack_rp_dense);
    delete A;
    return B200_OK;
 }
@@ -293,6 +322,9 @@ int halo_start(b200_parcsr *A, const double *x)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
+   // peer-memory path: pack fused with the transfer, one kernel on the compute stream; the
+   // boundary-row kernel does the waiting (p2p.cuh)
+   if (A->ch_fwd) { return p2p_put(c, A->ch_fwd, A->d_send_map, x); }
    if (A->n_send_elmts > 0)
    {
       int grid = (A->n_send_elmts + 255) / 256;
@@ -323,6 +355,7 @@ int halo_finish(b200_parcsr *A)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
+   if (A->ch_fwd) { return B200_OK; }
    CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
    return B200_OK;
 }
@@ -342,12 +375,28 @@ __global__ void halo_unpack_add_kernel(int n_rows, const int *__restrict__ rows,
       y[rows[i]] += alpha * t;
    }
 }
+// same, contributions arrive through the reverse peer-memory channel
+__global__ void halo_unpack_add_p2p_kernel(P2PChan ch, int n_rows, const int *__restrict__ rows,
+                                           const int *__restrict__ rp, const int *__restrict__ pos,
+                                           double alpha, double *__restrict__ y)
+{
+   const int par = p2p_wait_all(ch);
+   const double *buf = ch.in_buf[par];
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += gridDim.x * blockDim.x)
+   {
+      double t = 0.0;
+      for (int k = rp[i]; k < rp[i + 1]; k++) { t += __ldcg(buf + pos[k]); }
+      y[rows[i]] += alpha * t;
+   }
+   p2p_consumer_done(ch);
+}
 
 // send the ghost-column contributions back to their owners (reverse of job 1)
 int halo_reverse_start(b200_parcsr *A)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
+   if (A->ch_rev) { return p2p_put(c, A->ch_rev, nullptr, A->d_ghost_out); }
    CUDA_TRY(cudaEventRecord(c->ev_pack, c->stream));
    CUDA_TRY(cudaStreamWaitEvent(c->cstream, c->ev_pack, 0));
    NCCL_TRY(ncclGroupStart());
@@ -370,6 +419,18 @@ int halo_reverse_finish_add(b200_parcsr *A, double alpha, double *y)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
+   if (A->ch_rev)
+   {
+      if (A->n_unpack_rows > 0)
+      {
+         int grid = (A->n_unpack_rows + 255) / 256;
+         if (grid > 4 * B200_NUM_SMS) { grid = 4 * B200_NUM_SMS; }
+         LAUNCH(c, halo_unpack_add_p2p_kernel, grid, 256, 0, p2p_chan_view(A->ch_rev), A->n_unpack_rows,
+                A->d_unpack_rows, A->d_unpack_rp, A->d_unpack_pos, alpha, y);
+         CHECK_LAUNCH();
+      }
+      return B200_OK;
+   }
    CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
    if (A->n_unpack_rows > 0)
    {

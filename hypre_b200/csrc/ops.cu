@@ -130,6 +130,12 @@ int op_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, doubl
    B200_TRY(parcsr_ensure_T(A));
    b200_ctx *c = A->ctx;
    const bool comm = c->nranks > 1 && (A->num_sends + A->num_recvs) > 0;
+   if (comm && A->ch_rev)
+   {
+      // peer-memory path: offd^T x -> owners, diag^T x and the deterministic add in one launch
+      EpiMatvec e{alpha, beta, y, y};
+      return run_rows_transposed_p2p(A, x, e);
+   }
    if (comm && A->n_cols_offd > 0)
    {
       EpiMatvec eo{1.0, 0.0, nullptr, A->d_ghost_out};

@@ -1,0 +1,128 @@
+// p2p.cuh -- neighbour exchange and small all-reduce over NVLink peer memory.
+//
+// Replaces the MPI_Irecv/Isend/Waitall of hypre_ParCSRCommHandleCreate_v2/Destroy
+// (src/parcsr_mv/par_csr_communication.c:483-504,653-663) and the MPI_Allreduce of
+// hypre_ParVectorInnerProd (src/parcsr_mv/par_vector.c:526) by plain stores into the
+// receiver's HBM: every rank owns an "arena" (one cudaMalloc block, CUDA-IPC mapped by all
+// peers); a sender's pack kernel gathers x[send_map] and writes it straight into the
+// receiver's ghost vector through NVLink, then publishes a sequence number with a
+// system-scope release store; the receiver's boundary-row kernel spins on that number with
+// acquire loads before it touches the ghosts.  No library call, no extra stream, no host
+// involvement per exchange -- one exchange costs one small kernel on the sender.
+//
+// Flow control: ghost buffers are double buffered (parity of the sequence number) and the
+// consumer acknowledges with its own sequence number, so a sender may run at most two
+// exchanges ahead of a receiver.  Sequence counters live in device memory and are advanced
+// by the last block of the kernels themselves, so a launch sequence is replayable (CUDA graphs).
+// Every spin loop is bounded (P2P_SPIN_LIMIT clock ticks); on expiry the kernel sets the
+// context's device error word and continues, so a protocol bug can never hang the GPU.
+#pragma once
+#include "common.cuh"
+
+typedef unsigned long long u64;
+
+constexpr long long P2P_SPIN_LIMIT = 60000000000LL;   // ~30 s at 1.9 GHz
+
+// One direction of a neighbour exchange.  "out" = peers I write to, "in" = peers that write to me.
+struct P2PChan {
+   int      n_out, n_in;
+   int      n_out_total;          // packed elements I send
+   const int *out_starts;         // [n_out+1] segment starts in packed order          (device)
+   double **out_dst[2];           // [n_out]  remote data pointers, one per parity     (device array of peer ptrs)
+   u64    **out_flag;             // [n_out]  remote flag word of my segment           (device array of peer ptrs)
+   u64     *out_ack;              // [n_out]  local: last sequence consumed by that receiver (written remotely)
+   double  *in_buf[2];            // local receive buffers (in my arena)
+   u64     *in_flag;              // [n_in]   local: last sequence completed by that sender (written remotely)
+   u64    **in_ack;               // [n_in]   remote ack word at that sender            (device array of peer ptrs)
+   u64     *seq_put;              // local counters advanced by the kernels
+   u64     *seq_wait;
+   unsigned *ticket;              // [2] block tickets (put kernel, consumer kernel)
+   int     *err;                  // context error word
+};
+
+__device__ __forceinline__ u64 ld_acquire_sys(const u64 *p)
+{
+   u64 v;
+   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+   return v;
+}
+__device__ __forceinline__ void st_release_sys(u64 *p, u64 v)
+{
+   asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ u64 ld_relaxed_gpu(const u64 *p)
+{
+   u64 v;
+   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+   return v;
+}
+
+// spin until *p >= want (bounded)
+__device__ __forceinline__ void p2p_spin_ge(const u64 *p, u64 want, int *err)
+{
+   if (ld_acquire_sys(p) >= want) { return; }
+   const long long t0 = clock64();
+   while (ld_acquire_sys(p) < want)
+   {
+      if (clock64() - t0 > P2P_SPIN_LIMIT) { atomicExch(err, 1); break; }
+      __nanosleep(20);
+   }
+}
+
+// Consumer side, start of kernel: every block waits until all senders published the current
+// sequence.  Returns the parity of the buffer to read.  Call with all threads of the block.
+__device__ __forceinline__ int p2p_wait_all(const P2PChan &ch)
+{
+   __shared__ int s_parity;
+   if (threadIdx.x == 0)
+   {
+      const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
+      for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); }
+      s_parity = (int)(seq & 1);
+   }
+   __syncthreads();
+   return s_parity;
+}
+
+// Consumer side, end of kernel: the last block acknowledges to every sender and advances the
+// local wait counter.  Call with all threads of the block after the last read of the buffer.
+__device__ __forceinline__ void p2p_consumer_done(const P2PChan &ch)
+{
+   __shared__ bool s_last_c;
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      __threadfence();
+      s_last_c = (atomicAdd(ch.ticket + 1, 1u) == gridDim.x - 1);
+   }
+   __syncthreads();
+   if (s_last_c)
+   {
+      const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
+      for (int j = threadIdx.x; j < ch.n_in; j += blockDim.x) { st_release_sys(ch.in_ack[j], seq); }
+      __syncthreads();
+      if (threadIdx.x == 0) { *ch.seq_wait = seq; ch.ticket[1] = 0u; __threadfence(); }
+   }
+}
+
+struct b200_p2p_chan;   // host-side owner of a P2PChan (p2p.cu)
+
+// host API (p2p.cu)
+int  p2p_bootstrap(b200_ctx *c);                     // arena + IPC exchange (after the NCCL communicator exists)
+void p2p_shutdown(b200_ctx *c);
+// collective over the participating neighbours: builds one direction of an exchange.
+//   out_procs/out_starts: peers I send to and the segment boundaries of my packed data
+//   in_procs/in_starts:   peers I receive from and where their data lands in my buffer
+int  p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out_starts,
+                     int n_in, const int *in_procs, const int *in_starts, b200_p2p_chan **out);
+void p2p_chan_destroy(b200_p2p_chan *ch);
+const P2PChan &p2p_chan_view(const b200_p2p_chan *ch);
+// gather src[map[i]] (map == nullptr: src[i]) for i < n_out_total and put it into the receivers' buffers
+int  p2p_put(b200_ctx *c, b200_p2p_chan *ch, const int *map, const double *src);
+// consumer-less ranks (n_in == 0) need no call; ranks with n_in > 0 must run exactly one kernel
+// that calls p2p_wait_all + p2p_consumer_done per put.
+// d[0..cnt) <- sum over ranks, deterministic rank order, result identical on all ranks
+int  p2p_allreduce(b200_ctx *c, double *d, int cnt);
+// stream-ordered rendezvous of all ranks without a time limit (NCCL): called once at the start of a
+// solve so that ranks that are still uploading do not trip the bounded spins of the peers
+int  ctx_rendezvous(b200_ctx *c);

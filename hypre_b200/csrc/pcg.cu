@@ -5,6 +5,7 @@
 // once per iteration for the reference's convergence / breakdown logic.
 #include "ops.cuh"
 #include "vecops.cuh"
+#include "p2p.cuh"
 #include <cmath>
 #include <cfloat>
 
@@ -103,6 +104,7 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
 
 #define PCG_TRY(expr) do { status = (expr); if (status != B200_OK) goto done; } while (0)
 
+   PCG_TRY(ctx_rendezvous(c));
    // bi_prod = <b,b>  (two_norm)  |  <C b, b>
    if (two_norm) { PCG_TRY(dot_to(c, n, b, b, S_TMP)); }
    else

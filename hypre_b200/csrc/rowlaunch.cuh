@@ -1,11 +1,13 @@
 // rowlaunch.cuh -- host-side dispatch of the fused row kernels.
 #pragma once
 #include "spmv.cuh"
+#include <cstring>
 
 static inline RedCtx make_redctx(b200_ctx *ctx, double *out, int accumulate)
 {
    RedCtx rc;
    rc.partials = ctx->d_partials; rc.counter = ctx->d_counter; rc.out = out; rc.accumulate = accumulate;
+   rc.stop = ctx->d_stop;
    return rc;
 }
 
@@ -20,21 +22,31 @@ static inline int rows_grid(long long work, int per_block)
    return (int)g;
 }
 
-template <bool SKIP, class Epi>
-static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const int *offd_rp, const double *x,
+static inline HaloArgs no_halo()
+{
+   HaloArgs h;
+   memset(&h, 0, sizeof(h));
+   return h;
+}
+
+template <int HALO, class Epi>
+static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, const double *x,
                               const Epi &epi, const RedCtx &rc)
 {
    MatView V = view_of(D);
-   if (D.n_rows == 0)
+   constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
+   if (D.n_rows == 0 && !P2P)
    {
       // reductions still have to publish a zero
       if (Epi::NRED > 0 && !rc.accumulate) { CUDA_TRY(cudaMemsetAsync(rc.out, 0, sizeof(double) * Epi::NRED, ctx->stream)); }
       return B200_OK;
    }
-   if (D.layout == 1)
+   // (a rank without rows still launches in the peer-memory modes: its blocks carry the put phase
+   //  and the reduction publishes the zero)
+   if (D.layout == 1 || D.n_rows == 0)
    {
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
-      LAUNCH(ctx, (rows_kernel<0, SKIP, Epi>), grid, ROWK_BLOCK, 0, V, offd_rp, x, epi, rc);
+      LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);
    }
    else
    {
@@ -43,7 +55,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const int *offd_rp, 
 #define CASE_T(TT)                                                                            \
    case TT: {                                                                                 \
       int grid = rows_grid(D.n_rows, ROWK_BLOCK / TT);                                        \
-      LAUNCH(ctx, (rows_kernel<TT, SKIP, Epi>), grid, ROWK_BLOCK, 0, V, offd_rp, x, epi, rc); \
+      LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);       \
    } break;
          CASE_T(2) CASE_T(4) CASE_T(8) CASE_T(16) CASE_T(32)
 #undef CASE_T
@@ -57,8 +69,9 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const int *offd_rp, 
 }
 
 // t_i = (diag x_local + offd x_ghost)_i for every local row i, then epi(i, t_i).
-// Multi-rank: pack+exchange on the comm stream, interior rows meanwhile,
-// boundary rows after the ghosts landed
+// Multi-rank, peer-memory path: ONE launch (rows_kernel<.., HALO_FWD, ..>: pack + put, rows,
+// lazy wait, acknowledge).  Multi-rank, NCCL path: pack+exchange on the comm stream, interior rows
+// meanwhile, boundary rows after the ghosts landed
 // (hypre_ParCSRMatrixMatvecOutOfPlaceHost, src/parcsr_mv/par_csr_matvec.c:163-218).
 // red_out: device scalars receiving the Epi::NRED fused reductions (local sums).
 template <class Epi>
@@ -68,8 +81,16 @@ static int run_rows(b200_parcsr *A, const DMat &D, const DMat &O, bool use_halo,
    b200_ctx *ctx = A->ctx;
    if (use_halo && (A->num_sends + A->num_recvs) > 0)
    {
+      HaloArgs h = no_halo();
+      h.O = view_of(O);
+      if (A->ch_fwd)
+      {
+         h.ch = p2p_chan_view(A->ch_fwd);
+         h.map = A->d_send_map;
+         return launch_rows_layout<HALO_FWD, Epi>(ctx, D, h, x, epi, make_redctx(ctx, red_out, 0));
+      }
       B200_TRY(halo_start(A, x));
-      B200_TRY((launch_rows_layout<true, Epi>(ctx, D, O.rp, x, epi, make_redctx(ctx, red_out, 0))));
+      B200_TRY((launch_rows_layout<HALO_SKIP, Epi>(ctx, D, h, x, epi, make_redctx(ctx, red_out, 0))));
       B200_TRY(halo_finish(A));
       if (A->n_bnd > 0)
       {
@@ -80,5 +101,17 @@ static int run_rows(b200_parcsr *A, const DMat &D, const DMat &O, bool use_halo,
       }
       return B200_OK;
    }
-   return launch_rows_layout<false, Epi>(ctx, D, nullptr, x, epi, make_redctx(ctx, red_out, 0));
+   return launch_rows_layout<HALO_NONE, Epi>(ctx, D, no_halo(), x, epi, make_redctx(ctx, red_out, 0));
+}
+
+// y = alpha*diag^T x + beta*y + alpha*(contributions of the other ranks), peer-memory path, one launch
+template <class Epi>
+static int run_rows_transposed_p2p(b200_parcsr *A, const double *x, const Epi &epi)
+{
+   HaloArgs h = no_halo();
+   h.O = view_of(A->offdT);
+   h.ch = p2p_chan_view(A->ch_rev);
+   h.urp = A->d_unpack_rp_dense;
+   h.upos = A->d_unpack_pos;
+   return launch_rows_layout<HALO_REV, Epi>(A->ctx, A->diagT, h, x, epi, make_redctx(A->ctx, nullptr, 0));
 }

@@ -6,6 +6,7 @@
 // products are reduced in the same launch.
 #pragma once
 #include "common.cuh"
+#include "p2p.cuh"
 
 constexpr int ROWK_BLOCK = 256;
 
@@ -29,7 +30,10 @@ struct RedCtx {
    unsigned *counter;
    double   *out;         // device scalars, NRED consecutive
    int       accumulate;  // add to out[] instead of overwriting (second pass of a split launch)
+   const int *stop;       // device word: non-zero -> the kernel returns immediately (device-side PCG
+                          // convergence: iterations queued ahead of the host become no-ops)
 };
+#define RETURN_IF_STOPPED(rc) do { if ((rc).stop != nullptr && *(rc).stop != 0) { return; } } while (0)
 
 // Deterministic grid reduction: block partials in a fixed slot, last block to
 // finish sums them in index order.  gridDim.x <= B200_MAX_PARTIALS is
@@ -122,7 +126,12 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
 }
 
 // CSR, T lanes per row; result valid in the group's lane 0
-template <int T>
+// CG: gather x with ld.global.cg (L2 only) -- for ghost vectors that a peer GPU wrote during this
+// kernel's lifetime, which must not be served from a stale L1 / read-only cache line
+template <bool CG>
+__device__ __forceinline__ double ld_x(const double *p) { return CG ? __ldcg(p) : __ldg(p); }
+
+template <int T, bool CG = false>
 __device__ __forceinline__ double rowsum_csr(const int *__restrict__ rp, const int *__restrict__ ci,
                                              const double *__restrict__ va, int row, int sub,
                                              const double *__restrict__ x)
@@ -134,26 +143,117 @@ __device__ __forceinline__ double rowsum_csr(const int *__restrict__ rp, const i
    {
       int    c0 = ld_stream(ci + k), c1 = ld_stream(ci + k + T);
       double v0 = ld_stream(va + k), v1 = ld_stream(va + k + T);
-      double x0 = __ldg(x + c0), x1 = __ldg(x + c1);
+      double x0 = ld_x<CG>(x + c0), x1 = ld_x<CG>(x + c1);
       t = fma(v0, x0, t); t = fma(v1, x1, t);
    }
-   if (k < end) { t = fma(ld_stream(va + k), __ldg(x + ld_stream(ci + k)), t); }
+   if (k < end) { t = fma(ld_stream(va + k), ld_x<CG>(x + ld_stream(ci + k)), t); }
 #pragma unroll
    for (int o = T >> 1; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o, T); }
    return t;
 }
 
 // ---------------------------------------------------------------- kernels
-// All rows of the diag block.  T == 0: sliced ELL thread-per-row; T > 0: CSR
-// with T lanes per row.  SKIP_BND: rows that own offd entries are left to the
-// row-list kernel (they need the halo), so this launch overlaps the exchange.
-template <int T, bool SKIP_BND, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK)
-rows_kernel(MatView D, const int *__restrict__ offd_rp, const double *__restrict__ x, Epi epi, RedCtx rc)
+// What a launch does about the off-process part of the operator:
+//   HALO_NONE   single rank, or an operator without ghosts (transposes, strict lower triangle)
+//   HALO_SKIP   NCCL path: rows that own offd entries are left to rowlist_kernel (they need the
+//               halo), so this launch overlaps the library exchange running on the comm stream
+//   HALO_FWD    peer-memory path, y-type operators (hypre_ParCSRMatrixMatvecOutOfPlace,
+//               src/parcsr_mv/par_csr_matvec.c:163-218) as ONE kernel: the first blocks pack
+//               x[send_map] and store it straight into the neighbours' ghost vectors (NVLink),
+//               all blocks then stream their rows; a warp that meets a row with offd entries waits
+//               (once) for the neighbours' sequence numbers, adds the offd part from the ghost
+//               vector and goes on -- interior rows never wait, the transfer overlaps the math
+//   HALO_REV    peer-memory path, A^T x (hypre_ParCSRMatrixMatvecT, par_csr_matvec.c:287-514):
+//               the first blocks compute offd^T x and store it into the owners' receive buffers,
+//               all blocks stream diag^T; rows that receive contributions wait and add them
+//               in a fixed order (unpack lists grouped by row)
+enum { HALO_NONE = 0, HALO_SKIP = 1, HALO_FWD = 2, HALO_REV = 3 };
+
+struct HaloArgs {
+   MatView     O;        // SKIP: offd (rp only); FWD: offd block; REV: offd^T block (rows = ghost columns)
+   P2PChan     ch;       // FWD: forward channel; REV: reverse channel
+   const int  *map;      // FWD: send_map_elmts
+   const int  *urp;      // REV: [n_rows+1] contributions per local row
+   const int  *upos;     // REV: positions in the receive buffer, grouped by row
+};
+
+// sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks)
+template <int HALO>
+__device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *__restrict__ x, int n_put_blocks)
 {
+   __shared__ u64  s_seq;
+   __shared__ bool s_last_p;
+   const P2PChan &ch = h.ch;
+   if (threadIdx.x == 0)
+   {
+      const u64 seq = ld_relaxed_gpu(ch.seq_put) + 1;
+      // flow control: buffer (seq & 1) was used by exchange seq-2; wait until it was consumed
+      if (seq > 2) { for (int i = 0; i < ch.n_out; i++) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
+      s_seq = seq;
+   }
+   __syncthreads();
+   const u64 seq = s_seq;
+   double *const *dst = ch.out_dst[(int)(seq & 1)];
+   int seg = 0;
+   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ch.n_out_total; i += n_put_blocks * blockDim.x)
+   {
+      while (i >= ch.out_starts[seg + 1]) { seg++; }
+      double v;
+      if (HALO == HALO_FWD) { v = x[h.map[i]]; }      // pack: x_buf[i] = x_local[send_map_elmts[i]]
+      else
+      {
+         // row i of offd^T: contribution of my rows to ghost column i
+         v = 0.0;
+         for (int k = h.O.rp[i]; k < h.O.rp[i + 1]; k++) { v = fma(h.O.va[k], x[h.O.ci[k]], v); }
+      }
+      dst[seg][i - ch.out_starts[seg]] = v;
+   }
+   __threadfence_system();
+   __syncthreads();
+   if (threadIdx.x == 0) { s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u); }
+   __syncthreads();
+   if (s_last_p)
+   {
+      __threadfence_system();
+      for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x) { st_release_sys(ch.out_flag[i], seq); }
+      __syncthreads();
+      if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; __threadfence(); }
+   }
+}
+
+// receiver part: called by a converged warp when one of its rows needs remote data; waits once per warp
+__device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const double *cur)
+{
+   if (cur != nullptr) { return cur; }
+   int par = 0;
+   if ((threadIdx.x & 31) == 0)
+   {
+      const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
+      for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); }
+      par = (int)(seq & 1);
+   }
+   par = __shfl_sync(0xffffffffu, par, 0);
+   return ch.in_buf[par];
+}
+
+// All rows of the diag block.  T == 0: sliced ELL thread-per-row; T > 0: CSR with T lanes per row.
+template <int T, int HALO, class Epi>
+__global__ void __launch_bounds__(ROWK_BLOCK)
+rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
+{
+   RETURN_IF_STOPPED(rc);
    double red[Epi::NRED > 0 ? Epi::NRED : 1];
 #pragma unroll
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
+
+   constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
+   if (P2P && h.ch.n_out > 0)
+   {
+      int n_put_blocks = (h.ch.n_out_total + ROWK_BLOCK - 1) / ROWK_BLOCK;
+      if (n_put_blocks > (int)gridDim.x) { n_put_blocks = gridDim.x; }
+      if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks); }
+   }
+   const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
 
    if (T == 0)
    {
@@ -163,11 +263,31 @@ rows_kernel(MatView D, const int *__restrict__ offd_rp, const double *__restrict
       for (int slice = blockIdx.x * wpb + (threadIdx.x >> 5); slice < n_slices; slice += gridDim.x * wpb)
       {
          const int row = (slice << 5) + lane;
+         const bool live = row < D.n_rows;
          double t = rowsum_sell(D, slice, lane, x);
-         if (row < D.n_rows)
+         bool skip = false;
+         if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
+         if (HALO == HALO_FWD)
          {
-            if (!SKIP_BND || offd_rp[row + 1] == offd_rp[row]) { epi(row, t, red); }
+            const int ob = live ? h.O.rp[row] : 0, oe = live ? h.O.rp[row + 1] : 0;
+            if (__any_sync(0xffffffffu, oe > ob))
+            {
+               xg = halo_warp_wait(h.ch, xg);
+               for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], __ldcg(xg + h.O.ci[k]), t); }
+            }
          }
+         if (HALO == HALO_REV)
+         {
+            const int ub = live ? h.urp[row] : 0, ue = live ? h.urp[row + 1] : 0;
+            if (__any_sync(0xffffffffu, ue > ub))
+            {
+               xg = halo_warp_wait(h.ch, xg);
+               double e = 0.0;
+               for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+               t += e;
+            }
+         }
+         if (live && !skip) { epi(row, t, red); }
       }
    }
    else
@@ -180,22 +300,48 @@ rows_kernel(MatView D, const int *__restrict__ offd_rp, const double *__restrict
       for (int row = blockIdx.x * gpb + threadIdx.x / TT; row < n_pad; row += gridDim.x * gpb)
       {
          const bool live = row < D.n_rows;
-         double t = rowsum_csr<TT>(D.rp, D.ci, D.va, live ? row : D.n_rows - 1, sub, x);
-         if (live && sub == 0)
+         const int r = live ? row : D.n_rows - 1;
+         double t = rowsum_csr<TT>(D.rp, D.ci, D.va, r, sub, x);
+         bool skip = false;
+         if (HALO == HALO_SKIP) { skip = h.O.rp[r + 1] != h.O.rp[r]; }
+         if (HALO == HALO_FWD)
          {
-            if (!SKIP_BND || offd_rp[row + 1] == offd_rp[row]) { epi(row, t, red); }
+            const bool has = live && h.O.rp[r + 1] > h.O.rp[r];
+            if (__any_sync(0xffffffffu, has))
+            {
+               xg = halo_warp_wait(h.ch, xg);
+               // all lanes take part (rows without offd entries have an empty range)
+               t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg);
+            }
          }
+         if (HALO == HALO_REV)
+         {
+            const int ub = live ? h.urp[r] : 0, ue = live ? h.urp[r + 1] : 0;
+            if (__any_sync(0xffffffffu, ue > ub))
+            {
+               xg = halo_warp_wait(h.ch, xg);
+               if (sub == 0)
+               {
+                  double e = 0.0;
+                  for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+                  t += e;
+               }
+            }
+         }
+         if (live && sub == 0 && !skip) { epi(row, t, red); }
       }
    }
    grid_reduce<Epi::NRED>(red, rc);
+   if (P2P && h.ch.n_in > 0) { p2p_consumer_done(h.ch); }
 }
 
-// Rows from a list (the boundary rows): diag CSR + offd CSR, 4 lanes per row.
+// Rows from a list (the boundary rows of the NCCL path): diag CSR + offd CSR, 4 lanes per row.
 template <class Epi>
 __global__ void __launch_bounds__(ROWK_BLOCK)
 rowlist_kernel(MatView D, MatView O, const int *__restrict__ rows, int n_list,
                const double *__restrict__ x, const double *__restrict__ xg, Epi epi, RedCtx rc)
 {
+   RETURN_IF_STOPPED(rc);
    double red[Epi::NRED > 0 ? Epi::NRED : 1];
 #pragma unroll
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }

@@ -1,5 +1,6 @@
 // vecops.cu -- BLAS-1 on device (hypre_SeqVector* of src/seq_mv/vector.c).
 #include "vecops.cuh"
+#include "p2p.cuh"
 
 struct FFill  { static constexpr int NRED = 0; double a; double *y;
    __device__ void operator()(int i, double *) const { y[i] = a; } };
@@ -36,6 +37,7 @@ int vec_dot(b200_ctx *c, int n, const double *x, const double *y, double *d_out)
 int scalars_allreduce(b200_ctx *c, double *d, int cnt)
 {
    if (c->nranks <= 1 || cnt == 0) { return B200_OK; }
+   if (c->use_p2p) { return p2p_allreduce(c, d, cnt); }
    // hypre_MPI_Allreduce of hypre_ParVectorInnerProd (src/parcsr_mv/par_vector.c:526)
    NCCL_TRY(ncclAllReduce(d, d, (size_t)cnt, ncclDouble, ncclSum, c->comm, c->stream));
    return B200_OK;
@@ -45,6 +47,12 @@ int scalars_to_host(b200_ctx *c, int first, int cnt)
 {
    CUDA_TRY(cudaMemcpyAsync(c->h_scalars + first, c->d_scalars + first, sizeof(double) * (size_t)cnt,
                             cudaMemcpyDeviceToHost, c->stream));
+   if (c->use_p2p) { CUDA_TRY(cudaMemcpyAsync(c->h_err, c->d_err, sizeof(int), cudaMemcpyDeviceToHost, c->stream)); }
    CUDA_TRY(cudaStreamSynchronize(c->stream));
+   if (c->use_p2p && *c->h_err)
+   {
+      b200_set_error("peer-memory exchange timed out (a neighbour rank did not publish its halo)");
+      return B200_ERR_NCCL;
+   }
    return B200_OK;
 }
