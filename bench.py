@@ -253,6 +253,10 @@ def run_b200(args, rank, world):
     capi.check(L.b200_ctx_sync(ctx))
     R.barrier()
     launches = L.b200_ctx_launch_count(ctx) - l0
+    if os.environ.get("B200_PROFILE"):
+        buf = C.create_string_buffer(1 << 16)
+        capi.check(L.b200_prof_report(ctx, buf, len(buf)))
+        sys.stderr.write(buf.value.decode())
     iters = res.num_iterations
     dev_s = R.max(ms.value * 1e-3)                         # max over ranks
     value = n_global * iters * args.steps / dev_s

@@ -61,6 +61,7 @@ def lib():
         "b200_timer_start": (i, [vp]),
         "b200_timer_stop": (i, [vp, C.POINTER(C.c_float)]),
         "b200_flush_l2": (i, [vp]),
+        "b200_prof_report": (i, [vp, C.c_char_p, i]),
         "b200_dev_alloc": (i, [vp, ll, c_void_pp]),
         "b200_dev_free": (i, [vp, vp]),
         "b200_h2d": (i, [vp, vp, vp, ll]),

@@ -44,6 +44,7 @@ void b200_set_error(const char *fmt, ...);
    } while (0)
 
 // ---------------------------------------------------------------- context
+struct ProfSample { const char *name; cudaEvent_t e0, e1; };
 constexpr int B200_NUM_SMS      = 148;   // B200: 2 dies x 74 SMs
 constexpr int B200_MAX_RED      = 4;     // fused reductions per kernel
 constexpr int B200_MAX_PARTIALS = 8192;  // per-block partial sums kept per reduction slot
@@ -83,7 +84,16 @@ struct b200_ctx {
    double      *h_stage = nullptr;
    size_t       h_stage_n = 0;
    bool         capturing = false;
+   int          prof = 0;            // B200_PROFILE
+   std::vector<ProfSample> prof_samples;
    int         *d_stop = nullptr;     // device stop word checked by every kernel (see RedCtx::stop)
+   int         *d_iter = nullptr;     // device iteration counter of the running PCG solve
+   void        *h_ring = nullptr;     // mapped pinned ring of per-iteration records (pcg.cu)
+   void        *d_ring = nullptr;     // device alias of h_ring
+   long long    pcg_epoch = 0;
+   cudaGraphExec_t pcg_graph = nullptr;
+   const void  *pcg_graph_key[8] = {nullptr};
+   long long    pcg_graph_launches = 0;
    // cached device work vectors (PCG p/s/r, host-entry b/x, ...): grown on demand, never
    // freed before the context dies, so repeated solves do not pay cudaMalloc/cudaFree
    static constexpr int NUM_WS = 12;
@@ -97,9 +107,16 @@ int ctx_workspace(b200_ctx *c, int slot, size_t n, double **out);
 
 constexpr int B200_NUM_SCALARS = 64;
 
+// B200_PROFILE=1: every launch is bracketed by CUDA events and accounted per kernel name
+// (b200_prof_report); used to see where a multi-rank step spends its time, where ncu cannot go
+void prof_begin(b200_ctx *c, const char *name);
+void prof_end(b200_ctx *c);
+
 #define LAUNCH(ctx, kern, grid, block, smem, ...)                                   \
    do {                                                                             \
+      if ((ctx)->prof) { prof_begin((ctx), #kern); }                                \
       kern<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                \
+      if ((ctx)->prof) { prof_end((ctx)); }                                         \
       (ctx)->launches++;                                                            \
    } while (0)
 

@@ -29,6 +29,7 @@ static int ctx_init_common(b200_ctx *c, int device)
    }
    ARG_CHECK(device >= 0 && device < ndev);
    c->device = device;
+   { const char *e = getenv("B200_PROFILE"); c->prof = e ? atoi(e) : 0; }
    CUDA_TRY(cudaSetDevice(device));
    CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
    CUDA_TRY(cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking));
@@ -44,6 +45,52 @@ static int ctx_init_common(b200_ctx *c, int device)
    CUDA_TRY(cudaMallocHost((void **)&c->h_scalars, sizeof(double) * B200_NUM_SCALARS));
    CUDA_TRY(cudaMalloc((void **)&c->d_stop, sizeof(int)));
    CUDA_TRY(cudaMemset(c->d_stop, 0, sizeof(int)));
+   CUDA_TRY(cudaMalloc((void **)&c->d_iter, sizeof(int)));
+   CUDA_TRY(cudaMemset(c->d_iter, 0, sizeof(int)));
+   CUDA_TRY(cudaHostAlloc(&c->h_ring, 4096, cudaHostAllocMapped));
+   memset(c->h_ring, 0, 4096);
+   CUDA_TRY(cudaHostGetDevicePointer(&c->d_ring, c->h_ring, 0));
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- event profiler
+void prof_begin(b200_ctx *c, const char *name)
+{
+   ProfSample s;
+   s.name = name;
+   cudaEventCreate(&s.e0); cudaEventCreate(&s.e1);
+   cudaEventRecord(s.e0, c->stream);
+   c->prof_samples.push_back(s);
+}
+void prof_end(b200_ctx *c) { cudaEventRecord(c->prof_samples.back().e1, c->stream); }
+
+// text table "kernel  launches  total ms  avg us" of everything launched since the last report
+extern "C" int b200_prof_report(b200_ctx *c, char *buf, int len)
+{
+   ARG_CHECK(c != nullptr && buf != nullptr && len > 0);
+   buf[0] = 0;
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   std::vector<std::string> names; std::vector<double> tot; std::vector<long> cnt;
+   for (auto &s : c->prof_samples)
+   {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, s.e0, s.e1);
+      cudaEventDestroy(s.e0); cudaEventDestroy(s.e1);
+      size_t k = 0;
+      for (; k < names.size(); k++) { if (names[k] == s.name) { break; } }
+      if (k == names.size()) { names.push_back(s.name); tot.push_back(0.0); cnt.push_back(0); }
+      tot[k] += ms; cnt[k]++;
+   }
+   c->prof_samples.clear();
+   int off = 0;
+   double all = 0.0;
+   for (double t : tot) { all += t; }
+   off += snprintf(buf + off, len - off, "rank %d: %.3f ms in %zu kernel kinds\n", c->rank, all, names.size());
+   for (size_t k = 0; k < names.size() && off < len - 200; k++)
+   {
+      off += snprintf(buf + off, len - off, "  %-60.60s %7ld %10.3f ms %8.1f us\n", names[k].c_str(), cnt[k], tot[k],
+                      1e3 * tot[k] / (double)cnt[k]);
+   }
    return B200_OK;
 }
 
@@ -98,7 +145,9 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    if (c->hcomm) { ncclCommDestroy(c->hcomm); }
    if (c->comm) { ncclCommDestroy(c->comm); }
    cudaFree(c->d_partials); cudaFree(c->d_counter); cudaFree(c->d_scalars);
-   cudaFreeHost(c->h_scalars); cudaFree(c->d_stop);
+   cudaFreeHost(c->h_scalars); cudaFree(c->d_stop); cudaFree(c->d_iter);
+   if (c->pcg_graph) { cudaGraphExecDestroy(c->pcg_graph); }
+   if (c->h_ring) { cudaFreeHost(c->h_ring); }
    if (c->d_flush) { cudaFree(c->d_flush); }
    if (c->h_stage) { cudaFreeHost(c->h_stage); }
    for (int k = 0; k < b200_ctx::NUM_WS; k++) { if (c->ws[k]) { cudaFree(c->ws[k]); } }

@@ -10,7 +10,7 @@ static int g_lanes_override  = -1;
 extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
 {
    ARG_CHECK(layout >= -1 && layout <= 1);
-   ARG_CHECK(lanes_per_row == -1 || lanes_per_row == 2 || lanes_per_row == 4 || lanes_per_row == 8 ||
+   ARG_CHECK(lanes_per_row == -1 || lanes_per_row == 1 || lanes_per_row == 2 || lanes_per_row == 4 || lanes_per_row == 8 ||
              lanes_per_row == 16 || lanes_per_row == 32);
    g_layout_override = layout;
    g_lanes_override  = lanes_per_row;
@@ -83,7 +83,8 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    else if (m->avg_row > 24.0) { lanes = 16; }
    else if (m->avg_row > 12.0) { lanes = 8; }
    else if (m->avg_row >  5.0) { lanes = 4; }
-   else                        { lanes = 2; }
+   else if (m->avg_row >  3.0) { lanes = 2; }
+   else                        { lanes = 1; }   // interpolation-like rows (1-4 entries): thread per row
    if (g_layout_override >= 0 && allow_sell) { layout = g_layout_override; }
    if (g_lanes_override > 0) { lanes = g_lanes_override; }
    m->layout = layout; m->lanes = lanes;
@@ -322,9 +323,6 @@ int halo_start(b200_parcsr *A, const double *x)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
-   // peer-memory path: pack fused with the transfer, one kernel on the compute stream; the
-   // boundary-row kernel does the waiting (p2p.cuh)
-   if (A->ch_fwd) { return p2p_put(c, A->ch_fwd, A->d_send_map, x); }
    if (A->n_send_elmts > 0)
    {
       int grid = (A->n_send_elmts + 255) / 256;
@@ -355,7 +353,6 @@ int halo_finish(b200_parcsr *A)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
-   if (A->ch_fwd) { return B200_OK; }
    CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
    return B200_OK;
 }
@@ -375,28 +372,11 @@ __global__ void halo_unpack_add_kernel(int n_rows, const int *__restrict__ rows,
       y[rows[i]] += alpha * t;
    }
 }
-// same, contributions arrive through the reverse peer-memory channel
-__global__ void halo_unpack_add_p2p_kernel(P2PChan ch, int n_rows, const int *__restrict__ rows,
-                                           const int *__restrict__ rp, const int *__restrict__ pos,
-                                           double alpha, double *__restrict__ y)
-{
-   const int par = p2p_wait_all(ch);
-   const double *buf = ch.in_buf[par];
-   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += gridDim.x * blockDim.x)
-   {
-      double t = 0.0;
-      for (int k = rp[i]; k < rp[i + 1]; k++) { t += __ldcg(buf + pos[k]); }
-      y[rows[i]] += alpha * t;
-   }
-   p2p_consumer_done(ch);
-}
-
 // send the ghost-column contributions back to their owners (reverse of job 1)
 int halo_reverse_start(b200_parcsr *A)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
-   if (A->ch_rev) { return p2p_put(c, A->ch_rev, nullptr, A->d_ghost_out); }
    CUDA_TRY(cudaEventRecord(c->ev_pack, c->stream));
    CUDA_TRY(cudaStreamWaitEvent(c->cstream, c->ev_pack, 0));
    NCCL_TRY(ncclGroupStart());
@@ -419,18 +399,6 @@ int halo_reverse_finish_add(b200_parcsr *A, double alpha, double *y)
 {
    b200_ctx *c = A->ctx;
    if (c->nranks <= 1 || (A->num_sends + A->num_recvs) == 0) { return B200_OK; }
-   if (A->ch_rev)
-   {
-      if (A->n_unpack_rows > 0)
-      {
-         int grid = (A->n_unpack_rows + 255) / 256;
-         if (grid > 4 * B200_NUM_SMS) { grid = 4 * B200_NUM_SMS; }
-         LAUNCH(c, halo_unpack_add_p2p_kernel, grid, 256, 0, p2p_chan_view(A->ch_rev), A->n_unpack_rows,
-                A->d_unpack_rows, A->d_unpack_rp, A->d_unpack_pos, alpha, y);
-         CHECK_LAUNCH();
-      }
-      return B200_OK;
-   }
    CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
    if (A->n_unpack_rows > 0)
    {

@@ -208,64 +208,15 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
    return B200_OK;
 }
 
-// ---------------------------------------------------------------- put
-// pack (hypre: x_buf[i] = x_local[send_map_elmts[i]], par_csr_matvec.c:170-175) fused with the
-// transfer: the gathered value is stored directly into the receiver's ghost vector.
-__global__ void __launch_bounds__(256) p2p_put_kernel(P2PChan ch, const int *__restrict__ map,
-                                                      const double *__restrict__ src)
-{
-   __shared__ u64  s_seq;
-   __shared__ bool s_last;
-   if (threadIdx.x == 0)
-   {
-      const u64 seq = ld_relaxed_gpu(ch.seq_put) + 1;
-      // flow control: buffer (seq & 1) was last used by exchange seq-2; wait until it was consumed
-      if (seq > 2) { for (int i = 0; i < ch.n_out; i++) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
-      s_seq = seq;
-   }
-   __syncthreads();
-   const u64 seq = s_seq;
-   const int par = (int)(seq & 1);
-   double *const *dst = ch.out_dst[par];
-   int seg = 0;
-   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ch.n_out_total; i += gridDim.x * blockDim.x)
-   {
-      while (i >= ch.out_starts[seg + 1]) { seg++; }     // segments are few (<= 26) and i only grows
-      const double v = map ? src[map[i]] : src[i];
-      dst[seg][i - ch.out_starts[seg]] = v;
-   }
-   __threadfence_system();
-   __syncthreads();
-   if (threadIdx.x == 0) { s_last = (atomicAdd(ch.ticket, 1u) == gridDim.x - 1); }
-   __syncthreads();
-   if (s_last)
-   {
-      __threadfence_system();
-      for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x) { st_release_sys(ch.out_flag[i], seq); }
-      __syncthreads();
-      if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; __threadfence(); }
-   }
-}
-
-int p2p_put(b200_ctx *c, b200_p2p_chan *ch, const int *map, const double *src)
-{
-   const P2PChan &v = ch->v;
-   if (v.n_out == 0) { return B200_OK; }
-   int grid = (v.n_out_total + 255) / 256;
-   if (grid > 4 * B200_NUM_SMS) { grid = 4 * B200_NUM_SMS; }
-   if (grid < 1) { grid = 1; }
-   LAUNCH(c, p2p_put_kernel, grid, 256, 0, v, map, src);
-   CHECK_LAUNCH();
-   return B200_OK;
-}
-
 // ---------------------------------------------------------------- all-reduce
 // Every rank stores its contribution into slot [parity][rank] of every peer's arena, publishes
 // the sequence number, waits for all peers and sums the slots in rank order: deterministic and
 // bit-identical on all ranks.  One launch, no library call.
 __global__ void __launch_bounds__(256) p2p_allreduce_kernel(char *const *__restrict__ peer, size_t vals_off, size_t flag_off,
-                                                            int rank, int nranks, u64 *seq_p, double *d, int cnt, int *err)
+                                                            int rank, int nranks, u64 *seq_p, double *d, int cnt, int *err,
+                                                            const int *stop)
 {
+   if (*stop != 0) { return; }      // identical on all ranks (derived from all-reduced scalars)
    const u64 seq = ld_relaxed_gpu(seq_p) + 1;
    const int par = (int)(seq & 1);
    for (int t = 0; t < nranks; t++)
@@ -293,7 +244,7 @@ int p2p_allreduce(b200_ctx *c, double *d, int cnt)
 {
    if (cnt > AR_MAX) { b200_set_error("p2p_allreduce: %d > %d values", cnt, AR_MAX); return B200_ERR_ARG; }
    LAUNCH(c, p2p_allreduce_kernel, 1, 256, 0, c->d_peer_arena, c->ar_vals_off, c->ar_flag_off, c->rank, c->nranks,
-          c->d_ar_seq, d, cnt, c->d_err);
+          c->d_ar_seq, d, cnt, c->d_err, c->d_stop);
    CHECK_LAUNCH();
    return B200_OK;
 }

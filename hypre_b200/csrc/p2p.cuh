@@ -69,21 +69,6 @@ __device__ __forceinline__ void p2p_spin_ge(const u64 *p, u64 want, int *err)
    }
 }
 
-// Consumer side, start of kernel: every block waits until all senders published the current
-// sequence.  Returns the parity of the buffer to read.  Call with all threads of the block.
-__device__ __forceinline__ int p2p_wait_all(const P2PChan &ch)
-{
-   __shared__ int s_parity;
-   if (threadIdx.x == 0)
-   {
-      const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
-      for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); }
-      s_parity = (int)(seq & 1);
-   }
-   __syncthreads();
-   return s_parity;
-}
-
 // Consumer side, end of kernel: the last block acknowledges to every sender and advances the
 // local wait counter.  Call with all threads of the block after the last read of the buffer.
 __device__ __forceinline__ void p2p_consumer_done(const P2PChan &ch)
@@ -117,10 +102,8 @@ int  p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *ou
                      int n_in, const int *in_procs, const int *in_starts, b200_p2p_chan **out);
 void p2p_chan_destroy(b200_p2p_chan *ch);
 const P2PChan &p2p_chan_view(const b200_p2p_chan *ch);
-// gather src[map[i]] (map == nullptr: src[i]) for i < n_out_total and put it into the receivers' buffers
-int  p2p_put(b200_ctx *c, b200_p2p_chan *ch, const int *map, const double *src);
-// consumer-less ranks (n_in == 0) need no call; ranks with n_in > 0 must run exactly one kernel
-// that calls p2p_wait_all + p2p_consumer_done per put.
+// The put / wait / acknowledge steps themselves are device code inside the row kernels (spmv.cuh:
+// halo_put_phase, halo_warp_wait, p2p_consumer_done): one launch per operator.
 // d[0..cnt) <- sum over ranks, deterministic rank order, result identical on all ranks
 int  p2p_allreduce(b200_ctx *c, double *d, int cnt);
 // stream-ordered rendezvous of all ranks without a time limit (NCCL): called once at the start of a

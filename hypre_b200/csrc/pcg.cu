@@ -12,18 +12,29 @@
 int     amg_cycle_ptr(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result);
 
 // scalar slots in ctx->d_scalars
-enum { S_SDOTP = 8, S_IPROD = 9, S_GAMMA = 10, S_FLAG = 11, S_TMP = 12 };
+enum { S_SDOTP = 8, S_IPROD = 9, S_GAMMA_NEW = 10, S_GAMMA = 11, S_BETA = 12, S_BIPROD = 13, S_EPS = 14, S_TMP = 15,
+       S_EPOCH = 20 /* solve counter (exact in a double), tags the records of this solve */ };
 
-// x += alpha p ; r -= alpha s ; red0 = <r,r>   with alpha = gamma / sdotp computed from the
-// device-resident sdotp; the reference's breakdown guards (pcg.c:581-629) are evaluated
-// here as well so that x and r stay untouched when the reference would `break`.
+// per-iteration record the device writes into mapped pinned host memory (zero-copy): the host
+// follows the iteration without any stream synchronisation
+enum { PCG_CONVERGED = 1, PCG_ERR_CONV = 2, PCG_BRK_PRE = 4, PCG_BRK_POST = 8 };
+struct PcgRecord {
+   volatile long long ready;   // (epoch << 32) | iteration, written last
+   int    stop, flags;
+   double sdotp, i_prod, gamma_new;
+};
+constexpr int PCG_RING = 8;
+
+// x += alpha p ; r -= alpha s ; red0 = <r,r>   with alpha = gamma / sdotp from device-resident
+// scalars; the reference's breakdown guards (pcg.c:581-629) are evaluated here as well so that x and
+// r stay untouched when the reference would `break`.
 struct FPcgUpdate {
    static constexpr int NRED = 1;
-   double gamma; int skip_break; const double *scal; const double *p; const double *s; double *x; double *r;
+   int skip_break; const double *scal; const double *p; const double *s; double *x; double *r;
    __device__ void operator()(int i, double *red) const
    {
       const double sdotp = scal[S_SDOTP];
-      const double alpha = gamma / sdotp;
+      const double alpha = scal[S_GAMMA] / sdotp;
       bool stop = (sdotp == 0.0);
       if (!stop)
       {
@@ -42,11 +53,11 @@ struct FPcgUpdate {
    }
 };
 
-// p = z + beta p   (pcg.c:960-971: ScaleVector(beta,p); Axpy(1,s,p))
+// p = z + beta p   (pcg.c:960-971: ScaleVector(beta,p); Axpy(1,s,p)), beta from the device
 struct FPcgDirection {
    static constexpr int NRED = 0;
-   double beta; const double *z; double *p;
-   __device__ void operator()(int i, double *) const { p[i] = beta * p[i] + z[i]; }
+   const double *scal; const double *z; double *p;
+   __device__ void operator()(int i, double *) const { p[i] = scal[S_BETA] * p[i] + z[i]; }
 };
 
 // z = r ./ d  (HYPRE_ParCSRDiagScale) and red0 = <r,z>
@@ -60,6 +71,56 @@ struct FDiagScaleDot {
       red[0] = fma(r[i], zi, red[0]);
    }
 };
+
+// The scalar logic of one iteration of hypre_PCGSolve (pcg.c:581-629 alpha guards, :745-843
+// convergence test, :845-883 gamma guards, :960 beta) on the device: one thread.  Sets the stop
+// word that turns every later kernel into a no-op, publishes the record for the host.
+__global__ void pcg_check_kernel(double *scal, int *stop, int *iter, PcgRecord *ring,
+                                 int two_norm, int skip_break, int max_iter)
+{
+   if (*stop != 0) { return; }
+   const long long epoch = (long long)scal[S_EPOCH];
+   const int i = *iter + 1;
+   const double sdotp = scal[S_SDOTP], gamma = scal[S_GAMMA];
+   int flags = 0, st = 0;
+   double gamma_new = 0.0, i_prod = 0.0;
+   bool brk = false;
+   if (sdotp == 0.0) { flags |= PCG_ERR_CONV; brk = true; }
+   else
+   {
+      const double alpha = gamma / sdotp;
+      if (alpha <= 0.0)                              { flags |= PCG_ERR_CONV; brk = skip_break < 3; }
+      else if (!(alpha >= 4.9406564584124654e-324))  { flags |= PCG_ERR_CONV; brk = skip_break < 2; }
+      else if (!(alpha >= DBL_MIN))                  { flags |= PCG_ERR_CONV; brk = skip_break < 1; }
+   }
+   if (brk) { flags |= PCG_BRK_PRE; st = 1; }
+   else
+   {
+      gamma_new = scal[S_GAMMA_NEW];
+      i_prod = two_norm ? scal[S_IPROD] : gamma_new;
+      if (i_prod / scal[S_BIPROD] < scal[S_EPS]) { flags |= PCG_CONVERGED; st = 1; }
+      else
+      {
+         bool gb = false;
+         if (gamma_new <= 0.0)                              { flags |= PCG_ERR_CONV; gb = skip_break < 3; }
+         else if (!(gamma_new >= 4.9406564584124654e-324))  { flags |= PCG_ERR_CONV; gb = skip_break < 2; }
+         else if (!(gamma_new >= DBL_MIN))                  { flags |= PCG_ERR_CONV; gb = skip_break < 1; }
+         if (gb) { flags |= PCG_BRK_POST; st = 1; }
+         else
+         {
+            scal[S_BETA] = gamma_new / gamma;
+            scal[S_GAMMA] = gamma_new;
+            if (i >= max_iter) { st = 1; }
+         }
+      }
+   }
+   *iter = i;
+   if (st) { *stop = 1; }
+   PcgRecord *rec = ring + (i % PCG_RING);
+   rec->stop = st; rec->flags = flags; rec->sdotp = sdotp; rec->i_prod = i_prod; rec->gamma_new = gamma_new;
+   __threadfence_system();
+   rec->ready = (epoch << 32) | (long long)i;
+}
 
 static int dot_to(b200_ctx *c, int n, const double *x, const double *y, int slot)
 {
@@ -82,6 +143,110 @@ static int apply_precond(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_
    return b200_vec_copy(c, n, r, z);   // identity: hypre_ParKrylovIdentity
 }
 
+// ---- one iteration, enqueued on the compute stream without any host synchronisation
+struct PcgIter {
+   b200_ctx *c; b200_parcsr *A; b200_amg *amg; const b200_pcg_params *prm;
+   int n; double *p, *s, *r, *x; long long epoch;
+};
+
+static int pcg_enqueue_iteration(const PcgIter &it)
+{
+   b200_ctx *c = it.c;
+   double *z = nullptr;
+   // s = A p ; sdotp = <s,p>
+   B200_TRY(op_matvec_dot(it.A, it.p, it.s, c->d_scalars + S_SDOTP));
+   B200_TRY(scalars_allreduce(c, c->d_scalars + S_SDOTP, 1));
+   // x += alpha p ; r -= alpha s ; <r,r>
+   {
+      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r};
+      B200_TRY(run_ewise(c, it.n, f, c->d_scalars + S_IPROD));
+   }
+   // s = C r ; gamma = <r,s>
+   B200_TRY(apply_precond(c, it.A, it.amg, it.prm, it.r, it.s, &z));
+   if (!it.amg && it.prm->diag_scale)
+   {
+      CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_GAMMA_NEW, c->d_scalars + S_TMP, sizeof(double),
+                               cudaMemcpyDeviceToDevice, c->stream));
+   }
+   else { B200_TRY(dot_to(c, it.n, it.r, z, S_GAMMA_NEW)); }
+   B200_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 2));
+   // scalar logic + record for the host
+   LAUNCH(c, pcg_check_kernel, 1, 1, 0, c->d_scalars, c->d_stop, c->d_iter, (PcgRecord *)c->d_ring,
+          it.prm->two_norm, it.prm->skip_break, it.prm->max_iter);
+   CHECK_LAUNCH();
+   // p = s + beta p
+   {
+      FPcgDirection f{c->d_scalars, z, it.p};
+      B200_TRY(run_ewise(c, it.n, f, nullptr));
+   }
+   return B200_OK;
+}
+
+// The iteration is identical from one trip to the next (all scalars live on the device), so it is
+// captured once into a CUDA graph and replayed: one graph launch instead of ~75 kernel launches.
+static bool pcg_graph_enabled(const b200_ctx *c)
+{
+   static int env = -1;
+   if (env < 0) { const char *e = getenv("B200_GRAPH"); env = e ? atoi(e) : 1; }
+   // the NCCL halo path forks onto the comm stream; keep it on plain launches
+   return env != 0 && !c->prof && (c->nranks == 1 || c->use_p2p);
+}
+
+static int pcg_launch_iteration(const PcgIter &it, int i)
+{
+   b200_ctx *c = it.c;
+   // iteration 1 runs on plain launches: it triggers every lazy allocation (transposes, workspaces)
+   if (!pcg_graph_enabled(c) || i < 2) { return pcg_enqueue_iteration(it); }
+   const void *key[8] = {it.A, it.amg, it.x, it.p, it.s, it.r,
+                         (const void *)(size_t)(it.prm->two_norm * 64 + it.prm->skip_break * 8 + it.prm->diag_scale),
+                         (const void *)(size_t)it.prm->max_iter};
+   if (c->pcg_graph == nullptr || memcmp(key, c->pcg_graph_key, sizeof(key)) != 0)
+   {
+      if (c->pcg_graph) { cudaGraphExecDestroy(c->pcg_graph); c->pcg_graph = nullptr; }
+      cudaGraph_t g = nullptr;
+      const long long l0 = c->launches;
+      CUDA_TRY(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      int st = pcg_enqueue_iteration(it);
+      cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+      c->pcg_graph_launches = c->launches - l0;
+      c->launches = l0;
+      if (st != B200_OK) { if (g) { cudaGraphDestroy(g); } return st; }
+      CUDA_TRY(e);
+      CUDA_TRY(cudaGraphInstantiate(&c->pcg_graph, g, 0));
+      CUDA_TRY(cudaGraphDestroy(g));
+      memcpy(c->pcg_graph_key, key, sizeof(key));
+   }
+   CUDA_TRY(cudaGraphLaunch(c->pcg_graph, c->stream));
+   c->launches += c->pcg_graph_launches;
+   return B200_OK;
+}
+
+// wait (host spin on mapped pinned memory) until the device published iteration i of this solve
+static int pcg_wait_record(b200_ctx *c, long long epoch, int i, PcgRecord *out)
+{
+   volatile PcgRecord *rec = (volatile PcgRecord *)c->h_ring + (i % PCG_RING);
+   const long long want = (epoch << 32) | (long long)i;
+   unsigned long long spins = 0;
+   while (rec->ready != want)
+   {
+      if ((++spins & 0x3fff) == 0)
+      {
+         cudaError_t q = cudaStreamQuery(c->stream);
+         if (q != cudaSuccess && q != cudaErrorNotReady) { CUDA_TRY(q); }
+         if (q == cudaSuccess && rec->ready != want)
+         {
+            // stream drained without publishing: the stop word was already set (cannot happen in a
+            // healthy run) -- report instead of spinning forever
+            b200_set_error("PCG iteration %d was never published by the device", i);
+            return B200_ERR_CUDA;
+         }
+      }
+   }
+   out->stop = rec->stop; out->flags = rec->flags; out->sdotp = rec->sdotp; out->i_prod = rec->i_prod;
+   out->gamma_new = rec->gamma_new;
+   return B200_OK;
+}
+
 extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_pcg_params *prm,
                               const double *b, double *x, b200_pcg_result *res,
                               double *norms_h, double *rel_norms_h)
@@ -98,12 +263,17 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
    B200_TRY(ctx_workspace(c, WS_PCG_S, n, &s));
    B200_TRY(ctx_workspace(c, WS_PCG_R, n, &r));
    int status = B200_OK;
-   int i = 0;
-   double bi_prod = 0.0, i_prod = 0.0, i_prod_0 = 0.0, gamma = 0.0, gamma_old = 0.0, eps = 0.0;
+   int i = 0, queued = 0;
+   double bi_prod = 0.0, i_prod = 0.0, i_prod_0 = 0.0, gamma = 0.0, eps = 0.0;
    double *z = nullptr;
+   const long long epoch = ++c->pcg_epoch;
+   PcgIter it{c, A, amg, prm, n, p, s, r, x, epoch};
+   constexpr int LOOKAHEAD = 1;     // iterations queued beyond the one the host is waiting for
 
 #define PCG_TRY(expr) do { status = (expr); if (status != B200_OK) goto done; } while (0)
 
+   CUDA_TRY(cudaMemsetAsync(c->d_stop, 0, sizeof(int), c->stream));
+   CUDA_TRY(cudaMemsetAsync(c->d_iter, 0, sizeof(int), c->stream));
    PCG_TRY(ctx_rendezvous(c));
    // bi_prod = <b,b>  (two_norm)  |  <C b, b>
    if (two_norm) { PCG_TRY(dot_to(c, n, b, b, S_TMP)); }
@@ -143,74 +313,46 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
    if (z != p) { PCG_TRY(b200_vec_copy(c, n, z, p)); }
    PCG_TRY(dot_to(c, n, r, p, S_GAMMA));
    PCG_TRY(dot_to(c, n, r, r, S_IPROD));
-   PCG_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 2));
-   PCG_TRY(scalars_to_host(c, S_IPROD, 2));
+   // S_IPROD (9) and S_GAMMA (11) are not adjacent: reduce the span 9..11 (S_GAMMA_NEW is scratch here)
+   PCG_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 3));
+   PCG_TRY(scalars_to_host(c, S_IPROD, 3));
    gamma = h[S_GAMMA];
    if (gamma != 0.0 && !(gamma / gamma == gamma / gamma)) { res->error_flag = 1; goto done; }
    i_prod_0 = two_norm ? h[S_IPROD] : gamma;
    if (norms_h) { norms_h[0] = sqrt(i_prod_0); }
+   // device-resident constants of the stopping rule
+   h[S_BIPROD] = bi_prod; h[S_EPS] = eps; h[S_EPOCH] = (double)epoch;
+   CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_BIPROD, h + S_BIPROD, 2 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+   CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_EPOCH, h + S_EPOCH, sizeof(double), cudaMemcpyHostToDevice, c->stream));
 
-   while ((i + 1) <= prm->max_iter)
+   while (i < prm->max_iter)
    {
+      // keep the device fed: queue up to LOOKAHEAD iterations beyond the one we wait for
+      while (queued < prm->max_iter && queued <= i + LOOKAHEAD) { PCG_TRY(pcg_launch_iteration(it, ++queued)); }
+      PcgRecord rec;
+      PCG_TRY(pcg_wait_record(c, epoch, i + 1, &rec));
       i++;
-      // s = A p ; sdotp = <s,p>
-      PCG_TRY(op_matvec_dot(A, p, s, c->d_scalars + S_SDOTP));
-      PCG_TRY(scalars_allreduce(c, c->d_scalars + S_SDOTP, 1));
-      // x += alpha p ; r -= alpha s ; <r,r>
-      {
-         FPcgUpdate f{gamma, prm->skip_break, c->d_scalars, p, s, x, r};
-         PCG_TRY(run_ewise(c, n, f, c->d_scalars + S_IPROD));
-      }
-      // s = C r ; gamma = <r,s>
-      PCG_TRY(apply_precond(c, A, amg, prm, r, s, &z));
-      if (!amg && prm->diag_scale)
-      {
-         CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_GAMMA, c->d_scalars + S_TMP, sizeof(double),
-                                  cudaMemcpyDeviceToDevice, c->stream));
-      }
-      else { PCG_TRY(dot_to(c, n, r, z, S_GAMMA)); }
-      PCG_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 2));
-      PCG_TRY(scalars_to_host(c, S_SDOTP, 3));
-
-      // ---- host-side logic of the reference on the three scalars
-      {
-         const double sdotp = h[S_SDOTP];
-         bool brk = false;
-         if (sdotp == 0.0) { res->error_flag |= 256; brk = true; }
-         else
-         {
-            const double alpha = gamma / sdotp;
-            if (alpha <= 0.0)                                  { res->error_flag |= 256; brk = prm->skip_break < 3; }
-            else if (!(alpha >= 4.9406564584124654e-324))      { res->error_flag |= 256; brk = prm->skip_break < 2; }
-            else if (!(alpha >= DBL_MIN))                      { res->error_flag |= 256; brk = prm->skip_break < 1; }
-         }
-         if (brk) { if (i == 1) { i_prod = i_prod_0; } break; }
-      }
-      gamma_old = gamma;
-      gamma = h[S_GAMMA];
-      i_prod = two_norm ? h[S_IPROD] : gamma;
+      if (rec.flags & PCG_ERR_CONV) { res->error_flag |= 256; }
+      if (rec.flags & PCG_BRK_PRE) { if (i == 1) { i_prod = i_prod_0; } break; }
+      gamma = rec.gamma_new;
+      i_prod = rec.i_prod;
       if (norms_h) { norms_h[i] = sqrt(i_prod); }
       if (rel_norms_h) { rel_norms_h[i] = bi_prod ? sqrt(i_prod / bi_prod) : 0.0; }
-
-      if (i_prod / bi_prod < eps) { res->converged = 1; break; }
-
-      if (gamma <= 0.0)                                   { res->error_flag |= 256; if (prm->skip_break < 3) { if (i == 1) { i_prod = i_prod_0; } break; } }
-      else if (!(gamma >= 4.9406564584124654e-324))       { res->error_flag |= 256; if (prm->skip_break < 2) { if (i == 1) { i_prod = i_prod_0; } break; } }
-      else if (!(gamma >= DBL_MIN))                       { res->error_flag |= 256; if (prm->skip_break < 1) { if (i == 1) { i_prod = i_prod_0; } break; } }
-
-      // p = s + beta p
-      {
-         FPcgDirection f{gamma / gamma_old, z, p};
-         PCG_TRY(run_ewise(c, n, f, nullptr));
-      }
+      if (rec.flags & PCG_CONVERGED) { res->converged = 1; break; }
+      if (rec.flags & PCG_BRK_POST) { if (i == 1) { i_prod = i_prod_0; } break; }
    }
    if (i >= prm->max_iter && (i_prod / bi_prod) >= eps && eps > 0) { res->error_flag |= 256; }
    res->num_iterations = i;
    res->rel_residual_norm = bi_prod > 0.0 ? sqrt(i_prod / bi_prod) : 0.0;
+   (void)gamma;
 
 done:
 #undef PCG_TRY
+   // drain (iterations queued past the stop are no-ops), then re-arm the kernels for other callers
    cudaStreamSynchronize(c->stream);
+   cudaMemsetAsync(c->d_stop, 0, sizeof(int), c->stream);
+   cudaStreamSynchronize(c->stream);
+   if (status == B200_OK && c->use_p2p && c->h_err && *c->h_err) { status = B200_ERR_NCCL; }
    return status;
 }
 

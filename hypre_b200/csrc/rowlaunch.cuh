@@ -57,7 +57,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
       int grid = rows_grid(D.n_rows, ROWK_BLOCK / TT);                                        \
       LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);       \
    } break;
-         CASE_T(2) CASE_T(4) CASE_T(8) CASE_T(16) CASE_T(32)
+         CASE_T(1) CASE_T(2) CASE_T(4) CASE_T(8) CASE_T(16) CASE_T(32)
 #undef CASE_T
          default:
             b200_set_error("unsupported lanes_per_row %d", D.lanes);

@@ -50,6 +50,9 @@ long long b200_ctx_launch_count(const b200_ctx *ctx);
 /* CUDA-event timing on the library's own compute stream (ms) */
 int b200_timer_start(b200_ctx *ctx);
 int b200_timer_stop(b200_ctx *ctx, float *ms);
+/* B200_PROFILE=1 in the environment brackets every launch with CUDA events; this returns the
+ * per-kernel table (launches, total ms, average us) accumulated since the last call */
+int b200_prof_report(b200_ctx *ctx, char *buf, int len);
 /* write `bytes` of scratch (evicts L2 between timed iterations) */
 int b200_flush_l2(b200_ctx *ctx);
 

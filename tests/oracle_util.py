@@ -159,6 +159,11 @@ CASES = {
     "lap7_24_rlx16": dict(gen="laplacian", dims=(24, 24, 24), rlx=16),
     "lap27_20_rlx11": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=11),
     "lap27_20_rlx12": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=12),
+    # W- and F-cycles, two sweeps, weighted Jacobi (no goldens: checked against the reference in-process)
+    "lap7_24_rlx18_W": dict(gen="laplacian", dims=(24, 24, 24), rlx=18, opts={"CycleType": 2}),
+    "lap7_24_rlx16_F": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"FCycle": 1}),
+    "lap27_20_rlx18_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=18, opts={"NumSweeps": 2}),
+    "lap7_24_rlx7_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxWt": 0.8}),
 }
 
 IJ_ARGS = {

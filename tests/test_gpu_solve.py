@@ -233,6 +233,55 @@ def test_pcg_matches_oracle_and_golden(H, ctx, cases, name):
     assert vec_err(x.numpy(), xo) < 1e-8
 
 
+@pytest.mark.parametrize("name", ["lap7_24_rlx18_W", "lap7_24_rlx16_F", "lap27_20_rlx18_ns2", "lap7_24_rlx7_w08"])
+def test_pcg_cycle_variants_match_oracle_and_reference(H, ctx, cases, name):
+    """W-cycle, F-cycle, two sweeps per level, weighted Jacobi (relax_type 7): device vs oracle vs the
+    reference's own hypre_PCGSolve in-process on the same hierarchy"""
+    A, b, x, amg, pcg = cases(name)
+    out = {}
+    for dev in (True, False):
+        H.set_device_path(dev)
+        x.numpy()[:] = 0.0
+        H.clear_errors()
+        pcg.Solve(A, b, x)
+        assert H.error_flag() == 0
+        out[dev] = (pcg.num_iterations, pcg.rel_norms(), x.numpy().copy())
+    H.set_device_path(True)
+    orc = O.OracleAMG(amg)
+    xo, ito, relo, conv = orc.pcg(b.numpy(), np.zeros(A.global_rows))
+    orc.destroy()
+    assert out[True][0] == out[False][0] == ito
+    np.testing.assert_allclose(out[True][1], out[False][1], rtol=NORM_TOL)
+    np.testing.assert_allclose(out[True][1], relo, rtol=NORM_TOL)
+    assert vec_err(out[True][2], out[False][2]) < 1e-8
+
+
+def test_pcg_nan_input_is_reported_like_the_reference(H, ctx, cases):
+    """pcg.c:425-445: INFs/NaNs in b -> hypre_error(HYPRE_ERROR_GENERIC), no iteration"""
+    A, b, x, amg, pcg = cases("lap7_32_rlx18")
+    bad = A.vector(1.0)
+    bad.numpy()[7] = np.nan
+    x.numpy()[:] = 0.0
+    H.clear_errors()
+    pcg.Solve(A, bad, x)
+    assert H.error_flag() & 1
+    H.clear_errors()
+    bad.destroy()
+
+
+def test_repeated_solves_reuse_the_graph_and_stay_identical(H, ctx, cases):
+    """the captured iteration graph is replayed by later solves: results must be bit-identical"""
+    A, b, x, amg, pcg = cases("lap7_32_rlx18")
+    hist = []
+    for _ in range(3):
+        x.numpy()[:] = 0.0
+        H.clear_errors()
+        pcg.Solve(A, b, x)
+        hist.append((pcg.num_iterations, pcg.rel_norms().copy(), x.numpy().copy()))
+    for h in hist[1:]:
+        assert h[0] == hist[0][0] and np.array_equal(h[1], hist[0][1]) and np.array_equal(h[2], hist[0][2])
+
+
 @pytest.mark.parametrize("precond", ["diag", "none"])
 def test_pcg_diag_scale_and_identity_match_reference(H, ctx, precond):
     """ij -solver 2 (DS-PCG) and unpreconditioned CG against the reference in-process"""
