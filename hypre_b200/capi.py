@@ -93,6 +93,7 @@ def lib():
         "b200_amg_destroy": (i, [vp]),
         "b200_amg_set_level": (i, [vp, i, vp, vp]),
         "b200_amg_set_cycle": (i, [vp, vp, vp, i, i]),
+        "b200_amg_set_replicated_from": (i, [vp, i]),
         "b200_amg_set_level_relax": (i, [vp, i, d, vp]),
         "b200_amg_set_level_cheby": (i, [vp, i, vp, vp, i, i]),
         "b200_amg_set_coarse_dense": (i, [vp, i, vp, i, vp]),

@@ -28,6 +28,11 @@ struct b200_amg {
    std::vector<int> coarse_rows_per_rank;
    double *d_Ainv = nullptr;   // this rank's rows of A_mat^{-1}: [n_local x coarse_n]
    double *d_fall = nullptr;   // gathered coarse rhs [coarse_n]
+   // levels >= repl_level are REPLICATED on every rank (full matrices, no communication): the
+   // counterpart of the reference's seq_threshold / hypre_seqAMGCycle (src/parcsr_ls/par_cycle.c:362-369).
+   // The level above holds P with global coarse columns; restriction onto repl_level is followed by
+   // a vector all-reduce, prolongation from it is local.
+   int  repl_level = 1 << 30;
    bool finalized = false;
 };
 
@@ -61,6 +66,13 @@ extern "C" int b200_amg_set_level(b200_amg *a, int level, b200_parcsr *A, b200_p
    ARG_CHECK(a != nullptr && level >= 0 && level < a->num_levels && A != nullptr);
    ARG_CHECK((level == a->num_levels - 1) == (P == nullptr));
    a->L[level].A = A; a->L[level].P = P; a->L[level].n = A->n_rows;
+   return B200_OK;
+}
+
+extern "C" int b200_amg_set_replicated_from(b200_amg *a, int level)
+{
+   ARG_CHECK(a != nullptr && level >= 1);
+   a->repl_level = level;
    return B200_OK;
 }
 
@@ -255,7 +267,7 @@ static int coarse_dense_solve(b200_amg *a, const double *f, double *u)
    b200_ctx *c = a->ctx;
    const int n_local = a->coarse_rows_per_rank[c->rank];
    if (a->coarse_n == 0) { return B200_OK; }
-   if (c->nranks > 1)
+   if (c->nranks > 1 && a->repl_level > a->num_levels - 1)
    {
       // hypre_MPI_Allgatherv of the coarse rhs (src/parcsr_ls/par_gauss_elim.c:575-576):
       // every rank contributes its slice into a zeroed vector, summed over ranks
@@ -358,6 +370,14 @@ static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_gues
          if (s.zero[fine]) { r = F[fine]; }   // f - A*0 == f
          else { B200_TRY(op_matvec(L.A, -1.0, U_cur(s, fine), 1.0, F[fine], a->Vtemp)); }
          B200_TRY(op_matvecT(L.P, 1.0, r, 0.0, a->L[coarse].F));
+         if (coarse == a->repl_level && a->ctx->nranks > 1)
+         {
+            // every rank restricted its own rows onto the whole coarse level: sum over ranks
+            b200_ctx *c = a->ctx;
+            const int nc = a->L[coarse].n;
+            if (c->use_p2p && nc <= p2p_allreduce_vec_max()) { B200_TRY(p2p_allreduce_vec(c, a->L[coarse].F, nc)); }
+            else { NCCL_TRY(ncclAllReduce(a->L[coarse].F, a->L[coarse].F, (size_t)nc, ncclDouble, ncclSum, c->comm, c->stream)); }
+         }
          ++level;
          lev_counter[level] = lev_counter[level] > a->cycle_type ? lev_counter[level] : a->cycle_type;
          cycle_param = (level == nl - 1) ? 3 : 1;

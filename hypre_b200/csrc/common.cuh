@@ -68,7 +68,7 @@ struct b200_ctx {
    size_t       arena_bytes = 0, arena_used = 0;
    std::vector<char *> peer_arena;
    char       **d_peer_arena = nullptr;
-   size_t       ar_vals_off = 0, ar_flag_off = 0;
+   size_t       ar_vals_off = 0, ar_flag_off = 0, arb_vals_off = 0, arb_flag_off = 0;
    unsigned long long *d_ar_seq = nullptr;
    int         *d_err = nullptr;      // set by a kernel whose bounded spin expired
    int         *h_err = nullptr;      // pinned mirror
@@ -204,6 +204,8 @@ struct b200_parcsr {
    double *d_recv_buf  = nullptr;  // [n_send_elmts]
    // deterministic unpack plan for job 2: CSR of (local row -> positions in recv buf)
    int    *d_unpack_rp = nullptr, *d_unpack_pos = nullptr;
+   unsigned char *d_grp_fwd = nullptr;    // [ceil(n_rows/32)] group has a row with offd entries
+   unsigned char *d_grp_rev = nullptr;    // [ceil(n_cols_diag/32)] group has a row receiving A^T contributions
    int    *d_unpack_rp_dense = nullptr;   // [n_cols_diag+1]: the same lists indexed by local row (fused kernel)
    int     n_unpack_rows = 0;
    int    *d_unpack_rows = nullptr;

@@ -210,6 +210,15 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
    }
    if (ctx->use_p2p && (num_sends + num_recvs) > 0)
    {
+      std::vector<unsigned char> gf((size_t)(n_rows + 31) / 32 + 1, 0), gr((size_t)(n_cols_diag + 31) / 32 + 1, 0);
+      if (n_cols_offd > 0)
+      {
+         for (int r = 0; r < n_rows; r++) { if (A->h_offd.i[r + 1] > A->h_offd.i[r]) { gf[(size_t)r >> 5] = 1; } }
+      }
+      for (int k = 0; k < A->n_send_elmts; k++) { gr[(size_t)send_map_elmts[k] >> 5] = 1; }
+      s = dev_upload(&A->d_grp_fwd, gf.data(), gf.size());
+      if (s == B200_OK) { s = dev_upload(&A->d_grp_rev, gr.data(), gr.size()); }
+      if (s != B200_OK) { b200_parcsr_destroy(A); return s; }
       if (A->d_unpack_rp_dense == nullptr)
       {
          // this rank receives no contributions for A^T x: the fused kernel still reads a per-row list
@@ -242,7 +251,7 @@ extern "C" int b200_parcsr_destroy(b200_parcsr *A)
    cudaFree(A->d_diagonal);
    cudaFree(A->d_send_map); cudaFree(A->d_send_buf); cudaFree(A->d_recv_buf);
    cudaFree(A->d_ghost); cudaFree(A->d_ghost_out); cudaFree(A->d_bnd_rows);
-   cudaFree(A->d_unpack_rp); cudaFree(A->d_unpack_pos); cudaFree(A->d_unpack_rows); cudaFree(A->d_unpack_rp_dense);
+   cudaFree(A->d_unpack_rp); cudaFree(A->d_unpack_pos); cudaFree(A->d_unpack_rows); cudaFree(A->d_unpack_rp_dense); cudaFree(A->d_grp_fwd); cudaFree(A->d_grp_rev);
    delete A;
    return B200_OK;
 }

@@ -25,7 +25,9 @@ static int arena_alloc(b200_ctx *c, size_t bytes, size_t *off)
    return B200_OK;
 }
 
-constexpr int AR_MAX = 256;     // doubles per all-reduce
+constexpr int AR_MAX = 256;     // doubles per small all-reduce (dots, coarse rhs)
+constexpr int AR_BIG_MAX = 1 << 18;   // doubles per vector all-reduce (restriction onto a replicated level)
+constexpr int AR_BIG_GRID = 2 * B200_NUM_SMS;   // all blocks must be co-resident (they wait on one another)
 
 int p2p_bootstrap(b200_ctx *c)
 {
@@ -79,8 +81,10 @@ int p2p_bootstrap(b200_ctx *c)
    // all-reduce slots: vals[2][nranks][AR_MAX] doubles, flag[nranks] u64, then a local seq word
    B200_TRY(arena_alloc(c, sizeof(double) * 2 * (size_t)c->nranks * AR_MAX, &c->ar_vals_off));
    B200_TRY(arena_alloc(c, sizeof(u64) * (size_t)c->nranks, &c->ar_flag_off));
-   CUDA_TRY(cudaMalloc((void **)&c->d_ar_seq, sizeof(u64)));
-   CUDA_TRY(cudaMemset(c->d_ar_seq, 0, sizeof(u64)));
+   B200_TRY(arena_alloc(c, sizeof(double) * 2 * (size_t)c->nranks * AR_BIG_MAX, &c->arb_vals_off));
+   B200_TRY(arena_alloc(c, sizeof(u64) * (size_t)c->nranks, &c->arb_flag_off));
+   CUDA_TRY(cudaMalloc((void **)&c->d_ar_seq, 4 * sizeof(u64)));     // [0] small seq, [1] big seq, [2..3] big tickets
+   CUDA_TRY(cudaMemset(c->d_ar_seq, 0, 4 * sizeof(u64)));
    B200_TRY(dev_upload(&c->d_peer_arena, c->peer_arena.data(), c->peer_arena.size()));
    c->use_p2p = 1;
    return B200_OK;
@@ -245,6 +249,61 @@ int p2p_allreduce(b200_ctx *c, double *d, int cnt)
    if (cnt > AR_MAX) { b200_set_error("p2p_allreduce: %d > %d values", cnt, AR_MAX); return B200_ERR_ARG; }
    LAUNCH(c, p2p_allreduce_kernel, 1, 256, 0, c->d_peer_arena, c->ar_vals_off, c->ar_flag_off, c->rank, c->nranks,
           c->d_ar_seq, d, cnt, c->d_err, c->d_stop);
+   CHECK_LAUNCH();
+   return B200_OK;
+}
+
+// Vector all-reduce (n <= AR_BIG_MAX): same protocol with several blocks.  Block b owns the elements
+// k = b*256 + tid (grid stride) in both phases; the last block to finish its stores publishes the
+// sequence number, every block then waits for all ranks and sums its elements in rank order.
+__global__ void __launch_bounds__(256) p2p_allreduce_big_kernel(char *const *__restrict__ peer, size_t vals_off, size_t flag_off,
+                                                                int rank, int nranks, u64 *seq_p, unsigned *tickets,
+                                                                double *d, int n, int *err, const int *stop)
+{
+   if (*stop != 0) { return; }
+   __shared__ bool s_last;
+   const u64 seq = ld_relaxed_gpu(seq_p) + 1;
+   const int par = (int)(seq & 1);
+   for (int t = 0; t < nranks; t++)
+   {
+      double *slot = (double *)(peer[t] + vals_off) + ((size_t)par * nranks + rank) * AR_BIG_MAX;
+      for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) { slot[k] = d[k]; }
+   }
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      __threadfence_system();
+      s_last = (atomicAdd(tickets, 1u) == gridDim.x - 1);
+   }
+   __syncthreads();
+   if (s_last && threadIdx.x < nranks) { st_release_sys((u64 *)(peer[threadIdx.x] + flag_off) + rank, seq); }
+   if (threadIdx.x < nranks) { p2p_spin_ge((const u64 *)(peer[rank] + flag_off) + threadIdx.x, seq, err); }
+   __syncthreads();
+   const double *mine = (const double *)(peer[rank] + vals_off) + (size_t)par * nranks * AR_BIG_MAX;
+   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+   {
+      double s = 0.0;
+      for (int t = 0; t < nranks; t++) { s += __ldcg(mine + (size_t)t * AR_BIG_MAX + k); }
+      d[k] = s;
+   }
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      // second ticket: the last block to finish advances the sequence and re-arms the tickets
+      if (atomicAdd(tickets + 1, 1u) == gridDim.x - 1) { *seq_p = seq; tickets[0] = 0u; tickets[1] = 0u; __threadfence(); }
+   }
+}
+
+int p2p_allreduce_vec_max(void) { return AR_BIG_MAX; }
+
+int p2p_allreduce_vec(b200_ctx *c, double *d, int n)
+{
+   if (n > AR_BIG_MAX) { b200_set_error("p2p_allreduce_vec: %d > %d values", n, AR_BIG_MAX); return B200_ERR_ARG; }
+   if (n <= 0) { return B200_OK; }
+   int grid = (n + 255) / 256;
+   if (grid > AR_BIG_GRID) { grid = AR_BIG_GRID; }
+   LAUNCH(c, p2p_allreduce_big_kernel, grid, 256, 0, c->d_peer_arena, c->arb_vals_off, c->arb_flag_off, c->rank, c->nranks,
+          c->d_ar_seq + 1, (unsigned *)(c->d_ar_seq + 2), d, n, c->d_err, c->d_stop);
    CHECK_LAUNCH();
    return B200_OK;
 }

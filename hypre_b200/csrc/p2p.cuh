@@ -50,6 +50,16 @@ __device__ __forceinline__ void st_release_sys(u64 *p, u64 v)
 {
    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(u64 *p, u64 v)
+{
+   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ u64 ld_relaxed_sys(const u64 *p)
+{
+   u64 v;
+   asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+   return v;
+}
 __device__ __forceinline__ u64 ld_relaxed_gpu(const u64 *p)
 {
    u64 v;
@@ -62,11 +72,11 @@ __device__ __forceinline__ void p2p_spin_ge(const u64 *p, u64 want, int *err)
 {
    if (ld_acquire_sys(p) >= want) { return; }
    const long long t0 = clock64();
-   while (ld_acquire_sys(p) < want)
+   while (ld_relaxed_sys(p) < want)
    {
       if (clock64() - t0 > P2P_SPIN_LIMIT) { atomicExch(err, 1); break; }
-      __nanosleep(20);
    }
+   (void)ld_acquire_sys(p);      // order the data reads after the observed sequence number
 }
 
 // Consumer side, end of kernel: the last block acknowledges to every sender and advances the
@@ -83,10 +93,11 @@ __device__ __forceinline__ void p2p_consumer_done(const P2PChan &ch)
    __syncthreads();
    if (s_last_c)
    {
+      // every block finished reading the buffer before it took its ticket (barrier + fence above), so
+      // the acknowledgement needs no further fence: a plain system-scope store
       const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
-      for (int j = threadIdx.x; j < ch.n_in; j += blockDim.x) { st_release_sys(ch.in_ack[j], seq); }
-      __syncthreads();
-      if (threadIdx.x == 0) { *ch.seq_wait = seq; ch.ticket[1] = 0u; __threadfence(); }
+      for (int j = threadIdx.x; j < ch.n_in; j += blockDim.x) { st_relaxed_sys(ch.in_ack[j], seq); }
+      if (threadIdx.x == 0) { *ch.seq_wait = seq; ch.ticket[1] = 0u; }
    }
 }
 
@@ -106,6 +117,9 @@ const P2PChan &p2p_chan_view(const b200_p2p_chan *ch);
 // halo_put_phase, halo_warp_wait, p2p_consumer_done): one launch per operator.
 // d[0..cnt) <- sum over ranks, deterministic rank order, result identical on all ranks
 int  p2p_allreduce(b200_ctx *c, double *d, int cnt);
+// vector version (n <= p2p_allreduce_vec_max()), several blocks
+int  p2p_allreduce_vec(b200_ctx *c, double *d, int n);
+int  p2p_allreduce_vec_max(void);
 // stream-ordered rendezvous of all ranks without a time limit (NCCL): called once at the start of a
 // solve so that ranks that are still uploading do not trip the bounded spins of the peers
 int  ctx_rendezvous(b200_ctx *c);

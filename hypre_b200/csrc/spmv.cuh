@@ -175,6 +175,7 @@ struct HaloArgs {
    const int  *map;      // FWD: send_map_elmts
    const int  *urp;      // REV: [n_rows+1] contributions per local row
    const int  *upos;     // REV: positions in the receive buffer, grouped by row
+   const unsigned char *grp;   // FWD/REV: [ceil(n_rows/32)] non-zero if a row of that 32-row group needs remote data
 };
 
 // sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks)
@@ -208,16 +209,24 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
       }
       dst[seg][i - ch.out_starts[seg]] = v;
    }
-   __threadfence_system();
+   // publish: the block barrier orders the block's stores before thread 0; with one put block its
+   // release store (fence.sys + store, cumulative) is the only system-scope fence on the critical path,
+   // with several blocks each block's thread 0 fences once before taking its ticket
    __syncthreads();
-   if (threadIdx.x == 0) { s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u); }
-   __syncthreads();
+   if (n_put_blocks == 1) { s_last_p = true; }
+   else
+   {
+      if (threadIdx.x == 0)
+      {
+         __threadfence_system();
+         s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u);
+      }
+      __syncthreads();
+   }
    if (s_last_p)
    {
-      __threadfence_system();
       for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x) { st_release_sys(ch.out_flag[i], seq); }
-      __syncthreads();
-      if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; __threadfence(); }
+      if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; }
    }
 }
 
@@ -260,32 +269,31 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       const int lane = threadIdx.x & 31;
       const int n_slices = (D.n_rows + 31) >> 5;
       const int wpb = ROWK_BLOCK / 32;
-      for (int slice = blockIdx.x * wpb + (threadIdx.x >> 5); slice < n_slices; slice += gridDim.x * wpb)
+      // peer-memory modes: start in the middle of the row range -- the rows that need remote data sit
+      // at both ends of a 1-D block partition, so they are reached when the halo has long arrived
+      const int shift = P2P ? (n_slices >> 1) : 0;
+      for (int s0 = blockIdx.x * wpb + (threadIdx.x >> 5); s0 < n_slices; s0 += gridDim.x * wpb)
       {
+         int slice = s0 + shift;
+         if (slice >= n_slices) { slice -= n_slices; }
          const int row = (slice << 5) + lane;
          const bool live = row < D.n_rows;
          double t = rowsum_sell(D, slice, lane, x);
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
-         if (HALO == HALO_FWD)
+         if (HALO == HALO_FWD && h.grp[slice])
          {
             const int ob = live ? h.O.rp[row] : 0, oe = live ? h.O.rp[row + 1] : 0;
-            if (__any_sync(0xffffffffu, oe > ob))
-            {
-               xg = halo_warp_wait(h.ch, xg);
-               for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], __ldcg(xg + h.O.ci[k]), t); }
-            }
+            xg = halo_warp_wait(h.ch, xg);
+            for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], __ldcg(xg + h.O.ci[k]), t); }
          }
-         if (HALO == HALO_REV)
+         if (HALO == HALO_REV && h.grp[slice])
          {
             const int ub = live ? h.urp[row] : 0, ue = live ? h.urp[row + 1] : 0;
-            if (__any_sync(0xffffffffu, ue > ub))
-            {
-               xg = halo_warp_wait(h.ch, xg);
-               double e = 0.0;
-               for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
-               t += e;
-            }
+            xg = halo_warp_wait(h.ch, xg);
+            double e = 0.0;
+            for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+            t += e;
          }
          if (live && !skip) { epi(row, t, red); }
       }
@@ -297,35 +305,33 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       const int gpb = ROWK_BLOCK / TT;
       // pad the loop so every lane of a warp takes part in the shuffles
       const int n_pad = (D.n_rows + (32 / TT) - 1) / (32 / TT) * (32 / TT);
-      for (int row = blockIdx.x * gpb + threadIdx.x / TT; row < n_pad; row += gridDim.x * gpb)
+      // same rotation as above, in whole warps (32/TT rows)
+      const int shift = P2P ? ((n_pad >> 1) / (32 / TT)) * (32 / TT) : 0;
+      for (int r0 = blockIdx.x * gpb + threadIdx.x / TT; r0 < n_pad; r0 += gridDim.x * gpb)
       {
+         int row = r0 + shift;
+         if (row >= n_pad) { row -= n_pad; }
          const bool live = row < D.n_rows;
          const int r = live ? row : D.n_rows - 1;
          double t = rowsum_csr<TT>(D.rp, D.ci, D.va, r, sub, x);
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = h.O.rp[r + 1] != h.O.rp[r]; }
-         if (HALO == HALO_FWD)
+         // a warp's rows lie in one 32-row group, so the flag is warp-uniform
+         if (HALO == HALO_FWD && h.grp[row >> 5])
          {
-            const bool has = live && h.O.rp[r + 1] > h.O.rp[r];
-            if (__any_sync(0xffffffffu, has))
-            {
-               xg = halo_warp_wait(h.ch, xg);
-               // all lanes take part (rows without offd entries have an empty range)
-               t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg);
-            }
+            xg = halo_warp_wait(h.ch, xg);
+            // all lanes take part (rows without offd entries have an empty range)
+            t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg);
          }
-         if (HALO == HALO_REV)
+         if (HALO == HALO_REV && h.grp[row >> 5])
          {
             const int ub = live ? h.urp[r] : 0, ue = live ? h.urp[r + 1] : 0;
-            if (__any_sync(0xffffffffu, ue > ub))
+            xg = halo_warp_wait(h.ch, xg);
+            if (sub == 0)
             {
-               xg = halo_warp_wait(h.ch, xg);
-               if (sub == 0)
-               {
-                  double e = 0.0;
-                  for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
-                  t += e;
-               }
+               double e = 0.0;
+               for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+               t += e;
             }
          }
          if (live && sub == 0 && !skip) { epi(row, t, red); }

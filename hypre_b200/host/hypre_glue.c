@@ -201,6 +201,23 @@ static b200_parcsr *upload_parcsr_rows(hypre_ParCSRMatrix *A, const int *rs, con
    return dA;
 }
 
+/* rows [r0, r1) of a single-rank hypre_ParCSRMatrix with ALL (global) columns, as a communication-free
+ * single-block b200_parcsr: interpolation onto a replicated coarse level */
+static b200_parcsr *upload_parcsr_row_slab(hypre_ParCSRMatrix *A, int r0, int r1)
+{
+   hypre_CSRMatrix *diag = hypre_ParCSRMatrixDiag(A);
+   const HYPRE_Int *ai = hypre_CSRMatrixI(diag);
+   b200_parcsr *dA = NULL;
+   int n = r1 - r0, k;
+   int *ri = (int *) malloc(sizeof(int) * (size_t)(n + 1));
+   for (k = 0; k <= n; k++) { ri[k] = ai[r0 + k] - ai[r0]; }
+   if (b200_parcsr_create(glue_ctx(), n, hypre_CSRMatrixNumCols(diag), ri, hypre_CSRMatrixJ(diag) + ai[r0],
+                          hypre_CSRMatrixData(diag) + ai[r0], 0, NULL, NULL, NULL, 0, NULL, NULL, NULL, 0, NULL, NULL,
+                          &dA) != B200_OK) { dA = NULL; }
+   free(ri);
+   return dA;
+}
+
 /* hypre_ParAMGData (after the reference's host setup) -> b200_amg */
 static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
 {
@@ -215,6 +232,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
    hypre_Vector **ds = hypre_ParAMGDataChebyDS(amg_data);
    HYPRE_Real **coefs = hypre_ParAMGDataChebyCoefs(amg_data);
    int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0;
+   int repl = 1 << 30;   /* distributed mode: first level replicated on every rank */
    int *starts = NULL;   /* distributed mode: (nl+1) x (g_nranks+1) row starts per level */
 #define STARTS(l) (starts + (size_t)(l) * (g_nranks + 1))
 
@@ -267,15 +285,36 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
          }
          if (!ok) { even_starts(nc, g_nranks, STARTS(l + 1)); }
       }
+      /* Small levels are latency-bound: below B200_REPL_NNZ nonzeros (default 4e6 = one ~8 us pass at
+       * HBM speed) every rank keeps the whole level and runs it without communication -- the
+       * reference's own answer to idle ranks on coarse grids is seq_threshold / hypre_seqAMGCycle
+       * (par_cycle.c:362-369).  Results do not depend on this choice for Jacobi / Chebyshev. */
+      {
+         const char *e = getenv("B200_REPL_NNZ");
+         double limit = e ? atof(e) : 4.0e6;
+         for (l = 1; l < nl; l++)
+         {
+            hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]);
+            if ((double) hypre_CSRMatrixNumNonzeros(d) <= limit && hypre_CSRMatrixNumRows(d) <= (1 << 18)) { repl = l; break; }
+         }
+      }
    }
    if (b200_amg_create(ctx, nl, &amg) != B200_OK) { free(starts); return NULL; }
    for (l = 0; l < nl; l++)
    {
       b200_parcsr *dA, *dP;
-      if (g_nranks > 1)
+      if (g_nranks > 1 && l >= repl)
+      {
+         /* replicated level: the whole single-rank matrices */
+         dA = upload_parcsr(A_array[l]);
+         dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+      }
+      else if (g_nranks > 1)
       {
          dA = upload_parcsr_rows(A_array[l], STARTS(l), STARTS(l));
-         dP = (l < nl - 1) ? upload_parcsr_rows(P_array[l], STARTS(l), STARTS(l + 1)) : NULL;
+         if (l == nl - 1) { dP = NULL; }
+         else if (l + 1 == repl) { dP = upload_parcsr_row_slab(P_array[l], STARTS(l)[g_rank], STARTS(l)[g_rank + 1]); }
+         else { dP = upload_parcsr_rows(P_array[l], STARTS(l), STARTS(l + 1)); }
       }
       else
       {
@@ -292,11 +331,12 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
       }
    }
    if (b200_amg_set_cycle(amg, relax_type, num_sweeps, hypre_ParAMGDataCycleType(amg_data),
-                          hypre_ParAMGDataFCycle(amg_data)) != B200_OK) { b200_amg_destroy(amg); return NULL; }
+                          hypre_ParAMGDataFCycle(amg_data)) != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
+   if (repl < nl && b200_amg_set_replicated_from(amg, repl) != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
    for (k = 0; k < 4; k++) { if (relax_type[k] == 16) { uses_cheby = 1; } }
    for (l = 0; l < nl; l++)
    {
-      const int off = starts ? STARTS(l)[g_rank] : 0;   /* this rank's slice of the level vectors */
+      const int off = (starts && l < repl) ? STARTS(l)[g_rank] : 0;   /* this rank's slice of the level vectors */
       const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) + off : NULL;
       if (b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d) != B200_OK)
       {
@@ -323,8 +363,9 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
       if (starts)
       {
          int *rows = (int *) calloc((size_t) g_nranks, sizeof(int)), r;
-         for (r = 0; r < g_nranks; r++) { rows[r] = STARTS(nl - 1)[r + 1] - STARTS(nl - 1)[r]; }
-         status = b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data), STARTS(nl - 1)[g_rank], rows);
+         for (r = 0; r < g_nranks; r++) { rows[r] = repl < nl ? (int) N : STARTS(nl - 1)[r + 1] - STARTS(nl - 1)[r]; }
+         status = b200_amg_set_coarse_dense(amg, N, hypre_ParAMGDataAMat(amg_data),
+                                            repl < nl ? 0 : STARTS(nl - 1)[g_rank], rows);
          free(rows);
       }
       else
@@ -342,8 +383,8 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
    {
       double bytes = 0.0;
       b200_amg_cycle_bytes(amg, &bytes);
-      fprintf(stderr, "hypre_b200: uploaded %d-level hierarchy, %.3f MB algorithmic bytes per cycle\n",
-              (int) nl, bytes * 1e-6);
+      fprintf(stderr, "hypre_b200: rank %d/%d uploaded %d-level hierarchy (replicated from level %d), %.3f MB algorithmic bytes per cycle\n",
+              g_rank, g_nranks, (int) nl, repl < nl ? repl : -1, bytes * 1e-6);
    }
    return amg;
 }

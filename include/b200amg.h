@@ -168,6 +168,11 @@ int b200_amg_destroy(b200_amg *amg);
 /* A_array[level]; P_array[level] (NULL on the coarsest level).  The amg object
  * takes ownership of A and P. */
 int b200_amg_set_level(b200_amg *amg, int level, b200_parcsr *A, b200_parcsr *P);
+/* N > 1 ranks: levels >= `level` (>= 1) are replicated on every rank -- their A/P are uploaded as
+ * whole single-rank matrices, P_array[level-1] with GLOBAL coarse columns -- so the small levels run
+ * without any communication (reference: seq_threshold / hypre_seqAMGCycle,
+ * src/parcsr_ls/par_cycle.c:362-369).  Call before b200_amg_finalize. */
+int b200_amg_set_replicated_from(b200_amg *amg, int level);
 /* grid_relax_type[1..3], num_grid_sweeps[1..3] (index = cycle_param: 1 down,
  * 2 up, 3 coarsest), cycle_type (1 = V, 2 = W), fcycle */
 int b200_amg_set_cycle(b200_amg *amg, const int relax_type[4], const int num_sweeps[4],
