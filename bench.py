@@ -306,7 +306,8 @@ def run_b200(args, rank, world):
     spmv_gbs = spmv_bytes / (spmv_ms * 1e-3) / 1e9
     # whole-iteration view: algorithmic bytes of one PCG iteration / time of one iteration
     iter_bytes = cyc_bytes.value + spmv_bytes + 8.0 * n * (4 + 2 + 3)   # update (4 streams+..), dot, direction
-    iter_gbs = iter_bytes * iters * args.steps / dev_s / 1e9
+    # a solve runs iters+1 preconditioner cycles and SpMVs (the initial residual and p = C r come first)
+    iter_gbs = iter_bytes * (iters + 1) * args.steps / dev_s / 1e9
 
     # ---------------- cpu_baseline: the reference's CPU PCG on this box, bounded sample
     cpu = None
@@ -355,13 +356,15 @@ def finish_multi(args, R, P, m):
     launches = R.sum(m["launches"])
     if R.rank == 0:
         peak, peak_src = measured_peaks()
-        iter_gbs = iter_bytes * m["iters"] * args.steps / m["dev_s"] / 1e9
+        iter_gbs = iter_bytes * (m["iters"] + 1) * args.steps / m["dev_s"] / 1e9
         out = {
             "metric": "AMG-PCG solve DOF*iterations/s", "value": m["value"], "unit": "DOF*it/s", "n_gpus": R.world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * m["dev_s"] / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": P["cmd"], "dof": m["n_global"], "iterations_per_step": m["iters"],
-                       "levels": m["levels"], "partition": "1-D row blocks, %d ranks, halo over NCCL/NVLink" % R.world,
+                       "levels": m["levels"], "partition": "1-D row blocks, %d ranks, halo = %s" % (
+                           R.world, "NCCL send/recv (baseline)" if os.environ.get("B200_HALO") == "nccl"
+                           else "peer-memory stores fused into the row kernels (NVLink)"),
                        "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration, all ranks)" % (iter_bytes / 1e9),
                        "final_rel_residual": float(m["rel"][m["iters"]])},
             "e2e": {"value": m["e2e_value"], "unit": "DOF*it/s", "h2d_bytes_per_step": 16 * m["n_global"],
