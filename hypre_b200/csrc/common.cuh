@@ -64,6 +64,7 @@ struct b200_ctx {
    long long    launches = 0;
    // peer-memory exchange (p2p.cuh): this rank's arena, the IPC-mapped arenas of all ranks
    int          use_p2p = 0;
+   int          p2p_debug = 0;       // B200_P2P_DEBUG (timing experiments)
    char        *arena = nullptr;
    size_t       arena_bytes = 0, arena_used = 0;
    std::vector<char *> peer_arena;
@@ -205,7 +206,8 @@ struct b200_parcsr {
    // deterministic unpack plan for job 2: CSR of (local row -> positions in recv buf)
    int    *d_unpack_rp = nullptr, *d_unpack_pos = nullptr;
    unsigned char *d_grp_fwd = nullptr;    // [ceil(n_rows/32)] group has a row with offd entries
-   unsigned char *d_grp_rev = nullptr;    // [ceil(n_cols_diag/32)] group has a row receiving A^T contributions
+   unsigned char *d_grp_rev = nullptr;
+   int     int_fwd[2] = {0, 0}, int_rev[2] = {0, 0};   // longest runs of groups without remote data    // [ceil(n_cols_diag/32)] group has a row receiving A^T contributions
    int    *d_unpack_rp_dense = nullptr;   // [n_cols_diag+1]: the same lists indexed by local row (fused kernel)
    int     n_unpack_rows = 0;
    int    *d_unpack_rows = nullptr;

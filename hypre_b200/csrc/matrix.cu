@@ -216,6 +216,20 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
          for (int r = 0; r < n_rows; r++) { if (A->h_offd.i[r + 1] > A->h_offd.i[r]) { gf[(size_t)r >> 5] = 1; } }
       }
       for (int k = 0; k < A->n_send_elmts; k++) { gr[(size_t)send_map_elmts[k] >> 5] = 1; }
+      auto longest_clear_run = [](const std::vector<unsigned char> &g, int n_groups, int *out) {
+         int best_b = 0, best_e = 0, b = 0;
+         for (int k = 0; k <= n_groups; k++)
+         {
+            if (k == n_groups || g[(size_t)k])
+            {
+               if (k - b > best_e - best_b) { best_b = b; best_e = k; }
+               b = k + 1;
+            }
+         }
+         out[0] = best_b; out[1] = best_e;
+      };
+      longest_clear_run(gf, (n_rows + 31) / 32, A->int_fwd);
+      longest_clear_run(gr, (n_cols_diag + 31) / 32, A->int_rev);
       s = dev_upload(&A->d_grp_fwd, gf.data(), gf.size());
       if (s == B200_OK) { s = dev_upload(&A->d_grp_rev, gr.data(), gr.size()); }
       if (s != B200_OK) { b200_parcsr_destroy(A); return s; }

@@ -86,6 +86,7 @@ int p2p_bootstrap(b200_ctx *c)
    CUDA_TRY(cudaMalloc((void **)&c->d_ar_seq, 4 * sizeof(u64)));     // [0] small seq, [1] big seq, [2..3] big tickets
    CUDA_TRY(cudaMemset(c->d_ar_seq, 0, 4 * sizeof(u64)));
    B200_TRY(dev_upload(&c->d_peer_arena, c->peer_arena.data(), c->peer_arena.size()));
+   { const char *e = getenv("B200_P2P_DEBUG"); c->p2p_debug = e ? atoi(e) : 0; }
    c->use_p2p = 1;
    return B200_OK;
 }

@@ -88,6 +88,8 @@ static int run_rows(b200_parcsr *A, const DMat &D, const DMat &O, bool use_halo,
          h.ch = p2p_chan_view(A->ch_fwd);
          h.map = A->d_send_map;
          h.grp = A->d_grp_fwd;
+         h.int_begin = A->int_fwd[0]; h.int_end = A->int_fwd[1];
+         h.dbg = ctx->p2p_debug;
          return launch_rows_layout<HALO_FWD, Epi>(ctx, D, h, x, epi, make_redctx(ctx, red_out, 0));
       }
       B200_TRY(halo_start(A, x));
@@ -115,5 +117,7 @@ static int run_rows_transposed_p2p(b200_parcsr *A, const double *x, const Epi &e
    h.urp = A->d_unpack_rp_dense;
    h.upos = A->d_unpack_pos;
    h.grp = A->d_grp_rev;
+   h.int_begin = A->int_rev[0]; h.int_end = A->int_rev[1];
+   h.dbg = A->ctx->p2p_debug;
    return launch_rows_layout<HALO_REV, Epi>(A->ctx, A->diagT, h, x, epi, make_redctx(A->ctx, nullptr, 0));
 }

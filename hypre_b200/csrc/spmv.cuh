@@ -175,6 +175,9 @@ struct HaloArgs {
    const int  *map;      // FWD: send_map_elmts
    const int  *urp;      // REV: [n_rows+1] contributions per local row
    const int  *upos;     // REV: positions in the receive buffer, grouped by row
+   int         dbg;      // B200_P2P_DEBUG bits (timing experiments only):
+                         // 2 no waiting, 4 no flow control / acknowledgements, 8 no system fences in the put
+   int         int_begin, int_end;   // FWD/REV: longest run of 32-row groups that need no remote data
    const unsigned char *grp;   // FWD/REV: [ceil(n_rows/32)] non-zero if a row of that 32-row group needs remote data
 };
 
@@ -189,7 +192,7 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
    {
       const u64 seq = ld_relaxed_gpu(ch.seq_put) + 1;
       // flow control: buffer (seq & 1) was used by exchange seq-2; wait until it was consumed
-      if (seq > 2) { for (int i = 0; i < ch.n_out; i++) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
+      if (seq > 2 && !(h.dbg & 4)) { for (int i = 0; i < ch.n_out; i++) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
       s_seq = seq;
    }
    __syncthreads();
@@ -218,64 +221,52 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
    {
       if (threadIdx.x == 0)
       {
-         __threadfence_system();
+         if (!(h.dbg & 8)) { __threadfence_system(); }
          s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u);
       }
       __syncthreads();
    }
    if (s_last_p)
    {
-      for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x) { st_release_sys(ch.out_flag[i], seq); }
+      for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x)
+      {
+         if (h.dbg & 8) { st_relaxed_sys(ch.out_flag[i], seq); } else { st_release_sys(ch.out_flag[i], seq); }
+      }
       if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; }
    }
 }
 
 // receiver part: called by a converged warp when one of its rows needs remote data; waits once per warp
-__device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const double *cur)
+__device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const double *cur, int dbg)
 {
    if (cur != nullptr) { return cur; }
    int par = 0;
    if ((threadIdx.x & 31) == 0)
    {
       const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
-      for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); }
+      if (!(dbg & 2)) { for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); } }
       par = (int)(seq & 1);
    }
    par = __shfl_sync(0xffffffffu, par, 0);
    return ch.in_buf[par];
 }
 
-// All rows of the diag block.  T == 0: sliced ELL thread-per-row; T > 0: CSR with T lanes per row.
+// Row groups [g_begin, g_end) (a group = 32 consecutive rows = one slice of the sliced-ELL layout) of
+// the diag block, grid-strided over the whole grid.  T == 0: sliced ELL thread-per-row; T > 0: CSR
+// with T lanes per row.  HALO as above; HALO_NONE / HALO_SKIP never touch the channel.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK)
-rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
+__device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
+                                           const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
+                                           int vblock)
 {
-   RETURN_IF_STOPPED(rc);
-   double red[Epi::NRED > 0 ? Epi::NRED : 1];
-#pragma unroll
-   for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
-
-   constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
-   if (P2P && h.ch.n_out > 0)
-   {
-      int n_put_blocks = (h.ch.n_out_total + ROWK_BLOCK - 1) / ROWK_BLOCK;
-      if (n_put_blocks > (int)gridDim.x) { n_put_blocks = gridDim.x; }
-      if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks); }
-   }
-   const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
-
+   // vblock: the block's position in this range's grid stride (a permutation of blockIdx.x), so that
+   // short ranges do not all land on the low-numbered blocks, which also carry the put phase
    if (T == 0)
    {
       const int lane = threadIdx.x & 31;
-      const int n_slices = (D.n_rows + 31) >> 5;
       const int wpb = ROWK_BLOCK / 32;
-      // peer-memory modes: start in the middle of the row range -- the rows that need remote data sit
-      // at both ends of a 1-D block partition, so they are reached when the halo has long arrived
-      const int shift = P2P ? (n_slices >> 1) : 0;
-      for (int s0 = blockIdx.x * wpb + (threadIdx.x >> 5); s0 < n_slices; s0 += gridDim.x * wpb)
+      for (int slice = g_begin + vblock * wpb + (threadIdx.x >> 5); slice < g_end; slice += gridDim.x * wpb)
       {
-         int slice = s0 + shift;
-         if (slice >= n_slices) { slice -= n_slices; }
          const int row = (slice << 5) + lane;
          const bool live = row < D.n_rows;
          double t = rowsum_sell(D, slice, lane, x);
@@ -284,13 +275,13 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
          if (HALO == HALO_FWD && h.grp[slice])
          {
             const int ob = live ? h.O.rp[row] : 0, oe = live ? h.O.rp[row + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg);
+            xg = halo_warp_wait(h.ch, xg, h.dbg);
             for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], __ldcg(xg + h.O.ci[k]), t); }
          }
          if (HALO == HALO_REV && h.grp[slice])
          {
             const int ub = live ? h.urp[row] : 0, ue = live ? h.urp[row + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg);
+            xg = halo_warp_wait(h.ch, xg, h.dbg);
             double e = 0.0;
             for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
             t += e;
@@ -303,30 +294,26 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       constexpr int TT = (T == 0 ? 1 : T);
       const int sub = threadIdx.x & (TT - 1);
       const int gpb = ROWK_BLOCK / TT;
-      // pad the loop so every lane of a warp takes part in the shuffles
-      const int n_pad = (D.n_rows + (32 / TT) - 1) / (32 / TT) * (32 / TT);
-      // same rotation as above, in whole warps (32/TT rows)
-      const int shift = P2P ? ((n_pad >> 1) / (32 / TT)) * (32 / TT) : 0;
-      for (int r0 = blockIdx.x * gpb + threadIdx.x / TT; r0 < n_pad; r0 += gridDim.x * gpb)
+      // whole warps: a warp's 32/TT rows lie in one group, so the group flag is warp-uniform and every
+      // lane takes part in the shuffles
+      const int r_end = g_end << 5;
+      for (int row = (g_begin << 5) + vblock * gpb + threadIdx.x / TT; row < r_end; row += gridDim.x * gpb)
       {
-         int row = r0 + shift;
-         if (row >= n_pad) { row -= n_pad; }
          const bool live = row < D.n_rows;
          const int r = live ? row : D.n_rows - 1;
          double t = rowsum_csr<TT>(D.rp, D.ci, D.va, r, sub, x);
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = h.O.rp[r + 1] != h.O.rp[r]; }
-         // a warp's rows lie in one 32-row group, so the flag is warp-uniform
          if (HALO == HALO_FWD && h.grp[row >> 5])
          {
-            xg = halo_warp_wait(h.ch, xg);
+            xg = halo_warp_wait(h.ch, xg, h.dbg);
             // all lanes take part (rows without offd entries have an empty range)
             t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg);
          }
          if (HALO == HALO_REV && h.grp[row >> 5])
          {
             const int ub = live ? h.urp[r] : 0, ue = live ? h.urp[r + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg);
+            xg = halo_warp_wait(h.ch, xg, h.dbg);
             if (sub == 0)
             {
                double e = 0.0;
@@ -337,8 +324,39 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
          if (live && sub == 0 && !skip) { epi(row, t, red); }
       }
    }
+}
+
+// All rows of the diag block.
+template <int T, int HALO, class Epi>
+__global__ void __launch_bounds__(ROWK_BLOCK)
+rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
+{
+   RETURN_IF_STOPPED(rc);
+   double red[Epi::NRED > 0 ? Epi::NRED : 1];
+#pragma unroll
+   for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
+
+   constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
+   const int n_groups = (D.n_rows + 31) >> 5;
+   const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
+   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x); }
+   else
+   {
+      if (h.ch.n_out > 0)
+      {
+         int n_put_blocks = (h.ch.n_out_total + ROWK_BLOCK - 1) / ROWK_BLOCK;
+         if (n_put_blocks > (int)gridDim.x) { n_put_blocks = gridDim.x; }
+         if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks); }
+      }
+      // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
+      // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
+      const int G = gridDim.x, b = blockIdx.x;
+      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G);
+   }
    grid_reduce<Epi::NRED>(red, rc);
-   if (P2P && h.ch.n_in > 0) { p2p_consumer_done(h.ch); }
+   if (P2P && h.ch.n_in > 0 && !(h.dbg & 4)) { p2p_consumer_done(h.ch); }
 }
 
 // Rows from a list (the boundary rows of the NCCL path): diag CSR + offd CSR, 4 lanes per row.

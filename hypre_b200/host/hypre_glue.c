@@ -285,13 +285,13 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
          }
          if (!ok) { even_starts(nc, g_nranks, STARTS(l + 1)); }
       }
-      /* Small levels are latency-bound: below B200_REPL_NNZ nonzeros (default 4e6 = one ~8 us pass at
+      /* Small levels are latency-bound: below B200_REPL_NNZ nonzeros (default 8e6 = one ~16 us pass at
        * HBM speed) every rank keeps the whole level and runs it without communication -- the
        * reference's own answer to idle ranks on coarse grids is seq_threshold / hypre_seqAMGCycle
        * (par_cycle.c:362-369).  Results do not depend on this choice for Jacobi / Chebyshev. */
       {
          const char *e = getenv("B200_REPL_NNZ");
-         double limit = e ? atof(e) : 4.0e6;
+         double limit = e ? atof(e) : 8.0e6;
          for (l = 1; l < nl; l++)
          {
             hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]);
