@@ -97,7 +97,12 @@ __device__ __forceinline__ void grid_reduce(double (&red)[NRED > 0 ? NRED : 1], 
 }
 
 // ---------------------------------------------------------------- row sums
-// sliced-ELL, one thread per row (lane = row within the 32-row slice)
+// sliced-ELL, one thread per row (lane = row within the 32-row slice).
+// Memory latency bounds this loop (ncu: >90 % of the stall samples are long-scoreboard) and
+// occupancy hides it: entries are taken in chunks of 4 with a guarded (warp-uniform) tail, which
+// keeps the kernel at 32 registers = 8 resident blocks per SM.  A chunk of 8 (two round trips for a
+// 7-point row) was measured: 54 registers, half the occupancy, 3-10 % slower on 7-pt and 27-pt.
+// The fma chain keeps the storage order.
 __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int lane,
                                               const double *__restrict__ x)
 {
@@ -106,26 +111,23 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
    const int    *ci = D.sl_ci + off + lane;
    const double *va = D.sl_va + off + lane;
    double t = 0.0;
-   int k = 0;
-   for (; k + 4 <= width; k += 4)
+   for (int k0 = 0; k0 < width; k0 += 4)
    {
-      int    c0 = ld_stream(ci + (k + 0) * 32), c1 = ld_stream(ci + (k + 1) * 32);
-      int    c2 = ld_stream(ci + (k + 2) * 32), c3 = ld_stream(ci + (k + 3) * 32);
-      double v0 = ld_stream(va + (k + 0) * 32), v1 = ld_stream(va + (k + 1) * 32);
-      double v2 = ld_stream(va + (k + 2) * 32), v3 = ld_stream(va + (k + 3) * 32);
-      double x0 = __ldg(x + c0), x1 = __ldg(x + c1), x2 = __ldg(x + c2), x3 = __ldg(x + c3);
-      t = fma(v0, x0, t); t = fma(v1, x1, t); t = fma(v2, x2, t); t = fma(v3, x3, t);
-   }
-   for (; k < width; k++)
-   {
-      int    c = ld_stream(ci + k * 32);
-      double v = ld_stream(va + k * 32);
-      t = fma(v, __ldg(x + c), t);
+      int    c[4];
+      double v[4], xv[4];
+      const int m = width - k0;          // entries left (uniform)
+#pragma unroll
+      for (int j = 0; j < 4; j++) { c[j] = (j < m) ? ld_stream(ci + (k0 + j) * 32) : 0; }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { v[j] = (j < m) ? ld_stream(va + (k0 + j) * 32) : 0.0; }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { xv[j] = (j < m) ? __ldg(x + c[j]) : 0.0; }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { if (j < m) { t = fma(v[j], xv[j], t); } }
    }
    return t;
 }
 
-// CSR, T lanes per row; result valid in the group's lane 0
 // CG: gather x with ld.global.cg (L2 only) -- for ghost vectors that a peer GPU wrote during this
 // kernel's lifetime, which must not be served from a stale L1 / read-only cache line
 template <bool CG>
@@ -326,9 +328,10 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
    }
 }
 
-// All rows of the diag block.
+// All rows of the diag block.  8 resident blocks per SM (32 registers): occupancy is what hides the
+// DRAM latency of this streaming kernel.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK)
+__global__ void __launch_bounds__(ROWK_BLOCK, 8)
 rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
