@@ -83,11 +83,11 @@ struct EpiGsInner {
 };
 
 // zero-initial-guess / alpha == 0 elementwise variants (A*0 == 0: same arithmetic, no SpMV)
-struct FScaleCopy { static constexpr int NRED = 0; double beta; const double *b; double *y;
+struct FScaleCopy { static constexpr int NRED = 0; __device__ void init() {} double beta; const double *b; double *y;
    __device__ void operator()(int i, double *) const { y[i] = beta * b[i]; } };
-struct FZero { static constexpr int NRED = 0; double w; const double *f; const double *l1; double *u;
+struct FZero { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *l1; double *u;
    __device__ void operator()(int i, double *) const { u[i] = (w * f[i]) / l1[i]; } };
-struct FChebyFirst0 { static constexpr int NRED = 0; int scale; double c; const double *f; const double *ds;
+struct FChebyFirst0 { static constexpr int NRED = 0; __device__ void init() {} int scale; double c; const double *f; const double *ds;
    double *rv; double *tmp;
    __device__ void operator()(int i, double *) const
    {
@@ -97,7 +97,7 @@ struct FChebyFirst0 { static constexpr int NRED = 0; int scale; double c; const 
       double u1 = res * c;
       tmp[i] = scale ? ds[i] * u1 : u1;
    } };
-struct FGsFirst0 { static constexpr int NRED = 0; double w; const double *f; const double *d; double *z;
+struct FGsFirst0 { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *d; double *z;
    __device__ void operator()(int i, double *) const { z[i] = (w * f[i]) / d[i]; } };
 
 // ---------------------------------------------------------------- operators
@@ -120,7 +120,7 @@ int op_matvec_dot(b200_parcsr *A, const double *x, double *y, double *d_out)
    return run_rows(A, A->diag, A->offd, true, x, e, d_out);
 }
 
-struct FScaleInPlace { static constexpr int NRED = 0; double beta; double *y;
+struct FScaleInPlace { static constexpr int NRED = 0; __device__ void init() {} double beta; double *y;
    __device__ void operator()(int i, double *) const { y[i] = beta * y[i]; } };
 
 // hypre_ParCSRMatrixMatvecTHost (src/parcsr_mv/par_csr_matvec.c:287-514):

@@ -31,17 +31,21 @@ constexpr int PCG_RING = 8;
 struct FPcgUpdate {
    static constexpr int NRED = 1;
    int skip_break; const double *scal; const double *p; const double *s; double *x; double *r;
-   __device__ void operator()(int i, double *red) const
+   double alpha; bool stop;      // set by init(), once per thread
+   __device__ void init()
    {
       const double sdotp = scal[S_SDOTP];
-      const double alpha = scal[S_GAMMA] / sdotp;
-      bool stop = (sdotp == 0.0);
+      alpha = scal[S_GAMMA] / sdotp;
+      stop = (sdotp == 0.0);
       if (!stop)
       {
          if (alpha <= 0.0)               { stop = skip_break < 3; }
          else if (!(alpha >= 4.9406564584124654e-324)) { stop = skip_break < 2; }
          else if (!(alpha >= DBL_MIN))   { stop = skip_break < 1; }
       }
+   }
+   __device__ void operator()(int i, double *red) const
+   {
       double ri = r[i];
       if (!stop)
       {
@@ -57,12 +61,14 @@ struct FPcgUpdate {
 struct FPcgDirection {
    static constexpr int NRED = 0;
    const double *scal; const double *z; double *p;
-   __device__ void operator()(int i, double *) const { p[i] = scal[S_BETA] * p[i] + z[i]; }
+   double beta;
+   __device__ void init() { beta = scal[S_BETA]; }
+   __device__ void operator()(int i, double *) const { p[i] = beta * p[i] + z[i]; }
 };
 
 // z = r ./ d  (HYPRE_ParCSRDiagScale) and red0 = <r,z>
 struct FDiagScaleDot {
-   static constexpr int NRED = 1;
+   static constexpr int NRED = 1; __device__ void init() {}
    const double *d; const double *r; double *z;
    __device__ void operator()(int i, double *red) const
    {
@@ -158,7 +164,7 @@ static int pcg_enqueue_iteration(const PcgIter &it)
    B200_TRY(scalars_allreduce(c, c->d_scalars + S_SDOTP, 1));
    // x += alpha p ; r -= alpha s ; <r,r>
    {
-      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r};
+      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r, 0.0, false};
       B200_TRY(run_ewise(c, it.n, f, c->d_scalars + S_IPROD));
    }
    // s = C r ; gamma = <r,s>
@@ -176,7 +182,7 @@ static int pcg_enqueue_iteration(const PcgIter &it)
    CHECK_LAUNCH();
    // p = s + beta p
    {
-      FPcgDirection f{c->d_scalars, z, it.p};
+      FPcgDirection f{c->d_scalars, z, it.p, 0.0};
       B200_TRY(run_ewise(c, it.n, f, nullptr));
    }
    return B200_OK;

@@ -2,13 +2,13 @@
 #include "vecops.cuh"
 #include "p2p.cuh"
 
-struct FFill  { static constexpr int NRED = 0; double a; double *y;
+struct FFill  { static constexpr int NRED = 0; __device__ void init() {} double a; double *y;
    __device__ void operator()(int i, double *) const { y[i] = a; } };
-struct FScale { static constexpr int NRED = 0; double a; double *y;
+struct FScale { static constexpr int NRED = 0; __device__ void init() {} double a; double *y;
    __device__ void operator()(int i, double *) const { y[i] *= a; } };
-struct FAxpy  { static constexpr int NRED = 0; double a; const double *x; double *y;
+struct FAxpy  { static constexpr int NRED = 0; __device__ void init() {} double a; const double *x; double *y;
    __device__ void operator()(int i, double *) const { y[i] = fma(a, x[i], y[i]); } };
-struct FDot   { static constexpr int NRED = 1; const double *x; const double *y;
+struct FDot   { static constexpr int NRED = 1; __device__ void init() {} const double *x; const double *y;
    __device__ void operator()(int i, double *red) const { red[0] = fma(x[i], y[i], red[0]); } };
 
 int vec_fill(b200_ctx *c, int n, double a, double *y)

@@ -9,6 +9,7 @@ template <class F>
 __global__ void __launch_bounds__(ROWK_BLOCK) ewise_kernel(int n, F f, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
+   f.init();      // per-thread preparation (scalars read once from device memory); no-op for most functors
    double red[F::NRED > 0 ? F::NRED : 1];
 #pragma unroll
    for (int k = 0; k < (F::NRED > 0 ? F::NRED : 1); k++) { red[k] = 0.0; }

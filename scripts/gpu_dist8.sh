@@ -1,0 +1,8 @@
+#!/bin/bash
+N=8
+mkdir -p gpurun_out
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29544"
+timeout 600 $TR tests/dist_gpu_worker.py > gpurun_out/dist${N}.log 2>&1; echo "rc=$?" >> gpurun_out/dist${N}.log
+timeout 300 $TR bench.py --gpus $N --workload lap7_100_l1jac --steps 3 --warmup 3 > gpurun_out/bench${N}_100.log 2>&1; echo "rc=$?" >> gpurun_out/bench${N}_100.log
+timeout 600 $TR bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench${N}_256.log 2>&1; echo "rc=$?" >> gpurun_out/bench${N}_256.log
+tail -n 9 gpurun_out/dist${N}.log; for f in gpurun_out/bench${N}_*.log; do echo $f; tail -n 2 $f | cut -c 1-330; done
