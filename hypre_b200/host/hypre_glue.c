@@ -53,6 +53,8 @@ typedef struct mirror_s {
    b200_amg        *amg;
    b200_parcsr     *A;        /* level-0 operator (owned by amg when amg != NULL) */
    int              first_row, first_col;   /* this rank's offset into the global host vectors */
+   int             *starts;   /* distributed mode: (levels) x (nranks+1) row starts; NULL otherwise */
+   int              num_levels, repl_level;
    struct mirror_s *next;
 } mirror_t;
 static mirror_t *g_mirrors = NULL;
@@ -117,6 +119,7 @@ static void mirror_drop(void *key)
          *pp = m->next;
          if (m->amg) { b200_amg_destroy(m->amg); }
          else if (m->A) { b200_parcsr_destroy(m->A); }
+         free(m->starts);
          free(m);
          return;
       }
@@ -219,7 +222,7 @@ static b200_parcsr *upload_parcsr_row_slab(hypre_ParCSRMatrix *A, int r0, int r1
 }
 
 /* hypre_ParAMGData (after the reference's host setup) -> b200_amg */
-static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
+static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *repl_out)
 {
    b200_ctx  *ctx = glue_ctx();
    b200_amg  *amg = NULL;
@@ -376,6 +379,8 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data)
       }
       if (status != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
    }
+   if (starts_out) { *starts_out = starts; starts = NULL; }
+   if (repl_out) { *repl_out = repl; }
    free(starts);
 #undef STARTS
    if (b200_amg_finalize(amg) != B200_OK) { b200_amg_destroy(amg); return NULL; }
@@ -432,10 +437,12 @@ static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
    mirror_t *m = mirror_find(amg_data);
    if (m) { return m; }
    {
-      b200_amg *amg = upload_amg(amg_data);
-      if (!amg) { return NULL; }
+      int *starts = NULL, repl = 1 << 30;
+      b200_amg *amg = upload_amg(amg_data, &starts, &repl);
+      if (!amg) { free(starts); return NULL; }
       m = (mirror_t *) calloc(1, sizeof(mirror_t));
       m->key = amg_data; m->amg = amg;
+      m->starts = starts; m->repl_level = repl; m->num_levels = (int) hypre_ParAMGDataNumLevels(amg_data);
       b200_amg_level_matrix(amg, 0, &m->A);
       if (g_nranks > 1)
       {
@@ -639,6 +646,16 @@ b200_parcsr *hypre_b200_matrix_mirror(void *parcsr)
 {
    mirror_t *m = mirror_for_matrix((hypre_ParCSRMatrix *) parcsr);
    return m ? m->A : NULL;
+}
+/* distributed mode: row starts (nranks+1 entries) of `level` of the mirrored hierarchy.  Returns the
+ * number of row blocks: nranks for a distributed level, 1 for a replicated level or a single rank. */
+int hypre_b200_amg_level_starts(void *amg_vdata, int level, int *out)
+{
+   mirror_t *m = mirror_find(amg_vdata);
+   int r;
+   if (!m || !m->starts || level < 0 || level >= m->num_levels || level >= m->repl_level) { return 1; }
+   for (r = 0; r <= g_nranks; r++) { out[r] = m->starts[(size_t) level * (g_nranks + 1) + r]; }
+   return g_nranks;
 }
 /* this rank's first row of the level-0 operator mirrored for `key` (amg data or matrix) */
 int hypre_b200_first_row(void *key)

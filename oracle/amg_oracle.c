@@ -92,6 +92,43 @@ void orc_relax_cheby(int n, const int *ia, const int *ja, const double *a, const
 /* relax_type 11 (inner 1) / 12 (inner 2)
  * (hypre_BoomerAMGRelaxTwoStageGaussSeidelHost, parcsr_ls/par_relax.c:1505-1588).
  * Returns 1 if a diagonal entry (first entry of a row) is zero (hypre_error_in_arg(1)). */
+/* N-rank form: the inner stages use the strict lower part of each rank's DIAG block only (local
+ * column < row, par_relax.c:1562-1581 loops over A_diag), i.e. entries whose column lies in the same
+ * row block [starts[b], starts[b+1]) as the row.  nblocks <= 1 or starts == NULL: one block. */
+int orc_relax_gs2_blocks(int n, const int *ia, const int *ja, const double *a, const double *f, double w,
+                         int inner, double *u, double *vtemp, int nblocks, const int *starts)
+{
+   int i, k, jj, b = 0, err = 0;
+   double multiplier = 1.0;
+   if (nblocks <= 1 || !starts) { return orc_relax_gs2(n, ia, ja, a, f, w, inner, u, vtemp); }
+   for (i = 0; i < n; i++) { if (a[ia[i]] == 0.0) { err = 1; } }
+   orc_csr_matvec(n, ia, ja, a, -w, u, w, f, vtemp);
+   for (i = 0; i < n; i++)
+   {
+      vtemp[i] /= a[ia[i]];
+      u[i] += multiplier * vtemp[i];
+   }
+   multiplier *= -1.0;
+   for (k = 0; k < inner; ++k)
+   {
+      b = nblocks - 1;
+      for (i = n - 1; i >= 0; i--)
+      {
+         double res = 0.0;
+         while (b > 0 && i < starts[b]) { b--; }
+         for (jj = ia[i]; jj < ia[i + 1]; jj++)
+         {
+            int ii = ja[jj];
+            if (ii < i && ii >= starts[b]) { res += a[jj] * vtemp[ii]; }
+         }
+         vtemp[i] = res / a[ia[i]];
+         u[i] += multiplier * vtemp[i];
+      }
+      multiplier *= -1.0;
+   }
+   return err;
+}
+
 int orc_relax_gs2(int n, const int *ia, const int *ja, const double *a, const double *f, double w,
                   int inner, double *u, double *vtemp)
 {

@@ -23,6 +23,8 @@ void orc_relax_cheby(int n, const int *ia, const int *ja, const double *a, const
                      double *v, double *r, double *orig_u, double *tmp);
 int  orc_relax_gs2(int n, const int *ia, const int *ja, const double *a, const double *f, double w,
                    int inner, double *u, double *vtemp);
+int  orc_relax_gs2_blocks(int n, const int *ia, const int *ja, const double *a, const double *f, double w,
+                          int inner, double *u, double *vtemp, int nblocks, const int *starts);
 int  orc_gselim(double *A, double *x, int n);
 
 orc_amg *orc_amg_create(int num_levels);
@@ -34,6 +36,8 @@ void orc_amg_set_level(orc_amg *h, int level, int n, const int *Ai, const int *A
 void orc_amg_set_cycle(orc_amg *h, const int relax_type[4], const int num_sweeps[4], int cycle_type,
                        int fcycle, int cheby_order, int cheby_scale);
 void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat);
+/* N-rank row partition of a level (nblocks+1 starts, copied): only two-stage GS depends on it */
+void orc_amg_set_level_blocks(orc_amg *h, int level, int nblocks, const int *starts);
 int  orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros);
 /* returns the iteration count; rel_norms[1..iters] = ||r||/||b|| (two_norm) */
 int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, int two_norm,

@@ -13,6 +13,7 @@ typedef struct {
    double relax_weight;
    double *F, *U;          /* owned for level > 0 */
    int all_zeros;          /* hypre_ParVectorAllZeros(U) */
+   int nblocks; int *starts;   /* N-rank row partition (two-stage GS only); NULL = one rank */
 } orc_level;
 
 struct orc_amg {
@@ -41,6 +42,7 @@ void orc_amg_destroy(orc_amg *h)
    int l;
    if (!h) { return; }
    for (l = 1; l < h->num_levels; l++) { free(h->L[l].F); free(h->L[l].U); }
+   for (l = 0; l < h->num_levels; l++) { free(h->L[l].starts); }
    free(h->L); free(h->A_mat); free(h->A_work); free(h->b_vec);
    free(h->Vtemp); free(h->Ztemp); free(h->Ptemp); free(h->Rtemp);
    free(h);
@@ -80,6 +82,20 @@ void orc_amg_set_cycle(orc_amg *h, const int relax_type[4], const int num_sweeps
    h->cheby_order = cheby_order; h->cheby_scale = cheby_scale;
 }
 
+void orc_amg_set_level_blocks(orc_amg *h, int level, int nblocks, const int *starts)
+{
+   orc_level *L = &h->L[level];
+   int k;
+   free(L->starts);
+   L->starts = NULL; L->nblocks = 0;
+   if (nblocks > 1 && starts)
+   {
+      L->starts = (int *) malloc(sizeof(int) * (size_t)(nblocks + 1));
+      for (k = 0; k <= nblocks; k++) { L->starts[k] = starts[k]; }
+      L->nblocks = nblocks;
+   }
+}
+
 void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat)
 {
    free(h->A_mat); free(h->A_work); free(h->b_vec);
@@ -106,7 +122,8 @@ static int orc_relax(orc_amg *h, int level, int relax_type, const double *f, dou
                          u, h->Vtemp, h->Ztemp, h->Ptemp, h->Rtemp);
          break;
       case 11: case 12:
-         err = orc_relax_gs2(L->n, L->Ai, L->Aj, L->Aa, f, L->relax_weight, relax_type == 11 ? 1 : 2, u, h->Vtemp);
+         err = orc_relax_gs2_blocks(L->n, L->Ai, L->Aj, L->Aa, f, L->relax_weight, relax_type == 11 ? 1 : 2, u, h->Vtemp,
+                                    L->nblocks, L->starts);
          break;
       case 9:
          /* hypre_GaussElimSolve type 9 (par_gauss_elim.c:563-651): copy A_mat, eliminate, copy slice */

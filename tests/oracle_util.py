@@ -29,6 +29,8 @@ def lib():
         L.orc_amg_set_level.argtypes = [vp, i, i, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, d]
         L.orc_amg_set_cycle.argtypes = [vp, vp, vp, i, i, i, i]
         L.orc_amg_set_coarse_dense.argtypes = [vp, i, vp]
+        L.orc_amg_set_level_blocks.argtypes = [vp, i, i, vp]
+        L.orc_relax_gs2_blocks.argtypes = [i, vp, vp, vp, vp, d, i, vp, vp, i, vp]
         L.orc_amg_cycle.argtypes = [vp, vp, vp, i]
         L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
         _lib = L
@@ -123,6 +125,11 @@ class OracleAMG:
         if dense is not None:
             dense = np.ascontiguousarray(dense)
             L.orc_amg_set_coarse_dense(self.h, dense.shape[0], p(dense))
+
+    def set_level_blocks(self, level, starts):
+        """N-rank row partition of a level (two-stage GS uses the rank-local strict lower triangle)"""
+        st = np.ascontiguousarray(starts, dtype=np.int32)
+        lib().orc_amg_set_level_blocks(self.h, level, len(st) - 1, p(st))
 
     def cycle(self, f, u, all_zeros):
         u = np.array(u, dtype=np.float64, copy=True)

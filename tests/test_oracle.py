@@ -142,3 +142,43 @@ def test_gselim_restatement():
         np.testing.assert_allclose(x, np.linalg.solve(M, rhs), rtol=1e-10)
     A = np.zeros((1, 1)); x = np.ones(1)
     assert O.lib().orc_gselim(O.p(A), O.p(x), 1) == 1
+
+
+@pytest.mark.parametrize("inner", [1, 2])
+def test_gs2_block_partitioned_restatement(ref_off, inner):
+    """N-rank two-stage GS: the inner stages use the strict lower triangle of each rank's diag block.
+    One block must reproduce the single-rank routine; several blocks are checked against a matrix
+    formulation z_{k+1} = D^{-1} L_blocks z_k, u += (-1)^k z_k."""
+    import scipy.sparse as sp
+    H = ref_off
+    A = H.laplacian_27pt(9, 8, 7).blocks()[0]
+    n = A.shape[0]
+    ii, jj, aa = O.csr_arrays(A)
+    rng = np.random.default_rng(3)
+    f, u0 = rng.standard_normal(n), rng.standard_normal(n)
+    L = O.lib()
+
+    def run(starts):
+        u = u0.copy(); vt = np.zeros(n)
+        st = np.ascontiguousarray(starts, dtype=np.int32)
+        err = L.orc_relax_gs2_blocks(n, O.p(ii), O.p(jj), O.p(aa), O.p(f), 1.0, inner, O.p(u), O.p(vt), len(st) - 1, O.p(st))
+        assert err == 0
+        return u
+
+    u_one, err = O.relax_gs2(A, f, 1.0, inner, u0)
+    assert np.array_equal(run([0, n]), u_one)
+    starts = [0, 100, 230, 231, n]
+    d = A.diagonal()
+    Lb = sp.tril(A, k=-1).tocoo()
+    blk = np.searchsorted(starts, np.arange(n), side="right") - 1
+    keep = blk[Lb.row] == blk[Lb.col]
+    Lb = sp.csr_matrix((Lb.data[keep], (Lb.row[keep], Lb.col[keep])), shape=(n, n))
+    z = (f - A @ u0) / d
+    u = u0 + z
+    sign = -1.0
+    for _ in range(inner):
+        z = (Lb @ z) / d
+        u = u + sign * z
+        sign = -sign
+    np.testing.assert_allclose(run(starts), u, rtol=1e-13, atol=1e-14)
+    assert not np.allclose(run(starts), u_one, rtol=1e-6)      # the partition does matter
