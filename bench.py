@@ -334,8 +334,8 @@ def run_b200(args, rank, world):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "levels": amg.num_levels,
                    "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration)" % (iter_bytes / 1e9),
-                   "final_rel_residual": float(rel[iters]), "level0_layout": "sliced-ELL" if layout.value == 1 else
-                   "CSR-vector/%d" % lanes.value},
+                   "final_rel_residual": float(rel[iters]), "level0_layout": {1: "sliced-ELL", 2: "sliced-ELL, rows sorted in 256-row windows"}.get(
+                       layout.value, "CSR-vector/%d" % lanes.value)},
         "e2e": {"value": e2e_value, "unit": "DOF*it/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 8 * n,
                 "iterations_per_step": e2e_iters, "ms_per_step": 1e3 * e2e_s / args.steps,
                 "final_rel_residual": float(api_rel[-1]) if len(api_rel) else None},

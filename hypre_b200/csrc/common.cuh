@@ -124,8 +124,12 @@ void prof_end(b200_ctx *c);
 #define CHECK_LAUNCH()  CUDA_TRY(cudaGetLastError())
 
 // ---------------------------------------------------------------- matrices
-// One CSR block in HBM.  Two layouts are kept:
+// One CSR block in HBM.  Three layouts:
 //   layout 0 (CSR-vector): rp/ci/va as given; `lanes` lanes of a warp cooperate on a row
+//   layout 2 (sliced ELL with row sorting, "SELL-32-256"): as layout 1, but inside every window of
+//            256 rows the rows are stably sorted by length before they are cut into slices, so
+//            ragged rows (interpolation: 1-4 entries, coarse operators) pad almost nothing;
+//            perm[p] = offset in its window of the row stored at position p
 //   layout 1 (sliced ELL, slice height 32): slice s holds rows 32s..32s+31, entry k of
 //            lane l at sl_off[s] + k*32 + l  -> every warp load is one contiguous
 //            128 B (ci) / 256 B (va) segment; padded entries have va = 0.
@@ -140,6 +144,8 @@ struct DMat {
    int        n_slices = 0;
    long long  sell_entries = 0;
    long long *sl_off = nullptr;  // [n_slices+1]
+   unsigned short *sl_perm = nullptr;   // layout 2: [n_slices*32]
+   std::vector<int> h_pos;              // layout 2: storage position of every row (host)
    int       *sl_ci  = nullptr;
    double    *sl_va  = nullptr;
    int        max_row = 0;
@@ -153,6 +159,7 @@ struct MatView {
    const int       *ci;
    const double    *va;
    const long long *sl_off;
+   const unsigned short *perm;   // layout 2 only, else nullptr
    const int       *sl_ci;
    const double    *sl_va;
 };
@@ -161,7 +168,7 @@ static inline MatView view_of(const DMat &m)
 {
    MatView v;
    v.n_rows = m.n_rows; v.rp = m.rp; v.ci = m.ci; v.va = m.va;
-   v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va;
+   v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va; v.perm = m.sl_perm;
    return v;
 }
 

@@ -9,7 +9,7 @@ static int g_lanes_override  = -1;
 
 extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
 {
-   ARG_CHECK(layout >= -1 && layout <= 1);
+   ARG_CHECK(layout >= -1 && layout <= 2);
    ARG_CHECK(lanes_per_row == -1 || lanes_per_row == 1 || lanes_per_row == 2 || lanes_per_row == 4 || lanes_per_row == 8 ||
              lanes_per_row == 16 || lanes_per_row == 32);
    g_layout_override = layout;
@@ -17,10 +17,25 @@ extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
    return B200_OK;
 }
 
+// longest run [out[0], out[1]) of groups whose flag is clear
+static void longest_clear_run(const std::vector<unsigned char> &g, int n_groups, int *out)
+{
+   int best_b = 0, best_e = 0, b = 0;
+   for (int k = 0; k <= n_groups; k++)
+   {
+      if (k == n_groups || g[(size_t)k])
+      {
+         if (k - b > best_e - best_b) { best_b = b; best_e = k; }
+         b = k + 1;
+      }
+   }
+   out[0] = best_b; out[1] = best_e;
+}
+
 void dmat_free(DMat *m)
 {
    cudaFree(m->rp); cudaFree(m->ci); cudaFree(m->va);
-   cudaFree(m->sl_off); cudaFree(m->sl_ci); cudaFree(m->sl_va);
+   cudaFree(m->sl_off); cudaFree(m->sl_ci); cudaFree(m->sl_va); cudaFree(m->sl_perm);
    *m = DMat();
 }
 
@@ -68,16 +83,43 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    m->avg_row = (double)m->nnz / (double)n;
 
    const int n_slices = (n + 31) / 32;
-   std::vector<long long> sl_off((size_t)n_slices + 1, 0);
-   for (int s = 0; s < n_slices; s++)
+   // storage order: identity (layout 1) or rows stably sorted by decreasing length inside every
+   // window of 256 rows (layout 2); order[p] = row stored at position p (>= n: padding lane)
+   auto slice_offsets = [&](const std::vector<int> &order, std::vector<long long> *off) {
+      off->assign((size_t)n_slices + 1, 0);
+      for (int sidx = 0; sidx < n_slices; sidx++)
+      {
+         int w = 0;
+         for (int l = 0; l < 32; l++)
+         {
+            const int r = order[(size_t)sidx * 32 + l];
+            if (r < n) { w = std::max(w, h.i[r + 1] - h.i[r]); }
+         }
+         (*off)[(size_t)sidx + 1] = (*off)[(size_t)sidx] + (long long)w * 32;
+      }
+   };
+   std::vector<int> ident((size_t)n_slices * 32), sorted((size_t)n_slices * 32);
+   for (size_t p = 0; p < ident.size(); p++) { ident[p] = (int)p; }
+   sorted = ident;
+   for (int w0 = 0; w0 < n_slices * 32; w0 += 256)
    {
-      int w = 0;
-      for (int r = s * 32; r < std::min(n, s * 32 + 32); r++) { w = std::max(w, h.i[r + 1] - h.i[r]); }
-      sl_off[s + 1] = sl_off[s] + (long long)w * 32;
+      const int w1 = std::min(w0 + 256, n_slices * 32);
+      std::stable_sort(sorted.begin() + w0, sorted.begin() + w1, [&](int a, int b) {
+         const int la = a < n ? h.i[a + 1] - h.i[a] : -1, lb = b < n ? h.i[b + 1] - h.i[b] : -1;
+         return la > lb;
+      });
    }
-   const long long padded = sl_off[n_slices];
+   std::vector<long long> off_plain, off_sorted;
+   slice_offsets(ident, &off_plain);
+   slice_offsets(sorted, &off_sorted);
+   const double nnz_d = (double)m->nnz;
 
-   int layout = (allow_sell && m->nnz > 0 && (double)padded <= 1.125 * (double)m->nnz) ? 1 : 0;
+   int layout = 0;
+   if (allow_sell && m->nnz > 0)
+   {
+      if ((double)off_plain[n_slices] <= 1.125 * nnz_d) { layout = 1; }
+      else if ((double)off_sorted[n_slices] <= 1.125 * nnz_d) { layout = 2; }
+   }
    int lanes;
    if      (m->avg_row > 48.0) { lanes = 32; }
    else if (m->avg_row > 24.0) { lanes = 16; }
@@ -89,22 +131,25 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    if (g_lanes_override > 0) { lanes = g_lanes_override; }
    m->layout = layout; m->lanes = lanes;
 
-   if (layout == 1)
+   if (layout >= 1)
    {
+      const std::vector<int> &order = layout == 2 ? sorted : ident;
+      const std::vector<long long> &sl_off = layout == 2 ? off_sorted : off_plain;
+      const long long padded = sl_off[n_slices];
       std::vector<int>    sci((size_t)padded);
       std::vector<double> sva((size_t)padded);
-      for (int s = 0; s < n_slices; s++)
+      for (int sidx = 0; sidx < n_slices; sidx++)
       {
-         const int w = (int)((sl_off[s + 1] - sl_off[s]) / 32);
+         const int w = (int)((sl_off[(size_t)sidx + 1] - sl_off[(size_t)sidx]) / 32);
          for (int l = 0; l < 32; l++)
          {
-            const int r = s * 32 + l;
+            const int r = order[(size_t)sidx * 32 + l];
             const int beg = r < n ? h.i[r] : 0, len = r < n ? h.i[r + 1] - h.i[r] : 0;
             // padding gathers a column this row already touches (or column 0)
             const int padc = len > 0 ? h.j[beg + len - 1] : 0;
             for (int k = 0; k < w; k++)
             {
-               const size_t p = (size_t)sl_off[s] + (size_t)k * 32 + l;
+               const size_t p = (size_t)sl_off[(size_t)sidx] + (size_t)k * 32 + l;
                if (k < len) { sci[p] = h.j[beg + k]; sva[p] = h.a[beg + k]; }
                else         { sci[p] = padc;         sva[p] = 0.0; }
             }
@@ -114,6 +159,17 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
       B200_TRY(dev_upload(&m->sl_off, sl_off.data(), sl_off.size()));
       B200_TRY(dev_upload(&m->sl_ci, sci.data(), sci.size()));
       B200_TRY(dev_upload(&m->sl_va, sva.data(), sva.size()));
+      if (layout == 2)
+      {
+         std::vector<unsigned short> perm(order.size());
+         m->h_pos.assign((size_t)n, 0);
+         for (size_t p = 0; p < order.size(); p++)
+         {
+            perm[p] = (unsigned short)(order[p] - (int)(p / 256) * 256);    // < 256 + 32
+            if (order[p] < n) { m->h_pos[(size_t)order[p]] = (int)p; }
+         }
+         B200_TRY(dev_upload(&m->sl_perm, perm.data(), perm.size()));
+      }
    }
    return B200_OK;
 }
@@ -210,28 +266,22 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
    }
    if (ctx->use_p2p && (num_sends + num_recvs) > 0)
    {
-      std::vector<unsigned char> gf((size_t)(n_rows + 31) / 32 + 1, 0), gr((size_t)(n_cols_diag + 31) / 32 + 1, 0);
+      // 32-row STORAGE groups of the diag block that contain a row with offd entries (layout 2 stores
+      // the rows of a window in sorted order: use the storage position)
+      std::vector<unsigned char> gf((size_t)(n_rows + 31) / 32 + 1, 0);
       if (n_cols_offd > 0)
       {
-         for (int r = 0; r < n_rows; r++) { if (A->h_offd.i[r + 1] > A->h_offd.i[r]) { gf[(size_t)r >> 5] = 1; } }
-      }
-      for (int k = 0; k < A->n_send_elmts; k++) { gr[(size_t)send_map_elmts[k] >> 5] = 1; }
-      auto longest_clear_run = [](const std::vector<unsigned char> &g, int n_groups, int *out) {
-         int best_b = 0, best_e = 0, b = 0;
-         for (int k = 0; k <= n_groups; k++)
+         for (int r = 0; r < n_rows; r++)
          {
-            if (k == n_groups || g[(size_t)k])
+            if (A->h_offd.i[r + 1] > A->h_offd.i[r])
             {
-               if (k - b > best_e - best_b) { best_b = b; best_e = k; }
-               b = k + 1;
+               const int pos = A->diag.layout == 2 ? A->diag.h_pos[(size_t)r] : r;
+               gf[(size_t)pos >> 5] = 1;
             }
          }
-         out[0] = best_b; out[1] = best_e;
-      };
+      }
       longest_clear_run(gf, (n_rows + 31) / 32, A->int_fwd);
-      longest_clear_run(gr, (n_cols_diag + 31) / 32, A->int_rev);
       s = dev_upload(&A->d_grp_fwd, gf.data(), gf.size());
-      if (s == B200_OK) { s = dev_upload(&A->d_grp_rev, gr.data(), gr.size()); }
       if (s != B200_OK) { b200_parcsr_destroy(A); return s; }
       if (A->d_unpack_rp_dense == nullptr)
       {
@@ -294,6 +344,25 @@ int parcsr_ensure_T(b200_parcsr *A)
       HostCsr to;
       host_transpose(A->h_offd, &to);
       B200_TRY(dmat_upload(A->ctx, to, &A->offdT, 0));
+   }
+   if (A->ctx->use_p2p && (A->num_sends + A->num_recvs) > 0)
+   {
+      // storage groups of diag^T whose rows receive contributions from other ranks (A^T x, job 2)
+      const int nr = A->n_cols_diag;
+      std::vector<unsigned char> gr((size_t)(nr + 31) / 32 + 1, 0);
+      std::vector<int> sme((size_t)A->n_send_elmts);
+      if (A->n_send_elmts > 0)
+      {
+         CUDA_TRY(cudaMemcpy(sme.data(), A->d_send_map, sizeof(int) * sme.size(), cudaMemcpyDeviceToHost));
+      }
+      for (int k = 0; k < A->n_send_elmts; k++)
+      {
+         const int pos = A->diagT.layout == 2 ? A->diagT.h_pos[(size_t)sme[(size_t)k]] : sme[(size_t)k];
+         gr[(size_t)pos >> 5] = 1;
+      }
+      longest_clear_run(gr, (nr + 31) / 32, A->int_rev);
+      cudaFree(A->d_grp_rev); A->d_grp_rev = nullptr;
+      B200_TRY(dev_upload(&A->d_grp_rev, gr.data(), gr.size()));
    }
    A->hasT = true;
    return B200_OK;

@@ -269,7 +269,8 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
       const int wpb = ROWK_BLOCK / 32;
       for (int slice = g_begin + vblock * wpb + (threadIdx.x >> 5); slice < g_end; slice += gridDim.x * wpb)
       {
-         const int row = (slice << 5) + lane;
+         int row = (slice << 5) + lane;
+         if (D.perm != nullptr) { row = ((slice >> 3) << 8) + D.perm[row]; }   // sorted inside 256-row windows
          const bool live = row < D.n_rows;
          double t = rowsum_sell(D, slice, lane, x);
          bool skip = false;

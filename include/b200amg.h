@@ -96,7 +96,7 @@ int b200_parcsr_create(b200_ctx *ctx,
                        b200_parcsr **A);
 int b200_parcsr_destroy(b200_parcsr *A);
 int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *nnz,
-                     int *layout /* 0 = CSR-vector, 1 = sliced-ELL */, int *lanes_per_row);
+                     int *layout /* 0 = CSR-vector, 1 = sliced-ELL, 2 = sliced-ELL with rows sorted in 256-row windows */, int *lanes_per_row);
 /* force the storage layout chosen for the diag block (tests/bench): -1 auto */
 int b200_set_layout_override(int layout, int lanes_per_row);
 

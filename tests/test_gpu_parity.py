@@ -47,7 +47,7 @@ def hier(H):
     return O.build_case(H, "lap7_32_rlx18")
 
 
-@pytest.mark.parametrize("override", [(-1, -1), (1, -1), (0, 1), (0, 2), (0, 4), (0, 8), (0, 16), (0, 32)])
+@pytest.mark.parametrize("override", [(-1, -1), (1, -1), (2, -1), (0, 1), (0, 2), (0, 4), (0, 8), (0, 16), (0, 32)])
 def test_spmv_matches_oracle_all_layouts(H, ctx, hier, override):
     L = capi.lib()
     rng = np.random.default_rng(10)
@@ -116,7 +116,7 @@ def test_edge_cases_empty_single_ragged(ctx):
     A[100:140, :] = 0.0                    # empty rows
     A = A.tocsr(); A.eliminate_zeros()
     x = rng.standard_normal(m)
-    for override in [(-1, -1), (1, -1), (0, 1), (0, 2), (0, 32)]:
+    for override in [(-1, -1), (1, -1), (2, -1), (0, 1), (0, 2), (0, 32)]:
         capi.check(L.b200_set_layout_override(*override))
         dA = capi.parcsr_from_scipy(ctx, A)
         dx, dy = dvec(ctx, x), capi.DeviceVector(ctx, n)
