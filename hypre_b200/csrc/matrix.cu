@@ -114,8 +114,10 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    slice_offsets(sorted, &off_sorted);
    const double nnz_d = (double)m->nnz;
 
+   // thread-per-row layouts need rows to fill the machine (148 SMs x 2048 threads); smaller blocks
+   // (coarse levels) keep CSR with several lanes per row, which exposes nnz-level parallelism
    int layout = 0;
-   if (allow_sell && m->nnz > 0)
+   if (allow_sell && m->nnz > 0 && n >= 131072)
    {
       if ((double)off_plain[n_slices] <= 1.125 * nnz_d) { layout = 1; }
       else if ((double)off_sorted[n_slices] <= 1.125 * nnz_d) { layout = 2; }

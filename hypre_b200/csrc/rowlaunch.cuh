@@ -43,7 +43,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    }
    // (a rank without rows still launches in the peer-memory modes: its blocks carry the put phase
    //  and the reduction publishes the zero)
-   if (D.layout == 1 || D.n_rows == 0)
+   if (D.layout >= 1 || D.n_rows == 0)
    {
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
       LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);
