@@ -468,6 +468,11 @@ extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes)
             case 18: case 7: return zero ? 24.0 * n : spmv + 32.0 * n;       // u,f,l1 in, u out
             case 16: {
                int k = (L.cheby_order > 4 ? 4 : L.cheby_order) - 1;
+               if (zero && k >= 1)
+               {
+                  // fused first step (EpiChebyZero): f, ds in, u (or out, r) out; then k-1 plain steps
+                  return spmv + 24.0 * n + (k > 1 ? 16.0 * n : 0.0) + (k - 1) * (spmv + 40.0 * n);
+               }
                double first = zero ? 32.0 * n : spmv + 40.0 * n;            // u,f,ds in; r,tmp out
                return first + k * (spmv + 40.0 * n);                         // tmp,r,ds,u in; u/out
             }

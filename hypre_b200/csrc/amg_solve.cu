@@ -9,6 +9,7 @@
 // r = b - t ; red0 += r*r
 struct EpiResidualNorm {
    static constexpr int NRED = 1;
+   EPI_PLAIN_X
    const double *b; double *r;
    __device__ void operator()(int row, double t, double *red) const
    {

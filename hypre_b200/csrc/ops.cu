@@ -7,6 +7,7 @@
 // y = alpha*t + beta*b           hypre_CSRMatrixMatvecOutOfPlaceHost (src/seq_mv/csr_matvec.c:683-847)
 struct EpiMatvec {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    double alpha, beta; const double *b; double *y;
    __device__ void operator()(int r, double t, double *) const
    {
@@ -18,6 +19,7 @@ struct EpiMatvec {
 // y = t, red0 += y*x             PCG: s = A p and <s,p> (src/krylov/pcg.c:577-580)
 struct EpiMatvecDot {
    static constexpr int NRED = 1;
+   EPI_PLAIN_X
    const double *x; double *y;
    __device__ void operator()(int r, double t, double *red) const
    {
@@ -28,6 +30,7 @@ struct EpiMatvecDot {
 // u_out = u_in + (w*(f - t)) / l1     hypre_BoomerAMGRelax7Jacobi (src/parcsr_ls/par_relax.c:1177-1254)
 struct EpiJacobi {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    double w; const double *f; const double *l1; const double *u_in; double *u_out;
    __device__ void operator()(int r, double t, double *) const
    {
@@ -38,6 +41,7 @@ struct EpiJacobi {
 //   r = ds.*(f - t)  [scale]  |  r = f - t ;  tmp = ds.*(c*r) | c*r
 struct EpiChebyFirst {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    int scale; double c; const double *f; const double *ds; double *rv; double *tmp;
    __device__ void operator()(int r, double t, double *) const
    {
@@ -52,6 +56,7 @@ struct EpiChebyFirst {
 //   out = ds.*u_i (next SpMV input)   or   u += ds.*u_i (last step)
 struct EpiChebyStep {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    int scale; int last; double c; const double *ds; const double *rv; double *out; double *u;
    __device__ void operator()(int r, double t, double *) const
    {
@@ -61,9 +66,37 @@ struct EpiChebyStep {
       else      { out[r] = su; }
    }
 };
+// Chebyshev with a zero initial guess (u == 0 on entry: PCG's ClearVector, the cycle's U[l+1] = 0):
+// the first step needs no SpMV (A*0 == 0): r = ds.*f, tmp = ds.*(c_k*r).  Instead of writing r and
+// tmp in an elementwise pass, the next SpMV computes its gathered operand tmp_j from f_j, ds_j on the
+// fly (xval) and recomputes r_i in the epilogue -- the same floating-point operations in the same
+// order (par_cheby.c:318-371), with r, tmp never written for order 2 and u written once.
+struct EpiChebyZero {
+   static constexpr int NRED = 0;
+   int scale; int last; int write_r; double ck; double ci; const double *f; const double *ds; double *rv;
+   double *out; double *u;
+   __device__ __forceinline__ double xval(const double *__restrict__, int j) const
+   {
+      double res = __ldg(f + j);
+      if (scale) { res = __ldg(ds + j) * res; }
+      const double u1 = res * ck;
+      return scale ? __ldg(ds + j) * u1 : u1;
+   }
+   __device__ void operator()(int r, double t, double *) const
+   {
+      double res = f[r];
+      if (scale) { res = ds[r] * res; }
+      if (write_r) { rv[r] = res; }
+      double ui = scale ? ci * res + ds[r] * t : ci * res + t;
+      double su = scale ? ds[r] * ui : ui;
+      if (last) { u[r] = su; }      // u == 0: 0 + su
+      else      { out[r] = su; }
+   }
+};
 // two-stage GS first stage (par_relax.c:1546-1557): z0 = (w*(f - t))/d
 struct EpiGsFirst {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    double w; const double *f; const double *d; double *z;
    __device__ void operator()(int r, double t, double *) const { z[r] = (w * (f[r] - t)) / d[r]; }
 };
@@ -71,6 +104,7 @@ struct EpiGsFirst {
 // (first inner stage also applies the pending u += z0)
 struct EpiGsInner {
    static constexpr int NRED = 0;
+   EPI_PLAIN_X
    int first; double mult; const double *d; const double *z_in; double *z_out; double *u;
    __device__ void operator()(int r, double t, double *) const
    {
@@ -169,7 +203,21 @@ int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *co
    const int k = order - 1;   // cheby_order (par_cheby.c:262)
    b200_ctx *c = A->ctx;
    const int n = A->n_rows;
-   if (zero_guess)
+   int i_first = k - 1;
+   double *in = tmp, *out = v;
+   // (the NCCL baseline path packs the raw vector with its own kernel, so it keeps the unfused form)
+   const bool can_fuse = (A->num_sends + A->num_recvs) == 0 || A->ch_fwd != nullptr;
+   if (zero_guess && k >= 1 && can_fuse)
+   {
+      // first elementwise step fused into the first polynomial SpMV (see EpiChebyZero)
+      const int last = (k == 1) ? 1 : 0;
+      EpiChebyZero e{scale, last, k > 1 ? 1 : 0, coefs_h[k], coefs_h[k - 1], f, ds, r, out, u};
+      B200_TRY(run_rows(A, A->diag, A->offd, true, f, e, nullptr));
+      if (last) { return B200_OK; }
+      double *t = in; in = out; out = t;
+      i_first = k - 2;
+   }
+   else if (zero_guess)
    {
       FChebyFirst0 f0{scale, coefs_h[k], f, ds, r, tmp};
       B200_TRY(run_ewise(c, n, f0, nullptr));
@@ -184,8 +232,7 @@ int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *co
       // u = orig_u + ds.*u1  (tmp already holds ds.*u1)
       return zero_guess ? b200_vec_copy(c, n, tmp, u) : vec_axpy(c, n, 1.0, tmp, u);
    }
-   double *in = tmp, *out = v;
-   for (int i = k - 1; i >= 0; i--)
+   for (int i = i_first; i >= 0; i--)
    {
       EpiChebyStep e{scale, i == 0 ? 1 : 0, coefs_h[i], ds, r, out, u};
       if (i == 0 && zero_guess)

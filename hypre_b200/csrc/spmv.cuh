@@ -97,14 +97,20 @@ __device__ __forceinline__ void grid_reduce(double (&red)[NRED > 0 ? NRED : 1], 
 }
 
 // ---------------------------------------------------------------- row sums
+// The gathered operand x_j is obtained through the epilogue functor: xval(x, j).  Plain operators
+// read x[j]; a fused operator may compute it from other vectors on the fly (Chebyshev with a zero
+// initial guess: x_j = ds_j * (c * (ds_j * f_j)), so the vectors r and tmp are never materialised).
+#define EPI_PLAIN_X __device__ __forceinline__ double xval(const double *__restrict__ x, int j) const { return __ldg(x + j); }
+struct XPlain { EPI_PLAIN_X };
 // sliced-ELL, one thread per row (lane = row within the 32-row slice).
 // Memory latency bounds this loop (ncu: >90 % of the stall samples are long-scoreboard) and
 // occupancy hides it: entries are taken in chunks of 4 with a guarded (warp-uniform) tail, which
 // keeps the kernel at 32 registers = 8 resident blocks per SM.  A chunk of 8 (two round trips for a
 // 7-point row) was measured: 54 registers, half the occupancy, 3-10 % slower on 7-pt and 27-pt.
 // The fma chain keeps the storage order.
+template <class XF>
 __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int lane,
-                                              const double *__restrict__ x)
+                                              const double *__restrict__ x, const XF &xf)
 {
    const long long off = D.sl_off[slice];
    const int width = (int)((D.sl_off[slice + 1] - off) >> 5);
@@ -121,7 +127,7 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
 #pragma unroll
       for (int j = 0; j < 4; j++) { v[j] = (j < m) ? ld_stream(va + (k0 + j) * 32) : 0.0; }
 #pragma unroll
-      for (int j = 0; j < 4; j++) { xv[j] = (j < m) ? __ldg(x + c[j]) : 0.0; }
+      for (int j = 0; j < 4; j++) { xv[j] = (j < m) ? xf.xval(x, c[j]) : 0.0; }
 #pragma unroll
       for (int j = 0; j < 4; j++) { if (j < m) { t = fma(v[j], xv[j], t); } }
    }
@@ -133,10 +139,10 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
 template <bool CG>
 __device__ __forceinline__ double ld_x(const double *p) { return CG ? __ldcg(p) : __ldg(p); }
 
-template <int T, bool CG = false>
+template <int T, bool CG, class XF>
 __device__ __forceinline__ double rowsum_csr(const int *__restrict__ rp, const int *__restrict__ ci,
                                              const double *__restrict__ va, int row, int sub,
-                                             const double *__restrict__ x)
+                                             const double *__restrict__ x, const XF &xf)
 {
    const int beg = rp[row], end = rp[row + 1];
    double t = 0.0;
@@ -145,10 +151,14 @@ __device__ __forceinline__ double rowsum_csr(const int *__restrict__ rp, const i
    {
       int    c0 = ld_stream(ci + k), c1 = ld_stream(ci + k + T);
       double v0 = ld_stream(va + k), v1 = ld_stream(va + k + T);
-      double x0 = ld_x<CG>(x + c0), x1 = ld_x<CG>(x + c1);
+      double x0 = CG ? __ldcg(x + c0) : xf.xval(x, c0), x1 = CG ? __ldcg(x + c1) : xf.xval(x, c1);
       t = fma(v0, x0, t); t = fma(v1, x1, t);
    }
-   if (k < end) { t = fma(ld_stream(va + k), ld_x<CG>(x + ld_stream(ci + k)), t); }
+   if (k < end)
+   {
+      const int c0 = ld_stream(ci + k);
+      t = fma(ld_stream(va + k), CG ? __ldcg(x + c0) : xf.xval(x, c0), t);
+   }
 #pragma unroll
    for (int o = T >> 1; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o, T); }
    return t;
@@ -184,8 +194,9 @@ struct HaloArgs {
 };
 
 // sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks)
-template <int HALO>
-__device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *__restrict__ x, int n_put_blocks)
+template <int HALO, class XF>
+__device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *__restrict__ x, int n_put_blocks,
+                                               const XF &xf)
 {
    __shared__ u64  s_seq;
    __shared__ bool s_last_p;
@@ -205,7 +216,7 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
    {
       while (i >= ch.out_starts[seg + 1]) { seg++; }
       double v;
-      if (HALO == HALO_FWD) { v = x[h.map[i]]; }      // pack: x_buf[i] = x_local[send_map_elmts[i]]
+      if (HALO == HALO_FWD) { v = xf.xval(x, h.map[i]); }   // pack: x_buf[i] = x_local[send_map_elmts[i]]
       else
       {
          // row i of offd^T: contribution of my rows to ghost column i
@@ -272,7 +283,7 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          int row = (slice << 5) + lane;
          if (D.perm != nullptr) { row = ((slice >> 3) << 8) + D.perm[row]; }   // sorted inside 256-row windows
          const bool live = row < D.n_rows;
-         double t = rowsum_sell(D, slice, lane, x);
+         double t = rowsum_sell(D, slice, lane, x, epi);
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
          if (HALO == HALO_FWD && h.grp[slice])
@@ -304,14 +315,14 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
       {
          const bool live = row < D.n_rows;
          const int r = live ? row : D.n_rows - 1;
-         double t = rowsum_csr<TT>(D.rp, D.ci, D.va, r, sub, x);
+         double t = rowsum_csr<TT, false>(D.rp, D.ci, D.va, r, sub, x, epi);
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = h.O.rp[r + 1] != h.O.rp[r]; }
          if (HALO == HALO_FWD && h.grp[row >> 5])
          {
             xg = halo_warp_wait(h.ch, xg, h.dbg);
             // all lanes take part (rows without offd entries have an empty range)
-            t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg);
+            t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg, epi);
          }
          if (HALO == HALO_REV && h.grp[row >> 5])
          {
@@ -350,7 +361,7 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       {
          int n_put_blocks = (h.ch.n_out_total + ROWK_BLOCK - 1) / ROWK_BLOCK;
          if (n_put_blocks > (int)gridDim.x) { n_put_blocks = gridDim.x; }
-         if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks); }
+         if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks, epi); }
       }
       // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
       // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
@@ -381,8 +392,8 @@ rowlist_kernel(MatView D, MatView O, const int *__restrict__ rows, int n_list,
    {
       const bool live = idx < n_list;
       const int row = rows[live ? idx : n_list - 1];
-      double t = rowsum_csr<TT>(D.rp, D.ci, D.va, row, sub, x);
-      t += rowsum_csr<TT>(O.rp, O.ci, O.va, row, sub, xg);
+      double t = rowsum_csr<TT, false>(D.rp, D.ci, D.va, row, sub, x, epi);
+      t += rowsum_csr<TT, false>(O.rp, O.ci, O.va, row, sub, xg, XPlain());    // ghosts hold finished values
       if (live && sub == 0) { epi(row, t, red); }
    }
    grid_reduce<Epi::NRED>(red, rc);
