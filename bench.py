@@ -39,6 +39,18 @@ WORKLOADS = {
 }
 
 
+def ncu_traffic(n, nnz):
+    """DRAM bytes per launch of the level-0 SpMV from the committed ncu --set full summary (same matrix)."""
+    p = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
+    try:
+        t = json.load(open(p))
+        if t["matrix"]["rows"] == n and t["matrix"]["nnz"] == nnz:
+            return t["spmv_level0"]["traffic_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -341,7 +353,8 @@ def run_b200(args, rank, world):
                 "final_rel_residual": float(api_rel[-1]) if len(api_rel) else None},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "rows_kernel (level-0 SpMV y=A*x, %.1f MB algorithmic)" % (spmv_bytes / 1e6),
-                     "achieved": spmv_gbs, "peak": peak, "unit": "GB/s", "frac": spmv_gbs / peak, "traffic": None,
+                     "achieved": spmv_gbs, "peak": peak, "unit": "GB/s", "frac": spmv_gbs / peak,
+                     "traffic": ncu_traffic(n, nnz0), "algorithmic_bytes": spmv_bytes,
                      "peak_source": peak_src, "frac_of_8000": spmv_gbs / 8000.0, "ms_per_launch": spmv_ms,
                      "pcg_iteration_gbs": iter_gbs, "pcg_iteration_frac": iter_gbs / peak,
                      "pcg_iteration_bytes": iter_bytes},
