@@ -29,6 +29,23 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+
+def _set_host_threads():
+    """OpenMP threads of the reference's host code, fixed BEFORE any library that carries an OpenMP
+    runtime is loaded (the runtime reads the variable once).  torchrun exports OMP_NUM_THREADS=1 to its
+    workers: the reference arm (rank 0 works alone) takes every host core, our arm shares the cores
+    between the ranks' replicated host setups.  B200_BENCH_THREADS overrides."""
+    ncores = os.cpu_count() or 1
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    ref = any(a == "reference" or a == "--impl=reference" for a in sys.argv[1:])
+    n = ncores if ref else max(1, ncores // max(world, 1))
+    n = int(os.environ.get("B200_BENCH_THREADS", n))
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    return n
+
+
+HOST_THREADS = _set_host_threads()
+
 WORKLOADS = {
     # name: (generator, args, relax_type, ij command line)
     "lap7_256_cheby": ("laplacian", (256, 256, 256), 16, "ij -laplacian -n 256 256 256 -solver 1 -rlx 16"),
@@ -128,8 +145,7 @@ def run_reference(args, rank):
         return
     from hypre_b200 import hypre as H
     H.set_device_path(False)
-    ncores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(ncores))
+    ncores = HOST_THREADS
     P = build_problem(H, args.workload, args.n)
     n = P["A"].global_rows
     P["pcg"].SetMaxIter(args.ref_iters)
@@ -206,9 +222,8 @@ class Ranks:
 
 
 def run_b200(args, rank, world):
-    ncores = os.cpu_count() or 1
-    # every rank runs the (replicated) reference host setup: share the cores
-    os.environ.setdefault("OMP_NUM_THREADS", str(max(1, ncores // world)))
+    # every rank runs the (replicated) reference host setup: the cores are shared (HOST_THREADS)
+    ncores = HOST_THREADS
     R = Ranks(rank, world)       # N > 1: imports torch first so that its bundled NCCL is the one loaded
     from hypre_b200 import capi, hypre as H
     L = capi.lib()
