@@ -56,15 +56,17 @@ WORKLOADS = {
 }
 
 
-def ncu_traffic(n, nnz):
-    """DRAM bytes per launch of the level-0 SpMV from the committed ncu --set full summary (same matrix)."""
-    p = os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")
-    try:
-        t = json.load(open(p))
-        if t["matrix"]["rows"] == n and t["matrix"]["nnz"] == nnz:
-            return t["spmv_level0"]["traffic_bytes_per_launch"]
-    except Exception:
-        pass
+def ncu_traffic(n, nnz, value_format):
+    """DRAM bytes per launch of the level-0 SpMV from a committed ncu --set full summary (same matrix,
+    same storage format)."""
+    for name in ("r01_ncu_traffic_compressed.json", "r01_ncu_traffic.json"):
+        try:
+            t = json.load(open(os.path.join(ROOT, "profiles", name)))
+            mt = t["matrix"]
+            if mt["rows"] == n and mt["nnz"] == nnz and mt.get("value_format", 0) == value_format:
+                return t["spmv_level0"]["traffic_bytes_per_launch"]
+        except Exception:
+            pass
     return None
 
 
@@ -246,8 +248,11 @@ def run_b200(args, rank, world):
     upload_s = time.perf_counter() - t0
     dA = C.c_void_p()
     capi.check(L.b200_amg_level_matrix(damg, 0, C.byref(dA)))
-    cyc_bytes = C.c_double()
+    cyc_bytes = C.c_double(); cyc_stored = C.c_double()
     capi.check(L.b200_amg_cycle_bytes(damg, C.byref(cyc_bytes)))
+    capi.check(L.b200_amg_cycle_bytes_stored(damg, C.byref(cyc_stored)))
+    vfmt = C.c_int(); st_b = C.c_longlong(); csr_b = C.c_longlong(); ndict = C.c_int()
+    capi.check(L.b200_parcsr_storage(dA, C.byref(vfmt), C.byref(st_b), C.byref(csr_b), C.byref(ndict)))
     nnz0 = C.c_longlong(); nrows = C.c_int(); layout = C.c_int(); lanes = C.c_int()
     capi.check(L.b200_parcsr_info(dA, C.byref(nrows), None, C.byref(nnz0), C.byref(layout), C.byref(lanes)))
     nnz0 = nnz0.value
@@ -334,6 +339,9 @@ def run_b200(args, rank, world):
     spmv_ms = ms.value / reps
     spmv_bytes = 12.0 * nnz0 + 4.0 * (n + 1) + 8.0 * n + 8.0 * n
     spmv_gbs = spmv_bytes / (spmv_ms * 1e-3) / 1e9
+    # bytes the device layout stores for the same pass (compressed sliced ELL reads fewer than CSR)
+    spmv_stored = spmv_bytes - csr_b.value + st_b.value
+    iter_stored = cyc_stored.value + spmv_stored + 8.0 * n * (4 + 2 + 3)
     # whole-iteration view: algorithmic bytes of one PCG iteration / time of one iteration
     iter_bytes = cyc_bytes.value + spmv_bytes + 8.0 * n * (4 + 2 + 3)   # update (4 streams+..), dot, direction
     # a solve runs iters+1 preconditioner cycles and SpMVs (the initial residual and p = C r come first)
@@ -360,7 +368,8 @@ def run_b200(args, rank, world):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "levels": amg.num_levels,
-                   "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration)" % (iter_bytes / 1e9),
+                   "l2": "inputs larger than L2 (hierarchy %.1f GB stored / %.1f GB as CSR streamed per iteration)" % (
+                       iter_stored / 1e9, iter_bytes / 1e9),
                    "final_rel_residual": float(rel[iters]), "level0_layout": {1: "sliced-ELL", 2: "sliced-ELL, rows sorted in 256-row windows"}.get(
                        layout.value, "CSR-vector/%d" % lanes.value)},
         "e2e": {"value": e2e_value, "unit": "DOF*it/s", "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 8 * n,
@@ -369,10 +378,19 @@ def run_b200(args, rank, world):
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "rows_kernel (level-0 SpMV y=A*x, %.1f MB algorithmic)" % (spmv_bytes / 1e6),
                      "achieved": spmv_gbs, "peak": peak, "unit": "GB/s", "frac": spmv_gbs / peak,
-                     "traffic": ncu_traffic(n, nnz0), "algorithmic_bytes": spmv_bytes,
+                     "traffic": ncu_traffic(n, nnz0, vfmt.value), "algorithmic_bytes": spmv_bytes,
+                     "stored_bytes": spmv_stored, "stored_gbs": spmv_stored / (spmv_ms * 1e-3) / 1e9,
+                     "stored_frac": spmv_stored / (spmv_ms * 1e-3) / 1e9 / peak,
+                     "storage": {0: "int32 column + fp64 value", 1: "u16 column offset + u8 dictionary code",
+                                 2: "u16 column offset + u16 dictionary code", 3: "u16 column offset + fp64 value"}[vfmt.value]
+                                + (" (%d distinct values)" % ndict.value if vfmt.value in (1, 2) else ""),
+                     "note": "achieved/frac count the reference's CSR bytes (SURVEY 8d); stored_* count the bytes the "
+                             "compressed layout really reads, traffic is the ncu DRAM figure",
                      "peak_source": peak_src, "frac_of_8000": spmv_gbs / 8000.0, "ms_per_launch": spmv_ms,
                      "pcg_iteration_gbs": iter_gbs, "pcg_iteration_frac": iter_gbs / peak,
-                     "pcg_iteration_bytes": iter_bytes},
+                     "pcg_iteration_bytes": iter_bytes, "pcg_iteration_stored_bytes": iter_stored,
+                     "pcg_iteration_stored_gbs": iter_stored * (iters + 1) * args.steps / dev_s / 1e9,
+                     "pcg_iteration_stored_frac": iter_stored * (iters + 1) * args.steps / dev_s / 1e9 / peak},
         "cpu_baseline": cpu, "clocks": clocks,
         "setup_s": P["setup_s"], "upload_s": upload_s,
     }

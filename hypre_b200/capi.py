@@ -77,6 +77,8 @@ def lib():
         "b200_parcsr_destroy": (i, [vp]),
         "b200_parcsr_info": (i, [vp, c_int_p, c_int_p, C.POINTER(ll), c_int_p, c_int_p]),
         "b200_set_layout_override": (i, [i, i]),
+        "b200_set_compression": (i, [i, i]),
+        "b200_parcsr_storage": (i, [vp, c_int_p, C.POINTER(ll), C.POINTER(ll), c_int_p]),
         "b200_rowpart_create": (i, [i, i, i, i, vp, vp, vp, vp, vp, c_void_pp]),
         "b200_rowpart_destroy": (i, [vp]),
         "b200_rowpart_sizes": (i, [vp] + [c_int_p] * 8),
@@ -100,6 +102,7 @@ def lib():
         "b200_amg_finalize": (i, [vp]),
         "b200_amg_cycle": (i, [vp, vp, vp, i]),
         "b200_amg_cycle_bytes": (i, [vp, c_dbl_p]),
+        "b200_amg_cycle_bytes_stored": (i, [vp, c_dbl_p]),
         "b200_amg_level_matrix": (i, [vp, i, c_void_pp]),
         "b200_amg_level_interp": (i, [vp, i, c_void_pp]),
         "b200_amg_level_info": (i, [vp, i, c_int_p, C.POINTER(ll), C.POINTER(ll)]),

@@ -452,7 +452,15 @@ extern "C" int b200_amg_level_info(const b200_amg *a, int level, int *n_rows, lo
 
 // Algorithmic bytes of one cycle (SURVEY.md section 8(d) formulas, int32 + fp64):
 //   SpMV-type pass over A: 12 nnz + 4 n + vectors (8 bytes per vector element streamed)
-extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes)
+static inline double dmat_pass_bytes(const DMat &D, bool stored)
+{
+   if (stored && D.layout >= 1) { return (double)D.stored_bytes; }
+   return 12.0 * (double)D.nnz + 4.0 * (double)D.n_rows;
+}
+
+// stored = false: the reference's CSR bytes (the algorithmic figure); stored = true: the bytes the
+// device layout of each block (compressed sliced ELL where chosen) makes one pass read
+static int cycle_bytes(const b200_amg *a, bool stored, double *bytes)
 {
    ARG_CHECK(a != nullptr && bytes != nullptr);
    double tot = 0.0;
@@ -461,7 +469,7 @@ extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes)
    {
       const AmgLevel &L = a->L[l];
       const double n = L.n, nnz = (double)(L.A->diag.nnz + L.A->offd.nnz);
-      const double spmv = 12.0 * nnz + 4.0 * n;
+      const double spmv = dmat_pass_bytes(L.A->diag, stored) + 12.0 * (double)L.A->offd.nnz;
       auto sweep_bytes = [&](int t, bool zero) -> double {
          switch (t)
          {
@@ -478,21 +486,24 @@ extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes)
             }
             case 11: case 12: {
                int inner = t == 11 ? 1 : 2;
-               double nl_ = L.A->hasL ? (double)L.A->lower.nnz : 0.5 * nnz;
+               double low = L.A->hasL ? dmat_pass_bytes(L.A->lower, stored) : 6.0 * nnz + 4.0 * n;
                double first = zero ? 24.0 * n : spmv + 32.0 * n;            // u,f,d in; z out
-               return first + inner * (12.0 * nl_ + 4.0 * n + 40.0 * n);     // z,d,u in; z,u out
+               return first + inner * (low + 40.0 * n);                      // z,d,u in; z,u out
             }
             default: return 0.0;
          }
       };
       if (l < nl - 1)
       {
-         const double nnzP = (double)(L.P->diag.nnz + L.P->offd.nnz), nc = a->L[l + 1].n;
+         const double nc = a->L[l + 1].n;
+         const double passP  = dmat_pass_bytes(L.P->diag, stored) + 12.0 * (double)L.P->offd.nnz;
+         const double passPT = (L.P->hasT ? dmat_pass_bytes(L.P->diagT, stored)
+                                          : 12.0 * (double)L.P->diag.nnz + 4.0 * nc) + 12.0 * (double)L.P->offd.nnz;
          // V-cycle: pre sweeps (first one with zero guess), residual, restriction, prolongation, post sweeps
          for (int j = 0; j < a->num_sweeps[1]; j++) { tot += sweep_bytes(a->relax_type[1], j == 0); }
          tot += spmv + 24.0 * n;                          // residual: u,f in; r out
-         tot += 12.0 * nnzP + 4.0 * nc + 8.0 * n + 8.0 * nc;   // restriction
-         tot += 12.0 * nnzP + 4.0 * n + 8.0 * nc + 16.0 * n;   // prolongation
+         tot += passPT + 8.0 * n + 8.0 * nc;                    // restriction
+         tot += passP + 8.0 * nc + 16.0 * n;                    // prolongation
          for (int j = 0; j < a->num_sweeps[2]; j++) { tot += sweep_bytes(a->relax_type[2], false); }
       }
       else if (a->relax_type[3] == 9) { tot += 8.0 * (double)a->coarse_n * a->coarse_n; }
@@ -501,3 +512,6 @@ extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes)
    *bytes = tot;
    return B200_OK;
 }
+
+extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes) { return cycle_bytes(a, false, bytes); }
+extern "C" int b200_amg_cycle_bytes_stored(const b200_amg *a, double *bytes) { return cycle_bytes(a, true, bytes); }

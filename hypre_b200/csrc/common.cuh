@@ -150,7 +150,21 @@ struct DMat {
    double    *sl_va  = nullptr;
    int        max_row = 0;
    double     avg_row = 0.0;
+   // compressed thread-per-row storage (cfmt != 0, layouts 1/2 only): 16-bit column offsets from a
+   // base per (slice, entry), values through a dictionary when the block holds few distinct ones
+   int        cfmt = 0;                  // CFMT_*
+   unsigned short *c_idx  = nullptr;     // [sell_entries] chunk-transposed: slice, chunk of 4 entries, lane, entry
+   int            *c_base = nullptr;     // [sell_entries/32] base column of (slice, entry) or CFMT_ESC
+   void           *c_code = nullptr;     // [sell_entries] value codes (u8 / u16), chunk-transposed like c_idx
+   double         *c_dict = nullptr;     // distinct values
+   int             n_dict = 0;
+   long long       stored_bytes = 0;     // bytes one pass over the block reads from the matrix arrays
 };
+
+// cfmt: value encoding of the compressed storage (column indices are always base + u16)
+enum { CFMT_NONE = 0, CFMT_VAL8 = 1, CFMT_VAL16 = 2, CFMT_VAL64 = 3 };
+constexpr int            CFMT_ESC = (int)0x80000000;   // c_base sentinel: this (slice, entry) keeps 32-bit columns in sl_ci
+constexpr unsigned short CFMT_PAD = 0xFFFFu;           // c_idx value of a padding lane
 
 // view passed by value to kernels
 struct MatView {
@@ -162,6 +176,10 @@ struct MatView {
    const unsigned short *perm;   // layout 2 only, else nullptr
    const int       *sl_ci;
    const double    *sl_va;
+   const unsigned short *c_idx;  // compressed storage (DMat::cfmt != 0), else nullptr
+   const int       *c_base;
+   const void      *c_code;
+   const double    *c_dict;
 };
 
 static inline MatView view_of(const DMat &m)
@@ -169,6 +187,7 @@ static inline MatView view_of(const DMat &m)
    MatView v;
    v.n_rows = m.n_rows; v.rp = m.rp; v.ci = m.ci; v.va = m.va;
    v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va; v.perm = m.sl_perm;
+   v.c_idx = m.c_idx; v.c_base = m.c_base; v.c_code = m.c_code; v.c_dict = m.c_dict;
    return v;
 }
 

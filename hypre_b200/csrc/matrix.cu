@@ -2,10 +2,26 @@
 #include "common.cuh"
 #include "p2p.cuh"
 #include <algorithm>
+#include <climits>
+#include <cstring>
 #include <numeric>
 
 static int g_layout_override = -1;
+// compressed thread-per-row storage: -1 automatic (default; B200_COMPRESS=0 in the environment turns it
+// off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it
+static int g_compress = []() { const char *e = getenv("B200_COMPRESS"); return e ? atoi(e) : -1; }();
 static int g_lanes_override  = -1;
+
+int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 3 ? v : 0; }();
+
+extern "C" int b200_set_compression(int mode, int pipeline)
+{
+   ARG_CHECK(mode >= -1 && mode <= CFMT_VAL64);
+   ARG_CHECK(pipeline >= -1 && pipeline <= 3);
+   g_compress = mode;
+   if (pipeline >= 0) { g_sellc_pipe = pipeline; }
+   return B200_OK;
+}
 
 extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
 {
@@ -36,6 +52,7 @@ void dmat_free(DMat *m)
 {
    cudaFree(m->rp); cudaFree(m->ci); cudaFree(m->va);
    cudaFree(m->sl_off); cudaFree(m->sl_ci); cudaFree(m->sl_va); cudaFree(m->sl_perm);
+   cudaFree(m->c_idx); cudaFree(m->c_base); cudaFree(m->c_code); cudaFree(m->c_dict);
    *m = DMat();
 }
 
@@ -58,6 +75,118 @@ void host_transpose(const HostCsr &a, HostCsr *t)
          t->j[p] = r; t->a[p] = a.a[k];
       }
    }
+}
+
+// Value dictionary: distinct bit patterns of a[], at most `cap`; returns false if there are more.
+// Open addressing on the bit pattern (the common case -- a handful of values -- stays in cache).
+static bool build_dictionary(const std::vector<double> &a, size_t cap, std::vector<double> *dict,
+                             std::vector<unsigned long long> *keys, std::vector<int> *codes)
+{
+   const size_t tab = 1u << 18, mask = tab - 1;
+   keys->assign(tab, 0); codes->assign(tab, -1);
+   dict->clear();
+   for (size_t k = 0; k < a.size(); k++)
+   {
+      unsigned long long bits; memcpy(&bits, &a[k], 8);
+      size_t hsh = (size_t)((bits * 0x9E3779B97F4A7C15ull) >> 40) & mask;
+      while ((*codes)[hsh] >= 0 && (*keys)[hsh] != bits) { hsh = (hsh + 1) & mask; }
+      if ((*codes)[hsh] < 0)
+      {
+         if (dict->size() >= cap) { return false; }
+         (*keys)[hsh] = bits; (*codes)[hsh] = (int)dict->size(); dict->push_back(a[k]);
+      }
+   }
+   return true;
+}
+static inline int dictionary_code(const std::vector<unsigned long long> &keys, const std::vector<int> &codes, double v)
+{
+   const size_t mask = keys.size() - 1;
+   unsigned long long bits; memcpy(&bits, &v, 8);
+   size_t hsh = (size_t)((bits * 0x9E3779B97F4A7C15ull) >> 40) & mask;
+   while (codes[hsh] >= 0 && keys[hsh] != bits) { hsh = (hsh + 1) & mask; }
+   return codes[hsh];
+}
+
+// Compressed thread-per-row storage of a block already laid out as (padded) sliced ELL: see
+// rowsum_sellc (spmv.cuh).  sci/sva/livef are entry-major ([slice][k][lane]); the compressed arrays
+// are chunk-transposed ([slice][k/4][lane][k%4]).
+struct ValueDict {
+   int cfmt = CFMT_NONE;
+   std::vector<double> dict;
+   std::vector<unsigned long long> keys;
+   std::vector<int> codes;
+};
+
+static int dmat_compress(DMat *m, const std::vector<int> &sci, const std::vector<double> &sva,
+                         const std::vector<unsigned char> &livef, const std::vector<long long> &sl_off,
+                         ValueDict &vd, bool *need_ci, bool *need_va)
+{
+   const long long padded = sl_off.back();
+   const size_t n_groups = (size_t)(padded / 32);
+   std::vector<int> base(n_groups, 0);
+   std::vector<unsigned short> idx((size_t)padded, CFMT_PAD);
+   long long n_esc = 0;
+   const int n_slices = (int)sl_off.size() - 1;
+   auto cpos = [](long long off, int k, int l) { return (size_t)off + (size_t)(k >> 2) * 128 + (size_t)l * 4 + (size_t)(k & 3); };
+   for (int sidx = 0; sidx < n_slices; sidx++)
+   {
+      const long long off = sl_off[(size_t)sidx];
+      const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
+      for (int k = 0; k < w; k++)
+      {
+         const size_t g = (size_t)(off / 32) + (size_t)k, e0 = (size_t)off + (size_t)k * 32;
+         int lo = INT_MAX, hi = INT_MIN;
+         for (int l = 0; l < 32; l++) { if (livef[e0 + l]) { lo = std::min(lo, sci[e0 + l]); hi = std::max(hi, sci[e0 + l]); } }
+         if (lo > hi) { base[g] = 0; continue; }                 // nothing live: all lanes stay CFMT_PAD
+         const bool esc = (long long)hi - (long long)lo > 65534;
+         base[g] = esc ? CFMT_ESC : lo;
+         n_esc += esc;
+         for (int l = 0; l < 32; l++)
+         {
+            if (livef[e0 + l]) { idx[cpos(off, k, l)] = esc ? (unsigned short)0 : (unsigned short)(sci[e0 + l] - lo); }
+         }
+      }
+   }
+   const int cfmt = vd.cfmt;
+   std::vector<double> &dict = vd.dict;
+   const std::vector<unsigned long long> &keys = vd.keys;
+   const std::vector<int> &codes = vd.codes;
+   if (cfmt != CFMT_VAL64)
+   {
+      if (dict.empty()) { dict.push_back(0.0); }
+      const size_t csz = cfmt == CFMT_VAL8 ? 1 : 2;
+      std::vector<unsigned char> code((size_t)padded * csz, 0);
+      for (int sidx = 0; sidx < n_slices; sidx++)
+      {
+         const long long off = sl_off[(size_t)sidx];
+         const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
+         for (int k = 0; k < w; k++)
+         {
+            for (int l = 0; l < 32; l++)
+            {
+               const size_t e = (size_t)off + (size_t)k * 32 + l;
+               if (!livef[e]) { continue; }
+               const int cd = dictionary_code(keys, codes, sva[e]);
+               const size_t p = cpos(off, k, l);
+               if (cfmt == CFMT_VAL8) { code[p] = (unsigned char)cd; }
+               else { const unsigned short c16 = (unsigned short)cd; memcpy(&code[p * 2], &c16, 2); }
+            }
+         }
+      }
+      unsigned char *d_code = nullptr;
+      B200_TRY(dev_upload(&d_code, code.data(), code.size()));
+      m->c_code = d_code;
+      B200_TRY(dev_upload(&m->c_dict, dict.data(), dict.size()));
+      m->n_dict = (int)dict.size();
+   }
+   B200_TRY(dev_upload(&m->c_idx, idx.data(), idx.size()));
+   B200_TRY(dev_upload(&m->c_base, base.data(), base.size()));
+   m->cfmt = cfmt;
+   *need_ci = n_esc > 0;
+   *need_va = cfmt == CFMT_VAL64;
+   const long long per_entry = 2 + (cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 8);
+   m->stored_bytes = per_entry * padded + 4 * (long long)n_groups + 8 * (long long)n_slices + 4 * 32 * n_esc;
+   return B200_OK;
 }
 
 // Choose the layout from the row-length statistics and upload.
@@ -136,10 +265,37 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    if (layout >= 1)
    {
       const std::vector<int> &order = layout == 2 ? sorted : ident;
-      const std::vector<long long> &sl_off = layout == 2 ? off_sorted : off_plain;
+      const std::vector<long long> &off_orig = layout == 2 ? off_sorted : off_plain;
+      std::vector<long long> sl_off = off_orig;
+      // compressed storage (rowsum_sellc): pick the value format, round the slice widths up to whole
+      // chunks of 4 entries, and keep it only if a pass over the block then reads fewer bytes
+      ValueDict vd;
+      if (g_compress != 0)
+      {
+         vd.cfmt = CFMT_VAL64;
+         if (g_compress != CFMT_VAL64 &&
+             build_dictionary(h.a, g_compress == CFMT_VAL8 ? 256 : 65536, &vd.dict, &vd.keys, &vd.codes))
+         {
+            vd.cfmt = (vd.dict.size() <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
+         }
+         std::vector<long long> off4((size_t)n_slices + 1, 0);
+         for (int sidx = 0; sidx < n_slices; sidx++)
+         {
+            const long long w = (off_orig[(size_t)sidx + 1] - off_orig[(size_t)sidx]) / 32;
+            off4[(size_t)sidx + 1] = off4[(size_t)sidx] + ((w + 3) & ~3LL) * 32;
+         }
+         const long long per_entry = 2 + (vd.cfmt == CFMT_VAL8 ? 1 : vd.cfmt == CFMT_VAL16 ? 2 : 8);
+         if (g_compress > 0 || per_entry * off4[(size_t)n_slices] + off4[(size_t)n_slices] / 8 < 12 * off_orig[(size_t)n_slices])
+         {
+            sl_off.swap(off4);
+         }
+         else { vd.cfmt = CFMT_NONE; }
+      }
+      const bool compress = vd.cfmt != CFMT_NONE;
       const long long padded = sl_off[n_slices];
       std::vector<int>    sci((size_t)padded);
       std::vector<double> sva((size_t)padded);
+      std::vector<unsigned char> livef(compress ? (size_t)padded : 0);
       for (int sidx = 0; sidx < n_slices; sidx++)
       {
          const int w = (int)((sl_off[(size_t)sidx + 1] - sl_off[(size_t)sidx]) / 32);
@@ -154,13 +310,17 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
                const size_t p = (size_t)sl_off[(size_t)sidx] + (size_t)k * 32 + l;
                if (k < len) { sci[p] = h.j[beg + k]; sva[p] = h.a[beg + k]; }
                else         { sci[p] = padc;         sva[p] = 0.0; }
+               if (compress) { livef[p] = k < len; }
             }
          }
       }
       m->n_slices = n_slices; m->sell_entries = padded;
+      m->stored_bytes = 12 * padded + 8 * (long long)n_slices;
       B200_TRY(dev_upload(&m->sl_off, sl_off.data(), sl_off.size()));
-      B200_TRY(dev_upload(&m->sl_ci, sci.data(), sci.size()));
-      B200_TRY(dev_upload(&m->sl_va, sva.data(), sva.size()));
+      bool need_ci = true, need_va = true;
+      if (compress) { B200_TRY(dmat_compress(m, sci, sva, livef, sl_off, vd, &need_ci, &need_va)); }
+      if (need_ci) { B200_TRY(dev_upload(&m->sl_ci, sci.data(), sci.size())); }
+      if (need_va) { B200_TRY(dev_upload(&m->sl_va, sva.data(), sva.size())); }
       if (layout == 2)
       {
          std::vector<unsigned short> perm(order.size());
@@ -331,6 +491,19 @@ extern "C" int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, 
    if (nnz)    { *nnz = A->diag.nnz + A->offd.nnz; }
    if (layout) { *layout = A->diag.layout; }
    if (lanes_per_row) { *lanes_per_row = A->diag.lanes; }
+   return B200_OK;
+}
+
+extern "C" int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stored_bytes,
+                                   long long *csr_bytes, int *n_dictionary)
+{
+   ARG_CHECK(A != nullptr);
+   const DMat &D = A->diag;
+   const long long csr = 12 * D.nnz + 4 * ((long long)D.n_rows + 1);
+   if (value_format) { *value_format = D.cfmt; }
+   if (stored_bytes) { *stored_bytes = D.layout >= 1 ? D.stored_bytes : csr; }
+   if (csr_bytes)    { *csr_bytes = csr; }
+   if (n_dictionary) { *n_dictionary = D.n_dict; }
    return B200_OK;
 }
 

@@ -22,6 +22,9 @@ static inline int rows_grid(long long work, int per_block)
    return (int)g;
 }
 
+// pipelining variant of the compressed row kernels (matrix.cu; B200_SELLC_PIPE = 0 | 1 | 2, b200_set_compression)
+extern int g_sellc_pipe;
+
 static inline HaloArgs no_halo()
 {
    HaloArgs h;
@@ -46,7 +49,16 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    if (D.layout >= 1 || D.n_rows == 0)
    {
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
-      LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);
+      switch (D.cfmt ? D.cfmt + 4 * g_sellc_pipe : 0)
+      {
+#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc); break;
+         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64)
+         CASE_C(CFMT_VAL8 + 4) CASE_C(CFMT_VAL16 + 4) CASE_C(CFMT_VAL64 + 4)
+         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8)
+         CASE_C(CFMT_VAL8 + 12) CASE_C(CFMT_VAL16 + 12) CASE_C(CFMT_VAL64 + 12)
+#undef CASE_C
+         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc); break;
+      }
    }
    else
    {

@@ -134,6 +134,94 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
    return t;
 }
 
+// Compressed sliced ELL (DMat::cfmt != 0).  HBM bandwidth bounds these kernels, so the matrix is
+// stored in fewer bytes, losslessly: the column of (slice, entry k, lane) is base[slice][k] + a 16-bit
+// offset (the 32 rows of a slice are neighbours, so their k-th columns are, too; a (slice, k) whose
+// columns span more than 65534 keeps 32-bit columns in sl_ci: base == CFMT_ESC), and a block with at most
+// 256 / 65536 distinct values (stencils, and the Galerkin products of stencils) stores 8- / 16-bit codes
+// into a dictionary that stays in L1/L2.  12 bytes per entry become 3 or 4 (10 without a dictionary).
+// Entries are stored in chunks of 4 per lane (one 8-byte offset load, one 4/8-byte code load and one
+// 16-byte broadcast base load per chunk); slice widths are multiples of 4, padding lanes are marked
+// by offset 0xFFFF and skipped.  Arithmetic and summation order are those of the CSR row.
+__device__ __forceinline__ unsigned long long ld_stream_u64(const void *p)
+{
+   unsigned long long v;
+   asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+   return v;
+}
+__device__ __forceinline__ unsigned ld_stream_u32(const void *p)
+{
+   unsigned v;
+   asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+   return v;
+}
+
+__device__ __forceinline__ void prefetch_l2(const void *p)
+{
+   asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+}
+// the warp asks L2 for [p, p + bytes): one 128-byte line per lane and trip
+__device__ __forceinline__ void prefetch_span_l2(const void *p, long long bytes, int lane)
+{
+   for (long long b = (long long)lane * 128; b < bytes; b += 32 * 128) { prefetch_l2((const char *)p + b); }
+}
+
+// One slice = entries [off, off + 128 n_chunks).  With 3-4 bytes per entry the loop is bound by load
+// latency, not by DRAM bandwidth (a thread has 12 bytes of matrix in flight), so PIPE == 2 lets the warp
+// pull the compressed streams of the slice it will process NEXT ([off_n, end_n), known one trip ahead,
+// see rows_range) into L2 while it works on this one: no registers, no scoreboard entry.
+template <int VF, int PIPE, class XF>
+__device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, int n_chunks, int lane,
+                                               const double *__restrict__ x, const XF &xf,
+                                               long long off_n, int n_chunks_n)
+{
+   const unsigned short *ip = D.c_idx + off + lane * 4;
+   const int4 *bp = reinterpret_cast<const int4 *>(D.c_base + (off >> 5));
+   double t = 0.0;
+   for (int c = 0; c < n_chunks; c++)
+   {
+      const unsigned long long id = ld_stream_u64(ip + c * 128);
+      const int4 b4 = __ldg(bp + c);
+      unsigned long long code = 0;
+      if (VF == CFMT_VAL8)  { code = ld_stream_u32((const unsigned char *)D.c_code + off + c * 128 + lane * 4); }
+      if (VF == CFMT_VAL16) { code = ld_stream_u64((const unsigned short *)D.c_code + off + c * 128 + lane * 4); }
+      if (PIPE >= 2 && c == 0 && n_chunks_n > 0)
+      {
+         const long long e = (long long)n_chunks_n << 7;
+         prefetch_span_l2(D.c_idx + off_n, 2 * e, lane);
+         if (VF == CFMT_VAL8)  { prefetch_span_l2((const unsigned char *)D.c_code + off_n, e, lane); }
+         if (VF == CFMT_VAL16) { prefetch_span_l2((const unsigned short *)D.c_code + off_n, 2 * e, lane); }
+         if (VF == CFMT_VAL64) { prefetch_span_l2(D.sl_va + off_n, 8 * e, lane); }
+         if (lane == 31) { prefetch_span_l2(D.c_base + (off_n >> 5), e >> 3, 0); }
+      }
+      const int b[4] = { b4.x, b4.y, b4.z, b4.w };
+      int    col[4];
+      double v[4], xv[4];
+      bool   live[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         const unsigned o = (unsigned)(id >> (16 * j)) & 0xFFFFu;
+         live[j] = (o != CFMT_PAD);
+         col[j] = b[j] + (int)o;
+         // warp-uniform and rare: this (slice, entry) keeps 32-bit columns
+         if (b[j] == CFMT_ESC) { col[j] = ld_stream(D.sl_ci + off + (c * 4 + j) * 32 + lane); }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         if (VF == CFMT_VAL8)       { v[j] = __ldg(D.c_dict + ((unsigned)(code >> (8 * j)) & 0xFFu)); }
+         else if (VF == CFMT_VAL16) { v[j] = __ldg(D.c_dict + ((unsigned)(code >> (16 * j)) & 0xFFFFu)); }
+         else { v[j] = live[j] ? ld_stream(D.sl_va + off + (c * 4 + j) * 32 + lane) : 0.0; }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { xv[j] = live[j] ? xf.xval(x, col[j]) : 0.0; }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { if (live[j]) { t = fma(v[j], xv[j], t); } }
+   }
+   return t;
+}
+
 // CG: gather x with ld.global.cg (L2 only) -- for ghost vectors that a peer GPU wrote during this
 // kernel's lifetime, which must not be served from a stale L1 / read-only cache line
 template <bool CG>
@@ -265,8 +353,8 @@ __device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const
 }
 
 // Row groups [g_begin, g_end) (a group = 32 consecutive rows = one slice of the sliced-ELL layout) of
-// the diag block, grid-strided over the whole grid.  T == 0: sliced ELL thread-per-row; T > 0: CSR
-// with T lanes per row.  HALO as above; HALO_NONE / HALO_SKIP never touch the channel.
+// the diag block, grid-strided over the whole grid.  T == 0: sliced ELL thread-per-row; T < 0: compressed
+// sliced ELL, value format (-T) & 3, pipelining variant (-T) >> 2; T > 0: CSR with T lanes per row.  HALO as above; HALO_NONE / HALO_SKIP never touch the channel.
 template <int T, int HALO, class Epi>
 __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
                                            const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
@@ -274,16 +362,37 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
 {
    // vblock: the block's position in this range's grid stride (a permutation of blockIdx.x), so that
    // short ranges do not all land on the low-numbered blocks, which also carry the put phase
-   if (T == 0)
+   if (T <= 0)
    {
+      constexpr int VF   = T < 0 ? ((-T) & 3) : CFMT_VAL64;   // T = -(CFMT_* + 4 PIPE): compressed storage
+      // 0 plain, 1 slice offsets one trip ahead, 2 + L2 prefetch, 3 = 2 at 40 registers / 6 blocks per SM
+      constexpr int PIPE = T < 0 ? ((-T) >> 2) : 0;
       const int lane = threadIdx.x & 31;
       const int wpb = ROWK_BLOCK / 32;
-      for (int slice = g_begin + vblock * wpb + (threadIdx.x >> 5); slice < g_end; slice += gridDim.x * wpb)
+      const int stride = gridDim.x * wpb;
+      int slice = g_begin + vblock * wpb + (threadIdx.x >> 5);
+      long long off = 0;
+      int nch = 0;
+      if (PIPE >= 1 && slice < g_end) { off = D.sl_off[slice]; nch = (int)((D.sl_off[slice + 1] - off) >> 7); }
+      for (; slice < g_end; slice += stride)
       {
+         // the offsets of the warp's next slice travel while this one is processed: the chain
+         // offset -> matrix stream -> gather loses its first link
+         long long off_n = 0;
+         int nch_n = 0;
+         if (PIPE >= 1 && slice + stride < g_end)
+         {
+            off_n = D.sl_off[slice + stride];
+            nch_n = (int)((D.sl_off[slice + stride + 1] - off_n) >> 7);
+         }
+         if (T < 0 && PIPE == 0) { off = D.sl_off[slice]; nch = (int)((D.sl_off[slice + 1] - off) >> 7); }
          int row = (slice << 5) + lane;
          if (D.perm != nullptr) { row = ((slice >> 3) << 8) + D.perm[row]; }   // sorted inside 256-row windows
          const bool live = row < D.n_rows;
-         double t = rowsum_sell(D, slice, lane, x, epi);
+         if (PIPE >= 2 && live) { epi.prefetch(row); }     // the epilogue's own vectors: in L2 by the time the row sum is done
+         double t = (T == 0) ? rowsum_sell(D, slice, lane, x, epi)
+                             : rowsum_sellc<VF, PIPE>(D, off, nch, lane, x, epi, off_n, nch_n);
+         off = off_n; nch = nch_n;
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
          if (HALO == HALO_FWD && h.grp[slice])
@@ -305,7 +414,7 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
    }
    else
    {
-      constexpr int TT = (T == 0 ? 1 : T);
+      constexpr int TT = (T <= 0 ? 1 : T);
       const int sub = threadIdx.x & (TT - 1);
       const int gpb = ROWK_BLOCK / TT;
       // whole warps: a warp's 32/TT rows lie in one group, so the group flag is warp-uniform and every
@@ -343,7 +452,7 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
 // All rows of the diag block.  8 resident blocks per SM (32 registers): occupancy is what hides the
 // DRAM latency of this streaming kernel.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK, 8)
+__global__ void __launch_bounds__(ROWK_BLOCK, (T <= -12) ? 6 : 8)
 rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);

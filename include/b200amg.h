@@ -97,6 +97,19 @@ int b200_parcsr_create(b200_ctx *ctx,
 int b200_parcsr_destroy(b200_parcsr *A);
 int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *nnz,
                      int *layout /* 0 = CSR-vector, 1 = sliced-ELL, 2 = sliced-ELL with rows sorted in 256-row windows */, int *lanes_per_row);
+/* Storage of the diag block.  Thread-per-row layouts (1, 2) are held compressed when that reads fewer
+ * bytes: 16-bit column offsets from a base per (slice, entry) and -- for blocks with at most 256 / 65536
+ * distinct values -- 8 / 16-bit codes into a value dictionary (lossless; same products, same order).
+ * value_format: 0 plain (int32 column + fp64 value), 1 dictionary u8, 2 dictionary u16, 3 fp64 values with
+ * 16-bit columns.  stored_bytes = matrix bytes one pass reads; csr_bytes = 12 nnz + 4 (n+1), what the
+ * reference's CSR (seq_mv/csr_matrix.h) would read. */
+int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stored_bytes,
+                        long long *csr_bytes, int *n_dictionary);
+/* mode: -1 automatic (default; environment B200_COMPRESS=0 disables), 0 off, 1/2/3 force that value
+ * format where the dictionary allows it (tests/bench).  pipeline: 0 plain loop (default, fastest measured),
+ * 1 slice offsets loaded one trip ahead, 2 additionally L2 prefetch of the next slice's streams, 3 = 2 at
+ * 6 blocks per SM; -1 leaves it (environment B200_SELLC_PIPE). */
+int b200_set_compression(int mode, int pipeline);
 /* force the storage layout chosen for the diag block (tests/bench): -1 auto */
 int b200_set_layout_override(int layout, int lanes_per_row);
 
@@ -197,6 +210,8 @@ int b200_amg_finalize(b200_amg *amg);
 int b200_amg_cycle(b200_amg *amg, const double *f, double *u, int zero_guess);
 /* algorithmic HBM bytes of one cycle, from the uploaded level sizes */
 int b200_amg_cycle_bytes(const b200_amg *amg, double *bytes);
+/* the same model with the bytes the device layouts actually store (b200_parcsr_storage) */
+int b200_amg_cycle_bytes_stored(const b200_amg *amg, double *bytes);
 /* borrowed handle to A_array[level] / P_array[level] (owned by amg) */
 int b200_amg_level_matrix(const b200_amg *amg, int level, b200_parcsr **A);
 int b200_amg_level_interp(const b200_amg *amg, int level, b200_parcsr **P);

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Extract per-launch DRAM traffic and duration of the level-0 SpMV kernel from an `ncu --set full`
 report of scripts/prof_ops.py and write the committed summary that bench.py quotes as roofline.traffic.
-usage: ncu_traffic.py gpurun_out/prof_rows.ncu-rep profiles/r01_ncu_traffic.json [rows nnz]"""
+usage: ncu_traffic.py gpurun_out/prof_rows.ncu-rep profiles/r01_ncu_traffic.json [rows nnz value_format]"""
 import csv
 import io
 import json
@@ -11,6 +11,7 @@ import sys
 rep, out = sys.argv[1], sys.argv[2]
 rows_n = int(sys.argv[3]) if len(sys.argv) > 3 else 256 ** 3
 nnz = int(sys.argv[4]) if len(sys.argv) > 4 else 117047296
+vfmt = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
@@ -40,7 +41,7 @@ spmv = [l for l in launches if "EpiMatvec>" in l["kernel"] or "EpiMatvec," in l[
 first = (spmv or launches)[0]
 summary = {
     "source": "ncu --set full --clock-control none -k regex:rows_kernel -s 3 -c 4 python scripts/prof_ops.py --reps 2",
-    "matrix": {"rows": rows_n, "nnz": nnz, "what": "7-pt Laplacian 256^3, level-0 diag block, sliced ELL"},
+    "matrix": {"rows": rows_n, "nnz": nnz, "value_format": vfmt, "what": "7-pt Laplacian 256^3, level-0 diag block, sliced ELL"},
     "spmv_level0": {"traffic_bytes_per_launch": first["dram_read_bytes"] + first["dram_write_bytes"],
                     "algorithmic_bytes_per_launch": 12.0 * nnz + 4.0 * (rows_n + 1) + 16.0 * rows_n, **first},
     "launches": launches,

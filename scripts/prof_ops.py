@@ -21,12 +21,15 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--layout", type=int, default=-1)
     ap.add_argument("--lanes", type=int, default=-1)
+    ap.add_argument("--compress", type=int, default=-1, help="b200_set_compression mode (-1 auto, 0 off, 1..3)")
+    ap.add_argument("--pipe", type=int, default=-1, help="pipelining variant of the compressed kernels (0..3)")
     a = ap.parse_args()
     L = capi.lib()
     HL = H.lib()
     ctx = C.c_void_p(HL.hypre_b200_context())
     A = getattr(H, a.gen)(a.n, a.n, a.n)
     capi.check(L.b200_set_layout_override(a.layout, a.lanes))
+    capi.check(L.b200_set_compression(a.compress, a.pipe))
     dA = A.device_mirror()
     n = A.global_rows
     nnz = C.c_longlong(); layout = C.c_int(); lanes = C.c_int()
@@ -49,7 +52,11 @@ def main():
         t = ms.value / a.reps
         return {"ms": t, "GB/s": bytes_ / t / 1e6, "MB": bytes_ / 1e6}
 
-    out = {"gen": a.gen, "n": a.n, "rows": n, "nnz": nnz, "layout": layout.value, "lanes": lanes.value}
+    vfmt = C.c_int(); st_b = C.c_longlong(); csr_b = C.c_longlong(); ndict = C.c_int()
+    capi.check(L.b200_parcsr_storage(dA, C.byref(vfmt), C.byref(st_b), C.byref(csr_b), C.byref(ndict)))
+    out = {"gen": a.gen, "n": a.n, "rows": n, "nnz": nnz, "layout": layout.value, "lanes": lanes.value,
+           "value_format": vfmt.value, "pipe": a.pipe, "matrix_stored_MB": st_b.value / 1e6,
+           "matrix_csr_MB": csr_b.value / 1e6, "note": "GB/s count the CSR (algorithmic) bytes"}
     out["spmv"] = timed(lambda: capi.check(L.b200_parcsr_matvec(dA, 1.0, v[0].ptr, 0.0, None, v[1].ptr)),
                         spmv + 16.0 * n)
     out["residual"] = timed(lambda: capi.check(L.b200_parcsr_matvec(dA, -1.0, v[0].ptr, 1.0, v[2].ptr, v[1].ptr)),

@@ -143,3 +143,131 @@ def test_blas1(ctx):
         assert np.all(dy.get() == 3.5)
         capi.check(L.b200_vec_copy(ctx, n, dx.ptr, dy.ptr))
         assert np.array_equal(dy.get(), x)
+
+
+# ------------------------------------------------------------------ compressed thread-per-row storage
+def _storage(L, dA):
+    fmt, nd = C.c_int(), C.c_int()
+    sb, cb = C.c_longlong(), C.c_longlong()
+    capi.check(L.b200_parcsr_storage(dA, C.byref(fmt), C.byref(sb), C.byref(cb), C.byref(nd)))
+    return fmt.value, sb.value, cb.value, nd.value
+
+
+_COMP_CACHE = {}
+
+
+def _random_matrices():
+    """built once (csr arithmetic only: lil assignment of wide slices is very slow)"""
+    if "r" not in _COMP_CACHE:
+        rng = np.random.default_rng(14)
+        # many distinct values, columns far apart (32-bit escape groups), empty rows, a long row
+        # (explicit coordinates: sp.random draws without replacement from rows*cols, minutes at this shape)
+        ri = rng.integers(0, 3000, 30000); cj = rng.integers(0, 400000, 30000)
+        ok = (ri < 200) | (ri >= 260)                                   # empty rows
+        cols = np.arange(0, 400000, 97)                                 # one long row
+        ri = np.concatenate([ri[ok], np.full(len(cols), 7)]); cj = np.concatenate([cj[ok], cols])
+        A = sp.csr_matrix((rng.standard_normal(len(ri)), (ri, cj)), shape=(3000, 400000))
+        A.sum_duplicates(); A.sort_indices()
+        B = sp.random(5000, 5000, density=0.004, random_state=6, format="csr")
+        Cm = B.copy(); Cm.data = np.round(Cm.data * 200.0) / 7.0        # ~200 distinct values, random columns
+        _COMP_CACHE["r"] = (A, B, Cm)
+    return _COMP_CACHE["r"]
+
+
+def _compression_matrices(H, hier):
+    amg = hier[3]
+    yield "lap7", H.laplacian(19, 17, 13).blocks()[0], 1            # 2 distinct values -> u8 codes
+    yield "lap27", H.laplacian_27pt(14, 12, 11).blocks()[0], 1
+    yield "A1", amg.A(1).blocks()[0], None
+    yield "P0", amg.P(0).blocks()[0], None
+    A, B, Cm = _random_matrices()
+    yield "wide_u16", A, 2                                          # <= 65536 distinct values
+    yield "distinct_f64", B, 3                                      # > 65536 distinct values
+    yield "random_u8", Cm, 1
+
+
+@pytest.mark.parametrize("layout", [1, 2])
+@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (0, 0), (1, 2), (2, 2), (2, 0), (3, 2), (3, 1), (3, 3)])
+def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
+    """16-bit column offsets + value dictionary (b200_parcsr_storage): same products, same order as
+    the CSR row of the reference (seq_mv/csr_matvec.c:21-857) -> SpMV parity <= 1e-12 in every format."""
+    L = capi.lib()
+    rng = np.random.default_rng(15)
+    capi.check(L.b200_set_layout_override(layout, -1))
+    capi.check(L.b200_set_compression(mode, pipe))
+    try:
+        for nm, A, auto_fmt in _compression_matrices(H, hier):
+            n, m = A.shape
+            dA = capi.parcsr_from_scipy(ctx, A)
+            fmt, stored, csr, nd = _storage(L, dA)
+            if mode == 0:
+                assert fmt == 0
+            elif mode == -1:
+                assert fmt in (0, 1, 2, 3)
+                if fmt and auto_fmt:
+                    assert fmt == auto_fmt, (nm, fmt)
+                if fmt and nm in ("lap7", "lap27", "A1"):      # regular rows: far fewer bytes than CSR
+                    assert stored < 0.5 * csr, (nm, stored, csr)
+            else:
+                assert fmt in (mode, 3) or (mode == 2 and fmt == 2), (nm, mode, fmt)
+            x = rng.standard_normal(m); b = rng.standard_normal(n)
+            dx, db, dy = dvec(ctx, x), dvec(ctx, b), capi.DeviceVector(ctx, n)
+            for alpha, beta in [(1.0, 0.0), (-1.0, 1.0)]:
+                capi.check(L.b200_parcsr_matvec(dA, alpha, dx.ptr, beta, db.ptr, dy.ptr))
+                assert row_err(dy.get(), O.matvec(A, alpha, x, beta, b), A, x) < SPMV_TOL, (nm, layout, mode, pipe, fmt)
+            # NaN in a column a row does not touch must not leak through padding lanes
+            xn = x.copy(); cols = np.setdiff1d(np.arange(m), A.indices)
+            if len(cols):
+                xn[cols[0]] = np.nan
+                dx.set(xn)
+                capi.check(L.b200_parcsr_matvec(dA, 1.0, dx.ptr, 0.0, db.ptr, dy.ptr))
+                assert np.all(np.isfinite(dy.get())), nm
+            for v in (dx, db, dy):
+                v.free()
+            L.b200_parcsr_destroy(dA)
+    finally:
+        L.b200_set_layout_override(-1, -1)
+        L.b200_set_compression(-1, 0)
+
+
+@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (3, 2), (2, 3)])
+def test_smoothers_on_compressed_storage(H, ctx, hier, mode, pipe):
+    """every fused epilogue on the compressed thread-per-row kernels against the oracle"""
+    L = capi.lib()
+    rng = np.random.default_rng(16)
+    amg = hier[3]
+    capi.check(L.b200_set_layout_override(1, -1))
+    capi.check(L.b200_set_compression(mode, pipe))
+    try:
+        for l in (0, 1):
+            A = amg.A(l).blocks()[0]
+            n = A.shape[0]
+            dA = capi.parcsr_from_scipy(ctx, A)
+            assert _storage(L, dA)[0] != 0
+            f = rng.standard_normal(n)
+            l1 = amg.level_array("l1", l, n)
+            ds = 1.0 / np.sqrt(np.abs(A.diagonal()))
+            coefs = np.array([0.9, -0.31, 0.077])
+            for zg in (0, 1):
+                u0 = np.zeros(n) if zg else rng.standard_normal(n)
+                df, dl1, dds, du = dvec(ctx, f), dvec(ctx, l1), dvec(ctx, ds), dvec(ctx, u0)
+                w = [capi.DeviceVector(ctx, n) for _ in range(3)]
+                capi.check(L.b200_relax_l1jacobi(dA, df.ptr, dl1.ptr, 0.9, du.ptr, w[0].ptr, zg))
+                assert vec_err_max(du.get(), O.relax_l1jacobi(A, f, l1, 0.9, u0, zg)) < 1e-11
+                du.set(u0)
+                capi.check(L.b200_relax_cheby(dA, df.ptr, dds.ptr, capi.ptr(coefs), 2, 1, du.ptr, w[0].ptr, w[1].ptr, w[2].ptr, zg))
+                assert vec_err_max(du.get(), O.relax_cheby(A, f, ds, coefs, 2, 1, u0)) < 1e-11
+                du.set(u0)
+                capi.check(L.b200_relax_2stage_gs(dA, df.ptr, 1.0, 1, du.ptr, w[0].ptr, w[1].ptr, zg))
+                uref, err = O.relax_gs2(A, f, 1.0, 1, u0)
+                assert err == 0 and vec_err_max(du.get(), uref) < 1e-11
+                for v in [df, dl1, dds, du] + w:
+                    v.free()
+            L.b200_parcsr_destroy(dA)
+    finally:
+        L.b200_set_layout_override(-1, -1)
+        L.b200_set_compression(-1, 0)
+
+
+def vec_err_max(a, b):
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
