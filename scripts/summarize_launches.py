@@ -15,6 +15,7 @@ tot = sum(t for _, t, _ in rows)
 agg = defaultdict(lambda: [0, 0.0])
 for k, t, g in rows:
     k = re.sub(r"^void ", "", k)
+    k = k.replace("(int)", "")
     k = re.sub(r"\(.*$", "", k)
     agg[k][0] += 1
     agg[k][1] += t
