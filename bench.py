@@ -363,6 +363,28 @@ def run_b200(args, rank, world):
         H.clear_errors()
         H.set_device_path(True)
 
+    # ---------------- aux: BASELINE.json configs[1], the stand-alone ParCSR SpMV microbench (27-pt 200^3),
+    # with the level-0 smoother sweeps on the same matrix; never allowed to break the line above it
+    aux = None
+    if not args.no_aux:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "scripts"))
+            import prof_ops
+            m = prof_ops.measure("laplacian_27pt", 200, 20)
+            st = (m["matrix_stored_MB"] - m["matrix_csr_MB"]) * 1e6       # stored minus CSR bytes of the matrix
+            aux = {"workload": "ParCSR SpMV microbench, 27-pt Laplacian 200^3 (BASELINE.json configs[1]); CUDA events, 20 launches",
+                   "rows": m["rows"], "nnz": m["nnz"], "value_format": m["value_format"], "peak_gbs": peak}
+            for k in ("spmv", "residual", "l1jacobi", "cheby2", "gs11"):
+                t = m[k]["ms"] * 1e-3
+                csr = m[k]["MB"] * 1e6
+                passes = 2 if k == "cheby2" else 1
+                aux[k] = {"ms": m[k]["ms"], "csr_gbs": csr / t / 1e9, "csr_frac": csr / t / 1e9 / peak}
+                if k != "gs11":         # (the strict-lower pass of GS has its own stored size)
+                    aux[k].update({"stored_gbs": (csr + passes * st) / t / 1e9,
+                                   "stored_frac": (csr + passes * st) / t / 1e9 / peak})
+        except Exception as e:          # noqa: BLE001
+            aux = {"error": repr(e)}
+
     out = {
         "metric": "AMG-PCG solve DOF*iterations/s", "value": value, "unit": "DOF*it/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps,
@@ -392,7 +414,7 @@ def run_b200(args, rank, world):
                      "pcg_iteration_stored_gbs": iter_stored * (iters + 1) * args.steps / dev_s / 1e9,
                      "pcg_iteration_stored_frac": iter_stored * (iters + 1) * args.steps / dev_s / 1e9 / peak},
         "cpu_baseline": cpu, "clocks": clocks,
-        "setup_s": P["setup_s"], "upload_s": upload_s,
+        "setup_s": P["setup_s"], "upload_s": upload_s, "aux_spmv_microbench": aux,
     }
     print(json.dumps(out))
 
@@ -436,6 +458,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-aux", action="store_true", help="skip the stand-alone SpMV microbench (configs[1])")
     ap.add_argument("--workload", default="lap7_256_cheby", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=None, help="override the grid edge (scaled-down smoke runs)")
     ap.add_argument("--ref-iters", type=int, default=3, help="PCG iterations per reference step (bounded sample)")

@@ -25,11 +25,18 @@ def main():
     ap.add_argument("--pipe", type=int, default=-1, help="pipelining variant of the compressed kernels (0..3)")
     a = ap.parse_args()
     L = capi.lib()
+    capi.check(L.b200_set_layout_override(a.layout, a.lanes))
+    capi.check(L.b200_set_compression(a.compress, a.pipe))
+    print(json.dumps(measure(a.gen, a.n, a.reps, a.pipe)))
+
+
+def measure(gen, size, reps, pipe=-1):
+    """level-0 operators of one generated stencil matrix: ms, CSR-equivalent GB/s, bytes (bench.py's aux leg too)"""
+    a = argparse.Namespace(gen=gen, n=size, reps=reps, pipe=pipe)
+    L = capi.lib()
     HL = H.lib()
     ctx = C.c_void_p(HL.hypre_b200_context())
     A = getattr(H, a.gen)(a.n, a.n, a.n)
-    capi.check(L.b200_set_layout_override(a.layout, a.lanes))
-    capi.check(L.b200_set_compression(a.compress, a.pipe))
     dA = A.device_mirror()
     n = A.global_rows
     nnz = C.c_longlong(); layout = C.c_int(); lanes = C.c_int()
@@ -71,7 +78,10 @@ def main():
     out["axpy"] = timed(lambda: capi.check(L.b200_vec_axpy(ctx, n, 0.5, v[0].ptr, v[1].ptr)), 24.0 * n)
     r = C.c_double()
     out["dot"] = timed(lambda: capi.check(L.b200_vec_dot(ctx, n, v[0].ptr, v[1].ptr, C.byref(r))), 16.0 * n)
-    print(json.dumps(out))
+    for vec in v:
+        vec.free()
+    A.destroy()
+    return out
 
 
 if __name__ == "__main__":
