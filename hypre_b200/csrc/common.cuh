@@ -250,6 +250,23 @@ static inline int dev_upload(T **dst, const T *src, size_t n)
    return B200_OK;
 }
 
+// host image of the layout arrays of a DMat (pack.cu: pure host code, CPU-tested)
+struct PackedDMat {
+   int layout = 0, lanes = 4, n_slices = 0, max_row = 0, cfmt = CFMT_NONE;
+   double avg_row = 0.0;
+   long long padded = 0, stored_bytes = 0, n_esc = 0;
+   std::vector<long long>      sl_off;      // [n_slices+1]
+   std::vector<int>            sci;         // entry-major 32-bit columns (plain layout; escape groups)
+   std::vector<double>         sva;         // entry-major fp64 values (plain layout; CFMT_VAL64)
+   std::vector<unsigned short> perm;        // layout 2
+   std::vector<int>            h_pos;       // layout 2
+   std::vector<unsigned short> idx;         // chunk-transposed 16-bit column offsets
+   std::vector<int>            base;        // [padded/32]
+   std::vector<unsigned char>  code;        // chunk-transposed value codes (u8, or u16 as byte pairs)
+   std::vector<double>         dict;
+};
+void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P);
+int  packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, double *y);
 int  dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell);
 void dmat_free(DMat *m);
 void host_transpose(const HostCsr &a, HostCsr *t);

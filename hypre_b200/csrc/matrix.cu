@@ -6,33 +6,6 @@
 #include <cstring>
 #include <numeric>
 
-static int g_layout_override = -1;
-// compressed thread-per-row storage: -1 automatic (default; B200_COMPRESS=0 in the environment turns it
-// off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it
-static int g_compress = []() { const char *e = getenv("B200_COMPRESS"); return e ? atoi(e) : -1; }();
-static int g_lanes_override  = -1;
-
-int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 3 ? v : 0; }();
-
-extern "C" int b200_set_compression(int mode, int pipeline)
-{
-   ARG_CHECK(mode >= -1 && mode <= CFMT_VAL64);
-   ARG_CHECK(pipeline >= -1 && pipeline <= 3);
-   g_compress = mode;
-   if (pipeline >= 0) { g_sellc_pipe = pipeline; }
-   return B200_OK;
-}
-
-extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
-{
-   ARG_CHECK(layout >= -1 && layout <= 2);
-   ARG_CHECK(lanes_per_row == -1 || lanes_per_row == 1 || lanes_per_row == 2 || lanes_per_row == 4 || lanes_per_row == 8 ||
-             lanes_per_row == 16 || lanes_per_row == 32);
-   g_layout_override = layout;
-   g_lanes_override  = lanes_per_row;
-   return B200_OK;
-}
-
 // longest run [out[0], out[1]) of groups whose flag is clear
 static void longest_clear_run(const std::vector<unsigned char> &g, int n_groups, int *out)
 {
@@ -77,122 +50,7 @@ void host_transpose(const HostCsr &a, HostCsr *t)
    }
 }
 
-// Value dictionary: distinct bit patterns of a[], at most `cap`; returns false if there are more.
-// Open addressing on the bit pattern (the common case -- a handful of values -- stays in cache).
-static bool build_dictionary(const std::vector<double> &a, size_t cap, std::vector<double> *dict,
-                             std::vector<unsigned long long> *keys, std::vector<int> *codes)
-{
-   const size_t tab = 1u << 18, mask = tab - 1;
-   keys->assign(tab, 0); codes->assign(tab, -1);
-   dict->clear();
-   for (size_t k = 0; k < a.size(); k++)
-   {
-      unsigned long long bits; memcpy(&bits, &a[k], 8);
-      size_t hsh = (size_t)((bits * 0x9E3779B97F4A7C15ull) >> 40) & mask;
-      while ((*codes)[hsh] >= 0 && (*keys)[hsh] != bits) { hsh = (hsh + 1) & mask; }
-      if ((*codes)[hsh] < 0)
-      {
-         if (dict->size() >= cap) { return false; }
-         (*keys)[hsh] = bits; (*codes)[hsh] = (int)dict->size(); dict->push_back(a[k]);
-      }
-   }
-   return true;
-}
-static inline int dictionary_code(const std::vector<unsigned long long> &keys, const std::vector<int> &codes, double v)
-{
-   const size_t mask = keys.size() - 1;
-   unsigned long long bits; memcpy(&bits, &v, 8);
-   size_t hsh = (size_t)((bits * 0x9E3779B97F4A7C15ull) >> 40) & mask;
-   while (codes[hsh] >= 0 && keys[hsh] != bits) { hsh = (hsh + 1) & mask; }
-   return codes[hsh];
-}
-
-// Compressed thread-per-row storage of a block already laid out as (padded) sliced ELL: see
-// rowsum_sellc (spmv.cuh).  sci/sva/livef are entry-major ([slice][k][lane]); the compressed arrays
-// are chunk-transposed ([slice][k/4][lane][k%4]).
-struct ValueDict {
-   int cfmt = CFMT_NONE;
-   std::vector<double> dict;
-   std::vector<unsigned long long> keys;
-   std::vector<int> codes;
-};
-
-static int dmat_compress(DMat *m, const std::vector<int> &sci, const std::vector<double> &sva,
-                         const std::vector<unsigned char> &livef, const std::vector<long long> &sl_off,
-                         ValueDict &vd, bool *need_ci, bool *need_va)
-{
-   const long long padded = sl_off.back();
-   const size_t n_groups = (size_t)(padded / 32);
-   std::vector<int> base(n_groups, 0);
-   std::vector<unsigned short> idx((size_t)padded, CFMT_PAD);
-   long long n_esc = 0;
-   const int n_slices = (int)sl_off.size() - 1;
-   auto cpos = [](long long off, int k, int l) { return (size_t)off + (size_t)(k >> 2) * 128 + (size_t)l * 4 + (size_t)(k & 3); };
-   for (int sidx = 0; sidx < n_slices; sidx++)
-   {
-      const long long off = sl_off[(size_t)sidx];
-      const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
-      for (int k = 0; k < w; k++)
-      {
-         const size_t g = (size_t)(off / 32) + (size_t)k, e0 = (size_t)off + (size_t)k * 32;
-         int lo = INT_MAX, hi = INT_MIN;
-         for (int l = 0; l < 32; l++) { if (livef[e0 + l]) { lo = std::min(lo, sci[e0 + l]); hi = std::max(hi, sci[e0 + l]); } }
-         if (lo > hi) { base[g] = 0; continue; }                 // nothing live: all lanes stay CFMT_PAD
-         const bool esc = (long long)hi - (long long)lo > 65534;
-         base[g] = esc ? CFMT_ESC : lo;
-         n_esc += esc;
-         for (int l = 0; l < 32; l++)
-         {
-            if (livef[e0 + l]) { idx[cpos(off, k, l)] = esc ? (unsigned short)0 : (unsigned short)(sci[e0 + l] - lo); }
-         }
-      }
-   }
-   const int cfmt = vd.cfmt;
-   std::vector<double> &dict = vd.dict;
-   const std::vector<unsigned long long> &keys = vd.keys;
-   const std::vector<int> &codes = vd.codes;
-   if (cfmt != CFMT_VAL64)
-   {
-      if (dict.empty()) { dict.push_back(0.0); }
-      const size_t csz = cfmt == CFMT_VAL8 ? 1 : 2;
-      std::vector<unsigned char> code((size_t)padded * csz, 0);
-      for (int sidx = 0; sidx < n_slices; sidx++)
-      {
-         const long long off = sl_off[(size_t)sidx];
-         const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
-         for (int k = 0; k < w; k++)
-         {
-            for (int l = 0; l < 32; l++)
-            {
-               const size_t e = (size_t)off + (size_t)k * 32 + l;
-               if (!livef[e]) { continue; }
-               const int cd = dictionary_code(keys, codes, sva[e]);
-               const size_t p = cpos(off, k, l);
-               if (cfmt == CFMT_VAL8) { code[p] = (unsigned char)cd; }
-               else { const unsigned short c16 = (unsigned short)cd; memcpy(&code[p * 2], &c16, 2); }
-            }
-         }
-      }
-      unsigned char *d_code = nullptr;
-      B200_TRY(dev_upload(&d_code, code.data(), code.size()));
-      m->c_code = d_code;
-      B200_TRY(dev_upload(&m->c_dict, dict.data(), dict.size()));
-      m->n_dict = (int)dict.size();
-   }
-   B200_TRY(dev_upload(&m->c_idx, idx.data(), idx.size()));
-   B200_TRY(dev_upload(&m->c_base, base.data(), base.size()));
-   m->cfmt = cfmt;
-   *need_ci = n_esc > 0;
-   *need_va = cfmt == CFMT_VAL64;
-   const long long per_entry = 2 + (cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 8);
-   m->stored_bytes = per_entry * padded + 4 * (long long)n_groups + 8 * (long long)n_slices + 4 * 32 * n_esc;
-   return B200_OK;
-}
-
-// Choose the layout from the row-length statistics and upload.
-//   sliced ELL (thread per row) when padding a 32-row slice to its longest row
-//   costs <= 12.5 % extra entries (stencil-like fine levels, P with regular rows);
-//   otherwise CSR with 2..32 lanes per row chosen from the average row length.
+// Choose the layout from the row-length statistics (dmat_pack, pack.cu) and upload.
 int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
 {
    (void)ctx;
@@ -206,133 +64,24 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    B200_TRY(dev_upload(&m->va, h.a.data(), (size_t)m->nnz));
    if (n == 0) { m->layout = 0; m->lanes = 4; return B200_OK; }
 
-   int max_row = 0;
-   for (int r = 0; r < n; r++) { max_row = std::max(max_row, h.i[r + 1] - h.i[r]); }
-   m->max_row = max_row;
-   m->avg_row = (double)m->nnz / (double)n;
-
-   const int n_slices = (n + 31) / 32;
-   // storage order: identity (layout 1) or rows stably sorted by decreasing length inside every
-   // window of 256 rows (layout 2); order[p] = row stored at position p (>= n: padding lane)
-   auto slice_offsets = [&](const std::vector<int> &order, std::vector<long long> *off) {
-      off->assign((size_t)n_slices + 1, 0);
-      for (int sidx = 0; sidx < n_slices; sidx++)
-      {
-         int w = 0;
-         for (int l = 0; l < 32; l++)
-         {
-            const int r = order[(size_t)sidx * 32 + l];
-            if (r < n) { w = std::max(w, h.i[r + 1] - h.i[r]); }
-         }
-         (*off)[(size_t)sidx + 1] = (*off)[(size_t)sidx] + (long long)w * 32;
-      }
-   };
-   std::vector<int> ident((size_t)n_slices * 32), sorted((size_t)n_slices * 32);
-   for (size_t p = 0; p < ident.size(); p++) { ident[p] = (int)p; }
-   sorted = ident;
-   for (int w0 = 0; w0 < n_slices * 32; w0 += 256)
-   {
-      const int w1 = std::min(w0 + 256, n_slices * 32);
-      std::stable_sort(sorted.begin() + w0, sorted.begin() + w1, [&](int a, int b) {
-         const int la = a < n ? h.i[a + 1] - h.i[a] : -1, lb = b < n ? h.i[b + 1] - h.i[b] : -1;
-         return la > lb;
-      });
-   }
-   std::vector<long long> off_plain, off_sorted;
-   slice_offsets(ident, &off_plain);
-   slice_offsets(sorted, &off_sorted);
-   const double nnz_d = (double)m->nnz;
-
-   // thread-per-row layouts need rows to fill the machine (148 SMs x 2048 threads); smaller blocks
-   // (coarse levels) keep CSR with several lanes per row, which exposes nnz-level parallelism
-   int layout = 0;
-   if (allow_sell && m->nnz > 0 && n >= 131072)
-   {
-      if ((double)off_plain[n_slices] <= 1.125 * nnz_d) { layout = 1; }
-      else if ((double)off_sorted[n_slices] <= 1.125 * nnz_d) { layout = 2; }
-   }
-   int lanes;
-   if      (m->avg_row > 48.0) { lanes = 32; }
-   else if (m->avg_row > 24.0) { lanes = 16; }
-   else if (m->avg_row > 12.0) { lanes = 8; }
-   else if (m->avg_row >  5.0) { lanes = 4; }
-   else if (m->avg_row >  3.0) { lanes = 2; }
-   else                        { lanes = 1; }   // interpolation-like rows (1-4 entries): thread per row
-   if (g_layout_override >= 0 && allow_sell) { layout = g_layout_override; }
-   if (g_lanes_override > 0) { lanes = g_lanes_override; }
-   m->layout = layout; m->lanes = lanes;
-
-   if (layout >= 1)
-   {
-      const std::vector<int> &order = layout == 2 ? sorted : ident;
-      const std::vector<long long> &off_orig = layout == 2 ? off_sorted : off_plain;
-      std::vector<long long> sl_off = off_orig;
-      // compressed storage (rowsum_sellc): pick the value format, round the slice widths up to whole
-      // chunks of 4 entries, and keep it only if a pass over the block then reads fewer bytes
-      ValueDict vd;
-      if (g_compress != 0)
-      {
-         vd.cfmt = CFMT_VAL64;
-         if (g_compress != CFMT_VAL64 &&
-             build_dictionary(h.a, g_compress == CFMT_VAL8 ? 256 : 65536, &vd.dict, &vd.keys, &vd.codes))
-         {
-            vd.cfmt = (vd.dict.size() <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
-         }
-         std::vector<long long> off4((size_t)n_slices + 1, 0);
-         for (int sidx = 0; sidx < n_slices; sidx++)
-         {
-            const long long w = (off_orig[(size_t)sidx + 1] - off_orig[(size_t)sidx]) / 32;
-            off4[(size_t)sidx + 1] = off4[(size_t)sidx] + ((w + 3) & ~3LL) * 32;
-         }
-         const long long per_entry = 2 + (vd.cfmt == CFMT_VAL8 ? 1 : vd.cfmt == CFMT_VAL16 ? 2 : 8);
-         if (g_compress > 0 || per_entry * off4[(size_t)n_slices] + off4[(size_t)n_slices] / 8 < 12 * off_orig[(size_t)n_slices])
-         {
-            sl_off.swap(off4);
-         }
-         else { vd.cfmt = CFMT_NONE; }
-      }
-      const bool compress = vd.cfmt != CFMT_NONE;
-      const long long padded = sl_off[n_slices];
-      std::vector<int>    sci((size_t)padded);
-      std::vector<double> sva((size_t)padded);
-      std::vector<unsigned char> livef(compress ? (size_t)padded : 0);
-      for (int sidx = 0; sidx < n_slices; sidx++)
-      {
-         const int w = (int)((sl_off[(size_t)sidx + 1] - sl_off[(size_t)sidx]) / 32);
-         for (int l = 0; l < 32; l++)
-         {
-            const int r = order[(size_t)sidx * 32 + l];
-            const int beg = r < n ? h.i[r] : 0, len = r < n ? h.i[r + 1] - h.i[r] : 0;
-            // padding gathers a column this row already touches (or column 0)
-            const int padc = len > 0 ? h.j[beg + len - 1] : 0;
-            for (int k = 0; k < w; k++)
-            {
-               const size_t p = (size_t)sl_off[(size_t)sidx] + (size_t)k * 32 + l;
-               if (k < len) { sci[p] = h.j[beg + k]; sva[p] = h.a[beg + k]; }
-               else         { sci[p] = padc;         sva[p] = 0.0; }
-               if (compress) { livef[p] = k < len; }
-            }
-         }
-      }
-      m->n_slices = n_slices; m->sell_entries = padded;
-      m->stored_bytes = 12 * padded + 8 * (long long)n_slices;
-      B200_TRY(dev_upload(&m->sl_off, sl_off.data(), sl_off.size()));
-      bool need_ci = true, need_va = true;
-      if (compress) { B200_TRY(dmat_compress(m, sci, sva, livef, sl_off, vd, &need_ci, &need_va)); }
-      if (need_ci) { B200_TRY(dev_upload(&m->sl_ci, sci.data(), sci.size())); }
-      if (need_va) { B200_TRY(dev_upload(&m->sl_va, sva.data(), sva.size())); }
-      if (layout == 2)
-      {
-         std::vector<unsigned short> perm(order.size());
-         m->h_pos.assign((size_t)n, 0);
-         for (size_t p = 0; p < order.size(); p++)
-         {
-            perm[p] = (unsigned short)(order[p] - (int)(p / 256) * 256);    // < 256 + 32
-            if (order[p] < n) { m->h_pos[(size_t)order[p]] = (int)p; }
-         }
-         B200_TRY(dev_upload(&m->sl_perm, perm.data(), perm.size()));
-      }
-   }
+   PackedDMat P;
+   dmat_pack(h, allow_sell, &P);
+   m->max_row = P.max_row; m->avg_row = P.avg_row;
+   m->layout = P.layout; m->lanes = P.lanes;
+   if (P.layout == 0) { return B200_OK; }
+   m->n_slices = P.n_slices; m->sell_entries = P.padded; m->stored_bytes = P.stored_bytes;
+   m->cfmt = P.cfmt; m->n_dict = (int)P.dict.size();
+   B200_TRY(dev_upload(&m->sl_off, P.sl_off.data(), P.sl_off.size()));
+   B200_TRY(dev_upload(&m->sl_ci, P.sci.data(), P.sci.size()));
+   B200_TRY(dev_upload(&m->sl_va, P.sva.data(), P.sva.size()));
+   B200_TRY(dev_upload(&m->sl_perm, P.perm.data(), P.perm.size()));
+   B200_TRY(dev_upload(&m->c_idx, P.idx.data(), P.idx.size()));
+   B200_TRY(dev_upload(&m->c_base, P.base.data(), P.base.size()));
+   unsigned char *d_code = nullptr;
+   B200_TRY(dev_upload(&d_code, P.code.data(), P.code.size()));
+   m->c_code = d_code;
+   B200_TRY(dev_upload(&m->c_dict, P.dict.data(), P.dict.size()));
+   m->h_pos.swap(P.h_pos);
    return B200_OK;
 }
 

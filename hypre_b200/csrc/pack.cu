@@ -1,0 +1,384 @@
+// pack.cu -- host-side construction of the HBM layouts of one CSR block (no CUDA calls):
+// layout choice from the row-length statistics, sliced ELL / SELL-32-256 packing, and the
+// lossless compressed form (16-bit column offsets + value dictionary) read by rowsum_sellc
+// (spmv.cuh).  dmat_upload (matrix.cu) copies the result to the device; packed_matvec_host
+// decodes it on the host with the kernels' addressing (tests of the storage format only --
+// no solve path calls it).
+//
+// The block is the reference's hypre_CSRMatrix (src/seq_mv/csr_matrix.h: i, j, data); row
+// order, entry order inside a row and the values are kept, only the encoding changes.
+#include "common.cuh"
+#include <algorithm>
+#include <climits>
+#include <cstring>
+
+static int g_layout_override = -1;
+static int g_lanes_override  = -1;
+// compressed thread-per-row storage: -1 automatic (default; B200_COMPRESS=0 in the environment turns it
+// off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it
+static int g_compress = []() { const char *e = getenv("B200_COMPRESS"); return e ? atoi(e) : -1; }();
+int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 3 ? v : 0; }();
+
+extern "C" int b200_set_compression(int mode, int pipeline)
+{
+   ARG_CHECK(mode >= -1 && mode <= CFMT_VAL64);
+   ARG_CHECK(pipeline >= -1 && pipeline <= 3);
+   g_compress = mode;
+   if (pipeline >= 0) { g_sellc_pipe = pipeline; }
+   return B200_OK;
+}
+
+extern "C" int b200_set_layout_override(int layout, int lanes_per_row)
+{
+   ARG_CHECK(layout >= -1 && layout <= 2);
+   ARG_CHECK(lanes_per_row == -1 || lanes_per_row == 1 || lanes_per_row == 2 || lanes_per_row == 4 || lanes_per_row == 8 ||
+             lanes_per_row == 16 || lanes_per_row == 32);
+   g_layout_override = layout;
+   g_lanes_override  = lanes_per_row;
+   return B200_OK;
+}
+
+// ---------------------------------------------------------------- value dictionary
+// Distinct bit patterns of a[], at most `cap`; open addressing on the bit pattern (the common case --
+// a handful of values -- stays in cache).  Returns false as soon as there are more than cap.
+struct ValueDict {
+   std::vector<double> dict;
+   std::vector<unsigned long long> keys;
+   std::vector<int> codes;
+   static size_t slot(unsigned long long bits, size_t mask) { return (size_t)((bits * 0x9E3779B97F4A7C15ull) >> 40) & mask; }
+   bool build(const std::vector<double> &a, size_t cap)
+   {
+      const size_t tab = 1u << 18, mask = tab - 1;     // cap <= 65536: load factor <= 1/4
+      keys.assign(tab, 0); codes.assign(tab, -1);
+      dict.clear();
+      for (size_t k = 0; k < a.size(); k++)
+      {
+         unsigned long long bits; memcpy(&bits, &a[k], 8);
+         size_t hsh = slot(bits, mask);
+         while (codes[hsh] >= 0 && keys[hsh] != bits) { hsh = (hsh + 1) & mask; }
+         if (codes[hsh] < 0)
+         {
+            if (dict.size() >= cap) { return false; }
+            keys[hsh] = bits; codes[hsh] = (int)dict.size(); dict.push_back(a[k]);
+         }
+      }
+      return true;
+   }
+   int code(double v) const
+   {
+      const size_t mask = keys.size() - 1;
+      unsigned long long bits; memcpy(&bits, &v, 8);
+      size_t hsh = slot(bits, mask);
+      while (codes[hsh] >= 0 && keys[hsh] != bits) { hsh = (hsh + 1) & mask; }
+      return codes[hsh];
+   }
+};
+
+// ---------------------------------------------------------------- layout choice + packing
+// Thread-per-row layouts: slice = 32 consecutive storage positions; order[p] = row stored at position p
+// (>= n: padding lane).  Layout 1 keeps the row order, layout 2 sorts the rows of every 256-row window
+// by decreasing length (stable) before cutting slices.
+static void slice_offsets(const HostCsr &h, const std::vector<int> *order, int n_slices, std::vector<long long> *off)
+{
+   const int n = h.n_rows;
+   std::vector<int> width((size_t)n_slices, 0);
+#pragma omp parallel for schedule(static)
+   for (int sidx = 0; sidx < n_slices; sidx++)
+   {
+      int w = 0;
+      for (int l = 0; l < 32; l++)
+      {
+         const int p = sidx * 32 + l;
+         const int r = order ? (*order)[(size_t)p] : p;
+         if (r < n) { w = std::max(w, h.i[r + 1] - h.i[r]); }
+      }
+      width[(size_t)sidx] = w;
+   }
+   off->assign((size_t)n_slices + 1, 0);
+   for (int sidx = 0; sidx < n_slices; sidx++) { (*off)[(size_t)sidx + 1] = (*off)[(size_t)sidx] + (long long)width[(size_t)sidx] * 32; }
+}
+
+static void sorted_order(const HostCsr &h, int n_slices, std::vector<int> *sorted)
+{
+   const int n = h.n_rows, np = n_slices * 32;
+   sorted->resize((size_t)np);
+#pragma omp parallel for schedule(static)
+   for (int w0 = 0; w0 < np; w0 += 256)
+   {
+      const int w1 = std::min(w0 + 256, np);
+      for (int p = w0; p < w1; p++) { (*sorted)[(size_t)p] = p; }
+      std::stable_sort(sorted->begin() + w0, sorted->begin() + w1, [&](int a, int b) {
+         const int la = a < n ? h.i[a + 1] - h.i[a] : -1, lb = b < n ? h.i[b + 1] - h.i[b] : -1;
+         return la > lb;
+      });
+   }
+}
+
+void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
+{
+   *P = PackedDMat();
+   const int n = h.n_rows;
+   const long long nnz = n > 0 ? (long long)h.i[n] : 0;
+   if (n == 0) { return; }
+
+   int max_row = 0;
+   for (int r = 0; r < n; r++) { max_row = std::max(max_row, h.i[r + 1] - h.i[r]); }
+   P->max_row = max_row;
+   P->avg_row = (double)nnz / (double)n;
+   int lanes;
+   if      (P->avg_row > 48.0) { lanes = 32; }
+   else if (P->avg_row > 24.0) { lanes = 16; }
+   else if (P->avg_row > 12.0) { lanes = 8; }
+   else if (P->avg_row >  5.0) { lanes = 4; }
+   else if (P->avg_row >  3.0) { lanes = 2; }
+   else                        { lanes = 1; }   // interpolation-like rows (1-4 entries): thread per row
+   if (g_lanes_override > 0) { lanes = g_lanes_override; }
+   P->lanes = lanes;
+
+   // thread-per-row layouts need rows to fill the machine (148 SMs x 2048 threads) and padding of at
+   // most 12.5 %; smaller blocks (coarse levels) keep CSR with several lanes per row
+   const int n_slices = (n + 31) / 32;
+   const double nnz_d = (double)nnz;
+   std::vector<int> sorted;
+   std::vector<long long> off_orig;
+   int layout = 0;
+   const bool forced = g_layout_override >= 0 && allow_sell;
+   if (forced) { layout = g_layout_override; }
+   else if (allow_sell && nnz > 0 && n >= 131072)
+   {
+      slice_offsets(h, nullptr, n_slices, &off_orig);
+      if ((double)off_orig[(size_t)n_slices] <= 1.125 * nnz_d) { layout = 1; }
+      else
+      {
+         sorted_order(h, n_slices, &sorted);
+         slice_offsets(h, &sorted, n_slices, &off_orig);
+         if ((double)off_orig[(size_t)n_slices] <= 1.125 * nnz_d) { layout = 2; }
+      }
+   }
+   P->layout = layout;
+   if (layout == 0) { return; }
+   if (forced)
+   {
+      if (layout == 2) { sorted_order(h, n_slices, &sorted); }
+      slice_offsets(h, layout == 2 ? &sorted : nullptr, n_slices, &off_orig);
+   }
+   const std::vector<int> *order = layout == 2 ? &sorted : nullptr;
+   auto row_at = [&](int p) { return order ? (*order)[(size_t)p] : p; };
+
+   // ---- compressed storage (rowsum_sellc): pick the value format, round the slice widths up to whole
+   // chunks of 4 entries, and keep it only if a pass over the block then reads fewer bytes
+   ValueDict vd;
+   int cfmt = CFMT_NONE;
+   std::vector<long long> sl_off = off_orig;
+   if (g_compress != 0)
+   {
+      cfmt = CFMT_VAL64;
+      if (g_compress != CFMT_VAL64 && vd.build(h.a, g_compress == CFMT_VAL8 ? 256 : 65536))
+      {
+         cfmt = (vd.dict.size() <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
+      }
+      std::vector<long long> off4((size_t)n_slices + 1, 0);
+      for (int sidx = 0; sidx < n_slices; sidx++)
+      {
+         const long long w = (off_orig[(size_t)sidx + 1] - off_orig[(size_t)sidx]) / 32;
+         off4[(size_t)sidx + 1] = off4[(size_t)sidx] + ((w + 3) & ~3LL) * 32;
+      }
+      const long long per_entry = 2 + (cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 8);
+      if (g_compress > 0 || per_entry * off4[(size_t)n_slices] + off4[(size_t)n_slices] / 8 < 12 * off_orig[(size_t)n_slices])
+      {
+         sl_off.swap(off4);
+      }
+      else { cfmt = CFMT_NONE; }
+   }
+   const long long padded = sl_off[(size_t)n_slices];
+   P->n_slices = n_slices; P->padded = padded; P->cfmt = cfmt;
+
+   if (layout == 2)
+   {
+      P->perm.resize(sorted.size());
+      P->h_pos.assign((size_t)n, 0);
+      for (size_t p = 0; p < sorted.size(); p++)
+      {
+         P->perm[p] = (unsigned short)(sorted[p] - (int)(p / 256) * 256);    // < 256 + 32
+         if (sorted[p] < n) { P->h_pos[(size_t)sorted[p]] = (int)p; }
+      }
+   }
+
+   // entry-major arrays ([slice][k][lane]): the plain layout, the fp64 values of CFMT_VAL64 and the
+   // 32-bit columns kept for escape groups.  Padding gathers a column the row already touches, value 0.
+   auto fill_entry_major = [&](bool want_ci, bool want_va) {
+      if (!want_ci && !want_va) { return; }
+      if (want_ci) { P->sci.resize((size_t)padded); }
+      if (want_va) { P->sva.resize((size_t)padded); }
+#pragma omp parallel for schedule(static)
+      for (int sidx = 0; sidx < n_slices; sidx++)
+      {
+         const long long off = sl_off[(size_t)sidx];
+         const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
+         for (int l = 0; l < 32; l++)
+         {
+            const int r = row_at(sidx * 32 + l);
+            const int beg = r < n ? h.i[r] : 0, len = r < n ? h.i[r + 1] - h.i[r] : 0;
+            const int padc = len > 0 ? h.j[beg + len - 1] : 0;
+            for (int k = 0; k < w; k++)
+            {
+               const size_t p = (size_t)off + (size_t)k * 32 + (size_t)l;
+               if (want_ci) { P->sci[p] = k < len ? h.j[beg + k] : padc; }
+               if (want_va) { P->sva[p] = k < len ? h.a[beg + k] : 0.0; }
+            }
+         }
+      }
+   };
+   if (cfmt == CFMT_NONE)
+   {
+      fill_entry_major(true, true);
+      P->stored_bytes = 12 * padded + 8 * (long long)n_slices;
+      P->sl_off.swap(sl_off);
+      return;
+   }
+
+   // chunk-transposed arrays ([slice][k/4][lane][k%4]): 16-bit column offsets from the base of
+   // (slice, k), value codes; CFMT_PAD marks padding lanes
+   const size_t n_groups = (size_t)(padded / 32);
+   const size_t csz = cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 0;
+   P->base.assign(n_groups, 0);
+   P->idx.assign((size_t)padded, CFMT_PAD);
+   P->code.assign((size_t)padded * csz, 0);
+   if (csz && vd.dict.empty()) { vd.dict.push_back(0.0); }
+   long long n_esc = 0;
+#pragma omp parallel for schedule(static) reduction(+ : n_esc)
+   for (int sidx = 0; sidx < n_slices; sidx++)
+   {
+      const long long off = sl_off[(size_t)sidx];
+      const int w = (int)((sl_off[(size_t)sidx + 1] - off) / 32);
+      int beg[32], len[32];
+      for (int l = 0; l < 32; l++)
+      {
+         const int r = row_at(sidx * 32 + l);
+         beg[l] = r < n ? h.i[r] : 0; len[l] = r < n ? h.i[r + 1] - h.i[r] : 0;
+      }
+      for (int k = 0; k < w; k++)
+      {
+         int lo = INT_MAX, hi = INT_MIN;
+         for (int l = 0; l < 32; l++) { if (k < len[l]) { const int c = h.j[beg[l] + k]; lo = std::min(lo, c); hi = std::max(hi, c); } }
+         if (lo > hi) { continue; }                              // nothing live: base 0, all lanes CFMT_PAD
+         const bool esc = (long long)hi - (long long)lo > 65534;
+         P->base[(size_t)(off / 32) + (size_t)k] = esc ? CFMT_ESC : lo;
+         n_esc += esc;
+         for (int l = 0; l < 32; l++)
+         {
+            if (k >= len[l]) { continue; }
+            const size_t p = (size_t)off + (size_t)(k >> 2) * 128 + (size_t)l * 4 + (size_t)(k & 3);
+            P->idx[p] = esc ? (unsigned short)0 : (unsigned short)(h.j[beg[l] + k] - lo);
+            if (csz)
+            {
+               const int cd = vd.code(h.a[beg[l] + k]);
+               if (csz == 1) { P->code[p] = (unsigned char)cd; }
+               else { const unsigned short c16 = (unsigned short)cd; memcpy(&P->code[p * 2], &c16, 2); }
+            }
+         }
+      }
+   }
+   P->n_esc = n_esc;
+   fill_entry_major(n_esc > 0, cfmt == CFMT_VAL64);
+   if (csz) { P->dict.swap(vd.dict); }
+   const long long per_entry = 2 + (cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 8);
+   P->stored_bytes = per_entry * padded + 4 * (long long)n_groups + 8 * (long long)n_slices + 4 * 32 * n_esc;
+   P->sl_off.swap(sl_off);
+}
+
+// ---------------------------------------------------------------- host decode (tests of the format)
+// y = A x from the packed arrays, with the addressing of rows_range / rowsum_sell / rowsum_sellc
+// (spmv.cuh) and the same fma chain per row.  Layout 0 has no packed form (the CSR arrays are used).
+int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, double *y)
+{
+   const int n = h.n_rows;
+   if (P.layout == 0)
+   {
+      for (int r = 0; r < n; r++)
+      {
+         double t = 0.0;
+         for (int k = h.i[r]; k < h.i[r + 1]; k++) { t = fma(h.a[k], x[h.j[k]], t); }
+         y[r] = t;
+      }
+      return B200_OK;
+   }
+   for (int slice = 0; slice < P.n_slices; slice++)
+   {
+      const long long off = P.sl_off[(size_t)slice];
+      const long long span = P.sl_off[(size_t)slice + 1] - off;
+      for (int lane = 0; lane < 32; lane++)
+      {
+         int row = slice * 32 + lane;
+         if (!P.perm.empty()) { row = (slice >> 3) * 256 + P.perm[(size_t)row]; }
+         double t = 0.0;
+         if (P.cfmt == CFMT_NONE)
+         {
+            const int width = (int)(span >> 5);
+            for (int k = 0; k < width; k++)
+            {
+               const size_t p = (size_t)off + (size_t)k * 32 + (size_t)lane;
+               const int c = P.sci[p];
+               if (c < 0 || c >= h.n_cols) { b200_set_error("packed column out of range"); return B200_ERR_ARG; }
+               t = fma(P.sva[p], x[c], t);
+            }
+         }
+         else
+         {
+            if (span & 127) { b200_set_error("compressed slice width not a multiple of 4"); return B200_ERR_ARG; }
+            const int n_chunks = (int)(span >> 7);
+            for (int c = 0; c < n_chunks; c++)
+            {
+               for (int j = 0; j < 4; j++)
+               {
+                  const size_t p = (size_t)off + (size_t)c * 128 + (size_t)lane * 4 + (size_t)j;
+                  const unsigned o = P.idx[p];
+                  if (o == CFMT_PAD) { continue; }
+                  const int b = P.base[(size_t)(off >> 5) + (size_t)c * 4 + (size_t)j];
+                  const size_t e = (size_t)off + (size_t)(c * 4 + j) * 32 + (size_t)lane;      // entry-major position
+                  int col;
+                  if (b == CFMT_ESC)
+                  {
+                     if (P.sci.empty()) { b200_set_error("escape group without 32-bit columns"); return B200_ERR_ARG; }
+                     col = P.sci[e];
+                  }
+                  else { col = b + (int)o; }
+                  if (col < 0 || col >= h.n_cols) { b200_set_error("packed column out of range"); return B200_ERR_ARG; }
+                  double v;
+                  if (P.cfmt == CFMT_VAL8)       { v = P.dict[P.code[p]]; }
+                  else if (P.cfmt == CFMT_VAL16) { unsigned short c16; memcpy(&c16, &P.code[p * 2], 2); v = P.dict[c16]; }
+                  else                           { v = P.sva[e]; }
+                  t = fma(v, x[col], t);
+               }
+            }
+         }
+         if (row < n) { y[row] = t; }
+         else if (t != 0.0) { b200_set_error("padding lane carries entries"); return B200_ERR_ARG; }
+      }
+   }
+   return B200_OK;
+}
+
+// C-ABI: pack a CSR block with the current layout / compression settings and decode it on the host.
+extern "C" int b200_storage_decode_host(int n_rows, int n_cols, const int *ai, const int *aj, const double *aa,
+                                        const double *x, double *y, int *layout, int *value_format,
+                                        long long *stored_bytes, long long *n_escape_groups)
+{
+   ARG_CHECK(n_rows >= 0 && n_cols >= 0 && (n_rows == 0 || (ai != nullptr && x != nullptr && y != nullptr)));
+   HostCsr h;
+   h.n_rows = n_rows; h.n_cols = n_cols;
+   h.i.assign(1, 0);
+   if (n_rows > 0)
+   {
+      h.i.assign(ai, ai + n_rows + 1);
+      h.j.assign(aj, aj + ai[n_rows]);
+      h.a.assign(aa, aa + ai[n_rows]);
+   }
+   PackedDMat P;
+   dmat_pack(h, 1, &P);
+   if (layout) { *layout = P.layout; }
+   if (value_format) { *value_format = P.cfmt; }
+   if (stored_bytes) { *stored_bytes = P.layout >= 1 ? P.stored_bytes : 12LL * (long long)h.j.size() + 4LL * (n_rows + 1); }
+   if (n_escape_groups) { *n_escape_groups = P.n_esc; }
+   return packed_matvec_host(P, h, x, y);
+}

@@ -110,6 +110,12 @@ int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stor
  * 1 slice offsets loaded one trip ahead, 2 additionally L2 prefetch of the next slice's streams, 3 = 2 at
  * 6 blocks per SM; -1 leaves it (environment B200_SELLC_PIPE). */
 int b200_set_compression(int mode, int pipeline);
+/* Test hook for the storage formats (host only, no device needed, never on a solve path): packs the CSR
+ * block with the current layout / compression settings exactly as b200_parcsr_create would and computes
+ * y = A x on the host FROM THE PACKED ARRAYS with the kernels' addressing (same fma chain per row). */
+int b200_storage_decode_host(int n_rows, int n_cols, const int *i, const int *j, const double *a,
+                             const double *x, double *y, int *layout, int *value_format,
+                             long long *stored_bytes, long long *n_escape_groups);
 /* force the storage layout chosen for the diag block (tests/bench): -1 auto */
 int b200_set_layout_override(int layout, int lanes_per_row);
 
