@@ -1,6 +1,7 @@
 """CPU tests of the N>1 host logic: b200_rowpart (row partition + halo plan, the counterpart of
 GenerateDiagAndOffd / hypre_MatvecCommPkgCreate) in a single-process emulation over several rank
-counts, and a real 2-process gloo run of tests/dist_worker.py."""
+counts, a real 2-process gloo run of tests/dist_worker.py, and a comparison with what N real ranks of
+the reference (oracle/_ref/dump_parcsr over oracle/mpishim) build and negotiate for a whole hierarchy."""
 import os
 import subprocess
 import sys
@@ -116,3 +117,79 @@ def test_two_process_gloo_halo_exchange(built):
            "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+# ------------------------------------------------------------------ against the reference on N real ranks
+REF_BIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+HAVE_MP = all(os.path.exists(os.path.join(REF_BIN, f)) for f in ("mpirun_shim", "dump_parcsr"))
+
+
+def read_dump(path):
+    """one rank's file written by oracle/mpishim/dump_parcsr.c"""
+    raw = np.fromfile(path, dtype=np.int32)
+    h = raw[:12]
+    (grows, gcols, first_row, n, first_col, ncd, nco, nnzd, nnzo, ns, nse, nr) = [int(v) for v in h]
+    pos = [12]
+
+    def take(k):
+        a = raw[pos[0]:pos[0] + k].copy(); pos[0] += k
+        return a
+    d = dict(global_rows=grows, global_cols=gcols, first_row=first_row, n_rows=n, first_col=first_col, n_cols_diag=ncd)
+    d["diag_i"], d["diag_j"] = take(n + 1), take(nnzd)
+    d["offd_i"], d["offd_j"] = take(n + 1), take(nnzo)
+    d["col_map_offd"] = take(nco)
+    d["send_procs"], d["send_map_starts"], d["send_map_elmts"] = take(ns), take(ns + 1), take(nse)
+    d["recv_procs"], d["recv_vec_starts"] = take(nr), take(nr + 1)
+    vals = raw[pos[0]:].view(np.float64)
+    d["diag_a"], d["offd_a"] = vals[:nnzd].copy(), vals[nnzd:nnzd + nnzo].copy()
+    assert len(vals) == nnzd + nnzo
+    return d
+
+
+def global_from_dumps(parts):
+    """global CSR in the reference's numbering; every row = its diag entries, then its offd entries, each in
+    the reference's storage order"""
+    ii, jj, aa = [0], [], []
+    for d in parts:
+        for r in range(d["n_rows"]):
+            dk = slice(d["diag_i"][r], d["diag_i"][r + 1]); ok = slice(d["offd_i"][r], d["offd_i"][r + 1])
+            jj += list(d["diag_j"][dk] + d["first_col"]) + list(d["col_map_offd"][d["offd_j"][ok]])
+            aa += list(d["diag_a"][dk]) + list(d["offd_a"][ok])
+            ii.append(len(jj))
+    shape = (parts[0]["global_rows"], parts[0]["global_cols"])
+    return sp.csr_matrix((np.array(aa), np.array(jj, dtype=np.int32), np.array(ii, dtype=np.int32)), shape=shape)
+
+
+@pytest.mark.skipif(not HAVE_MP, reason="oracle/_ref multi-rank build absent (make -C oracle)")
+@pytest.mark.parametrize("pts,n,P", [(7, (12, 10, 8), (2, 2, 1)), (27, (9, 8, 7), (1, 3, 1)), (7, (6, 6, 9), (1, 1, 2)),
+                                     (7, (16, 12, 10), (2, 2, 2))])
+def test_rowpart_equals_the_reference_on_real_ranks(tmp_path, pts, n, P):
+    """b200_rowpart_create (no communication) against what N ranks of the reference build and negotiate for
+    every operator of a BoomerAMG hierarchy -- A_l and the rectangular P_l: diag/offd blocks, col_map_offd
+    and the whole hypre_ParCSRCommPkg (send_procs, send_map_starts, send_map_elmts, recv_procs,
+    recv_vec_starts) must be identical, rank by rank."""
+    nranks = P[0] * P[1] * P[2]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    p = subprocess.run([os.path.join(REF_BIN, "mpirun_shim"), "-np", str(nranks), os.path.join(REF_BIN, "dump_parcsr"),
+                        str(pts)] + [str(v) for v in n + P] + [str(tmp_path)], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0 and "DUMP_OK" in p.stdout, p.stderr[-500:]
+    levels = int(p.stdout.split("levels")[1].split()[0])
+    checked = 0
+    for name in ["A%d" % l for l in range(levels)] + ["P%d" % l for l in range(levels - 1)]:
+        parts = [read_dump(os.path.join(str(tmp_path), "%s.%d.bin" % (name, r))) for r in range(nranks)]
+        A = global_from_dumps(parts)
+        rs = [d["first_row"] for d in parts] + [parts[0]["global_rows"]]
+        cs = [d["first_col"] for d in parts] + [parts[0]["global_cols"]]
+        for r, d in enumerate(parts):
+            rp = capi.RowPart(r, nranks, A, rs, cs)
+            for key in ("diag_i", "diag_j", "offd_i", "offd_j", "col_map_offd", "recv_procs", "send_procs",
+                        "send_map_elmts"):
+                assert np.array_equal(getattr(rp, key), d[key]), (name, r, key)
+            # (the reference leaves a one-element starts array when a rank has no neighbours)
+            assert np.array_equal(rp.send_map_starts, d["send_map_starts"]), (name, r)
+            if len(d["recv_procs"]):
+                assert np.array_equal(rp.recv_vec_starts, d["recv_vec_starts"]), (name, r)
+            assert np.array_equal(rp.diag_a, d["diag_a"]) and np.array_equal(rp.offd_a, d["offd_a"]), (name, r)
+            rp.destroy()
+            checked += 1
+    assert checked == nranks * (2 * levels - 1)
