@@ -8,7 +8,14 @@
  * and checks that hypre_b200's communication-free restatement (hypre_b200/csrc/partition.cu,
  * b200_rowpart_create) produces, rank by rank, exactly the same blocks and the same plan.
  *
- *    mpirun_shim -np N dump_parcsr <7|27> nx ny nz P Q R outdir
+ *    mpirun_shim -np N dump_parcsr <7|27> nx ny nz P Q R outdir [relax_type [rhsrand]]
+ *
+ * With a relax type the program also does what `ij -solver 1 -rlx <type> [-rhsrand]` does -- BoomerAMG with
+ * the driver's defaults (src/test/ij.c:248-302) as preconditioner of PCG, tol 1e-8 -- and writes what a
+ * serial restatement needs to repeat that solve on the gathered hierarchy (tests/test_oracle_multirank.py):
+ * per level and rank l1_<l>.<rank>.f64 / ds_<l>.<rank>.f64 (l1 norms, Chebyshev diagonal scaling), per level
+ * coefs_<l>.f64, the gathered dense coarse matrix dense.f64, b.<rank>.f64, x.<rank>.f64 (solution),
+ * norms.f64 / rel_norms.f64 (PCG log) and meta.txt.
  *
  * File <outdir>/<name>.<rank>.bin: int32 header {global_rows, global_cols, first_row, n_rows, first_col,
  * n_cols_diag, n_cols_offd, nnz_diag, nnz_offd, num_sends, n_send_elmts, num_recvs}, then int32 arrays
@@ -17,9 +24,20 @@
  */
 #include "_hypre_parcsr_ls.h"
 #include <stdio.h>
+#include <math.h>
 #include <stdlib.h>
 
 static void put_i(FILE *f, const HYPRE_Int *a, HYPRE_Int n) { if (n > 0) { fwrite(a, sizeof(HYPRE_Int), (size_t)n, f); } }
+
+static void put_f64(const char *dir, const char *name, const HYPRE_Real *a, HYPRE_Int n)
+{
+   char path[1024];
+   snprintf(path, sizeof(path), "%s/%s", dir, name);
+   FILE *f = fopen(path, "wb");
+   if (!f) { perror(path); MPI_Abort(MPI_COMM_WORLD, 4); }
+   if (n > 0) { fwrite(a, sizeof(HYPRE_Real), (size_t)n, f); }
+   fclose(f);
+}
 
 static void dump(hypre_ParCSRMatrix *A, const char *dir, const char *name, int rank)
 {
@@ -66,6 +84,7 @@ int main(int argc, char **argv)
    int pts = atoi(argv[1]), nx = atoi(argv[2]), ny = atoi(argv[3]), nz = atoi(argv[4]);
    int P = atoi(argv[5]), Q = atoi(argv[6]), R = atoi(argv[7]);
    const char *dir = argv[8];
+   int rlx = argc > 9 ? atoi(argv[9]) : -1, rhsrand = argc > 10 ? atoi(argv[10]) : 0;
    if (P * Q * R != size) { if (!rank) { fprintf(stderr, "P*Q*R != ranks\n"); } MPI_Abort(MPI_COMM_WORLD, 2); }
    /* rank -> box coordinates as src/test/ij.c BuildParLaplacian does */
    int p = rank % P, q = ((rank - p) / P) % Q, r = (rank - p - P * q) / (P * Q);
@@ -92,24 +111,114 @@ int main(int argc, char **argv)
    HYPRE_ParVectorCreate(MPI_COMM_WORLD, hypre_ParCSRMatrixGlobalNumRows((hypre_ParCSRMatrix *)A),
                          hypre_ParCSRMatrixRowStarts((hypre_ParCSRMatrix *)A), &x);
    HYPRE_ParVectorInitialize(x); HYPRE_ParVectorSetConstantValues(x, 0.0);
-   /* the defaults src/test/ij.c passes (ij.c:248-302): HMIS, ext+i, Pmax 4 */
-   HYPRE_Solver amg;
+   if (rhsrand)
+   {
+      /* ij -rhsrand (src/test/ij.c build_rhs_type 3): random values, scaled to unit 2-norm */
+      HYPRE_Real nrm;
+      HYPRE_ParVectorSetRandomValues(b, 22775);
+      HYPRE_ParVectorInnerProd(b, b, &nrm);
+      HYPRE_ParVectorScale(1.0 / sqrt(nrm), b);
+   }
+   /* the defaults src/test/ij.c passes (ij.c:248-302): HMIS, ext+i, Pmax 4, relax_order 0, max coarse 9 */
+   HYPRE_Solver amg, pcg = NULL;
    HYPRE_BoomerAMGCreate(&amg);
    HYPRE_BoomerAMGSetCoarsenType(amg, 10);
    HYPRE_BoomerAMGSetInterpType(amg, 6);
    HYPRE_BoomerAMGSetPMaxElmts(amg, 4);
    HYPRE_BoomerAMGSetRelaxOrder(amg, 0);
-   HYPRE_BoomerAMGSetRelaxType(amg, 18);
+   HYPRE_BoomerAMGSetMaxCoarseSize(amg, 9);
+   HYPRE_BoomerAMGSetMinCoarseSize(amg, 0);
+   HYPRE_BoomerAMGSetMaxRowSum(amg, 1.0);
+   HYPRE_BoomerAMGSetStrongThreshold(amg, 0.25);
+   HYPRE_BoomerAMGSetMaxLevels(amg, 25);
+   HYPRE_BoomerAMGSetMeasureType(amg, 0);
+   HYPRE_BoomerAMGSetNumSweeps(amg, 1);
+   HYPRE_BoomerAMGSetTruncFactor(amg, 0.0);
+   HYPRE_BoomerAMGSetAggNumLevels(amg, 0);
    HYPRE_BoomerAMGSetPrintLevel(amg, 0);
-   HYPRE_BoomerAMGSetup(amg, A, b, x);
+   HYPRE_BoomerAMGSetChebyOrder(amg, 2);
+   HYPRE_BoomerAMGSetChebyEigEst(amg, 10);
+   HYPRE_BoomerAMGSetChebyVariant(amg, 0);
+   HYPRE_BoomerAMGSetChebyScale(amg, 1);
+   HYPRE_BoomerAMGSetChebyFraction(amg, 0.3);
+   HYPRE_BoomerAMGSetRelaxType(amg, rlx >= 0 ? rlx : 18);
+   int iters = 0;
+   if (rlx >= 0)
+   {
+      HYPRE_BoomerAMGSetTol(amg, 0.0);
+      HYPRE_BoomerAMGSetMaxIter(amg, 1);
+      HYPRE_ParCSRPCGCreate(MPI_COMM_WORLD, &pcg);
+      HYPRE_PCGSetMaxIter(pcg, 1000);
+      HYPRE_PCGSetTol(pcg, 1.e-8);
+      HYPRE_PCGSetTwoNorm(pcg, 1);
+      HYPRE_PCGSetRelChange(pcg, 0);
+      HYPRE_PCGSetPrintLevel(pcg, 0);
+      HYPRE_PCGSetLogging(pcg, 1);
+      HYPRE_PCGSetPrecond(pcg, (HYPRE_PtrToSolverFcn)HYPRE_BoomerAMGSolve, (HYPRE_PtrToSolverFcn)HYPRE_BoomerAMGSetup, amg);
+      HYPRE_ParCSRPCGSetup(pcg, A, b, x);
+      HYPRE_ParCSRPCGSolve(pcg, A, b, x);
+      HYPRE_PCGGetNumIterations(pcg, &iters);
+   }
+   else { HYPRE_BoomerAMGSetup(amg, A, b, x); }
    hypre_ParAMGData *d = (hypre_ParAMGData *)amg;
    int nl = hypre_ParAMGDataNumLevels(d);
    for (int l = 0; l < nl; l++)
    {
-      char name[32];
+      char name[64];
       snprintf(name, sizeof(name), "A%d", l);
       dump(hypre_ParAMGDataAArray(d)[l], dir, name, rank);
       if (l < nl - 1) { snprintf(name, sizeof(name), "P%d", l); dump(hypre_ParAMGDataPArray(d)[l], dir, name, rank); }
+      if (rlx < 0) { continue; }
+      HYPRE_Int n = hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(hypre_ParAMGDataAArray(d)[l]));
+      hypre_Vector **l1 = hypre_ParAMGDataL1Norms(d), **ds = hypre_ParAMGDataChebyDS(d);
+      HYPRE_Real **cf = hypre_ParAMGDataChebyCoefs(d);
+      snprintf(name, sizeof(name), "l1_%d.%d.f64", l, rank);
+      put_f64(dir, name, (l1 && l1[l]) ? hypre_VectorData(l1[l]) : NULL, (l1 && l1[l]) ? n : 0);
+      snprintf(name, sizeof(name), "ds_%d.%d.f64", l, rank);
+      put_f64(dir, name, (ds && ds[l]) ? hypre_VectorData(ds[l]) : NULL, (ds && ds[l]) ? n : 0);
+      if (!rank)
+      {
+         snprintf(name, sizeof(name), "coefs_%d.f64", l);
+         put_f64(dir, name, (cf && cf[l]) ? cf[l] : NULL, (cf && cf[l]) ? hypre_ParAMGDataChebyOrder(d) + 1 : 0);
+      }
+   }
+   if (rlx >= 0)
+   {
+      char name[64];
+      hypre_ParCSRMatrix *Ac = hypre_ParAMGDataAArray(d)[nl - 1];
+      HYPRE_Int N = (HYPRE_Int)hypre_ParCSRMatrixGlobalNumRows(Ac);
+      /* the gathered dense coarse matrix of relax type 9 lives on every rank that owns coarse rows */
+      if (hypre_ParAMGDataGridRelaxType(d)[3] == 9 && hypre_ParAMGDataAMat(d) && hypre_ParCSRMatrixFirstRowIndex(Ac) == 0 &&
+          hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(Ac)) > 0)
+      {
+         put_f64(dir, "dense.f64", hypre_ParAMGDataAMat(d), N * N);
+      }
+      HYPRE_Int nloc = hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag((hypre_ParCSRMatrix *)A));
+      snprintf(name, sizeof(name), "b.%d.f64", rank);
+      put_f64(dir, name, hypre_VectorData(hypre_ParVectorLocalVector((hypre_ParVector *)b)), nloc);
+      snprintf(name, sizeof(name), "x.%d.f64", rank);
+      put_f64(dir, name, hypre_VectorData(hypre_ParVectorLocalVector((hypre_ParVector *)x)), nloc);
+      if (!rank)
+      {
+         hypre_PCGData *pd = (hypre_PCGData *)pcg;
+         put_f64(dir, "norms.f64", pd->norms, iters + 1);
+         put_f64(dir, "rel_norms.f64", pd->rel_norms, iters + 1);
+         char path[1024];
+         snprintf(path, sizeof(path), "%s/meta.txt", dir);
+         FILE *f = fopen(path, "w");
+         fprintf(f, "levels %d\niterations %d\nfinal_rel %.15e\n", nl, iters, pd->rel_residual_norm);
+         fprintf(f, "relax_type %d %d %d %d\n", hypre_ParAMGDataGridRelaxType(d)[0], hypre_ParAMGDataGridRelaxType(d)[1],
+                 hypre_ParAMGDataGridRelaxType(d)[2], hypre_ParAMGDataGridRelaxType(d)[3]);
+         fprintf(f, "num_sweeps %d %d %d %d\n", hypre_ParAMGDataNumGridSweeps(d)[0], hypre_ParAMGDataNumGridSweeps(d)[1],
+                 hypre_ParAMGDataNumGridSweeps(d)[2], hypre_ParAMGDataNumGridSweeps(d)[3]);
+         fprintf(f, "cycle_type %d\nfcycle %d\ncheby_order %d\ncheby_scale %d\n", hypre_ParAMGDataCycleType(d),
+                 hypre_ParAMGDataFCycle(d), hypre_ParAMGDataChebyOrder(d), hypre_ParAMGDataChebyScale(d));
+         fprintf(f, "relax_weight");
+         for (int l = 0; l < nl; l++) { fprintf(f, " %.17g", hypre_ParAMGDataRelaxWeight(d)[l]); }
+         fprintf(f, "\n");
+         fclose(f);
+      }
+      HYPRE_ParCSRPCGDestroy(pcg);
    }
    if (!rank) { printf("DUMP_OK levels %d ranks %d\n", nl, size); }
    HYPRE_BoomerAMGDestroy(amg);

@@ -126,6 +126,39 @@ class OracleAMG:
             dense = np.ascontiguousarray(dense)
             L.orc_amg_set_coarse_dense(self.h, dense.shape[0], p(dense))
 
+    @classmethod
+    def from_arrays(cls, levels, relax_type, num_sweeps, cycle_type, fcycle, cheby_order, cheby_scale, dense):
+        """orc_amg from plain arrays: levels = [dict(A=csr, P=csr|None, l1=, ds=, coefs=, weight=)], e.g. a
+        hierarchy gathered from N ranks of the reference (tests/test_oracle_multirank.py)"""
+        self = cls.__new__(cls)
+        L = lib()
+        self.keep, self.n = [], []
+        nl = len(levels)
+        self.h = C.c_void_p(L.orc_amg_create(nl))
+        for l, lv in enumerate(levels):
+            Ai, Aj, Aa = csr_arrays(lv["A"])
+            n = lv["A"].shape[0]
+            self.n.append(n)
+            if lv.get("P") is not None:
+                Pi, Pj, Pa = csr_arrays(lv["P"]); nc = lv["P"].shape[1]
+            else:
+                Pi = Pj = Pa = None; nc = 0
+            f64 = lambda a: None if a is None or len(a) == 0 else np.ascontiguousarray(a, dtype=np.float64)  # noqa: E731
+            l1, ds, coefs = f64(lv.get("l1")), f64(lv.get("ds")), f64(lv.get("coefs"))
+            self.keep.append((Ai, Aj, Aa, Pi, Pj, Pa, l1, ds, coefs))
+            L.orc_amg_set_level(self.h, l, n, p(Ai), p(Aj), p(Aa), nc, p(Pi), p(Pj), p(Pa), p(l1), p(ds), p(coefs),
+                                float(lv.get("weight", 1.0)))
+        rt = np.array(relax_type, dtype=np.int32)
+        if rt[3] == 19:
+            rt[3] = 9
+        ns = np.array(num_sweeps, dtype=np.int32)
+        L.orc_amg_set_cycle(self.h, p(rt), p(ns), int(cycle_type), int(fcycle), int(cheby_order), int(cheby_scale))
+        if dense is not None:
+            dense = np.ascontiguousarray(dense, dtype=np.float64)
+            self.keep.append(dense)
+            L.orc_amg_set_coarse_dense(self.h, dense.shape[0], p(dense))
+        return self
+
     def set_level_blocks(self, level, starts):
         """N-rank row partition of a level (two-stage GS uses the rank-local strict lower triangle)"""
         st = np.ascontiguousarray(starts, dtype=np.int32)
