@@ -162,7 +162,6 @@ extern "C" int b200_amg_set_coarse_dense(b200_amg *a, int n_global, const double
                                          const int *rows_per_rank_h)
 {
    ARG_CHECK(a != nullptr && n_global >= 0);
-   ARG_CHECK(n_global == 0 || A_mat_h != nullptr);
    b200_ctx *c = a->ctx;
    a->coarse_n = n_global; a->coarse_first_row = first_row;
    a->coarse_rows_per_rank.assign(c->nranks, 0);
@@ -171,14 +170,20 @@ extern "C" int b200_amg_set_coarse_dense(b200_amg *a, int n_global, const double
    else { b200_set_error("rows_per_rank required for nranks > 1"); return B200_ERR_ARG; }
    cudaFree(a->d_Ainv); cudaFree(a->d_fall); a->d_Ainv = nullptr; a->d_fall = nullptr;
    if (n_global == 0) { return B200_OK; }
-   std::vector<double> inv;
-   if (invert_like_gselim(n_global, A_mat_h, &inv) != 0)
-   {
-      b200_set_error("coarse matrix is singular (hypre_gselim error)");
-      return B200_ERR_NUMERIC;
-   }
    const int n_local = a->coarse_rows_per_rank[c->rank];
-   B200_TRY(dev_upload(&a->d_Ainv, inv.data() + (size_t)first_row * n_global, (size_t)n_local * n_global));
+   // a rank without coarse rows holds no matrix (the reference gathers it on the owners only,
+   // par_gauss_elim.c:60-200); it still takes part in the sum of the right-hand side
+   ARG_CHECK(n_local == 0 || A_mat_h != nullptr);
+   if (n_local > 0)
+   {
+      std::vector<double> inv;
+      if (invert_like_gselim(n_global, A_mat_h, &inv) != 0)
+      {
+         b200_set_error("coarse matrix is singular (hypre_gselim error)");
+         return B200_ERR_NUMERIC;
+      }
+      B200_TRY(dev_upload(&a->d_Ainv, inv.data() + (size_t)first_row * n_global, (size_t)n_local * n_global));
+   }
    CUDA_TRY(cudaMalloc((void **)&a->d_fall, sizeof(double) * (size_t)n_global));
    return B200_OK;
 }

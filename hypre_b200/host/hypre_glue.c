@@ -47,6 +47,10 @@ int  hypre_b200_get_enabled(void) { return g_enabled; }
  * single-rank hypre objects; process `g_rank` mirrors rows [first_row, first_row + n_local)
  * of every level on its GPU (hypre's 1-D row partition) and the solve runs over NCCL. */
 static int g_rank = 0, g_nranks = 1;
+/* native mode: this library was compiled against an MPI build of hypre (HYPRE_SEQUENTIAL undefined) and
+ * the application runs on N ranks, one per GPU: hypre's objects ARE distributed -- every rank mirrors
+ * what it owns, with the communication packages hypre negotiated (section 2 of INTEGRATION.md). */
+static int g_native = 0;
 
 typedef struct mirror_s {
    void            *key;      /* hypre_ParAMGData* or hypre_ParCSRMatrix* */
@@ -67,6 +71,35 @@ static int verbose(void)
 
 static b200_ctx *glue_ctx(void)
 {
+#ifndef HYPRE_SEQUENTIAL
+   if (!g_ctx)
+   {
+      /* first use is collective (a solve): rank 0 creates the NCCL id, hypre's own MPI layer carries it */
+      HYPRE_Int np = 1, id = 0;
+      hypre_MPI_Comm_size(hypre_MPI_COMM_WORLD, &np);
+      hypre_MPI_Comm_rank(hypre_MPI_COMM_WORLD, &id);
+      if (np > 1)
+      {
+         char uid[128];
+         const char *e = getenv("HYPRE_B200_DEVICE");
+         int dev = e ? atoi(e) : (getenv("LOCAL_RANK") ? atoi(getenv("LOCAL_RANK")) : (int) id);
+         memset(uid, 0, sizeof(uid));
+         if (id == 0 && b200_nccl_unique_id(uid) != B200_OK)
+         {
+            fprintf(stderr, "hypre_b200: cannot create the NCCL id: %s\n", b200_last_error());
+         }
+         hypre_MPI_Bcast(uid, 128, hypre_MPI_BYTE, 0, hypre_MPI_COMM_WORLD);
+         if (b200_ctx_create_dist(dev, (int) id, (int) np, uid, &g_ctx) != B200_OK)
+         {
+            fprintf(stderr, "hypre_b200: rank %d cannot create the distributed context: %s\n", (int) id, b200_last_error());
+            g_ctx = NULL;
+            return NULL;
+         }
+         g_rank = (int) id; g_nranks = (int) np; g_native = 1;
+         return g_ctx;
+      }
+   }
+#endif
    if (!g_ctx)
    {
       int dev = 0;
@@ -260,7 +293,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    }
    if (relax_type[3] == 19) { relax_type[3] = 9; }
 
-   if (g_nranks > 1)
+   if (g_nranks > 1 && !g_native)
    {
       /* Row partition of every level.  Level 0: hypre's even split.  Level l+1 inherits the
        * partition of level l: coarse point c belongs to the rank that owns its fine point
@@ -306,7 +339,13 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    for (l = 0; l < nl; l++)
    {
       b200_parcsr *dA, *dP;
-      if (g_nranks > 1 && l >= repl)
+      if (g_native)
+      {
+         /* hypre's own distributed objects: what this rank owns, with the CommPkg hypre negotiated */
+         dA = upload_parcsr(A_array[l]);
+         dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+      }
+      else if (g_nranks > 1 && l >= repl)
       {
          /* replicated level: the whole single-rank matrices */
          dA = upload_parcsr(A_array[l]);
@@ -363,7 +402,18 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       int status;
       if (!hypre_ParAMGDataGSSetup(amg_data)) { hypre_GaussElimSetup(amg_data, nl - 1, grt[3]); }
       hypre_MPI_Comm_size(hypre_ParCSRMatrixComm(Ac), &np);
-      if (starts)
+      if (g_native)
+      {
+         /* rows of the coarsest level per WORLD rank (hypre's comm_info is indexed by the ranks of the
+          * sub-communicator of owners, par_gauss_elim.c:60-100); ranks without coarse rows hold no A_mat */
+         HYPRE_Int mine = hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(Ac));
+         HYPRE_Int *rows = (HYPRE_Int *) calloc((size_t) g_nranks, sizeof(HYPRE_Int));
+         hypre_MPI_Allgather(&mine, 1, HYPRE_MPI_INT, rows, 1, HYPRE_MPI_INT, hypre_ParCSRMatrixComm(Ac));
+         status = b200_amg_set_coarse_dense(amg, N, mine > 0 ? hypre_ParAMGDataAMat(amg_data) : NULL,
+                                            (int) hypre_ParCSRMatrixFirstRowIndex(Ac), rows);
+         free(rows);
+      }
+      else if (starts)
       {
          int *rows = (int *) calloc((size_t) g_nranks, sizeof(int)), r;
          for (r = 0; r < g_nranks; r++) { rows[r] = repl < nl ? (int) N : STARTS(nl - 1)[r + 1] - STARTS(nl - 1)[r]; }
@@ -444,7 +494,7 @@ static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
       m->key = amg_data; m->amg = amg;
       m->starts = starts; m->repl_level = repl; m->num_levels = (int) hypre_ParAMGDataNumLevels(amg_data);
       b200_amg_level_matrix(amg, 0, &m->A);
-      if (g_nranks > 1)
+      if (g_nranks > 1 && !g_native)
       {
          int *st = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
          even_starts((int) hypre_ParCSRMatrixGlobalNumRows(hypre_ParAMGDataAArray(amg_data)[0]), g_nranks, st);
@@ -463,7 +513,7 @@ static mirror_t *mirror_for_matrix(hypre_ParCSRMatrix *A)
    {
       b200_parcsr *dA = NULL;
       int first_row = 0, first_col = 0;
-      if (glue_ctx() && g_nranks > 1)
+      if (glue_ctx() && g_nranks > 1 && !g_native)
       {
          int *rs = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
          int *cs = (int *) calloc((size_t) g_nranks + 1, sizeof(int));

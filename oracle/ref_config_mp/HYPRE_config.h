@@ -6,7 +6,7 @@
  * own configure step would generate (template: src/config/HYPRE_config.h.in)
  * for a `--with-MPI --with-openmp` host-only build, the MPI being oracle/mpishim
  * (mpi.h there; N processes on one machine).  Used for ONE thing: reproducing the
- * reference's multi-rank goldens (src/test/TEST_ij/*.saved) with oracle/_ref/ij_ref_mp.
+ * reference's multi-rank goldens (src/test/TEST_ij, .saved files) with oracle/_ref/ij_ref_mp.
  *   - HYPRE_HAVE_MPI        : hypre_MPI_* call MPI_* (src/utilities/mpistubs.c:919-1530)
  *   - HYPRE_USING_OPENMP    : OpenMP row loops (src/seq_mv/csr_matvec.c:673-848)
  *   - HYPRE_USING_HOST_MEMORY: every object lives in host memory
