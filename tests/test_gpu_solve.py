@@ -383,3 +383,41 @@ def test_multi_gpu_pcg_matches_single_rank_oracle(built):
            "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests", "dist_gpu_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=1200)
     assert r.returncode == 0 and "DIST_GPU_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def _gpu_count():
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=60).stdout
+        return len([ln for ln in out.splitlines() if ln.startswith("GPU ")])
+    except Exception:
+        return 0
+
+
+@pytest.mark.parametrize("args", ["-n 40 40 40 -P 2 1 1 -solver 1 -rlx 18", "-n 40 40 40 -P 2 1 1 -solver 1 -rlx 16",
+                                  "-27pt -n 24 24 24 -P 1 2 1 -solver 1 -rlx 11"])
+def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
+    """The reference's unchanged src/test/ij.c on 2 ranks, hypre's own DISTRIBUTED host setup (MPI build of the
+    reference over oracle/mpishim), solve on 2 GPUs (hypre_b200/lib/ij_b200_mp) -- against the same command on
+    the reference's CPU path (oracle/_ref/ij_ref_mp): identical iteration count, final residual to 1e-6
+    relative (the printed digits).  Measured in round 1 (profiles/r01_ij_b200_mp_2gpu_*.log): 13 iterations /
+    3.629277e-09 and 8 / 6.133724e-10, both identical to the reference."""
+    from hypre_b200 import ROOT
+    shim = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
+    ij_mp = os.path.join(ROOT, "hypre_b200", "lib", "ij_b200_mp")
+    ij_ref = os.path.join(ROOT, "oracle", "_ref", "ij_ref_mp")
+    if not all(os.path.exists(f) for f in (shim, ij_mp, ij_ref)):
+        pytest.skip("multi-rank builds absent")
+    if _gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+
+    def run(binary):
+        r = subprocess.run([shim, "-np", "2", binary] + args.split(), capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        it = int(re.search(r"^Iterations = (\d+)", r.stdout, re.M).group(1))
+        fin = float(re.search(r"Final Relative Residual Norm = (\S+)", r.stdout).group(1))
+        return it, fin
+    it_d, fin_d = run(ij_mp)
+    it_r, fin_r = run(ij_ref)
+    assert it_d == it_r, (it_d, it_r)
+    assert abs(fin_d - fin_r) <= 2e-6 * fin_r, (fin_d, fin_r)
