@@ -3,9 +3,10 @@
  * A small message-passing library with the MPI-1/2 subset the reference calls through its
  * hypre_MPI_* wrappers (src/utilities/mpistubs.c:919-1530), so that the reference's host code can
  * run on N ranks (N processes on one machine) on boxes that have no MPI installation.  It exists
- * for ONE purpose: reproducing the reference's multi-rank golden results (src/test/TEST_ij/
- * *.saved, all recorded with mpirun -np 2..4) with the reference library compiled by
- * oracle/Makefile.  Ranks are processes started by oracle/_ref/mpirun_shim, connected pairwise
+ * to reproduce the reference's multi-rank golden results (src/test/TEST_ij, the .saved files, all
+ * recorded with mpirun -np 2..4) with the reference library compiled by oracle/Makefile, and to
+ * host the ranks of the multi-GPU demonstration of the binding (hypre_b200/lib/ij_b200_mp; with a
+ * real MPI installation that binary links the real library instead).  Ranks are processes started by oracle/_ref/mpirun_shim, connected pairwise
  * by Unix stream sockets; sends are buffered (eager), receives match on (communicator, source,
  * tag) in arrival order, collectives are linear algorithms over point-to-point messages with a
  * fixed combination order (rank 0, 1, 2, ...), hence deterministic.
