@@ -6,13 +6,14 @@
  * to reproduce the reference's multi-rank golden results (src/test/TEST_ij, the .saved files, all
  * recorded with mpirun -np 2..4) with the reference library compiled by oracle/Makefile, and to
  * host the ranks of the multi-GPU demonstration of the binding (hypre_b200/lib/ij_b200_mp; with a
- * real MPI installation that binary links the real library instead).  Ranks are processes started by oracle/_ref/mpirun_shim, connected pairwise
- * by Unix stream sockets; sends are buffered (eager), receives match on (communicator, source,
- * tag) in arrival order, collectives are linear algorithms over point-to-point messages with a
- * fixed combination order (rank 0, 1, 2, ...), hence deterministic.
+ * real MPI installation that binary links the real library instead).
+ * Ranks are processes started by oracle/_ref/mpirun_shim, connected pairwise by Unix stream
+ * sockets; sends are buffered (eager), receives match on (communicator, source, tag) in arrival
+ * order, collectives are linear algorithms over point-to-point messages with a fixed
+ * combination order (rank 0, 1, 2, ...), hence deterministic.
  *
- * Not a general MPI: derived datatypes other than contiguous, one-sided operations, I/O,
- * topologies, inter-communicators and threads are not provided (calls abort with a message).
+ * Not a general MPI: one-sided operations, I/O, topologies, inter-communicators, error handlers
+ * and threads are not provided.
  */
 #ifndef ORACLE_MPISHIM_MPI_H
 #define ORACLE_MPISHIM_MPI_H
