@@ -101,3 +101,23 @@ def test_unsupported_pcg_options_are_rejected_loudly(H):
     pcg.Solve(A, b, x)
     assert H.error_flag() & 1
     H.clear_errors()
+
+
+def test_multirank_binding_fails_loudly_without_gpu(built):
+    """native multi-rank mode (ij_b200_mp over oracle/mpishim): without a device every rank reports the
+    failure and the solve does not silently run on the CPU (0 iterations, hypre error raised)"""
+    if has_gpu():
+        pytest.skip("GPU present")
+    from hypre_b200 import ROOT
+    shim = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
+    ij_mp = os.path.join(ROOT, "hypre_b200", "lib", "ij_b200_mp")
+    if not (os.path.exists(shim) and os.path.exists(ij_mp)):
+        pytest.skip("multi-rank builds absent")
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run([shim, "-np", "2", ij_mp, "-n", "12", "12", "12", "-P", "2", "1", "1", "-solver", "1", "-rlx", "18"],
+                       capture_output=True, text=True, timeout=120, env=env)
+    err = r.stderr
+    assert err.count("cannot create the distributed context") == 2, err[-800:]
+    assert "no CPU fallback" in err
+    assert "hierarchy upload failed" in err
+    assert "Iterations = 0" in r.stdout
