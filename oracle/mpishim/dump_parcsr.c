@@ -8,7 +8,7 @@
  * and checks that hypre_b200's communication-free restatement (hypre_b200/csrc/partition.cu,
  * b200_rowpart_create) produces, rank by rank, exactly the same blocks and the same plan.
  *
- *    mpirun_shim -np N dump_parcsr <7|27> nx ny nz P Q R outdir [relax_type [rhsrand]]
+ *    mpirun_shim -np N dump_parcsr <7|27> nx ny nz P Q R outdir [relax_type [rhsrand [cycle_type [num_sweeps [agg_levels]]]]]
  *
  * With a relax type the program also does what `ij -solver 1 -rlx <type> [-rhsrand]` does -- BoomerAMG with
  * the driver's defaults (src/test/ij.c:248-302) as preconditioner of PCG, tol 1e-8 -- and writes what a
@@ -85,6 +85,7 @@ int main(int argc, char **argv)
    int P = atoi(argv[5]), Q = atoi(argv[6]), R = atoi(argv[7]);
    const char *dir = argv[8];
    int rlx = argc > 9 ? atoi(argv[9]) : -1, rhsrand = argc > 10 ? atoi(argv[10]) : 0;
+   int cycle_type = argc > 11 ? atoi(argv[11]) : 1, sweeps = argc > 12 ? atoi(argv[12]) : 1, agg = argc > 13 ? atoi(argv[13]) : 0;
    if (P * Q * R != size) { if (!rank) { fprintf(stderr, "P*Q*R != ranks\n"); } MPI_Abort(MPI_COMM_WORLD, 2); }
    /* rank -> box coordinates as src/test/ij.c BuildParLaplacian does */
    int p = rank % P, q = ((rank - p) / P) % Q, r = (rank - p - P * q) / (P * Q);
@@ -132,9 +133,10 @@ int main(int argc, char **argv)
    HYPRE_BoomerAMGSetStrongThreshold(amg, 0.25);
    HYPRE_BoomerAMGSetMaxLevels(amg, 25);
    HYPRE_BoomerAMGSetMeasureType(amg, 0);
-   HYPRE_BoomerAMGSetNumSweeps(amg, 1);
+   HYPRE_BoomerAMGSetNumSweeps(amg, sweeps);
+   HYPRE_BoomerAMGSetCycleType(amg, cycle_type);
    HYPRE_BoomerAMGSetTruncFactor(amg, 0.0);
-   HYPRE_BoomerAMGSetAggNumLevels(amg, 0);
+   HYPRE_BoomerAMGSetAggNumLevels(amg, agg);
    HYPRE_BoomerAMGSetPrintLevel(amg, 0);
    HYPRE_BoomerAMGSetChebyOrder(amg, 2);
    HYPRE_BoomerAMGSetChebyEigEst(amg, 10);

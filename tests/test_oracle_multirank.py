@@ -22,15 +22,20 @@ pytestmark = pytest.mark.skipif(not HAVE_MP, reason="oracle/_ref multi-rank buil
 
 NORM_TOL = 1e-9
 
-# (points, n, P, relax, rhsrand, golden (iterations, final) from TEST_ij/smoother.saved or None)
+# (points, n, P, relax, rhsrand, golden (iterations, final) from TEST_ij/smoother.saved or None,
+#  extra driver arguments: cycle_type (2 = W), num_sweeps, aggressive-coarsening levels)
 CONFIGS = [
-    (7, (20, 20, 10), (2, 2, 1), 16, 1, (6, 2.510130e-09)),     # smoother.jobs:72  -> smoother.out.12
-    (7, (40, 40, 20), (2, 2, 1), 16, 0, (7, 7.310897e-09)),     # smoother.jobs:102 -> smoother.out.22
-    (7, (20, 20, 10), (2, 2, 1), 18, 1, None),
-    (7, (15, 30, 10), (1, 3, 1), 18, 1, None),
-    (27, (12, 12, 12), (2, 1, 2), 11, 0, None),
-    (27, (12, 12, 12), (2, 2, 2), 12, 1, None),
-    (7, (24, 24, 24), (2, 2, 2), 7, 0, None),
+    (7, (20, 20, 10), (2, 2, 1), 16, 1, (6, 2.510130e-09), ()),     # smoother.jobs:72  -> smoother.out.12
+    (7, (40, 40, 20), (2, 2, 1), 16, 0, (7, 7.310897e-09), ()),     # smoother.jobs:102 -> smoother.out.22
+    (7, (20, 20, 10), (2, 2, 1), 18, 1, None, ()),
+    (7, (15, 30, 10), (1, 3, 1), 18, 1, None, ()),
+    (27, (12, 12, 12), (2, 1, 2), 11, 0, None, ()),
+    (27, (12, 12, 12), (2, 2, 2), 12, 1, None, ()),
+    (7, (24, 24, 24), (2, 2, 2), 7, 0, None, ()),
+    (7, (20, 20, 20), (2, 2, 1), 18, 1, None, (2, 1, 0)),           # W-cycle
+    (27, (14, 14, 14), (1, 2, 2), 16, 0, None, (1, 2, 0)),          # two sweeps
+    (7, (24, 24, 12), (2, 2, 1), 18, 1, None, (1, 1, 1)),           # one level of aggressive coarsening
+    (7, (20, 20, 20), (3, 1, 1), 11, 1, None, (2, 2, 0)),           # W-cycle, two sweeps, two-stage GS, 3 ranks
 ]
 
 
@@ -38,13 +43,13 @@ def f64(path):
     return np.fromfile(path, dtype=np.float64)
 
 
-@pytest.mark.parametrize("pts,n,P,rlx,rhsrand,golden", CONFIGS)
-def test_oracle_repeats_the_multirank_reference_solve(tmp_path, pts, n, P, rlx, rhsrand, golden):
+@pytest.mark.parametrize("pts,n,P,rlx,rhsrand,golden,extra", CONFIGS)
+def test_oracle_repeats_the_multirank_reference_solve(tmp_path, pts, n, P, rlx, rhsrand, golden, extra):
     nranks = P[0] * P[1] * P[2]
     d = str(tmp_path)
     env = dict(os.environ, OMP_NUM_THREADS="1")
     p = subprocess.run([os.path.join(REF_BIN, "mpirun_shim"), "-np", str(nranks), os.path.join(REF_BIN, "dump_parcsr"),
-                        str(pts)] + [str(v) for v in n + P] + [d, str(rlx), str(rhsrand)],
+                        str(pts)] + [str(v) for v in n + P] + [d, str(rlx), str(rhsrand)] + [str(v) for v in extra],
                        capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0 and "DUMP_OK" in p.stdout, p.stderr[-500:]
     meta = {ln.split()[0]: ln.split()[1:] for ln in open(os.path.join(d, "meta.txt"))}
