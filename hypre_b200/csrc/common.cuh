@@ -159,6 +159,7 @@ struct DMat {
    double         *c_dict = nullptr;     // distinct values
    int             n_dict = 0;
    long long       stored_bytes = 0;     // bytes one pass over the block reads from the matrix arrays
+   int             zpad = 0;             // compressed storage without CFMT_PAD lanes (padding = valid column x value 0)
 };
 
 // cfmt: value encoding of the compressed storage (column indices are always base + u16)
@@ -180,6 +181,7 @@ struct MatView {
    const int       *c_base;
    const void      *c_code;
    const double    *c_dict;
+   int              n_dict;      // entries of c_dict (<= 256 for CFMT_VAL8)
 };
 
 static inline MatView view_of(const DMat &m)
@@ -187,7 +189,7 @@ static inline MatView view_of(const DMat &m)
    MatView v;
    v.n_rows = m.n_rows; v.rp = m.rp; v.ci = m.ci; v.va = m.va;
    v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va; v.perm = m.sl_perm;
-   v.c_idx = m.c_idx; v.c_base = m.c_base; v.c_code = m.c_code; v.c_dict = m.c_dict;
+   v.c_idx = m.c_idx; v.c_base = m.c_base; v.c_code = m.c_code; v.c_dict = m.c_dict; v.n_dict = m.n_dict;
    return v;
 }
 
@@ -255,6 +257,7 @@ struct PackedDMat {
    int layout = 0, lanes = 4, n_slices = 0, max_row = 0, cfmt = CFMT_NONE;
    double avg_row = 0.0;
    long long padded = 0, stored_bytes = 0, n_esc = 0;
+   int zpad = 0;
    std::vector<long long>      sl_off;      // [n_slices+1]
    std::vector<int>            sci;         // entry-major 32-bit columns (plain layout; escape groups)
    std::vector<double>         sva;         // entry-major fp64 values (plain layout; CFMT_VAL64)

@@ -69,7 +69,7 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    m->max_row = P.max_row; m->avg_row = P.avg_row;
    m->layout = P.layout; m->lanes = P.lanes;
    if (P.layout == 0) { return B200_OK; }
-   m->n_slices = P.n_slices; m->sell_entries = P.padded; m->stored_bytes = P.stored_bytes;
+   m->n_slices = P.n_slices; m->sell_entries = P.padded; m->stored_bytes = P.stored_bytes; m->zpad = P.zpad;
    m->cfmt = P.cfmt; m->n_dict = (int)P.dict.size();
    B200_TRY(dev_upload(&m->sl_off, P.sl_off.data(), P.sl_off.size()));
    B200_TRY(dev_upload(&m->sl_ci, P.sci.data(), P.sci.size()));

@@ -17,12 +17,12 @@ static int g_lanes_override  = -1;
 // compressed thread-per-row storage: -1 automatic (default; B200_COMPRESS=0 in the environment turns it
 // off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it
 static int g_compress = []() { const char *e = getenv("B200_COMPRESS"); return e ? atoi(e) : -1; }();
-int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 3 ? v : 0; }();
+int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 5 ? v : 0; }();
 
 extern "C" int b200_set_compression(int mode, int pipeline)
 {
    ARG_CHECK(mode >= -1 && mode <= CFMT_VAL64);
-   ARG_CHECK(pipeline >= -1 && pipeline <= 3);
+   ARG_CHECK(pipeline >= -1 && pipeline <= 5);
    g_compress = mode;
    if (pipeline >= 0) { g_sellc_pipe = pipeline; }
    return B200_OK;
@@ -169,13 +169,17 @@ void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
    // chunks of 4 entries, and keep it only if a pass over the block then reads fewer bytes
    ValueDict vd;
    int cfmt = CFMT_NONE;
+   bool zpad = false;
    std::vector<long long> sl_off = off_orig;
    if (g_compress != 0)
    {
       cfmt = CFMT_VAL64;
-      if (g_compress != CFMT_VAL64 && vd.build(h.a, g_compress == CFMT_VAL8 ? 256 : 65536))
+      // loop variant 5 (rowsum_sellc_z) has no padding marker: padding lanes gather a valid column and
+      // multiply it by a dictionary entry 0.0 (as the plain sliced-ELL layout does); one code is kept for it
+      zpad = (g_sellc_pipe == 5);
+      if (g_compress != CFMT_VAL64 && vd.build(h.a, (g_compress == CFMT_VAL8 ? 256 : 65536) - (size_t)zpad))
       {
-         cfmt = (vd.dict.size() <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
+         cfmt = (vd.dict.size() + (size_t)zpad <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
       }
       std::vector<long long> off4((size_t)n_slices + 1, 0);
       for (int sidx = 0; sidx < n_slices; sidx++)
@@ -242,8 +246,25 @@ void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
    const size_t n_groups = (size_t)(padded / 32);
    const size_t csz = cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 0;
    P->base.assign(n_groups, 0);
-   P->idx.assign((size_t)padded, CFMT_PAD);
-   P->code.assign((size_t)padded * csz, 0);
+   int zero_code = 0;
+   if (csz && zpad)
+   {
+      zero_code = vd.dict.empty() ? -1 : vd.code(0.0);
+      if (zero_code < 0) { zero_code = (int)vd.dict.size(); vd.dict.push_back(0.0); }    // codes of h.a are assigned already
+   }
+   P->zpad = zpad;
+   P->idx.assign((size_t)padded, zpad ? (unsigned short)0 : CFMT_PAD);
+   if (csz == 1) { P->code.assign((size_t)padded, (unsigned char)zero_code); }
+   else
+   {
+      P->code.assign((size_t)padded * csz, 0);
+      if (csz == 2 && zero_code != 0)
+      {
+         const unsigned short z16 = (unsigned short)zero_code;
+#pragma omp parallel for schedule(static)
+         for (long long p = 0; p < padded; p++) { memcpy(&P->code[(size_t)p * 2], &z16, 2); }
+      }
+   }
    if (csz && vd.dict.empty()) { vd.dict.push_back(0.0); }
    long long n_esc = 0;
 #pragma omp parallel for schedule(static) reduction(+ : n_esc)
@@ -261,13 +282,39 @@ void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
       {
          int lo = INT_MAX, hi = INT_MIN;
          for (int l = 0; l < 32; l++) { if (k < len[l]) { const int c = h.j[beg[l] + k]; lo = std::min(lo, c); hi = std::max(hi, c); } }
-         if (lo > hi) { continue; }                              // nothing live: base 0, all lanes CFMT_PAD
+         int padcol[32];
+         if (zpad)
+         {
+            // a padding lane multiplies 0.0 with x at one of ITS OWN row's columns (so that nothing a row does
+            // not reference can reach it): the one that widens [lo, hi] least.  Rows without entries take lo.
+            for (int l = 0; l < 32; l++)
+            {
+               padcol[l] = -1;
+               if (k < len[l] || len[l] == 0) { continue; }
+               long long best = LLONG_MAX;
+               for (int q = 0; q < len[l]; q++)
+               {
+                  const int c = h.j[beg[l] + q];
+                  const long long span = lo > hi ? 0 : (long long)std::max(hi, c) - (long long)std::min(lo, c);
+                  if (span < best) { best = span; padcol[l] = c; }
+               }
+               lo = std::min(lo, padcol[l]); hi = std::max(hi, padcol[l]);
+            }
+         }
+         if (lo > hi) { continue; }                    // nothing live: base 0, all lanes CFMT_PAD (or offset 0 x 0.0)
          const bool esc = (long long)hi - (long long)lo > 65534;
          P->base[(size_t)(off / 32) + (size_t)k] = esc ? CFMT_ESC : lo;
          n_esc += esc;
          for (int l = 0; l < 32; l++)
          {
-            if (k >= len[l]) { continue; }
+            if (k >= len[l])
+            {
+               if (zpad && !esc && padcol[l] >= 0)
+               {
+                  P->idx[(size_t)off + (size_t)(k >> 2) * 128 + (size_t)l * 4 + (size_t)(k & 3)] = (unsigned short)(padcol[l] - lo);
+               }
+               continue;
+            }
             const size_t p = (size_t)off + (size_t)(k >> 2) * 128 + (size_t)l * 4 + (size_t)(k & 3);
             P->idx[p] = esc ? (unsigned short)0 : (unsigned short)(h.j[beg[l] + k] - lo);
             if (csz)
@@ -312,6 +359,7 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
          int row = slice * 32 + lane;
          if (!P.perm.empty()) { row = (slice >> 3) * 256 + P.perm[(size_t)row]; }
          double t = 0.0;
+         bool stray = false;      // a row beyond n_rows multiplied a non-zero value
          if (P.cfmt == CFMT_NONE)
          {
             const int width = (int)(span >> 5);
@@ -321,6 +369,7 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
                const int c = P.sci[p];
                if (c < 0 || c >= h.n_cols) { b200_set_error("packed column out of range"); return B200_ERR_ARG; }
                t = fma(P.sva[p], x[c], t);
+               stray |= (row >= n && P.sva[p] != 0.0);
             }
          }
          else
@@ -349,11 +398,12 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
                   else if (P.cfmt == CFMT_VAL16) { unsigned short c16; memcpy(&c16, &P.code[p * 2], 2); v = P.dict[c16]; }
                   else                           { v = P.sva[e]; }
                   t = fma(v, x[col], t);
+                  stray |= (row >= n && v != 0.0);
                }
             }
          }
          if (row < n) { y[row] = t; }
-         else if (t != 0.0) { b200_set_error("padding lane carries entries"); return B200_ERR_ARG; }
+         else if (stray) { b200_set_error("padding lane carries entries"); return B200_ERR_ARG; }
       }
    }
    return B200_OK;

@@ -222,6 +222,105 @@ __device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, 
    return t;
 }
 
+// Round-2 candidate (loop variant 4, CFMT_VAL8 only; opt-in through B200_SELLC_PIPE=4 /
+// b200_set_compression(.., 4)): the dictionary (<= 256 doubles) is staged in shared memory once per block
+// and the escape test is one branch per chunk.  At 32 registers ptxas then issues the four gathers of a
+// chunk back to back (one L2 round trip per chunk instead of four, scripts/sass_probe/README.md) and
+// predicates the DFMAs.  Same products, same order.
+template <class XF>
+__device__ __forceinline__ double rowsum_sellc_sd(const MatView &D, long long off, int n_chunks, int lane,
+                                                  const double *__restrict__ x, const XF &xf,
+                                                  const double *s_dict)
+{
+   const unsigned short *ip = D.c_idx + off + lane * 4;
+   const unsigned char *cp = (const unsigned char *)D.c_code + off + lane * 4;
+   const int4 *bp = reinterpret_cast<const int4 *>(D.c_base + (off >> 5));
+   double t = 0.0;
+   for (int c = 0; c < n_chunks; c++)
+   {
+      const unsigned long long id = ld_stream_u64(ip + c * 128);
+      const unsigned code = ld_stream_u32(cp + c * 128);
+      const int4 b4 = __ldg(bp + c);
+      int col[4] = { b4.x + (int)((unsigned)id & 0xFFFFu), b4.y + (int)((unsigned)(id >> 16) & 0xFFFFu),
+                     b4.z + (int)((unsigned)(id >> 32) & 0xFFFFu), b4.w + (int)(unsigned)(id >> 48) };
+      if ((b4.x | b4.y | b4.z | b4.w) < 0)       // CFMT_ESC has the sign bit: some entry keeps 32-bit columns
+      {
+         const int *e = D.sl_ci + off + (c * 4) * 32 + lane;
+         if (b4.x < 0) { col[0] = ld_stream(e); }
+         if (b4.y < 0) { col[1] = ld_stream(e + 32); }
+         if (b4.z < 0) { col[2] = ld_stream(e + 64); }
+         if (b4.w < 0) { col[3] = ld_stream(e + 96); }
+      }
+      double xv[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         const bool live = ((unsigned)(id >> (16 * j)) & 0xFFFFu) != CFMT_PAD;
+         xv[j] = live ? xf.xval(x, col[j]) : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         const bool live = ((unsigned)(id >> (16 * j)) & 0xFFFFu) != CFMT_PAD;
+         const double v = s_dict[(code >> (8 * j)) & 0xFFu];
+         if (live) { t = fma(v, xv[j], t); }
+      }
+   }
+   return t;
+}
+
+// Round-2 candidate (loop variant 5; needs storage packed without CFMT_PAD lanes, DMat::zpad, i.e.
+// b200_set_compression(.., 5) BEFORE the upload): no predicate anywhere in the chunk.  Padding lanes gather
+// a valid column and multiply it by a dictionary entry 0.0 -- what rowsum_sell does in the plain layout --
+// so a chunk is 3 stream loads, 4 gathers, 4 dictionary reads (shared memory for u8 codes) and 4 DFMAs:
+// about half the instructions of rowsum_sellc, whose issue slots are 55 % busy
+// (profiles/r01_ncu_full_rows_kernel_compressed.txt).  Row sums equal rowsum_sellc's except that a sum of
+// exactly -0.0 becomes +0.0 and a non-finite x in the padded column reaches the row.
+template <int VF, class XF>
+__device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off, int n_chunks, int lane,
+                                                 const double *__restrict__ x, const XF &xf,
+                                                 const double *s_dict)
+{
+   const unsigned short *ip = D.c_idx + off + lane * 4;
+   const int4 *bp = reinterpret_cast<const int4 *>(D.c_base + (off >> 5));
+   double t = 0.0;
+#pragma unroll 1        // unrolled by two it spills at 32 registers
+   for (int c = 0; c < n_chunks; c++)
+   {
+      const unsigned long long id = ld_stream_u64(ip + c * 128);
+      unsigned long long code = 0;
+      if (VF == CFMT_VAL8)  { code = ld_stream_u32((const unsigned char *)D.c_code + off + c * 128 + lane * 4); }
+      if (VF == CFMT_VAL16) { code = ld_stream_u64((const unsigned short *)D.c_code + off + c * 128 + lane * 4); }
+      const int4 b4 = __ldg(bp + c);
+      double v[4], xv[4];
+      if (VF == CFMT_VAL64)
+      {
+#pragma unroll
+         for (int j = 0; j < 4; j++) { v[j] = ld_stream(D.sl_va + off + (c * 4 + j) * 32 + lane); }
+      }
+      int col[4] = { b4.x + (int)((unsigned)id & 0xFFFFu), b4.y + (int)((unsigned)(id >> 16) & 0xFFFFu),
+                     b4.z + (int)((unsigned)(id >> 32) & 0xFFFFu), b4.w + (int)(unsigned)(id >> 48) };
+      if ((b4.x | b4.y | b4.z | b4.w) < 0)       // CFMT_ESC has the sign bit: some entry keeps 32-bit columns
+      {
+         const int *e = D.sl_ci + off + (c * 4) * 32 + lane;
+         if (b4.x < 0) { col[0] = ld_stream(e); }
+         if (b4.y < 0) { col[1] = ld_stream(e + 32); }
+         if (b4.z < 0) { col[2] = ld_stream(e + 64); }
+         if (b4.w < 0) { col[3] = ld_stream(e + 96); }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { xv[j] = xf.xval(x, col[j]); }
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         if (VF == CFMT_VAL8)  { v[j] = s_dict[(unsigned)(code >> (8 * j)) & 0xFFu]; }
+         if (VF == CFMT_VAL16) { v[j] = __ldg(D.c_dict + ((unsigned)(code >> (16 * j)) & 0xFFFFu)); }
+         t = fma(v[j], xv[j], t);
+      }
+   }
+   return t;
+}
+
 // CG: gather x with ld.global.cg (L2 only) -- for ghost vectors that a peer GPU wrote during this
 // kernel's lifetime, which must not be served from a stale L1 / read-only cache line
 template <bool CG>
@@ -358,15 +457,20 @@ __device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const
 template <int T, int HALO, class Epi>
 __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
                                            const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
-                                           int vblock)
+                                           int vblock, const double *s_dict = nullptr)
 {
    // vblock: the block's position in this range's grid stride (a permutation of blockIdx.x), so that
    // short ranges do not all land on the low-numbered blocks, which also carry the put phase
    if (T <= 0)
    {
       constexpr int VF   = T < 0 ? ((-T) & 3) : CFMT_VAL64;   // T = -(CFMT_* + 4 PIPE): compressed storage
-      // 0 plain, 1 slice offsets one trip ahead, 2 + L2 prefetch, 3 = 2 at 40 registers / 6 blocks per SM
-      constexpr int PIPE = T < 0 ? ((-T) >> 2) : 0;
+      // 0 plain, 1 slice offsets one trip ahead, 2 + L2 prefetch, 3 = 2 at 40 registers / 6 blocks per SM,
+      // 4 = plain loop with the dictionary in shared memory (rowsum_sellc_sd)
+      constexpr int PIPE_RAW = T < 0 ? ((-T) >> 2) : 0;
+      // 5 = predicate-free loop on storage without padding markers (rowsum_sellc_z)
+      constexpr bool SMEM_DICT = PIPE_RAW == 4;
+      constexpr bool ZPAD = PIPE_RAW == 5;
+      constexpr int PIPE = (SMEM_DICT || ZPAD) ? 0 : PIPE_RAW;
       const int lane = threadIdx.x & 31;
       const int wpb = ROWK_BLOCK / 32;
       const int stride = gridDim.x * wpb;
@@ -391,7 +495,9 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          const bool live = row < D.n_rows;
          if (PIPE >= 2 && live) { epi.prefetch(row); }     // the epilogue's own vectors: in L2 by the time the row sum is done
          double t = (T == 0) ? rowsum_sell(D, slice, lane, x, epi)
-                             : rowsum_sellc<VF, PIPE>(D, off, nch, lane, x, epi, off_n, nch_n);
+                    : SMEM_DICT ? rowsum_sellc_sd(D, off, nch, lane, x, epi, s_dict)
+                    : ZPAD ? rowsum_sellc_z<VF>(D, off, nch, lane, x, epi, s_dict)
+                                : rowsum_sellc<VF, PIPE>(D, off, nch, lane, x, epi, off_n, nch_n);
          off = off_n; nch = nch_n;
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
@@ -452,7 +558,7 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
 // All rows of the diag block.  8 resident blocks per SM (32 registers): occupancy is what hides the
 // DRAM latency of this streaming kernel.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK, (T <= -12) ? 6 : 8)
+__global__ void __launch_bounds__(ROWK_BLOCK, (T <= -12 && T > -16) ? 6 : 8)
 rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
@@ -461,9 +567,16 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
 
    constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
+   constexpr bool SMEM_DICT = (T == -(CFMT_VAL8 + 16) || T == -(CFMT_VAL8 + 20));
+   __shared__ double s_dict[SMEM_DICT ? 256 : 1];
+   if (SMEM_DICT)
+   {
+      if ((int)threadIdx.x < D.n_dict) { s_dict[threadIdx.x] = D.c_dict[threadIdx.x]; }
+      __syncthreads();
+   }
    const int n_groups = (D.n_rows + 31) >> 5;
    const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
-   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x); }
+   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, s_dict); }
    else
    {
       if (h.ch.n_out > 0)
@@ -475,9 +588,9 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
       // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
       const int G = gridDim.x, b = blockIdx.x;
-      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G);
+      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, s_dict);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, s_dict);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, s_dict);
    }
    grid_reduce<Epi::NRED>(red, rc);
    if (P2P && h.ch.n_in > 0 && !(h.dbg & 4)) { p2p_consumer_done(h.ch); }

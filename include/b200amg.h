@@ -108,7 +108,10 @@ int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stor
 /* mode: -1 automatic (default; environment B200_COMPRESS=0 disables), 0 off, 1/2/3 force that value
  * format where the dictionary allows it (tests/bench).  pipeline: 0 plain loop (default, fastest measured),
  * 1 slice offsets loaded one trip ahead, 2 additionally L2 prefetch of the next slice's streams, 3 = 2 at
- * 6 blocks per SM; -1 leaves it (environment B200_SELLC_PIPE). */
+ * 6 blocks per SM, 4 = plain loop with the value dictionary staged in shared memory (u8 codes only; a
+ * round-2 candidate, see scripts/sass_probe/), 5 = predicate-free loop: set BEFORE the upload, the block is then
+ * packed without padding markers (padding = valid column x dictionary entry 0.0, as in the plain sliced-ELL
+ * layout); -1 leaves it (environment B200_SELLC_PIPE). */
 int b200_set_compression(int mode, int pipeline);
 /* Test hook for the storage formats (host only, no device needed, never on a solve path): packs the CSR
  * block with the current layout / compression settings exactly as b200_parcsr_create would and computes

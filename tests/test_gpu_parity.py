@@ -186,8 +186,15 @@ def _compression_matrices(H, hier):
     yield "random_u8", Cm, 1
 
 
+# loop variants 4 (dictionary in shared memory) and 5 (storage without padding markers) are round-2 candidates:
+# opt-in (B200_TEST_CANDIDATES=1) until they have been through a GPU run of this file
+_CANDIDATES = pytest.mark.skipif(os.environ.get("B200_TEST_CANDIDATES", "0") != "1",
+                                 reason="candidate kernels: set B200_TEST_CANDIDATES=1")
+_CAND = [pytest.param(m, p, marks=_CANDIDATES) for m, p in [(-1, 4), (1, 4), (-1, 5), (1, 5), (2, 5), (3, 5)]]
+
+
 @pytest.mark.parametrize("layout", [1, 2])
-@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (0, 0), (1, 2), (2, 2), (2, 0), (3, 2), (3, 1), (3, 3)])
+@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (0, 0), (1, 2), (2, 2), (2, 0), (3, 2), (3, 1), (3, 3)] + _CAND)
 def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
     """16-bit column offsets + value dictionary (b200_parcsr_storage): same products, same order as
     the CSR row of the reference (seq_mv/csr_matvec.c:21-857) -> SpMV parity <= 1e-12 in every format."""
@@ -230,7 +237,7 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
         L.b200_set_compression(-1, 0)
 
 
-@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (3, 2), (2, 3)])
+@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (3, 2), (2, 3)] + _CAND)
 def test_smoothers_on_compressed_storage(H, ctx, hier, mode, pipe):
     """every fused epilogue on the compressed thread-per-row kernels against the oracle"""
     L = capi.lib()

@@ -13,7 +13,7 @@ import scipy.sparse as sp
 from hypre_b200 import capi
 
 
-def decode(A, x, layout, mode):
+def decode(A, x, layout, mode, pipeline=0):
     L = capi.lib()
     A = sp.csr_matrix(A)
     n, m = A.shape
@@ -24,13 +24,13 @@ def decode(A, x, layout, mode):
     lay, fmt = C.c_int(), C.c_int()
     stored, nesc = C.c_longlong(), C.c_longlong()
     capi.check(L.b200_set_layout_override(layout, -1))
-    capi.check(L.b200_set_compression(mode, -1))
+    capi.check(L.b200_set_compression(mode, pipeline))
     try:
         capi.check(L.b200_storage_decode_host(n, m, capi.ptr(ai), capi.ptr(aj), capi.ptr(aa), capi.ptr(x), capi.ptr(y),
                                               C.byref(lay), C.byref(fmt), C.byref(stored), C.byref(nesc)))
     finally:
         L.b200_set_layout_override(-1, -1)
-        L.b200_set_compression(-1, -1)
+        L.b200_set_compression(-1, 0)
     return y, lay.value, fmt.value, stored.value, nesc.value
 
 
@@ -111,6 +111,54 @@ def test_padding_lanes_do_not_touch_other_columns():
         for mode in (0, -1, 2, 3):
             y = decode(A, x, layout, mode)[0]
             assert np.all(np.isfinite(y)), (layout, mode)
+
+
+@pytest.mark.parametrize("name,A", list(matrices()))
+def test_storage_without_padding_markers(name, A):
+    """loop variant 5 (b200_set_compression(mode, 5) before the upload): padding lanes are (own column) x (a
+    dictionary entry 0.0) instead of a marker.  Same row sums (a sum of -0.0 may become +0.0, which
+    array_equal does not see), one more dictionary entry at most, and a NaN in a column a row does not
+    reference still cannot reach that row."""
+    rng = np.random.default_rng(5)
+    A = sp.csr_matrix(A)
+    x = rng.standard_normal(A.shape[1])
+    y_csr = decode(A, x, 0, 0)[0]
+    lens = np.diff(A.indptr)
+    for layout in (1, 2):
+        for mode in (-1, 1, 2, 3):
+            y, lay, fmt, stored, nesc = decode(A, x, layout, mode, pipeline=5)
+            y0, _, fmt0, stored0, nesc0 = decode(A, x, layout, mode, pipeline=0)
+            assert lay == layout and np.array_equal(y, y_csr), (name, layout, mode, fmt)
+            assert nesc >= nesc0 and stored >= stored0
+            if nesc == nesc0 and fmt == fmt0:
+                assert stored == stored0                 # same arrays, only their padding differs
+            # poison one column, rows that do not reference it (and have entries) stay finite
+            col = int(A.indices[len(A.indices) // 2]) if A.nnz else 0
+            xp = x.copy(); xp[col] = np.nan
+            yp = decode(A, xp, layout, mode, pipeline=5)[0]
+            touched = np.zeros(A.shape[0], dtype=bool)
+            touched[np.repeat(np.arange(A.shape[0]), lens)[A.indices == col]] = True
+            assert np.all(np.isnan(yp[touched]))
+            assert np.all(np.isfinite(yp[~touched & (lens > 0)])), (name, layout, mode)
+
+
+def test_no_marker_storage_keeps_the_u8_dictionary_within_256_codes():
+    """255 distinct values + the padding zero still fit u8 codes; 256 distinct values move to u16"""
+    rng = np.random.default_rng(9)
+    n = 600
+    for distinct, want in ((255, 1), (256, 2)):
+        vals = np.arange(1, distinct + 1, dtype=np.float64)
+        rows = np.repeat(np.arange(n), 3); cols = (rows * 7 + np.tile(np.arange(3), n) * 11) % n
+        keep = rng.random(rows.size) < 0.8                       # ragged: padding lanes exist
+        keep[:distinct] = True
+        data = np.resize(vals, rows.size)
+        A = sp.csr_matrix((data[keep], (rows[keep], cols[keep])), shape=(n, n)); A.sum_duplicates()
+        assert len(np.unique(A.data)) >= distinct or distinct == 256
+        x = rng.standard_normal(n)
+        y, lay, fmt, _, _ = decode(A, x, 1, -1, pipeline=5)
+        assert np.array_equal(y, decode(A, x, 0, 0)[0])
+        if len(np.unique(A.data)) == distinct:
+            assert fmt == want
 
 
 def test_automatic_choice_keeps_small_blocks_in_csr_and_compresses_large_stencils():
