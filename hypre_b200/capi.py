@@ -104,6 +104,7 @@ def lib():
         "b200_amg_cycle": (i, [vp, vp, vp, i]),
         "b200_amg_cycle_bytes": (i, [vp, c_dbl_p]),
         "b200_amg_cycle_bytes_stored": (i, [vp, c_dbl_p]),
+        "b200_cycle_sweep_counts": (i, [i, i, i, vp, vp]),
         "b200_amg_level_matrix": (i, [vp, i, c_void_pp]),
         "b200_amg_level_interp": (i, [vp, i, c_void_pp]),
         "b200_amg_level_info": (i, [vp, i, c_int_p, C.POINTER(ll), C.POINTER(ll)]),

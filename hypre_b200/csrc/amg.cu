@@ -520,3 +520,42 @@ static int cycle_bytes(const b200_amg *a, bool stored, double *bytes)
 
 extern "C" int b200_amg_cycle_bytes(const b200_amg *a, double *bytes) { return cycle_bytes(a, false, bytes); }
 extern "C" int b200_amg_cycle_bytes_stored(const b200_amg *a, double *bytes) { return cycle_bytes(a, true, bytes); }
+
+// Relaxation sweeps per level in ONE cycle: a dry run of the level-counter state machine of amg_cycle_core
+// (hypre_BoomerAMGCycle, par_cycle.c:200-300, 640-780) that launches nothing.  The binding needs it for the
+// "cycle complexity" line hypre_BoomerAMGSolve prints (par_amg_solve.c:338-395: sum over the sweeps of the
+// nonzeros of their level / nonzeros of level 0; par_cycle.c:417-430).  Pure host arithmetic.
+extern "C" int b200_cycle_sweep_counts(int num_levels, int cycle_type, int fcycle, const int *num_sweeps,
+                                       long long *sweeps_per_level)
+{
+   ARG_CHECK(num_levels >= 1 && cycle_type >= 1 && num_sweeps != nullptr && sweeps_per_level != nullptr);
+   const int nl = num_levels;
+   for (int l = 0; l < nl; l++) { sweeps_per_level[l] = 0; }
+   std::vector<int> lev_counter(nl);
+   lev_counter[0] = 1;
+   for (int k = 1; k < nl; k++) { lev_counter[k] = fcycle ? 1 : cycle_type; }
+   int fcycle_lev = nl - 2, level = 0, cycle_param = 1;
+   for (;;)
+   {
+      sweeps_per_level[level] += nl > 1 ? num_sweeps[cycle_param] : num_sweeps[0];
+      --lev_counter[level];
+      if (lev_counter[level] >= 0 && level != nl - 1)
+      {
+         ++level;
+         lev_counter[level] = lev_counter[level] > cycle_type ? lev_counter[level] : cycle_type;
+         cycle_param = (level == nl - 1) ? 3 : 1;
+      }
+      else if (level != 0)
+      {
+         --level;
+         cycle_param = 2;
+         if (fcycle && fcycle_lev == level)
+         {
+            lev_counter[level] = lev_counter[level] > 1 ? lev_counter[level] : 1;
+            fcycle_lev--;
+         }
+      }
+      else { break; }
+   }
+   return B200_OK;
+}

@@ -6,6 +6,7 @@
  * include/b200amg.h, and routes the solve-phase entry points to the device:
  *
  *   hypre_PCGSolve               (src/krylov/pcg.c:317)            -> b200_pcg_solve_host
+ *   hypre_BoomerAMGSolve         (src/parcsr_ls/par_amg_solve.c:21) -> b200_amg_solve
  *   HYPRE_ParCSRMatrixMatvec     (src/parcsr_mv/HYPRE_parcsr_matrix.c) -> b200_parcsr_matvec_host
  *   hypre_BoomerAMGSetup/Destroy (mirror invalidation)
  *
@@ -650,6 +651,189 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
    pcg->num_iterations = res.num_iterations;
    pcg->rel_residual_norm = res.rel_residual_norm;
    hypre_ParVectorAllZeros(px) = 0;
+   return hypre_error_flag;
+}
+
+/* The closing statistics of hypre_BoomerAMGSolve (src/parcsr_ls/par_amg_solve.c:338-416) and its residual
+ * table (:257-264, :327-331) from the history the device solve returned.  hist[k] = ||r_k||_2, k = 0..cycles;
+ * rhs_norm = ||f||_2 (0 when it vanishes).  Host arithmetic and printing only; also reachable from the tests
+ * (hypre_b200_amg_report) so that the text can be compared with the reference's without a GPU. */
+static void amg_solve_report(hypre_ParAMGData *amg_data, hypre_ParCSRMatrix *A, int cycles, const double *hist,
+                             double rhs_norm, int not_converged, int table)
+{
+   const HYPRE_Int nl = hypre_ParAMGDataNumLevels(amg_data);
+   hypre_ParCSRMatrix **A_array = hypre_ParAMGDataAArray(amg_data);
+   HYPRE_Int *ngs = hypre_ParAMGDataNumGridSweeps(amg_data);
+   int sweeps_in[4], k, l;
+   long long *sweeps = (long long *) calloc((size_t) nl, sizeof(long long));
+   double vars = 0.0, coeffs = 0.0, ops = 0.0, vars0, coeffs0, factor = 1.0;
+
+   if (table)
+   {
+      for (k = 1; k <= cycles; k++)
+      {
+         const double f = hist[k - 1] != 0.0 ? hist[k] / hist[k - 1] : hist[k];
+         hypre_printf("    Cycle %2d   %e    %f     %e \n", k, hist[k], f, rhs_norm != 0.0 ? hist[k] / rhs_norm : hist[k]);
+      }
+   }
+   for (k = 0; k < 4; k++) { sweeps_in[k] = (int) ngs[k]; }
+   b200_cycle_sweep_counts((int) nl, (int) hypre_ParAMGDataCycleType(amg_data), (int) hypre_ParAMGDataFCycle(amg_data),
+                           sweeps_in, sweeps);
+   vars0 = (double) hypre_ParCSRMatrixGlobalNumRows(A);
+   coeffs0 = (double) hypre_ParCSRMatrixDNumNonzeros(A);
+   for (l = 0; l < nl; l++)
+   {
+      /* statistics use the integer count on the coarse levels, the cycle count the double one (as the reference) */
+      vars   += l == 0 ? vars0 : (double) hypre_ParCSRMatrixGlobalNumRows(A_array[l]);
+      coeffs += l == 0 ? coeffs0 : (double) hypre_ParCSRMatrixNumNonzeros(A_array[l]);
+      ops    += (double) sweeps[l] * (double) hypre_ParCSRMatrixDNumNonzeros(A_array[l]);
+   }
+   free(sweeps);
+   if (cycles > 0 && hist[0] != 0.0) { factor = pow(hist[cycles] / hist[0], 1.0 / (double) cycles); }
+   if (not_converged)
+   {
+      hypre_printf("\n\n==============================================");
+      hypre_printf("\n NOTE: Convergence tolerance was not achieved\n");
+      hypre_printf("      within the allowed %d V-cycles\n", (int) hypre_ParAMGDataMaxIter(amg_data));
+      hypre_printf("==============================================");
+   }
+   hypre_printf("\n\n Average Convergence Factor = %f", factor);
+   hypre_printf("\n\n     Complexity:    grid = %f\n", vars0 != 0.0 ? vars / vars0 : 0.0);
+   hypre_printf("                operator = %f\n", coeffs0 != 0.0 ? coeffs / coeffs0 : 0.0);
+   hypre_printf("                   cycle = %f\n\n\n\n", coeffs0 != 0.0 ? ops / coeffs0 : 0.0);
+}
+
+/* test hook: print the table and the statistics for a given history (CPU test of the text) */
+void hypre_b200_amg_report(void *amg_vdata, int cycles, const double *hist, double rhs_norm, int not_converged)
+{
+   hypre_ParAMGData *amg_data = (hypre_ParAMGData *) amg_vdata;
+   amg_solve_report(amg_data, hypre_ParAMGDataAArray(amg_data)[0], cycles, hist, rhs_norm, not_converged, 1);
+   fflush(stdout);
+}
+
+/* hypre_BoomerAMGSolve (src/parcsr_ls/par_amg_solve.c:21-424): the stand-alone AMG iteration of `ij -solver 0`,
+ * and the preconditioner call of every Krylov solver of the reference that is not interposed here (GMRES,
+ * BiCGSTAB, ...: one device cycle per application, vectors copied in and out). */
+HYPRE_Int hypre_BoomerAMGSolve(void *amg_vdata, hypre_ParCSRMatrix *A, hypre_ParVector *f, hypre_ParVector *u)
+{
+   static amg_setup_fn next = NULL;      /* same signature */
+   hypre_ParAMGData *amg_data = (hypre_ParAMGData *) amg_vdata;
+   mirror_t *m;
+   b200_ctx *ctx;
+   double *db = NULL, *dx = NULL, *hist = NULL, *fh, *uh;
+   double tol, rel = 1.0, rhs_norm = 0.0;
+   HYPRE_Int my_id = 0, print_level, logging, min_iter, max_iter;
+   int n_local = 0, cycles = 0, status, track;
+
+   if (!next) { next = (amg_setup_fn) next_sym("hypre_BoomerAMGSolve"); }
+   if (!g_enabled) { return next(amg_vdata, A, f, u); }
+
+   print_level = hypre_ParAMGDataPrintLevel(amg_data);
+   logging     = hypre_ParAMGDataLogging(amg_data);
+   tol         = hypre_ParAMGDataTol(amg_data);
+   min_iter    = hypre_ParAMGDataMinIter(amg_data);
+   max_iter    = hypre_ParAMGDataMaxIter(amg_data);
+   if (hypre_ParVectorNumVectors(f) != hypre_ParVectorNumVectors(u))
+   {
+      hypre_error_w_msg(HYPRE_ERROR_GENERIC, "Error: num_vectors for RHS and LHS do not match!\n");
+      return hypre_error_flag;
+   }
+   if (hypre_ParVectorNumVectors(f) > 1 || hypre_ParAMGDataConvergeType(amg_data) != 0 || logging > 1)
+   {
+      GLUE_FAIL("BoomerAMG solve option outside the device path (multivector / converge_type / logging > 1)");
+      return hypre_error_flag;
+   }
+   if (hypre_ParAMGDataAArray(amg_data) == NULL || hypre_ParAMGDataAArray(amg_data)[0] != A)
+   {
+      GLUE_FAIL("BoomerAMG was not set up for this matrix");
+      return hypre_error_flag;
+   }
+   m = mirror_for_amg(amg_data);
+   if (!m) { GLUE_FAIL("hierarchy upload failed"); return hypre_error_flag; }
+   ctx = glue_ctx();
+   if (g_nranks > 1 && !g_native && tol <= 0.0 && max_iter == 1)
+   {
+      /* processes holding replicated hypre objects each get their slice of u back: fine for a solve, useless
+       * to a host Krylov solver that wants the whole preconditioned vector */
+      GLUE_FAIL("BoomerAMG as preconditioner of a host Krylov solver needs the native multi-rank mode");
+      return hypre_error_flag;
+   }
+   hypre_MPI_Comm_rank(hypre_ParCSRMatrixComm(A), &my_id);
+   if (g_rank != 0) { my_id = 1; }                    /* replicated processes: only process 0 prints */
+
+   if (b200_parcsr_info(m->A, &n_local, NULL, NULL, NULL, NULL) != B200_OK)
+   {
+      GLUE_FAIL("device AMG solve failed"); return hypre_error_flag;
+   }
+   /* this rank's slice of the host vectors (offset 0 unless the processes hold replicated objects) */
+   fh = hypre_VectorData(hypre_ParVectorLocalVector(f)) + m->first_row;
+   uh = hypre_VectorData(hypre_ParVectorLocalVector(u)) + m->first_row;
+   track = (print_level > 1 || tol > 0.0);
+   if (track) { hist = (double *) calloc((size_t) (max_iter > 0 ? max_iter : 0) + 2, sizeof(double)); }
+   status = b200_dev_alloc(ctx, n_local > 0 ? n_local : 1, &db);
+   if (status == B200_OK) { status = b200_dev_alloc(ctx, n_local > 0 ? n_local : 1, &dx); }
+   if (status == B200_OK && n_local > 0) { status = b200_h2d(ctx, db, fh, n_local); }
+   if (status == B200_OK && n_local > 0) { status = b200_h2d(ctx, dx, uh, n_local); }
+
+   if (status == B200_OK && my_id == 0 && print_level > 1)
+   {
+      hypre_BoomerAMGWriteSolverParams(amg_data);
+      if (tol > 0.0) { hypre_printf("\n\nAMG SOLUTION INFO:\n"); }
+   }
+   if (status == B200_OK)
+   {
+      status = b200_amg_solve(m->amg, db, dx, tol, (int) min_iter, (int) max_iter, &cycles, &rel, hist);
+   }
+   if (status == B200_ERR_NUMERIC)
+   {
+      if (print_level > 0)
+      {
+         hypre_printf("\n\nERROR detected by Hypre ...  BEGIN\n");
+         hypre_printf("ERROR -- hypre_BoomerAMGSolve: INFs and/or NaNs detected in input.\n");
+         hypre_printf("User probably placed non-numerics in supplied A, x_0, or b.\n");
+         hypre_printf("ERROR detected by Hypre ...  END\n\n\n");
+      }
+      hypre_error(HYPRE_ERROR_GENERIC);
+   }
+   else if (status == B200_OK && n_local > 0) { status = b200_d2h(ctx, uh, dx, n_local); }
+   if (db) { b200_dev_free(ctx, db); }
+   if (dx) { b200_dev_free(ctx, dx); }
+   if (status != B200_OK)
+   {
+      if (status != B200_ERR_NUMERIC) { GLUE_FAIL("device AMG solve failed"); }
+      free(hist);
+      return hypre_error_flag;
+   }
+
+   hypre_ParAMGDataNumIterations(amg_data) = cycles;
+   if (track) { hypre_ParAMGDataRelativeResidualNorm(amg_data) = rel; }
+   hypre_ParVectorAllZeros(u) = 0;
+   if (cycles == max_iter && tol > 0.0) { hypre_error(HYPRE_ERROR_CONV); }
+
+   if (track)
+   {
+      /* ||f|| from the last residual and its relative value (rel = ||r|| / ||f||, or ||r|| when f == 0) */
+      if (rel != 0.0 && hist[cycles] != rel) { rhs_norm = hist[cycles] / rel; }
+      if (tol <= 0.0 && rhs_norm != 0.0)
+      {
+         /* the reference skips the first residual when no tolerance is set and reports ||f|| instead
+          * (par_amg_solve.c:176-192) */
+         hist[0] = rhs_norm;
+      }
+   }
+   if (my_id == 0 && print_level > 1)
+   {
+      hypre_printf("                                            relative\n");
+      hypre_printf("               residual        factor       residual\n");
+      hypre_printf("               --------        ------       --------\n");
+      hypre_printf("    Initial    %e                 %e\n", hist[0], rhs_norm != 0.0 ? hist[0] / rhs_norm : hist[0]);
+      amg_solve_report(amg_data, A, cycles, hist, rhs_norm, cycles == max_iter && tol > 0.0, 1);
+   }
+   if (verbose() && my_id == 0)
+   {
+      fprintf(stderr, "hypre_b200: BoomerAMG solve on the device: %d cycles, relative residual %.6e\n", cycles, rel);
+   }
+   free(hist);
    return hypre_error_flag;
 }
 

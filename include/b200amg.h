@@ -226,6 +226,11 @@ int b200_amg_level_matrix(const b200_amg *amg, int level, b200_parcsr **A);
 int b200_amg_level_interp(const b200_amg *amg, int level, b200_parcsr **P);
 int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *nnz_A,
                         long long *nnz_P);
+/* relaxation sweeps per level of one cycle (host arithmetic, no device): what hypre_BoomerAMGCycle adds up
+ * into the "cycle complexity" hypre_BoomerAMGSolve prints (src/parcsr_ls/par_cycle.c:417-430,
+ * par_amg_solve.c:338-395).  num_sweeps[4] as in b200_amg_create; sweeps_per_level has num_levels entries. */
+int b200_cycle_sweep_counts(int num_levels, int cycle_type, int fcycle, const int *num_sweeps,
+                            long long *sweeps_per_level);
 /* stand-alone AMG iteration (ij -solver 0): hypre_BoomerAMGSolve
  * (src/parcsr_ls/par_amg_solve.c:21-424) with converge_type 0. */
 int b200_amg_solve(b200_amg *amg, const double *b, double *x, double tol, int min_iter,

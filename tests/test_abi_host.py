@@ -57,6 +57,36 @@ def test_no_cpu_fallback_without_gpu(H):
     H.clear_errors()
 
 
+def test_standalone_amg_has_no_cpu_fallback_either(H):
+    """HYPRE_BoomerAMGSolve (ij -solver 0) is interposed too: without a GPU it raises the error flag and
+    leaves x alone; with the device path switched off (test hook) the same call reaches the reference"""
+    if has_gpu():
+        pytest.skip("GPU present")
+    A = H.laplacian(8, 8, 8)
+    b = A.vector(1.0); x = A.vector(0.0)
+    amg = H.BoomerAMG(relax_type=18, as_precond=False)
+    amg.SetTol(1e-8); amg.SetMaxIter(20)
+    H.set_device_path(False)
+    try:
+        amg.Setup(A, b, x)
+    finally:
+        H.set_device_path(True)
+    H.clear_errors()
+    amg.Solve(A, b, x)
+    assert H.error_flag() & 1 and not np.any(x.numpy())
+    H.clear_errors()
+    H.set_device_path(False)
+    try:
+        amg.Solve(A, b, x)
+    finally:
+        H.set_device_path(True)
+    assert H.error_flag() == 0 and np.any(x.numpy())
+    it = C.c_int()
+    H.lib().HYPRE_BoomerAMGGetNumIterations(amg.h, C.byref(it))
+    assert 3 < it.value < 20
+    amg.destroy(); A.destroy()
+
+
 def test_ij_driver_links_against_the_binding(built):
     """the reference's unchanged ij.c resolves hypre_PCGSolve to the interposer"""
     if not os.path.exists(IJ_B200):
