@@ -125,12 +125,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def build_problem(H, name, nscale=None):
+def build_problem(H, name, nscale=None, grid=None, weak=False):
     gen, dims, rlx, cmd = WORKLOADS[name]
     if nscale:
         dims = tuple(nscale for _ in dims)
         cmd = cmd + " [scaled to n=%d]" % nscale
-    A = getattr(H, gen)(*dims)
+    if grid and weak:                    # --native --weak: the named grid is the PER-GPU problem
+        dims = tuple(d * g for d, g in zip(dims, grid))
+        cmd = cmd + " [per GPU; global -n %d %d %d]" % dims
+    if grid:
+        cmd = cmd + " -P %d %d %d" % grid
+    A = getattr(H, gen)(*dims, grid=grid) if grid else getattr(H, gen)(*dims)
     b = A.vector(1.0)
     x = A.vector(0.0)
     amg = H.BoomerAMG(relax_type=rlx)
@@ -230,14 +235,20 @@ def run_b200(args, rank, world):
     from hypre_b200 import capi, hypre as H
     L = capi.lib()
     HL = H.lib()
-    if world > 1:
+    native = bool(args.native and world > 1)
+    if native:
+        # hypre's own distributed setup on `world` ranks (MPI build of the reference over oracle/mpishim, ranks
+        # met through SHIM_DIR in main()); the binding bootstraps NCCL through hypre's MPI layer at first use
+        assert H.NATIVE and H.world() == (rank, world), (H.NATIVE, H.world(), rank, world)
+    elif world > 1:
         uid = C.create_string_buffer(128)
         if rank == 0:
             capi.check(L.b200_nccl_unique_id(uid))
         uid = C.create_string_buffer(R.bcast_bytes(uid.raw), 128)
         if HL.hypre_b200_init_dist(R.local, rank, world, uid) != 0:
             raise capi.B200Error("hypre_b200_init_dist failed: " + L.b200_last_error().decode())
-    P = build_problem(H, args.workload, args.n)
+    P = build_problem(H, args.workload, args.n, H.process_grid(world) if native else None, args.weak)
+    P["native"], P["weak"] = native, bool(native and args.weak)
     A, b, x, amg, pcg = P["A"], P["b"], P["x"], P["amg"], P["pcg"]
     n_global = A.global_rows
     ctx = C.c_void_p(HL.hypre_b200_context())
@@ -257,7 +268,7 @@ def run_b200(args, rank, world):
     capi.check(L.b200_parcsr_info(dA, C.byref(nrows), None, C.byref(nnz0), C.byref(layout), C.byref(lanes)))
     nnz0 = nnz0.value
     n = nrows.value                                        # this rank's rows (== n_global for N = 1)
-    first = HL.hypre_b200_first_row(amg.h) if world > 1 else 0
+    first = HL.hypre_b200_first_row(amg.h) if world > 1 and not native else 0   # native: vectors are local already
 
     # ---------------- value: device-resident solve, CUDA events on the library's stream
     db = capi.DeviceVector(ctx, n, b.numpy()[first:first + n])
@@ -431,9 +442,14 @@ def finish_multi(args, R, P, m):
         out = {
             "metric": "AMG-PCG solve DOF*iterations/s", "value": m["value"], "unit": "DOF*it/s", "n_gpus": R.world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * m["dev_s"] / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak" if P.get("weak") else "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
             "config": {"workload": P["cmd"], "dof": m["n_global"], "iterations_per_step": m["iters"],
-                       "levels": m["levels"], "partition": "1-D row blocks, %d ranks, halo = %s" % (
+                       "levels": m["levels"],
+                       "setup": ("hypre's distributed setup on %d ranks (MPI build over oracle/mpishim)" % R.world)
+                       if P.get("native") else "single-rank host setup replicated on every process",
+                       "partition": "%s, %d ranks, halo = %s" % (
+                           "hypre's box partition and CommPkg" if P.get("native") else "1-D row blocks",
                            R.world, "NCCL send/recv (baseline)" if os.environ.get("B200_HALO") == "nccl"
                            else "peer-memory stores fused into the row kernels (NVLink)"),
                        "l2": "inputs larger than L2 (hierarchy %.1f GB streamed per iteration, all ranks)" % (iter_bytes / 1e9),
@@ -463,10 +479,20 @@ def main():
     ap.add_argument("--n", type=int, default=None, help="override the grid edge (scaled-down smoke runs)")
     ap.add_argument("--ref-iters", type=int, default=3, help="PCG iterations per reference step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--native", action="store_true",
+                    help="N > 1: hypre's own distributed setup on N ranks (native multi-rank mode, INTEGRATION.md 4b) "
+                         "instead of the replicated single-rank setup")
+    ap.add_argument("--weak", action="store_true", help="with --native: the workload's grid is per GPU (weak scaling)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.native and world > 1 and args.impl == "b200":
+        # before hypre_b200.hypre is imported: the MPI build, ranks meeting in a directory named after the job
+        os.environ["HYPRE_B200_NATIVE"] = "1"
+        d = os.environ.setdefault("SHIM_DIR", "/tmp/b200_shim_%s_%s" % (os.environ.get("MASTER_PORT", "0"),
+                                                                        os.environ.get("TORCHELASTIC_RUN_ID", "run")))
+        os.makedirs(d, exist_ok=True)
     if args.impl == "reference":
         run_reference(args, rank)
     else:

@@ -20,10 +20,11 @@ REF_DIR = os.path.join(ORACLE_DIR, "_ref")
 
 LIB_B200 = os.path.join(LIB_DIR, "libb200amg.so")
 LIB_HYPRE_B200 = os.path.join(LIB_DIR, "libHYPRE_b200.so")
+LIB_HYPRE_B200_MP = os.path.join(LIB_DIR, "libHYPRE_b200_mp.so")   # the binding over the MPI build of the reference
 LIB_HYPRE_REF = os.path.join(REF_DIR, "libHYPRE_ref.so")
 LIB_ORACLE = os.path.join(REF_DIR, "liboracle.so")
 IJ_B200 = os.path.join(LIB_DIR, "ij_b200")
 IJ_REF = os.path.join(REF_DIR, "ij_ref")
 
-__all__ = ["ROOT", "LIB_DIR", "LIB_B200", "LIB_HYPRE_B200", "LIB_HYPRE_REF", "LIB_ORACLE",
+__all__ = ["ROOT", "LIB_DIR", "LIB_B200", "LIB_HYPRE_B200", "LIB_HYPRE_B200_MP", "LIB_HYPRE_REF", "LIB_ORACLE",
            "IJ_B200", "IJ_REF"]

@@ -12,10 +12,14 @@ import os
 
 import numpy as np
 
-from . import LIB_HYPRE_B200, capi
+from . import LIB_HYPRE_B200, LIB_HYPRE_B200_MP, capi
 
 _lib = None
-COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h)
+COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h) and of oracle/mpishim
+# Native multi-rank mode: this process is one of N ranks (one per GPU), the
+# reference is its MPI build over oracle/mpishim and hypre's own distributed setup runs.  Ranks started by
+# torchrun meet through SHIM_DIR (oracle/mpishim/mpishim.c); under mpirun_shim nothing else is needed.
+NATIVE = os.environ.get("HYPRE_B200_NATIVE", "0") == "1"
 
 
 def lib():
@@ -23,10 +27,12 @@ def lib():
     if _lib is not None:
         return _lib
     capi.lib()   # libb200amg.so first: fail loudly if the CUDA library is missing
-    if not os.path.exists(LIB_HYPRE_B200):
-        raise capi.B200Error("%s is missing (built from hypre_b200/host with the reference headers)"
-                             % LIB_HYPRE_B200)
-    L = C.CDLL(LIB_HYPRE_B200, mode=C.RTLD_GLOBAL)
+    path = LIB_HYPRE_B200_MP if NATIVE else LIB_HYPRE_B200
+    if not os.path.exists(path):
+        raise capi.B200Error("%s is missing (built from hypre_b200/host with the reference headers)" % path)
+    L = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    if NATIVE:
+        L.MPI_Init(None, None)
     vp, i, d = C.c_void_p, C.c_int, C.c_double
     for name in ("GenerateLaplacian", "GenerateLaplacian27pt", "GenerateRotate7pt", "hb_vector_create",
                  "hb_vector_create_cols", "hb_amg_A", "hb_amg_P", "hb_amg_F", "hb_amg_U", "hb_amg_Vtemp",
@@ -68,6 +74,42 @@ def lib():
     L.HYPRE_Initialize()
     _lib = L
     return L
+
+
+def world():
+    """(rank, size) of hypre's world communicator; (0, 1) outside the native multi-rank mode"""
+    if not NATIVE:
+        return 0, 1
+    r, n = C.c_int(), C.c_int()
+    lib().MPI_Comm_rank(COMM_WORLD, C.byref(r))
+    lib().MPI_Comm_size(COMM_WORLD, C.byref(n))
+    return r.value, n.value
+
+
+def process_grid(size):
+    """P x Q x R with P >= Q >= R, as balanced as the factors of `size` allow (8 -> 2 2 2, 4 -> 2 2 1)"""
+    best = (size, 1, 1)
+    for r in range(1, size + 1):
+        for q in range(r, size + 1):
+            if size % (r * q) == 0 and size // (r * q) >= q:
+                cand = (size // (r * q), q, r)
+                if cand[0] - cand[2] < best[0] - best[2]:
+                    best = cand
+    return best
+
+
+def _grid_args(grid):
+    """(P, Q, R, p, q, r) for the generators: this rank's box of the process grid (ij.c:9620-9626)"""
+    rank, size = world()
+    if size == 1:
+        return 1, 1, 1, 0, 0, 0
+    P, Q, R = grid if grid else (size, 1, 1)
+    if P * Q * R != size:
+        raise ValueError("process grid %s does not match %d ranks" % ((P, Q, R), size))
+    p = rank % P
+    q = ((rank - p) // P) % Q
+    r = (rank - p - P * q) // (P * Q)
+    return P, Q, R, p, q, r
 
 
 def set_device_path(enabled):
@@ -155,23 +197,23 @@ class ParVector:
             self.h = None
 
 
-def laplacian(nx, ny, nz, c=(1.0, 1.0, 1.0)):
+def laplacian(nx, ny, nz, c=(1.0, 1.0, 1.0), grid=None):
     """ij -laplacian -n nx ny nz [-c cx cy cz]   (BuildParLaplacian, src/test/ij.c:9559-9790)."""
     cx, cy, cz = c
     v = np.zeros(4)
     v[1], v[2], v[3] = -cx, -cy, -cz
     v[0] = (2.0 * cx if nx > 1 else 0.0) + (2.0 * cy if ny > 1 else 0.0) + (2.0 * cz if nz > 1 else 0.0)
-    return ParCSRMatrix(lib().GenerateLaplacian(COMM_WORLD, nx, ny, nz, 1, 1, 1, 0, 0, 0, capi.ptr(v)))
+    return ParCSRMatrix(lib().GenerateLaplacian(COMM_WORLD, nx, ny, nz, *_grid_args(grid), capi.ptr(v)))
 
 
-def laplacian_27pt(nx, ny, nz):
+def laplacian_27pt(nx, ny, nz, grid=None):
     """ij -27pt -n nx ny nz   (BuildParLaplacian27pt, src/test/ij.c:10984-10996)."""
     v = np.array([26.0, -1.0])
     if nx == 1 or ny == 1 or nz == 1:
         v[0] = 8.0
     if nx * ny == 1 or nx * nz == 1 or ny * nz == 1:
         v[0] = 2.0
-    return ParCSRMatrix(lib().GenerateLaplacian27pt(COMM_WORLD, nx, ny, nz, 1, 1, 1, 0, 0, 0, capi.ptr(v)))
+    return ParCSRMatrix(lib().GenerateLaplacian27pt(COMM_WORLD, nx, ny, nz, *_grid_args(grid), capi.ptr(v)))
 
 
 def rotate_7pt(nx, ny, alpha, eps):

@@ -1,7 +1,9 @@
 /* oracle/mpishim/mpishim.c -- TEST INFRASTRUCTURE: the message-passing library behind
  * oracle/mpishim/mpi.h (see there for scope).  One process per rank, started by mpirun_shim,
  * which hands every rank one connected Unix stream socket per peer (environment SHIM_RANK,
- * SHIM_SIZE, SHIM_FDS).  Without those variables the library runs as a single rank.
+ * SHIM_SIZE, SHIM_FDS).  Ranks started by something else (torchrun, a job script) meet through
+ * Unix sockets in a directory instead: SHIM_DIR=<dir> with SHIM_RANK/SHIM_SIZE or torchrun's
+ * RANK/WORLD_SIZE.  Without those variables the library runs as a single rank.
  *
  * Progress model: all sockets are non-blocking; every blocking call (Recv, Wait*, Probe, the
  * collectives, Finalize) drives one poll()-based engine that drains incoming bytes into
@@ -19,6 +21,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/socket.h>
+#include <sys/un.h>
 #include <time.h>
 #include <unistd.h>
 
@@ -439,17 +443,90 @@ static int req_inactive(MPI_Request q)
 }
 
 /* ------------------------------------------------------------------ init / finalize */
+static void set_nonblocking(int fd, int peer)
+{
+   int fl = fcntl(fd, F_GETFL, 0);
+   if (fl < 0 || fcntl(fd, F_SETFL, fl | O_NONBLOCK) < 0) { die("fcntl on the socket to rank %d: %s", peer, strerror(errno)); }
+}
+static void full_io(int fd, void *buf, size_t n, int out)
+{
+   char *p = (char *)buf;
+   while (n > 0)
+   {
+      ssize_t k = out ? write(fd, p, n) : read(fd, p, n);
+      if (k < 0 && errno == EINTR) { continue; }
+      if (k <= 0) { die("rendezvous: short %s (%s)", out ? "write" : "read", strerror(errno)); }
+      p += k; n -= (size_t)k;
+   }
+}
+/* Ranks that were not started by mpirun_shim meet in a directory: rank r listens on <dir>/r<r>.sock, connects
+ * to every lower rank (retrying until it is up, <= 120 s) and accepts one connection from every higher rank;
+ * the connecting side sends its rank number.  The result is the same full mesh of stream sockets. */
+static void rendezvous(const char *dir)
+{
+   struct sockaddr_un a;
+   memset(&a, 0, sizeof(a));
+   a.sun_family = AF_UNIX;
+   if (snprintf(a.sun_path, sizeof(a.sun_path), "%s/r%d.sock", dir, g_rank) >= (int)sizeof(a.sun_path)) { die("SHIM_DIR too long"); }
+   int ls = socket(AF_UNIX, SOCK_STREAM, 0);
+   if (ls < 0) { die("socket: %s", strerror(errno)); }
+   unlink(a.sun_path);
+   if (bind(ls, (struct sockaddr *)&a, sizeof(a)) < 0 || listen(ls, g_size) < 0) { die("bind/listen %s: %s", a.sun_path, strerror(errno)); }
+   for (int j = 0; j < g_rank; j++)
+   {
+      struct sockaddr_un b;
+      memset(&b, 0, sizeof(b));
+      b.sun_family = AF_UNIX;
+      snprintf(b.sun_path, sizeof(b.sun_path), "%s/r%d.sock", dir, j);
+      int fd = -1;
+      for (int attempt = 0; attempt < 12000; attempt++)
+      {
+         fd = socket(AF_UNIX, SOCK_STREAM, 0);
+         if (fd < 0) { die("socket: %s", strerror(errno)); }
+         if (connect(fd, (struct sockaddr *)&b, sizeof(b)) == 0) { break; }
+         close(fd); fd = -1;
+         struct timespec ts = { 0, 10 * 1000 * 1000 };
+         nanosleep(&ts, NULL);
+      }
+      if (fd < 0) { die("rendezvous: rank %d did not appear in %s", j, dir); }
+      int me = g_rank;
+      full_io(fd, &me, sizeof(me), 1);
+      g_peer[j].fd = fd;
+   }
+   for (int k = g_rank + 1; k < g_size; k++)
+   {
+      int fd;
+      do { fd = accept(ls, NULL, NULL); } while (fd < 0 && errno == EINTR);
+      if (fd < 0) { die("accept: %s", strerror(errno)); }
+      int who = -1;
+      full_io(fd, &who, sizeof(who), 0);
+      if (who <= g_rank || who >= g_size || g_peer[who].fd >= 0) { die("rendezvous: unexpected rank %d", who); }
+      g_peer[who].fd = fd;
+   }
+   close(ls);
+   unlink(a.sun_path);
+   for (int i = 0; i < g_size; i++) { if (i != g_rank) { set_nonblocking(g_peer[i].fd, i); } }
+}
+
 int MPI_Init(int *argc, char ***argv)
 {
    (void)argc; (void)argv;
    if (g_init) { return MPI_SUCCESS; }
    g_init = 1;
    const char *es = getenv("SHIM_SIZE"), *er = getenv("SHIM_RANK"), *ef = getenv("SHIM_FDS");
-   if (es && er && ef) { g_size = atoi(es); g_rank = atoi(er); }
+   const char *ed = getenv("SHIM_DIR");
+   if (!ef && ed)
+   {
+      if (!es) { es = getenv("WORLD_SIZE"); }
+      if (!er) { er = getenv("RANK"); }
+   }
+   if (es && er && (ef || ed)) { g_size = atoi(es); g_rank = atoi(er); }
+   if (g_size < 1 || g_rank < 0 || g_rank >= g_size) { die("bad rank %d of %d", g_rank, g_size); }
    g_peer = (peer_t *)calloc((size_t)g_size, sizeof(peer_t));
    g_req = (req_t *)calloc(MAX_REQS, sizeof(req_t));
    for (int i = 0; i < g_size; i++) { g_peer[i].fd = -1; }
-   if (g_size > 1)
+   if (g_size > 1 && !ef) { rendezvous(ed); }
+   else if (g_size > 1)
    {
       char *copy = strdup(ef), *save = NULL;
       int i = 0;
