@@ -106,5 +106,10 @@ double *hb_pcg_norms(void *pcg) { return ((hypre_PCGData *) pcg)->norms; }
 double *hb_pcg_rel_norms(void *pcg) { return ((hypre_PCGData *) pcg)->rel_norms; }
 void   *hb_pcg_precond_data(void *pcg) { return ((hypre_PCGData *) pcg)->precond_data; }
 
+/* ---- hypre_GMRESData / hypre_BiCGSTABData logging arrays (gmres.c:610-630, bicgstab.c:470-474) */
+double *hb_gmres_norms(void *g) { return ((hypre_GMRESData *) g)->norms; }
+double *hb_bicgstab_norms(void *g) { return ((hypre_BiCGSTABData *) g)->norms; }
+int     hb_bicgstab_converged(void *g) { return ((hypre_BiCGSTABData *) g)->converged; }
+
 int  hb_error_flag(void) { return (int) hypre_error_flag; }
 void hb_clear_errors(void) { HYPRE_ClearAllErrors(); }

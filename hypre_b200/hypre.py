@@ -40,7 +40,7 @@ def lib():
                  "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
         getattr(L, name).restype = vp
     for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
-                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms"):
+                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_bicgstab_norms"):
         getattr(L, name).restype = C.POINTER(d)
     L.hb_amg_relax_weight.restype = d
     L.hb_amg_omega.restype = d
@@ -52,6 +52,7 @@ def lib():
     L.hb_vector_create_cols.argtypes = [vp, d]
     for name in ("hb_vector_destroy", "hb_vector_data", "hb_vector_size", "hb_amg_num_levels", "hb_amg_Vtemp",
                  "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
+                 "hb_gmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
                  "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
                  "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
                  "HYPRE_ParCSRPCGDestroy"):
@@ -374,3 +375,87 @@ class ParCSRPCG(_Solver):
         if self.h:
             lib().HYPRE_ParCSRPCGDestroy(self.h)
             self.h = None
+
+
+class _ParCSRKrylov(_Solver):
+    """shared shape of HYPRE_ParCSRGMRES* / HYPRE_ParCSRBiCGSTAB* (src/parcsr_ls/HYPRE_parcsr_gmres.c,
+    HYPRE_parcsr_bicgstab.c; setters in src/krylov/HYPRE_gmres.c, HYPRE_bicgstab.c)"""
+    _prefix = ""
+    _par = ""
+    _norms = ""
+
+    def __init__(self, tol=1e-8, max_iter=100, print_level=0, logging=1):
+        self.h = C.c_void_p()
+        getattr(lib(), self._par + "Create")(COMM_WORLD, C.byref(self.h))
+        self.SetMaxIter(max_iter)
+        self.SetTol(float(tol))
+        self.SetPrintLevel(print_level)
+        self.SetLogging(logging)
+        self.max_iter = max_iter
+        self.precond = None
+
+    def SetPrecond(self, amg):
+        L = lib()
+        self.precond = amg
+        return getattr(L, self._prefix + "SetPrecond")(self.h, L.HYPRE_BoomerAMGSolve, L.HYPRE_BoomerAMGSetup, amg.h)
+
+    def SetDiagScalePrecond(self):
+        L = lib()
+        return getattr(L, self._prefix + "SetPrecond")(self.h, L.HYPRE_ParCSRDiagScale, L.HYPRE_ParCSRDiagScaleSetup, None)
+
+    def Setup(self, A, b, x):
+        return getattr(lib(), self._par + "Setup")(self.h, A.h, b.h, x.h)
+
+    def Solve(self, A, b, x):
+        return getattr(lib(), self._par + "Solve")(self.h, A.h, b.h, x.h)
+
+    @property
+    def num_iterations(self):
+        n = C.c_int()
+        getattr(lib(), self._prefix + "GetNumIterations")(self.h, C.byref(n))
+        return n.value
+
+    @property
+    def final_rel_norm(self):
+        v = C.c_double()
+        getattr(lib(), self._prefix + "GetFinalRelativeResidualNorm")(self.h, C.byref(v))
+        return v.value
+
+    @property
+    def converged(self):
+        n = C.c_int()
+        getattr(lib(), self._prefix + "GetConverged")(self.h, C.byref(n))
+        return n.value
+
+    def norms(self):
+        """residual norms the solver logged: entries 0..num_iterations"""
+        p = getattr(lib(), self._norms)(self.h)
+        return np.ctypeslib.as_array(p, (self.max_iter + 1,))[:self.num_iterations + 1].copy()
+
+    def destroy(self):
+        if self.h:
+            getattr(lib(), self._par + "Destroy")(self.h)
+            self.h = None
+
+
+class ParCSRGMRES(_ParCSRKrylov):
+    """HYPRE_ParCSRGMRES* / HYPRE_GMRES*: ij -solver 3 (AMG) / 4 (diagonal scaling), k_dim 5 (ij.c:1731)."""
+    _prefix = "HYPRE_GMRES"
+    _par = "HYPRE_ParCSRGMRES"
+    _norms = "hb_gmres_norms"
+
+    def __init__(self, k_dim=5, **kw):
+        super().__init__(**kw)
+        self.SetKDim(k_dim)
+
+
+class ParCSRBiCGSTAB(_ParCSRKrylov):
+    """HYPRE_ParCSRBiCGSTAB* / HYPRE_BiCGSTAB*: ij -solver 9 (AMG) / 10 (diagonal scaling)."""
+    _prefix = "HYPRE_BiCGSTAB"
+    _par = "HYPRE_ParCSRBiCGSTAB"
+    _norms = "hb_bicgstab_norms"
+
+    @property
+    def converged(self):
+        # no HYPRE_BiCGSTABGetConverged in the reference's API: read hypre_BiCGSTABData.converged
+        return lib().hb_bicgstab_converged(self.h)

@@ -43,6 +43,17 @@ int  orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros);
 int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, int two_norm,
              double *norms, double *rel_norms, int *converged);
 
+/* precond_kind: 0 = one AMG cycle, 1 = diagonal scaling (HYPRE_ParCSRDiagScale), 2 = identity.
+ * hypre_GMRESSolve (krylov/gmres.c:274-930, rel_change = 0, cf_tol = 0): returns the iteration count;
+ * norms[0..iters] as the reference logs them. */
+int  orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+               int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
+               int *converged);
+/* hypre_BiCGSTABSolve (krylov/bicgstab.c:226-640, stop_crit = 0, cf_tol = 0): iteration count, or
+ * -(iter) - 1 where the reference reports a breakdown */
+int  orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol,
+                  int min_iter, int max_iter, double *norms, double *rel_resid, int *converged);
+
 #ifdef __cplusplus
 }
 #endif

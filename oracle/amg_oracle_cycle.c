@@ -248,3 +248,213 @@ int orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, in
    free(p); free(s); free(r);
    return i;
 }
+
+/* ---- preconditioner shared by the GMRES / BiCGSTAB restatements below.
+ * kind 0: one AMG cycle with a zero initial guess (the callers ClearVector first, which sets all_zeros);
+ * kind 1: HYPRE_ParCSRDiagScale (parcsr_ls/HYPRE_parcsr_pcg.c:267-277): z = r ./ a_ii, diagonal entry first
+ * in its row; kind 2: hypre_ParKrylovIdentity (par_krylov_func.c:312-330): z = r. */
+static void orc_precond(orc_amg *h, int kind, const double *r, double *z)
+{
+   orc_level *L0 = &h->L[0];
+   const int n = L0->n;
+   int k;
+   if (kind == 0) { memset(z, 0, sizeof(double) * (size_t) n); orc_amg_cycle(h, r, z, 1); }
+   else if (kind == 1) { for (k = 0; k < n; k++) { z[k] = r[k] / L0->Aa[L0->Ai[k]]; } }
+   else { memcpy(z, r, sizeof(double) * (size_t) n); }
+}
+
+/* hypre_GMRESSolve (krylov/gmres.c:274-930) with rel_change = 0 and cf_tol = 0 (what ij -solver 3/4 passes):
+ * right-preconditioned restarted GMRES(k_dim), modified Gram-Schmidt, Givens rotations, true-residual
+ * check on convergence.  norms[0..iters] = the residual norms the reference logs.  Returns the iteration
+ * count; *converged as gmres_data->converged; *rel_resid as gmres_data->rel_residual_norm. */
+int orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+              int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
+{
+   orc_level *L0 = &h->L[0];
+   const int n = L0->n;
+   const double epsmac = 1.e-16;
+   double **p = (double **) calloc((size_t) k_dim + 1, sizeof(double *));
+   double *r = (double *) calloc((size_t) n, sizeof(double));
+   double *w = (double *) calloc((size_t) n, sizeof(double));
+   double *rs = (double *) calloc((size_t) k_dim + 1, sizeof(double));
+   double *c = (double *) calloc((size_t) k_dim, sizeof(double));
+   double *s = (double *) calloc((size_t) k_dim, sizeof(double));
+   double **hh = (double **) calloc((size_t) k_dim + 1, sizeof(double *));
+   double b_norm, r_norm, den_norm, epsilon, t, gamma, real_r_norm_old, real_r_norm_new;
+   int i, j, k, q, iter = 0;
+   for (i = 0; i <= k_dim; i++)
+   {
+      p[i] = (double *) calloc((size_t) n, sizeof(double));
+      hh[i] = (double *) calloc((size_t) k_dim, sizeof(double));
+   }
+   if (converged) { *converged = 0; }
+   orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, p[0]);
+   b_norm = sqrt(orc_dot(n, b, b));
+   real_r_norm_old = b_norm;
+   r_norm = sqrt(orc_dot(n, p[0], p[0]));
+   if (norms) { norms[0] = r_norm; }
+   den_norm = b_norm > 0.0 ? b_norm : r_norm;
+   epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
+   while (iter < max_iter)
+   {
+      rs[0] = r_norm;
+      if (r_norm == 0.0) { goto finish_no_norm; }
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
+         r_norm = sqrt(orc_dot(n, r, r));
+         if (r_norm <= epsilon) { break; }
+      }
+      t = 1.0 / r_norm;
+      for (q = 0; q < n; q++) { p[0][q] *= t; }
+      i = 0;
+      while (i < k_dim && iter < max_iter)
+      {
+         i++; iter++;
+         orc_precond(h, precond_kind, p[i - 1], r);
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, NULL, p[i]);
+         for (j = 0; j < i; j++)
+         {
+            hh[j][i - 1] = orc_dot(n, p[j], p[i]);
+            for (q = 0; q < n; q++) { p[i][q] += -hh[j][i - 1] * p[j][q]; }
+         }
+         t = sqrt(orc_dot(n, p[i], p[i]));
+         hh[i][i - 1] = t;
+         if (t != 0.0) { t = 1.0 / t; for (q = 0; q < n; q++) { p[i][q] *= t; } }
+         for (j = 1; j < i; j++)
+         {
+            t = hh[j - 1][i - 1];
+            hh[j - 1][i - 1] = s[j - 1] * hh[j][i - 1] + c[j - 1] * t;
+            hh[j][i - 1] = -s[j - 1] * t + c[j - 1] * hh[j][i - 1];
+         }
+         t = hh[i][i - 1] * hh[i][i - 1];
+         t += hh[i - 1][i - 1] * hh[i - 1][i - 1];
+         gamma = sqrt(t);
+         if (gamma == 0.0) { gamma = epsmac; }
+         c[i - 1] = hh[i - 1][i - 1] / gamma;
+         s[i - 1] = hh[i][i - 1] / gamma;
+         rs[i] = -hh[i][i - 1] * rs[i - 1];
+         rs[i] /= gamma;
+         rs[i - 1] = c[i - 1] * rs[i - 1];
+         hh[i - 1][i - 1] = s[i - 1] * hh[i][i - 1] + c[i - 1] * hh[i - 1][i - 1];
+         r_norm = fabs(rs[i]);
+         if (norms) { norms[iter] = r_norm; }
+         if (r_norm <= epsilon && iter >= min_iter) { break; }
+      }
+      /* solution of the upper triangular system, update of x through the preconditioner */
+      rs[i - 1] = rs[i - 1] / hh[i - 1][i - 1];
+      for (k = i - 2; k >= 0; k--)
+      {
+         t = 0.0;
+         for (j = k + 1; j < i; j++) { t -= hh[k][j] * rs[j]; }
+         t += rs[k];
+         rs[k] = t / hh[k][k];
+      }
+      memcpy(w, p[i - 1], sizeof(double) * (size_t) n);
+      for (q = 0; q < n; q++) { w[q] *= rs[i - 1]; }
+      for (j = i - 2; j >= 0; j--) { for (q = 0; q < n; q++) { w[q] += rs[j] * p[j][q]; } }
+      orc_precond(h, precond_kind, w, r);
+      for (q = 0; q < n; q++) { x[q] += r[q]; }
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         if (skip_real_r_check) { if (converged) { *converged = 1; } break; }
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
+         real_r_norm_new = r_norm = sqrt(orc_dot(n, r, r));
+         if (r_norm <= epsilon) { if (converged) { *converged = 1; } break; }
+         if (real_r_norm_new >= real_r_norm_old) { if (converged) { *converged = 1; } break; }
+         memcpy(p[0], r, sizeof(double) * (size_t) n);
+         i = 0;
+         real_r_norm_old = real_r_norm_new;
+      }
+      /* residual vector of the restart */
+      for (j = i; j > 0; j--)
+      {
+         rs[j - 1] = -s[j - 1] * rs[j];
+         rs[j] = c[j - 1] * rs[j];
+      }
+      if (i) { for (q = 0; q < n; q++) { p[i][q] += (rs[i] - 1.0) * p[i][q]; } }
+      for (j = i - 1; j > 0; j--) { for (q = 0; q < n; q++) { p[i][q] += rs[j] * p[j][q]; } }
+      if (i)
+      {
+         for (q = 0; q < n; q++) { p[0][q] += (rs[0] - 1.0) * p[0][q]; }
+         for (q = 0; q < n; q++) { p[0][q] += p[i][q]; }
+      }
+   }
+   if (rel_resid) { *rel_resid = b_norm > 0.0 ? r_norm / b_norm : r_norm; }
+finish_no_norm:
+   for (i = 0; i <= k_dim; i++) { free(p[i]); free(hh[i]); }
+   free(p); free(hh); free(r); free(w); free(rs); free(c); free(s);
+   return iter;
+}
+
+/* hypre_BiCGSTABSolve (krylov/bicgstab.c:226-640) with stop_crit = 0 and cf_tol = 0 (ij -solver 9/10).
+ * Returns the iteration count, or -(iter) - 1 when the reference would report a breakdown
+ * (hypre_error_w_msg "BiCGSTAB broke down", :433-437, :519-523, :533-538). */
+int orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol,
+                 int min_iter, int max_iter, double *norms, double *rel_resid, int *converged)
+{
+   orc_level *L0 = &h->L[0];
+   const int n = L0->n;
+   const double epsmac = 2.2250738585072014e-308;   /* HYPRE_REAL_MIN */
+   double *r = (double *) calloc((size_t) n, sizeof(double));
+   double *r0 = (double *) calloc((size_t) n, sizeof(double));
+   double *s = (double *) calloc((size_t) n, sizeof(double));
+   double *v = (double *) calloc((size_t) n, sizeof(double));
+   double *p = (double *) calloc((size_t) n, sizeof(double));
+   double *q = (double *) calloc((size_t) n, sizeof(double));
+   double alpha, beta, gamma, epsilon, temp, res, r_norm, b_norm, den_norm, gn, gd;
+   int iter = 0, k, ret;
+   if (converged) { *converged = 0; }
+   orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r0);
+   memcpy(r, r0, sizeof(double) * (size_t) n);
+   memcpy(p, r0, sizeof(double) * (size_t) n);
+   b_norm = sqrt(orc_dot(n, b, b));
+   res = orc_dot(n, r0, r0);
+   r_norm = sqrt(res);
+   if (norms) { norms[0] = r_norm; }
+   den_norm = b_norm > 0.0 ? b_norm : r_norm;
+   epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
+   if (rel_resid && b_norm > 0.0) { *rel_resid = r_norm / b_norm; }
+   ret = 0;
+   if (r_norm == 0.0) { goto done; }
+   if (r_norm <= epsilon && iter >= min_iter) { if (converged) { *converged = 1; } goto done; }
+   while (iter < max_iter)
+   {
+      iter++;
+      orc_precond(h, precond_kind, p, v);
+      orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, v, 0.0, NULL, q);
+      temp = orc_dot(n, r0, q);
+      if (fabs(temp) >= epsmac) { alpha = res / temp; }
+      else { ret = -iter - 1; goto done; }
+      for (k = 0; k < n; k++) { x[k] += alpha * v[k]; }
+      for (k = 0; k < n; k++) { r[k] += -alpha * q[k]; }
+      orc_precond(h, precond_kind, r, v);
+      orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, v, 0.0, NULL, s);
+      gn = orc_dot(n, r, s);
+      gd = orc_dot(n, s, s);
+      gamma = (gn == 0.0 && gd == 0.0) ? 0.0 : gn / gd;
+      for (k = 0; k < n; k++) { x[k] += gamma * v[k]; }
+      for (k = 0; k < n; k++) { r[k] += -gamma * s[k]; }
+      r_norm = sqrt(orc_dot(n, r, r));
+      if (norms) { norms[iter] = r_norm; }
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
+         r_norm = sqrt(orc_dot(n, r, r));
+         if (r_norm <= epsilon) { if (converged) { *converged = 1; } break; }
+      }
+      if (fabs(res) >= epsmac) { beta = 1.0 / res; }
+      else { ret = -iter - 1; goto done; }
+      res = orc_dot(n, r0, r);
+      beta *= res;
+      for (k = 0; k < n; k++) { p[k] += -gamma * q[k]; }
+      if (fabs(gamma) >= epsmac) { const double f = beta * alpha / gamma; for (k = 0; k < n; k++) { p[k] *= f; } }
+      else { ret = -iter - 1; goto done; }
+      for (k = 0; k < n; k++) { p[k] += r[k]; }
+   }
+   if (rel_resid) { *rel_resid = b_norm > 0.0 ? r_norm / b_norm : r_norm; }
+   ret = iter;
+done:
+   free(r); free(r0); free(s); free(v); free(p); free(q);
+   return ret;
+}

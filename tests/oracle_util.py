@@ -33,6 +33,8 @@ def lib():
         L.orc_relax_gs2_blocks.argtypes = [i, vp, vp, vp, vp, d, i, vp, vp, i, vp]
         L.orc_amg_cycle.argtypes = [vp, vp, vp, i]
         L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
+        L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
+        L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -177,6 +179,24 @@ class OracleAMG:
         it = lib().orc_pcg(self.h, p(np.ascontiguousarray(b)), p(x), tol, max_iter, two_norm, p(norms), p(rel),
                            C.byref(conv))
         return x, it, rel[1:it + 1].copy(), conv.value
+
+    def gmres(self, b, x0, precond=0, tol=1e-8, a_tol=0.0, k_dim=5, min_iter=0, max_iter=100, skip_real_r_check=0):
+        """orc_gmres: (x, iterations, norms[0..iterations], final relative residual, converged)"""
+        x = np.array(x0, dtype=np.float64, copy=True)
+        norms = np.zeros(max_iter + 1)
+        rel, conv = C.c_double(), C.c_int()
+        it = lib().orc_gmres(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, k_dim, min_iter, max_iter,
+                             skip_real_r_check, p(norms), C.byref(rel), C.byref(conv))
+        return x, it, norms[:it + 1].copy(), rel.value, conv.value
+
+    def bicgstab(self, b, x0, precond=0, tol=1e-8, a_tol=0.0, min_iter=0, max_iter=100):
+        """orc_bicgstab: (x, iterations (negative: breakdown), norms[0..iterations], final relative residual, converged)"""
+        x = np.array(x0, dtype=np.float64, copy=True)
+        norms = np.zeros(max_iter + 1)
+        rel, conv = C.c_double(), C.c_int()
+        it = lib().orc_bicgstab(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, min_iter, max_iter,
+                                p(norms), C.byref(rel), C.byref(conv))
+        return x, it, norms[:max(it, 0) + 1].copy(), rel.value, conv.value
 
     def destroy(self):
         if self.h:
