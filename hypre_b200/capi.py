@@ -29,6 +29,21 @@ class PcgResult(C.Structure):
                 ("rel_residual_norm", C.c_double), ("bi_prod", C.c_double)]
 
 
+class GmresParams(C.Structure):
+    _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
+                ("k_dim", C.c_int), ("skip_real_r_check", C.c_int), ("diag_scale", C.c_int)]
+
+
+class BicgstabParams(C.Structure):
+    _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
+                ("diag_scale", C.c_int)]
+
+
+class KrylovResult(C.Structure):
+    _fields_ = [("num_iterations", C.c_int), ("converged", C.c_int), ("error_flag", C.c_int),
+                ("rel_residual_norm", C.c_double), ("b_norm", C.c_double), ("real_residual_exit", C.c_int)]
+
+
 def declared_symbols():
     """Every function name declared in include/b200amg.h."""
     text = open(os.path.join(ROOT, "include", "b200amg.h")).read()
@@ -111,6 +126,10 @@ def lib():
         "b200_amg_solve": (i, [vp, vp, vp, d, i, i, c_int_p, c_dbl_p, vp]),
         "b200_pcg_solve": (i, [vp, vp, vp, C.POINTER(PcgParams), vp, vp, C.POINTER(PcgResult), vp, vp]),
         "b200_pcg_solve_host": (i, [vp, vp, vp, C.POINTER(PcgParams), vp, vp, C.POINTER(PcgResult), vp, vp]),
+        "b200_gmres_solve": (i, [vp, vp, vp, C.POINTER(GmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
+        "b200_gmres_solve_host": (i, [vp, vp, vp, C.POINTER(GmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
+        "b200_bicgstab_solve": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
+        "b200_bicgstab_solve_host": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError if the .so does not export a declared symbol

@@ -100,9 +100,12 @@ struct b200_ctx {
    static constexpr int NUM_WS = 12;
    double      *ws[NUM_WS] = {nullptr};
    size_t       ws_n[NUM_WS] = {0};
+   // pinned mirror of the device scalars of a GMRES / BiCGSTAB solve (krylov.cu)
+   double      *h_kry = nullptr;
+   size_t       h_kry_n = 0;
 };
 
-enum { WS_PCG_P = 0, WS_PCG_S, WS_PCG_R, WS_HOST_B, WS_HOST_X, WS_HOST_Y, WS_AMG_R };
+enum { WS_PCG_P = 0, WS_PCG_S, WS_PCG_R, WS_HOST_B, WS_HOST_X, WS_HOST_Y, WS_AMG_R, WS_KRYLOV };
 // device work vector `slot` with at least n doubles
 int ctx_workspace(b200_ctx *c, int slot, size_t n, double **out);
 

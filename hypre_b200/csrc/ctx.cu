@@ -150,6 +150,7 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    if (c->h_ring) { cudaFreeHost(c->h_ring); }
    if (c->d_flush) { cudaFree(c->d_flush); }
    if (c->h_stage) { cudaFreeHost(c->h_stage); }
+   if (c->h_kry) { cudaFreeHost(c->h_kry); }
    for (int k = 0; k < b200_ctx::NUM_WS; k++) { if (c->ws[k]) { cudaFree(c->ws[k]); } }
    cudaEventDestroy(c->ev_pack); cudaEventDestroy(c->ev_halo);
    cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);

@@ -654,6 +654,235 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
    return hypre_error_flag;
 }
 
+/* ------------------------------------------------------------ GMRES / BiCGSTAB
+ * Preconditioner of a ParCSR Krylov solver -> device objects: BoomerAMG (one cycle), diagonal scaling or
+ * identity, as for PCG above.  Returns NULL after GLUE_FAIL when there is no device implementation. */
+static mirror_t *krylov_precond_mirror(HYPRE_Int (*precond)(void *, void *, void *, void *), void *precond_data,
+                                       hypre_ParCSRMatrix *pA, b200_amg **amg, int *diag_scale)
+{
+   mirror_t *m = NULL;
+   *amg = NULL; *diag_scale = 0;
+   if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_BoomerAMGSolve ||
+       precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_BoomerAMGSolve)
+   {
+      hypre_ParAMGData *amg_data = (hypre_ParAMGData *) precond_data;
+      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) != 1)
+      {
+         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 and max_iter 1");
+         return NULL;
+      }
+      if (hypre_ParAMGDataAArray(amg_data) == NULL || hypre_ParAMGDataAArray(amg_data)[0] != pA)
+      {
+         GLUE_FAIL("BoomerAMG was not set up for this matrix");
+         return NULL;
+      }
+      m = mirror_for_amg(amg_data);
+      if (!m) { GLUE_FAIL("hierarchy upload failed"); return NULL; }
+      *amg = m->amg;
+   }
+   else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_ParCSRDiagScale)
+   {
+      *diag_scale = 1;
+      m = mirror_for_matrix(pA);
+      if (!m) { GLUE_FAIL("matrix upload failed"); }
+   }
+   else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_ParKrylovIdentity)
+   {
+      m = mirror_for_matrix(pA);
+      if (!m) { GLUE_FAIL("matrix upload failed"); }
+   }
+   else
+   {
+      GLUE_FAIL("preconditioner has no device implementation (BoomerAMG, diagonal scaling, identity are supported)");
+   }
+   return m;
+}
+
+static void krylov_nan_message(const char *who)
+{
+   hypre_printf("\n\nERROR detected by Hypre ... BEGIN\n");
+   hypre_printf("ERROR -- %s: INFs and/or NaNs detected in input.\n", who);
+   hypre_printf("Returning error flag += 101.  Program not terminated.\n");
+   hypre_printf("ERROR detected by Hypre ... END\n\n\n");
+}
+
+/* residual table of hypre_GMRESSolve / hypre_BiCGSTABSolve (gmres.c:417-460, 612-630; bicgstab.c:354-362,
+ * 406-421, 491-499) from the history the device solve returned */
+static void krylov_print_table(const double *norms, int iters, double b_norm)
+{
+   int i;
+   hypre_printf("L2 norm of b: %e\n", b_norm);
+   if (b_norm == 0.0) { hypre_printf("Rel_resid_norm actually contains the residual norm\n"); }
+   hypre_printf("Initial L2 norm of residual: %e\n", norms[0]);
+   hypre_printf("=============================================\n\n");
+   if (b_norm > 0.0)
+   {
+      hypre_printf("Iters     resid.norm     conv.rate  rel.res.norm\n");
+      hypre_printf("-----    ------------    ---------- ------------\n");
+   }
+   else
+   {
+      hypre_printf("Iters     resid.norm     conv.rate\n");
+      hypre_printf("-----    ------------    ----------\n");
+   }
+   for (i = 1; i <= iters; i++)
+   {
+      if (b_norm > 0.0) { hypre_printf("% 5d    %e    %f   %e\n", i, norms[i], norms[i] / norms[i - 1], norms[i] / b_norm); }
+      else { hypre_printf("% 5d    %e    %f\n", i, norms[i], norms[i] / norms[i - 1]); }
+   }
+}
+
+/* Everything hypre_GMRESSolve (kind 0, print_level > 1) / hypre_BiCGSTABSolve (kind 1, print_level > 0) print
+ * for a solve with this history: table, "Final L2 norm of residual" after the exits that evaluated b - A x
+ * (gmres.c:512-520, 783-851, 895-898; bicgstab.c:436-441, 508-512).  Host printing only; exported so that the
+ * CPU tests can compare the text with the reference driver's. */
+void hypre_b200_krylov_report(int kind, const double *norms, int iters, double b_norm, double rel_norm, int real_residual_exit)
+{
+   krylov_print_table(norms, iters, b_norm);
+   if (real_residual_exit)
+   {
+      hypre_printf("\n\n");
+      if (kind == 1 && iters == 0) { hypre_printf("Tolerance and min_iter requirements satisfied by initial data.\n"); }
+      hypre_printf("Final L2 norm of residual: %e\n\n", b_norm > 0.0 ? rel_norm * b_norm : rel_norm);
+   }
+   if (kind == 0) { hypre_printf("\n\n"); }
+}
+
+/* hypre_GMRESSolve (src/krylov/gmres.c:274-930) for the ParCSR operator table. */
+HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
+{
+   static pcg_solve_fn next = NULL;
+   hypre_GMRESData      *g  = (hypre_GMRESData *) gmres_vdata;
+   hypre_GMRESFunctions *fn = g->functions;
+   hypre_ParCSRMatrix   *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector      *pb = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
+   mirror_t *m;
+   b200_amg *amg = NULL;
+   b200_gmres_params prm;
+   b200_krylov_result res;
+   HYPRE_Int my_id, num_procs;
+   double *norms, *own_norms = NULL;
+   int status, diag_scale = 0;
+
+   if (!next) { next = (pcg_solve_fn) next_sym("hypre_GMRESSolve"); }
+   if (!g_enabled) { return next(gmres_vdata, A, b, x); }
+   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(gmres_vdata, A, b, x); }
+
+   if (g->rel_change || g->cf_tol > 0.0 || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   {
+      GLUE_FAIL("GMRES option outside the device path (rel_change / cf_tol / stop_crit / hybrid / multivector)");
+      return hypre_error_flag;
+   }
+   m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
+   if (!m) { return hypre_error_flag; }
+
+   memset(&prm, 0, sizeof(prm));
+   prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
+   prm.k_dim = g->k_dim; prm.skip_real_r_check = g->skip_real_r_check; prm.diag_scale = diag_scale;
+   g->converged = 0;
+   (*(fn->CommInfo))(A, &my_id, &num_procs);
+   /* norms exists when logging or print_level is set (hypre_GMRESSetup, gmres.c:246-256).  The reference
+    * fills norms[0] then and norms[iter] only when print_level > 0 (gmres.c:413, 610); here the whole history
+    * is stored in both cases */
+   norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
+   if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
+
+   status = b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                  hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                  hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   if (status != B200_OK) { free(own_norms); GLUE_FAIL("device GMRES failed"); return hypre_error_flag; }
+   if (verbose() && g_rank == 0)
+   {
+      fprintf(stderr, "hypre_b200: GMRES(%d) solve on the device: %d iterations, relative residual %.6e\n",
+              (int) g->k_dim, res.num_iterations, res.rel_residual_norm);
+   }
+   if (res.error_flag & 1)
+   {
+      if (g->logging > 0 || g->print_level > 0) { krylov_nan_message("hypre_GMRESSolve"); }
+      free(own_norms);
+      hypre_error(HYPRE_ERROR_GENERIC);
+      return hypre_error_flag;
+   }
+   if (g->print_level > 1 && my_id == 0 && g_rank == 0)
+   {
+      hypre_b200_krylov_report(0, norms, res.num_iterations, res.b_norm, res.rel_residual_norm, res.real_residual_exit);
+   }
+   free(own_norms);
+   g->converged = res.converged;
+   g->num_iterations = res.num_iterations;
+   g->rel_residual_norm = res.rel_residual_norm;
+   hypre_ParVectorAllZeros(px) = 0;
+   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   return hypre_error_flag;
+}
+
+/* hypre_BiCGSTABSolve (src/krylov/bicgstab.c:226-640) for the ParCSR operator table. */
+HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
+{
+   static pcg_solve_fn next = NULL;
+   hypre_BiCGSTABData      *g  = (hypre_BiCGSTABData *) bicgstab_vdata;
+   hypre_BiCGSTABFunctions *fn = g->functions;
+   hypre_ParCSRMatrix      *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector         *pb = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
+   mirror_t *m;
+   b200_amg *amg = NULL;
+   b200_bicgstab_params prm;
+   b200_krylov_result res;
+   HYPRE_Int my_id, num_procs;
+   double *norms, *own_norms = NULL;
+   int status, diag_scale = 0;
+
+   if (!next) { next = (pcg_solve_fn) next_sym("hypre_BiCGSTABSolve"); }
+   if (!g_enabled) { return next(bicgstab_vdata, A, b, x); }
+   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(bicgstab_vdata, A, b, x); }
+
+   if (g->cf_tol > 0.0 || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   {
+      GLUE_FAIL("BiCGSTAB option outside the device path (cf_tol / stop_crit / hybrid / multivector)");
+      return hypre_error_flag;
+   }
+   m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
+   if (!m) { return hypre_error_flag; }
+
+   memset(&prm, 0, sizeof(prm));
+   prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
+   prm.diag_scale = diag_scale;
+   g->converged = 0;
+   (*(fn->CommInfo))(A, &my_id, &num_procs);
+   norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
+   if (!norms && g->print_level > 0) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
+
+   status = b200_bicgstab_solve_host(glue_ctx(), m->A, amg, &prm,
+                                     hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                     hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   if (status != B200_OK) { free(own_norms); GLUE_FAIL("device BiCGSTAB failed"); return hypre_error_flag; }
+   if (verbose() && g_rank == 0)
+   {
+      fprintf(stderr, "hypre_b200: BiCGSTAB solve on the device: %d iterations, relative residual %.6e\n",
+              res.num_iterations, res.rel_residual_norm);
+   }
+   if (res.error_flag & 1)
+   {
+      if (g->logging > 0 || g->print_level > 0) { krylov_nan_message("hypre_BiCGSTABSolve"); }
+      free(own_norms);
+      hypre_error(HYPRE_ERROR_GENERIC);
+      return hypre_error_flag;
+   }
+   if (g->print_level > 0 && my_id == 0 && g_rank == 0)
+   {
+      hypre_b200_krylov_report(1, norms, res.num_iterations, res.b_norm, res.rel_residual_norm, res.real_residual_exit);
+   }
+   free(own_norms);
+   g->converged = res.converged;
+   g->num_iterations = res.num_iterations;
+   /* the reference leaves rel_residual_norm untouched when b == 0 and the solve ends before the loop */
+   if (res.b_norm > 0.0 || res.num_iterations > 0 || (res.error_flag & 256)) { g->rel_residual_norm = res.rel_residual_norm; }
+   hypre_ParVectorAllZeros(px) = 0;
+   if (res.error_flag & 2) { hypre_error_w_msg(HYPRE_ERROR_GENERIC, "BiCGSTAB broke down!! divide by near zero\n"); }
+   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   return hypre_error_flag;
+}
+
 /* The closing statistics of hypre_BoomerAMGSolve (src/parcsr_ls/par_amg_solve.c:338-416) and its residual
  * table (:257-264, :327-331) from the history the device solve returned.  hist[k] = ||r_k||_2, k = 0..cycles;
  * rhs_norm = ||f||_2 (0 when it vanishes).  Host arithmetic and printing only; also reachable from the tests

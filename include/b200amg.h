@@ -270,6 +270,55 @@ int b200_pcg_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200
                         const double *b_h, double *x_h, b200_pcg_result *res,
                         double *norms_h, double *rel_norms_h);
 
+/* --------------------------------------------------- GMRES / BiCGSTAB
+ * hypre_GMRESSolve (src/krylov/gmres.c:274-930; ij -solver 3 / 4) and hypre_BiCGSTABSolve
+ * (src/krylov/bicgstab.c:226-640; ij -solver 9 / 10) with the ParCSR operator table
+ * (src/parcsr_ls/par_krylov_func.c:14-330): right preconditioning by one b200_amg_cycle (amg != NULL),
+ * diagonal scaling (diag_scale, HYPRE_ParCSRDiagScale) or nothing.  Options the reference switches off by
+ * default are not implemented and must be off: rel_change, cf_tol, stop_crit, hybrid.  b, x dev pointers;
+ * norms_h (HOST, max_iter + 1 entries, may be NULL) receives the residual norms the reference logs
+ * (gmres.c:413, 610; bicgstab.c:353, 489). */
+typedef struct {
+   double tol;               /* r_tol */
+   double a_tol;
+   int    max_iter;
+   int    min_iter;
+   int    k_dim;             /* restart length (HYPRE_GMRESSetKDim; ij default 5) */
+   int    skip_real_r_check; /* gmres.c:767-771 */
+   int    diag_scale;        /* as b200_pcg_params */
+} b200_gmres_params;
+
+typedef struct {
+   double tol;
+   double a_tol;
+   int    max_iter;
+   int    min_iter;
+   int    diag_scale;
+} b200_bicgstab_params;
+
+typedef struct {
+   int    num_iterations;
+   int    converged;
+   int    error_flag;        /* 0, or a sum of: 1 Inf/NaN in the input (HYPRE_ERROR_GENERIC), 2 BiCGSTAB
+                              * breakdown (HYPRE_ERROR_GENERIC with message), 256 HYPRE_ERROR_CONV */
+   double rel_residual_norm;
+   double b_norm;
+   int    real_residual_exit;/* 1: the solve ended on an evaluation of b - A x (the exits after which the
+                              * reference prints "Final L2 norm of residual", gmres.c:512-520, 783-851;
+                              * bicgstab.c:436-441, 508-512) */
+} b200_krylov_result;
+
+int b200_gmres_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_gmres_params *prm,
+                     const double *b, double *x, b200_krylov_result *res, double *norms_h);
+int b200_bicgstab_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
+                        const double *b, double *x, b200_krylov_result *res, double *norms_h);
+/* the same with HOST b/x (H2D of b and x, device solve, D2H of x): the calls the hypre_GMRESSolve /
+ * hypre_BiCGSTABSolve bindings make for host-resident hypre vectors */
+int b200_gmres_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_gmres_params *prm,
+                          const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
+int b200_bicgstab_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
+                             const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -155,3 +155,41 @@ def test_oracle_krylov_matches_ij_driver(ref_off, key):
     assert it == it_ref
     np.testing.assert_allclose(rel, fin_ref, rtol=2e-6)
     orc.destroy()
+
+
+@pytest.mark.parametrize("kind", ["gmres", "bicgstab"])
+@pytest.mark.parametrize("opts", [dict(tol=1e-2, min_iter=9), dict(tol=0.0, a_tol=1e-5), dict(max_iter=0),
+                                  dict(skip_real_r_check=1, k_dim=6)])
+def test_oracle_krylov_options_match_reference(ref_off, kind, opts):
+    """min_iter, absolute tolerance, max_iter 0, skip_real_r_check (GMRES only)"""
+    H = ref_off
+    if kind == "bicgstab" and "skip_real_r_check" in opts:
+        pytest.skip("GMRES option")
+    A = H.laplacian(9, 8, 7)
+    b, x = A.vector(1.0), A.vector(0.0)
+    s = _solver(H, kind, None, k_dim=opts.get("k_dim", 5), tol=opts.get("tol", 1e-8), max_iter=opts.get("max_iter", 200))
+    if "min_iter" in opts:
+        s.SetMinIter(opts["min_iter"])
+    if "a_tol" in opts:
+        s.SetAbsoluteTol(float(opts["a_tol"]))
+    if "skip_real_r_check" in opts:
+        s.SetSkipRealResidualCheck(1)
+    s.Setup(A, b, x)
+    H.clear_errors()
+    s.Solve(A, b, x)
+    flag = H.error_flag()
+    H.clear_errors()
+    Ad, _ = A.blocks()
+    orc = O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
+    kw = dict(precond=1, tol=opts.get("tol", 1e-8), a_tol=opts.get("a_tol", 0.0), min_iter=opts.get("min_iter", 0),
+              max_iter=opts.get("max_iter", 200))
+    if kind == "gmres":
+        kw.update(k_dim=opts.get("k_dim", 5), skip_real_r_check=opts.get("skip_real_r_check", 0))
+    xo, it, norms, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size), **kw)
+    assert it == s.num_iterations and conv == s.converged
+    assert flag == (256 if opts.get("max_iter", 200) == 0 else 0)
+    if it > 0:
+        np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
+    np.testing.assert_allclose(rel, s.final_rel_norm, rtol=1e-9)
+    np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
+    orc.destroy()
