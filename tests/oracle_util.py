@@ -224,6 +224,10 @@ CASES = {
     "lap7_24_rlx16_F": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"FCycle": 1}),
     "lap27_20_rlx18_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=18, opts={"NumSweeps": 2}),
     "lap7_24_rlx7_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxWt": 0.8}),
+    # Chebyshev variant 1 (par_cheby.c:29-33: only the setup's coefficients differ), orders 3 and 4, unscaled
+    "lap7_24_rlx16_var1": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyVariant": 1}),
+    "lap7_24_rlx16_o4": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyOrder": 4}),
+    "lap7_24_rlx16_o3_noscale": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyOrder": 3, "ChebyScale": 0}),
 }
 
 IJ_ARGS = {

@@ -182,3 +182,21 @@ def test_gs2_block_partitioned_restatement(ref_off, inner):
         sign = -sign
     np.testing.assert_allclose(run(starts), u, rtol=1e-13, atol=1e-14)
     assert not np.allclose(run(starts), u_one, rtol=1e-6)      # the partition does matter
+
+
+@pytest.mark.parametrize("name", ["lap7_24_rlx18_W", "lap7_24_rlx16_F", "lap27_20_rlx18_ns2", "lap7_24_rlx7_w08",
+                                  "lap7_24_rlx16_var1", "lap7_24_rlx16_o4", "lap7_24_rlx16_o3_noscale"])
+def test_oracle_pcg_option_cases_match_reference(ref_off, name):
+    """cycle and smoother options without a golden (W / F cycle, two sweeps, weighted Jacobi, Chebyshev variant 1,
+    orders 3 / 4, unscaled): the oracle against hypre_PCGSolve in-process on the same hierarchy"""
+    H = ref_off
+    A, b, x, amg, pcg = O.build_case(H, name)
+    H.clear_errors()
+    pcg.Solve(A, b, x)
+    assert H.error_flag() == 0
+    orc = O.OracleAMG(amg)
+    xs, it, rel, conv = orc.pcg(b.numpy(), np.zeros(x.size))
+    assert it == pcg.num_iterations and conv == 1
+    np.testing.assert_allclose(rel, pcg.rel_norms(), rtol=1e-9)
+    np.testing.assert_allclose(xs, x.numpy(), rtol=1e-9, atol=1e-12)
+    orc.destroy()
