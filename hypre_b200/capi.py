@@ -104,6 +104,7 @@ def lib():
         "b200_parcsr_matvec": (i, [vp, d, vp, d, vp, vp]),
         "b200_parcsr_matvecT": (i, [vp, d, vp, d, vp]),
         "b200_parcsr_matvec_host": (i, [vp, d, vp, d, vp, vp]),
+        "b200_parcsr_matvecT_host": (i, [vp, d, vp, d, vp]),
         "b200_relax_l1jacobi": (i, [vp, vp, vp, d, vp, vp, i]),
         "b200_relax_cheby": (i, [vp, vp, vp, vp, i, i, vp, vp, vp, vp, i]),
         "b200_relax_2stage_gs": (i, [vp, vp, d, i, vp, vp, vp, i]),

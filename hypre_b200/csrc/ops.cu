@@ -385,3 +385,23 @@ extern "C" int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const doubl
    CUDA_TRY(cudaStreamSynchronize(c->stream));
    return B200_OK;
 }
+
+// host-vector SpMV^T: what HYPRE_ParCSRMatrixMatvecT costs end to end for host-resident hypre vectors
+// (H2D x [, y], kernels, D2H y).  x has n_rows entries, y this rank's n_cols_diag.
+extern "C" int b200_parcsr_matvecT_host(b200_parcsr *A, double alpha, const double *x_h, double beta, double *y_h)
+{
+   ARG_CHECK(A != nullptr && x_h != nullptr && y_h != nullptr);
+   b200_ctx *c = A->ctx;
+   double *dx = nullptr, *dy = nullptr;
+   B200_TRY(ctx_workspace(c, WS_HOST_X, A->n_rows, &dx));
+   B200_TRY(ctx_workspace(c, WS_HOST_Y, A->n_cols_diag, &dy));
+   CUDA_TRY(cudaMemcpyAsync(dx, x_h, sizeof(double) * (size_t)A->n_rows, cudaMemcpyHostToDevice, c->stream));
+   if (beta != 0.0)
+   {
+      CUDA_TRY(cudaMemcpyAsync(dy, y_h, sizeof(double) * (size_t)A->n_cols_diag, cudaMemcpyHostToDevice, c->stream));
+   }
+   B200_TRY(op_matvecT(A, alpha, dx, beta, dy));
+   CUDA_TRY(cudaMemcpyAsync(y_h, dy, sizeof(double) * (size_t)A->n_cols_diag, cudaMemcpyDeviceToHost, c->stream));
+   CUDA_TRY(cudaStreamSynchronize(c->stream));
+   return B200_OK;
+}

@@ -1100,6 +1100,38 @@ HYPRE_Int HYPRE_ParCSRMatrixMatvec(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HY
 }
 
 /* handles for tests / bench (python ctypes) */
+/* y = alpha A^T x + beta y for host-resident hypre vectors: HYPRE_ParCSRMatrixMatvecT
+ * (src/parcsr_mv/HYPRE_parcsr_matrix.c) -> hypre_ParCSRMatrixMatvecT (par_csr_matvec.c:522-546).  x lives on the
+ * row partition, y on the column partition of A. */
+HYPRE_Int HYPRE_ParCSRMatrixMatvecT(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HYPRE_ParVector x,
+                                    HYPRE_Complex beta, HYPRE_ParVector y)
+{
+   hypre_ParCSRMatrix *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector    *px = (hypre_ParVector *) x, *py = (hypre_ParVector *) y;
+   mirror_t *m;
+   if (!g_enabled)
+   {
+      typedef HYPRE_Int (*mv_fn)(HYPRE_Complex, HYPRE_ParCSRMatrix, HYPRE_ParVector, HYPRE_Complex, HYPRE_ParVector);
+      static mv_fn next = NULL;
+      if (!next) { next = (mv_fn) next_sym("HYPRE_ParCSRMatrixMatvecT"); }
+      return next(alpha, A, x, beta, y);
+   }
+   if (hypre_ParVectorNumVectors(px) > 1)
+   {
+      GLUE_FAIL("multivector SpMV is outside the device path");
+      return hypre_error_flag;
+   }
+   m = mirror_for_matrix(pA);
+   if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
+   if (b200_parcsr_matvecT_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, beta,
+                                hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_col) != B200_OK)
+   {
+      GLUE_FAIL("device SpMV^T failed");
+   }
+   hypre_ParVectorAllZeros(py) = 0;
+   return hypre_error_flag;
+}
+
 b200_amg *hypre_b200_amg_mirror(void *amg_vdata)
 {
    mirror_t *m = mirror_for_amg((hypre_ParAMGData *) amg_vdata);

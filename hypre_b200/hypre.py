@@ -65,6 +65,7 @@ def lib():
     L.hb_matrix_blocks.argtypes = [vp] + [vp] * 9
     L.hypre_b200_set_enabled.argtypes = [i]
     L.HYPRE_ParCSRMatrixMatvec.argtypes = [d, vp, vp, d, vp]
+    L.HYPRE_ParCSRMatrixMatvecT.argtypes = [d, vp, vp, d, vp]
     L.hypre_ParCSRMatrixMatvecOutOfPlace.argtypes = [d, vp, vp, d, vp, vp]
     L.hypre_ParCSRMatrixMatvecT.argtypes = [d, vp, vp, d, vp]
     L.hypre_BoomerAMGRelax.argtypes = [vp, vp, vp, i, i, d, d, vp, vp, vp, vp]

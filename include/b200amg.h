@@ -159,6 +159,10 @@ int b200_parcsr_matvecT(b200_parcsr *A, double alpha, const double *x,
  * HYPRE_ParCSRMatrixMatvec binding makes for host-resident hypre vectors. */
 int b200_parcsr_matvec_host(b200_parcsr *A, double alpha, const double *x_h,
                             double beta, const double *b_h, double *y_h);
+/* The transposed product with HOST vectors (x_h: n_rows entries, y_h: this rank's n_cols_diag): the call the
+ * HYPRE_ParCSRMatrixMatvecT binding makes (src/parcsr_mv/HYPRE_parcsr_matrix.c; hypre_ParCSRMatrixMatvecT,
+ * src/parcsr_mv/par_csr_matvec.c:522-546). */
+int b200_parcsr_matvecT_host(b200_parcsr *A, double alpha, const double *x_h, double beta, double *y_h);
 
 /* --------------------------------------------------------------- smoothers
  * One sweep each, dev pointers.  `tmp` arguments are caller-provided work

@@ -151,3 +151,33 @@ def test_multirank_binding_fails_loudly_without_gpu(built):
     assert "no CPU fallback" in err
     assert "hierarchy upload failed" in err
     assert "Iterations = 0" in r.stdout
+
+
+@pytest.mark.parametrize("kind", ["gmres", "bicgstab"])
+def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, kind):
+    """hypre_GMRESSolve / hypre_BiCGSTABSolve are interposed: without a GPU the solve raises the hypre error flag
+    and leaves x alone; options outside the device path are rejected the same way (never run on the CPU)"""
+    if has_gpu():
+        pytest.skip("GPU present")
+    H.set_device_path(True)
+    A = H.laplacian(8, 8, 8)
+    b = A.vector(1.0); x = A.vector(0.0)
+    s = H.ParCSRGMRES() if kind == "gmres" else H.ParCSRBiCGSTAB()
+    s.SetDiagScalePrecond()
+    s.Setup(A, b, x)
+    H.clear_errors()
+    s.Solve(A, b, x)
+    assert H.error_flag() & 1 and s.num_iterations == 0 and not np.any(x.numpy())
+    H.clear_errors()
+    if kind == "gmres":
+        s.SetRelChange(1)
+    else:
+        s.SetStopCrit(1)
+    s.Solve(A, b, x)
+    assert H.error_flag() & 1 and not np.any(x.numpy())
+    H.clear_errors()
+    # the transposed product, too
+    y = A.vector(0.0, cols=True)
+    H.lib().HYPRE_ParCSRMatrixMatvecT(1.0, A.h, b.h, 0.0, y.h)
+    assert H.error_flag() & 1 and not np.any(y.numpy())
+    H.clear_errors()

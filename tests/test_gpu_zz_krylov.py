@@ -176,3 +176,26 @@ def test_unchanged_ij_gmres_bicgstab_on_the_device(args):
         assert kd == kr and abs(rd - rr) <= tol * rr + 1e-13 * rows_r[0][1], (kd, rd, rr)
     if it_d == it_r:
         assert abs(fin_d - fin_r) <= (1e-3 if long_run else 2e-6) * fin_r + 1e-15
+
+
+def test_host_spmvT_entry_matches_reference(H, ctx):
+    """HYPRE_ParCSRMatrixMatvecT with host vectors, on a rectangular operator (the interpolation of a hierarchy:
+    y = alpha P^T x + beta y is the restriction of par_cycle.c:704-705) and on a square one"""
+    A0, b, x0, amg, pcg = O.build_case(H, "lap7_24_rlx16")
+    for M in (amg.P(0), A0):
+        x = M.vector(0.0); y = M.vector(0.0, cols=True)
+        x.numpy()[:] = np.sin(np.arange(x.size)) * 1e-3 + 1.0
+        out = {}
+        for beta in (0.0, -1.0):
+            for dev in (False, True):
+                H.set_device_path(dev)
+                y.numpy()[:] = 0.5
+                H.clear_errors()
+                H.lib().HYPRE_ParCSRMatrixMatvecT(2.0, M.h, x.h, beta, y.h)
+                assert H.error_flag() == 0
+                out[dev] = y.numpy().copy()
+            H.set_device_path(True)
+            Md = M.blocks()[0]
+            scale = np.abs(Md).T.dot(np.abs(x.numpy())) * 2.0 + 0.5
+            assert np.max(np.abs(out[True] - out[False]) / scale) < 1e-12, beta
+        x.destroy(); y.destroy()
