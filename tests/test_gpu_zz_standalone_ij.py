@@ -11,7 +11,9 @@ import pytest
 
 from hypre_b200 import IJ_B200, IJ_REF
 
-pytestmark = pytest.mark.gpu
+from conftest import FIRST_RUN
+
+pytestmark = [pytest.mark.gpu, FIRST_RUN]
 
 KEYS = {"iterations": r"BoomerAMG Iterations = (\d+)",
         "final_rel": r"Final Relative Residual Norm = (\S+)",
