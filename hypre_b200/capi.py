@@ -117,6 +117,7 @@ def lib():
         "b200_amg_set_level_cheby": (i, [vp, i, vp, vp, i, i]),
         "b200_amg_set_coarse_dense": (i, [vp, i, vp, i, vp]),
         "b200_amg_finalize": (i, [vp]),
+        "b200_amg_set_precond_cycles": (i, [vp, i]),
         "b200_amg_cycle": (i, [vp, vp, vp, i]),
         "b200_amg_cycle_bytes": (i, [vp, c_dbl_p]),
         "b200_amg_cycle_bytes_stored": (i, [vp, c_dbl_p]),

@@ -33,6 +33,7 @@ struct b200_amg {
    // The level above holds P with global coarse columns; restriction onto repl_level is followed by
    // a vector all-reduce, prolongation from it is local.
    int  repl_level = 1 << 30;
+   int  precond_cycles = 1;    // cycles per preconditioner application (hypre_ParAMGDataMaxIter with tol 0)
    bool finalized = false;
 };
 
@@ -422,6 +423,28 @@ int amg_cycle_ptr(b200_amg *a, const double *f, double *u, int zero_guess, doubl
    return amg_cycle_core(a, f, u, zero_guess, u_result);
 }
 double *amg_level0_alt(b200_amg *a) { return a->L[0].Ualt; }
+
+// BoomerAMG as a preconditioner: z = B r.  hypre_BoomerAMGSolve with tol 0 and max_iter k (ij -precon_cycles k)
+// runs k cycles without looking at the residual (src/parcsr_ls/par_amg_solve.c:257-336); the Krylov solver cleared
+// u before the call, so the first cycle starts from a zero guess and the others continue on its result.
+int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result)
+{
+   B200_TRY(amg_cycle_core(a, f, u, 1, u_result));
+   for (int k = 1; k < a->precond_cycles; k++)
+   {
+      if (*u_result != u) { B200_TRY(b200_vec_copy(a->ctx, a->L[0].n, *u_result, u)); }
+      B200_TRY(amg_cycle_core(a, f, u, 0, u_result));
+   }
+   return B200_OK;
+}
+int amg_precond_cycles(const b200_amg *a) { return a->precond_cycles; }
+
+extern "C" int b200_amg_set_precond_cycles(b200_amg *a, int cycles)
+{
+   ARG_CHECK(a != nullptr && cycles >= 1);
+   a->precond_cycles = cycles;
+   return B200_OK;
+}
 
 extern "C" int b200_amg_cycle(b200_amg *a, const double *f, double *u, int zero_guess)
 {

@@ -14,7 +14,7 @@
 #include "p2p.cuh"
 #include "krylov_core.hpp"
 
-int amg_cycle_ptr(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result);
+int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result);
 
 // z = r ./ d   (HYPRE_ParCSRDiagScale, src/parcsr_ls/HYPRE_parcsr_pcg.c:267-277)
 struct FDiagScale {
@@ -100,7 +100,7 @@ struct DevKrylovOps {
       if (amg)
       {
          double *out = nullptr;
-         B200_TRY(amg_cycle_ptr(amg, r, z, 1, &out));
+         B200_TRY(amg_precond_ptr(amg, r, z, &out));
          *zr = out;
          return B200_OK;
       }

@@ -9,7 +9,8 @@
 #include <cmath>
 #include <cfloat>
 
-int     amg_cycle_ptr(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result);
+int     amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result);
+int     amg_precond_cycles(const b200_amg *a);
 
 // scalar slots in ctx->d_scalars
 enum { S_SDOTP = 8, S_IPROD = 9, S_GAMMA_NEW = 10, S_GAMMA = 11, S_BETA = 12, S_BIPROD = 13, S_EPS = 14, S_TMP = 15,
@@ -139,7 +140,7 @@ static int apply_precond(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_
 {
    const int n = A->n_rows;
    *z_out = z;
-   if (amg) { return amg_cycle_ptr(amg, r, z, 1, z_out); }
+   if (amg) { return amg_precond_ptr(amg, r, z, z_out); }
    if (prm->diag_scale)
    {
       B200_TRY(parcsr_ensure_L(A));
@@ -204,7 +205,8 @@ static int pcg_launch_iteration(const PcgIter &it, int i)
    // iteration 1 runs on plain launches: it triggers every lazy allocation (transposes, workspaces)
    if (!pcg_graph_enabled(c) || i < 2) { return pcg_enqueue_iteration(it); }
    const void *key[8] = {it.A, it.amg, it.x, it.p, it.s, it.r,
-                         (const void *)(size_t)(it.prm->two_norm * 64 + it.prm->skip_break * 8 + it.prm->diag_scale),
+                         (const void *)(size_t)(it.prm->two_norm * 64 + it.prm->skip_break * 8 + it.prm->diag_scale +
+                                                (it.amg ? 4096 * amg_precond_cycles(it.amg) : 0)),
                          (const void *)(size_t)it.prm->max_iter};
    if (c->pcg_graph == nullptr || memcmp(key, c->pcg_graph_key, sizeof(key)) != 0)
    {

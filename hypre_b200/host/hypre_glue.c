@@ -566,9 +566,9 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
        precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_BoomerAMGSolve)
    {
       hypre_ParAMGData *amg_data = (hypre_ParAMGData *) pcg->precond_data;
-      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) != 1)
+      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) < 1 || hypre_ParAMGDataMinIter(amg_data) > hypre_ParAMGDataMaxIter(amg_data))
       {
-         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 and max_iter 1");
+         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 (a fixed number of cycles, max_iter >= 1)");
          return hypre_error_flag;
       }
       if (hypre_ParAMGDataAArray(amg_data) == NULL || hypre_ParAMGDataAArray(amg_data)[0] != pA)
@@ -579,6 +579,7 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
       m = mirror_for_amg(amg_data);
       if (!m) { GLUE_FAIL("hierarchy upload failed"); return hypre_error_flag; }
       amg = m->amg;
+      b200_amg_set_precond_cycles(amg, (int) hypre_ParAMGDataMaxIter(amg_data));     /* ij -precon_cycles */
    }
    else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_ParCSRDiagScale)
    {
@@ -608,6 +609,11 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
                                 (pcg->logging > 0 || pcg->print_level > 0) ? pcg->norms : NULL,
                                 (pcg->logging > 0 || pcg->print_level > 0) ? pcg->rel_norms : NULL);
    if (status != B200_OK) { GLUE_FAIL("device PCG failed"); return hypre_error_flag; }
+   if (verbose() && g_rank == 0)
+   {
+      fprintf(stderr, "hypre_b200: PCG solve on the device: %d iterations, relative residual %.6e\n",
+              res.num_iterations, res.rel_residual_norm);
+   }
 
    /* the reference's printed table (pcg.c:405-409,536-560,772-792,983-986) */
    if (pcg->print_level > 1 && my_id == 0 && g_rank == 0)
@@ -666,9 +672,9 @@ static mirror_t *krylov_precond_mirror(HYPRE_Int (*precond)(void *, void *, void
        precond == (HYPRE_Int (*)(void *, void *, void *, void *)) hypre_BoomerAMGSolve)
    {
       hypre_ParAMGData *amg_data = (hypre_ParAMGData *) precond_data;
-      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) != 1)
+      if (hypre_ParAMGDataTol(amg_data) != 0.0 || hypre_ParAMGDataMaxIter(amg_data) < 1 || hypre_ParAMGDataMinIter(amg_data) > hypre_ParAMGDataMaxIter(amg_data))
       {
-         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 and max_iter 1");
+         GLUE_FAIL("BoomerAMG as preconditioner must use tol 0 (a fixed number of cycles, max_iter >= 1)");
          return NULL;
       }
       if (hypre_ParAMGDataAArray(amg_data) == NULL || hypre_ParAMGDataAArray(amg_data)[0] != pA)
@@ -679,6 +685,7 @@ static mirror_t *krylov_precond_mirror(HYPRE_Int (*precond)(void *, void *, void
       m = mirror_for_amg(amg_data);
       if (!m) { GLUE_FAIL("hierarchy upload failed"); return NULL; }
       *amg = m->amg;
+      b200_amg_set_precond_cycles(*amg, (int) hypre_ParAMGDataMaxIter(amg_data));    /* ij -precon_cycles */
    }
    else if (precond == (HYPRE_Int (*)(void *, void *, void *, void *)) HYPRE_ParCSRDiagScale)
    {

@@ -216,6 +216,10 @@ int b200_amg_set_level_cheby(b200_amg *amg, int level, const double *ds_h,
  * rank's first row and the per-rank row counts for the gather. */
 int b200_amg_set_coarse_dense(b200_amg *amg, int n_global, const double *A_mat_h,
                               int first_row, const int *rows_per_rank_h);
+/* cycles per application when the hierarchy preconditions a Krylov solver (b200_pcg_solve, b200_gmres_solve,
+ * b200_bicgstab_solve): hypre_ParAMGDataMaxIter with tol 0 -- hypre_BoomerAMGSolve then runs that many cycles
+ * without residual norms (src/parcsr_ls/par_amg_solve.c:257-336; ij -precon_cycles).  Default 1. */
+int b200_amg_set_precond_cycles(b200_amg *amg, int cycles);
 /* finalise: allocates F/U/work vectors, builds transposes and the launch plan */
 int b200_amg_finalize(b200_amg *amg);
 /* one multigrid cycle u <- u + B(f - A u)   (dev pointers, level-0 size)

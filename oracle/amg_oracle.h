@@ -39,6 +39,8 @@ void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat);
 /* N-rank row partition of a level (nblocks+1 starts, copied): only two-stage GS depends on it */
 void orc_amg_set_level_blocks(orc_amg *h, int level, int nblocks, const int *starts);
 int  orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros);
+/* cycles per preconditioner application (hypre_ParAMGDataMaxIter with tol 0; ij -precon_cycles), default 1 */
+void orc_amg_set_precond_cycles(orc_amg *h, int cycles);
 /* returns the iteration count; rel_norms[1..iters] = ||r||/||b|| (two_norm) */
 int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, int two_norm,
              double *norms, double *rel_norms, int *converged);

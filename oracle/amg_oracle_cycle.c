@@ -21,6 +21,7 @@ struct orc_amg {
    orc_level *L;
    int relax_type[4], num_sweeps[4], cycle_type, fcycle, cheby_order, cheby_scale;
    int coarse_n;
+   int precond_cycles;     /* hypre_ParAMGDataMaxIter of a preconditioner (ij -precon_cycles), default 1 */
    double *A_mat, *A_work, *b_vec;
    double *Vtemp, *Ztemp, *Ptemp, *Rtemp;
    int maxn;
@@ -34,6 +35,7 @@ orc_amg *orc_amg_create(int num_levels)
    h->relax_type[1] = h->relax_type[2] = 18; h->relax_type[3] = 9;
    h->num_sweeps[0] = h->num_sweeps[1] = h->num_sweeps[2] = h->num_sweeps[3] = 1;
    h->cycle_type = 1; h->cheby_order = 2; h->cheby_scale = 1;
+   h->precond_cycles = 1;
    return h;
 }
 
@@ -192,6 +194,19 @@ int orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros)
    return err;
 }
 
+void orc_amg_set_precond_cycles(orc_amg *h, int cycles) { h->precond_cycles = cycles < 1 ? 1 : cycles; }
+
+/* BoomerAMG as a preconditioner: hypre_BoomerAMGSolve with tol 0 and max_iter k runs k cycles without looking at
+ * the residual (par_amg_solve.c:257-336; tol > 0 would compute norms); the Krylov solver cleared z before the call
+ * (ClearVector sets all_zeros), so the first cycle starts from a zero guess and the others continue on it. */
+static void orc_amg_precond(orc_amg *h, const double *r, double *z)
+{
+   int k;
+   memset(z, 0, sizeof(double) * (size_t) h->L[0].n);
+   orc_amg_cycle(h, r, z, 1);
+   for (k = 1; k < h->precond_cycles; k++) { orc_amg_cycle(h, r, z, 0); }
+}
+
 static double orc_dot(int n, const double *x, const double *y)
 {
    double s = 0.0;
@@ -214,12 +229,11 @@ int orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, in
    int i = 0, k;
    if (converged) { *converged = 0; }
    if (two_norm) { bi_prod = orc_dot(n, b, b); }
-   else { orc_amg_cycle(h, b, p, 1); bi_prod = orc_dot(n, p, b); }
+   else { orc_amg_precond(h, b, p); bi_prod = orc_dot(n, p, b); }
    eps = tol * tol;
    if (bi_prod <= 0.0) { memcpy(x, b, sizeof(double) * (size_t) n); free(p); free(s); free(r); return 0; }
    orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
-   memset(p, 0, sizeof(double) * (size_t) n);
-   orc_amg_cycle(h, r, p, 1);
+   orc_amg_precond(h, r, p);
    gamma = orc_dot(n, r, p);
    if (norms) { norms[0] = sqrt(two_norm ? orc_dot(n, r, r) : gamma); }
    while ((i + 1) <= max_iter)
@@ -233,8 +247,7 @@ int orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, in
       gamma_old = gamma;
       for (k = 0; k < n; k++) { x[k] += alpha * p[k]; }
       for (k = 0; k < n; k++) { r[k] += -alpha * s[k]; }
-      memset(s, 0, sizeof(double) * (size_t) n);
-      orc_amg_cycle(h, r, s, 1);
+      orc_amg_precond(h, r, s);
       gamma = orc_dot(n, r, s);
       i_prod = two_norm ? orc_dot(n, r, r) : gamma;
       if (norms) { norms[i] = sqrt(i_prod); }
@@ -258,7 +271,7 @@ static void orc_precond(orc_amg *h, int kind, const double *r, double *z)
    orc_level *L0 = &h->L[0];
    const int n = L0->n;
    int k;
-   if (kind == 0) { memset(z, 0, sizeof(double) * (size_t) n); orc_amg_cycle(h, r, z, 1); }
+   if (kind == 0) { orc_amg_precond(h, r, z); }
    else if (kind == 1) { for (k = 0; k < n; k++) { z[k] = r[k] / L0->Aa[L0->Ai[k]]; } }
    else { memcpy(z, r, sizeof(double) * (size_t) n); }
 }

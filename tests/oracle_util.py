@@ -33,6 +33,7 @@ def lib():
         L.orc_relax_gs2_blocks.argtypes = [i, vp, vp, vp, vp, d, i, vp, vp, i, vp]
         L.orc_amg_cycle.argtypes = [vp, vp, vp, i]
         L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
+        L.orc_amg_set_precond_cycles.argtypes = [vp, i]
         L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
@@ -127,6 +128,10 @@ class OracleAMG:
         if dense is not None:
             dense = np.ascontiguousarray(dense)
             L.orc_amg_set_coarse_dense(self.h, dense.shape[0], p(dense))
+        # cycles per application when the solver is a preconditioner (tol 0; ij -precon_cycles)
+        mi = C.c_int(1)
+        amg.GetMaxIter(C.byref(mi))
+        L.orc_amg_set_precond_cycles(self.h, mi.value)
 
     @classmethod
     def from_arrays(cls, levels, relax_type, num_sweeps, cycle_type, fcycle, cheby_order, cheby_scale, dense):
@@ -225,6 +230,9 @@ CASES = {
     "lap27_20_rlx18_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=18, opts={"NumSweeps": 2}),
     "lap7_24_rlx7_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxWt": 0.8}),
     # Chebyshev variant 1 (par_cheby.c:29-33: only the setup's coefficients differ), orders 3 and 4, unscaled
+    # BoomerAMG as preconditioner with three cycles per application (ij -precon_cycles 3; TEST_ij/solvers.jobs:54)
+    "lap7_24_rlx18_pc3": dict(gen="laplacian", dims=(24, 24, 24), rlx=18, opts={"MaxIter": 3}),
+    "lap7_24_rlx16_pc2": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"MaxIter": 2}),
     "lap7_24_rlx16_var1": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyVariant": 1}),
     "lap7_24_rlx16_o4": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyOrder": 4}),
     "lap7_24_rlx16_o3_noscale": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"ChebyOrder": 3, "ChebyScale": 0}),

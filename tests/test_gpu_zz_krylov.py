@@ -50,7 +50,7 @@ def device_solve(ctx, kind, dA, damg, b, x0, diag_scale=0, tol=1e-8, a_tol=0.0, 
 
 
 @pytest.mark.parametrize("kind", ["gmres", "bicgstab"])
-@pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W"])
+@pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
     H.set_device_path(True)
     A, b, x, amg, pcg = O.build_case(H, name)
@@ -58,6 +58,9 @@ def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
     damg = amg.device_mirror()
     dA = C.c_void_p()
     capi.check(capi.lib().b200_amg_level_matrix(damg, 0, C.byref(dA)))
+    mi = C.c_int(1)
+    amg.GetMaxIter(C.byref(mi))                 # cycles per application (ij -precon_cycles); the binding sets it per solve
+    capi.check(capi.lib().b200_amg_set_precond_cycles(damg, mi.value))
     xd, res, norms = device_solve(ctx, kind, dA, damg, b.numpy(), np.zeros(x.size))
     xo, it, no, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size))
     assert res.num_iterations == it and res.converged == conv == 1 and res.error_flag == 0
@@ -150,7 +153,8 @@ def test_interposed_hypre_api_matches_reference_in_process(H, kind):
     np.testing.assert_allclose(x_d, x_r, rtol=1e-8, atol=1e-11)
 
 
-IJ_CASES = ["-laplacian -n 24 24 24 -solver 3 -rlx 16", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
+IJ_CASES = ["-laplacian -n 24 24 24 -solver 3 -rlx 16", "-laplacian -n 23 29 31 -solver 3 -precon_cycles 3 -rlx 18",
+            "-laplacian -n 24 24 24 -solver 1 -rlx 16 -precon_cycles 2", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
             "-laplacian -n 12 11 10 -solver 4", "-27pt -n 20 20 20 -solver 9 -rlx 11", "-laplacian -n 12 11 10 -solver 10"]
 
 

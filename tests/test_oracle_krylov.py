@@ -52,7 +52,7 @@ def _case(H, name):
 
 
 @pytest.mark.parametrize("kind", ["gmres", "bicgstab"])
-@pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W"])
+@pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     H = ref_off
     A, b, x, amg = _case(H, name)
