@@ -40,6 +40,39 @@ struct FMgsStep {
    }
 };
 
+// Classical Gram-Schmidt (COGMRES), four basis vectors per pass:
+//   red[q] = <pi, pj[q]>                                   (hypre_ParKrylovMassInnerProd: one all-reduce for all)
+struct FMassDot4 {
+   static constexpr int NRED = 4; __device__ void init() {}
+   int cnt; const double *pi; const double *pj[4];
+   __device__ void operator()(int i, double *red) const
+   {
+      const double v = pi[i];
+#pragma unroll
+      for (int q = 0; q < 4; q++) { if (q < cnt) { red[q] = fma(v, pj[q][i], red[q]); } }
+   }
+};
+//   pi += sum_q (-h[q]) pj[q]   in the order q = 0..cnt-1 (hypre_SeqVectorMassAxpy, vector_batched.c:236-246),
+//   and on the last pass red0 = <pi, pi>
+struct FMassAxpy4 {
+   static constexpr int NRED = 1;
+   int cnt, last; const double *h_dev; const double *pj[4]; double *pi;
+   double h[4];
+   __device__ void init()
+   {
+#pragma unroll
+      for (int q = 0; q < 4; q++) { h[q] = q < cnt ? h_dev[q] : 0.0; }
+   }
+   __device__ void operator()(int i, double *red) const
+   {
+      double v = pi[i];
+#pragma unroll
+      for (int q = 0; q < 4; q++) { if (q < cnt) { v = fma(-h[q], pj[q][i], v); } }
+      pi[i] = v;
+      if (last) { red[0] = fma(v, v, red[0]); }
+   }
+};
+
 // x += a v ; r -= a q
 struct FBicgHalf {
    static constexpr int NRED = 0; __device__ void init() {}
@@ -73,6 +106,7 @@ struct FBicgDir {
 };
 
 // ---------------------------------------------------------------- device backend of krylov_core.hpp
+constexpr int AR_CHUNK = 128;     // scalars per all-reduce call (p2p_allreduce takes at most 256)
 struct DevKrylovOps {
    b200_ctx *c; b200_parcsr *A; b200_amg *amg; int diag_scale; int n;
    double *d_sc;      // device scalars of this solve (k_dim + 2 doubles behind the work vectors)
@@ -133,6 +167,32 @@ struct DevKrylovOps {
          B200_TRY(run_ewise(c, n, f, d_sc + j + 1));
          B200_TRY(scalars_allreduce(c, d_sc + j + 1, 1));
       }
+      B200_TRY(fetch(i + 1));
+      for (int j = 0; j <= i; j++) { h[j] = h_sc[j]; }
+      return B200_OK;
+   }
+   // COGMRES: ceil(i/4) passes for the i inner products (one all-reduce for all of them), ceil(i/4) passes for
+   // the update, the last of which also yields <p_i, p_i>; d_sc[0..i-1] = h, d_sc[i] = the squared norm
+   int cgs(int i, double *const *p, double *h)
+   {
+      for (int j0 = 0; j0 < i; j0 += 4)
+      {
+         const int cnt = i - j0 < 4 ? i - j0 : 4;
+         FMassDot4 f{cnt, p[i], {p[j0], p[j0 + (cnt > 1 ? 1 : 0)], p[j0 + (cnt > 2 ? 2 : 0)], p[j0 + (cnt > 3 ? 3 : 0)]}};
+         // the reduction writes NRED = 4 scalars: d_sc has k_dim + 2 + 4 entries, later passes overwrite the spill
+         B200_TRY(run_ewise(c, n, f, d_sc + j0));
+      }
+      for (int j0 = 0; j0 < i; j0 += AR_CHUNK) { B200_TRY(scalars_allreduce(c, d_sc + j0, i - j0 < AR_CHUNK ? i - j0 : AR_CHUNK)); }
+      for (int j0 = 0; j0 < i; j0 += 4)
+      {
+         const int cnt = i - j0 < 4 ? i - j0 : 4;
+         const int last = j0 + 4 >= i;
+         FMassAxpy4 f{cnt, last, d_sc + j0, {p[j0], p[j0 + (cnt > 1 ? 1 : 0)], p[j0 + (cnt > 2 ? 2 : 0)], p[j0 + (cnt > 3 ? 3 : 0)]},
+                      p[i], {0.0, 0.0, 0.0, 0.0}};
+         // only the last pass reduces; the others park their (zero) sum in the spare slot behind the column
+         B200_TRY(run_ewise(c, n, f, d_sc + (last ? i : i + 1)));
+      }
+      B200_TRY(scalars_allreduce(c, d_sc + i, 1));
       B200_TRY(fetch(i + 1));
       for (int j = 0; j <= i; j++) { h[j] = h_sc[j]; }
       return B200_OK;
@@ -203,7 +263,8 @@ extern "C" int b200_gmres_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, cons
    const int n = A->n_rows;
    std::vector<double *> vec;
    double *d_sc = nullptr, *h_sc = nullptr;
-   B200_TRY(krylov_workspace(c, n, prm->k_dim + 3, prm->k_dim + 2, &vec, &d_sc, &h_sc));
+   ARG_CHECK(prm->ortho == 0 || prm->ortho == 1);
+   B200_TRY(krylov_workspace(c, n, prm->k_dim + 3, prm->k_dim + 2 + 4, &vec, &d_sc, &h_sc));
    B200_TRY(krylov_prepare(c, A, amg, prm->diag_scale));
    DevKrylovOps ops{c, A, amg, prm->diag_scale, n, d_sc, h_sc};
    // vec[0..k_dim] = the Arnoldi basis p, then r and w (gmres.c:203-240)

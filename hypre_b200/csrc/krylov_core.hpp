@@ -17,6 +17,10 @@
 //   mgs(i, p, h)                        modified Gram-Schmidt of p[i] against p[0..i-1] in that order:
 //                                       h[j] = <p[j], p[i]>, p[i] -= h[j] p[j]  (j = 0..i-1), then
 //                                       h[i] = <p[i], p[i]>; h on the HOST        (gmres.c:552-563)
+//   cgs(i, p, h)                        classical Gram-Schmidt (COGMRES, cogmres.c:553-577 with cgs == 1): h[j] =
+//                                       <p[i], p[j]> for all j < i from the SAME p[i] (MassInnerProd), then
+//                                       p[i] += sum_j (-h[j]) p[j] in the order j = 0..i-1 (MassAxpy), then
+//                                       h[i] = <p[i], p[i]>
 //   bicg_half(alpha, v, q, x, r)        x += alpha v ; r -= alpha q                (bicgstab.c:439-440)
 //   bicg_full(gamma, v, s, r0, x, r, out)   x += gamma v ; r -= gamma s ; out = {<r,r>, <r0,r>}   (:461-464, :525)
 //   bicg_dir(gamma, f, q, r, p)         p = f (p - gamma q) + r                    (:528-540)
@@ -32,7 +36,9 @@
 // true when v is an Inf or a NaN (the reference's ieee_check: v / v != v / v, gmres.c:378-404)
 static inline bool kry_not_finite(double v) { return v != 0.0 && !(v / v == v / v); }
 
-// Right-preconditioned restarted GMRES(k_dim) with rel_change = 0 and cf_tol = 0.
+// Right-preconditioned restarted GMRES(k_dim) with rel_change = 0 and cf_tol = 0; prm->ortho == 1 gives
+// hypre_COGMRESSolve with cgs == 1, which differs from hypre_GMRESSolve in the orthogonalisation only
+// (and stores the same Hessenberg matrix column-major).
 // p: k_dim + 1 basis vectors; r, w: work vectors.  norms_h (HOST, max_iter + 1 entries) may be nullptr.
 template <class B>
 int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x, double *const *p,
@@ -85,7 +91,8 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
          i++; iter++;
          KRY_TRY(ops.precond(p[i - 1], r, &z));
          KRY_TRY(ops.matvec(1.0, z, 0.0, nullptr, p[i]));
-         KRY_TRY(ops.mgs(i, p, col.data()));
+         if (prm->ortho == 1) { KRY_TRY(ops.cgs(i, p, col.data())); }
+         else                 { KRY_TRY(ops.mgs(i, p, col.data())); }
          for (j = 0; j < i; j++) { HH(j, i - 1) = col[j]; }
          t = sqrt(col[i]);
          HH(i, i - 1) = t;

@@ -739,7 +739,8 @@ static void krylov_print_table(const double *norms, int iters, double b_norm)
    }
 }
 
-/* Everything hypre_GMRESSolve (kind 0, print_level > 1) / hypre_BiCGSTABSolve (kind 1, print_level > 0) print
+/* Everything hypre_GMRESSolve (kind 0, print_level > 1) / hypre_COGMRESSolve (kind 2: as GMRES without the closing
+ * blank lines) / hypre_BiCGSTABSolve (kind 1, print_level > 0) print
  * for a solve with this history: table, "Final L2 norm of residual" after the exits that evaluated b - A x
  * (gmres.c:512-520, 783-851, 895-898; bicgstab.c:436-441, 508-512).  Host printing only; exported so that the
  * CPU tests can compare the text with the reference driver's. */
@@ -813,6 +814,73 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    if (g->print_level > 1 && my_id == 0 && g_rank == 0)
    {
       hypre_b200_krylov_report(0, norms, res.num_iterations, res.b_norm, res.rel_residual_norm, res.real_residual_exit);
+   }
+   free(own_norms);
+   g->converged = res.converged;
+   g->num_iterations = res.num_iterations;
+   g->rel_residual_norm = res.rel_residual_norm;
+   hypre_ParVectorAllZeros(px) = 0;
+   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   return hypre_error_flag;
+}
+
+/* hypre_COGMRESSolve (src/krylov/cogmres.c:277-…) for the ParCSR operator table: GMRES with classical
+ * Gram-Schmidt through MassInnerProd / MassAxpy (cgs == 1; `unroll` only regroups the host loops). */
+HYPRE_Int hypre_COGMRESSolve(void *cogmres_vdata, void *A, void *b, void *x)
+{
+   static pcg_solve_fn next = NULL;
+   hypre_COGMRESData      *g  = (hypre_COGMRESData *) cogmres_vdata;
+   hypre_COGMRESFunctions *fn = g->functions;
+   hypre_ParCSRMatrix     *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector        *pb = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
+   mirror_t *m;
+   b200_amg *amg = NULL;
+   b200_gmres_params prm;
+   b200_krylov_result res;
+   HYPRE_Int my_id, num_procs;
+   double *norms, *own_norms = NULL;
+   int status, diag_scale = 0;
+
+   if (!next) { next = (pcg_solve_fn) next_sym("hypre_COGMRESSolve"); }
+   if (!g_enabled) { return next(cogmres_vdata, A, b, x); }
+   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(cogmres_vdata, A, b, x); }
+
+   if (g->rel_change || g->cf_tol > 0.0 || g->cgs > 1 || hypre_ParVectorNumVectors(pb) > 1)
+   {
+      GLUE_FAIL("COGMRES option outside the device path (rel_change / cf_tol / cgs 2 / multivector)");
+      return hypre_error_flag;
+   }
+   m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
+   if (!m) { return hypre_error_flag; }
+
+   memset(&prm, 0, sizeof(prm));
+   prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
+   prm.k_dim = g->k_dim; prm.skip_real_r_check = g->skip_real_r_check; prm.diag_scale = diag_scale;
+   prm.ortho = 1;
+   g->converged = 0;
+   (*(fn->CommInfo))(A, &my_id, &num_procs);
+   norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
+   if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
+
+   status = b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                  hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                  hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   if (status != B200_OK) { free(own_norms); GLUE_FAIL("device COGMRES failed"); return hypre_error_flag; }
+   if (verbose() && g_rank == 0)
+   {
+      fprintf(stderr, "hypre_b200: COGMRES(%d) solve on the device: %d iterations, relative residual %.6e\n",
+              (int) g->k_dim, res.num_iterations, res.rel_residual_norm);
+   }
+   if (res.error_flag & 1)
+   {
+      if (g->logging > 0 || g->print_level > 0) { krylov_nan_message("hypre_COGMRESSolve"); }
+      free(own_norms);
+      hypre_error(HYPRE_ERROR_GENERIC);
+      return hypre_error_flag;
+   }
+   if (g->print_level > 1 && my_id == 0 && g_rank == 0)
+   {
+      hypre_b200_krylov_report(2, norms, res.num_iterations, res.b_norm, res.rel_residual_norm, res.real_residual_exit);
    }
    free(own_norms);
    g->converged = res.converged;

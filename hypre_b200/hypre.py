@@ -40,7 +40,7 @@ def lib():
                  "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
         getattr(L, name).restype = vp
     for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
-                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_bicgstab_norms"):
+                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_bicgstab_norms"):
         getattr(L, name).restype = C.POINTER(d)
     L.hb_amg_relax_weight.restype = d
     L.hb_amg_omega.restype = d
@@ -52,7 +52,8 @@ def lib():
     L.hb_vector_create_cols.argtypes = [vp, d]
     for name in ("hb_vector_destroy", "hb_vector_data", "hb_vector_size", "hb_amg_num_levels", "hb_amg_Vtemp",
                  "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
-                 "hb_gmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
+                 "hb_gmres_norms", "hb_cogmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy",
+                 "HYPRE_ParCSRCOGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
                  "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
                  "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
                  "HYPRE_ParCSRPCGDestroy"):
@@ -444,6 +445,17 @@ class ParCSRGMRES(_ParCSRKrylov):
     _prefix = "HYPRE_GMRES"
     _par = "HYPRE_ParCSRGMRES"
     _norms = "hb_gmres_norms"
+
+    def __init__(self, k_dim=5, **kw):
+        super().__init__(**kw)
+        self.SetKDim(k_dim)
+
+
+class ParCSRCOGMRES(_ParCSRKrylov):
+    """HYPRE_ParCSRCOGMRES* / HYPRE_COGMRES*: ij -solver 16 (AMG) / 17 (diagonal scaling); cgs 1, unroll 0 (ij.c defaults)."""
+    _prefix = "HYPRE_COGMRES"
+    _par = "HYPRE_ParCSRCOGMRES"
+    _norms = "hb_cogmres_norms"
 
     def __init__(self, k_dim=5, **kw):
         super().__init__(**kw)

@@ -278,8 +278,9 @@ int b200_pcg_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200
                         const double *b_h, double *x_h, b200_pcg_result *res,
                         double *norms_h, double *rel_norms_h);
 
-/* --------------------------------------------------- GMRES / BiCGSTAB
- * hypre_GMRESSolve (src/krylov/gmres.c:274-930; ij -solver 3 / 4) and hypre_BiCGSTABSolve
+/* --------------------------------------------------- GMRES / COGMRES / BiCGSTAB
+ * hypre_GMRESSolve (src/krylov/gmres.c:274-930; ij -solver 3 / 4), hypre_COGMRESSolve (src/krylov/cogmres.c;
+ * ij -solver 16 / 17; b200_gmres_params.ortho = 1) and hypre_BiCGSTABSolve
  * (src/krylov/bicgstab.c:226-640; ij -solver 9 / 10) with the ParCSR operator table
  * (src/parcsr_ls/par_krylov_func.c:14-330): right preconditioning by one b200_amg_cycle (amg != NULL),
  * diagonal scaling (diag_scale, HYPRE_ParCSRDiagScale) or nothing.  Options the reference switches off by
@@ -294,6 +295,10 @@ typedef struct {
    int    k_dim;             /* restart length (HYPRE_GMRESSetKDim; ij default 5) */
    int    skip_real_r_check; /* gmres.c:767-771 */
    int    diag_scale;        /* as b200_pcg_params */
+   int    ortho;             /* 0: modified Gram-Schmidt = hypre_GMRESSolve; 1: classical Gram-Schmidt with one
+                              * multi-vector inner product and one multi-vector axpy per iteration =
+                              * hypre_COGMRESSolve with cgs 1 (src/krylov/cogmres.c:289-…; MassInnerProd / MassAxpy,
+                              * src/parcsr_ls/par_krylov_func.c:195-262; ij -solver 16 / 17) */
 } b200_gmres_params;
 
 typedef struct {

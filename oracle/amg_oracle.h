@@ -51,6 +51,10 @@ int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, i
 int  orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
                int *converged);
+/* hypre_COGMRESSolve (krylov/cogmres.c, cgs = 1): as orc_gmres with classical Gram-Schmidt */
+int  orc_cogmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+                 int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
+                 int *converged);
 /* hypre_BiCGSTABSolve (krylov/bicgstab.c:226-640, stop_crit = 0, cf_tol = 0): iteration count, or
  * -(iter) - 1 where the reference reports a breakdown */
 int  orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol,

@@ -280,8 +280,9 @@ static void orc_precond(orc_amg *h, int kind, const double *r, double *z)
  * right-preconditioned restarted GMRES(k_dim), modified Gram-Schmidt, Givens rotations, true-residual
  * check on convergence.  norms[0..iters] = the residual norms the reference logs.  Returns the iteration
  * count; *converged as gmres_data->converged; *rel_resid as gmres_data->rel_residual_norm. */
-int orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
-              int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
+static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+                          int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
+                          int *converged, int cgs)
 {
    orc_level *L0 = &h->L[0];
    const int n = L0->n;
@@ -326,10 +327,20 @@ int orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double t
          i++; iter++;
          orc_precond(h, precond_kind, p[i - 1], r);
          orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, NULL, p[i]);
-         for (j = 0; j < i; j++)
+         if (cgs)
          {
-            hh[j][i - 1] = orc_dot(n, p[j], p[i]);
-            for (q = 0; q < n; q++) { p[i][q] += -hh[j][i - 1] * p[j][q]; }
+            /* hypre_COGMRESSolve with cgs == 1 (cogmres.c:553-577): all inner products from the same p[i]
+             * (MassInnerProd), then one multi-vector update (MassAxpy, vector_batched.c:212-247) */
+            for (j = 0; j < i; j++) { hh[j][i - 1] = orc_dot(n, p[i], p[j]); }
+            for (j = 0; j < i; j++) { for (q = 0; q < n; q++) { p[i][q] += -hh[j][i - 1] * p[j][q]; } }
+         }
+         else
+         {
+            for (j = 0; j < i; j++)
+            {
+               hh[j][i - 1] = orc_dot(n, p[j], p[i]);
+               for (q = 0; q < n; q++) { p[i][q] += -hh[j][i - 1] * p[j][q]; }
+            }
          }
          t = sqrt(orc_dot(n, p[i], p[i]));
          hh[i][i - 1] = t;
@@ -398,6 +409,22 @@ finish_no_norm:
    for (i = 0; i <= k_dim; i++) { free(p[i]); free(hh[i]); }
    free(p); free(hh); free(r); free(w); free(rs); free(c); free(s);
    return iter;
+}
+
+int orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+              int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
+{
+   return orc_gmres_impl(h, precond_kind, b, x, tol, a_tol, k_dim, min_iter, max_iter, skip_real_r_check, norms,
+                         rel_resid, converged, 0);
+}
+
+/* hypre_COGMRESSolve (krylov/cogmres.c) with cgs = 1, rel_change = 0, cf_tol = 0 (ij -solver 16/17): GMRES with
+ * classical Gram-Schmidt through MassInnerProd / MassAxpy; everything else as hypre_GMRESSolve */
+int orc_cogmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+                int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
+{
+   return orc_gmres_impl(h, precond_kind, b, x, tol, a_tol, k_dim, min_iter, max_iter, skip_real_r_check, norms,
+                         rel_resid, converged, 1);
 }
 
 /* hypre_BiCGSTABSolve (krylov/bicgstab.c:226-640) with stop_crit = 0 and cf_tol = 0 (ij -solver 9/10).

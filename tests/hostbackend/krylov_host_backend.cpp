@@ -58,6 +58,13 @@ struct HostKrylovOps {
       h[i] = dot(n, p[i], p[i]);
       return B200_OK;
    }
+   int cgs(int i, double *const *p, double *h)
+   {
+      for (int j = 0; j < i; j++) { h[j] = dot(n, p[i], p[j]); }
+      for (int j = 0; j < i; j++) { for (int k = 0; k < n; k++) { p[i][k] += -h[j] * p[j][k]; } }
+      h[i] = dot(n, p[i], p[i]);
+      return B200_OK;
+   }
    int bicg_half(double al, const double *v, const double *q, double *x, double *r)
    {
       for (int k = 0; k < n; k++) { x[k] += al * v[k]; }

@@ -35,6 +35,7 @@ def lib():
         L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
         L.orc_amg_set_precond_cycles.argtypes = [vp, i]
         L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
+        L.orc_cogmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
@@ -185,12 +186,17 @@ class OracleAMG:
                            C.byref(conv))
         return x, it, rel[1:it + 1].copy(), conv.value
 
-    def gmres(self, b, x0, precond=0, tol=1e-8, a_tol=0.0, k_dim=5, min_iter=0, max_iter=100, skip_real_r_check=0):
+    def cogmres(self, b, x0, **kw):
+        """orc_cogmres (classical Gram-Schmidt): same arguments and results as gmres"""
+        return self.gmres(b, x0, _fn="orc_cogmres", **kw)
+
+    def gmres(self, b, x0, precond=0, tol=1e-8, a_tol=0.0, k_dim=5, min_iter=0, max_iter=100, skip_real_r_check=0,
+              _fn="orc_gmres"):
         """orc_gmres: (x, iterations, norms[0..iterations], final relative residual, converged)"""
         x = np.array(x0, dtype=np.float64, copy=True)
         norms = np.zeros(max_iter + 1)
         rel, conv = C.c_double(), C.c_int()
-        it = lib().orc_gmres(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, k_dim, min_iter, max_iter,
+        it = getattr(lib(), _fn)(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, k_dim, min_iter, max_iter,
                              skip_real_r_check, p(norms), C.byref(rel), C.byref(conv))
         return x, it, norms[:it + 1].copy(), rel.value, conv.value
 

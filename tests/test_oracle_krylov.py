@@ -32,8 +32,9 @@ def ref_off(H):
 
 
 def _solver(H, kind, amg, k_dim=5, tol=1e-8, max_iter=100):
-    if kind == "gmres":
-        s = H.ParCSRGMRES(k_dim=k_dim, tol=tol, max_iter=max_iter, print_level=1)   # print_level 1: norms[] logged
+    if kind in ("gmres", "cogmres"):
+        cls = H.ParCSRGMRES if kind == "gmres" else H.ParCSRCOGMRES
+        s = cls(k_dim=k_dim, tol=tol, max_iter=max_iter, print_level=1)   # print_level 1: norms[] logged
     else:
         s = H.ParCSRBiCGSTAB(tol=tol, max_iter=max_iter, print_level=0, logging=1)
     if amg is not None:
@@ -51,7 +52,7 @@ def _case(H, name):
     return A, b, x, amg
 
 
-@pytest.mark.parametrize("kind", ["gmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     H = ref_off
@@ -70,7 +71,8 @@ def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind,k_dim", [("gmres", 5), ("gmres", 3), ("gmres", 20), ("bicgstab", 0)])
+@pytest.mark.parametrize("kind,k_dim", [("gmres", 5), ("gmres", 3), ("gmres", 20), ("cogmres", 5), ("cogmres", 9), ("cogmres", 20),
+                                        ("bicgstab", 0)])
 def test_oracle_diagscale_krylov_matches_reference(ref_off, kind, k_dim):
     """ij -solver 4 / 10: diagonal scaling, many iterations, several GMRES restarts"""
     H = ref_off
@@ -85,7 +87,7 @@ def test_oracle_diagscale_krylov_matches_reference(ref_off, kind, k_dim):
     Ad, _ = A.blocks()
     orc = O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
     kw = dict(precond=1, max_iter=500)
-    if kind == "gmres":
+    if kind != "bicgstab":
         kw["k_dim"] = k_dim
     xo, it, norms, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size), **kw)
     assert it == s.num_iterations and it > 10 and conv == s.converged == 1
@@ -121,6 +123,8 @@ def test_oracle_gmres_max_iter_and_nonzero_guess(ref_off):
 IJ_KRYLOV = {
     "gmres_amg": ("-laplacian -n 24 24 24 -solver 3 -rlx 16", "gmres", 0),
     "gmres_ds": ("-laplacian -n 12 11 10 -solver 4", "gmres", 1),
+    "cogmres_amg": ("-laplacian -n 24 24 24 -solver 16 -rlx 18", "cogmres", 0),
+    "cogmres_ds": ("-laplacian -n 12 11 10 -solver 17", "cogmres", 1),
     "bicgstab_amg": ("-27pt -n 20 20 20 -solver 9 -rlx 11", "bicgstab", 0),
     "bicgstab_ds": ("-laplacian -n 12 11 10 -solver 10", "bicgstab", 1),
 }
