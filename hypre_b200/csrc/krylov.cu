@@ -264,11 +264,13 @@ extern "C" int b200_gmres_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, cons
    std::vector<double *> vec;
    double *d_sc = nullptr, *h_sc = nullptr;
    ARG_CHECK(prm->ortho == 0 || prm->ortho == 1);
-   B200_TRY(krylov_workspace(c, n, prm->k_dim + 3, prm->k_dim + 2 + 4, &vec, &d_sc, &h_sc));
+   // flexible GMRES keeps k_dim preconditioned vectors behind p[0..k_dim], r, w
+   B200_TRY(krylov_workspace(c, n, prm->k_dim + 3 + (prm->flex ? prm->k_dim : 0), prm->k_dim + 2 + 4, &vec, &d_sc, &h_sc));
    B200_TRY(krylov_prepare(c, A, amg, prm->diag_scale));
    DevKrylovOps ops{c, A, amg, prm->diag_scale, n, d_sc, h_sc};
    // vec[0..k_dim] = the Arnoldi basis p, then r and w (gmres.c:203-240)
-   const int status = gmres_core(ops, prm, b, x, vec.data(), vec[prm->k_dim + 1], vec[prm->k_dim + 2], res, norms_h);
+   const int status = gmres_core(ops, prm, b, x, vec.data(), vec[prm->k_dim + 1], vec[prm->k_dim + 2], res, norms_h,
+                                 prm->flex ? vec.data() + prm->k_dim + 3 : nullptr);
    return krylov_finish(c, status);
 }
 

@@ -40,10 +40,12 @@ static inline bool kry_not_finite(double v) { return v != 0.0 && !(v / v == v / 
 // hypre_COGMRESSolve with cgs == 1, which differs from hypre_GMRESSolve in the orthogonalisation only
 // (and stores the same Hessenberg matrix column-major).
 // p: k_dim + 1 basis vectors; r, w: work vectors.  norms_h (HOST, max_iter + 1 entries) may be nullptr.
+// prm->flex == 1 gives hypre_FlexGMRESSolve (flexgmres.c): pp = k_dim further vectors that keep C p[j].
 template <class B>
 int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x, double *const *p,
-               double *r, double *w, b200_krylov_result *res, double *norms_h)
+               double *r, double *w, b200_krylov_result *res, double *norms_h, double *const *pp = nullptr)
 {
+   const bool flex = prm->flex != 0;
    const int k_dim = prm->k_dim, max_iter = prm->max_iter, min_iter = prm->min_iter;
    const double epsmac = 1.e-16;
    std::vector<double> rs(k_dim + 1, 0.0), c(k_dim, 0.0), s(k_dim, 0.0), col(k_dim + 2, 0.0);
@@ -89,7 +91,14 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
       while (i < k_dim && iter < max_iter)                                    // restart cycle, :536-726
       {
          i++; iter++;
-         KRY_TRY(ops.precond(p[i - 1], r, &z));
+         if (flex)
+         {
+            // flexgmres.c:470-480: the preconditioned vector is stored (pre_vecs[i-1])
+            KRY_TRY(ops.precond(p[i - 1], pp[i - 1], &z));
+            if (z != pp[i - 1]) { KRY_TRY(ops.copy(z, pp[i - 1])); }
+            z = pp[i - 1];
+         }
+         else { KRY_TRY(ops.precond(p[i - 1], r, &z)); }
          KRY_TRY(ops.matvec(1.0, z, 0.0, nullptr, p[i]));
          if (prm->ortho == 1) { KRY_TRY(ops.cgs(i, p, col.data())); }
          else                 { KRY_TRY(ops.mgs(i, p, col.data())); }
@@ -127,23 +136,34 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
          t += rs[k];
          rs[k] = t / HH(k, k);
       }
-      KRY_TRY(ops.copy(p[i - 1], w));
-      KRY_TRY(ops.scale(rs[i - 1], w));
-      for (j = i - 2; j >= 0; j--) { KRY_TRY(ops.axpy(rs[j], p[j], w)); }
-      KRY_TRY(ops.precond(w, r, &z));
-      KRY_TRY(ops.axpy(1.0, z, x));
+      if (flex)
+      {
+         // linear combination of the stored preconditioned vectors (flexgmres.c:575-590)
+         KRY_TRY(ops.copy(pp[i - 1], w));
+         KRY_TRY(ops.scale(rs[i - 1], w));
+         for (j = i - 2; j >= 0; j--) { KRY_TRY(ops.axpy(rs[j], pp[j], w)); }
+         KRY_TRY(ops.axpy(1.0, w, x));
+      }
+      else
+      {
+         KRY_TRY(ops.copy(p[i - 1], w));
+         KRY_TRY(ops.scale(rs[i - 1], w));
+         for (j = i - 2; j >= 0; j--) { KRY_TRY(ops.axpy(rs[j], p[j], w)); }
+         KRY_TRY(ops.precond(w, r, &z));
+         KRY_TRY(ops.axpy(1.0, z, x));
+      }
 
       // convergence: evaluate the actual residual (:765-871)
       if (r_norm <= epsilon && iter >= min_iter)
       {
-         if (prm->skip_real_r_check) { res->converged = 1; break; }
+         if (prm->skip_real_r_check && !flex) { res->converged = 1; break; }
          KRY_TRY(ops.matvec(-1.0, x, 1.0, b, r));
          const double *xs[1] = {r};
          KRY_TRY(ops.dots(1, xs, xs, d2));
          real_r_norm_new = r_norm = sqrt(d2[0]);
          if (r_norm <= epsilon) { res->converged = 1; res->real_residual_exit = 1; break; }
          // the true residual disagrees: stop if it no longer decreases, else restart from it
-         if (real_r_norm_new >= real_r_norm_old) { res->converged = 1; res->real_residual_exit = 1; break; }
+         if (!flex && real_r_norm_new >= real_r_norm_old) { res->converged = 1; res->real_residual_exit = 1; break; }
          KRY_TRY(ops.copy(r, p[0]));
          i = 0;
          real_r_norm_old = real_r_norm_new;

@@ -299,6 +299,10 @@ typedef struct {
                               * multi-vector inner product and one multi-vector axpy per iteration =
                               * hypre_COGMRESSolve with cgs 1 (src/krylov/cogmres.c:289-…; MassInnerProd / MassAxpy,
                               * src/parcsr_ls/par_krylov_func.c:195-262; ij -solver 16 / 17) */
+   int    flex;              /* 1: flexible GMRES = hypre_FlexGMRESSolve (src/krylov/flexgmres.c:282-…; ij -solver 61 / 60)
+                              * with the default (empty) modify_pc: the preconditioned basis vectors are kept and
+                              * the solution is updated from them without a further preconditioner application;
+                              * true-residual check without the "residual no longer decreases" exit */
 } b200_gmres_params;
 
 typedef struct {

@@ -51,6 +51,10 @@ int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, i
 int  orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
                int *converged);
+/* hypre_FlexGMRESSolve (krylov/flexgmres.c, default modify_pc): skip_real_r_check is ignored (the reference has none) */
+int  orc_flexgmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+                   int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
+                   int *converged);
 /* hypre_COGMRESSolve (krylov/cogmres.c, cgs = 1): as orc_gmres with classical Gram-Schmidt */
 int  orc_cogmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                  int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,

@@ -282,7 +282,7 @@ static void orc_precond(orc_amg *h, int kind, const double *r, double *z)
  * count; *converged as gmres_data->converged; *rel_resid as gmres_data->rel_residual_norm. */
 static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                           int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
-                          int *converged, int cgs)
+                          int *converged, int cgs, int flex)
 {
    orc_level *L0 = &h->L[0];
    const int n = L0->n;
@@ -294,12 +294,14 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
    double *c = (double *) calloc((size_t) k_dim, sizeof(double));
    double *s = (double *) calloc((size_t) k_dim, sizeof(double));
    double **hh = (double **) calloc((size_t) k_dim + 1, sizeof(double *));
+   double **pv = (double **) calloc((size_t) k_dim + 1, sizeof(double *));   /* flexgmres.c: pre_vecs */
    double b_norm, r_norm, den_norm, epsilon, t, gamma, real_r_norm_old, real_r_norm_new;
    int i, j, k, q, iter = 0;
    for (i = 0; i <= k_dim; i++)
    {
       p[i] = (double *) calloc((size_t) n, sizeof(double));
       hh[i] = (double *) calloc((size_t) k_dim, sizeof(double));
+      pv[i] = flex ? (double *) calloc((size_t) n, sizeof(double)) : NULL;
    }
    if (converged) { *converged = 0; }
    orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, p[0]);
@@ -325,8 +327,16 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
       while (i < k_dim && iter < max_iter)
       {
          i++; iter++;
-         orc_precond(h, precond_kind, p[i - 1], r);
-         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, NULL, p[i]);
+         if (flex)
+         {
+            orc_precond(h, precond_kind, p[i - 1], pv[i - 1]);
+            orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, pv[i - 1], 0.0, NULL, p[i]);
+         }
+         else
+         {
+            orc_precond(h, precond_kind, p[i - 1], r);
+            orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, NULL, p[i]);
+         }
          if (cgs)
          {
             /* hypre_COGMRESSolve with cgs == 1 (cogmres.c:553-577): all inner products from the same p[i]
@@ -374,18 +384,31 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
          t += rs[k];
          rs[k] = t / hh[k][k];
       }
-      memcpy(w, p[i - 1], sizeof(double) * (size_t) n);
-      for (q = 0; q < n; q++) { w[q] *= rs[i - 1]; }
-      for (j = i - 2; j >= 0; j--) { for (q = 0; q < n; q++) { w[q] += rs[j] * p[j][q]; } }
-      orc_precond(h, precond_kind, w, r);
-      for (q = 0; q < n; q++) { x[q] += r[q]; }
+      if (flex)
+      {
+         /* hypre_FlexGMRESSolve (flexgmres.c:575-592): the correction is a combination of the stored
+          * preconditioned vectors */
+         memcpy(w, pv[i - 1], sizeof(double) * (size_t) n);
+         for (q = 0; q < n; q++) { w[q] *= rs[i - 1]; }
+         for (j = i - 2; j >= 0; j--) { for (q = 0; q < n; q++) { w[q] += rs[j] * pv[j][q]; } }
+         for (q = 0; q < n; q++) { x[q] += w[q]; }
+      }
+      else
+      {
+         memcpy(w, p[i - 1], sizeof(double) * (size_t) n);
+         for (q = 0; q < n; q++) { w[q] *= rs[i - 1]; }
+         for (j = i - 2; j >= 0; j--) { for (q = 0; q < n; q++) { w[q] += rs[j] * p[j][q]; } }
+         orc_precond(h, precond_kind, w, r);
+         for (q = 0; q < n; q++) { x[q] += r[q]; }
+      }
       if (r_norm <= epsilon && iter >= min_iter)
       {
-         if (skip_real_r_check) { if (converged) { *converged = 1; } break; }
+         if (skip_real_r_check && !flex) { if (converged) { *converged = 1; } break; }
          orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
          real_r_norm_new = r_norm = sqrt(orc_dot(n, r, r));
          if (r_norm <= epsilon) { if (converged) { *converged = 1; } break; }
-         if (real_r_norm_new >= real_r_norm_old) { if (converged) { *converged = 1; } break; }
+         /* flexgmres.c:598-618 has no "residual no longer decreases" exit */
+         if (!flex && real_r_norm_new >= real_r_norm_old) { if (converged) { *converged = 1; } break; }
          memcpy(p[0], r, sizeof(double) * (size_t) n);
          i = 0;
          real_r_norm_old = real_r_norm_new;
@@ -406,8 +429,8 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
    }
    if (rel_resid) { *rel_resid = b_norm > 0.0 ? r_norm / b_norm : r_norm; }
 finish_no_norm:
-   for (i = 0; i <= k_dim; i++) { free(p[i]); free(hh[i]); }
-   free(p); free(hh); free(r); free(w); free(rs); free(c); free(s);
+   for (i = 0; i <= k_dim; i++) { free(p[i]); free(hh[i]); free(pv[i]); }
+   free(p); free(hh); free(pv); free(r); free(w); free(rs); free(c); free(s);
    return iter;
 }
 
@@ -415,7 +438,15 @@ int orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double t
               int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
 {
    return orc_gmres_impl(h, precond_kind, b, x, tol, a_tol, k_dim, min_iter, max_iter, skip_real_r_check, norms,
-                         rel_resid, converged, 0);
+                         rel_resid, converged, 0, 0);
+}
+
+/* hypre_FlexGMRESSolve (krylov/flexgmres.c) with the default modify_pc (ij -solver 61 AMG / 60 diagonal scaling) */
+int orc_flexgmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+                  int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
+{
+   return orc_gmres_impl(h, precond_kind, b, x, tol, a_tol, k_dim, min_iter, max_iter, skip_real_r_check, norms,
+                         rel_resid, converged, 0, 1);
 }
 
 /* hypre_COGMRESSolve (krylov/cogmres.c) with cgs = 1, rel_change = 0, cf_tol = 0 (ij -solver 16/17): GMRES with
@@ -424,7 +455,7 @@ int orc_cogmres(orc_amg *h, int precond_kind, const double *b, double *x, double
                 int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid, int *converged)
 {
    return orc_gmres_impl(h, precond_kind, b, x, tol, a_tol, k_dim, min_iter, max_iter, skip_real_r_check, norms,
-                         rel_resid, converged, 1);
+                         rel_resid, converged, 1, 0);
 }
 
 /* hypre_BiCGSTABSolve (krylov/bicgstab.c:226-640) with stop_crit = 0 and cf_tol = 0 (ij -solver 9/10).

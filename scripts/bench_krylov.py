@@ -48,14 +48,15 @@ def main():
             prm, res = capi.PcgParams(1e-8, 0.0, 1000, 1, 0, 0), capi.PcgResult()
             return res, lambda: capi.check(L.b200_pcg_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
                                                             capi.ptr(norms), capi.ptr(rel)))
-        if kind in ("gmres", "cogmres"):
-            prm, res = capi.GmresParams(1e-8, 0.0, 1000, 0, args.k, 0, 0, 1 if kind == "cogmres" else 0), capi.KrylovResult()
+        if kind in ("gmres", "cogmres", "flexgmres"):
+            prm = capi.GmresParams(1e-8, 0.0, 1000, 0, args.k, 0, 0, 1 if kind == "cogmres" else 0, 1 if kind == "flexgmres" else 0)
+            res = capi.KrylovResult()
             return res, lambda: capi.check(L.b200_gmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
                                                               capi.ptr(norms)))
         prm, res = capi.BicgstabParams(1e-8, 0.0, 1000, 0, 0), capi.KrylovResult()
         return res, lambda: capi.check(L.b200_bicgstab_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
                                                              capi.ptr(norms)))
-    for kind in ("pcg", "gmres", "cogmres", "bicgstab"):
+    for kind in ("pcg", "gmres", "cogmres", "flexgmres", "bicgstab"):
         res, run = solver(kind)
 
         def step():
@@ -75,7 +76,7 @@ def main():
                           "dof_it_per_s": n * it * args.steps / (ms.value * 1e-3),
                           "rel_residual": res.rel_residual_norm, "converged": res.converged,
                           "launches_per_solve": (L.b200_ctx_launch_count(ctx) - l0) / args.steps,
-                          "k_dim": args.k if kind in ("gmres", "cogmres") else None}))
+                          "k_dim": args.k if "gmres" in kind else None}))
 
 
 if __name__ == "__main__":

@@ -92,10 +92,11 @@ extern "C" int kht_gmres(int n, const int *ia, const int *ja, const double *a, o
                          double *norms)
 {
    HostKrylovOps ops{n, ia, ja, a, amg, kind};
-   std::vector<std::vector<double>> store(prm->k_dim + 3, std::vector<double>((size_t)n, 0.0));
+   std::vector<std::vector<double>> store(prm->k_dim + 3 + (prm->flex ? prm->k_dim : 0), std::vector<double>((size_t)n, 0.0));
    std::vector<double *> vec;
    for (auto &v : store) { vec.push_back(v.data()); }
-   return gmres_core(ops, prm, b, x, vec.data(), vec[prm->k_dim + 1], vec[prm->k_dim + 2], res, norms);
+   return gmres_core(ops, prm, b, x, vec.data(), vec[prm->k_dim + 1], vec[prm->k_dim + 2], res, norms,
+                     prm->flex ? vec.data() + prm->k_dim + 3 : nullptr);
 }
 
 extern "C" int kht_bicgstab(int n, const int *ia, const int *ja, const double *a, orc_amg *amg, int kind,

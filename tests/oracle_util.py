@@ -36,6 +36,7 @@ def lib():
         L.orc_amg_set_precond_cycles.argtypes = [vp, i]
         L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_cogmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
+        L.orc_flexgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
@@ -185,6 +186,10 @@ class OracleAMG:
         it = lib().orc_pcg(self.h, p(np.ascontiguousarray(b)), p(x), tol, max_iter, two_norm, p(norms), p(rel),
                            C.byref(conv))
         return x, it, rel[1:it + 1].copy(), conv.value
+
+    def flexgmres(self, b, x0, **kw):
+        """orc_flexgmres (preconditioned basis kept): same arguments and results as gmres"""
+        return self.gmres(b, x0, _fn="orc_flexgmres", **kw)
 
     def cogmres(self, b, x0, **kw):
         """orc_cogmres (classical Gram-Schmidt): same arguments and results as gmres"""

@@ -1,5 +1,5 @@
 """GPU tests, collected last (first GPU run pending -- written in a session without GPU minutes): GMRES(k),
-COGMRES(k) and BiCGSTAB on the device (hypre_b200/csrc/krylov.cu) behind hypre_GMRESSolve / hypre_BiCGSTABSolve
+COGMRES(k), FlexGMRES(k) and BiCGSTAB on the device (hypre_b200/csrc/krylov.cu) behind hypre_GMRESSolve / hypre_BiCGSTABSolve
 (src/krylov/gmres.c:274-930, bicgstab.c:226-640).
 
  * C-ABI (b200_gmres_solve / b200_bicgstab_solve) against the plain-C oracle, which tests/test_oracle_krylov.py
@@ -38,8 +38,9 @@ def device_solve(ctx, kind, dA, damg, b, x0, diag_scale=0, tol=1e-8, a_tol=0.0, 
     db, dx = capi.DeviceVector(ctx, n, b), capi.DeviceVector(ctx, n, x0)
     norms = np.zeros(max_iter + 1)
     res = capi.KrylovResult()
-    if kind in ("gmres", "cogmres"):
-        prm = capi.GmresParams(tol, a_tol, max_iter, min_iter, k_dim, skip, diag_scale, 1 if kind == "cogmres" else 0)
+    if kind in ("gmres", "cogmres", "flexgmres"):
+        prm = capi.GmresParams(tol, a_tol, max_iter, min_iter, k_dim, skip, diag_scale, 1 if kind == "cogmres" else 0,
+                               1 if kind == "flexgmres" else 0)
         capi.check(L.b200_gmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res), capi.ptr(norms)))
     else:
         prm = capi.BicgstabParams(tol, a_tol, max_iter, min_iter, diag_scale)
@@ -49,7 +50,7 @@ def device_solve(ctx, kind, dA, damg, b, x0, diag_scale=0, tol=1e-8, a_tol=0.0, 
     return x, res, norms
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
     H.set_device_path(True)
@@ -71,6 +72,7 @@ def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
 
 @pytest.mark.parametrize("kind,k_dim,diag", [("gmres", 5, 1), ("gmres", 3, 1), ("gmres", 20, 1), ("gmres", 7, 0),
                                              ("cogmres", 5, 1), ("cogmres", 13, 1), ("cogmres", 6, 0),
+                                             ("flexgmres", 5, 1), ("flexgmres", 11, 0),
                                              ("bicgstab", 0, 1), ("bicgstab", 0, 0)])
 def test_device_long_runs_and_restarts_match_oracle(H, ctx, kind, k_dim, diag):
     """diagonal scaling / no preconditioner on a 7-pt Laplacian: many iterations and restart cycles"""
@@ -100,7 +102,7 @@ def test_device_long_runs_and_restarts_match_oracle(H, ctx, kind, k_dim, diag):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
 def test_device_exits(H, ctx, kind):
     """max_iter exit (HYPRE_ERROR_CONV), zero right-hand side, Inf in b, nonzero initial guess"""
     A = H.laplacian(10, 9, 8)
@@ -128,7 +130,7 @@ def test_device_exits(H, ctx, kind):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
 def test_interposed_hypre_api_matches_reference_in_process(H, kind):
     """HYPRE_ParCSRGMRESSolve / HYPRE_ParCSRBiCGSTABSolve: device path and the reference's CPU loop on the same
     objects in one process"""
@@ -137,7 +139,7 @@ def test_interposed_hypre_api_matches_reference_in_process(H, kind):
         A = H.laplacian(24, 24, 24)
         b, x = A.vector(1.0), A.vector(0.0)
         amg = H.BoomerAMG(relax_type=16)
-        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES}[kind](print_level=1) if kind != "bicgstab" else H.ParCSRBiCGSTAB()
+        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES}[kind](print_level=1) if kind != "bicgstab" else H.ParCSRBiCGSTAB()
         s.SetPrecond(amg)
         s.Setup(A, b, x)
         H.clear_errors()
@@ -157,6 +159,7 @@ def test_interposed_hypre_api_matches_reference_in_process(H, kind):
 IJ_CASES = ["-laplacian -n 24 24 24 -solver 3 -rlx 16", "-laplacian -n 23 29 31 -solver 3 -precon_cycles 3 -rlx 18",
             "-laplacian -n 24 24 24 -solver 1 -rlx 16 -precon_cycles 2", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
             "-laplacian -n 12 11 10 -solver 4", "-laplacian -n 24 24 24 -solver 16 -rlx 18", "-laplacian -n 12 11 10 -solver 17",
+            "-laplacian -n 24 24 24 -solver 61 -rlx 18", "-laplacian -n 12 11 10 -solver 60",
             "-27pt -n 20 20 20 -solver 9 -rlx 11", "-laplacian -n 12 11 10 -solver 10"]
 
 
@@ -177,7 +180,7 @@ def test_unchanged_ij_gmres_bicgstab_on_the_device(args):
     it_d, fin_d, rows_d, out_d = run(IJ_B200)
     it_r, fin_r, rows_r, _ = run(IJ_REF)
     assert "solve on the device" in out_d            # not the reference's CPU loop
-    long_run = any(k in args for k in ("-solver 4", "-solver 10", "-solver 17"))
+    long_run = any(k in args for k in ("-solver 4", "-solver 10", "-solver 17", "-solver 60"))
     assert abs(it_d - it_r) <= (1 if long_run else 0), (it_d, it_r)
     m = min(len(rows_d), len(rows_r))
     assert m >= min(it_d, it_r) - 1 and m > 0       # the binding prints the reference's residual table

@@ -32,8 +32,8 @@ def ref_off(H):
 
 
 def _solver(H, kind, amg, k_dim=5, tol=1e-8, max_iter=100):
-    if kind in ("gmres", "cogmres"):
-        cls = H.ParCSRGMRES if kind == "gmres" else H.ParCSRCOGMRES
+    if kind in ("gmres", "cogmres", "flexgmres"):
+        cls = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES}[kind]
         s = cls(k_dim=k_dim, tol=tol, max_iter=max_iter, print_level=1)   # print_level 1: norms[] logged
     else:
         s = H.ParCSRBiCGSTAB(tol=tol, max_iter=max_iter, print_level=0, logging=1)
@@ -44,6 +44,11 @@ def _solver(H, kind, amg, k_dim=5, tol=1e-8, max_iter=100):
     return s
 
 
+def _converged(s):
+    """hypre_*Data.converged; HYPRE_FlexGMRESGetConverged exists like the GMRES one"""
+    return s.converged
+
+
 def _case(H, name):
     c = O.CASES[name]
     A = getattr(H, c["gen"])(*c["dims"])
@@ -52,7 +57,7 @@ def _case(H, name):
     return A, b, x, amg
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     H = ref_off
@@ -64,7 +69,7 @@ def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     assert H.error_flag() == 0
     orc = O.OracleAMG(amg)
     xo, it, norms, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size))
-    assert it == s.num_iterations and conv == s.converged == 1
+    assert it == s.num_iterations and conv == _converged(s) == 1
     np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
     np.testing.assert_allclose(rel, s.final_rel_norm, rtol=1e-9)
     np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
@@ -72,7 +77,7 @@ def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
 
 
 @pytest.mark.parametrize("kind,k_dim", [("gmres", 5), ("gmres", 3), ("gmres", 20), ("cogmres", 5), ("cogmres", 9), ("cogmres", 20),
-                                        ("bicgstab", 0)])
+                                        ("flexgmres", 5), ("flexgmres", 8), ("bicgstab", 0)])
 def test_oracle_diagscale_krylov_matches_reference(ref_off, kind, k_dim):
     """ij -solver 4 / 10: diagonal scaling, many iterations, several GMRES restarts"""
     H = ref_off
@@ -90,7 +95,7 @@ def test_oracle_diagscale_krylov_matches_reference(ref_off, kind, k_dim):
     if kind != "bicgstab":
         kw["k_dim"] = k_dim
     xo, it, norms, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size), **kw)
-    assert it == s.num_iterations and it > 10 and conv == s.converged == 1
+    assert it == s.num_iterations and it > 10 and conv == _converged(s) == 1
     # long recurrences: rounding differences of the compiled reference (same operations, same order) stay tiny
     np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
     np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
@@ -125,6 +130,8 @@ IJ_KRYLOV = {
     "gmres_ds": ("-laplacian -n 12 11 10 -solver 4", "gmres", 1),
     "cogmres_amg": ("-laplacian -n 24 24 24 -solver 16 -rlx 18", "cogmres", 0),
     "cogmres_ds": ("-laplacian -n 12 11 10 -solver 17", "cogmres", 1),
+    "flexgmres_amg": ("-laplacian -n 24 24 24 -solver 61 -rlx 18", "flexgmres", 0),
+    "flexgmres_ds": ("-laplacian -n 12 11 10 -solver 60", "flexgmres", 1),
     "bicgstab_amg": ("-27pt -n 20 20 20 -solver 9 -rlx 11", "bicgstab", 0),
     "bicgstab_ds": ("-laplacian -n 12 11 10 -solver 10", "bicgstab", 1),
 }
