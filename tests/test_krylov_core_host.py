@@ -193,3 +193,16 @@ def test_product_library_does_not_contain_the_host_backend(built):
         assert "krylov_host_test" not in ldd
     # and the device library does not link the oracle
     assert "liboracle" not in subprocess.run(["ldd", LIB_B200], capture_output=True, text=True).stdout
+
+
+@pytest.mark.parametrize("nranks", [2, 3])
+def test_krylov_loops_on_row_partitioned_ranks_over_gloo(kht, nranks):
+    """world_size 2 and 3 over gloo (tests/dist_krylov_worker.py): the same loops on a row-partitioned problem --
+    halo exchange by point-to-point messages following b200_rowpart's plan, inner products by all_reduce -- reach
+    the single-rank oracle's iteration counts, histories and solution for GMRES, COGMRES, FlexGMRES and BiCGSTAB"""
+    import sys
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nranks),
+           "--master-addr", "127.0.0.1", "--master-port", str(29550 + nranks), os.path.join(ROOT, "tests", "dist_krylov_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "DIST_KRYLOV_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
