@@ -268,7 +268,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    hypre_Vector **l1 = hypre_ParAMGDataL1Norms(amg_data);
    hypre_Vector **ds = hypre_ParAMGDataChebyDS(amg_data);
    HYPRE_Real **coefs = hypre_ParAMGDataChebyCoefs(amg_data);
-   int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0;
+   int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0, uses_jac0 = 0;
    int repl = 1 << 30;   /* distributed mode: first level replicated on every rank */
    int *starts = NULL;   /* distributed mode: (nl+1) x (g_nranks+1) row starts per level */
 #define STARTS(l) (starts + (size_t)(l) * (g_nranks + 1))
@@ -293,6 +293,24 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       if (relax_type[0] == -1) { relax_type[0] = 6; }
    }
    if (relax_type[3] == 19) { relax_type[3] = 9; }
+   /* relax_type 0 (weighted point Jacobi, hypre_BoomerAMGRelax0WeightedJacobi, par_relax.c:179-335:
+    * u_i = (1-w) u_i + w (f_i - sum_{j != i} a_ij u_j) / a_ii) is u + w (f - A u) ./ d with d = the diagonal: the
+    * device's Jacobi kernel (relax 7) with the diagonal in the place of the l1 norms.  The setup holds no l1 norms
+    * for it; mixing it with the l1 smoothers (one scaling vector per level on the device) is rejected. */
+   for (k = 0; k < 4; k++) { if (relax_type[k] == 0) { uses_jac0 = 1; } }
+   if (uses_jac0)
+   {
+      for (k = 0; k < 4; k++)
+      {
+         if (relax_type[k] == 7 || relax_type[k] == 18)
+         {
+            b200_ctx_sync(ctx);
+            fprintf(stderr, "hypre_b200: relax_type 0 cannot be combined with relax_type 7 / 18 in one cycle on the device path\n");
+            return NULL;
+         }
+         if (relax_type[k] == 0) { relax_type[k] = 7; }
+      }
+   }
 
    if (g_nranks > 1 && !g_native)
    {
@@ -381,7 +399,23 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    {
       const int off = (starts && l < repl) ? STARTS(l)[g_rank] : 0;   /* this rank's slice of the level vectors */
       const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) + off : NULL;
-      if (b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d) != B200_OK)
+      double *diag0 = NULL;
+      int status;
+      if (uses_jac0)
+      {
+         /* the diagonal of this level (first entry of each row of the diag block) in the place of the l1 norms */
+         hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]);
+         HYPRE_Int nr = hypre_CSRMatrixNumRows(d), r;
+         diag0 = (double *) calloc((size_t) (nr > 0 ? nr : 1), sizeof(double));
+         for (r = 0; r < nr; r++)
+         {
+            diag0[r] = hypre_CSRMatrixI(d)[r + 1] > hypre_CSRMatrixI(d)[r] ? hypre_CSRMatrixData(d)[hypre_CSRMatrixI(d)[r]] : 0.0;
+         }
+         l1d = diag0 + off;
+      }
+      status = b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d);
+      free(diag0);
+      if (status != B200_OK)
       {
          b200_amg_destroy(amg); free(starts); return NULL;
       }

@@ -118,6 +118,27 @@ static int orc_relax(orc_amg *h, int level, int relax_type, const double *f, dou
       case 18: case 7:
          orc_relax_l1jacobi(L->n, L->Ai, L->Aj, L->Aa, f, L->l1, L->relax_weight, u, h->Vtemp, L->all_zeros);
          break;
+      case 0:
+      {
+         /* hypre_BoomerAMGRelax0WeightedJacobi (par_relax.c:320-335) -> hypre_BoomerAMGRelaxWeightedJacobi_core
+          * with Skip_diag = 1 and no l1 norms (:179-314): u_i = (1-w) u_i + w (f_i - sum_{j != i} a_ij u_j) / a_ii,
+          * the diagonal entry first in its row; rows with a zero diagonal are skipped */
+         const double w = L->relax_weight, omw = 1.0 - L->relax_weight;
+         int i, jj;
+         memcpy(h->Vtemp, u, sizeof(double) * (size_t) L->n);
+         for (i = 0; i < L->n; i++)
+         {
+            const double di = L->Aa[L->Ai[i]];
+            if (di != 0.0)
+            {
+               double res = f[i];
+               for (jj = L->Ai[i] + 1; jj < L->Ai[i + 1]; jj++) { res -= L->Aa[jj] * h->Vtemp[L->Aj[jj]]; }
+               u[i] *= omw;
+               u[i] += w * res / di;
+            }
+         }
+         break;
+      }
       case 16:
          /* hypre_ParCSRRelax_Cheby_Solve(A, f, ds, coefs, order, scale, variant, u, Vtemp, Ztemp, Ptemp, Rtemp) */
          orc_relax_cheby(L->n, L->Ai, L->Aj, L->Aa, f, L->ds, L->coefs, h->cheby_order, h->cheby_scale,

@@ -240,6 +240,9 @@ CASES = {
     "lap7_24_rlx16_F": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"FCycle": 1}),
     "lap27_20_rlx18_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=18, opts={"NumSweeps": 2}),
     "lap7_24_rlx7_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxWt": 0.8}),
+    # relax_type 0: weighted point Jacobi (par_relax.c:320-335), five jobs of the reference's TEST_ij suites
+    "lap7_24_rlx0_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=0, opts={"RelaxWt": 0.8}),
+    "lap27_20_rlx0_w07_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=0, opts={"RelaxWt": 0.7, "NumSweeps": 2}),
     # Chebyshev variant 1 (par_cheby.c:29-33: only the setup's coefficients differ), orders 3 and 4, unscaled
     # BoomerAMG as preconditioner with three cycles per application (ij -precon_cycles 3; TEST_ij/solvers.jobs:54)
     "lap7_24_rlx18_pc3": dict(gen="laplacian", dims=(24, 24, 24), rlx=18, opts={"MaxIter": 3}),

@@ -157,7 +157,7 @@ def test_interposed_hypre_api_matches_reference_in_process(H, kind):
 
 
 IJ_CASES = ["-laplacian -n 24 24 24 -solver 3 -rlx 16", "-laplacian -n 23 29 31 -solver 3 -precon_cycles 3 -rlx 18",
-            "-laplacian -n 24 24 24 -solver 1 -rlx 16 -precon_cycles 2", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
+            "-laplacian -n 24 24 24 -solver 1 -rlx 16 -precon_cycles 2", "-laplacian -n 24 24 24 -solver 1 -rlx 0 -w 0.8", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
             "-laplacian -n 12 11 10 -solver 4", "-laplacian -n 24 24 24 -solver 16 -rlx 18", "-laplacian -n 12 11 10 -solver 17",
             "-laplacian -n 24 24 24 -solver 61 -rlx 18", "-laplacian -n 12 11 10 -solver 60",
             "-27pt -n 20 20 20 -solver 9 -rlx 11", "-laplacian -n 12 11 10 -solver 10"]
