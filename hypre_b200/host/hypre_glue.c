@@ -161,9 +161,11 @@ static void mirror_drop(void *key)
    }
 }
 
+void hypre_b200_drop_vector_bindings(void);
 void hypre_b200_reset(void)
 {
    while (g_mirrors) { mirror_drop(g_mirrors->key); }
+   hypre_b200_drop_vector_bindings();
    if (g_ctx) { b200_ctx_destroy(g_ctx); g_ctx = NULL; }
 }
 
@@ -174,6 +176,74 @@ void hypre_b200_reset(void)
       fprintf(stderr, "%s\n", _b);                                                  \
       hypre_error_w_msg(HYPRE_ERROR_GENERIC, _b);                                   \
    } while (0)
+
+/* ------------------------------------------------- device-resident vectors
+ * SURVEY 8(f)-2.  The reference passes device vectors through the memory location of the hypre_Vector
+ * (HYPRE_IJVectorInitialize_v2(.., HYPRE_MEMORY_DEVICE), ij -memory_device; docs/usr-manual/solvers-boomeramg.rst:
+ * 217-253).  The host-only build of the reference this binding sits on has no device memory location, so an
+ * application states it here instead: it BINDS a device array (this rank's local part, b200_dev_alloc or any
+ * cudaMalloc pointer on the binding's device) to a hypre_ParVector.  The Krylov bindings below then solve on
+ * those arrays in place -- no host<->device copy of b or x -- and leave the vector's host array untouched until
+ * hypre_b200_vector_sync_to_host is called. */
+typedef struct devvec_s { void *key; double *dev; struct devvec_s *next; } devvec_t;
+static devvec_t *g_devvecs = NULL;
+
+static double *devvec_find(void *key)
+{
+   devvec_t *d;
+   for (d = g_devvecs; d; d = d->next) { if (d->key == key) { return d->dev; } }
+   return NULL;
+}
+
+/* dev == NULL removes the binding.  Returns 0. */
+int hypre_b200_vector_bind_device(void *par_vector, double *dev)
+{
+   devvec_t **pp = &g_devvecs, *d;
+   while (*pp && (*pp)->key != par_vector) { pp = &(*pp)->next; }
+   if (*pp)
+   {
+      if (dev) { (*pp)->dev = dev; }
+      else { d = *pp; *pp = d->next; free(d); }
+      return 0;
+   }
+   if (!dev) { return 0; }
+   d = (devvec_t *) calloc(1, sizeof(devvec_t));
+   d->key = par_vector; d->dev = dev; d->next = g_devvecs; g_devvecs = d;
+   return 0;
+}
+double *hypre_b200_vector_device(void *par_vector) { return devvec_find(par_vector); }
+
+/* copy entries [first, first + n) of the vector's host array from / to the bound device array (n < 0: the whole
+ * local vector).  Returns 0, or -1 when the vector is not bound or the copy fails. */
+static int devvec_sync(void *par_vector, int first, int n, int to_host)
+{
+   hypre_Vector *loc = hypre_ParVectorLocalVector((hypre_ParVector *) par_vector);
+   double *dev = devvec_find(par_vector);
+   b200_ctx *ctx = glue_ctx();
+   if (!dev || !ctx) { return -1; }
+   if (n < 0) { first = 0; n = (int) hypre_VectorSize(loc); }
+   if (to_host) { return b200_d2h(ctx, hypre_VectorData(loc) + first, dev, n) == B200_OK ? 0 : -1; }
+   return b200_h2d(ctx, dev, hypre_VectorData(loc) + first, n) == B200_OK ? 0 : -1;
+}
+int hypre_b200_vector_sync_to_host(void *par_vector, int first, int n) { return devvec_sync(par_vector, first, n, 1); }
+int hypre_b200_vector_sync_to_device(void *par_vector, int first, int n) { return devvec_sync(par_vector, first, n, 0); }
+
+void hypre_b200_drop_vector_bindings(void)
+{
+   while (g_devvecs) { devvec_t *d = g_devvecs; g_devvecs = d->next; free(d); }
+}
+
+/* operands of a Krylov binding: both vectors bound to device arrays (solve in place), or both on the host */
+static int krylov_operands(hypre_ParVector *pb, hypre_ParVector *px, double **db, double **dx)
+{
+   *db = devvec_find(pb); *dx = devvec_find(px);
+   if ((*db == NULL) != (*dx == NULL))
+   {
+      GLUE_FAIL("right-hand side and solution must both be bound to device arrays (hypre_b200_vector_bind_device) or both live on the host");
+      return -1;
+   }
+   return 0;
+}
 
 /* --------------------------------------------------------------- uploads */
 /* hypre_ParCSRMatrix -> b200_parcsr (diag, offd, halo plan of the CommPkg) */
@@ -637,11 +707,17 @@ HYPRE_Int hypre_PCGSolve(void *pcg_vdata, void *A, void *b, void *x)
    (*(fn->CommInfo))(A, &my_id, &num_procs);
 
    /* distributed mode: this rank's slice of the replicated host vectors (offset 0 otherwise) */
-   status = b200_pcg_solve_host(glue_ctx(), m->A, amg, &prm,
-                                hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res,
-                                (pcg->logging > 0 || pcg->print_level > 0) ? pcg->norms : NULL,
-                                (pcg->logging > 0 || pcg->print_level > 0) ? pcg->rel_norms : NULL);
+   {
+      double *db, *dx;
+      double *hn = (pcg->logging > 0 || pcg->print_level > 0) ? pcg->norms : NULL;
+      double *hr = (pcg->logging > 0 || pcg->print_level > 0) ? pcg->rel_norms : NULL;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { return hypre_error_flag; }
+      /* device-bound vectors: solve in place on the application's arrays (no copy of b or x) */
+      status = db ? b200_pcg_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, hn, hr)
+                  : b200_pcg_solve_host(glue_ctx(), m->A, amg, &prm,
+                                        hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                        hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, hn, hr);
+   }
    if (status != B200_OK) { GLUE_FAIL("device PCG failed"); return hypre_error_flag; }
    if (verbose() && g_rank == 0)
    {
@@ -829,9 +905,14 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
    if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
 
-   status = b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   {
+      double *db, *dx;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
+      status = db ? b200_gmres_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, norms)
+                  : b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   }
    if (status != B200_OK) { free(own_norms); GLUE_FAIL("device GMRES failed"); return hypre_error_flag; }
    if (verbose() && g_rank == 0)
    {
@@ -896,9 +977,14 @@ HYPRE_Int hypre_COGMRESSolve(void *cogmres_vdata, void *A, void *b, void *x)
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
    if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
 
-   status = b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   {
+      double *db, *dx;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
+      status = db ? b200_gmres_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, norms)
+                  : b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   }
    if (status != B200_OK) { free(own_norms); GLUE_FAIL("device COGMRES failed"); return hypre_error_flag; }
    if (verbose() && g_rank == 0)
    {
@@ -964,9 +1050,14 @@ HYPRE_Int hypre_FlexGMRESSolve(void *fgmres_vdata, void *A, void *b, void *x)
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
    if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
 
-   status = b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                  hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   {
+      double *db, *dx;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
+      status = db ? b200_gmres_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, norms)
+                  : b200_gmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                          hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   }
    if (status != B200_OK) { free(own_norms); GLUE_FAIL("device FlexGMRES failed"); return hypre_error_flag; }
    if (verbose() && g_rank == 0)
    {
@@ -1029,9 +1120,14 @@ HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
    if (!norms && g->print_level > 0) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
 
-   status = b200_bicgstab_solve_host(glue_ctx(), m->A, amg, &prm,
-                                     hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                     hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   {
+      double *db, *dx;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
+      status = db ? b200_bicgstab_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, norms)
+                  : b200_bicgstab_solve_host(glue_ctx(), m->A, amg, &prm,
+                                             hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                             hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   }
    if (status != B200_OK) { free(own_norms); GLUE_FAIL("device BiCGSTAB failed"); return hypre_error_flag; }
    if (verbose() && g_rank == 0)
    {

@@ -191,6 +191,30 @@ class ParVector:
             return np.zeros(0)
         return np.ctypeslib.as_array(lib().hb_vector_data(self.h), (n,))
 
+    # ---- device-resident form (hypre_glue.c "device-resident vectors")
+    def bind_device(self, dev_ptr):
+        """state that this vector's local part lives in the device array `dev_ptr` (capi.DeviceVector.ptr):
+        the Krylov bindings then solve on it in place; None removes the binding"""
+        L = lib()
+        L.hypre_b200_vector_bind_device.argtypes = [C.c_void_p, C.c_void_p]
+        return L.hypre_b200_vector_bind_device(self.h, dev_ptr)
+
+    def bound_device(self):
+        L = lib()
+        L.hypre_b200_vector_device.argtypes = [C.c_void_p]
+        L.hypre_b200_vector_device.restype = C.c_void_p
+        return L.hypre_b200_vector_device(self.h)
+
+    def sync_to_host(self, first=0, n=-1):
+        L = lib()
+        L.hypre_b200_vector_sync_to_host.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        return L.hypre_b200_vector_sync_to_host(self.h, first, n)
+
+    def sync_to_device(self, first=0, n=-1):
+        L = lib()
+        L.hypre_b200_vector_sync_to_device.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        return L.hypre_b200_vector_sync_to_device(self.h, first, n)
+
     def set_all_zeros_flag(self, flag):
         lib().hb_vector_set_all_zeros(self.h, int(flag))
 

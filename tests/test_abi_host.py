@@ -186,3 +186,32 @@ def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, k
     H.lib().HYPRE_ParCSRMatrixMatvecT(1.0, A.h, b.h, 0.0, y.h)
     assert H.error_flag() & 1 and not np.any(y.numpy())
     H.clear_errors()
+
+
+def test_device_vector_bindings_table_and_mixed_operands(H):
+    """hypre_b200_vector_bind_device: bind / rebind / unbind; syncing an unbound vector fails; with a
+    half-bound pair of operands no solve runs (here, without a device, the upload fails first -- the rejection of
+    mixed operands itself is asserted on the GPU, tests/test_gpu_zz_krylov.py).  The fake pointers are never
+    dereferenced."""
+    H.set_device_path(True)
+    A = H.laplacian(6, 6, 6)
+    b = A.vector(1.0); x = A.vector(0.0)
+    assert b.bound_device() is None
+    fake1, fake2 = C.c_void_p(0x1000), C.c_void_p(0x2000)
+    assert b.bind_device(fake1) == 0 and b.bound_device() == 0x1000
+    assert b.bind_device(fake2) == 0 and b.bound_device() == 0x2000       # rebinding replaces
+    assert x.bound_device() is None
+    s = H.ParCSRPCG()
+    s.SetDiagScalePrecond()
+    s.Setup(A, b, x)
+    for solver in (s, H.ParCSRGMRES(), H.ParCSRBiCGSTAB()):
+        if solver is not s:
+            solver.SetDiagScalePrecond()
+            solver.Setup(A, b, x)
+        H.clear_errors()
+        solver.Solve(A, b, x)
+        assert H.error_flag() & 1 and not np.any(x.numpy())
+    H.clear_errors()
+    assert b.bind_device(None) == 0 and b.bound_device() is None         # unbound again
+    assert b.bind_device(None) == 0                                     # idempotent
+    assert b.sync_to_host() == -1 and b.sync_to_device() == -1          # not bound

@@ -212,3 +212,39 @@ def test_host_spmvT_entry_matches_reference(H, ctx):
             scale = np.abs(Md).T.dot(np.abs(x.numpy())) * 2.0 + 0.5
             assert np.max(np.abs(out[True] - out[False]) / scale) < 1e-12, beta
         x.destroy(); y.destroy()
+
+
+@pytest.mark.parametrize("kind", ["pcg", "gmres", "cogmres", "flexgmres", "bicgstab"])
+def test_device_bound_vectors_solve_in_place(H, ctx, kind):
+    """b and x bound to device arrays (hypre_b200_vector_bind_device) -- the HYPRE_*Solve call runs on
+    them in place: same iterations and solution as the host-vector call, the host array of x untouched until
+    sync_to_host; a half-bound pair is rejected"""
+    H.set_device_path(True)
+    A = H.laplacian(24, 24, 24)
+    b, x = A.vector(1.0), A.vector(0.0)
+    amg = H.BoomerAMG(relax_type=16)
+    s = {"pcg": H.ParCSRPCG, "gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
+         "bicgstab": H.ParCSRBiCGSTAB}[kind]()
+    s.SetPrecond(amg)
+    s.Setup(A, b, x)
+    H.clear_errors()
+    s.Solve(A, b, x)                               # host vectors
+    assert H.error_flag() == 0
+    it_host, x_host = s.num_iterations, x.numpy().copy()
+    n = x.size
+    db, dx = capi.DeviceVector(ctx, n, b.numpy()), capi.DeviceVector(ctx, n, np.zeros(n))
+    x.numpy()[:] = -7.0                            # sentinel: the host array must not be written by the solve
+    b.bind_device(db.ptr)
+    H.clear_errors()
+    s.Solve(A, b, x)                               # half-bound: rejected
+    assert H.error_flag() & 1
+    H.clear_errors()
+    x.bind_device(dx.ptr)
+    s.Solve(A, b, x)
+    assert H.error_flag() == 0 and s.num_iterations == it_host
+    assert np.all(x.numpy() == -7.0)
+    np.testing.assert_array_equal(dx.get(), x_host)          # same device code on the same data
+    assert x.sync_to_host() == 0
+    np.testing.assert_array_equal(x.numpy(), x_host)
+    b.bind_device(None); x.bind_device(None)
+    db.free(); dx.free()
