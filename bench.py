@@ -330,6 +330,10 @@ def run_b200(args, rank, world):
     e2e_value = n_global * e2e_iters * args.steps / e2e_s
     api_rel = pcg.rel_norms()
     if world > 1:
+        try:                                   # reported beside the line, never allowed to break it
+            P["halo"] = halo_per_iteration(L, damg, dA, amg)
+        except Exception as e:                 # noqa: BLE001
+            P["halo"] = repr(e)
         return finish_multi(args, R, P, dict(value=value, dev_s=dev_s, iters=iters, launches=launches,
                                              e2e_value=e2e_value, e2e_s=e2e_s, e2e_iters=e2e_iters, rel=rel,
                                              api_rel=api_rel, clocks=clocks, n_global=n_global, n_local=n,
@@ -430,12 +434,63 @@ def run_b200(args, rank, world):
     print(json.dumps(out))
 
 
+def halo_per_iteration(L, damg, dA, amg):
+    """bytes / messages THIS rank puts on the wire per PCG iteration (one cycle from a zero guess + the level-0 SpMV):
+    exchange counts of the cycle (b200_cycle_exchange_counts) x plan sizes of every level (b200_parcsr_halo_info).
+    Replicated coarse levels have no plan; the vector all-reduce at the transition is not counted."""
+    prm = amg.params()
+    nl = amg.num_levels
+    rt = np.array([7 if t == 0 else 9 if t == 19 else t for t in prm["relax_type"]], dtype=np.int32)
+    ns = np.array(prm["num_sweeps"], dtype=np.int32)
+    fa, fp, rp = (np.zeros(nl, dtype=np.int64) for _ in range(3))
+    capi_ = sys.modules["hypre_b200.capi"]
+    capi_.check(L.b200_cycle_exchange_counts(nl, prm["cycle_type"], prm["fcycle"], capi_.ptr(rt), capi_.ptr(ns),
+                                             prm["cheby_order"], 1, capi_.ptr(fa), capi_.ptr(fp), capi_.ptr(rp)))
+    nbytes, msgs = 0.0, 0
+
+    def info(M):
+        a, b, c, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        capi_.check(L.b200_parcsr_halo_info(M, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return a.value, b.value, c.value, d.value
+    for l in range(nl):
+        M = C.c_void_p()
+        capi_.check(L.b200_amg_level_matrix(damg, l, C.byref(M)))
+        s_, e_, r_, o_ = info(M)
+        k = int(fa[l]) + (1 if l == 0 else 0)           # + the SpMV of the PCG loop on level 0
+        nbytes += 8.0 * k * e_
+        msgs += k * s_
+        if l < nl - 1:
+            capi_.check(L.b200_amg_level_interp(damg, l, C.byref(M)))
+            s_, e_, r_, o_ = info(M)
+            nbytes += 8.0 * (int(fp[l]) * e_ + int(rp[l]) * o_)
+            msgs += int(fp[l]) * s_ + int(rp[l]) * r_
+    return nbytes, msgs
+
+
 def finish_multi(args, R, P, m):
     """N > 1: whole-job numbers (max-over-ranks time), per-rank algorithmic bytes summed over ranks."""
     n = m["n_local"]
     spmv_bytes = 12.0 * m["nnz0"] + 4.0 * (n + 1) + 16.0 * n
     iter_bytes = R.sum(m["cyc_bytes"] + spmv_bytes + 8.0 * n * 9)
     launches = R.sum(m["launches"])
+    # NVLink side of the roofline (SURVEY 8d-iii): bytes the busiest rank sends per PCG iteration against 900 GB/s
+    # per direction; the exchange is fused into the operator kernels, so the time it is held against is the whole
+    # iteration (a lower bound of the link rate, an upper bound of the share of the iteration the wire could explain)
+    halo = None
+    h = P.get("halo")
+    ok = isinstance(h, tuple)
+    hb = R.max(h[0] if ok else -1.0)
+    hm = R.max(float(h[1]) if ok else -1.0)
+    if hb >= 0:
+        it_s = m["dev_s"] / args.steps / (m["iters"] + 1)
+        halo = {"bytes_per_iteration_busiest_gpu": hb, "messages_per_iteration_busiest_gpu": int(hm),
+                "peak": 900.0, "unit": "GB/s", "achieved_over_whole_iteration": hb / it_s / 1e9,
+                "frac": hb / it_s / 1e9 / 900.0, "wire_time_at_peak_us": hb / 900e9 * 1e6,
+                "iteration_us": it_s * 1e6,
+                "note": "bytes = exchange counts of one cycle + the level-0 SpMV x plan sizes of every level; the "
+                        "exchange is fused into the operator kernels, its own duration is not separable"}
+    elif not ok and R.rank == 0:
+        halo = {"error": str(h)}
     if R.rank == 0:
         peak, peak_src = measured_peaks()
         iter_gbs = iter_bytes * (m["iters"] + 1) * args.steps / m["dev_s"] / 1e9
@@ -463,6 +518,7 @@ def finish_multi(args, R, P, m):
                          "achieved": iter_gbs, "peak": peak * R.world, "unit": "GB/s", "frac": iter_gbs / (peak * R.world),
                          "traffic": None, "peak_source": peak_src + " x n_gpus", "pcg_iteration_bytes": iter_bytes},
             "cpu_baseline": None, "clocks": m["clocks"], "setup_s": P["setup_s"], "upload_s": m["upload_s"],
+            "halo": halo,
         }
         print(json.dumps(out))
     R.close()

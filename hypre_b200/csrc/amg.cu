@@ -582,3 +582,78 @@ extern "C" int b200_cycle_sweep_counts(int num_levels, int cycle_type, int fcycl
    }
    return B200_OK;
 }
+
+// Halo exchanges per level in ONE cycle, from the cycle parameters alone: the same dry run of the level-counter
+// state machine as above, tracking the all-zeros flag of U as amg_cycle_core does.  fwdA[l] = forward exchanges
+// (ghost values of the operand, hypre_ParCSRCommHandleCreate job 1) of SpMV-type launches on A_l (smoother sweeps,
+// residual); fwdP[l] = forward exchanges on P_l (prolongation from level l+1); revP[l] = reverse exchanges
+// (job 2) on P_l (restriction onto level l+1).  bench.py turns them into bytes on the wire with the plan sizes of
+// b200_parcsr_halo_info: the NVLink side of the roofline.  Pure host arithmetic.
+static long long sweep_exchanges(int t, bool zero, int cheby_order)
+{
+   switch (t)
+   {
+      case 18: case 7: return zero ? 0 : 1;                       // zero guess: u = w f ./ l1, no SpMV
+      case 16: { const int k = (cheby_order > 4 ? 4 : cheby_order < 1 ? 1 : cheby_order) - 1; return zero ? k : k + 1; }
+      case 11: case 12: return zero ? 0 : 1;                      // the strict-lower passes are rank-local
+      default: return 0;                                          // 9: dense solve (gather of the coarse rhs)
+   }
+}
+
+extern "C" int b200_cycle_exchange_counts(int num_levels, int cycle_type, int fcycle, const int *relax_type,
+                                          const int *num_sweeps, int cheby_order, int zero_guess,
+                                          long long *fwdA, long long *fwdP, long long *revP)
+{
+   ARG_CHECK(num_levels >= 1 && cycle_type >= 1 && relax_type != nullptr && num_sweeps != nullptr);
+   ARG_CHECK(fwdA != nullptr && fwdP != nullptr && revP != nullptr);
+   const int nl = num_levels;
+   for (int l = 0; l < nl; l++) { fwdA[l] = fwdP[l] = revP[l] = 0; }
+   std::vector<int> lev_counter(nl), zero(nl, 0);
+   lev_counter[0] = 1;
+   for (int k = 1; k < nl; k++) { lev_counter[k] = fcycle ? 1 : cycle_type; }
+   zero[0] = zero_guess ? 1 : 0;
+   int fcycle_lev = nl - 2, level = 0, cycle_param = 1;
+   for (;;)
+   {
+      const int t = nl > 1 ? relax_type[cycle_param] : relax_type[0];
+      const int ns = nl > 1 ? num_sweeps[cycle_param] : num_sweeps[0];
+      for (int j = 0; j < ns; j++) { fwdA[level] += sweep_exchanges(t, zero[level] != 0, cheby_order); zero[level] = 0; }
+      --lev_counter[level];
+      if (lev_counter[level] >= 0 && level != nl - 1)
+      {
+         if (!zero[level]) { fwdA[level] += 1; }      // residual r = f - A u (skipped while u == 0: r = f)
+         revP[level] += 1;                            // restriction
+         ++level;
+         zero[level] = 1;
+         lev_counter[level] = lev_counter[level] > cycle_type ? lev_counter[level] : cycle_type;
+         cycle_param = (level == nl - 1) ? 3 : 1;
+      }
+      else if (level != 0)
+      {
+         fwdP[level - 1] += 1;                        // prolongation
+         zero[level - 1] = 0;
+         --level;
+         cycle_param = 2;
+         if (fcycle && fcycle_lev == level)
+         {
+            lev_counter[level] = lev_counter[level] > 1 ? lev_counter[level] : 1;
+            fcycle_lev--;
+         }
+      }
+      else { break; }
+   }
+   return B200_OK;
+}
+
+// sizes of the halo plan of a ParCSR block (hypre_ParCSRCommPkg): messages and doubles per forward exchange
+// (num_sends, n_send_elmts) and per reverse exchange (num_recvs, n_cols_offd)
+extern "C" int b200_parcsr_halo_info(const b200_parcsr *A, int *num_sends, int *n_send_elmts, int *num_recvs,
+                                     int *n_cols_offd)
+{
+   ARG_CHECK(A != nullptr);
+   if (num_sends) { *num_sends = A->num_sends; }
+   if (n_send_elmts) { *n_send_elmts = A->n_send_elmts; }
+   if (num_recvs) { *num_recvs = A->num_recvs; }
+   if (n_cols_offd) { *n_cols_offd = A->n_cols_offd; }
+   return B200_OK;
+}

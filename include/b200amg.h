@@ -239,6 +239,17 @@ int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *
  * par_amg_solve.c:338-395).  num_sweeps[4] as in b200_amg_create; sweeps_per_level has num_levels entries. */
 int b200_cycle_sweep_counts(int num_levels, int cycle_type, int fcycle, const int *num_sweeps,
                             long long *sweeps_per_level);
+/* halo exchanges per level of one cycle (host arithmetic, no device): fwdA[l] forward exchanges (job 1 of
+ * hypre_ParCSRCommHandleCreate, src/parcsr_mv/par_csr_communication.c:357-637) of the SpMV-type launches on A_l,
+ * fwdP[l] forward exchanges on P_l (prolongation), revP[l] reverse exchanges (job 2) on P_l (restriction); arrays
+ * of num_levels entries.  With b200_parcsr_halo_info they give the bytes a cycle puts on NVLink. */
+int b200_cycle_exchange_counts(int num_levels, int cycle_type, int fcycle, const int *relax_type,
+                               const int *num_sweeps, int cheby_order, int zero_guess,
+                               long long *fwdA, long long *fwdP, long long *revP);
+/* plan sizes of a block: messages / doubles per forward exchange (num_sends, n_send_elmts) and per reverse exchange
+ * (num_recvs, n_cols_offd); any pointer may be NULL */
+int b200_parcsr_halo_info(const b200_parcsr *A, int *num_sends, int *n_send_elmts, int *num_recvs,
+                          int *n_cols_offd);
 /* stand-alone AMG iteration (ij -solver 0): hypre_BoomerAMGSolve
  * (src/parcsr_ls/par_amg_solve.c:21-424) with converge_type 0. */
 int b200_amg_solve(b200_amg *amg, const double *b, double *x, double tol, int min_iter,

@@ -215,3 +215,40 @@ def test_device_vector_bindings_table_and_mixed_operands(H):
     assert b.bind_device(None) == 0 and b.bound_device() is None         # unbound again
     assert b.bind_device(None) == 0                                     # idempotent
     assert b.sync_to_host() == -1 and b.sync_to_device() == -1          # not bound
+
+
+def test_cycle_exchange_counts():
+    """b200_cycle_exchange_counts: halo exchanges per level of one cycle (host arithmetic), against hand counts
+    for V-cycles and against b200_cycle_sweep_counts for W / F cycles"""
+    L = capi.lib()
+
+    def counts(nl, cycle_type, fcycle, rt, ns, order, zg):
+        rt, ns = np.array(rt, dtype=np.int32), np.array(ns, dtype=np.int32)
+        a, p, r = (np.zeros(nl, dtype=np.int64) for _ in range(3))
+        capi.check(L.b200_cycle_exchange_counts(nl, cycle_type, fcycle, capi.ptr(rt), capi.ptr(ns), order, zg,
+                                                capi.ptr(a), capi.ptr(p), capi.ptr(r)))
+        sw = np.zeros(nl, dtype=np.int64)
+        capi.check(L.b200_cycle_sweep_counts(nl, cycle_type, fcycle, capi.ptr(ns), capi.ptr(sw)))
+        return a.tolist(), p.tolist(), r.tolist(), sw.tolist()
+    # V-cycle, l1-Jacobi, zero initial guess: the first pre-sweep of every level is u = w f ./ l1 (no SpMV) and
+    # stays out; residual, post-sweep -> 2 per level; nothing on the dense coarsest level
+    a, p, r, sw = counts(3, 1, 0, [0, 18, 18, 9], [1, 1, 1, 1], 2, 1)
+    assert a == [2, 2, 0] and p == [1, 1, 0] and r == [1, 1, 0]
+    # nonzero guess on level 0 only: its pre-sweep needs the halo, too
+    a, p, r, sw = counts(3, 1, 0, [0, 18, 18, 9], [1, 1, 1, 1], 2, 0)
+    assert a == [3, 2, 0]
+    # Chebyshev order 2 = 2 SpMVs per sweep, 1 from a zero guess: 1 + residual + 2
+    a, p, r, sw = counts(4, 1, 0, [0, 16, 16, 9], [1, 1, 1, 1], 2, 1)
+    assert a == [4, 4, 4, 0] and p == r == [1, 1, 1, 0]
+    # two-stage GS, two sweeps: (0 + 1) pre, residual, 2 post
+    a, p, r, sw = counts(3, 1, 0, [0, 11, 11, 9], [2, 2, 2, 1], 2, 1)
+    assert a == [4, 4, 0]
+    # W and F cycles: every descent comes back (fwdP == revP), level l is entered revP[l-1] times, and with
+    # Jacobi one sweep each: exchanges = sweeps - zero-guess first sweeps + residuals
+    for ct, fc in ((2, 0), (1, 1), (2, 1)):
+        a, p, r, sw = counts(5, ct, fc, [0, 18, 18, 9], [1, 1, 1, 1], 2, 1)
+        assert p == r and r[-1] == 0
+        entered = [1] + r[:-1]
+        for l in range(4):
+            assert a[l] == sw[l] - entered[l] + r[l], (ct, fc, l, a, sw, r)
+        assert a[4] == 0
