@@ -40,7 +40,7 @@ def lib():
                  "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
         getattr(L, name).restype = vp
     for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
-                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_bicgstab_norms"):
+                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_lgmres_norms", "hb_bicgstab_norms"):
         getattr(L, name).restype = C.POINTER(d)
     L.hb_amg_relax_weight.restype = d
     L.hb_amg_omega.restype = d
@@ -53,7 +53,7 @@ def lib():
     for name in ("hb_vector_destroy", "hb_vector_data", "hb_vector_size", "hb_amg_num_levels", "hb_amg_Vtemp",
                  "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
                  "hb_gmres_norms", "hb_cogmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy",
-                 "HYPRE_ParCSRCOGMRESDestroy", "hb_flexgmres_norms", "HYPRE_ParCSRFlexGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
+                 "HYPRE_ParCSRCOGMRESDestroy", "hb_flexgmres_norms", "HYPRE_ParCSRFlexGMRESDestroy", "hb_lgmres_norms", "HYPRE_ParCSRLGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
                  "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
                  "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
                  "HYPRE_ParCSRPCGDestroy"):
@@ -495,6 +495,18 @@ class ParCSRFlexGMRES(_ParCSRKrylov):
     def __init__(self, k_dim=5, **kw):
         super().__init__(**kw)
         self.SetKDim(k_dim)
+
+
+class ParCSRLGMRES(_ParCSRKrylov):
+    """HYPRE_ParCSRLGMRES* / HYPRE_LGMRES*: ij -solver 51 (AMG) / 50 (diagonal scaling); aug_dim 2 (ij.c / lgmres.c:104)."""
+    _prefix = "HYPRE_LGMRES"
+    _par = "HYPRE_ParCSRLGMRES"
+    _norms = "hb_lgmres_norms"
+
+    def __init__(self, k_dim=5, aug_dim=2, **kw):
+        super().__init__(**kw)
+        self.SetKDim(k_dim)
+        self.SetAugDim(aug_dim)
 
 
 class ParCSRBiCGSTAB(_ParCSRKrylov):

@@ -550,3 +550,176 @@ done:
    free(r); free(r0); free(s); free(v); free(p); free(q);
    return ret;
 }
+
+/* hypre_LGMRESSolve (krylov/lgmres.c:337-...; ij -solver 51 AMG / 50 diagonal scaling) with cf_tol = 0:
+ * restarted GMRES whose Krylov space is augmented with the last aug_dim error approximations (aug_vecs) and
+ * their images (a_aug_vecs); approx_constant keeps the space at k_dim vectors.  Modified Gram-Schmidt, Givens
+ * rotations and the true-residual check as in hypre_FlexGMRESSolve. */
+int orc_lgmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
+               int aug_dim, int approx_constant, int min_iter, int max_iter, double *norms, double *rel_resid,
+               int *converged)
+{
+   orc_level *L0 = &h->L[0];
+   const int n = L0->n, kd = k_dim + aug_dim;
+   const double epsmac = 1.e-16;
+   const size_t nb = sizeof(double) * (size_t) n;
+   double **p = (double **) calloc((size_t) k_dim + 1, sizeof(double *));
+   double **av = (double **) calloc((size_t) aug_dim + 1, sizeof(double *));
+   double **aav = (double **) calloc((size_t) aug_dim + 1, sizeof(double *));
+   int *aug_order = (int *) calloc((size_t) aug_dim + 1, sizeof(int));
+   double *r = (double *) calloc((size_t) n, sizeof(double));
+   double *w = (double *) calloc((size_t) n, sizeof(double));
+   double *rs = (double *) calloc((size_t) kd + 1, sizeof(double));
+   double *c = (double *) calloc((size_t) kd + 1, sizeof(double));
+   double *s = (double *) calloc((size_t) kd + 1, sizeof(double));
+   double **hh = (double **) calloc((size_t) kd + 1, sizeof(double *));
+   double b_norm, r_norm, r_norm_last = 0.0, den_norm, epsilon, t, gamma, tmp_norm;
+   int i, j, k, q, ii, iter = 0, aug_ct = 0, it_arnoldi, it_total, it_aug, order, spot = 0;
+   for (i = 0; i <= k_dim; i++) { p[i] = (double *) calloc((size_t) n, sizeof(double)); }
+   for (i = 0; i <= aug_dim; i++) { av[i] = (double *) calloc((size_t) n, sizeof(double)); aav[i] = (double *) calloc((size_t) n, sizeof(double)); }
+   for (i = 0; i <= kd; i++) { hh[i] = (double *) calloc((size_t) kd + 1, sizeof(double)); }
+   if (converged) { *converged = 0; }
+   if (rel_resid) { *rel_resid = 0.0; }
+   orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, p[0]);
+   b_norm = sqrt(orc_dot(n, b, b));
+   r_norm = sqrt(orc_dot(n, p[0], p[0]));
+   if (norms) { norms[0] = r_norm; }
+   den_norm = b_norm > 0.0 ? b_norm : r_norm;
+   epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
+   while (iter < max_iter)
+   {
+      rs[0] = r_norm;
+      if (r_norm == 0.0) { goto done; }
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
+         r_norm = sqrt(orc_dot(n, r, r));
+         if (r_norm <= epsilon) { break; }
+      }
+      t = 1.0 / r_norm;
+      r_norm_last = r_norm;
+      for (q = 0; q < n; q++) { p[0][q] *= t; }
+      i = 0;
+      it_arnoldi = approx_constant ? k_dim - aug_ct : k_dim - aug_dim;
+      it_total = it_arnoldi + aug_ct;
+      it_aug = 0;
+      while (i < it_total && iter < max_iter)
+      {
+         i++; iter++;
+         if (i <= it_arnoldi)
+         {
+            orc_precond(h, precond_kind, p[i - 1], r);
+            orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, NULL, p[i]);
+         }
+         else
+         {
+            it_aug++;
+            order = i - it_arnoldi - 1;
+            for (ii = 0; ii < aug_dim; ii++) { if (aug_order[ii] == order) { spot = ii; break; } }
+            memcpy(p[i], aav[spot], nb);
+         }
+         for (j = 0; j < i; j++)
+         {
+            hh[j][i - 1] = orc_dot(n, p[j], p[i]);
+            for (q = 0; q < n; q++) { p[i][q] += -hh[j][i - 1] * p[j][q]; }
+         }
+         t = sqrt(orc_dot(n, p[i], p[i]));
+         hh[i][i - 1] = t;
+         if (t != 0.0) { t = 1.0 / t; for (q = 0; q < n; q++) { p[i][q] *= t; } }
+         for (j = 1; j < i; j++)
+         {
+            t = hh[j - 1][i - 1];
+            hh[j - 1][i - 1] = s[j - 1] * hh[j][i - 1] + c[j - 1] * t;
+            hh[j][i - 1] = -s[j - 1] * t + c[j - 1] * hh[j][i - 1];
+         }
+         t = hh[i][i - 1] * hh[i][i - 1];
+         t += hh[i - 1][i - 1] * hh[i - 1][i - 1];
+         gamma = sqrt(t);
+         if (gamma == 0.0) { gamma = epsmac; }
+         c[i - 1] = hh[i - 1][i - 1] / gamma;
+         s[i - 1] = hh[i][i - 1] / gamma;
+         rs[i] = -hh[i][i - 1] * rs[i - 1];
+         rs[i] /= gamma;
+         rs[i - 1] = c[i - 1] * rs[i - 1];
+         hh[i - 1][i - 1] = s[i - 1] * hh[i][i - 1] + c[i - 1] * hh[i - 1][i - 1];
+         r_norm = fabs(rs[i]);
+         if (norms) { norms[iter] = r_norm; }
+         if (r_norm <= epsilon && iter >= min_iter) { break; }
+      }
+      rs[i - 1] = rs[i - 1] / hh[i - 1][i - 1];
+      for (k = i - 2; k >= 0; k--)
+      {
+         t = 0.0;
+         for (j = k + 1; j < i; j++) { t -= hh[k][j] * rs[j]; }
+         t += rs[k];
+         rs[k] = t / hh[k][k];
+      }
+      if (it_arnoldi > i) { it_arnoldi = i; }
+      if (!it_aug)
+      {
+         memcpy(w, p[i - 1], nb);
+         for (q = 0; q < n; q++) { w[q] *= rs[i - 1]; }
+         for (j = i - 2; j >= 0; j--) { for (q = 0; q < n; q++) { w[q] += rs[j] * p[j][q]; } }
+      }
+      else
+      {
+         memcpy(w, p[0], nb);
+         for (q = 0; q < n; q++) { w[q] *= rs[0]; }
+         for (j = 1; j < it_arnoldi; j++) { for (q = 0; q < n; q++) { w[q] += rs[j] * p[j][q]; } }
+         for (ii = 0; ii < it_aug; ii++)
+         {
+            for (j = 0; j < aug_dim; j++) { if (aug_order[j] == ii) { spot = j; break; } }
+            for (q = 0; q < n; q++) { w[q] += rs[it_arnoldi + ii] * av[spot][q]; }
+         }
+      }
+      memcpy(av[aug_dim], w, nb);                 /* the new error approximation, before the preconditioner */
+      orc_precond(h, precond_kind, w, r);
+      for (q = 0; q < n; q++) { x[q] += r[q]; }
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
+         r_norm = sqrt(orc_dot(n, r, r));
+         if (r_norm <= epsilon) { if (converged) { *converged = 1; } break; }
+         memcpy(p[0], r, nb);
+         i = 0;
+      }
+      /* r0 (not scaled) into w, residual vector of the restart into p[0] */
+      memcpy(w, p[0], nb);
+      for (q = 0; q < n; q++) { w[q] *= r_norm_last; }
+      for (j = i; j > 0; j--)
+      {
+         rs[j - 1] = -s[j - 1] * rs[j];
+         rs[j] = c[j - 1] * rs[j];
+      }
+      if (i) { for (q = 0; q < n; q++) { p[i][q] += (rs[i] - 1.0) * p[i][q]; } }
+      for (j = i - 1; j > 0; j--) { for (q = 0; q < n; q++) { p[i][q] += rs[j] * p[j][q]; } }
+      if (i)
+      {
+         for (q = 0; q < n; q++) { p[0][q] += (rs[0] - 1.0) * p[0][q]; }
+         for (q = 0; q < n; q++) { p[0][q] += p[i][q]; }
+      }
+      if (aug_dim > 0)
+      {
+         if (!aug_ct) { spot = 0; aug_ct++; }
+         else if (aug_ct < aug_dim) { spot = aug_ct; aug_ct++; }
+         else { for (ii = 0; ii < aug_dim; ii++) { if (aug_order[ii] == aug_dim - 1) { spot = ii; } } }
+         memcpy(av[spot], av[aug_dim], nb);
+         tmp_norm = 1.0 / sqrt(orc_dot(n, av[spot], av[spot]));
+         for (q = 0; q < n; q++) { av[spot][q] *= tmp_norm; }
+         for (ii = 0; ii < aug_dim; ii++) { aug_order[ii]++; }
+         aug_order[spot] = 0;
+         /* A * augvec = (r0 - rm) / norm : r0 is in w, rm in p[0] */
+         memcpy(aav[spot], w, nb);
+         for (q = 0; q < n; q++) { aav[spot][q] *= -1.0; }
+         for (q = 0; q < n; q++) { aav[spot][q] += p[0][q]; }
+         for (q = 0; q < n; q++) { aav[spot][q] *= -tmp_norm; }
+      }
+   }
+   if (rel_resid) { *rel_resid = b_norm > 0.0 ? r_norm / b_norm : r_norm; }
+done:
+   for (i = 0; i <= k_dim; i++) { free(p[i]); }
+   for (i = 0; i <= aug_dim; i++) { free(av[i]); free(aav[i]); }
+   for (i = 0; i <= kd; i++) { free(hh[i]); }
+   free(p); free(av); free(aav); free(aug_order); free(hh); free(r); free(w); free(rs); free(c); free(s);
+   return iter;
+}

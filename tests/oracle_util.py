@@ -37,6 +37,7 @@ def lib():
         L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_cogmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_flexgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
+        L.orc_lgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, i, vp, vp, vp]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
@@ -186,6 +187,16 @@ class OracleAMG:
         it = lib().orc_pcg(self.h, p(np.ascontiguousarray(b)), p(x), tol, max_iter, two_norm, p(norms), p(rel),
                            C.byref(conv))
         return x, it, rel[1:it + 1].copy(), conv.value
+
+    def lgmres(self, b, x0, precond=0, tol=1e-8, a_tol=0.0, k_dim=5, aug_dim=2, approx_constant=1, min_iter=0,
+               max_iter=100, skip_real_r_check=0):
+        """orc_lgmres: (x, iterations, norms[0..iterations], final relative residual, converged)"""
+        x = np.array(x0, dtype=np.float64, copy=True)
+        norms = np.zeros(max_iter + 1)
+        rel, conv = C.c_double(), C.c_int()
+        it = lib().orc_lgmres(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, k_dim, aug_dim,
+                              approx_constant, min_iter, max_iter, p(norms), C.byref(rel), C.byref(conv))
+        return x, it, norms[:it + 1].copy(), rel.value, conv.value
 
     def flexgmres(self, b, x0, **kw):
         """orc_flexgmres (preconditioned basis kept): same arguments and results as gmres"""

@@ -32,8 +32,9 @@ def ref_off(H):
 
 
 def _solver(H, kind, amg, k_dim=5, tol=1e-8, max_iter=100):
-    if kind in ("gmres", "cogmres", "flexgmres"):
-        cls = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES}[kind]
+    if kind in ("gmres", "cogmres", "flexgmres", "lgmres"):
+        cls = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
+               "lgmres": H.ParCSRLGMRES}[kind]
         s = cls(k_dim=k_dim, tol=tol, max_iter=max_iter, print_level=1)   # print_level 1: norms[] logged
     else:
         s = H.ParCSRBiCGSTAB(tol=tol, max_iter=max_iter, print_level=0, logging=1)
@@ -57,7 +58,7 @@ def _case(H, name):
     return A, b, x, amg
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
     H = ref_off
@@ -77,7 +78,8 @@ def test_oracle_amg_krylov_matches_reference(ref_off, kind, name):
 
 
 @pytest.mark.parametrize("kind,k_dim", [("gmres", 5), ("gmres", 3), ("gmres", 20), ("cogmres", 5), ("cogmres", 9), ("cogmres", 20),
-                                        ("flexgmres", 5), ("flexgmres", 8), ("bicgstab", 0)])
+                                        ("flexgmres", 5), ("flexgmres", 8), ("lgmres", 5), ("lgmres", 9), ("lgmres", 3),
+                                        ("bicgstab", 0)])
 def test_oracle_diagscale_krylov_matches_reference(ref_off, kind, k_dim):
     """ij -solver 4 / 10: diagonal scaling, many iterations, several GMRES restarts"""
     H = ref_off
@@ -132,6 +134,8 @@ IJ_KRYLOV = {
     "cogmres_ds": ("-laplacian -n 12 11 10 -solver 17", "cogmres", 1),
     "flexgmres_amg": ("-laplacian -n 24 24 24 -solver 61 -rlx 18", "flexgmres", 0),
     "flexgmres_ds": ("-laplacian -n 12 11 10 -solver 60", "flexgmres", 1),
+    "lgmres_amg": ("-laplacian -n 24 24 24 -solver 51 -rlx 18", "lgmres", 0),
+    "lgmres_ds": ("-laplacian -n 12 11 10 -solver 50", "lgmres", 1),
     "bicgstab_amg": ("-27pt -n 20 20 20 -solver 9 -rlx 11", "bicgstab", 0),
     "bicgstab_ds": ("-laplacian -n 12 11 10 -solver 10", "bicgstab", 1),
 }
