@@ -40,6 +40,11 @@ class BicgstabParams(C.Structure):
                 ("diag_scale", C.c_int)]
 
 
+class LgmresParams(C.Structure):
+    _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
+                ("k_dim", C.c_int), ("aug_dim", C.c_int), ("approx_constant", C.c_int), ("diag_scale", C.c_int)]
+
+
 class KrylovResult(C.Structure):
     _fields_ = [("num_iterations", C.c_int), ("converged", C.c_int), ("error_flag", C.c_int),
                 ("rel_residual_norm", C.c_double), ("b_norm", C.c_double), ("real_residual_exit", C.c_int)]
@@ -135,6 +140,8 @@ def lib():
         "b200_gmres_solve_host": (i, [vp, vp, vp, C.POINTER(GmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_bicgstab_solve": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_bicgstab_solve_host": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
+        "b200_lgmres_solve": (i, [vp, vp, vp, C.POINTER(LgmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
+        "b200_lgmres_solve_host": (i, [vp, vp, vp, C.POINTER(LgmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError if the .so does not export a declared symbol

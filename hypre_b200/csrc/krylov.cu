@@ -290,6 +290,25 @@ extern "C" int b200_bicgstab_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, c
    return krylov_finish(c, status);
 }
 
+extern "C" int b200_lgmres_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
+                                 const double *b, double *x, b200_krylov_result *res, double *norms_h)
+{
+   ARG_CHECK(c != nullptr && A != nullptr && prm != nullptr && b != nullptr && x != nullptr && res != nullptr);
+   ARG_CHECK(prm->max_iter >= 0 && prm->aug_dim >= 0 && prm->k_dim > prm->aug_dim);
+   const int n = A->n_rows;
+   const int kd = prm->k_dim, ad = prm->aug_dim;
+   std::vector<double *> vec;
+   double *d_sc = nullptr, *h_sc = nullptr;
+   // p[0..k_dim], aug_vecs[0..aug_dim], a_aug_vecs[0..aug_dim-1], r, w (lgmres.c:255-290)
+   const int nvec = (kd + 1) + (ad + 1) + ad + 2;
+   B200_TRY(krylov_workspace(c, n, nvec, kd + ad + 2 + 4, &vec, &d_sc, &h_sc));
+   B200_TRY(krylov_prepare(c, A, amg, prm->diag_scale));
+   DevKrylovOps ops{c, A, amg, prm->diag_scale, n, d_sc, h_sc};
+   const int status = lgmres_core(ops, prm, b, x, vec.data(), vec.data() + kd + 1, vec.data() + kd + 1 + ad + 1,
+                                  vec[nvec - 2], vec[nvec - 1], res, norms_h);
+   return krylov_finish(c, status);
+}
+
 // host b/x: same staging as b200_pcg_solve_host
 template <class Prm, class Solve>
 static int solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const Prm *prm, const double *b_h, double *x_h,
@@ -316,4 +335,10 @@ extern "C" int b200_bicgstab_solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *a
                                         const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h)
 {
    return solve_host(c, A, amg, prm, b_h, x_h, res, norms_h, b200_bicgstab_solve);
+}
+
+extern "C" int b200_lgmres_solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
+                                      const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h)
+{
+   return solve_host(c, A, amg, prm, b_h, x_h, res, norms_h, b200_lgmres_solve);
 }

@@ -270,3 +270,184 @@ int bicgstab_core(B &ops, const b200_bicgstab_params *prm, const double *b, doub
    if (iter >= max_iter && r_norm > epsilon && epsilon > 0) { res->error_flag |= 256; }
    return B200_OK;
 }
+
+// LGMRES (hypre_LGMRESSolve, src/krylov/lgmres.c:337-...; ij -solver 51 / 50) with cf_tol = 0: restarted GMRES
+// whose space is augmented with the last aug_dim error approximations.  p: k_dim + 1 basis vectors; av: aug_dim + 1
+// vectors (the approximations, the last one a scratch slot); aav: aug_dim vectors (their images under A C);
+// r, w: work vectors.  Same backend methods as gmres_core (modified Gram-Schmidt).
+template <class B>
+int lgmres_core(B &ops, const b200_lgmres_params *prm, const double *b, double *x, double *const *p,
+                double *const *av, double *const *aav, double *r, double *w, b200_krylov_result *res, double *norms_h)
+{
+   const int k_dim = prm->k_dim, aug_dim = prm->aug_dim, kd = k_dim + aug_dim;
+   const int max_iter = prm->max_iter, min_iter = prm->min_iter;
+   const double epsmac = 1.e-16;
+   std::vector<double> rs(kd + 1, 0.0), c(kd + 1, 0.0), s(kd + 1, 0.0), col(kd + 2, 0.0);
+   std::vector<double> hh((size_t)(kd + 1) * (kd + 1), 0.0);
+   std::vector<int> aug_order(aug_dim + 1, 0);
+#define HH(a, bb) hh[(size_t)(a) * (kd + 1) + (bb)]
+   double d2[2] = {0.0, 0.0};
+   double b_norm, r_norm, r_norm_last = 0.0, den_norm, epsilon, t, gamma, tmp_norm;
+   int i = 0, j, k, ii, iter = 0, aug_ct = 0, it_arnoldi, it_total, it_aug, order, spot = 0;
+   const double *z = nullptr;
+   memset(res, 0, sizeof(*res));
+
+   KRY_TRY(ops.matvec(-1.0, x, 1.0, b, p[0]));
+   {
+      const double *xs[2] = {b, p[0]};
+      KRY_TRY(ops.dots(2, xs, xs, d2));
+   }
+   b_norm = sqrt(d2[0]);
+   res->b_norm = b_norm;
+   if (kry_not_finite(b_norm)) { res->error_flag = 1; return B200_OK; }
+   r_norm = sqrt(d2[1]);
+   if (kry_not_finite(r_norm)) { res->error_flag = 1; return B200_OK; }
+   if (norms_h) { norms_h[0] = r_norm; }
+   den_norm = b_norm > 0.0 ? b_norm : r_norm;
+   epsilon = prm->a_tol > prm->tol * den_norm ? prm->a_tol : prm->tol * den_norm;
+
+   while (iter < max_iter)
+   {
+      rs[0] = r_norm;
+      if (r_norm == 0.0) { return B200_OK; }           // lgmres.c:546-560 (num_iterations stays 0)
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         KRY_TRY(ops.matvec(-1.0, x, 1.0, b, r));
+         const double *xs[1] = {r};
+         KRY_TRY(ops.dots(1, xs, xs, d2));
+         r_norm = sqrt(d2[0]);
+         if (r_norm <= epsilon) { res->real_residual_exit = 1; break; }
+      }
+      t = 1.0 / r_norm;
+      r_norm_last = r_norm;
+      KRY_TRY(ops.scale(t, p[0]));
+      i = 0;
+      // number of Arnoldi steps of this cycle: the space keeps k_dim vectors (approx_constant) (:588-603)
+      it_arnoldi = prm->approx_constant ? k_dim - aug_ct : k_dim - aug_dim;
+      it_total = it_arnoldi + aug_ct;
+      it_aug = 0;
+      while (i < it_total && iter < max_iter)
+      {
+         i++; iter++;
+         if (i <= it_arnoldi)
+         {
+            KRY_TRY(ops.precond(p[i - 1], r, &z));
+            KRY_TRY(ops.matvec(1.0, z, 0.0, nullptr, p[i]));
+         }
+         else
+         {
+            // augmentation step: the stored image of the approximation of this order (:617-636)
+            it_aug++;
+            order = i - it_arnoldi - 1;
+            for (ii = 0; ii < aug_dim; ii++) { if (aug_order[ii] == order) { spot = ii; break; } }
+            KRY_TRY(ops.copy(aav[spot], p[i]));
+         }
+         KRY_TRY(ops.mgs(i, p, col.data()));
+         for (j = 0; j < i; j++) { HH(j, i - 1) = col[j]; }
+         t = sqrt(col[i]);
+         HH(i, i - 1) = t;
+         if (t != 0.0) { t = 1.0 / t; KRY_TRY(ops.scale(t, p[i])); }
+         for (j = 1; j < i; j++)
+         {
+            t = HH(j - 1, i - 1);
+            HH(j - 1, i - 1) = s[j - 1] * HH(j, i - 1) + c[j - 1] * t;
+            HH(j, i - 1) = -s[j - 1] * t + c[j - 1] * HH(j, i - 1);
+         }
+         t = HH(i, i - 1) * HH(i, i - 1);
+         t += HH(i - 1, i - 1) * HH(i - 1, i - 1);
+         gamma = sqrt(t);
+         if (gamma == 0.0) { gamma = epsmac; }
+         c[i - 1] = HH(i - 1, i - 1) / gamma;
+         s[i - 1] = HH(i, i - 1) / gamma;
+         rs[i] = -HH(i, i - 1) * rs[i - 1];
+         rs[i] /= gamma;
+         rs[i - 1] = c[i - 1] * rs[i - 1];
+         HH(i - 1, i - 1) = s[i - 1] * HH(i, i - 1) + c[i - 1] * HH(i - 1, i - 1);
+         r_norm = fabs(rs[i]);
+         if (norms_h) { norms_h[iter] = r_norm; }
+         if (r_norm <= epsilon && iter >= min_iter) { break; }
+      }
+      rs[i - 1] = rs[i - 1] / HH(i - 1, i - 1);
+      for (k = i - 2; k >= 0; k--)
+      {
+         t = 0.0;
+         for (j = k + 1; j < i; j++) { t -= HH(k, j) * rs[j]; }
+         t += rs[k];
+         rs[k] = t / HH(k, k);
+      }
+      // correction before the preconditioner = combination of the Arnoldi directions and of the approximations
+      // that served in this cycle (:712-755)
+      if (it_arnoldi > i) { it_arnoldi = i; }
+      if (!it_aug)
+      {
+         KRY_TRY(ops.copy(p[i - 1], w));
+         KRY_TRY(ops.scale(rs[i - 1], w));
+         for (j = i - 2; j >= 0; j--) { KRY_TRY(ops.axpy(rs[j], p[j], w)); }
+      }
+      else
+      {
+         KRY_TRY(ops.copy(p[0], w));
+         KRY_TRY(ops.scale(rs[0], w));
+         for (j = 1; j < it_arnoldi; j++) { KRY_TRY(ops.axpy(rs[j], p[j], w)); }
+         for (ii = 0; ii < it_aug; ii++)
+         {
+            for (j = 0; j < aug_dim; j++) { if (aug_order[j] == ii) { spot = j; break; } }
+            KRY_TRY(ops.axpy(rs[it_arnoldi + ii], av[spot], w));
+         }
+      }
+      KRY_TRY(ops.copy(w, av[aug_dim]));          // the new approximation, kept aside until the cycle is closed
+      KRY_TRY(ops.precond(w, r, &z));
+      KRY_TRY(ops.axpy(1.0, z, x));
+
+      if (r_norm <= epsilon && iter >= min_iter)
+      {
+         KRY_TRY(ops.matvec(-1.0, x, 1.0, b, r));
+         const double *xs[1] = {r};
+         KRY_TRY(ops.dots(1, xs, xs, d2));
+         r_norm = sqrt(d2[0]);
+         if (r_norm <= epsilon) { res->converged = 1; res->real_residual_exit = 1; break; }
+         KRY_TRY(ops.copy(r, p[0]));
+         i = 0;
+      }
+
+      // r0 (unscaled) into w; residual vector of the restart into p[0] (:785-810)
+      KRY_TRY(ops.copy(p[0], w));
+      KRY_TRY(ops.scale(r_norm_last, w));
+      for (j = i; j > 0; j--)
+      {
+         rs[j - 1] = -s[j - 1] * rs[j];
+         rs[j] = c[j - 1] * rs[j];
+      }
+      if (i) { KRY_TRY(ops.axpy(rs[i] - 1.0, p[i], p[i])); }
+      for (j = i - 1; j > 0; j--) { KRY_TRY(ops.axpy(rs[j], p[j], p[i])); }
+      if (i)
+      {
+         KRY_TRY(ops.axpy(rs[0] - 1.0, p[0], p[0]));
+         KRY_TRY(ops.axpy(1.0, p[i], p[0]));
+      }
+
+      // keep the new approximation (normalised) and its image A C z = (r0 - rm) / ||z|| for later cycles (:812-860)
+      if (aug_dim > 0)
+      {
+         if (!aug_ct) { spot = 0; aug_ct++; }
+         else if (aug_ct < aug_dim) { spot = aug_ct; aug_ct++; }
+         else { for (ii = 0; ii < aug_dim; ii++) { if (aug_order[ii] == aug_dim - 1) { spot = ii; } } }
+         KRY_TRY(ops.copy(av[aug_dim], av[spot]));
+         const double *xs[1] = {av[spot]};
+         KRY_TRY(ops.dots(1, xs, xs, d2));
+         tmp_norm = 1.0 / sqrt(d2[0]);
+         KRY_TRY(ops.scale(tmp_norm, av[spot]));
+         for (ii = 0; ii < aug_dim; ii++) { aug_order[ii]++; }
+         aug_order[spot] = 0;
+         KRY_TRY(ops.copy(w, aav[spot]));
+         KRY_TRY(ops.scale(-1.0, aav[spot]));
+         KRY_TRY(ops.axpy(1.0, p[0], aav[spot]));
+         KRY_TRY(ops.scale(-tmp_norm, aav[spot]));
+      }
+   }
+#undef HH
+   res->num_iterations = iter;
+   res->rel_residual_norm = b_norm > 0.0 ? r_norm / b_norm : r_norm;
+   if (iter >= max_iter && r_norm > epsilon && epsilon > 0) { res->error_flag |= 256; }
+   return B200_OK;
+}

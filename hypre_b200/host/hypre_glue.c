@@ -1084,6 +1084,76 @@ HYPRE_Int hypre_FlexGMRESSolve(void *fgmres_vdata, void *A, void *b, void *x)
    return hypre_error_flag;
 }
 
+/* hypre_LGMRESSolve (src/krylov/lgmres.c:337-...) for the ParCSR operator table: GMRES augmented with the last
+ * aug_dim error approximations (ij -solver 51 / 50). */
+HYPRE_Int hypre_LGMRESSolve(void *lgmres_vdata, void *A, void *b, void *x)
+{
+   static pcg_solve_fn next = NULL;
+   hypre_LGMRESData      *g  = (hypre_LGMRESData *) lgmres_vdata;
+   hypre_LGMRESFunctions *fn = g->functions;
+   hypre_ParCSRMatrix    *pA = (hypre_ParCSRMatrix *) A;
+   hypre_ParVector       *pb = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
+   mirror_t *m;
+   b200_amg *amg = NULL;
+   b200_lgmres_params prm;
+   b200_krylov_result res;
+   HYPRE_Int my_id, num_procs;
+   double *norms, *own_norms = NULL;
+   int status, diag_scale = 0;
+
+   if (!next) { next = (pcg_solve_fn) next_sym("hypre_LGMRESSolve"); }
+   if (!g_enabled) { return next(lgmres_vdata, A, b, x); }
+   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(lgmres_vdata, A, b, x); }
+
+   if (g->cf_tol > 0.0 || g->k_dim <= g->aug_dim || hypre_ParVectorNumVectors(pb) > 1)
+   {
+      GLUE_FAIL("LGMRES option outside the device path (cf_tol / aug_dim >= k_dim / multivector)");
+      return hypre_error_flag;
+   }
+   m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
+   if (!m) { return hypre_error_flag; }
+
+   memset(&prm, 0, sizeof(prm));
+   prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
+   prm.k_dim = g->k_dim; prm.aug_dim = g->aug_dim; prm.approx_constant = g->approx_constant; prm.diag_scale = diag_scale;
+   g->converged = 0;
+   (*(fn->CommInfo))(A, &my_id, &num_procs);
+   norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
+   if (!norms && g->print_level > 1) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
+   {
+      double *db, *dx;
+      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
+      status = db ? b200_lgmres_solve(glue_ctx(), m->A, amg, &prm, db, dx, &res, norms)
+                  : b200_lgmres_solve_host(glue_ctx(), m->A, amg, &prm,
+                                           hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
+                                           hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
+   }
+   if (status != B200_OK) { free(own_norms); GLUE_FAIL("device LGMRES failed"); return hypre_error_flag; }
+   if (verbose() && g_rank == 0)
+   {
+      fprintf(stderr, "hypre_b200: LGMRES(%d,%d) solve on the device: %d iterations, relative residual %.6e\n",
+              (int) g->k_dim, (int) g->aug_dim, res.num_iterations, res.rel_residual_norm);
+   }
+   if (res.error_flag & 1)
+   {
+      if (g->logging > 0 || g->print_level > 0) { krylov_nan_message("hypre_LGMRESSolve"); }
+      free(own_norms);
+      hypre_error(HYPRE_ERROR_GENERIC);
+      return hypre_error_flag;
+   }
+   if (g->print_level > 1 && my_id == 0 && g_rank == 0)
+   {
+      hypre_b200_krylov_report(0, norms, res.num_iterations, res.b_norm, res.rel_residual_norm, res.real_residual_exit);
+   }
+   free(own_norms);
+   g->converged = res.converged;
+   g->num_iterations = res.num_iterations;
+   g->rel_residual_norm = res.rel_residual_norm;
+   hypre_ParVectorAllZeros(px) = 0;
+   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   return hypre_error_flag;
+}
+
 /* hypre_BiCGSTABSolve (src/krylov/bicgstab.c:226-640) for the ParCSR operator table. */
 HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
 {

@@ -324,6 +324,20 @@ typedef struct {
    int    diag_scale;
 } b200_bicgstab_params;
 
+/* hypre_LGMRESSolve (src/krylov/lgmres.c:337-...; ij -solver 51 / 50): GMRES(k_dim) augmented with the last
+ * aug_dim error approximations (HYPRE_LGMRESSetAugDim, default 2); approx_constant = 1 keeps the space at k_dim
+ * vectors (lgmres.c:105, the reference's fixed setting) */
+typedef struct {
+   double tol;
+   double a_tol;
+   int    max_iter;
+   int    min_iter;
+   int    k_dim;
+   int    aug_dim;
+   int    approx_constant;
+   int    diag_scale;
+} b200_lgmres_params;
+
 typedef struct {
    int    num_iterations;
    int    converged;
@@ -340,12 +354,16 @@ int b200_gmres_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_gm
                      const double *b, double *x, b200_krylov_result *res, double *norms_h);
 int b200_bicgstab_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
                         const double *b, double *x, b200_krylov_result *res, double *norms_h);
+int b200_lgmres_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
+                      const double *b, double *x, b200_krylov_result *res, double *norms_h);
 /* the same with HOST b/x (H2D of b and x, device solve, D2H of x): the calls the hypre_GMRESSolve /
  * hypre_BiCGSTABSolve bindings make for host-resident hypre vectors */
 int b200_gmres_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_gmres_params *prm,
                           const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
 int b200_bicgstab_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
                              const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
+int b200_lgmres_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
+                           const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
 
 #ifdef __cplusplus
 }

@@ -53,10 +53,14 @@ def main():
             res = capi.KrylovResult()
             return res, lambda: capi.check(L.b200_gmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
                                                               capi.ptr(norms)))
+        if kind == "lgmres":
+            prm, res = capi.LgmresParams(1e-8, 0.0, 1000, 0, args.k, 2, 1, 0), capi.KrylovResult()
+            return res, lambda: capi.check(L.b200_lgmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
+                                                               capi.ptr(norms)))
         prm, res = capi.BicgstabParams(1e-8, 0.0, 1000, 0, 0), capi.KrylovResult()
         return res, lambda: capi.check(L.b200_bicgstab_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res),
                                                              capi.ptr(norms)))
-    for kind in ("pcg", "gmres", "cogmres", "flexgmres", "bicgstab"):
+    for kind in ("pcg", "gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"):
         res, run = solver(kind)
 
         def step():

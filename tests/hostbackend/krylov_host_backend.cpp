@@ -199,3 +199,18 @@ extern "C" int kht_bicgstab_dist(int n_local, const double *diag, kht_matvec_cb 
    return bicgstab_core(ops, prm, b, x, store[0].data(), store[1].data(), store[2].data(), store[3].data(),
                         store[4].data(), store[5].data(), res, norms);
 }
+
+extern "C" int kht_lgmres(int n, const int *ia, const int *ja, const double *a, orc_amg *amg, int kind,
+                          const b200_lgmres_params *prm, const double *b, double *x, b200_krylov_result *res,
+                          double *norms)
+{
+   HostKrylovOps ops{n, ia, ja, a, amg, kind};
+   const int nv = prm->k_dim + 1 + (prm->aug_dim + 1) + prm->aug_dim + 2;
+   std::vector<std::vector<double>> store(nv, std::vector<double>((size_t)n, 0.0));
+   std::vector<double *> vec;
+   for (auto &v : store) { vec.push_back(v.data()); }
+   double *const *p = vec.data();
+   double *const *av = vec.data() + prm->k_dim + 1;
+   double *const *aav = av + prm->aug_dim + 1;
+   return lgmres_core(ops, prm, b, x, p, av, aav, vec[nv - 2], vec[nv - 1], res, norms);
+}

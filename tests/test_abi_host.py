@@ -153,7 +153,7 @@ def test_multirank_binding_fails_loudly_without_gpu(built):
     assert "Iterations = 0" in r.stdout
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, kind):
     """hypre_GMRESSolve / hypre_BiCGSTABSolve are interposed: without a GPU the solve raises the hypre error flag
     and leaves x alone; options outside the device path are rejected the same way (never run on the CPU)"""
@@ -163,7 +163,7 @@ def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, k
     A = H.laplacian(8, 8, 8)
     b = A.vector(1.0); x = A.vector(0.0)
     s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
-         "bicgstab": H.ParCSRBiCGSTAB}[kind]()
+         "lgmres": H.ParCSRLGMRES, "bicgstab": H.ParCSRBiCGSTAB}[kind]()
     s.SetDiagScalePrecond()
     s.Setup(A, b, x)
     H.clear_errors()
@@ -174,7 +174,7 @@ def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, k
         s.SetRelChange(1)
     elif kind == "cogmres":
         s.SetCGS(2)
-    elif kind == "flexgmres":
+    elif kind in ("flexgmres", "lgmres"):
         s.SetConvergenceFactorTol(0.5)
     else:
         s.SetStopCrit(1)

@@ -42,6 +42,9 @@ def device_solve(ctx, kind, dA, damg, b, x0, diag_scale=0, tol=1e-8, a_tol=0.0, 
         prm = capi.GmresParams(tol, a_tol, max_iter, min_iter, k_dim, skip, diag_scale, 1 if kind == "cogmres" else 0,
                                1 if kind == "flexgmres" else 0)
         capi.check(L.b200_gmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res), capi.ptr(norms)))
+    elif kind == "lgmres":
+        prm = capi.LgmresParams(tol, a_tol, max_iter, min_iter, k_dim, 2, 1, diag_scale)
+        capi.check(L.b200_lgmres_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res), capi.ptr(norms)))
     else:
         prm = capi.BicgstabParams(tol, a_tol, max_iter, min_iter, diag_scale)
         capi.check(L.b200_bicgstab_solve(ctx, dA, damg, C.byref(prm), db.ptr, dx.ptr, C.byref(res), capi.ptr(norms)))
@@ -50,7 +53,7 @@ def device_solve(ctx, kind, dA, damg, b, x0, diag_scale=0, tol=1e-8, a_tol=0.0, 
     return x, res, norms
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap7_32_rlx18", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx18_pc3"])
 def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
     H.set_device_path(True)
@@ -73,6 +76,7 @@ def test_device_amg_krylov_matches_oracle(H, ctx, kind, name):
 @pytest.mark.parametrize("kind,k_dim,diag", [("gmres", 5, 1), ("gmres", 3, 1), ("gmres", 20, 1), ("gmres", 7, 0),
                                              ("cogmres", 5, 1), ("cogmres", 13, 1), ("cogmres", 6, 0),
                                              ("flexgmres", 5, 1), ("flexgmres", 11, 0),
+                                             ("lgmres", 5, 1), ("lgmres", 9, 0),
                                              ("bicgstab", 0, 1), ("bicgstab", 0, 0)])
 def test_device_long_runs_and_restarts_match_oracle(H, ctx, kind, k_dim, diag):
     """diagonal scaling / no preconditioner on a 7-pt Laplacian: many iterations and restart cycles"""
@@ -102,7 +106,7 @@ def test_device_long_runs_and_restarts_match_oracle(H, ctx, kind, k_dim, diag):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_device_exits(H, ctx, kind):
     """max_iter exit (HYPRE_ERROR_CONV), zero right-hand side, Inf in b, nonzero initial guess"""
     A = H.laplacian(10, 9, 8)
@@ -130,7 +134,7 @@ def test_device_exits(H, ctx, kind):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_interposed_hypre_api_matches_reference_in_process(H, kind):
     """HYPRE_ParCSRGMRESSolve / HYPRE_ParCSRBiCGSTABSolve: device path and the reference's CPU loop on the same
     objects in one process"""
@@ -139,7 +143,8 @@ def test_interposed_hypre_api_matches_reference_in_process(H, kind):
         A = H.laplacian(24, 24, 24)
         b, x = A.vector(1.0), A.vector(0.0)
         amg = H.BoomerAMG(relax_type=16)
-        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES}[kind](print_level=1) if kind != "bicgstab" else H.ParCSRBiCGSTAB()
+        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
+             "lgmres": H.ParCSRLGMRES}[kind](print_level=1) if kind != "bicgstab" else H.ParCSRBiCGSTAB()
         s.SetPrecond(amg)
         s.Setup(A, b, x)
         H.clear_errors()
@@ -160,6 +165,7 @@ IJ_CASES = ["-laplacian -n 24 24 24 -solver 3 -rlx 16", "-laplacian -n 23 29 31 
             "-laplacian -n 24 24 24 -solver 1 -rlx 16 -precon_cycles 2", "-laplacian -n 24 24 24 -solver 1 -rlx 0 -w 0.8", "-laplacian -n 32 32 32 -solver 3 -rlx 18 -k 3",
             "-laplacian -n 12 11 10 -solver 4", "-laplacian -n 24 24 24 -solver 16 -rlx 18", "-laplacian -n 12 11 10 -solver 17",
             "-laplacian -n 24 24 24 -solver 61 -rlx 18", "-laplacian -n 12 11 10 -solver 60",
+            "-laplacian -n 24 24 24 -solver 51 -rlx 18", "-laplacian -n 12 11 10 -solver 50",
             "-27pt -n 20 20 20 -solver 9 -rlx 11", "-laplacian -n 12 11 10 -solver 10"]
 
 
@@ -180,7 +186,7 @@ def test_unchanged_ij_gmres_bicgstab_on_the_device(args):
     it_d, fin_d, rows_d, out_d = run(IJ_B200)
     it_r, fin_r, rows_r, _ = run(IJ_REF)
     assert "solve on the device" in out_d            # not the reference's CPU loop
-    long_run = any(k in args for k in ("-solver 4", "-solver 10", "-solver 17", "-solver 60"))
+    long_run = any(k in args for k in ("-solver 4", "-solver 10", "-solver 17", "-solver 60", "-solver 50"))
     assert abs(it_d - it_r) <= (1 if long_run else 0), (it_d, it_r)
     m = min(len(rows_d), len(rows_r))
     assert m >= min(it_d, it_r) - 1 and m > 0       # the binding prints the reference's residual table
@@ -214,7 +220,7 @@ def test_host_spmvT_entry_matches_reference(H, ctx):
         x.destroy(); y.destroy()
 
 
-@pytest.mark.parametrize("kind", ["pcg", "gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["pcg", "gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_device_bound_vectors_solve_in_place(H, ctx, kind):
     """b and x bound to device arrays (hypre_b200_vector_bind_device) -- the HYPRE_*Solve call runs on
     them in place: same iterations and solution as the host-vector call, the host array of x untouched until
@@ -224,7 +230,7 @@ def test_device_bound_vectors_solve_in_place(H, ctx, kind):
     b, x = A.vector(1.0), A.vector(0.0)
     amg = H.BoomerAMG(relax_type=16)
     s = {"pcg": H.ParCSRPCG, "gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
-         "bicgstab": H.ParCSRBiCGSTAB}[kind]()
+         "lgmres": H.ParCSRLGMRES, "bicgstab": H.ParCSRBiCGSTAB}[kind]()
     s.SetPrecond(amg)
     s.Setup(A, b, x)
     H.clear_errors()

@@ -21,7 +21,7 @@ from hypre_b200 import ROOT
 HB = os.path.join(ROOT, "tests", "hostbackend")
 
 
-from hypre_b200.capi import BicgstabParams, GmresParams, KrylovResult  # noqa: E402  (layout of include/b200amg.h)
+from hypre_b200.capi import BicgstabParams, GmresParams, KrylovResult, LgmresParams  # noqa: E402  (layout of include/b200amg.h)
 
 
 @pytest.fixture(scope="module")
@@ -39,6 +39,7 @@ def kht(built):
     vp, i = C.c_void_p, C.c_int
     L.kht_gmres.argtypes = [i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp]
     L.kht_bicgstab.argtypes = [i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp]
+    L.kht_lgmres.argtypes = [i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp]
     return L
 
 
@@ -65,6 +66,10 @@ def run_core(kht, kind, Ad, orc, precond, b, x0, tol=1e-8, a_tol=0.0, k_dim=5, m
                           1 if kind == "flexgmres" else 0)
         st = kht.kht_gmres(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
                            C.byref(res), O.p(norms))
+    elif kind == "lgmres":
+        prm = LgmresParams(tol, a_tol, max_iter, min_iter, k_dim, 2, 1, 1 if precond == 1 else 0)
+        st = kht.kht_lgmres(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
+                            C.byref(res), O.p(norms))
     else:
         prm = BicgstabParams(tol, a_tol, max_iter, min_iter, 1 if precond == 1 else 0)
         st = kht.kht_bicgstab(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
@@ -77,7 +82,7 @@ def check_against_oracle(kht, kind, Ad, orc, precond, b, x0, **kw):
     x, res, norms = run_core(kht, kind, Ad, orc, precond, b, x0, **kw)
     okw = dict(precond=precond, tol=kw.get("tol", 1e-8), a_tol=kw.get("a_tol", 0.0), min_iter=kw.get("min_iter", 0),
                max_iter=kw.get("max_iter", 100))
-    if kind in ("gmres", "cogmres", "flexgmres"):
+    if kind in ("gmres", "cogmres", "flexgmres", "lgmres"):
         okw.update(k_dim=kw.get("k_dim", 5), skip_real_r_check=kw.get("skip", 0))
     xo, it, no, rel, conv = getattr(orc, kind)(b, x0, **okw)
     assert res.num_iterations == it and res.converged == conv
@@ -87,7 +92,7 @@ def check_against_oracle(kht, kind, Ad, orc, precond, b, x0, **kw):
     return res
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 @pytest.mark.parametrize("name", ["lap7_24_rlx16", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx7_w08"])
 def test_core_with_amg_preconditioner(kht, ref_off, kind, name):
     H = ref_off
@@ -106,6 +111,7 @@ def test_core_with_amg_preconditioner(kht, ref_off, kind, name):
 @pytest.mark.parametrize("kind,k_dim,precond", [("gmres", 5, 1), ("gmres", 3, 1), ("gmres", 20, 1), ("gmres", 1, 1),
                                                 ("gmres", 7, 2), ("cogmres", 5, 1), ("cogmres", 6, 2), ("cogmres", 13, 1),
                                                 ("flexgmres", 5, 1), ("flexgmres", 4, 2), ("flexgmres", 11, 1),
+                                                ("lgmres", 5, 1), ("lgmres", 3, 2), ("lgmres", 12, 1),
                                                 ("bicgstab", 0, 1), ("bicgstab", 0, 2)])
 def test_core_restarts_and_long_runs(kht, ref_off, kind, k_dim, precond):
     """diagonal scaling / no preconditioner: tens to hundreds of iterations, many restart cycles"""
@@ -118,7 +124,7 @@ def test_core_restarts_and_long_runs(kht, ref_off, kind, k_dim, precond):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 @pytest.mark.parametrize("max_iter", [0, 1, 7, 10])
 def test_core_max_iter_exit_sets_conv_error(kht, ref_off, kind, max_iter):
     A = ref_off.laplacian(10, 9, 8)
@@ -131,7 +137,7 @@ def test_core_max_iter_exit_sets_conv_error(kht, ref_off, kind, max_iter):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_core_min_iter_skip_check_and_abs_tol(kht, ref_off, kind):
     A = ref_off.laplacian(9, 8, 7)
     Ad, _ = A.blocks()
@@ -145,7 +151,7 @@ def test_core_min_iter_skip_check_and_abs_tol(kht, ref_off, kind):
     orc.destroy()
 
 
-@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "bicgstab"])
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
 def test_core_trivial_inputs(kht, ref_off, kind):
     """zero right-hand side with zero guess (r_norm == 0: immediate return), exact initial guess (already
     converged before the first iteration), Inf in b (error flag 1, as hypre_error(HYPRE_ERROR_GENERIC))"""

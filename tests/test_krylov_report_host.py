@@ -13,7 +13,7 @@ import pytest
 from test_amg_report_host import capture_stdout, same_text
 
 
-@pytest.mark.parametrize("kind,precond", [("gmres", "amg"), ("gmres", "ds"), ("cogmres", "amg"), ("cogmres", "ds"), ("flexgmres", "amg"), ("flexgmres", "ds"),
+@pytest.mark.parametrize("kind,precond", [("gmres", "amg"), ("gmres", "ds"), ("cogmres", "amg"), ("cogmres", "ds"), ("flexgmres", "amg"), ("flexgmres", "ds"), ("lgmres", "amg"), ("lgmres", "ds"),
                                           ("bicgstab", "amg"), ("bicgstab", "ds")])
 def test_krylov_report_equals_the_reference_text(H, kind, precond):
     L = H.lib()
@@ -23,7 +23,8 @@ def test_krylov_report_equals_the_reference_text(H, kind, precond):
     try:
         A = H.laplacian(13, 12, 11)
         b, x = A.vector(1.0), A.vector(0.0)
-        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES}[kind](print_level=3, max_iter=300) if kind != "bicgstab" \
+        s = {"gmres": H.ParCSRGMRES, "cogmres": H.ParCSRCOGMRES, "flexgmres": H.ParCSRFlexGMRES,
+             "lgmres": H.ParCSRLGMRES}[kind](print_level=3, max_iter=300) if kind != "bicgstab" \
             else H.ParCSRBiCGSTAB(print_level=3, logging=3, max_iter=300)
         if precond == "amg":
             amg = H.BoomerAMG(relax_type=18)
@@ -39,7 +40,7 @@ def test_krylov_report_equals_the_reference_text(H, kind, precond):
     norms = np.ascontiguousarray(s.norms())
     it = s.num_iterations
     b_norm = float(np.sqrt(b.numpy() @ b.numpy()))
-    ours = capture_stdout(lambda: L.hypre_b200_krylov_report({"gmres": 0, "flexgmres": 0, "bicgstab": 1, "cogmres": 2}[kind], norms.ctypes.data_as(C.c_void_p),
+    ours = capture_stdout(lambda: L.hypre_b200_krylov_report({"gmres": 0, "flexgmres": 0, "lgmres": 0, "bicgstab": 1, "cogmres": 2}[kind], norms.ctypes.data_as(C.c_void_p),
                                                              it, b_norm, s.final_rel_norm, 1))
     assert "Final L2 norm of residual" in ref_text and "Iters     resid.norm     conv.rate  rel.res.norm" in ref_text
     same_text(ours, ref_text)
