@@ -45,6 +45,9 @@ void orc_amg_set_precond_cycles(orc_amg *h, int cycles);
 int  orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, int two_norm,
              double *norms, double *rel_norms, int *converged);
 
+/* options read by the Krylov restatements below at the start of a solve: convergence-factor tolerance (all) and
+ * BiCGSTAB's stop_crit; set, solve, reset to (0, 0) */
+void orc_krylov_set_options(double cf_tol, int stop_crit);
 /* precond_kind: 0 = one AMG cycle, 1 = diagonal scaling (HYPRE_ParCSRDiagScale), 2 = identity.
  * hypre_GMRESSolve (krylov/gmres.c:274-930, rel_change = 0, cf_tol = 0): returns the iteration count;
  * norms[0..iters] as the reference logs them. */

@@ -283,6 +283,25 @@ int orc_pcg(orc_amg *h, const double *b, double *x, double tol, int max_iter, in
    return i;
 }
 
+/* Options the Krylov restatements below read at the start of a solve (test infrastructure: set, solve, reset):
+ * cf_tol = convergence-factor tolerance (gmres.c:632-652, bicgstab.c:519-540, ...), stop_crit = BiCGSTAB's absolute
+ * stopping rule (bicgstab.c:372-392). */
+static double g_orc_cf_tol = 0.0;
+static int    g_orc_stop_crit = 0;
+void orc_krylov_set_options(double cf_tol, int stop_crit) { g_orc_cf_tol = cf_tol; g_orc_stop_crit = stop_crit; }
+
+/* the reference's "adequate progress" test: returns 1 when the weighted average convergence factor exceeds cf_tol */
+static int orc_cf_exceeded(double cf_tol, double r_norm, double r_norm_0, int iter, double *cf_ave_0, double *cf_ave_1)
+{
+   double weight;
+   *cf_ave_0 = *cf_ave_1;
+   *cf_ave_1 = pow(r_norm / r_norm_0, 1.0 / (2.0 * iter));
+   weight = fabs(*cf_ave_1 - *cf_ave_0);
+   weight = weight / (*cf_ave_1 > *cf_ave_0 ? *cf_ave_1 : *cf_ave_0);
+   weight = 1.0 - weight;
+   return weight * *cf_ave_1 > cf_tol;
+}
+
 /* ---- preconditioner shared by the GMRES / BiCGSTAB restatements below.
  * kind 0: one AMG cycle with a zero initial guess (the callers ClearVector first, which sets all_zeros);
  * kind 1: HYPRE_ParCSRDiagScale (parcsr_ls/HYPRE_parcsr_pcg.c:267-277): z = r ./ a_ii, diagonal entry first
@@ -317,7 +336,9 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
    double **hh = (double **) calloc((size_t) k_dim + 1, sizeof(double *));
    double **pv = (double **) calloc((size_t) k_dim + 1, sizeof(double *));   /* flexgmres.c: pre_vecs */
    double b_norm, r_norm, den_norm, epsilon, t, gamma, real_r_norm_old, real_r_norm_new;
-   int i, j, k, q, iter = 0;
+   const double cf_tol = g_orc_cf_tol;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
+   int i, j, k, q, iter = 0, break_value = 0;
    for (i = 0; i <= k_dim; i++)
    {
       p[i] = (double *) calloc((size_t) n, sizeof(double));
@@ -329,6 +350,7 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
    b_norm = sqrt(orc_dot(n, b, b));
    real_r_norm_old = b_norm;
    r_norm = sqrt(orc_dot(n, p[0], p[0]));
+   r_norm_0 = r_norm;
    if (norms) { norms[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
@@ -394,8 +416,10 @@ static int orc_gmres_impl(orc_amg *h, int precond_kind, const double *b, double 
          hh[i - 1][i - 1] = s[i - 1] * hh[i][i - 1] + c[i - 1] * hh[i - 1][i - 1];
          r_norm = fabs(rs[i]);
          if (norms) { norms[iter] = r_norm; }
+         if (cf_tol > 0.0 && orc_cf_exceeded(cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break_value = 1; break; }
          if (r_norm <= epsilon && iter >= min_iter) { break; }
       }
+      if (break_value) { break; }        /* cf_tol: leave without the update of this cycle (gmres.c:732-735) */
       /* solution of the upper triangular system, update of x through the preconditioner */
       rs[i - 1] = rs[i - 1] / hh[i - 1][i - 1];
       for (k = i - 2; k >= 0; k--)
@@ -495,6 +519,8 @@ int orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, doubl
    double *p = (double *) calloc((size_t) n, sizeof(double));
    double *q = (double *) calloc((size_t) n, sizeof(double));
    double alpha, beta, gamma, epsilon, temp, res, r_norm, b_norm, den_norm, gn, gd;
+   const double cf_tol = g_orc_cf_tol;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
    int iter = 0, k, ret;
    if (converged) { *converged = 0; }
    orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r0);
@@ -503,9 +529,11 @@ int orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, doubl
    b_norm = sqrt(orc_dot(n, b, b));
    res = orc_dot(n, r0, r0);
    r_norm = sqrt(res);
+   r_norm_0 = r_norm;
    if (norms) { norms[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
+   if (g_orc_stop_crit) { epsilon = a_tol == 0.0 ? tol : a_tol; }     /* bicgstab.c:372-383 */
    if (rel_resid && b_norm > 0.0) { *rel_resid = r_norm / b_norm; }
    ret = 0;
    if (r_norm == 0.0) { goto done; }
@@ -535,6 +563,7 @@ int orc_bicgstab(orc_amg *h, int precond_kind, const double *b, double *x, doubl
          r_norm = sqrt(orc_dot(n, r, r));
          if (r_norm <= epsilon) { if (converged) { *converged = 1; } break; }
       }
+      if (cf_tol > 0.0 && orc_cf_exceeded(cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break; }
       if (fabs(res) >= epsmac) { beta = 1.0 / res; }
       else { ret = -iter - 1; goto done; }
       res = orc_dot(n, r0, r);
@@ -574,7 +603,9 @@ int orc_lgmres(orc_amg *h, int precond_kind, const double *b, double *x, double 
    double *s = (double *) calloc((size_t) kd + 1, sizeof(double));
    double **hh = (double **) calloc((size_t) kd + 1, sizeof(double *));
    double b_norm, r_norm, r_norm_last = 0.0, den_norm, epsilon, t, gamma, tmp_norm;
-   int i, j, k, q, ii, iter = 0, aug_ct = 0, it_arnoldi, it_total, it_aug, order, spot = 0;
+   const double cf_tol = g_orc_cf_tol;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
+   int i, j, k, q, ii, iter = 0, aug_ct = 0, it_arnoldi, it_total, it_aug, order, spot = 0, break_value = 0;
    for (i = 0; i <= k_dim; i++) { p[i] = (double *) calloc((size_t) n, sizeof(double)); }
    for (i = 0; i <= aug_dim; i++) { av[i] = (double *) calloc((size_t) n, sizeof(double)); aav[i] = (double *) calloc((size_t) n, sizeof(double)); }
    for (i = 0; i <= kd; i++) { hh[i] = (double *) calloc((size_t) kd + 1, sizeof(double)); }
@@ -583,6 +614,7 @@ int orc_lgmres(orc_amg *h, int precond_kind, const double *b, double *x, double 
    orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, p[0]);
    b_norm = sqrt(orc_dot(n, b, b));
    r_norm = sqrt(orc_dot(n, p[0], p[0]));
+   r_norm_0 = r_norm;
    if (norms) { norms[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = a_tol > tol * den_norm ? a_tol : tol * den_norm;
@@ -644,8 +676,10 @@ int orc_lgmres(orc_amg *h, int precond_kind, const double *b, double *x, double 
          hh[i - 1][i - 1] = s[i - 1] * hh[i][i - 1] + c[i - 1] * hh[i - 1][i - 1];
          r_norm = fabs(rs[i]);
          if (norms) { norms[iter] = r_norm; }
+         if (cf_tol > 0.0 && orc_cf_exceeded(cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break_value = 1; break; }
          if (r_norm <= epsilon && iter >= min_iter) { break; }
       }
+      if (break_value) { break; }
       rs[i - 1] = rs[i - 1] / hh[i - 1][i - 1];
       for (k = i - 2; k >= 0; k--)
       {

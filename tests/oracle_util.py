@@ -38,6 +38,7 @@ def lib():
         L.orc_cogmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_flexgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_lgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, i, vp, vp, vp]
+        L.orc_krylov_set_options.argtypes = [d, i]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
@@ -229,6 +230,19 @@ class OracleAMG:
         if self.h:
             lib().orc_amg_destroy(self.h)
             self.h = None
+
+
+class krylov_options:
+    """with krylov_options(cf_tol=0.7): ...   the oracle's Krylov solves inside read these (orc_krylov_set_options)"""
+
+    def __init__(self, cf_tol=0.0, stop_crit=0):
+        self.v = (float(cf_tol), int(stop_crit))
+
+    def __enter__(self):
+        lib().orc_krylov_set_options(*self.v)
+
+    def __exit__(self, *a):
+        lib().orc_krylov_set_options(0.0, 0)
 
 
 def golden():

@@ -208,3 +208,56 @@ def test_oracle_krylov_options_match_reference(ref_off, kind, opts):
     np.testing.assert_allclose(rel, s.final_rel_norm, rtol=1e-9)
     np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
     orc.destroy()
+
+
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
+@pytest.mark.parametrize("cf_tol", [0.7, 0.95])
+def test_oracle_convergence_factor_tolerance_matches_reference(ref_off, kind, cf_tol):
+    """cf_tol (HYPRE_*SetConvergenceFactorTol): the solve is abandoned when the weighted average convergence factor
+    exceeds it -- GMRES-type solvers then leave WITHOUT the update of the running restart cycle (gmres.c:732-735)"""
+    H = ref_off
+    A = H.laplacian(9, 8, 7)
+    b, x = A.vector(1.0), A.vector(0.0)
+    s = _solver(H, kind, None, k_dim=6, max_iter=300)
+    s.SetConvergenceFactorTol(float(cf_tol))
+    s.Setup(A, b, x)
+    H.clear_errors()
+    s.Solve(A, b, x)
+    H.clear_errors()
+    Ad, _ = A.blocks()
+    orc = O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
+    kw = dict(precond=1, max_iter=300)
+    if kind != "bicgstab":
+        kw["k_dim"] = 6
+    with O.krylov_options(cf_tol=cf_tol):
+        xo, it, norms, rel, conv = getattr(orc, kind)(b.numpy(), np.zeros(x.size), **kw)
+    assert it == s.num_iterations and conv == s.converged
+    if cf_tol == 0.7:
+        assert it < 20 and conv == 0          # diagonal scaling on a Laplacian contracts by ~0.9 per step: abandoned
+    np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
+    np.testing.assert_allclose(rel, s.final_rel_norm, rtol=1e-9)
+    np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
+    orc.destroy()
+
+
+def test_oracle_bicgstab_stop_crit_matches_reference(ref_off):
+    """stop_crit = 1: |r| <= tol as an ABSOLUTE bound (a_tol when that is set), bicgstab.c:372-383"""
+    H = ref_off
+    A = H.laplacian(9, 8, 7)
+    Ad, _ = A.blocks()
+    orc = O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
+    for tol, a_tol in ((1e-3, 0.0), (1e-3, 1e-6)):
+        b, x = A.vector(1.0), A.vector(0.0)
+        s = _solver(H, "bicgstab", None, tol=tol, max_iter=300)
+        s.SetStopCrit(1)
+        s.SetAbsoluteTol(float(a_tol))
+        s.Setup(A, b, x)
+        H.clear_errors()
+        s.Solve(A, b, x)
+        assert H.error_flag() == 0
+        with O.krylov_options(stop_crit=1):
+            xo, it, norms, rel, conv = orc.bicgstab(b.numpy(), np.zeros(x.size), precond=1, tol=tol, a_tol=a_tol, max_iter=300)
+        assert it == s.num_iterations and conv == s.converged == 1
+        np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
+        np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
+    orc.destroy()
