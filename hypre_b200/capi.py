@@ -32,17 +32,18 @@ class PcgResult(C.Structure):
 class GmresParams(C.Structure):
     _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
                 ("k_dim", C.c_int), ("skip_real_r_check", C.c_int), ("diag_scale", C.c_int), ("ortho", C.c_int),
-                ("flex", C.c_int)]
+                ("flex", C.c_int), ("cf_tol", C.c_double)]
 
 
 class BicgstabParams(C.Structure):
     _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
-                ("diag_scale", C.c_int)]
+                ("diag_scale", C.c_int), ("stop_crit", C.c_int), ("cf_tol", C.c_double)]
 
 
 class LgmresParams(C.Structure):
     _fields_ = [("tol", C.c_double), ("a_tol", C.c_double), ("max_iter", C.c_int), ("min_iter", C.c_int),
-                ("k_dim", C.c_int), ("aug_dim", C.c_int), ("approx_constant", C.c_int), ("diag_scale", C.c_int)]
+                ("k_dim", C.c_int), ("aug_dim", C.c_int), ("approx_constant", C.c_int), ("diag_scale", C.c_int),
+                ("cf_tol", C.c_double)]
 
 
 class KrylovResult(C.Structure):

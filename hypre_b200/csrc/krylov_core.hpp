@@ -33,6 +33,18 @@
 
 #define KRY_TRY(expr) do { int _s = (expr); if (_s != B200_OK) return _s; } while (0)
 
+// the reference's "adequate progress" test (gmres.c:632-652, bicgstab.c:519-540): true when the weighted average
+// convergence factor exceeds cf_tol
+static inline bool kry_cf_exceeded(double cf_tol, double r_norm, double r_norm_0, int iter, double *cf_ave_0, double *cf_ave_1)
+{
+   *cf_ave_0 = *cf_ave_1;
+   *cf_ave_1 = pow(r_norm / r_norm_0, 1.0 / (2.0 * iter));
+   double weight = fabs(*cf_ave_1 - *cf_ave_0);
+   weight = weight / (*cf_ave_1 > *cf_ave_0 ? *cf_ave_1 : *cf_ave_0);
+   weight = 1.0 - weight;
+   return weight * *cf_ave_1 > cf_tol;
+}
+
 // true when v is an Inf or a NaN (the reference's ieee_check: v / v != v / v, gmres.c:378-404)
 static inline bool kry_not_finite(double v) { return v != 0.0 && !(v / v == v / v); }
 
@@ -53,6 +65,8 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
 #define HH(a, bb) hh[(size_t)(a) * k_dim + (bb)]
    double d2[2] = {0.0, 0.0};
    double b_norm, r_norm, den_norm, epsilon, t, gamma, real_r_norm_old, real_r_norm_new;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
+   bool break_value = false;
    int i = 0, j, k, iter = 0;
    const double *z = nullptr;
    memset(res, 0, sizeof(*res));
@@ -69,6 +83,7 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
    if (kry_not_finite(b_norm)) { res->error_flag = 1; return B200_OK; }
    r_norm = sqrt(d2[1]);
    if (kry_not_finite(r_norm)) { res->error_flag = 1; return B200_OK; }
+   r_norm_0 = r_norm;
    if (norms_h) { norms_h[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = prm->a_tol > prm->tol * den_norm ? prm->a_tol : prm->tol * den_norm;
@@ -124,9 +139,11 @@ int gmres_core(B &ops, const b200_gmres_params *prm, const double *b, double *x,
          HH(i - 1, i - 1) = s[i - 1] * HH(i, i - 1) + c[i - 1] * HH(i - 1, i - 1);
          r_norm = fabs(rs[i]);
          if (norms_h) { norms_h[iter] = r_norm; }
+         if (prm->cf_tol > 0.0 && kry_cf_exceeded(prm->cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break_value = true; break; }
          if (r_norm <= epsilon && iter >= min_iter) { break; }
       }
 
+      if (break_value) { break; }      // cf_tol: leave without the update of this cycle (:732-735)
       // upper triangular solve, x += C (sum_j rs[j] p[j])   (:735-762)
       rs[i - 1] = rs[i - 1] / HH(i - 1, i - 1);
       for (k = i - 2; k >= 0; k--)
@@ -200,6 +217,7 @@ int bicgstab_core(B &ops, const b200_bicgstab_params *prm, const double *b, doub
    const double epsmac = DBL_MIN;    // HYPRE_REAL_MIN
    double d2[2] = {0.0, 0.0};
    double alpha, beta, gamma, epsilon, temp, rres, r_norm, b_norm, den_norm;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
    int iter = 0;
    const double *z = nullptr;
    memset(res, 0, sizeof(*res));
@@ -218,9 +236,11 @@ int bicgstab_core(B &ops, const b200_bicgstab_params *prm, const double *b, doub
    rres = d2[1];
    r_norm = sqrt(rres);
    if (kry_not_finite(r_norm)) { res->error_flag = 1; return B200_OK; }
+   r_norm_0 = r_norm;
    if (norms_h) { norms_h[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = prm->a_tol > prm->tol * den_norm ? prm->a_tol : prm->tol * den_norm;
+   if (prm->stop_crit) { epsilon = prm->a_tol == 0.0 ? prm->tol : prm->a_tol; }      // bicgstab.c:372-383
    if (b_norm > 0.0) { res->rel_residual_norm = r_norm / b_norm; }
    if (r_norm == 0.0) { return B200_OK; }                                             // :403-408
    if (r_norm <= epsilon && iter >= min_iter) { res->converged = 1; res->real_residual_exit = 1; return B200_OK; }  // :409-419
@@ -258,6 +278,7 @@ int bicgstab_core(B &ops, const b200_bicgstab_params *prm, const double *b, doub
          r_norm = sqrt(d2[0]);
          if (r_norm <= epsilon) { res->converged = 1; res->real_residual_exit = 1; break; }
       }
+      if (prm->cf_tol > 0.0 && kry_cf_exceeded(prm->cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break; }
       if (fabs(rres) >= epsmac) { beta = 1.0 / rres; }
       else { res->error_flag |= 2; return B200_OK; }
       rres = d2[1];
@@ -288,6 +309,8 @@ int lgmres_core(B &ops, const b200_lgmres_params *prm, const double *b, double *
 #define HH(a, bb) hh[(size_t)(a) * (kd + 1) + (bb)]
    double d2[2] = {0.0, 0.0};
    double b_norm, r_norm, r_norm_last = 0.0, den_norm, epsilon, t, gamma, tmp_norm;
+   double r_norm_0, cf_ave_0 = 0.0, cf_ave_1 = 0.0;
+   bool break_value = false;
    int i = 0, j, k, ii, iter = 0, aug_ct = 0, it_arnoldi, it_total, it_aug, order, spot = 0;
    const double *z = nullptr;
    memset(res, 0, sizeof(*res));
@@ -302,6 +325,7 @@ int lgmres_core(B &ops, const b200_lgmres_params *prm, const double *b, double *
    if (kry_not_finite(b_norm)) { res->error_flag = 1; return B200_OK; }
    r_norm = sqrt(d2[1]);
    if (kry_not_finite(r_norm)) { res->error_flag = 1; return B200_OK; }
+   r_norm_0 = r_norm;
    if (norms_h) { norms_h[0] = r_norm; }
    den_norm = b_norm > 0.0 ? b_norm : r_norm;
    epsilon = prm->a_tol > prm->tol * den_norm ? prm->a_tol : prm->tol * den_norm;
@@ -365,8 +389,10 @@ int lgmres_core(B &ops, const b200_lgmres_params *prm, const double *b, double *
          HH(i - 1, i - 1) = s[i - 1] * HH(i, i - 1) + c[i - 1] * HH(i - 1, i - 1);
          r_norm = fabs(rs[i]);
          if (norms_h) { norms_h[iter] = r_norm; }
+         if (prm->cf_tol > 0.0 && kry_cf_exceeded(prm->cf_tol, r_norm, r_norm_0, iter, &cf_ave_0, &cf_ave_1)) { break_value = true; break; }
          if (r_norm <= epsilon && iter >= min_iter) { break; }
       }
+      if (break_value) { break; }
       rs[i - 1] = rs[i - 1] / HH(i - 1, i - 1);
       for (k = i - 2; k >= 0; k--)
       {

@@ -886,9 +886,9 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(gmres_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(gmres_vdata, A, b, x); }
 
-   if (g->rel_change || g->cf_tol > 0.0 || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   if (g->rel_change || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("GMRES option outside the device path (rel_change / cf_tol / stop_crit / hybrid / multivector)");
+      GLUE_FAIL("GMRES option outside the device path (rel_change / stop_crit / hybrid / multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -897,6 +897,7 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    memset(&prm, 0, sizeof(prm));
    prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
    prm.k_dim = g->k_dim; prm.skip_real_r_check = g->skip_real_r_check; prm.diag_scale = diag_scale;
+   prm.cf_tol = g->cf_tol;
    g->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
    /* norms exists when logging or print_level is set (hypre_GMRESSetup, gmres.c:246-256).  The reference
@@ -960,9 +961,9 @@ HYPRE_Int hypre_COGMRESSolve(void *cogmres_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(cogmres_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(cogmres_vdata, A, b, x); }
 
-   if (g->rel_change || g->cf_tol > 0.0 || g->cgs > 1 || hypre_ParVectorNumVectors(pb) > 1)
+   if (g->rel_change || g->cgs > 1 || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("COGMRES option outside the device path (rel_change / cf_tol / cgs 2 / multivector)");
+      GLUE_FAIL("COGMRES option outside the device path (rel_change / cgs 2 / multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -971,7 +972,7 @@ HYPRE_Int hypre_COGMRESSolve(void *cogmres_vdata, void *A, void *b, void *x)
    memset(&prm, 0, sizeof(prm));
    prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
    prm.k_dim = g->k_dim; prm.skip_real_r_check = g->skip_real_r_check; prm.diag_scale = diag_scale;
-   prm.ortho = 1;
+   prm.ortho = 1; prm.cf_tol = g->cf_tol;
    g->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
@@ -1033,10 +1034,10 @@ HYPRE_Int hypre_FlexGMRESSolve(void *fgmres_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(fgmres_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(fgmres_vdata, A, b, x); }
 
-   if (g->cf_tol > 0.0 || hypre_ParVectorNumVectors(pb) > 1 ||
+   if (hypre_ParVectorNumVectors(pb) > 1 ||
        (fn->modify_pc != NULL && fn->modify_pc != hypre_FlexGMRESModifyPCDefault))
    {
-      GLUE_FAIL("FlexGMRES option outside the device path (cf_tol / multivector / a modify_pc callback)");
+      GLUE_FAIL("FlexGMRES option outside the device path (multivector / a modify_pc callback)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -1044,7 +1045,7 @@ HYPRE_Int hypre_FlexGMRESSolve(void *fgmres_vdata, void *A, void *b, void *x)
 
    memset(&prm, 0, sizeof(prm));
    prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
-   prm.k_dim = g->k_dim; prm.diag_scale = diag_scale; prm.flex = 1;
+   prm.k_dim = g->k_dim; prm.diag_scale = diag_scale; prm.flex = 1; prm.cf_tol = g->cf_tol;
    g->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
@@ -1105,9 +1106,9 @@ HYPRE_Int hypre_LGMRESSolve(void *lgmres_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(lgmres_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(lgmres_vdata, A, b, x); }
 
-   if (g->cf_tol > 0.0 || g->k_dim <= g->aug_dim || hypre_ParVectorNumVectors(pb) > 1)
+   if (g->k_dim <= g->aug_dim || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("LGMRES option outside the device path (cf_tol / aug_dim >= k_dim / multivector)");
+      GLUE_FAIL("LGMRES option outside the device path (aug_dim >= k_dim / multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -1116,6 +1117,7 @@ HYPRE_Int hypre_LGMRESSolve(void *lgmres_vdata, void *A, void *b, void *x)
    memset(&prm, 0, sizeof(prm));
    prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
    prm.k_dim = g->k_dim; prm.aug_dim = g->aug_dim; prm.approx_constant = g->approx_constant; prm.diag_scale = diag_scale;
+   prm.cf_tol = g->cf_tol;
    g->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;
@@ -1174,9 +1176,9 @@ HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(bicgstab_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(bicgstab_vdata, A, b, x); }
 
-   if (g->cf_tol > 0.0 || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   if (g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("BiCGSTAB option outside the device path (cf_tol / stop_crit / hybrid / multivector)");
+      GLUE_FAIL("BiCGSTAB option outside the device path (hybrid / multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -1184,7 +1186,7 @@ HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
 
    memset(&prm, 0, sizeof(prm));
    prm.tol = g->tol; prm.a_tol = g->a_tol; prm.max_iter = g->max_iter; prm.min_iter = g->min_iter;
-   prm.diag_scale = diag_scale;
+   prm.diag_scale = diag_scale; prm.stop_crit = g->stop_crit ? 1 : 0; prm.cf_tol = g->cf_tol;
    g->converged = 0;
    (*(fn->CommInfo))(A, &my_id, &num_procs);
    norms = ((g->logging > 0 || g->print_level > 0) && g->norms) ? g->norms : NULL;

@@ -295,7 +295,7 @@ int b200_pcg_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200
  * (src/krylov/bicgstab.c:226-640; ij -solver 9 / 10) with the ParCSR operator table
  * (src/parcsr_ls/par_krylov_func.c:14-330): right preconditioning by one b200_amg_cycle (amg != NULL),
  * diagonal scaling (diag_scale, HYPRE_ParCSRDiagScale) or nothing.  Options the reference switches off by
- * default are not implemented and must be off: rel_change, cf_tol, stop_crit, hybrid.  b, x dev pointers;
+ * default and that are not implemented must be off: rel_change, hybrid (GMRES: stop_crit).  b, x dev pointers;
  * norms_h (HOST, max_iter + 1 entries, may be NULL) receives the residual norms the reference logs
  * (gmres.c:413, 610; bicgstab.c:353, 489). */
 typedef struct {
@@ -314,6 +314,8 @@ typedef struct {
                               * with the default (empty) modify_pc: the preconditioned basis vectors are kept and
                               * the solution is updated from them without a further preconditioner application;
                               * true-residual check without the "residual no longer decreases" exit */
+   double cf_tol;            /* > 0: abandon the solve when the weighted average convergence factor exceeds it
+                              * (HYPRE_GMRESSetConvergenceFactorTol, gmres.c:632-652, 732-735); 0 = off */
 } b200_gmres_params;
 
 typedef struct {
@@ -322,6 +324,8 @@ typedef struct {
    int    max_iter;
    int    min_iter;
    int    diag_scale;
+   int    stop_crit;         /* 1: |r| <= tol (a_tol when set) as an absolute bound, bicgstab.c:372-383 */
+   double cf_tol;            /* as b200_gmres_params (bicgstab.c:519-540) */
 } b200_bicgstab_params;
 
 /* hypre_LGMRESSolve (src/krylov/lgmres.c:337-...; ij -solver 51 / 50): GMRES(k_dim) augmented with the last
@@ -336,6 +340,7 @@ typedef struct {
    int    aug_dim;
    int    approx_constant;
    int    diag_scale;
+   double cf_tol;            /* as b200_gmres_params (lgmres.c) */
 } b200_lgmres_params;
 
 typedef struct {

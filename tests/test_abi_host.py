@@ -174,10 +174,13 @@ def test_gmres_bicgstab_have_no_cpu_fallback_and_reject_unsupported_options(H, k
         s.SetRelChange(1)
     elif kind == "cogmres":
         s.SetCGS(2)
-    elif kind in ("flexgmres", "lgmres"):
-        s.SetConvergenceFactorTol(0.5)
+    elif kind == "lgmres":
+        s.SetKDim(2)                      # aug_dim (2) >= k_dim
+    elif kind == "flexgmres":
+        cb = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_double)(lambda data, it, rel: 0)
+        H.lib().HYPRE_FlexGMRESSetModifyPC(s.h, cb)      # a callback that could retune the preconditioner
     else:
-        s.SetStopCrit(1)
+        pass                              # BiCGSTAB: stop_crit and cf_tol are implemented; nothing left to reject here
     s.Solve(A, b, x)
     assert H.error_flag() & 1 and not np.any(x.numpy())
     H.clear_errors()

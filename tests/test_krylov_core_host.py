@@ -54,7 +54,8 @@ def _one_level(Ad):
     return O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
 
 
-def run_core(kht, kind, Ad, orc, precond, b, x0, tol=1e-8, a_tol=0.0, k_dim=5, min_iter=0, max_iter=100, skip=0):
+def run_core(kht, kind, Ad, orc, precond, b, x0, tol=1e-8, a_tol=0.0, k_dim=5, min_iter=0, max_iter=100, skip=0, cf_tol=0.0,
+             stop_crit=0):
     ia, ja, aa = O.csr_arrays(Ad)
     x = np.array(x0, dtype=np.float64, copy=True)
     norms = np.zeros(max_iter + 1)
@@ -63,15 +64,15 @@ def run_core(kht, kind, Ad, orc, precond, b, x0, tol=1e-8, a_tol=0.0, k_dim=5, m
     h = orc.h if orc is not None else None
     if kind in ("gmres", "cogmres", "flexgmres"):
         prm = GmresParams(tol, a_tol, max_iter, min_iter, k_dim, skip, 1 if precond == 1 else 0, 1 if kind == "cogmres" else 0,
-                          1 if kind == "flexgmres" else 0)
+                          1 if kind == "flexgmres" else 0, cf_tol)
         st = kht.kht_gmres(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
                            C.byref(res), O.p(norms))
     elif kind == "lgmres":
-        prm = LgmresParams(tol, a_tol, max_iter, min_iter, k_dim, 2, 1, 1 if precond == 1 else 0)
+        prm = LgmresParams(tol, a_tol, max_iter, min_iter, k_dim, 2, 1, 1 if precond == 1 else 0, cf_tol)
         st = kht.kht_lgmres(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
                             C.byref(res), O.p(norms))
     else:
-        prm = BicgstabParams(tol, a_tol, max_iter, min_iter, 1 if precond == 1 else 0)
+        prm = BicgstabParams(tol, a_tol, max_iter, min_iter, 1 if precond == 1 else 0, stop_crit, cf_tol)
         st = kht.kht_bicgstab(Ad.shape[0], O.p(ia), O.p(ja), O.p(aa), h, precond, C.byref(prm), O.p(b), O.p(x),
                               C.byref(res), O.p(norms))
     assert st == 0
@@ -84,7 +85,8 @@ def check_against_oracle(kht, kind, Ad, orc, precond, b, x0, **kw):
                max_iter=kw.get("max_iter", 100))
     if kind in ("gmres", "cogmres", "flexgmres", "lgmres"):
         okw.update(k_dim=kw.get("k_dim", 5), skip_real_r_check=kw.get("skip", 0))
-    xo, it, no, rel, conv = getattr(orc, kind)(b, x0, **okw)
+    with O.krylov_options(cf_tol=kw.get("cf_tol", 0.0), stop_crit=kw.get("stop_crit", 0)):
+        xo, it, no, rel, conv = getattr(orc, kind)(b, x0, **okw)
     assert res.num_iterations == it and res.converged == conv
     np.testing.assert_allclose(norms[:it + 1], no, rtol=1e-12)
     np.testing.assert_allclose(res.rel_residual_norm, rel, rtol=1e-12)
@@ -212,3 +214,21 @@ def test_krylov_loops_on_row_partitioned_ranks_over_gloo(kht, nranks):
            "--master-addr", "127.0.0.1", "--master-port", str(29550 + nranks), os.path.join(ROOT, "tests", "dist_krylov_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0 and "DIST_KRYLOV_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("kind", ["gmres", "cogmres", "flexgmres", "lgmres", "bicgstab"])
+def test_core_convergence_factor_tolerance_and_stop_crit(kht, ref_off, kind):
+    """cf_tol abandons a slowly converging solve (GMRES-type loops leave without the update of the running cycle);
+    BiCGSTAB's stop_crit makes tol an absolute bound"""
+    A = ref_off.laplacian(9, 8, 7)
+    Ad, _ = A.blocks()
+    orc = _one_level(Ad)
+    n = Ad.shape[0]
+    for cf in (0.7, 0.95):
+        res = check_against_oracle(kht, kind, Ad, orc, 1, np.ones(n), np.zeros(n), k_dim=6, max_iter=300, cf_tol=cf)
+        if cf == 0.7:
+            assert res.converged == 0 and res.num_iterations < 20 and res.error_flag == 0
+    if kind == "bicgstab":
+        res = check_against_oracle(kht, kind, Ad, orc, 1, np.ones(n), np.zeros(n), tol=1e-3, max_iter=300, stop_crit=1)
+        assert res.converged == 1
+    orc.destroy()
