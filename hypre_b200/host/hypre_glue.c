@@ -886,9 +886,11 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(gmres_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(gmres_vdata, A, b, x); }
 
-   if (g->rel_change || g->stop_crit || g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   /* hybrid == -1 (set by HYPRE_ParCSRHybrid on its inner solver, parcsr_ls/amg_hybrid.c:1968, 2029; krylov/gmres.c:908) only
+    * silences HYPRE_ERROR_CONV at the end */
+   if (g->rel_change || g->stop_crit || (g->hybrid != 0 && g->hybrid != -1) || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("GMRES option outside the device path (rel_change / stop_crit / hybrid / multivector)");
+      GLUE_FAIL("GMRES option outside the device path (rel_change / stop_crit / multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -936,7 +938,7 @@ HYPRE_Int hypre_GMRESSolve(void *gmres_vdata, void *A, void *b, void *x)
    g->num_iterations = res.num_iterations;
    g->rel_residual_norm = res.rel_residual_norm;
    hypre_ParVectorAllZeros(px) = 0;
-   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   if ((res.error_flag & 256) && g->hybrid != -1) { hypre_error(HYPRE_ERROR_CONV); }
    return hypre_error_flag;
 }
 
@@ -1176,9 +1178,9 @@ HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
    if (!g_enabled) { return next(bicgstab_vdata, A, b, x); }
    if (fn->Matvec != hypre_ParKrylovMatvec) { return next(bicgstab_vdata, A, b, x); }
 
-   if (g->hybrid || hypre_ParVectorNumVectors(pb) > 1)
+   if ((g->hybrid != 0 && g->hybrid != -1) || hypre_ParVectorNumVectors(pb) > 1)
    {
-      GLUE_FAIL("BiCGSTAB option outside the device path (hybrid / multivector)");
+      GLUE_FAIL("BiCGSTAB option outside the device path (multivector)");
       return hypre_error_flag;
    }
    m = krylov_precond_mirror((HYPRE_Int (*)(void *, void *, void *, void *)) fn->precond, g->precond_data, pA, &amg, &diag_scale);
@@ -1224,7 +1226,7 @@ HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
    if (res.b_norm > 0.0 || res.num_iterations > 0 || (res.error_flag & 256)) { g->rel_residual_norm = res.rel_residual_norm; }
    hypre_ParVectorAllZeros(px) = 0;
    if (res.error_flag & 2) { hypre_error_w_msg(HYPRE_ERROR_GENERIC, "BiCGSTAB broke down!! divide by near zero\n"); }
-   if (res.error_flag & 256) { hypre_error(HYPRE_ERROR_CONV); }
+   if ((res.error_flag & 256) && g->hybrid != -1) { hypre_error(HYPRE_ERROR_CONV); }
    return hypre_error_flag;
 }
 
