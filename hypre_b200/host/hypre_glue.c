@@ -579,6 +579,16 @@ HYPRE_Int hypre_BoomerAMGDestroy(void *amg_vdata)
    return next(amg_vdata);
 }
 
+/* a vector that goes away takes its device binding with it (its address may be handed out again) */
+HYPRE_Int hypre_ParVectorDestroy(hypre_ParVector *v)
+{
+   typedef HYPRE_Int (*vec_destroy_fn)(hypre_ParVector *);
+   static vec_destroy_fn next = NULL;
+   if (!next) { next = (vec_destroy_fn) next_sym("hypre_ParVectorDestroy"); }
+   if (v && g_devvecs) { hypre_b200_vector_bind_device(v, NULL); }
+   return next(v);
+}
+
 HYPRE_Int hypre_ParCSRMatrixDestroy(hypre_ParCSRMatrix *A)
 {
    static mat_destroy_fn next = NULL;

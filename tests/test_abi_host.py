@@ -255,3 +255,17 @@ def test_cycle_exchange_counts():
         for l in range(4):
             assert a[l] == sw[l] - entered[l] + r[l], (ct, fc, l, a, sw, r)
         assert a[4] == 0
+
+
+def test_device_binding_goes_away_with_the_vector(H):
+    """hypre_ParVectorDestroy is interposed: a destroyed vector loses its device binding (its address may be reused)"""
+    A = H.laplacian(5, 5, 5)
+    v = A.vector(1.0)
+    handle = v.h.value
+    v.bind_device(C.c_void_p(0x3000))
+    assert v.bound_device() == 0x3000
+    v.destroy()
+    L = H.lib()
+    L.hypre_b200_vector_device.argtypes = [C.c_void_p]
+    L.hypre_b200_vector_device.restype = C.c_void_p
+    assert L.hypre_b200_vector_device(C.c_void_p(handle)) is None

@@ -240,17 +240,20 @@ def test_device_bound_vectors_solve_in_place(H, ctx, kind):
     n = x.size
     db, dx = capi.DeviceVector(ctx, n, b.numpy()), capi.DeviceVector(ctx, n, np.zeros(n))
     x.numpy()[:] = -7.0                            # sentinel: the host array must not be written by the solve
-    b.bind_device(db.ptr)
-    H.clear_errors()
-    s.Solve(A, b, x)                               # half-bound: rejected
-    assert H.error_flag() & 1
-    H.clear_errors()
-    x.bind_device(dx.ptr)
-    s.Solve(A, b, x)
-    assert H.error_flag() == 0 and s.num_iterations == it_host
-    assert np.all(x.numpy() == -7.0)
-    np.testing.assert_array_equal(dx.get(), x_host)          # same device code on the same data
-    assert x.sync_to_host() == 0
-    np.testing.assert_array_equal(x.numpy(), x_host)
-    b.bind_device(None); x.bind_device(None)
-    db.free(); dx.free()
+    try:
+        b.bind_device(db.ptr)
+        H.clear_errors()
+        s.Solve(A, b, x)                           # half-bound: rejected
+        assert H.error_flag() & 1
+        H.clear_errors()
+        x.bind_device(dx.ptr)
+        s.Solve(A, b, x)
+        assert H.error_flag() == 0 and s.num_iterations == it_host
+        assert np.all(x.numpy() == -7.0)
+        np.testing.assert_array_equal(dx.get(), x_host)      # same device code on the same data
+        assert x.sync_to_host() == 0
+        np.testing.assert_array_equal(x.numpy(), x_host)
+    finally:
+        H.clear_errors()
+        b.bind_device(None); x.bind_device(None)
+        db.free(); dx.free()
