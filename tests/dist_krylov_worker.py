@@ -1,4 +1,4 @@
-"""gloo worker (world_size >= 2, CPU): the GMRES / COGMRES / FlexGMRES / BiCGSTAB loops of
+"""gloo worker (world_size >= 2, CPU): the GMRES / COGMRES / FlexGMRES / LGMRES / BiCGSTAB loops of
 hypre_b200/csrc/krylov_core.hpp on a row-partitioned problem.  Every rank partitions the same global matrix with
 b200_rowpart; the operator is the halo exchange of tests/dist_worker.py (torch.distributed point-to-point
 messages following the plan) plus the local diag/offd products, inner products are summed with
@@ -44,6 +44,7 @@ def main():
     vp, i = C.c_void_p, C.c_int
     L.kht_gmres_dist.argtypes = [i, vp, MV, AR, vp, vp, vp, vp, vp]
     L.kht_bicgstab_dist.argtypes = [i, vp, MV, AR, vp, vp, vp, vp, vp]
+    L.kht_lgmres_dist.argtypes = [i, vp, MV, AR, vp, vp, vp, vp, vp]
     A = lap7(9, 7, 2 * world + 2)
     n = A.shape[0]
     rs = capi.even_starts(n, world)
@@ -75,7 +76,7 @@ def main():
     b = np.ascontiguousarray(bg[rs[rank]:rs[rank + 1]])
     orc = O.OracleAMG.from_arrays([dict(A=diag_first(A), P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None) if rank == 0 else None
     ok = True
-    for kind, k_dim, precond in (("gmres", 5, 1), ("gmres", 4, 2), ("cogmres", 6, 1), ("flexgmres", 5, 1), ("bicgstab", 0, 1),
+    for kind, k_dim, precond in (("gmres", 5, 1), ("gmres", 4, 2), ("cogmres", 6, 1), ("flexgmres", 5, 1), ("lgmres", 6, 1), ("bicgstab", 0, 1),
                                  ("bicgstab", 0, 2)):
         x = np.zeros(nl)
         norms = np.zeros(501)
@@ -84,6 +85,9 @@ def main():
         if kind == "bicgstab":
             prm = capi.BicgstabParams(1e-8, 0.0, 500, 0, 1 if precond == 1 else 0)
             st = L.kht_bicgstab_dist(nl, dptr, mv_cb, ar_cb, C.byref(prm), capi.ptr(b), capi.ptr(x), C.byref(res), capi.ptr(norms))
+        elif kind == "lgmres":
+            prm = capi.LgmresParams(1e-8, 0.0, 500, 0, k_dim, 2, 1, 1 if precond == 1 else 0)
+            st = L.kht_lgmres_dist(nl, dptr, mv_cb, ar_cb, C.byref(prm), capi.ptr(b), capi.ptr(x), C.byref(res), capi.ptr(norms))
         else:
             prm = capi.GmresParams(1e-8, 0.0, 500, 0, k_dim, 0, 1 if precond == 1 else 0, 1 if kind == "cogmres" else 0,
                                    1 if kind == "flexgmres" else 0)

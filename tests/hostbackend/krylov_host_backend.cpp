@@ -214,3 +214,16 @@ extern "C" int kht_lgmres(int n, const int *ia, const int *ja, const double *a, 
    double *const *aav = av + prm->aug_dim + 1;
    return lgmres_core(ops, prm, b, x, p, av, aav, vec[nv - 2], vec[nv - 1], res, norms);
 }
+
+extern "C" int kht_lgmres_dist(int n_local, const double *diag, kht_matvec_cb mv, kht_allreduce_cb ar,
+                               const b200_lgmres_params *prm, const double *b, double *x, b200_krylov_result *res,
+                               double *norms)
+{
+   CbKrylovOps ops{n_local, diag, mv, ar};
+   const int nv = prm->k_dim + 1 + (prm->aug_dim + 1) + prm->aug_dim + 2;
+   std::vector<std::vector<double>> store(nv, std::vector<double>((size_t)(n_local > 0 ? n_local : 1), 0.0));
+   std::vector<double *> vec;
+   for (auto &v : store) { vec.push_back(v.data()); }
+   double *const *av = vec.data() + prm->k_dim + 1;
+   return lgmres_core(ops, prm, b, x, vec.data(), av, av + prm->aug_dim + 1, vec[nv - 2], vec[nv - 1], res, norms);
+}
