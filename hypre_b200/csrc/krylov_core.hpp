@@ -1,11 +1,17 @@
-// krylov_core.hpp -- the scalar logic of restarted GMRES and of BiCGSTAB over a vector backend.
+// krylov_core.hpp -- the scalar logic of the restarted-GMRES family and of BiCGSTAB over a vector backend.
 //
-// hypre_GMRESSolve (src/krylov/gmres.c:274-930) and hypre_BiCGSTABSolve (src/krylov/bicgstab.c:226-640)
-// are, like hypre_PCGSolve, host loops over an operator table (hypre_GMRESFunctions, gmres.h:64-90).
-// Here the loops are templates over a backend `B` whose methods are the (fused) vector operations;
-// libb200amg instantiates them with the device backend of krylov.cu only.  The header has no CUDA in
-// it, so the CPU tests can instantiate the very same loops over a host backend (tests/krylov_host_backend.cpp,
-// test infrastructure) and compare every iterate with the oracle without a GPU.
+//   gmres_core     hypre_GMRESSolve      src/krylov/gmres.c:274-930       (ortho = 0, flex = 0)
+//                  hypre_COGMRESSolve    src/krylov/cogmres.c, cgs == 1   (ortho = 1)
+//                  hypre_FlexGMRESSolve  src/krylov/flexgmres.c           (flex = 1, default modify_pc)
+//   lgmres_core    hypre_LGMRESSolve     src/krylov/lgmres.c
+//   bicgstab_core  hypre_BiCGSTABSolve   src/krylov/bicgstab.c:226-640
+//
+// In the reference these are, like hypre_PCGSolve, host loops over an operator table (hypre_GMRESFunctions,
+// gmres.h:64-90).  Here the loops are templates over a backend `B` whose methods are the (fused) vector
+// operations; libb200amg instantiates them with the device backend of krylov.cu only.  The header has no CUDA
+// in it, so the CPU tests can instantiate the very same loops over a host backend
+// (tests/hostbackend/krylov_host_backend.cpp, test infrastructure) and compare every iterate with the oracle
+// without a GPU.
 //
 // Backend concept (all vectors are `double *` handles of length ops.n owned by the caller; every method
 // returns B200_OK or a negative error code which the loops pass straight up):
