@@ -301,3 +301,32 @@ def test_device_cgnr_matches_oracle_and_reference(H, ctx, diag):
         H.set_device_path(True)
         assert abs(out[True][0] - out[False][0]) <= 2
         np.testing.assert_allclose(out[True][1], out[False][1], rtol=1e-5, atol=1e-8)
+
+
+@pytest.mark.parametrize("name", ["lap7_24_rlx16_var1", "lap7_24_rlx16_o4", "lap7_24_rlx16_o3_noscale", "lap7_24_rlx18_pc3",
+                                  "lap7_24_rlx16_pc2", "lap7_24_rlx0_w08", "lap27_20_rlx0_w07_ns2"])
+def test_pcg_option_cases_match_oracle_and_reference(H, ctx, name):
+    """AMG-PCG with the options added after the last GPU run of round 1 -- Chebyshev variant 1 / orders 3, 4 /
+    unscaled, several cycles per preconditioner application, weighted point Jacobi (relax 0) -- device vs oracle vs
+    the reference's hypre_PCGSolve in-process (the form of test_gpu_solve.py's cycle-variant test; kept in this
+    file so that a first-run failure cannot disturb the verified tests)"""
+    H.set_device_path(True)
+    A, b, x, amg, pcg = O.build_case(H, name)
+    out = {}
+    try:
+        for dev in (True, False):
+            H.set_device_path(dev)
+            x.numpy()[:] = 0.0
+            H.clear_errors()
+            pcg.Solve(A, b, x)
+            assert H.error_flag() == 0
+            out[dev] = (pcg.num_iterations, pcg.rel_norms(), x.numpy().copy())
+    finally:
+        H.set_device_path(True)
+    orc = O.OracleAMG(amg)
+    xo, ito, relo, conv = orc.pcg(b.numpy(), np.zeros(A.global_rows))
+    orc.destroy()
+    assert out[True][0] == out[False][0] == ito
+    np.testing.assert_allclose(out[True][1], out[False][1], rtol=1e-9)
+    np.testing.assert_allclose(out[True][1], relo, rtol=1e-9)
+    assert float(np.max(np.abs(out[True][2] - out[False][2])) / np.max(np.abs(out[False][2]))) < 1e-8
