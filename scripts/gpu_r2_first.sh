@@ -12,5 +12,10 @@ python bench.py > gpurun_out/r2_bench1_256.log 2>&1; tail -n 1 gpurun_out/r2_ben
 python scripts/bench_krylov.py --n 128 > gpurun_out/r2_bench_krylov_128.jsonl 2>&1; cat gpurun_out/r2_bench_krylov_128.jsonl | cut -c 1-400
 python scripts/bench_krylov.py --n 256 --steps 2 > gpurun_out/r2_bench_krylov_256.jsonl 2>&1; cat gpurun_out/r2_bench_krylov_256.jsonl | cut -c 1-400
 B200_SELLC_PIPE=5 python bench.py --no-cpu-baseline --no-aux > gpurun_out/r2_bench1_256_pipe5.log 2>&1; tail -n 1 gpurun_out/r2_bench1_256_pipe5.log | cut -c 1-400
+# launch list of the Krylov solvers (shares of the Gram-Schmidt / update kernels per solve), only after the same
+# command has exited 0 without ncu
+python scripts/bench_krylov.py --n 128 --steps 1 --warmup 1 > gpurun_out/r2_krylov_plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/r2_launches_krylov.csv python scripts/bench_krylov.py --n 128 --steps 1 --warmup 1 > gpurun_out/r2_ncu_krylov.log 2>&1
+tail -n 1 gpurun_out/r2_ncu_krylov.log | cut -c 1-200
 # with 4 GPUs (gpurun --gpus 4): the reference's own regression jobs on the binding, N ranks = N GPUs
 #   python scripts/run_saved_jobs_b200.py > gpurun_out/r2_saved_jobs_b200.json
