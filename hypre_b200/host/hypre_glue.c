@@ -239,7 +239,7 @@ static int krylov_operands(hypre_ParVector *pb, hypre_ParVector *px, double **db
    *db = devvec_find(pb); *dx = devvec_find(px);
    if ((*db == NULL) != (*dx == NULL))
    {
-      GLUE_FAIL("right-hand side and solution must both be bound to device arrays (hypre_b200_vector_bind_device) or both live on the host");
+      GLUE_FAIL("both vector operands must be bound to device arrays (hypre_b200_vector_bind_device) or both live on the host");
       return -1;
    }
    return 0;
@@ -1533,11 +1533,16 @@ HYPRE_Int HYPRE_ParCSRMatrixMatvec(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, HY
    }
    m = mirror_for_matrix(pA);
    if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
-   if (b200_parcsr_matvec_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_col, beta,
-                               hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row,
-                               hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row) != B200_OK)
    {
-      GLUE_FAIL("device SpMV failed");
+      /* device-bound operands (hypre_b200_vector_bind_device): the product runs on them in place */
+      double *dx, *dy;
+      int st;
+      if (krylov_operands(px, py, &dx, &dy) != 0) { return hypre_error_flag; }
+      st = dx ? b200_parcsr_matvec(m->A, alpha, dx, beta, dy, dy)
+              : b200_parcsr_matvec_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_col, beta,
+                                        hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row,
+                                        hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_row);
+      if (st != B200_OK) { GLUE_FAIL("device SpMV failed"); }
    }
    hypre_ParVectorAllZeros(py) = 0;
    return hypre_error_flag;
@@ -1567,10 +1572,14 @@ HYPRE_Int HYPRE_ParCSRMatrixMatvecT(HYPRE_Complex alpha, HYPRE_ParCSRMatrix A, H
    }
    m = mirror_for_matrix(pA);
    if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
-   if (b200_parcsr_matvecT_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, beta,
-                                hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_col) != B200_OK)
    {
-      GLUE_FAIL("device SpMV^T failed");
+      double *dx, *dy;
+      int st;
+      if (krylov_operands(px, py, &dx, &dy) != 0) { return hypre_error_flag; }
+      st = dx ? b200_parcsr_matvecT(m->A, alpha, dx, beta, dy)
+              : b200_parcsr_matvecT_host(m->A, alpha, hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, beta,
+                                         hypre_VectorData(hypre_ParVectorLocalVector(py)) + m->first_col);
+      if (st != B200_OK) { GLUE_FAIL("device SpMV^T failed"); }
    }
    hypre_ParVectorAllZeros(py) = 0;
    return hypre_error_flag;

@@ -330,3 +330,35 @@ def test_pcg_option_cases_match_oracle_and_reference(H, ctx, name):
     np.testing.assert_allclose(out[True][1], out[False][1], rtol=1e-9)
     np.testing.assert_allclose(out[True][1], relo, rtol=1e-9)
     assert float(np.max(np.abs(out[True][2] - out[False][2])) / np.max(np.abs(out[False][2]))) < 1e-8
+
+
+def test_device_bound_vectors_spmv_in_place(H, ctx):
+    """HYPRE_ParCSRMatrixMatvec / MatvecT on vectors bound to device arrays (the SpMV microbench of BASELINE.json
+    configs[1] with device-resident operands): same values as the host-vector call, host arrays untouched"""
+    H.set_device_path(True)
+    A = H.laplacian_27pt(14, 13, 12)
+    n = A.global_rows
+    x = A.vector(0.0, cols=True); y = A.vector(0.0)
+    x.numpy()[:] = np.sin(np.arange(n)) * 1e-3 + 1.0
+    y.numpy()[:] = 0.5
+    H.clear_errors()
+    H.lib().HYPRE_ParCSRMatrixMatvec(2.0, A.h, x.h, -1.0, y.h)              # host vectors
+    y_host = y.numpy().copy()
+    H.lib().HYPRE_ParCSRMatrixMatvecT(2.0, A.h, y.h, 0.0, x.h)
+    xT_host = x.numpy().copy()
+    assert H.error_flag() == 0
+    x.numpy()[:] = np.sin(np.arange(n)) * 1e-3 + 1.0
+    dx, dy = capi.DeviceVector(ctx, n, x.numpy()), capi.DeviceVector(ctx, n, np.full(n, 0.5))
+    y.numpy()[:] = -7.0
+    try:
+        x.bind_device(dx.ptr); y.bind_device(dy.ptr)
+        H.lib().HYPRE_ParCSRMatrixMatvec(2.0, A.h, x.h, -1.0, y.h)
+        assert H.error_flag() == 0 and np.all(y.numpy() == -7.0)
+        np.testing.assert_array_equal(dy.get(), y_host)
+        H.lib().HYPRE_ParCSRMatrixMatvecT(2.0, A.h, y.h, 0.0, x.h)
+        assert H.error_flag() == 0
+        np.testing.assert_array_equal(dx.get(), xT_host)
+    finally:
+        H.clear_errors()
+        x.bind_device(None); y.bind_device(None)
+        dx.free(); dy.free()
