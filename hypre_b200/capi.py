@@ -46,10 +46,6 @@ class LgmresParams(C.Structure):
                 ("cf_tol", C.c_double)]
 
 
-class CgnrParams(C.Structure):
-    _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("stop_crit", C.c_int), ("diag_scale", C.c_int)]
-
-
 class KrylovResult(C.Structure):
     _fields_ = [("num_iterations", C.c_int), ("converged", C.c_int), ("error_flag", C.c_int),
                 ("rel_residual_norm", C.c_double), ("b_norm", C.c_double), ("real_residual_exit", C.c_int)]
@@ -145,8 +141,6 @@ def lib():
         "b200_gmres_solve_host": (i, [vp, vp, vp, C.POINTER(GmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_bicgstab_solve": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_bicgstab_solve_host": (i, [vp, vp, vp, C.POINTER(BicgstabParams), vp, vp, C.POINTER(KrylovResult), vp]),
-        "b200_cgnr_solve": (i, [vp, vp, vp, C.POINTER(CgnrParams), vp, vp, C.POINTER(KrylovResult), vp]),
-        "b200_cgnr_solve_host": (i, [vp, vp, vp, C.POINTER(CgnrParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_lgmres_solve": (i, [vp, vp, vp, C.POINTER(LgmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
         "b200_lgmres_solve_host": (i, [vp, vp, vp, C.POINTER(LgmresParams), vp, vp, C.POINTER(KrylovResult), vp]),
     }

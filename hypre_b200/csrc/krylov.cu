@@ -310,24 +310,6 @@ extern "C" int b200_lgmres_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, con
    return krylov_finish(c, status);
 }
 
-extern "C" int b200_cgnr_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_cgnr_params *prm,
-                               const double *b, double *x, b200_krylov_result *res, double *norms_h)
-{
-   ARG_CHECK(c != nullptr && A != nullptr && prm != nullptr && b != nullptr && x != nullptr && res != nullptr);
-   ARG_CHECK(prm->max_iter >= 0);
-   if (amg != nullptr) { b200_set_error("CGNR with BoomerAMG needs the transposed cycle (HYPRE_BoomerAMGSolveT): not implemented"); return B200_ERR_UNSUPPORTED; }
-   if (A->n_rows != A->n_cols_diag) { b200_set_error("CGNR needs a square operator"); return B200_ERR_ARG; }
-   const int n = A->n_rows;
-   std::vector<double *> vec;
-   double *d_sc = nullptr, *h_sc = nullptr;
-   B200_TRY(krylov_workspace(c, n, 4, 4, &vec, &d_sc, &h_sc));
-   B200_TRY(krylov_prepare(c, A, nullptr, prm->diag_scale));
-   DevKrylovOps ops{c, A, nullptr, prm->diag_scale, n, d_sc, h_sc};
-   // p, q, r, t (cgnr.c:150-165)
-   const int status = cgnr_core(ops, prm, b, x, vec[0], vec[1], vec[2], vec[3], res, norms_h);
-   return krylov_finish(c, status);
-}
-
 // host b/x: same staging as b200_pcg_solve_host
 template <class Prm, class Solve>
 static int solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const Prm *prm, const double *b_h, double *x_h,
@@ -362,8 +344,3 @@ extern "C" int b200_lgmres_solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg
    return solve_host(c, A, amg, prm, b_h, x_h, res, norms_h, b200_lgmres_solve);
 }
 
-extern "C" int b200_cgnr_solve_host(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_cgnr_params *prm,
-                                    const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h)
-{
-   return solve_host(c, A, amg, prm, b_h, x_h, res, norms_h, b200_cgnr_solve);
-}

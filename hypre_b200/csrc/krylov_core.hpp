@@ -484,106 +484,3 @@ int lgmres_core(B &ops, const b200_lgmres_params *prm, const double *b, double *
    return B200_OK;
 }
 
-// CGNR (hypre_CGNRSolve, src/krylov/cgnr.c:209-...; ij -solver 6): conjugate gradients on the normal equations of
-// the right-preconditioned system, for a SYMMETRIC preconditioner (diagonal scaling or none: precondT == precond).
-// During the loop x holds the un-preconditioned variable; it is mapped back through C at the end (:385-392).
-// Further backend method: matvecT(alpha, x, beta, y)  y = alpha A^T x + beta y.   p, q, r, t: work vectors.
-// res->error_flag: 1 = Inf/NaN input (the reference returns ierr 101); the reference raises no HYPRE_ERROR_CONV.
-template <class B>
-int cgnr_core(B &ops, const b200_cgnr_params *prm, const double *b, double *x, double *p, double *q, double *r,
-              double *t, b200_krylov_result *res, double *norms_h)
-{
-   const int max_iter = prm->max_iter;
-   double d2[2] = {0.0, 0.0};
-   double alpha, beta, gamma, gamma_old, bi_prod, i_prod, eps, last_norm;
-   int i = 0;
-   bool x_not_set = true;
-   const double *z = nullptr;
-   memset(res, 0, sizeof(*res));
-   {
-      const double *xs[1] = {b};
-      KRY_TRY(ops.dots(1, xs, xs, d2));
-   }
-   bi_prod = d2[0];
-   res->b_norm = sqrt(bi_prod);
-   if (kry_not_finite(bi_prod)) { res->error_flag = 1; return B200_OK; }
-   eps = prm->stop_crit ? prm->tol * prm->tol : (prm->tol * prm->tol) * bi_prod;
-   if (bi_prod == 0.0)
-   {
-      KRY_TRY(ops.copy(b, x));
-      if (norms_h) { norms_h[0] = 0.0; }
-      return B200_OK;
-   }
-   KRY_TRY(ops.matvec(-1.0, x, 1.0, b, r));
-   {
-      const double *xs[1] = {r};
-      KRY_TRY(ops.dots(1, xs, xs, d2));
-   }
-   last_norm = sqrt(d2[0]);
-   if (norms_h) { norms_h[0] = last_norm; }
-   if (kry_not_finite(last_norm)) { res->error_flag = 1; return B200_OK; }
-   KRY_TRY(ops.matvecT(1.0, r, 0.0, q));
-   KRY_TRY(ops.precond(q, t, &z));
-   if (z != t) { KRY_TRY(ops.copy(z, t)); }
-   KRY_TRY(ops.copy(r, p));
-   {
-      const double *xs[1] = {t};
-      KRY_TRY(ops.dots(1, xs, xs, d2));
-   }
-   gamma = d2[0];
-   if (kry_not_finite(gamma)) { res->error_flag = 1; return B200_OK; }
-
-   while ((i + 1) <= max_iter)
-   {
-      i++;
-      KRY_TRY(ops.precond(p, t, &z));
-      KRY_TRY(ops.matvec(1.0, z, 0.0, nullptr, q));
-      {
-         const double *xs[1] = {q};
-         KRY_TRY(ops.dots(1, xs, xs, d2));
-      }
-      alpha = gamma / d2[0];
-      gamma_old = gamma;
-      KRY_TRY(ops.bicg_half(alpha, p, q, x, r));          // x += alpha p ; r -= alpha q
-      KRY_TRY(ops.matvecT(1.0, r, 0.0, q));
-      KRY_TRY(ops.precond(q, t, &z));
-      if (z != t) { KRY_TRY(ops.copy(z, t)); }
-      {
-         const double *xs[2] = {t, r};
-         KRY_TRY(ops.dots(2, xs, xs, d2));
-      }
-      gamma = d2[0];
-      i_prod = d2[1];
-      last_norm = sqrt(i_prod);
-      if (norms_h) { norms_h[i] = last_norm; }
-      if (i_prod < eps)
-      {
-         // the solution in the original variable and its true residual (:357-372)
-         KRY_TRY(ops.precond(x, q, &z));
-         if (z != q) { KRY_TRY(ops.copy(z, q)); }
-         KRY_TRY(ops.matvec(-1.0, q, 1.0, b, r));
-         const double *xs[1] = {r};
-         KRY_TRY(ops.dots(1, xs, xs, d2));
-         i_prod = d2[0];
-         if (i_prod < eps)
-         {
-            KRY_TRY(ops.copy(q, x));
-            x_not_set = false;
-            res->converged = 1; res->real_residual_exit = 1;
-            break;
-         }
-      }
-      beta = gamma / gamma_old;
-      KRY_TRY(ops.scale(beta, p));
-      KRY_TRY(ops.axpy(1.0, t, p));
-   }
-   if (x_not_set)
-   {
-      KRY_TRY(ops.copy(x, q));
-      KRY_TRY(ops.precond(q, x, &z));
-      if (z != x) { KRY_TRY(ops.copy(z, x)); }
-   }
-   res->num_iterations = i;
-   res->rel_residual_norm = last_norm / sqrt(bi_prod);
-   return B200_OK;
-}

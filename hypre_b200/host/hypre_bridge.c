@@ -109,7 +109,6 @@ void   *hb_pcg_precond_data(void *pcg) { return ((hypre_PCGData *) pcg)->precond
 /* ---- hypre_GMRESData / hypre_BiCGSTABData logging arrays (gmres.c:610-630, bicgstab.c:470-474) */
 double *hb_gmres_norms(void *g) { return ((hypre_GMRESData *) g)->norms; }
 double *hb_flexgmres_norms(void *g) { return ((hypre_FlexGMRESData *) g)->norms; }
-double *hb_cgnr_norms(void *g) { return ((hypre_CGNRData *) g)->norms; }
 double *hb_lgmres_norms(void *g) { return ((hypre_LGMRESData *) g)->norms; }
 double *hb_cogmres_norms(void *g) { return ((hypre_COGMRESData *) g)->norms; }
 double *hb_bicgstab_norms(void *g) { return ((hypre_BiCGSTABData *) g)->norms; }

@@ -1168,93 +1168,6 @@ HYPRE_Int hypre_LGMRESSolve(void *lgmres_vdata, void *A, void *b, void *x)
    return hypre_error_flag;
 }
 
-/* hypre_CGNRSolve (src/krylov/cgnr.c:209-...) for the ParCSR operator table with diagonal scaling as C and C^T
- * (ij -solver 6).  BoomerAMG (ij -solver 5) would need HYPRE_BoomerAMGSolveT on the device: rejected.  Like the
- * reference, returns its own ierr (101 for Inf/NaN input) and raises no hypre error for non-convergence. */
-HYPRE_Int hypre_CGNRSolve(void *cgnr_vdata, void *A, void *b, void *x)
-{
-   static pcg_solve_fn next = NULL;
-   hypre_CGNRData      *g  = (hypre_CGNRData *) cgnr_vdata;
-   hypre_CGNRFunctions *fn = g->functions;
-   hypre_ParCSRMatrix  *pA = (hypre_ParCSRMatrix *) A;
-   hypre_ParVector     *pb = (hypre_ParVector *) b, *px = (hypre_ParVector *) x;
-   mirror_t *m;
-   b200_cgnr_params prm;
-   b200_krylov_result res;
-   HYPRE_Int my_id, num_procs, i;
-   double *norms, *own_norms = NULL, bi_prod;
-   int status, diag_scale = 0;
-   typedef HYPRE_Int (*pc_fn)(void *, void *, void *, void *);
-
-   if (!next) { next = (pcg_solve_fn) next_sym("hypre_CGNRSolve"); }
-   if (!g_enabled) { return next(cgnr_vdata, A, b, x); }
-   if (fn->Matvec != hypre_ParKrylovMatvec) { return next(cgnr_vdata, A, b, x); }
-
-   if ((pc_fn) fn->precond == (pc_fn) HYPRE_ParCSRDiagScale && (pc_fn) fn->precondT == (pc_fn) HYPRE_ParCSRDiagScale) { diag_scale = 1; }
-   else if ((pc_fn) fn->precond == (pc_fn) hypre_ParKrylovIdentity && (pc_fn) fn->precondT == (pc_fn) hypre_ParKrylovIdentity) { diag_scale = 0; }
-   else
-   {
-      GLUE_FAIL("CGNR preconditioner has no device implementation (diagonal scaling and identity are supported; BoomerAMG needs the transposed cycle)");
-      return hypre_error_flag;
-   }
-   if (hypre_ParVectorNumVectors(pb) > 1 || hypre_ParCSRMatrixGlobalNumRows(pA) != hypre_ParCSRMatrixGlobalNumCols(pA))
-   {
-      GLUE_FAIL("CGNR on the device path needs a square operator and single vectors");
-      return hypre_error_flag;
-   }
-   m = mirror_for_matrix(pA);
-   if (!m) { GLUE_FAIL("matrix upload failed"); return hypre_error_flag; }
-
-   memset(&prm, 0, sizeof(prm));
-   prm.tol = g->tol; prm.max_iter = g->max_iter; prm.stop_crit = g->stop_crit; prm.diag_scale = diag_scale;
-   (*(fn->CommInfo))(A, &my_id, &num_procs);
-   norms = (g->logging > 0 && g->norms) ? g->norms : NULL;
-   if (!norms) { norms = own_norms = (double *) calloc((size_t) g->max_iter + 1, sizeof(double)); }
-   {
-      double *db, *dx;
-      if (krylov_operands(pb, px, &db, &dx) != 0) { free(own_norms); return hypre_error_flag; }
-      status = db ? b200_cgnr_solve(glue_ctx(), m->A, NULL, &prm, db, dx, &res, norms)
-                  : b200_cgnr_solve_host(glue_ctx(), m->A, NULL, &prm,
-                                         hypre_VectorData(hypre_ParVectorLocalVector(pb)) + m->first_row,
-                                         hypre_VectorData(hypre_ParVectorLocalVector(px)) + m->first_row, &res, norms);
-   }
-   if (status != B200_OK) { free(own_norms); GLUE_FAIL("device CGNR failed"); return hypre_error_flag; }
-   if (verbose() && g_rank == 0)
-   {
-      fprintf(stderr, "hypre_b200: CGNR solve on the device: %d iterations, relative residual %.6e\n",
-              res.num_iterations, res.rel_residual_norm);
-   }
-   if (res.error_flag & 1)
-   {
-      if (g->logging > 0) { krylov_nan_message("hypre_CGNRSolve"); }
-      free(own_norms);
-      return 101;
-   }
-   /* the reference's table (cgnr.c:229-234, 390-397, 442-445): the last column divides by <b,b>, as there */
-   bi_prod = res.b_norm * res.b_norm;
-   if (g->logging > 1 && my_id == 0 && g_rank == 0)
-   {
-      hypre_printf("Iters       ||r||_2      conv.rate  ||r||_2/||b||_2\n");
-      hypre_printf("-----    ------------    ---------  ------------ \n");
-      if (bi_prod != 0.0)
-      {
-         for (i = 1; i <= res.num_iterations; i++)
-         {
-            hypre_printf("% 5d    %e    %f   %e\n", i, norms[i], norms[i] / norms[i - 1], norms[i] / bi_prod);
-         }
-         hypre_printf("\n\n");
-      }
-   }
-   free(own_norms);
-   if (bi_prod != 0.0)
-   {
-      g->num_iterations = res.num_iterations;
-      g->rel_residual_norm = res.rel_residual_norm;
-   }
-   hypre_ParVectorAllZeros(px) = 0;
-   return 0;
-}
-
 /* hypre_BiCGSTABSolve (src/krylov/bicgstab.c:226-640) for the ParCSR operator table. */
 HYPRE_Int hypre_BiCGSTABSolve(void *bicgstab_vdata, void *A, void *b, void *x)
 {

@@ -40,7 +40,7 @@ def lib():
                  "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
         getattr(L, name).restype = vp
     for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
-                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_lgmres_norms", "hb_cgnr_norms", "hb_bicgstab_norms"):
+                 "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_lgmres_norms", "hb_bicgstab_norms"):
         getattr(L, name).restype = C.POINTER(d)
     L.hb_amg_relax_weight.restype = d
     L.hb_amg_omega.restype = d
@@ -53,7 +53,7 @@ def lib():
     for name in ("hb_vector_destroy", "hb_vector_data", "hb_vector_size", "hb_amg_num_levels", "hb_amg_Vtemp",
                  "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
                  "hb_gmres_norms", "hb_cogmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy",
-                 "HYPRE_ParCSRCOGMRESDestroy", "hb_flexgmres_norms", "HYPRE_ParCSRFlexGMRESDestroy", "hb_lgmres_norms", "HYPRE_ParCSRLGMRESDestroy", "hb_cgnr_norms", "HYPRE_ParCSRCGNRDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
+                 "HYPRE_ParCSRCOGMRESDestroy", "hb_flexgmres_norms", "HYPRE_ParCSRFlexGMRESDestroy", "hb_lgmres_norms", "HYPRE_ParCSRLGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
                  "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
                  "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
                  "HYPRE_ParCSRPCGDestroy"):
@@ -507,32 +507,6 @@ class ParCSRLGMRES(_ParCSRKrylov):
         super().__init__(**kw)
         self.SetKDim(k_dim)
         self.SetAugDim(aug_dim)
-
-
-class ParCSRCGNR(_ParCSRKrylov):
-    """HYPRE_ParCSRCGNR* / HYPRE_CGNR*: ij -solver 6 (diagonal scaling for C and C^T); -solver 5 (BoomerAMG with
-    HYPRE_BoomerAMGSolveT) has no device implementation."""
-    _prefix = "HYPRE_CGNR"
-    _par = "HYPRE_ParCSRCGNR"
-    _norms = "hb_cgnr_norms"
-
-    def __init__(self, tol=1e-8, max_iter=100, logging=1, **kw):
-        self.h = C.c_void_p()
-        lib().HYPRE_ParCSRCGNRCreate(COMM_WORLD, C.byref(self.h))
-        self.SetMaxIter(max_iter)
-        self.SetTol(float(tol))
-        self.SetLogging(logging)
-        self.max_iter = max_iter
-        self.precond = None
-
-    def SetDiagScalePrecond(self):
-        L = lib()
-        return L.HYPRE_CGNRSetPrecond(self.h, L.HYPRE_ParCSRDiagScale, L.HYPRE_ParCSRDiagScale,
-                                      L.HYPRE_ParCSRDiagScaleSetup, None)
-
-    @property
-    def converged(self):
-        return None          # hypre_CGNRData has no such field
 
 
 class ParCSRBiCGSTAB(_ParCSRKrylov):

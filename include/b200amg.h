@@ -343,16 +343,6 @@ typedef struct {
    double cf_tol;            /* as b200_gmres_params (lgmres.c) */
 } b200_lgmres_params;
 
-/* hypre_CGNRSolve (src/krylov/cgnr.c:209-...; ij -solver 6): CG on the normal equations with a SYMMETRIC
- * preconditioner -- diagonal scaling (diag_scale) or none; amg must be NULL (the reference's AMG form needs the
- * transposed cycle, HYPRE_BoomerAMGSolveT).  A must be square. */
-typedef struct {
-   double tol;
-   int    max_iter;
-   int    stop_crit;         /* 1: ||r||^2 < tol^2 instead of tol^2 <b,b> (cgnr.c:262-270) */
-   int    diag_scale;
-} b200_cgnr_params;
-
 typedef struct {
    int    num_iterations;
    int    converged;
@@ -369,8 +359,6 @@ int b200_gmres_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_gm
                      const double *b, double *x, b200_krylov_result *res, double *norms_h);
 int b200_bicgstab_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
                         const double *b, double *x, b200_krylov_result *res, double *norms_h);
-int b200_cgnr_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_cgnr_params *prm,
-                    const double *b, double *x, b200_krylov_result *res, double *norms_h);
 int b200_lgmres_solve(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
                       const double *b, double *x, b200_krylov_result *res, double *norms_h);
 /* the same with HOST b/x (H2D of b and x, device solve, D2H of x): the calls the hypre_GMRESSolve /
@@ -379,8 +367,6 @@ int b200_gmres_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b2
                           const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
 int b200_bicgstab_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_bicgstab_params *prm,
                              const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
-int b200_cgnr_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_cgnr_params *prm,
-                         const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
 int b200_lgmres_solve_host(b200_ctx *ctx, b200_parcsr *A, b200_amg *amg, const b200_lgmres_params *prm,
                            const double *b_h, double *x_h, b200_krylov_result *res, double *norms_h);
 

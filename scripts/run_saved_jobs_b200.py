@@ -25,8 +25,8 @@ RTOL = 2e-6          # the printed 7 digits (tests/test_ref_multirank.py)
 
 
 # solver ids the binding runs on the device: 0 AMG, 1/2 PCG, 3/4 GMRES, 16/17 COGMRES, 61/60 FlexGMRES, 51/50 LGMRES,
-# 9/10 BiCGSTAB, 6 DS-CGNR (hypre_glue.c); a job without -solver is ij's default 0
-BOUND = {0, 1, 2, 3, 4, 6, 9, 10, 16, 17, 50, 51, 60, 61}
+# 9/10 BiCGSTAB (hypre_glue.c); a job without -solver is ij's default 0
+BOUND = {0, 1, 2, 3, 4, 9, 10, 16, 17, 50, 51, 60, 61}
 
 
 def relevant(job):

@@ -9,14 +9,6 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 os.environ.setdefault("OMP_NUM_THREADS", str(min(8, os.cpu_count() or 1)))
 
 
-# GPU tests written after a round's GPU minutes were spent have never run: they are collected last
-# (test_gpu_zz_*.py) and marked with FIRST_RUN -- a non-strict xfail, so that they RUN at round end and show up as
-# XPASS / xfail in the log without turning the suite red on a tolerance that was chosen blind.
-# B200_TEST_UNVERIFIED=1 (scripts/gpu_r2_first.sh) turns the mark off: failures are then failures.
-FIRST_RUN = pytest.mark.xfail(condition=os.environ.get("B200_TEST_UNVERIFIED", "0") != "1", strict=False,
-                              reason="first GPU run pending (written without GPU minutes); B200_TEST_UNVERIFIED=1 makes it strict")
-
-
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

@@ -233,10 +233,3 @@ extern "C" int kht_lgmres_dist(int n_local, const double *diag, kht_matvec_cb mv
    return lgmres_core(ops, prm, b, x, vec.data(), av, av + prm->aug_dim + 1, vec[nv - 2], vec[nv - 1], res, norms);
 }
 
-extern "C" int kht_cgnr(int n, const int *ia, const int *ja, const double *a, orc_amg *amg, int kind,
-                        const b200_cgnr_params *prm, const double *b, double *x, b200_krylov_result *res, double *norms)
-{
-   HostKrylovOps ops{n, ia, ja, a, amg, kind};
-   std::vector<std::vector<double>> store(4, std::vector<double>((size_t)n, 0.0));
-   return cgnr_core(ops, prm, b, x, store[0].data(), store[1].data(), store[2].data(), store[3].data(), res, norms);
-}

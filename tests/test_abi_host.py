@@ -271,18 +271,3 @@ def test_device_binding_goes_away_with_the_vector(H):
     assert L.hypre_b200_vector_device(C.c_void_p(handle)) is None
 
 
-def test_cgnr_has_no_cpu_fallback_and_rejects_amg(H):
-    """hypre_CGNRSolve is interposed (diagonal scaling / identity): without a GPU it raises the hypre error flag and
-    leaves x alone"""
-    if has_gpu():
-        pytest.skip("GPU present")
-    H.set_device_path(True)
-    A = H.laplacian(6, 6, 6)
-    b = A.vector(1.0); x = A.vector(0.0)
-    s = H.ParCSRCGNR()
-    s.SetDiagScalePrecond()
-    s.Setup(A, b, x)
-    H.clear_errors()
-    s.Solve(A, b, x)
-    assert H.error_flag() & 1 and not np.any(x.numpy())
-    H.clear_errors()

@@ -11,9 +11,8 @@ import pytest
 
 from hypre_b200 import IJ_B200, IJ_REF
 
-from conftest import FIRST_RUN
 
-pytestmark = [pytest.mark.gpu, FIRST_RUN]
+pytestmark = [pytest.mark.gpu]
 
 KEYS = {"iterations": r"BoomerAMG Iterations = (\d+)",
         "final_rel": r"Final Relative Residual Norm = (\S+)",

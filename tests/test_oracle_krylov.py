@@ -263,25 +263,3 @@ def test_oracle_bicgstab_stop_crit_matches_reference(ref_off):
     orc.destroy()
 
 
-@pytest.mark.parametrize("dims,x0kind,max_iter", [((9, 8, 7), "zero", 400), ((6, 5, 4), "sin", 400), ((9, 8, 7), "zero", 12)])
-def test_oracle_cgnr_matches_reference(ref_off, dims, x0kind, max_iter):
-    """hypre_CGNRSolve with diagonal scaling (ij -solver 6): histories, iteration counts, solution; also the exit at
-    max_iter (x is un-preconditioned at the end, cgnr.c:385-392)"""
-    H = ref_off
-    A = H.laplacian(*dims)
-    b, x = A.vector(1.0), A.vector(0.0)
-    x0 = np.zeros(x.size) if x0kind == "zero" else 0.1 * np.sin(np.arange(x.size))
-    x.numpy()[:] = x0
-    s = H.ParCSRCGNR(tol=1e-8, max_iter=max_iter)
-    s.SetDiagScalePrecond()
-    s.Setup(A, b, x)
-    H.clear_errors()
-    s.Solve(A, b, x)
-    Ad, _ = A.blocks()
-    orc = O.OracleAMG.from_arrays([dict(A=Ad, P=None)], [18, 18, 18, 18], [1, 1, 1, 1], 1, 0, 2, 1, None)
-    xo, it, norms, rel = orc.cgnr(b.numpy(), x0, precond=1, max_iter=max_iter)
-    assert it == s.num_iterations and (it == 12 if max_iter == 12 else it > 12)
-    np.testing.assert_allclose(norms, s.norms(), rtol=1e-9)
-    np.testing.assert_allclose(rel, s.final_rel_norm, rtol=1e-9)
-    np.testing.assert_allclose(xo, x.numpy(), rtol=1e-9, atol=1e-12)
-    orc.destroy()
