@@ -100,6 +100,7 @@ def lib():
         "b200_parcsr_info": (i, [vp, c_int_p, c_int_p, C.POINTER(ll), c_int_p, c_int_p]),
         "b200_set_layout_override": (i, [i, i]),
         "b200_set_compression": (i, [i, i]),
+        "b200_set_kernel_options": (i, [i, i]),
         "b200_storage_decode_host": (i, [i, i, vp, vp, vp, vp, vp, c_int_p, c_int_p, C.POINTER(ll), C.POINTER(ll)]),
         "b200_parcsr_storage": (i, [vp, c_int_p, C.POINTER(ll), C.POINTER(ll), c_int_p]),
         "b200_rowpart_create": (i, [i, i, i, i, vp, vp, vp, vp, vp, c_void_pp]),

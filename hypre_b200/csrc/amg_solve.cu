@@ -11,7 +11,6 @@ struct EpiResidualNorm {
    static constexpr int NRED = 1;
    EPI_PLAIN_X
    const double *b; double *r;
-   __device__ __forceinline__ void prefetch(int row) const { prefetch_l2(b + row); }
    __device__ void operator()(int row, double t, double *red) const
    {
       double v = b[row] - t;

@@ -166,7 +166,8 @@ struct DMat {
 };
 
 // cfmt: value encoding of the compressed storage (column indices are always base + u16)
-enum { CFMT_NONE = 0, CFMT_VAL8 = 1, CFMT_VAL16 = 2, CFMT_VAL64 = 3 };
+// CFMT_PAT8: one byte per entry = index of its (column - row, value) pattern, lane-uniform entries once per slice
+enum { CFMT_NONE = 0, CFMT_VAL8 = 1, CFMT_VAL16 = 2, CFMT_VAL64 = 3, CFMT_PAT8 = 4 };
 constexpr int            CFMT_ESC = (int)0x80000000;   // c_base sentinel: this (slice, entry) keeps 32-bit columns in sl_ci
 constexpr unsigned short CFMT_PAD = 0xFFFFu;           // c_idx value of a padding lane
 
@@ -269,7 +270,8 @@ struct PackedDMat {
    std::vector<unsigned short> idx;         // chunk-transposed 16-bit column offsets
    std::vector<int>            base;        // [padded/32]
    std::vector<unsigned char>  code;        // chunk-transposed value codes (u8, or u16 as byte pairs)
-   std::vector<double>         dict;
+   std::vector<double>         dict;        // value dictionary; CFMT_PAT8: (value, delta bits) pairs
+   std::vector<unsigned char>  pat;         // CFMT_PAT8: the slice streams (sl_off = byte offsets)
 };
 void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P);
 int  packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, double *y);

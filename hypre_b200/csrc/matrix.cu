@@ -78,7 +78,8 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    B200_TRY(dev_upload(&m->c_idx, P.idx.data(), P.idx.size()));
    B200_TRY(dev_upload(&m->c_base, P.base.data(), P.base.size()));
    unsigned char *d_code = nullptr;
-   B200_TRY(dev_upload(&d_code, P.code.data(), P.code.size()));
+   if (P.cfmt == CFMT_PAT8) { B200_TRY(dev_upload(&d_code, P.pat.data(), P.pat.size())); m->n_dict = (int)(P.dict.size() / 2); }
+   else { B200_TRY(dev_upload(&d_code, P.code.data(), P.code.size())); }
    m->c_code = d_code;
    B200_TRY(dev_upload(&m->c_dict, P.dict.data(), P.dict.size()));
    m->h_pos.swap(P.h_pos);

@@ -9,7 +9,6 @@ struct EpiMatvec {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    double alpha, beta; const double *b; double *y;
-   __device__ __forceinline__ void prefetch(int r) const { if (beta != 0.0) { prefetch_l2(b + r); } }
    __device__ void operator()(int r, double t, double *) const
    {
       double v = alpha * t;
@@ -22,7 +21,6 @@ struct EpiMatvecDot {
    static constexpr int NRED = 1;
    EPI_PLAIN_X
    const double *x; double *y;
-   __device__ __forceinline__ void prefetch(int) const {}
    __device__ void operator()(int r, double t, double *red) const
    {
       y[r] = t;
@@ -34,7 +32,6 @@ struct EpiJacobi {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    double w; const double *f; const double *l1; const double *u_in; double *u_out;
-   __device__ __forceinline__ void prefetch(int r) const { prefetch_l2(f + r); prefetch_l2(l1 + r); }
    __device__ void operator()(int r, double t, double *) const
    {
       u_out[r] = u_in[r] + (w * (f[r] - t)) / l1[r];
@@ -46,7 +43,6 @@ struct EpiChebyFirst {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    int scale; double c; const double *f; const double *ds; double *rv; double *tmp;
-   __device__ __forceinline__ void prefetch(int r) const { prefetch_l2(f + r); if (scale) { prefetch_l2(ds + r); } }
    __device__ void operator()(int r, double t, double *) const
    {
       double res = f[r] - t;
@@ -62,12 +58,6 @@ struct EpiChebyStep {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    int scale; int last; double c; const double *ds; const double *rv; double *out; double *u;
-   __device__ __forceinline__ void prefetch(int r) const
-   {
-      prefetch_l2(rv + r);
-      if (scale) { prefetch_l2(ds + r); }
-      if (last) { prefetch_l2(u + r); }
-   }
    __device__ void operator()(int r, double t, double *) const
    {
       double ui = scale ? c * rv[r] + ds[r] * t : c * rv[r] + t;
@@ -92,7 +82,6 @@ struct EpiChebyZero {
       const double u1 = res * ck;
       return scale ? __ldg(ds + j) * u1 : u1;
    }
-   __device__ __forceinline__ void prefetch(int) const {}     // f, ds are the gathered operands
    __device__ void operator()(int r, double t, double *) const
    {
       double res = f[r];
@@ -109,7 +98,6 @@ struct EpiGsFirst {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    double w; const double *f; const double *d; double *z;
-   __device__ __forceinline__ void prefetch(int r) const { prefetch_l2(f + r); prefetch_l2(d + r); }
    __device__ void operator()(int r, double t, double *) const { z[r] = (w * (f[r] - t)) / d[r]; }
 };
 // inner stage over the strict lower triangle (par_relax.c:1562-1585): z' = t/d ; u += mult*z'
@@ -118,11 +106,6 @@ struct EpiGsInner {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    int first; double mult; const double *d; const double *z_in; double *z_out; double *u;
-   __device__ __forceinline__ void prefetch(int r) const
-   {
-      prefetch_l2(d + r); prefetch_l2(u + r);
-      if (first) { prefetch_l2(z_in + r); }
-   }
    __device__ void operator()(int r, double t, double *) const
    {
       double zn = t / d[r];

@@ -11,20 +11,37 @@
 #include <algorithm>
 #include <climits>
 #include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 static int g_layout_override = -1;
 static int g_lanes_override  = -1;
 // compressed thread-per-row storage: -1 automatic (default; B200_COMPRESS=0 in the environment turns it
-// off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it
-static int g_compress = []() { const char *e = getenv("B200_COMPRESS"); return e ? atoi(e) : -1; }();
-int g_sellc_pipe = []() { const char *e = getenv("B200_SELLC_PIPE"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 5 ? v : 0; }();
+// off), 0 off, CFMT_VAL8 / CFMT_VAL16 / CFMT_VAL64 force that value format where the dictionary allows it,
+// CFMT_PAT8 forces the pattern storage where the block qualifies (automatic choice otherwise)
+static int env_int(const char *name, int dflt) { const char *e = getenv(name); return e ? atoi(e) : dflt; }
+static int g_compress = env_int("B200_COMPRESS", -1);
+// VAL* storage without padding markers (rowsum_sellc_z): B200_ZPAD
+static int g_zpad = env_int("B200_ZPAD", 0) != 0;
+// launch options of the thread-per-row kernels (rowlaunch.cuh)
+int g_rows_chunked = env_int("B200_CHUNKED", 1) != 0;
+int g_pat_regs = env_int("B200_PAT_REGS", 0) != 0;
 
-extern "C" int b200_set_compression(int mode, int pipeline)
+extern "C" int b200_set_compression(int mode, int no_padding_markers)
 {
-   ARG_CHECK(mode >= -1 && mode <= CFMT_VAL64);
-   ARG_CHECK(pipeline >= -1 && pipeline <= 5);
+   ARG_CHECK(mode >= -1 && mode <= CFMT_PAT8);
+   ARG_CHECK(no_padding_markers >= -1 && no_padding_markers <= 1);
    g_compress = mode;
-   if (pipeline >= 0) { g_sellc_pipe = pipeline; }
+   if (no_padding_markers >= 0) { g_zpad = no_padding_markers; }
+   return B200_OK;
+}
+
+extern "C" int b200_set_kernel_options(int chunked, int pat_regs)
+{
+   ARG_CHECK(chunked >= -1 && chunked <= 1 && pat_regs >= -1 && pat_regs <= 1);
+   if (chunked >= 0) { g_rows_chunked = chunked; }
+   if (pat_regs >= 0) { g_pat_regs = pat_regs; }
    return B200_OK;
 }
 
@@ -73,6 +90,187 @@ struct ValueDict {
       return codes[hsh];
    }
 };
+
+// ---------------------------------------------------------------- pattern dictionary (CFMT_PAT8)
+// (column - row, value bits) -> code, at most PAT_CAP patterns; open addressing in a small table
+constexpr int PAT_CAP = 254;            // 0xFF marks "differs between lanes" in a slice header
+struct PatDict {
+   static constexpr unsigned TAB = 1024;
+   int           dl[TAB];
+   unsigned long long vb[TAB];
+   short         cd[TAB];
+   std::vector<int> deltas;
+   std::vector<unsigned long long> vals;
+   PatDict() { for (unsigned k = 0; k < TAB; k++) { cd[k] = -1; } }
+   static unsigned slot(int d, unsigned long long b)
+   {
+      return (unsigned)(((b ^ ((unsigned long long)(unsigned)d * 0x9E3779B97F4A7C15ull)) * 0xD6E8FEB86659FD93ull) >> 54);
+   }
+   int find(int d, unsigned long long b) const
+   {
+      unsigned h = slot(d, b);
+      while (cd[h] >= 0 && (dl[h] != d || vb[h] != b)) { h = (h + 1) & (TAB - 1); }
+      return cd[h];
+   }
+   // code of the pattern, added if new; -1 when the dictionary is full
+   int add(int d, unsigned long long b)
+   {
+      unsigned h = slot(d, b);
+      while (cd[h] >= 0 && (dl[h] != d || vb[h] != b)) { h = (h + 1) & (TAB - 1); }
+      if (cd[h] >= 0) { return cd[h]; }
+      if ((int)deltas.size() >= PAT_CAP) { return -1; }
+      dl[h] = d; vb[h] = b; cd[h] = (short)deltas.size();
+      deltas.push_back(d); vals.push_back(b);
+      return cd[h];
+   }
+};
+
+static inline unsigned long long dbits(double v) { unsigned long long b; memcpy(&b, &v, 8); return b; }
+
+// Pattern storage of a thread-per-row block (format: rowsum_pat, spmv.cuh).  order: storage position -> row
+// (layout 2) or nullptr; width[s]: entries of the longest row of slice s.  Returns false -- leaving P
+// untouched -- when the block does not qualify: more than PAT_CAP patterns, an empty row (its padding would
+// have no column of its own to gather), or a slice wider than 1020 entries.
+static bool pack_patterns(const HostCsr &h, const std::vector<int> *order, int n_slices,
+                          const std::vector<long long> &off_orig, PackedDMat *P)
+{
+   const int n = h.n_rows;
+   auto row_at = [&](int p) { return order ? (*order)[(size_t)p] : p; };
+   std::vector<int> w4((size_t)n_slices);
+   for (int s = 0; s < n_slices; s++)
+   {
+      const long long w = (off_orig[(size_t)s + 1] - off_orig[(size_t)s]) / 32;
+      if (w > 1020) { return false; }
+      w4[(size_t)s] = (int)((w + 3) & ~3LL);
+   }
+   // ---- dictionary: per-thread over row ranges, merged in thread order (deterministic)
+   int nthreads = 1;
+#ifdef _OPENMP
+   nthreads = omp_get_max_threads();
+#endif
+   std::vector<PatDict> local((size_t)nthreads);
+   std::vector<int> slice_of_row;
+   if (order)
+   {
+      slice_of_row.assign((size_t)n, 0);
+      for (int p = 0; p < n_slices * 32; p++) { const int r = (*order)[(size_t)p]; if (r < n) { slice_of_row[(size_t)r] = p >> 5; } }
+   }
+   bool fail = false;
+#pragma omp parallel num_threads(nthreads)
+   {
+      int tid = 0, nt = 1;
+#ifdef _OPENMP
+      tid = omp_get_thread_num(); nt = omp_get_num_threads();
+#endif
+      PatDict &d = local[(size_t)tid];
+      const int r0 = (int)((long long)n * tid / nt), r1 = (int)((long long)n * (tid + 1) / nt);
+      bool bad = false;
+      for (int r = r0; r < r1 && !bad; r++)
+      {
+         const int beg = h.i[r], len = h.i[r + 1] - beg;
+         if (len == 0) { bad = true; break; }
+         for (int k = 0; k < len; k++) { if (d.add(h.j[beg + k] - r, dbits(h.a[beg + k])) < 0) { bad = true; break; } }
+         const int sl = order ? slice_of_row[(size_t)r] : (r >> 5);
+         if (!bad && len < w4[(size_t)sl] && d.add(h.j[beg + len - 1] - r, 0ull) < 0) { bad = true; }
+      }
+      if (bad)
+      {
+#pragma omp atomic write
+         fail = true;
+      }
+   }
+   if (fail) { return false; }
+   PatDict dict;
+   for (auto &d : local)
+   {
+      for (size_t k = 0; k < d.deltas.size(); k++) { if (dict.add(d.deltas[k], d.vals[k]) < 0) { return false; } }
+   }
+   // dead lanes of the last slice repeat the padding pattern of the last row (same clamped row in the kernel)
+   const int last_beg = h.i[n - 1], last_len = h.i[n] - last_beg;
+   const int dead_code = dict.add(h.j[last_beg + last_len - 1] - (n - 1), 0ull);
+   if (dead_code < 0) { return false; }
+
+   // ---- codes of every (slice, k, lane), entry-major per slice
+   std::vector<long long> coff((size_t)n_slices + 1, 0);
+   for (int s = 0; s < n_slices; s++) { coff[(size_t)s + 1] = coff[(size_t)s] + (long long)w4[(size_t)s] * 32; }
+   std::vector<unsigned char> codes((size_t)coff[(size_t)n_slices]);
+   std::vector<long long> bytes((size_t)n_slices + 1, 0);
+#pragma omp parallel for schedule(static)
+   for (int s = 0; s < n_slices; s++)
+   {
+      unsigned char *cs = codes.data() + coff[(size_t)s];
+      const int w = w4[(size_t)s];
+      for (int l = 0; l < 32; l++)
+      {
+         const int r = row_at(s * 32 + l);
+         if (r >= n) { for (int k = 0; k < w; k++) { cs[k * 32 + l] = (unsigned char)dead_code; } continue; }
+         const int beg = h.i[r], len = h.i[r + 1] - beg;
+         for (int k = 0; k < len; k++) { cs[k * 32 + l] = (unsigned char)dict.find(h.j[beg + k] - r, dbits(h.a[beg + k])); }
+         if (len < w)
+         {
+            const unsigned char pc = (unsigned char)dict.find(h.j[beg + len - 1] - r, 0ull);
+            for (int k = len; k < w; k++) { cs[k * 32 + l] = pc; }
+         }
+      }
+      int lane_words = 0;
+      for (int i = 0; i < w / 4; i++)
+      {
+         bool mixed = false;
+         for (int k = 4 * i; k < 4 * i + 4 && !mixed; k++)
+         {
+            for (int l = 1; l < 32; l++) { if (cs[k * 32 + l] != cs[k * 32]) { mixed = true; break; } }
+         }
+         lane_words += mixed;
+      }
+      bytes[(size_t)s + 1] = ((4 + 4 * (long long)(w / 4) + 15) & ~15LL) + 128LL * lane_words;
+   }
+   for (int s = 0; s < n_slices; s++) { bytes[(size_t)s + 1] += bytes[(size_t)s]; }
+   P->pat.assign((size_t)bytes[(size_t)n_slices], 0);
+#pragma omp parallel for schedule(static)
+   for (int s = 0; s < n_slices; s++)
+   {
+      const unsigned char *cs = codes.data() + coff[(size_t)s];
+      const int nw = w4[(size_t)s] / 4;
+      unsigned *w0 = reinterpret_cast<unsigned *>(P->pat.data() + bytes[(size_t)s]);
+      unsigned *lanew = w0 + ((nw + 4) & ~3);
+      w0[0] = (unsigned)nw;
+      for (int i = 0; i < nw; i++)
+      {
+         unsigned hw = 0, mixed_any = 0;
+         for (int j = 0; j < 4; j++)
+         {
+            const unsigned char *ck = cs + (4 * i + j) * 32;
+            bool mixed = false;
+            for (int l = 1; l < 32; l++) { if (ck[l] != ck[0]) { mixed = true; break; } }
+            hw |= (mixed ? 0xFFu : (unsigned)ck[0]) << (8 * j);
+            mixed_any |= mixed;
+         }
+         w0[1 + i] = hw;
+         if (mixed_any)
+         {
+            for (int l = 0; l < 32; l++)
+            {
+               unsigned lw = 0;
+               for (int j = 0; j < 4; j++) { lw |= (unsigned)cs[(4 * i + j) * 32 + l] << (8 * j); }
+               lanew[l] = lw;
+            }
+            lanew += 32;
+         }
+      }
+   }
+   P->dict.assign(2 * dict.deltas.size(), 0.0);
+   for (size_t k = 0; k < dict.deltas.size(); k++)
+   {
+      memcpy(&P->dict[2 * k], &dict.vals[k], 8);
+      const long long dl = (long long)(unsigned)dict.deltas[k];       // delta in the low word of the second double
+      memcpy(&P->dict[2 * k + 1], &dl, 8);
+   }
+   P->sl_off.swap(bytes);
+   P->cfmt = CFMT_PAT8;
+   P->padded = coff[(size_t)n_slices];
+   P->stored_bytes = (long long)P->pat.size() + 8 * (long long)n_slices + 16 * (long long)dict.deltas.size();
+   return true;
+}
 
 // ---------------------------------------------------------------- layout choice + packing
 // Thread-per-row layouts: slice = 32 consecutive storage positions; order[p] = row stored at position p
@@ -171,15 +369,38 @@ void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
    int cfmt = CFMT_NONE;
    bool zpad = false;
    std::vector<long long> sl_off = off_orig;
+   // pattern storage first: where a block qualifies (stencils and their first Galerkin products) nothing else
+   // comes close -- one byte per entry at most, none for lane-uniform entries
+   if (g_compress == -1 || g_compress == CFMT_PAT8)
+   {
+      PackedDMat Q = *P;
+      if (pack_patterns(h, order, n_slices, off_orig, &Q))
+      {
+         Q.n_slices = n_slices;
+         if (layout == 2)
+         {
+            Q.perm.resize(sorted.size());
+            Q.h_pos.assign((size_t)n, 0);
+            for (size_t p = 0; p < sorted.size(); p++)
+            {
+               Q.perm[p] = (unsigned short)(sorted[p] - (int)(p / 256) * 256);
+               if (sorted[p] < n) { Q.h_pos[(size_t)sorted[p]] = (int)p; }
+            }
+         }
+         *P = std::move(Q);
+         return;
+      }
+   }
    if (g_compress != 0)
    {
       cfmt = CFMT_VAL64;
-      // loop variant 5 (rowsum_sellc_z) has no padding marker: padding lanes gather a valid column and
+      // storage without padding markers (rowsum_sellc_z): padding lanes gather a valid column and
       // multiply it by a dictionary entry 0.0 (as the plain sliced-ELL layout does); one code is kept for it
-      zpad = (g_sellc_pipe == 5);
-      if (g_compress != CFMT_VAL64 && vd.build(h.a, (g_compress == CFMT_VAL8 ? 256 : 65536) - (size_t)zpad))
+      zpad = g_zpad != 0;
+      const int vmode = g_compress == CFMT_PAT8 ? -1 : g_compress;
+      if (vmode != CFMT_VAL64 && vd.build(h.a, (vmode == CFMT_VAL8 ? 256 : 65536) - (size_t)zpad))
       {
-         cfmt = (vd.dict.size() + (size_t)zpad <= 256 && g_compress != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
+         cfmt = (vd.dict.size() + (size_t)zpad <= 256 && vmode != CFMT_VAL16) ? CFMT_VAL8 : CFMT_VAL16;
       }
       std::vector<long long> off4((size_t)n_slices + 1, 0);
       for (int sidx = 0; sidx < n_slices; sidx++)
@@ -188,7 +409,7 @@ void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P)
          off4[(size_t)sidx + 1] = off4[(size_t)sidx] + ((w + 3) & ~3LL) * 32;
       }
       const long long per_entry = 2 + (cfmt == CFMT_VAL8 ? 1 : cfmt == CFMT_VAL16 ? 2 : 8);
-      if (g_compress > 0 || per_entry * off4[(size_t)n_slices] + off4[(size_t)n_slices] / 8 < 12 * off_orig[(size_t)n_slices])
+      if (vmode > 0 || per_entry * off4[(size_t)n_slices] + off4[(size_t)n_slices] / 8 < 12 * off_orig[(size_t)n_slices])
       {
          sl_off.swap(off4);
       }
@@ -360,7 +581,36 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
          if (!P.perm.empty()) { row = (slice >> 3) * 256 + P.perm[(size_t)row]; }
          double t = 0.0;
          bool stray = false;      // a row beyond n_rows multiplied a non-zero value
-         if (P.cfmt == CFMT_NONE)
+         if (P.cfmt == CFMT_PAT8)
+         {
+            // the addressing of rowsum_pat: header words, lane words at the next 16-byte boundary
+            const unsigned *w0 = reinterpret_cast<const unsigned *>(P.pat.data() + off);
+            const unsigned nw = w0[0] & 0xFFu;
+            const unsigned *lp = w0 + ((nw + 4) & ~3u) + lane;
+            const int rowc = row < n ? row : n - 1;
+            for (unsigned i = 0; i < nw; i++)
+            {
+               unsigned hw = w0[1 + i], m = 0;
+               for (int j = 0; j < 4; j++) { if (((hw >> (8 * j)) & 0xFFu) == 0xFFu) { m |= 0xFFu << (8 * j); } }
+               if (m)
+               {
+                  if ((const unsigned char *)(lp + 1) > P.pat.data() + P.sl_off[(size_t)slice + 1]) { b200_set_error("pattern stream overrun"); return B200_ERR_ARG; }
+                  hw = (*lp & m) | (hw & ~m); lp += 32;
+               }
+               for (int j = 0; j < 4; j++)
+               {
+                  const unsigned cd = (hw >> (8 * j)) & 0xFFu;
+                  if (2 * (size_t)cd + 1 >= P.dict.size()) { b200_set_error("pattern code out of range"); return B200_ERR_ARG; }
+                  const double v = P.dict[2 * cd];
+                  int delta; memcpy(&delta, &P.dict[2 * cd + 1], 4);
+                  const int col = rowc + delta;
+                  if (col < 0 || col >= h.n_cols) { b200_set_error("packed column out of range"); return B200_ERR_ARG; }
+                  t = fma(v, x[col], t);
+                  stray |= (row >= n && v != 0.0);
+               }
+            }
+         }
+         else if (P.cfmt == CFMT_NONE)
          {
             const int width = (int)(span >> 5);
             for (int k = 0; k < width; k++)

@@ -22,8 +22,9 @@ static inline int rows_grid(long long work, int per_block)
    return (int)g;
 }
 
-// pipelining variant of the compressed row kernels (matrix.cu; B200_SELLC_PIPE = 0 | 1 | 2, b200_set_compression)
-extern int g_sellc_pipe;
+// launch options of the thread-per-row kernels (pack.cu; environment B200_CHUNKED, B200_PAT_REGS,
+// b200_set_kernel_options): slice-to-block mapping and the PAT8 instantiation
+extern int g_rows_chunked, g_pat_regs;
 
 static inline HaloArgs no_halo()
 {
@@ -49,20 +50,16 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    if (D.layout >= 1 || D.n_rows == 0)
    {
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
-      // loop variant 4 (dictionary in shared memory) exists for u8 codes only
-      // and variant 5 (no predicates) needs storage packed without padding markers
-      const int variant = (g_sellc_pipe == 4 && D.cfmt != CFMT_VAL8) || (g_sellc_pipe == 5 && !D.zpad) ? 0 : g_sellc_pipe;
-      switch (D.cfmt ? D.cfmt + 4 * variant : 0)
+      HaloArgs hh = h;
+      hh.chunked = g_rows_chunked;
+      const int variant = D.cfmt == CFMT_PAT8 ? (g_pat_regs ? 1 : 0) : (D.zpad ? 1 : 0);
+      switch (D.cfmt ? D.cfmt + 8 * variant : 0)
       {
-#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc); break;
-         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64)
-         CASE_C(CFMT_VAL8 + 4) CASE_C(CFMT_VAL16 + 4) CASE_C(CFMT_VAL64 + 4)
-         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8)
-         CASE_C(CFMT_VAL8 + 12) CASE_C(CFMT_VAL16 + 12) CASE_C(CFMT_VAL64 + 12)
-         CASE_C(CFMT_VAL8 + 16)
-         CASE_C(CFMT_VAL8 + 20) CASE_C(CFMT_VAL16 + 20) CASE_C(CFMT_VAL64 + 20)
+#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
+         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_C(CFMT_PAT8)
+         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_C(CFMT_PAT8 + 8)
 #undef CASE_C
-         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc); break;
+         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
       }
    }
    else

@@ -134,15 +134,15 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
    return t;
 }
 
-// Compressed sliced ELL (DMat::cfmt != 0).  HBM bandwidth bounds these kernels, so the matrix is
-// stored in fewer bytes, losslessly: the column of (slice, entry k, lane) is base[slice][k] + a 16-bit
-// offset (the 32 rows of a slice are neighbours, so their k-th columns are, too; a (slice, k) whose
+// Compressed sliced ELL (DMat::cfmt = CFMT_VAL8 / VAL16 / VAL64).  HBM bandwidth bounds these kernels, so
+// the matrix is stored in fewer bytes, losslessly: the column of (slice, entry k, lane) is base[slice][k] + a
+// 16-bit offset (the 32 rows of a slice are neighbours, so their k-th columns are, too; a (slice, k) whose
 // columns span more than 65534 keeps 32-bit columns in sl_ci: base == CFMT_ESC), and a block with at most
 // 256 / 65536 distinct values (stencils, and the Galerkin products of stencils) stores 8- / 16-bit codes
 // into a dictionary that stays in L1/L2.  12 bytes per entry become 3 or 4 (10 without a dictionary).
 // Entries are stored in chunks of 4 per lane (one 8-byte offset load, one 4/8-byte code load and one
-// 16-byte broadcast base load per chunk); slice widths are multiples of 4, padding lanes are marked
-// by offset 0xFFFF and skipped.  Arithmetic and summation order are those of the CSR row.
+// 16-byte broadcast base load per chunk); slice widths are multiples of 4.  Arithmetic and summation order
+// are those of the CSR row.
 __device__ __forceinline__ unsigned long long ld_stream_u64(const void *p)
 {
    unsigned long long v;
@@ -156,24 +156,15 @@ __device__ __forceinline__ unsigned ld_stream_u32(const void *p)
    return v;
 }
 
-__device__ __forceinline__ void prefetch_l2(const void *p)
-{
-   asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-}
-// the warp asks L2 for [p, p + bytes): one 128-byte line per lane and trip
-__device__ __forceinline__ void prefetch_span_l2(const void *p, long long bytes, int lane)
-{
-   for (long long b = (long long)lane * 128; b < bytes; b += 32 * 128) { prefetch_l2((const char *)p + b); }
-}
-
-// One slice = entries [off, off + 128 n_chunks).  With 3-4 bytes per entry the loop is bound by load
-// latency, not by DRAM bandwidth (a thread has 12 bytes of matrix in flight), so PIPE == 2 lets the warp
-// pull the compressed streams of the slice it will process NEXT ([off_n, end_n), known one trip ahead,
-// see rows_range) into L2 while it works on this one: no registers, no scoreboard entry.
-template <int VF, int PIPE, class XF>
+// One slice = entries [off, off + 128 n_chunks).  Two forms of the same storage (DMat::zpad):
+//   rowsum_sellc    padding lanes carry the offset CFMT_PAD and are skipped (no gather, no fma)
+//   rowsum_sellc_z  no markers: a padding lane gathers a column of its OWN row and multiplies it by a
+//                   dictionary entry 0.0 (what rowsum_sell does in the plain layout), so the chunk has no
+//                   predicates; u8 dictionaries are read from shared memory.  Row sums are those of
+//                   rowsum_sellc except that a sum of exactly -0.0 becomes +0.0.
+template <int VF, class XF>
 __device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, int n_chunks, int lane,
-                                               const double *__restrict__ x, const XF &xf,
-                                               long long off_n, int n_chunks_n)
+                                               const double *__restrict__ x, const XF &xf)
 {
    const unsigned short *ip = D.c_idx + off + lane * 4;
    const int4 *bp = reinterpret_cast<const int4 *>(D.c_base + (off >> 5));
@@ -185,15 +176,6 @@ __device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, 
       unsigned long long code = 0;
       if (VF == CFMT_VAL8)  { code = ld_stream_u32((const unsigned char *)D.c_code + off + c * 128 + lane * 4); }
       if (VF == CFMT_VAL16) { code = ld_stream_u64((const unsigned short *)D.c_code + off + c * 128 + lane * 4); }
-      if (PIPE >= 2 && c == 0 && n_chunks_n > 0)
-      {
-         const long long e = (long long)n_chunks_n << 7;
-         prefetch_span_l2(D.c_idx + off_n, 2 * e, lane);
-         if (VF == CFMT_VAL8)  { prefetch_span_l2((const unsigned char *)D.c_code + off_n, e, lane); }
-         if (VF == CFMT_VAL16) { prefetch_span_l2((const unsigned short *)D.c_code + off_n, 2 * e, lane); }
-         if (VF == CFMT_VAL64) { prefetch_span_l2(D.sl_va + off_n, 8 * e, lane); }
-         if (lane == 31) { prefetch_span_l2(D.c_base + (off_n >> 5), e >> 3, 0); }
-      }
       const int b[4] = { b4.x, b4.y, b4.z, b4.w };
       int    col[4];
       double v[4], xv[4];
@@ -222,60 +204,6 @@ __device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, 
    return t;
 }
 
-// Round-2 candidate (loop variant 4, CFMT_VAL8 only; opt-in through B200_SELLC_PIPE=4 /
-// b200_set_compression(.., 4)): the dictionary (<= 256 doubles) is staged in shared memory once per block
-// and the escape test is one branch per chunk.  At 32 registers ptxas then issues the four gathers of a
-// chunk back to back (one L2 round trip per chunk instead of four, scripts/sass_probe/README.md) and
-// predicates the DFMAs.  Same products, same order.
-template <class XF>
-__device__ __forceinline__ double rowsum_sellc_sd(const MatView &D, long long off, int n_chunks, int lane,
-                                                  const double *__restrict__ x, const XF &xf,
-                                                  const double *s_dict)
-{
-   const unsigned short *ip = D.c_idx + off + lane * 4;
-   const unsigned char *cp = (const unsigned char *)D.c_code + off + lane * 4;
-   const int4 *bp = reinterpret_cast<const int4 *>(D.c_base + (off >> 5));
-   double t = 0.0;
-   for (int c = 0; c < n_chunks; c++)
-   {
-      const unsigned long long id = ld_stream_u64(ip + c * 128);
-      const unsigned code = ld_stream_u32(cp + c * 128);
-      const int4 b4 = __ldg(bp + c);
-      int col[4] = { b4.x + (int)((unsigned)id & 0xFFFFu), b4.y + (int)((unsigned)(id >> 16) & 0xFFFFu),
-                     b4.z + (int)((unsigned)(id >> 32) & 0xFFFFu), b4.w + (int)(unsigned)(id >> 48) };
-      if ((b4.x | b4.y | b4.z | b4.w) < 0)       // CFMT_ESC has the sign bit: some entry keeps 32-bit columns
-      {
-         const int *e = D.sl_ci + off + (c * 4) * 32 + lane;
-         if (b4.x < 0) { col[0] = ld_stream(e); }
-         if (b4.y < 0) { col[1] = ld_stream(e + 32); }
-         if (b4.z < 0) { col[2] = ld_stream(e + 64); }
-         if (b4.w < 0) { col[3] = ld_stream(e + 96); }
-      }
-      double xv[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         const bool live = ((unsigned)(id >> (16 * j)) & 0xFFFFu) != CFMT_PAD;
-         xv[j] = live ? xf.xval(x, col[j]) : 0.0;
-      }
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         const bool live = ((unsigned)(id >> (16 * j)) & 0xFFFFu) != CFMT_PAD;
-         const double v = s_dict[(code >> (8 * j)) & 0xFFu];
-         if (live) { t = fma(v, xv[j], t); }
-      }
-   }
-   return t;
-}
-
-// Round-2 candidate (loop variant 5; needs storage packed without CFMT_PAD lanes, DMat::zpad, i.e.
-// b200_set_compression(.., 5) BEFORE the upload): no predicate anywhere in the chunk.  Padding lanes gather
-// a valid column and multiply it by a dictionary entry 0.0 -- what rowsum_sell does in the plain layout --
-// so a chunk is 3 stream loads, 4 gathers, 4 dictionary reads (shared memory for u8 codes) and 4 DFMAs:
-// about half the instructions of rowsum_sellc, whose issue slots are 55 % busy
-// (profiles/r01_ncu_full_rows_kernel_compressed.txt).  Row sums equal rowsum_sellc's except that a sum of
-// exactly -0.0 becomes +0.0 and a non-finite x in the padded column reaches the row.
 template <int VF, class XF>
 __device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off, int n_chunks, int lane,
                                                  const double *__restrict__ x, const XF &xf,
@@ -317,6 +245,45 @@ __device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off
          if (VF == CFMT_VAL16) { v[j] = __ldg(D.c_dict + ((unsigned)(code >> (16 * j)) & 0xFFFFu)); }
          t = fma(v[j], xv[j], t);
       }
+   }
+   return t;
+}
+
+// Pattern storage (DMat::cfmt == CFMT_PAT8): stencil operators and their first Galerkin products have a
+// handful of distinct (column - row, value) pairs ("patterns": 7 for the 7-pt Laplacian, 151 on level 1 of
+// its HMIS hierarchy), so an entry is ONE byte -- the index of its pattern in a dictionary of <= 254
+// (value, delta) pairs kept in shared memory -- and where all 32 rows of a slice have the same pattern in
+// their k-th entry (interior of a stencil) not even that: the byte sits once in the slice header.  Stream of
+// a slice (16-byte aligned, byte offset in sl_off): word 0 = number of header words, then one header word
+// per 4 entries (a pattern code per entry, PAT_LANE = "differs between lanes"), then -- at the next 16-byte
+// boundary -- 32 lane words for every header word that contains PAT_LANE (the lane's codes at the byte
+// positions of the marked entries).  Padding entries are patterns (delta of the row's own last entry, 0.0):
+// no predicate anywhere.  Level 0 of a stencil problem then streams little more than x and y.
+constexpr unsigned PAT_LANE = 0xFFu;
+template <class XF>
+__device__ __forceinline__ double rowsum_pat(const MatView &D, long long off_bytes, int lane, int row,
+                                             const double *__restrict__ x, const XF &xf, const double2 *s_pat)
+{
+   const unsigned *w = reinterpret_cast<const unsigned *>((const unsigned char *)D.c_code + off_bytes);
+   const unsigned nw = __ldg(w) & 0xFFu;
+   const unsigned *hp = w + 1;
+   const unsigned *lp = w + ((nw + 4) & ~3u) + lane;
+   double t = 0.0;
+   for (unsigned i = 0; i < nw; i++)
+   {
+      unsigned h = __ldg(hp + i);
+      const unsigned m = __vcmpeq4(h, 0xFFFFFFFFu);          // 0xFF in the bytes marked PAT_LANE (warp-uniform)
+      if (m) { const unsigned lw = ld_stream_u32(lp); lp += 32; h = (lw & m) | (h & ~m); }
+      double v[4], xv[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+      {
+         const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
+         v[j] = pd.x;
+         xv[j] = xf.xval(x, row + __double2loint(pd.y));
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { t = fma(v[j], xv[j], t); }
    }
    return t;
 }
@@ -378,6 +345,7 @@ struct HaloArgs {
                          // 2 no waiting, 4 no flow control / acknowledgements, 8 no system fences in the put
    int         int_begin, int_end;   // FWD/REV: longest run of 32-row groups that need no remote data
    const unsigned char *grp;   // FWD/REV: [ceil(n_rows/32)] non-zero if a row of that 32-row group needs remote data
+   int         chunked;  // thread-per-row layouts: contiguous run of slices per block instead of a grid stride
 };
 
 // sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks)
@@ -451,54 +419,57 @@ __device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const
    return ch.in_buf[par];
 }
 
-// Row groups [g_begin, g_end) (a group = 32 consecutive rows = one slice of the sliced-ELL layout) of
-// the diag block, grid-strided over the whole grid.  T == 0: sliced ELL thread-per-row; T < 0: compressed
-// sliced ELL, value format (-T) & 3, pipelining variant (-T) >> 2; T > 0: CSR with T lanes per row.  HALO as above; HALO_NONE / HALO_SKIP never touch the channel.
+// Row groups [g_begin, g_end) (a group = 32 consecutive rows = one slice of the sliced-ELL layouts) of the
+// diag block.  T == 0: sliced ELL thread-per-row; T < 0: compressed thread-per-row storage, format
+// (-T) & 7 (CFMT_*), variant (-T) >> 3 (VAL*: 1 = storage without padding markers, rowsum_sellc_z; PAT8:
+// 1 = the instantiation with more registers per thread); T > 0: CSR with T lanes per row.
+// HALO as above; HALO_NONE / HALO_SKIP never touch the channel.
+// Thread-per-row mapping: h.chunked != 0 gives every block ONE contiguous run of slices (its warps walk it
+// 8 slices at a time), so that the gathers of neighbouring rows -- the +-nx lines of a stencil -- meet in the
+// SM's L1 instead of each costing an L2 read; 0 = grid stride.
 template <int T, int HALO, class Epi>
 __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
                                            const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
-                                           int vblock, const double *s_dict = nullptr)
+                                           int vblock, const double2 *s_tab = nullptr)
 {
-   // vblock: the block's position in this range's grid stride (a permutation of blockIdx.x), so that
+   // vblock: the block's position in this range's grid (a permutation of blockIdx.x), so that
    // short ranges do not all land on the low-numbered blocks, which also carry the put phase
    if (T <= 0)
    {
-      constexpr int VF   = T < 0 ? ((-T) & 3) : CFMT_VAL64;   // T = -(CFMT_* + 4 PIPE): compressed storage
-      // 0 plain, 1 slice offsets one trip ahead, 2 + L2 prefetch, 3 = 2 at 40 registers / 6 blocks per SM,
-      // 4 = plain loop with the dictionary in shared memory (rowsum_sellc_sd)
-      constexpr int PIPE_RAW = T < 0 ? ((-T) >> 2) : 0;
-      // 5 = predicate-free loop on storage without padding markers (rowsum_sellc_z)
-      constexpr bool SMEM_DICT = PIPE_RAW == 4;
-      constexpr bool ZPAD = PIPE_RAW == 5;
-      constexpr int PIPE = (SMEM_DICT || ZPAD) ? 0 : PIPE_RAW;
+      constexpr int FMT  = T < 0 ? ((-T) & 7) : 0;
+      constexpr bool ZPAD = T < 0 && FMT != CFMT_PAT8 && ((-T) >> 3) == 1;
       const int lane = threadIdx.x & 31;
       const int wpb = ROWK_BLOCK / 32;
-      const int stride = gridDim.x * wpb;
-      int slice = g_begin + vblock * wpb + (threadIdx.x >> 5);
-      long long off = 0;
-      int nch = 0;
-      if (PIPE >= 1 && slice < g_end) { off = D.sl_off[slice]; nch = (int)((D.sl_off[slice + 1] - off) >> 7); }
-      for (; slice < g_end; slice += stride)
+      int slice, s_end, step;
+      if (h.chunked)
       {
-         // the offsets of the warp's next slice travel while this one is processed: the chain
-         // offset -> matrix stream -> gather loses its first link
-         long long off_n = 0;
-         int nch_n = 0;
-         if (PIPE >= 1 && slice + stride < g_end)
-         {
-            off_n = D.sl_off[slice + stride];
-            nch_n = (int)((D.sl_off[slice + stride + 1] - off_n) >> 7);
-         }
-         if (T < 0 && PIPE == 0) { off = D.sl_off[slice]; nch = (int)((D.sl_off[slice + 1] - off) >> 7); }
+         const int per_block = ((g_end - g_begin + (int)gridDim.x * wpb - 1) / ((int)gridDim.x * wpb)) * wpb;
+         slice = g_begin + vblock * per_block;
+         s_end = slice + per_block < g_end ? slice + per_block : g_end;
+         slice += (threadIdx.x >> 5);
+         step = wpb;
+      }
+      else
+      {
+         slice = g_begin + vblock * wpb + (threadIdx.x >> 5);
+         s_end = g_end;
+         step = gridDim.x * wpb;
+      }
+      for (; slice < s_end; slice += step)
+      {
          int row = (slice << 5) + lane;
          if (D.perm != nullptr) { row = ((slice >> 3) << 8) + D.perm[row]; }   // sorted inside 256-row windows
          const bool live = row < D.n_rows;
-         if (PIPE >= 2 && live) { epi.prefetch(row); }     // the epilogue's own vectors: in L2 by the time the row sum is done
-         double t = (T == 0) ? rowsum_sell(D, slice, lane, x, epi)
-                    : SMEM_DICT ? rowsum_sellc_sd(D, off, nch, lane, x, epi, s_dict)
-                    : ZPAD ? rowsum_sellc_z<VF>(D, off, nch, lane, x, epi, s_dict)
-                                : rowsum_sellc<VF, PIPE>(D, off, nch, lane, x, epi, off_n, nch_n);
-         off = off_n; nch = nch_n;
+         double t;
+         if (T == 0) { t = rowsum_sell(D, slice, lane, x, epi); }
+         else if (FMT == CFMT_PAT8) { t = rowsum_pat(D, D.sl_off[slice], lane, live ? row : D.n_rows - 1, x, epi, s_tab); }
+         else
+         {
+            const long long off = D.sl_off[slice];
+            const int nch = (int)((D.sl_off[slice + 1] - off) >> 7);
+            t = ZPAD ? rowsum_sellc_z<FMT>(D, off, nch, lane, x, epi, reinterpret_cast<const double *>(s_tab))
+                     : rowsum_sellc<FMT>(D, off, nch, lane, x, epi);
+         }
          bool skip = false;
          if (HALO == HALO_SKIP) { skip = live && h.O.rp[row + 1] != h.O.rp[row]; }
          if (HALO == HALO_FWD && h.grp[slice])
@@ -555,10 +526,19 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
    }
 }
 
-// All rows of the diag block.  8 resident blocks per SM (32 registers): occupancy is what hides the
-// DRAM latency of this streaming kernel.
+// resident blocks per SM: 8 x 256 threads at 32 registers hide the DRAM latency of the streaming kernels;
+// the second PAT8 instantiation trades occupancy for registers (the four gathers of a header word in flight)
+template <int T> struct RowsKernelCfg {
+   static constexpr int FMT = T < 0 ? ((-T) & 7) : 0;
+   static constexpr int VAR = T < 0 ? ((-T) >> 3) : 0;
+   static constexpr bool PAT = FMT == CFMT_PAT8;
+   static constexpr bool SMEM_TAB = PAT || (VAR == 1 && FMT == CFMT_VAL8);
+   static constexpr int MIN_BLOCKS = (PAT && VAR == 1) ? 5 : 8;
+};
+
+// All rows of the diag block.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK, (T <= -12 && T > -16) ? 6 : 8)
+__global__ void __launch_bounds__(ROWK_BLOCK, RowsKernelCfg<T>::MIN_BLOCKS)
 rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
@@ -567,30 +547,35 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
 
    constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
-   constexpr bool SMEM_DICT = (T == -(CFMT_VAL8 + 16) || T == -(CFMT_VAL8 + 20));
-   __shared__ double s_dict[SMEM_DICT ? 256 : 1];
-   if (SMEM_DICT)
+   using Cfg = RowsKernelCfg<T>;
+   // pattern dictionary (value, delta) / u8 value dictionary, staged once per block
+   __shared__ double2 s_tab[Cfg::SMEM_TAB ? 256 : 1];
+   if (Cfg::SMEM_TAB)
    {
-      if ((int)threadIdx.x < D.n_dict) { s_dict[threadIdx.x] = D.c_dict[threadIdx.x]; }
+      if (Cfg::PAT) { if ((int)threadIdx.x < D.n_dict) { s_tab[threadIdx.x] = reinterpret_cast<const double2 *>(D.c_dict)[threadIdx.x]; } }
+      else if ((int)threadIdx.x < D.n_dict) { reinterpret_cast<double *>(s_tab)[threadIdx.x] = D.c_dict[threadIdx.x]; }
       __syncthreads();
    }
    const int n_groups = (D.n_rows + 31) >> 5;
    const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
-   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, s_dict); }
+   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, s_tab); }
    else
    {
       if (h.ch.n_out > 0)
       {
+         // the put blocks must all be co-resident with the blocks that spin on the peers' flags (the peer is
+         // in the same state): at most one wave of the smallest residency, the pack is grid-strided
          int n_put_blocks = (h.ch.n_out_total + ROWK_BLOCK - 1) / ROWK_BLOCK;
+         if (n_put_blocks > B200_NUM_SMS * 4) { n_put_blocks = B200_NUM_SMS * 4; }
          if (n_put_blocks > (int)gridDim.x) { n_put_blocks = gridDim.x; }
          if ((int)blockIdx.x < n_put_blocks) { halo_put_phase<HALO>(h, x, n_put_blocks, epi); }
       }
       // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
       // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
       const int G = gridDim.x, b = blockIdx.x;
-      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, s_dict);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, s_dict);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, s_dict);
+      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, s_tab);
    }
    grid_reduce<Epi::NRED>(red, rc);
    if (P2P && h.ch.n_in > 0 && !(h.dbg & 4)) { p2p_consumer_done(h.ch); }

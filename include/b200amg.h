@@ -98,21 +98,27 @@ int b200_parcsr_destroy(b200_parcsr *A);
 int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *nnz,
                      int *layout /* 0 = CSR-vector, 1 = sliced-ELL, 2 = sliced-ELL with rows sorted in 256-row windows */, int *lanes_per_row);
 /* Storage of the diag block.  Thread-per-row layouts (1, 2) are held compressed when that reads fewer
- * bytes: 16-bit column offsets from a base per (slice, entry) and -- for blocks with at most 256 / 65536
- * distinct values -- 8 / 16-bit codes into a value dictionary (lossless; same products, same order).
- * value_format: 0 plain (int32 column + fp64 value), 1 dictionary u8, 2 dictionary u16, 3 fp64 values with
- * 16-bit columns.  stored_bytes = matrix bytes one pass reads; csr_bytes = 12 nnz + 4 (n+1), what the
- * reference's CSR (seq_mv/csr_matrix.h) would read. */
+ * bytes (lossless; same products, same order as the CSR row of seq_mv/csr_matvec.c):
+ *   value_format 4  pattern storage: one byte per entry = index of its (column - row, value) pair in a
+ *                   dictionary of <= 254 pairs, and nothing per entry where the 32 rows of a slice share the
+ *                   pattern (stencil operators and their first Galerkin products);
+ *   value_format 1/2  16-bit column offsets from a base per (slice, entry) + 8 / 16-bit codes into a value
+ *                   dictionary (<= 256 / 65536 distinct values);  3  16-bit columns + fp64 values;
+ *   value_format 0  plain (int32 column + fp64 value).
+ * stored_bytes = matrix bytes one pass reads; csr_bytes = 12 nnz + 4 (n+1), what the reference's CSR
+ * (seq_mv/csr_matrix.h) would read. */
 int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stored_bytes,
                         long long *csr_bytes, int *n_dictionary);
 /* mode: -1 automatic (default; environment B200_COMPRESS=0 disables), 0 off, 1/2/3 force that value
- * format where the dictionary allows it (tests/bench).  pipeline: 0 plain loop (default, fastest measured),
- * 1 slice offsets loaded one trip ahead, 2 additionally L2 prefetch of the next slice's streams, 3 = 2 at
- * 6 blocks per SM, 4 = plain loop with the value dictionary staged in shared memory (u8 codes only; a
- * round-2 candidate, see scripts/sass_probe/), 5 = predicate-free loop: set BEFORE the upload, the block is then
- * packed without padding markers (padding = valid column x dictionary entry 0.0, as in the plain sliced-ELL
- * layout); -1 leaves it (environment B200_SELLC_PIPE). */
-int b200_set_compression(int mode, int pipeline);
+ * format where the dictionary allows it, 4 the pattern storage where the block qualifies (tests/bench).
+ * no_padding_markers (formats 1-3; set BEFORE the upload): 1 packs padding lanes as (own column) x
+ * (dictionary entry 0.0) instead of a marker, which gives a predicate-free loop; 0 markers; -1 leaves it
+ * (environment B200_ZPAD). */
+int b200_set_compression(int mode, int no_padding_markers);
+/* launch options of the thread-per-row kernels (A/B measurements): chunked 1 = every block walks one
+ * contiguous run of 32-row slices (default; neighbouring rows meet in L1), 0 = grid stride; pat_regs 1 =
+ * the pattern kernel instantiated at 48 registers / 5 blocks per SM instead of 32 / 8; -1 leaves a value. */
+int b200_set_kernel_options(int chunked, int pat_regs);
 /* Test hook for the storage formats (host only, no device needed, never on a solve path): packs the CSR
  * block with the current layout / compression settings exactly as b200_parcsr_create would and computes
  * y = A x on the host FROM THE PACKED ARRAYS with the kernels' addressing (same fma chain per row). */

@@ -21,18 +21,18 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--layout", type=int, default=-1)
     ap.add_argument("--lanes", type=int, default=-1)
-    ap.add_argument("--compress", type=int, default=-1, help="b200_set_compression mode (-1 auto, 0 off, 1..3)")
-    ap.add_argument("--pipe", type=int, default=-1, help="pipelining variant of the compressed kernels (0..3)")
+    ap.add_argument("--compress", type=int, default=-1, help="b200_set_compression mode (-1 auto, 0 off, 1..3 value formats, 4 patterns)")
+    ap.add_argument("--zpad", type=int, default=-1, help="1: value formats packed without padding markers")
     a = ap.parse_args()
     L = capi.lib()
     capi.check(L.b200_set_layout_override(a.layout, a.lanes))
-    capi.check(L.b200_set_compression(a.compress, a.pipe))
-    print(json.dumps(measure(a.gen, a.n, a.reps, a.pipe)))
+    capi.check(L.b200_set_compression(a.compress, a.zpad))
+    print(json.dumps(measure(a.gen, a.n, a.reps)))
 
 
-def measure(gen, size, reps, pipe=-1):
+def measure(gen, size, reps):
     """level-0 operators of one generated stencil matrix: ms, CSR-equivalent GB/s, bytes (bench.py's aux leg too)"""
-    a = argparse.Namespace(gen=gen, n=size, reps=reps, pipe=pipe)
+    a = argparse.Namespace(gen=gen, n=size, reps=reps)
     L = capi.lib()
     HL = H.lib()
     ctx = C.c_void_p(HL.hypre_b200_context())
@@ -62,7 +62,7 @@ def measure(gen, size, reps, pipe=-1):
     vfmt = C.c_int(); st_b = C.c_longlong(); csr_b = C.c_longlong(); ndict = C.c_int()
     capi.check(L.b200_parcsr_storage(dA, C.byref(vfmt), C.byref(st_b), C.byref(csr_b), C.byref(ndict)))
     out = {"gen": a.gen, "n": a.n, "rows": n, "nnz": nnz, "layout": layout.value, "lanes": lanes.value,
-           "value_format": vfmt.value, "pipe": a.pipe, "matrix_stored_MB": st_b.value / 1e6,
+           "value_format": vfmt.value, "matrix_stored_MB": st_b.value / 1e6,
            "matrix_csr_MB": csr_b.value / 1e6, "note": "GB/s count the CSR (algorithmic) bytes"}
     out["spmv"] = timed(lambda: capi.check(L.b200_parcsr_matvec(dA, 1.0, v[0].ptr, 0.0, None, v[1].ptr)),
                         spmv + 16.0 * n)

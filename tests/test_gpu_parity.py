@@ -176,8 +176,8 @@ def _random_matrices():
 
 def _compression_matrices(H, hier):
     amg = hier[3]
-    yield "lap7", H.laplacian(19, 17, 13).blocks()[0], 1            # 2 distinct values -> u8 codes
-    yield "lap27", H.laplacian_27pt(14, 12, 11).blocks()[0], 1
+    yield "lap7", H.laplacian(19, 17, 13).blocks()[0], 4            # 7 (delta, value) patterns -> pattern storage
+    yield "lap27", H.laplacian_27pt(14, 12, 11).blocks()[0], 4
     yield "A1", amg.A(1).blocks()[0], None
     yield "P0", amg.P(0).blocks()[0], None
     A, B, Cm = _random_matrices()
@@ -186,22 +186,22 @@ def _compression_matrices(H, hier):
     yield "random_u8", Cm, 1
 
 
-# loop variants 4 (dictionary in shared memory) and 5 (storage without padding markers) are round-2 candidates:
-# opt-in (B200_TEST_CANDIDATES=1) until they have been through a GPU run of this file
-_CANDIDATES = pytest.mark.skipif(os.environ.get("B200_TEST_CANDIDATES", "0") != "1",
-                                 reason="candidate kernels: set B200_TEST_CANDIDATES=1")
-_CAND = [pytest.param(m, p, marks=_CANDIDATES) for m, p in [(-1, 4), (1, 4), (-1, 5), (1, 5), (2, 5), (3, 5)]]
+# (mode, no_padding_markers, chunked, pat_regs): every storage format in both padding forms, the pattern kernel in
+# both instantiations, both slice-to-block mappings
+_FORMATS = [(-1, 0, 1, 0), (0, 0, 1, 0), (1, 0, 1, 0), (2, 0, 1, 0), (3, 0, 1, 0), (4, 0, 1, 0), (4, 0, 0, 1), (4, 0, 1, 1),
+            (-1, 1, 1, 0), (1, 1, 0, 0), (2, 1, 1, 0), (3, 1, 1, 0), (1, 0, 0, 0)]
 
 
 @pytest.mark.parametrize("layout", [1, 2])
-@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (0, 0), (1, 2), (2, 2), (2, 0), (3, 2), (3, 1), (3, 3)] + _CAND)
-def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
+@pytest.mark.parametrize("mode,zpad,chunked,pat_regs", _FORMATS)
+def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, zpad, chunked, pat_regs):
     """16-bit column offsets + value dictionary (b200_parcsr_storage): same products, same order as
     the CSR row of the reference (seq_mv/csr_matvec.c:21-857) -> SpMV parity <= 1e-12 in every format."""
     L = capi.lib()
     rng = np.random.default_rng(15)
     capi.check(L.b200_set_layout_override(layout, -1))
-    capi.check(L.b200_set_compression(mode, pipe))
+    capi.check(L.b200_set_compression(mode, zpad))
+    capi.check(L.b200_set_kernel_options(chunked, pat_regs))
     try:
         for nm, A, auto_fmt in _compression_matrices(H, hier):
             n, m = A.shape
@@ -209,19 +209,29 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
             fmt, stored, csr, nd = _storage(L, dA)
             if mode == 0:
                 assert fmt == 0
-            elif mode == -1:
-                assert fmt in (0, 1, 2, 3)
+            elif mode in (-1, 4):
+                assert fmt in (0, 1, 2, 3, 4)
                 if fmt and auto_fmt:
                     assert fmt == auto_fmt, (nm, fmt)
+                if nm == "A1":
+                    assert fmt == 4, fmt                       # first Galerkin product of a stencil: still patterns
                 if fmt and nm in ("lap7", "lap27", "A1"):      # regular rows: far fewer bytes than CSR
-                    assert stored < 0.5 * csr, (nm, stored, csr)
+                    assert stored < 0.2 * csr, (nm, stored, csr)
             else:
                 assert fmt in (mode, 3) or (mode == 2 and fmt == 2), (nm, mode, fmt)
             x = rng.standard_normal(m); b = rng.standard_normal(n)
             dx, db, dy = dvec(ctx, x), dvec(ctx, b), capi.DeviceVector(ctx, n)
             for alpha, beta in [(1.0, 0.0), (-1.0, 1.0)]:
                 capi.check(L.b200_parcsr_matvec(dA, alpha, dx.ptr, beta, db.ptr, dy.ptr))
-                assert row_err(dy.get(), O.matvec(A, alpha, x, beta, b), A, x) < SPMV_TOL, (nm, layout, mode, pipe, fmt)
+                assert row_err(dy.get(), O.matvec(A, alpha, x, beta, b), A, x) < SPMV_TOL, (nm, layout, mode, zpad, fmt)
+            # every format computes the CSR row's fma chain: bit-identical to the plain layout
+            dx.set(x)
+            capi.check(L.b200_parcsr_matvec(dA, 1.0, dx.ptr, 0.0, db.ptr, dy.ptr))
+            key = (nm, layout)
+            if key in _BITS:
+                assert np.array_equal(dy.get(), _BITS[key]), (nm, layout, mode, zpad, fmt)
+            else:
+                _BITS[key] = dy.get()
             # NaN in a column a row does not touch must not leak through padding lanes
             xn = x.copy(); cols = np.setdiff1d(np.arange(m), A.indices)
             if len(cols):
@@ -235,16 +245,21 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, pipe):
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 0)
+        L.b200_set_kernel_options(1, 0)
 
 
-@pytest.mark.parametrize("mode,pipe", [(-1, 2), (-1, 0), (-1, 1), (-1, 3), (3, 2), (2, 3)] + _CAND)
-def test_smoothers_on_compressed_storage(H, ctx, hier, mode, pipe):
+_BITS = {}      # SpMV result of the first format run on (matrix, layout): the others must reproduce it bit for bit
+
+
+@pytest.mark.parametrize("mode,zpad,chunked,pat_regs", [(-1, 0, 1, 0), (4, 0, 0, 1), (1, 0, 1, 0), (1, 1, 1, 0), (2, 1, 0, 0), (3, 0, 1, 0), (3, 1, 1, 0)])
+def test_smoothers_on_compressed_storage(H, ctx, hier, mode, zpad, chunked, pat_regs):
     """every fused epilogue on the compressed thread-per-row kernels against the oracle"""
     L = capi.lib()
     rng = np.random.default_rng(16)
     amg = hier[3]
     capi.check(L.b200_set_layout_override(1, -1))
-    capi.check(L.b200_set_compression(mode, pipe))
+    capi.check(L.b200_set_compression(mode, zpad))
+    capi.check(L.b200_set_kernel_options(chunked, pat_regs))
     try:
         for l in (0, 1):
             A = amg.A(l).blocks()[0]
@@ -274,6 +289,7 @@ def test_smoothers_on_compressed_storage(H, ctx, hier, mode, pipe):
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 0)
+        L.b200_set_kernel_options(1, 0)
 
 
 def vec_err_max(a, b):
