@@ -419,8 +419,9 @@ def run_b200(args, rank, world):
                      "stored_bytes": spmv_stored, "stored_gbs": spmv_stored / (spmv_ms * 1e-3) / 1e9,
                      "stored_frac": spmv_stored / (spmv_ms * 1e-3) / 1e9 / peak,
                      "storage": {0: "int32 column + fp64 value", 1: "u16 column offset + u8 dictionary code",
-                                 2: "u16 column offset + u16 dictionary code", 3: "u16 column offset + fp64 value"}[vfmt.value]
-                                + (" (%d distinct values)" % ndict.value if vfmt.value in (1, 2) else ""),
+                                 2: "u16 column offset + u16 dictionary code", 3: "u16 column offset + fp64 value",
+                                 4: "u8 (column - row, value) pattern code, lane-uniform entries once per 32-row slice"}[vfmt.value]
+                                + (" (%d distinct %s)" % (ndict.value, "patterns" if vfmt.value == 4 else "values") if vfmt.value in (1, 2, 4) else ""),
                      "note": "achieved/frac count the reference's CSR bytes (SURVEY 8d); stored_* count the bytes the "
                              "compressed layout really reads, traffic is the ncu DRAM figure",
                      "peak_source": peak_src, "frac_of_8000": spmv_gbs / 8000.0, "ms_per_launch": spmv_ms,

@@ -163,6 +163,7 @@ struct DMat {
    int             n_dict = 0;
    long long       stored_bytes = 0;     // bytes one pass over the block reads from the matrix arrays
    int             zpad = 0;             // compressed storage without CFMT_PAD lanes (padding = valid column x value 0)
+   int             pat_stride = 0;       // CFMT_PAT8: 16-byte units per slice header (headers in c_code, lane words in c_idx)
 };
 
 // cfmt: value encoding of the compressed storage (column indices are always base + u16)
@@ -186,6 +187,7 @@ struct MatView {
    const void      *c_code;
    const double    *c_dict;
    int              n_dict;      // entries of c_dict (<= 256 for CFMT_VAL8)
+   int              aux;         // CFMT_PAT8: 16-byte units per slice header
 };
 
 static inline MatView view_of(const DMat &m)
@@ -193,7 +195,7 @@ static inline MatView view_of(const DMat &m)
    MatView v;
    v.n_rows = m.n_rows; v.rp = m.rp; v.ci = m.ci; v.va = m.va;
    v.sl_off = m.sl_off; v.sl_ci = m.sl_ci; v.sl_va = m.sl_va; v.perm = m.sl_perm;
-   v.c_idx = m.c_idx; v.c_base = m.c_base; v.c_code = m.c_code; v.c_dict = m.c_dict; v.n_dict = m.n_dict;
+   v.c_idx = m.c_idx; v.c_base = m.c_base; v.c_code = m.c_code; v.c_dict = m.c_dict; v.n_dict = m.n_dict; v.aux = m.pat_stride;
    return v;
 }
 
@@ -271,7 +273,9 @@ struct PackedDMat {
    std::vector<int>            base;        // [padded/32]
    std::vector<unsigned char>  code;        // chunk-transposed value codes (u8, or u16 as byte pairs)
    std::vector<double>         dict;        // value dictionary; CFMT_PAT8: (value, delta bits) pairs
-   std::vector<unsigned char>  pat;         // CFMT_PAT8: the slice streams (sl_off = byte offsets)
+   std::vector<unsigned char>  pat;         // CFMT_PAT8: slice headers, pat_stride x 16 bytes each
+   std::vector<unsigned>       pat_lanes;   // CFMT_PAT8: lane words (32 per header word that differs between lanes)
+   int                         pat_stride = 0;
 };
 void dmat_pack(const HostCsr &h, int allow_sell, PackedDMat *P);
 int  packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, double *y);

@@ -75,10 +75,18 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
    B200_TRY(dev_upload(&m->sl_ci, P.sci.data(), P.sci.size()));
    B200_TRY(dev_upload(&m->sl_va, P.sva.data(), P.sva.size()));
    B200_TRY(dev_upload(&m->sl_perm, P.perm.data(), P.perm.size()));
-   B200_TRY(dev_upload(&m->c_idx, P.idx.data(), P.idx.size()));
+   if (P.cfmt != CFMT_PAT8) { B200_TRY(dev_upload(&m->c_idx, P.idx.data(), P.idx.size())); }
    B200_TRY(dev_upload(&m->c_base, P.base.data(), P.base.size()));
    unsigned char *d_code = nullptr;
-   if (P.cfmt == CFMT_PAT8) { B200_TRY(dev_upload(&d_code, P.pat.data(), P.pat.size())); m->n_dict = (int)(P.dict.size() / 2); }
+   if (P.cfmt == CFMT_PAT8)
+   {
+      B200_TRY(dev_upload(&d_code, P.pat.data(), P.pat.size()));
+      unsigned *d_lanes = nullptr;
+      B200_TRY(dev_upload(&d_lanes, P.pat_lanes.data(), P.pat_lanes.size()));
+      m->c_idx = reinterpret_cast<unsigned short *>(d_lanes);      // lane words live in the c_idx slot
+      m->n_dict = (int)(P.dict.size() / 2);
+      m->pat_stride = P.pat_stride;
+   }
    else { B200_TRY(dev_upload(&d_code, P.code.data(), P.code.size())); }
    m->c_code = d_code;
    B200_TRY(dev_upload(&m->c_dict, P.dict.data(), P.dict.size()));

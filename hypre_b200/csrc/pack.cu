@@ -25,7 +25,7 @@ static int g_compress = env_int("B200_COMPRESS", -1);
 // VAL* storage without padding markers (rowsum_sellc_z): B200_ZPAD
 static int g_zpad = env_int("B200_ZPAD", 0) != 0;
 // launch options of the thread-per-row kernels (rowlaunch.cuh)
-int g_rows_chunked = env_int("B200_CHUNKED", 1) != 0;
+int g_rows_chunked = env_int("B200_CHUNKED", 1);
 int g_pat_regs = env_int("B200_PAT_REGS", 0) != 0;
 
 extern "C" int b200_set_compression(int mode, int no_padding_markers)
@@ -39,7 +39,7 @@ extern "C" int b200_set_compression(int mode, int no_padding_markers)
 
 extern "C" int b200_set_kernel_options(int chunked, int pat_regs)
 {
-   ARG_CHECK(chunked >= -1 && chunked <= 1 && pat_regs >= -1 && pat_regs <= 1);
+   ARG_CHECK(chunked >= -1 && chunked <= 2 && pat_regs >= -1 && pat_regs <= 1);   // chunked 2: also the VAL* / plain kernels
    if (chunked >= 0) { g_rows_chunked = chunked; }
    if (pat_regs >= 0) { g_pat_regs = pat_regs; }
    return B200_OK;
@@ -222,18 +222,24 @@ static bool pack_patterns(const HostCsr &h, const std::vector<int> *order, int n
          }
          lane_words += mixed;
       }
-      bytes[(size_t)s + 1] = ((4 + 4 * (long long)(w / 4) + 15) & ~15LL) + 128LL * lane_words;
+      bytes[(size_t)s + 1] = lane_words;       // 32-lane-word groups of this slice
    }
    for (int s = 0; s < n_slices; s++) { bytes[(size_t)s + 1] += bytes[(size_t)s]; }
-   P->pat.assign((size_t)bytes[(size_t)n_slices], 0);
+   if (bytes[(size_t)n_slices] >= (1LL << 24)) { return false; }     // the group offset has 24 bits in word 0
+   int nw_max = 0;
+   for (int s = 0; s < n_slices; s++) { nw_max = std::max(nw_max, w4[(size_t)s] / 4); }
+   const int stride16 = (4 + 4 * nw_max + 15) / 16;                   // 16-byte units per slice header
+   P->pat_stride = stride16;
+   P->pat.assign((size_t)n_slices * 16 * (size_t)stride16, 0);
+   P->pat_lanes.assign((size_t)bytes[(size_t)n_slices] * 32, 0u);
 #pragma omp parallel for schedule(static)
    for (int s = 0; s < n_slices; s++)
    {
       const unsigned char *cs = codes.data() + coff[(size_t)s];
       const int nw = w4[(size_t)s] / 4;
-      unsigned *w0 = reinterpret_cast<unsigned *>(P->pat.data() + bytes[(size_t)s]);
-      unsigned *lanew = w0 + ((nw + 4) & ~3);
-      w0[0] = (unsigned)nw;
+      unsigned *w0 = reinterpret_cast<unsigned *>(P->pat.data() + (size_t)s * 16 * (size_t)stride16);
+      unsigned *lanew = P->pat_lanes.data() + (size_t)bytes[(size_t)s] * 32;
+      w0[0] = (unsigned)nw | ((unsigned)bytes[(size_t)s] << 8);
       for (int i = 0; i < nw; i++)
       {
          unsigned hw = 0, mixed_any = 0;
@@ -265,10 +271,10 @@ static bool pack_patterns(const HostCsr &h, const std::vector<int> *order, int n
       const long long dl = (long long)(unsigned)dict.deltas[k];       // delta in the low word of the second double
       memcpy(&P->dict[2 * k + 1], &dl, 8);
    }
-   P->sl_off.swap(bytes);
+   P->sl_off.clear();
    P->cfmt = CFMT_PAT8;
    P->padded = coff[(size_t)n_slices];
-   P->stored_bytes = (long long)P->pat.size() + 8 * (long long)n_slices + 16 * (long long)dict.deltas.size();
+   P->stored_bytes = (long long)P->pat.size() + 4 * (long long)P->pat_lanes.size() + 16 * (long long)dict.deltas.size();
    return true;
 }
 
@@ -573,8 +579,8 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
    }
    for (int slice = 0; slice < P.n_slices; slice++)
    {
-      const long long off = P.sl_off[(size_t)slice];
-      const long long span = P.sl_off[(size_t)slice + 1] - off;
+      const long long off = P.cfmt == CFMT_PAT8 ? 0 : P.sl_off[(size_t)slice];
+      const long long span = P.cfmt == CFMT_PAT8 ? 0 : P.sl_off[(size_t)slice + 1] - off;
       for (int lane = 0; lane < 32; lane++)
       {
          int row = slice * 32 + lane;
@@ -583,10 +589,11 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
          bool stray = false;      // a row beyond n_rows multiplied a non-zero value
          if (P.cfmt == CFMT_PAT8)
          {
-            // the addressing of rowsum_pat: header words, lane words at the next 16-byte boundary
-            const unsigned *w0 = reinterpret_cast<const unsigned *>(P.pat.data() + off);
+            // the addressing of rowsum_pat: fixed-stride header, lane words in their own stream
+            const unsigned *w0 = reinterpret_cast<const unsigned *>(P.pat.data() + (size_t)slice * 16 * (size_t)P.pat_stride);
             const unsigned nw = w0[0] & 0xFFu;
-            const unsigned *lp = w0 + ((nw + 4) & ~3u) + lane;
+            if (4 + 4 * (int)nw > 16 * P.pat_stride) { b200_set_error("pattern header wider than its stride"); return B200_ERR_ARG; }
+            const unsigned *lp = P.pat_lanes.data() + (size_t)(w0[0] >> 8) * 32 + lane;
             const int rowc = row < n ? row : n - 1;
             for (unsigned i = 0; i < nw; i++)
             {
@@ -594,7 +601,7 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
                for (int j = 0; j < 4; j++) { if (((hw >> (8 * j)) & 0xFFu) == 0xFFu) { m |= 0xFFu << (8 * j); } }
                if (m)
                {
-                  if ((const unsigned char *)(lp + 1) > P.pat.data() + P.sl_off[(size_t)slice + 1]) { b200_set_error("pattern stream overrun"); return B200_ERR_ARG; }
+                  if (lp >= P.pat_lanes.data() + P.pat_lanes.size()) { b200_set_error("pattern stream overrun"); return B200_ERR_ARG; }
                   hw = (*lp & m) | (hw & ~m); lp += 32;
                }
                for (int j = 0; j < 4; j++)

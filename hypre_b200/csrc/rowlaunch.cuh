@@ -51,7 +51,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    {
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
       HaloArgs hh = h;
-      hh.chunked = g_rows_chunked;
+      hh.chunked = D.cfmt == CFMT_PAT8 ? g_rows_chunked : (g_rows_chunked > 1);
       const int variant = D.cfmt == CFMT_PAT8 ? (g_pat_regs ? 1 : 0) : (D.zpad ? 1 : 0);
       switch (D.cfmt ? D.cfmt + 8 * variant : 0)
       {

@@ -253,38 +253,49 @@ __device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off
 // handful of distinct (column - row, value) pairs ("patterns": 7 for the 7-pt Laplacian, 151 on level 1 of
 // its HMIS hierarchy), so an entry is ONE byte -- the index of its pattern in a dictionary of <= 254
 // (value, delta) pairs kept in shared memory -- and where all 32 rows of a slice have the same pattern in
-// their k-th entry (interior of a stencil) not even that: the byte sits once in the slice header.  Stream of
-// a slice (16-byte aligned, byte offset in sl_off): word 0 = number of header words, then one header word
-// per 4 entries (a pattern code per entry, PAT_LANE = "differs between lanes"), then -- at the next 16-byte
-// boundary -- 32 lane words for every header word that contains PAT_LANE (the lane's codes at the byte
-// positions of the marked entries).  Padding entries are patterns (delta of the row's own last entry, 0.0):
-// no predicate anywhere.  Level 0 of a stencil problem then streams little more than x and y.
+// their k-th entry (interior of a stencil) not even that: the byte sits once in the slice header.
+// Slice s owns a header of D.aux x 16 bytes at a FIXED stride (no offset array, so the header of the warp's
+// next slice is requested while this one is processed and the chain header -> gather loses a link): word 0 =
+// number of header words | first lane-word group << 8, then one header word per 4 entries (a pattern code
+// per entry, PAT_LANE = "differs between lanes").  For every header word that contains PAT_LANE the lane
+// stream (c_idx slot) holds 32 lane words (the lane's codes at the byte positions of the marked entries).
+// Padding entries are patterns (delta of the row's own last entry, 0.0): no predicate anywhere.  Level 0 of a
+// stencil problem then streams little more than x and y.
 constexpr unsigned PAT_LANE = 0xFFu;
+
+// one header word = 4 entries
 template <class XF>
-__device__ __forceinline__ double rowsum_pat(const MatView &D, long long off_bytes, int lane, int row,
+__device__ __forceinline__ double pat_word(unsigned h, const unsigned *&lp, int row, double t,
+                                           const double *__restrict__ x, const XF &xf, const double2 *s_pat)
+{
+   const unsigned m = __vcmpeq4(h, 0xFFFFFFFFu);          // 0xFF in the bytes marked PAT_LANE (warp-uniform)
+   if (m) { const unsigned lw = ld_stream_u32(lp); lp += 32; h = (lw & m) | (h & ~m); }
+   double v[4], xv[4];
+#pragma unroll
+   for (int j = 0; j < 4; j++)
+   {
+      const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
+      v[j] = pd.x;
+      xv[j] = xf.xval(x, row + __double2loint(pd.y));
+   }
+#pragma unroll
+   for (int j = 0; j < 4; j++) { t = fma(v[j], xv[j], t); }
+   return t;
+}
+
+// h0 = the first 16 bytes of the slice header (already in registers), hdr = the header in memory
+template <class XF>
+__device__ __forceinline__ double rowsum_pat(const MatView &D, const uint4 &h0, const uint4 *hdr, int lane, int row,
                                              const double *__restrict__ x, const XF &xf, const double2 *s_pat)
 {
-   const unsigned *w = reinterpret_cast<const unsigned *>((const unsigned char *)D.c_code + off_bytes);
-   const unsigned nw = __ldg(w) & 0xFFu;
-   const unsigned *hp = w + 1;
-   const unsigned *lp = w + ((nw + 4) & ~3u) + lane;
+   const unsigned nw = h0.x & 0xFFu;
+   const unsigned *lp = reinterpret_cast<const unsigned *>(D.c_idx) + (size_t)(h0.x >> 8) * 32 + lane;
    double t = 0.0;
-   for (unsigned i = 0; i < nw; i++)
-   {
-      unsigned h = __ldg(hp + i);
-      const unsigned m = __vcmpeq4(h, 0xFFFFFFFFu);          // 0xFF in the bytes marked PAT_LANE (warp-uniform)
-      if (m) { const unsigned lw = ld_stream_u32(lp); lp += 32; h = (lw & m) | (h & ~m); }
-      double v[4], xv[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
-         v[j] = pd.x;
-         xv[j] = xf.xval(x, row + __double2loint(pd.y));
-      }
-#pragma unroll
-      for (int j = 0; j < 4; j++) { t = fma(v[j], xv[j], t); }
-   }
+   if (nw > 0) { t = pat_word(h0.y, lp, row, t, x, xf, s_pat); }
+   if (nw > 1) { t = pat_word(h0.z, lp, row, t, x, xf, s_pat); }
+   if (nw > 2) { t = pat_word(h0.w, lp, row, t, x, xf, s_pat); }
+   const unsigned *hw = reinterpret_cast<const unsigned *>(hdr) + 1;
+   for (unsigned i = 3; i < nw; i++) { t = pat_word(__ldg(hw + i), lp, row, t, x, xf, s_pat); }
    return t;
 }
 
@@ -455,6 +466,9 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          s_end = g_end;
          step = gridDim.x * wpb;
       }
+      const uint4 *hdr = reinterpret_cast<const uint4 *>(D.c_code);
+      uint4 h_cur = make_uint4(0u, 0u, 0u, 0u);
+      if (FMT == CFMT_PAT8 && slice < s_end) { h_cur = __ldg(hdr + (size_t)slice * D.aux); }
       for (; slice < s_end; slice += step)
       {
          int row = (slice << 5) + lane;
@@ -462,7 +476,14 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          const bool live = row < D.n_rows;
          double t;
          if (T == 0) { t = rowsum_sell(D, slice, lane, x, epi); }
-         else if (FMT == CFMT_PAT8) { t = rowsum_pat(D, D.sl_off[slice], lane, live ? row : D.n_rows - 1, x, epi, s_tab); }
+         else if (FMT == CFMT_PAT8)
+         {
+            // the header of the warp's next slice travels while this one is processed
+            uint4 h_next = make_uint4(0u, 0u, 0u, 0u);
+            if (slice + step < s_end) { h_next = __ldg(hdr + (size_t)(slice + step) * D.aux); }
+            t = rowsum_pat(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi, s_tab);
+            h_cur = h_next;
+         }
          else
          {
             const long long off = D.sl_off[slice];
@@ -533,7 +554,7 @@ template <int T> struct RowsKernelCfg {
    static constexpr int VAR = T < 0 ? ((-T) >> 3) : 0;
    static constexpr bool PAT = FMT == CFMT_PAT8;
    static constexpr bool SMEM_TAB = PAT || (VAR == 1 && FMT == CFMT_VAL8);
-   static constexpr int MIN_BLOCKS = (PAT && VAR == 1) ? 5 : 8;
+   static constexpr int MIN_BLOCKS = (PAT && VAR == 1) ? 6 : 8;
 };
 
 // All rows of the diag block.

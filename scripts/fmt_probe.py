@@ -20,7 +20,8 @@ from hypre_b200 import capi, hypre as H   # noqa: E402
 
 # name: (compression mode, no_padding_markers, [(chunked, pat_regs), ...] launch options timed on that upload)
 CONFIGS = {
-    "pat8": (-1, 0, [(1, 0), (0, 0), (1, 1), (0, 1)]),
+    "pat8": (-1, 0, [(1, 0), (0, 0), (1, 1)]),
+    "auto_zpad": (-1, 1, [(1, 0)]),
     "val_markers": (1, 0, [(1, 0), (0, 0)]),
     "val_zpad": (1, 1, [(1, 0), (0, 0)]),
     "plain": (0, 0, [(1, 0), (0, 0)]),
