@@ -23,7 +23,7 @@ static int g_lanes_override  = -1;
 static int env_int(const char *name, int dflt) { const char *e = getenv(name); return e ? atoi(e) : dflt; }
 static int g_compress = env_int("B200_COMPRESS", -1);
 // VAL* storage without padding markers (rowsum_sellc_z): B200_ZPAD
-static int g_zpad = env_int("B200_ZPAD", 0) != 0;
+static int g_zpad = env_int("B200_ZPAD", 1) != 0;
 // launch options of the thread-per-row kernels (rowlaunch.cuh)
 int g_rows_chunked = env_int("B200_CHUNKED", 1);
 int g_pat_regs = env_int("B200_PAT_REGS", 0) != 0;

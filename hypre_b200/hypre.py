@@ -12,9 +12,30 @@ import os
 
 import numpy as np
 
-from . import LIB_HYPRE_B200, LIB_HYPRE_B200_MP, capi
+from . import LIB_BRIDGE, LIB_BRIDGE_MP, LIB_HYPRE_B200, LIB_HYPRE_B200_MP, LIB_HYPRE_REF, capi
 
 _lib = None
+# Reference-only mode (bench.py --impl reference, the cpu_baseline leg): this process loads the oracle's separately
+# built reference library (oracle/_ref/libHYPRE_ref.so) and NOTHING of the product -- no libb200amg.so, no binding,
+# no product host library -- so that what is timed is the unmodified reference alone.  Device entry points do not
+# exist in this mode.
+REFERENCE_ONLY = os.environ.get("HYPRE_B200_REFERENCE_ONLY", "0") == "1"
+
+
+class _Libs:
+    """symbol lookup over the hypre library of this process and the accessor bridge (tests / bench plumbing)"""
+
+    def __init__(self, main, bridge):
+        self._main, self._bridge = main, bridge
+
+    def __getattr__(self, name):
+        try:
+            f = getattr(self._bridge if name.startswith("hb_") else self._main, name)
+        except AttributeError:
+            f = getattr(self._main if name.startswith("hb_") else self._bridge, name)
+        setattr(self, name, f)
+        return f
+
 COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h) and of oracle/mpishim
 # Native multi-rank mode (INTEGRATION.md section 4b): this process is one of N ranks (one per GPU), the
 # reference is its MPI build over oracle/mpishim and hypre's own distributed setup runs.  Ranks started by
@@ -26,18 +47,27 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    capi.lib()   # libb200amg.so first: fail loudly if the CUDA library is missing
-    path = LIB_HYPRE_B200_MP if NATIVE else LIB_HYPRE_B200
+    if REFERENCE_ONLY:
+        if NATIVE:
+            raise capi.B200Error("reference-only mode is single-rank")
+        path = LIB_HYPRE_REF
+    else:
+        capi.lib()   # libb200amg.so first: fail loudly if the CUDA library is missing
+        path = LIB_HYPRE_B200_MP if NATIVE else LIB_HYPRE_B200
     if not os.path.exists(path):
-        raise capi.B200Error("%s is missing (built from hypre_b200/host with the reference headers)" % path)
-    L = C.CDLL(path, mode=C.RTLD_GLOBAL)
+        raise capi.B200Error("%s is missing (built from hypre_b200/host or oracle/ with the reference sources)" % path)
+    main = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    bridge_path = LIB_BRIDGE_MP if NATIVE else LIB_BRIDGE
+    if not os.path.exists(bridge_path):
+        raise capi.B200Error("%s is missing (built from hypre_b200/host)" % bridge_path)
+    L = _Libs(main, C.CDLL(bridge_path, mode=C.RTLD_GLOBAL))
     if NATIVE:
         L.MPI_Init(None, None)
     vp, i, d = C.c_void_p, C.c_int, C.c_double
     for name in ("GenerateLaplacian", "GenerateLaplacian27pt", "GenerateRotate7pt", "hb_vector_create",
                  "hb_vector_create_cols", "hb_amg_A", "hb_amg_P", "hb_amg_F", "hb_amg_U", "hb_amg_Vtemp",
-                 "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_precond_data",
-                 "hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror"):
+                 "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_precond_data") + \
+            (() if REFERENCE_ONLY else ("hypre_b200_context", "hypre_b200_amg_mirror", "hypre_b200_matrix_mirror")):
         getattr(L, name).restype = vp
     for name in ("hb_vector_data", "hb_amg_l1", "hb_amg_cheby_ds", "hb_amg_cheby_coefs",
                  "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_lgmres_norms", "hb_bicgstab_norms"):
@@ -54,9 +84,8 @@ def lib():
                  "hb_amg_Ztemp", "hb_amg_Ptemp", "hb_amg_Rtemp", "hb_pcg_norms", "hb_pcg_rel_norms",
                  "hb_gmres_norms", "hb_cogmres_norms", "hb_bicgstab_norms", "hb_bicgstab_converged", "HYPRE_ParCSRGMRESDestroy",
                  "HYPRE_ParCSRCOGMRESDestroy", "hb_flexgmres_norms", "HYPRE_ParCSRFlexGMRESDestroy", "hb_lgmres_norms", "HYPRE_ParCSRLGMRESDestroy", "HYPRE_ParCSRBiCGSTABDestroy",
-                 "hb_pcg_precond_data", "hb_matrix_global_rows", "hypre_b200_amg_mirror",
-                 "hypre_b200_matrix_mirror", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
-                 "HYPRE_ParCSRPCGDestroy"):
+                 "hb_pcg_precond_data", "hb_matrix_global_rows", "HYPRE_ParCSRMatrixDestroy", "HYPRE_BoomerAMGDestroy",
+                 "HYPRE_ParCSRPCGDestroy") + (() if REFERENCE_ONLY else ("hypre_b200_amg_mirror", "hypre_b200_matrix_mirror")):
         getattr(L, name).argtypes = [vp]
     for name in ("hb_amg_A", "hb_amg_P", "hb_amg_F", "hb_amg_U", "hb_amg_l1", "hb_amg_cheby_ds",
                  "hb_amg_cheby_coefs", "hb_amg_relax_weight", "hb_amg_omega", "hb_vector_set_all_zeros"):
@@ -64,7 +93,8 @@ def lib():
     L.hb_amg_params.argtypes = [vp, vp]
     L.hb_amg_coarse_dense.argtypes = [vp, C.POINTER(i)]
     L.hb_matrix_blocks.argtypes = [vp] + [vp] * 9
-    L.hypre_b200_set_enabled.argtypes = [i]
+    if not REFERENCE_ONLY:
+        L.hypre_b200_set_enabled.argtypes = [i]
     L.HYPRE_ParCSRMatrixMatvec.argtypes = [d, vp, vp, d, vp]
     L.HYPRE_ParCSRMatrixMatvecT.argtypes = [d, vp, vp, d, vp]
     L.hypre_ParCSRMatrixMatvecOutOfPlace.argtypes = [d, vp, vp, d, vp, vp]
@@ -116,7 +146,12 @@ def _grid_args(grid):
 
 
 def set_device_path(enabled):
-    """False: interposed entry points call the reference (CPU).  Tests / cpu_baseline only."""
+    """False: interposed entry points call the host library's own (CPU) implementation.  Tests only."""
+    if REFERENCE_ONLY:
+        if enabled:
+            raise capi.B200Error("reference-only mode: the device path is not loaded in this process")
+        lib()
+        return
     lib().hypre_b200_set_enabled(1 if enabled else 0)
 
 

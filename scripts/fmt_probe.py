@@ -105,7 +105,7 @@ def main():
             capi.check(L.b200_parcsr_destroy(dA))
         for v in [vx, vf, vl1] + w:
             v.free()
-    capi.check(L.b200_set_compression(-1, 0))
+    capi.check(L.b200_set_compression(-1, 1))
     capi.check(L.b200_set_kernel_options(1, 0))
 
 

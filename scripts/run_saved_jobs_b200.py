@@ -42,7 +42,7 @@ def main():
     ap.add_argument("--match", default="", help="only jobs whose output name contains this")
     a = ap.parse_args()
     jobs = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_saved_goldens.json")))["jobs"]
-    launcher = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
+    launcher = os.path.join(ROOT, "hypre_b200", "lib", "mpirun_shim")
     binary = os.path.join(ROOT, "hypre_b200", "lib", "ij_b200_mp")
     for f in (launcher, binary):
         if not os.path.exists(f):

@@ -97,7 +97,7 @@ def test_ij_driver_links_against_the_binding(built):
     lines = [l for l in r.stderr.splitlines() if "`hypre_PCGSolve'" in l and "binding file" in l]
     # calls made from inside the reference library (HYPRE_PCGSolve -> hypre_PCGSolve) land in the binding;
     # the binding's own RTLD_NEXT lookup is the only one that resolves to the reference
-    from_ref = [l for l in lines if "libHYPRE_ref.so" in l.split(" to ")[0]]
+    from_ref = [l for l in lines if "libHYPRE_host.so" in l.split(" to ")[0]]
     assert from_ref and all("libHYPRE_b200.so" in l.split(" to ")[1] for l in from_ref), lines[:3]
 
 
@@ -134,12 +134,12 @@ def test_unsupported_pcg_options_are_rejected_loudly(H):
 
 
 def test_multirank_binding_fails_loudly_without_gpu(built):
-    """native multi-rank mode (ij_b200_mp over oracle/mpishim): without a device every rank reports the
+    """native multi-rank mode (ij_b200_mp over hypre_b200/host/mpishim): without a device every rank reports the
     failure and the solve does not silently run on the CPU (0 iterations, hypre error raised)"""
     if has_gpu():
         pytest.skip("GPU present")
     from hypre_b200 import ROOT
-    shim = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
+    shim = os.path.join(ROOT, "hypre_b200", "lib", "mpirun_shim")
     ij_mp = os.path.join(ROOT, "hypre_b200", "lib", "ij_b200_mp")
     if not (os.path.exists(shim) and os.path.exists(ij_mp)):
         pytest.skip("multi-rank builds absent")
@@ -271,3 +271,17 @@ def test_device_binding_goes_away_with_the_vector(H):
     assert L.hypre_b200_vector_device(C.c_void_p(handle)) is None
 
 
+
+
+def test_product_libraries_do_not_depend_on_the_oracle(built):
+    """nothing under hypre_b200/lib links, rpaths or loads anything under oracle/ (the checker is built
+    separately under oracle/_ref; the product's host library is hypre_b200/lib/libHYPRE_host.so)"""
+    from hypre_b200 import LIB_DIR
+    for name in sorted(os.listdir(LIB_DIR)):
+        path = os.path.join(LIB_DIR, name)
+        if not (name.endswith(".so") or name.startswith("ij_b200") or name == "mpirun_shim"):
+            continue
+        r = subprocess.run(["ldd", path], capture_output=True, text=True)
+        assert "oracle" not in r.stdout, (name, r.stdout)
+        d = subprocess.run(["readelf", "-d", path], capture_output=True, text=True).stdout
+        assert "oracle" not in d, (name, d)

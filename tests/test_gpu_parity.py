@@ -244,7 +244,7 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, zpad, chunke
             L.b200_parcsr_destroy(dA)
     finally:
         L.b200_set_layout_override(-1, -1)
-        L.b200_set_compression(-1, 0)
+        L.b200_set_compression(-1, 1)
         L.b200_set_kernel_options(1, 0)
 
 
@@ -288,7 +288,7 @@ def test_smoothers_on_compressed_storage(H, ctx, hier, mode, zpad, chunked, pat_
             L.b200_parcsr_destroy(dA)
     finally:
         L.b200_set_layout_override(-1, -1)
-        L.b200_set_compression(-1, 0)
+        L.b200_set_compression(-1, 1)
         L.b200_set_kernel_options(1, 0)
 
 

@@ -402,17 +402,18 @@ def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
     relative (the printed digits).  Measured in round 1 (profiles/r01_ij_b200_mp_2gpu_*.log): 13 iterations /
     3.629277e-09 and 8 / 6.133724e-10, both identical to the reference."""
     from hypre_b200 import ROOT
-    shim = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
+    shim = os.path.join(ROOT, "hypre_b200", "lib", "mpirun_shim")
+    shim_ref = os.path.join(ROOT, "oracle", "_ref", "mpirun_shim")
     ij_mp = os.path.join(ROOT, "hypre_b200", "lib", "ij_b200_mp")
     ij_ref = os.path.join(ROOT, "oracle", "_ref", "ij_ref_mp")
-    if not all(os.path.exists(f) for f in (shim, ij_mp, ij_ref)):
+    if not all(os.path.exists(f) for f in (shim, shim_ref, ij_mp, ij_ref)):
         pytest.skip("multi-rank builds absent")
     if _gpu_count() < 2:
         pytest.skip("needs 2 GPUs")
     env = dict(os.environ, OMP_NUM_THREADS="2")
 
     def run(binary):
-        r = subprocess.run([shim, "-np", "2", binary] + args.split(), capture_output=True, text=True, timeout=600, env=env)
+        r = subprocess.run([shim if binary == ij_mp else shim_ref, "-np", "2", binary] + args.split(), capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         it = int(re.search(r"^Iterations = (\d+)", r.stdout, re.M).group(1))
         fin = float(re.search(r"Final Relative Residual Norm = (\S+)", r.stdout).group(1))

@@ -30,7 +30,7 @@ def decode(A, x, layout, mode, zpad=0):
                                               C.byref(lay), C.byref(fmt), C.byref(stored), C.byref(nesc)))
     finally:
         L.b200_set_layout_override(-1, -1)
-        L.b200_set_compression(-1, 0)
+        L.b200_set_compression(-1, 1)
     return y, lay.value, fmt.value, stored.value, nesc.value
 
 
