@@ -10,13 +10,19 @@ region, in the reference's host code (north star) and the hierarchy is uploaded 
     value : device-resident solve (b, x in HBM; CUDA events on the library's stream)
     e2e   : HYPRE_ParCSRPCGSolve through the interposed C API with HOST vectors
             (pinned): H2D of b and x0 and D2H of x inside the timed region, wall clock
-    --impl reference : the reference's own CPU hypre_PCGSolve (oracle/_ref) on the host
-            cores, each step a bounded sample (PCG capped at --ref-iters iterations)
+    --impl reference : the reference's own CPU hypre_PCGSolve (oracle/_ref/libHYPRE_ref.so, loaded
+            ALONE: no product library is mapped in that process) on all host cores, the full
+            solve of the same config (--ref-iters N caps it, for quick local runs only)
+    parity : the device solve's per-iteration relative residual norms against the reference's
+            history of the same command line (tests/golden/bench_histories.json, printed 7 digits)
+            and -- at N = 1 -- against the reference arm run in a subprocess (cpu_baseline leg,
+            full precision), iteration counts included
 
 Prints ONE JSON line on rank 0.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -47,27 +53,82 @@ def _set_host_threads():
 HOST_THREADS = _set_host_threads()
 
 WORKLOADS = {
-    # name: (generator, args, relax_type, ij command line)
-    "lap7_256_cheby": ("laplacian", (256, 256, 256), 16, "ij -laplacian -n 256 256 256 -solver 1 -rlx 16"),
-    "lap7_256_l1jac": ("laplacian", (256, 256, 256), 18, "ij -laplacian -n 256 256 256 -solver 1 -rlx 18"),
-    "lap7_100_l1jac": ("laplacian", (100, 100, 100), 18, "ij -laplacian -n 100 100 100 -solver 1 -rlx 18"),
-    "lap27_128_gs11": ("laplacian_27pt", (128, 128, 128), 11, "ij -27pt -n 128 128 128 -solver 1 -rlx 11"),
-    "lap7_64_cheby": ("laplacian", (64, 64, 64), 16, "ij -laplacian -n 64 64 64 -solver 1 -rlx 16"),
+    # name: (generator, args, relax_type, ij command line, extra BoomerAMG options)
+    "lap7_256_cheby": ("laplacian", (256, 256, 256), 16, "ij -laplacian -n 256 256 256 -solver 1 -rlx 16", {}),
+    "lap7_256_l1jac": ("laplacian", (256, 256, 256), 18, "ij -laplacian -n 256 256 256 -solver 1 -rlx 18", {}),
+    "lap7_100_l1jac": ("laplacian", (100, 100, 100), 18, "ij -laplacian -n 100 100 100 -solver 1 -rlx 18", {}),
+    "lap27_128_gs11": ("laplacian_27pt", (128, 128, 128), 11, "ij -27pt -n 128 128 128 -solver 1 -rlx 11", {}),
+    "lap27_200_gs11": ("laplacian_27pt", (200, 200, 200), 11, "ij -27pt -n 200 200 200 -solver 1 -rlx 11", {}),
+    "lap27_320_gs11": ("laplacian_27pt", (320, 320, 320), 11, "ij -27pt -n 320 320 320 -solver 1 -rlx 11", {}),
+    "lap7_64_cheby": ("laplacian", (64, 64, 64), 16, "ij -laplacian -n 64 64 64 -solver 1 -rlx 16", {}),
+    # BASELINE.json configs[4]: 2-D rotated anisotropy with aggressive coarsening (src/test/ij.c:11184-11193)
+    "rot_2048_l1jac_agg1": ("rotate_7pt", (2048, 2048, 45.0, 0.001), 18,
+                            "ij -rotate -n 2048 2048 -alpha 45 -eps 0.001 -solver 1 -rlx 18 -agg_nl 1", {"AggNumLevels": 1}),
+    "rot_8192_l1jac_agg1": ("rotate_7pt", (8192, 8192, 45.0, 0.001), 18,
+                            "ij -rotate -n 8192 8192 -alpha 45 -eps 0.001 -solver 1 -rlx 18 -agg_nl 1", {"AggNumLevels": 1}),
 }
 
 
+def _sha(path):
+    try:
+        return hashlib.sha256(open(path, "rb").read()).hexdigest()[:16]
+    except Exception:
+        return None
+
+
 def ncu_traffic(n, nnz, value_format):
-    """DRAM bytes per launch of the level-0 SpMV from a committed ncu --set full summary (same matrix,
-    same storage format)."""
-    for name in ("r01_ncu_traffic_compressed.json", "r01_ncu_traffic.json"):
+    """DRAM bytes per launch of the level-0 SpMV from a committed ncu --set full summary: same matrix, same
+    storage format AND the same kernel source (sha of hypre_b200/csrc/spmv.cuh recorded at capture time);
+    anything else is refused (None)."""
+    here = _sha(os.path.join(ROOT, "hypre_b200", "csrc", "spmv.cuh"))
+    for name in sorted(os.listdir(os.path.join(ROOT, "profiles")), reverse=True):
+        if not (name.startswith("r") and "ncu_traffic" in name and name.endswith(".json")):
+            continue
         try:
             t = json.load(open(os.path.join(ROOT, "profiles", name)))
             mt = t["matrix"]
-            if mt["rows"] == n and mt["nnz"] == nnz and mt.get("value_format", 0) == value_format:
+            if mt["rows"] == n and mt["nnz"] == nnz and mt.get("value_format", 0) == value_format and \
+                    t.get("spmv_cuh_sha16") == here:
                 return t["spmv_level0"]["traffic_bytes_per_launch"]
         except Exception:
             pass
     return None
+
+
+def golden_history(workload, nscale):
+    """the reference's history for this bench workload at full size (tests/golden/bench_histories.json)"""
+    if nscale:
+        return None
+    try:
+        return json.load(open(os.path.join(ROOT, "tests", "golden", "bench_histories.json"))).get(workload)
+    except Exception:
+        return None
+
+
+def parity_block(rel, iters, gold, ref=None):
+    """rel[1..iters] of the device solve against the golden (printed 7 digits: 2e-6) and, when the reference arm
+    ran in this bench (N = 1), against its full-precision history (1e-9); iteration counts must agree (+-1)"""
+    out = {"iterations": int(iters), "ref_iterations": None, "max_rel_norm_diff": None, "tolerance": None, "ok": None}
+    dev = np.asarray(rel[1:iters + 1], dtype=np.float64)
+    checks = []
+    if gold:
+        g = np.asarray(gold["rel_norms"], dtype=np.float64)
+        m = min(len(g), len(dev))
+        d = float(np.max(np.abs(dev[:m] - g[:m]) / g[:m])) if m else None
+        out.update({"ref_iterations": int(gold["iterations"]), "golden": "tests/golden/bench_histories.json",
+                    "max_rel_norm_diff_vs_golden": d, "golden_tolerance": 2e-6})
+        checks.append(abs(iters - gold["iterations"]) <= 1 and d is not None and d <= 2e-6)
+    if ref and ref.get("rel_norms"):
+        r = np.asarray(ref["rel_norms"], dtype=np.float64)
+        m = min(len(r), len(dev))
+        d = float(np.max(np.abs(dev[:m] - r[:m]) / r[:m])) if m else None
+        out.update({"ref_iterations": int(ref["iterations"]), "max_rel_norm_diff": d, "tolerance": 1e-9,
+                    "reference": "oracle/_ref/libHYPRE_ref.so in a subprocess (cpu_baseline leg), same config"})
+        checks.append(abs(iters - ref["iterations"]) <= 1 and d is not None and d <= 1e-9)
+    elif gold:
+        out.update({"max_rel_norm_diff": out["max_rel_norm_diff_vs_golden"], "tolerance": 2e-6})
+    out["ok"] = bool(checks) and all(checks)
+    return out
 
 
 def measured_peaks():
@@ -126,9 +187,9 @@ class ClockSampler:
 
 
 def build_problem(H, name, nscale=None, grid=None, weak=False):
-    gen, dims, rlx, cmd = WORKLOADS[name]
+    gen, dims, rlx, cmd, opts = WORKLOADS[name]
     if nscale:
-        dims = tuple(nscale for _ in dims)
+        dims = tuple(nscale if isinstance(d, int) else d for d in dims)
         cmd = cmd + " [scaled to n=%d]" % nscale
     if grid and weak:                    # --native --weak: the named grid is the PER-GPU problem
         dims = tuple(d * g for d, g in zip(dims, grid))
@@ -138,7 +199,7 @@ def build_problem(H, name, nscale=None, grid=None, weak=False):
     A = getattr(H, gen)(*dims, grid=grid) if grid else getattr(H, gen)(*dims)
     b = A.vector(1.0)
     x = A.vector(0.0)
-    amg = H.BoomerAMG(relax_type=rlx)
+    amg = H.BoomerAMG(relax_type=rlx, **opts)
     pcg = H.ParCSRPCG(tol=1e-8, max_iter=100, two_norm=1, print_level=0, logging=1)
     pcg.SetPrecond(amg)
     t0 = time.perf_counter()
@@ -146,16 +207,32 @@ def build_problem(H, name, nscale=None, grid=None, weak=False):
     return dict(A=A, b=b, x=x, amg=amg, pcg=pcg, rlx=rlx, cmd=cmd, setup_s=time.perf_counter() - t0)
 
 
+def mapped_native_libs():
+    """shared objects of this repo mapped into the process (what the driver's loader hook would see)"""
+    libs = set()
+    try:
+        for line in open("/proc/self/maps"):
+            path = line.split()[-1]
+            if path.startswith(ROOT) and ".so" in path:
+                libs.add(os.path.relpath(path, ROOT))
+    except Exception:
+        pass
+    return sorted(libs)
+
+
 def run_reference(args, rank):
-    """--impl reference: the reference's CPU hypre_PCGSolve on the host cores."""
+    """--impl reference: the reference's CPU hypre_PCGSolve on the host cores, the full solve of the same config.
+    main() put hypre_b200.hypre into reference-only mode before it was imported: this process maps
+    oracle/_ref/libHYPRE_ref.so (+ the accessor bridge) and no product library."""
     if rank != 0:
         return
     from hypre_b200 import hypre as H
-    H.set_device_path(False)
+    assert H.REFERENCE_ONLY
     ncores = HOST_THREADS
     P = build_problem(H, args.workload, args.n)
     n = P["A"].global_rows
-    P["pcg"].SetMaxIter(args.ref_iters)
+    if args.ref_iters > 0:
+        P["pcg"].SetMaxIter(args.ref_iters)
     xs = P["x"].numpy()
     times, iters = [], 0
     for s in range(args.warmup + args.steps):
@@ -170,17 +247,41 @@ def run_reference(args, rank):
             times.append(dt)
     tot = sum(times)
     value = n * iters * len(times) / tot
-    sample = "%s, PCG capped at %d iterations per step, %d OpenMP threads" % (P["cmd"], args.ref_iters, ncores)
+    rel = [float(v) for v in P["pcg"].rel_norms()]
+    gold = golden_history(args.workload, args.n)
+    capped = args.ref_iters > 0
+    sample = "%s, %s, %d OpenMP threads, oracle/_ref/libHYPRE_ref.so" % (
+        P["cmd"], "PCG capped at %d iterations per step" % args.ref_iters if capped else "full solve (%d iterations)" % iters, ncores)
     out = {
         "impl": "reference", "metric": "AMG-PCG solve DOF*iterations/s", "value": value, "unit": "DOF*it/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "l2": "inputs larger than L2"},
+        "config": {"workload": P["cmd"], "dof": n, "iterations_per_step": iters, "levels": P["amg"].num_levels,
+                   "l2": "inputs larger than L2", "final_rel_residual": rel[-1] if rel else None},
         "cpu_baseline": {"value": value, "unit": "DOF*it/s", "cores": ncores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "DOF*it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0, "setup_s": P["setup_s"],
+        "gpu_launches": 0, "setup_s": P["setup_s"], "iterations": iters, "rel_norms": rel,
+        "parity": parity_block([0.0] + rel, iters, gold) if not capped else None,
+        "native_so_loaded": mapped_native_libs(),
     }
     print(json.dumps(out))
+
+
+def reference_subprocess(args):
+    """cpu_baseline leg at N = 1: the reference arm of this file in its own process (so that no product library is
+    mapped while the reference is timed), one full solve of the same config, all host cores"""
+    env = {k: v for k, v in os.environ.items()
+           if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS",
+                        "HYPRE_B200_NATIVE", "B200_PROFILE")}
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "1", "--warmup", "0",
+           "--workload", args.workload, "--ref-iters", str(args.ref_iters)]
+    if args.n:
+        cmd += ["--n", str(args.n)]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=3000)
+    for line in reversed(r.stdout.strip().splitlines()):
+        if line.startswith("{"):
+            return json.loads(line)
+    raise RuntimeError("reference arm failed: " + r.stderr[-400:])
 
 
 class Ranks:
@@ -362,21 +463,16 @@ def run_b200(args, rank, world):
     # a solve runs iters+1 preconditioner cycles and SpMVs (the initial residual and p = C r come first)
     iter_gbs = iter_bytes * (iters + 1) * args.steps / dev_s / 1e9
 
-    # ---------------- cpu_baseline: the reference's CPU PCG on this box, bounded sample
-    cpu = None
+    # ---------------- cpu_baseline: the reference arm (its own process), one full solve of the same config
+    cpu, ref_line = None, None
     if not args.no_cpu_baseline:
-        H.set_device_path(False)
-        pcg.SetMaxIter(args.ref_iters)
-        xh[:] = 0.0
-        H.clear_errors()
-        t0 = time.perf_counter()
-        pcg.Solve(A, b, x)
-        dt = time.perf_counter() - t0
-        cpu = {"value": n * pcg.num_iterations / dt, "unit": "DOF*it/s", "cores": ncores, "kind": "reference",
-               "sample": "%s capped at %d PCG iterations, 1 solve, %d OpenMP threads (oracle/_ref/libHYPRE_ref.so)"
-                         % (P["cmd"], args.ref_iters, ncores)}
-        H.clear_errors()
-        H.set_device_path(True)
+        try:
+            ref_line = reference_subprocess(args)
+            cpu = dict(ref_line["cpu_baseline"])
+            cpu["native_so_loaded"] = ref_line.get("native_so_loaded")
+        except Exception as e:          # noqa: BLE001
+            cpu = {"error": repr(e)[:300]}
+    parity = parity_block(rel, iters, golden_history(args.workload, args.n), ref_line)
 
     # ---------------- aux: BASELINE.json configs[1], the stand-alone ParCSR SpMV microbench (27-pt 200^3),
     # with the level-0 smoother sweeps on the same matrix; never allowed to break the line above it
@@ -429,7 +525,7 @@ def run_b200(args, rank, world):
                      "pcg_iteration_bytes": iter_bytes, "pcg_iteration_stored_bytes": iter_stored,
                      "pcg_iteration_stored_gbs": iter_stored * (iters + 1) * args.steps / dev_s / 1e9,
                      "pcg_iteration_stored_frac": iter_stored * (iters + 1) * args.steps / dev_s / 1e9 / peak},
-        "cpu_baseline": cpu, "clocks": clocks,
+        "cpu_baseline": cpu, "parity": parity, "clocks": clocks,
         "setup_s": P["setup_s"], "upload_s": upload_s, "aux_spmv_microbench": aux,
     }
     print(json.dumps(out))
@@ -518,7 +614,8 @@ def finish_multi(args, R, P, m):
             "roofline": {"bound": "hbm", "kernel": "whole PCG iteration, all ranks (per-kernel roofline is reported at N=1)",
                          "achieved": iter_gbs, "peak": peak * R.world, "unit": "GB/s", "frac": iter_gbs / (peak * R.world),
                          "traffic": None, "peak_source": peak_src + " x n_gpus", "pcg_iteration_bytes": iter_bytes},
-            "cpu_baseline": None, "clocks": m["clocks"], "setup_s": P["setup_s"], "upload_s": m["upload_s"],
+            "cpu_baseline": None, "parity": parity_block(m["rel"], m["iters"], golden_history(args.workload, args.n)),
+            "clocks": m["clocks"], "setup_s": P["setup_s"], "upload_s": m["upload_s"],
             "halo": halo,
         }
         print(json.dumps(out))
@@ -534,7 +631,9 @@ def main():
     ap.add_argument("--no-aux", action="store_true", help="skip the stand-alone SpMV microbench (configs[1])")
     ap.add_argument("--workload", default="lap7_256_cheby", choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=None, help="override the grid edge (scaled-down smoke runs)")
-    ap.add_argument("--ref-iters", type=int, default=3, help="PCG iterations per reference step (bounded sample)")
+    ap.add_argument("--ref-iters", type=int, default=0,
+                    help="cap the reference's PCG iterations per step (0 = the full solve, the default; the reference "
+                         "needs ~7 s per 256^3 solve on 16 cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--native", action="store_true",
                     help="N > 1: hypre's own distributed setup on N ranks (native multi-rank mode, INTEGRATION.md 4b) "
@@ -551,6 +650,7 @@ def main():
                                                                         os.environ.get("TORCHELASTIC_RUN_ID", "run")))
         os.makedirs(d, exist_ok=True)
     if args.impl == "reference":
+        os.environ["HYPRE_B200_REFERENCE_ONLY"] = "1"      # before hypre_b200.hypre is imported
         run_reference(args, rank)
     else:
         run_b200(args, rank, world)

@@ -163,6 +163,7 @@ struct DMat {
    int             n_dict = 0;
    long long       stored_bytes = 0;     // bytes one pass over the block reads from the matrix arrays
    int             zpad = 0;             // compressed storage without CFMT_PAD lanes (padding = valid column x value 0)
+   std::vector<double> h_dict;           // CFMT_PAT8: host copy of the (value, delta) dictionary (kernel parameter)
    int             pat_stride = 0;       // CFMT_PAT8: 16-byte units per slice header (headers in c_code, lane words in c_idx)
 };
 

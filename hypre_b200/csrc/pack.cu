@@ -27,6 +27,7 @@ static int g_zpad = env_int("B200_ZPAD", 1) != 0;
 // launch options of the thread-per-row kernels (rowlaunch.cuh)
 int g_rows_chunked = env_int("B200_CHUNKED", 1);
 int g_pat_regs = env_int("B200_PAT_REGS", 0) != 0;
+int g_rows_waves = std::min(4, std::max(1, env_int("B200_PAT_WAVES", 1)));    // grid of the pattern kernel in waves of 148 x 8 blocks
 
 extern "C" int b200_set_compression(int mode, int no_padding_markers)
 {
@@ -39,9 +40,15 @@ extern "C" int b200_set_compression(int mode, int no_padding_markers)
 
 extern "C" int b200_set_kernel_options(int chunked, int pat_regs)
 {
-   ARG_CHECK(chunked >= -1 && chunked <= 2 && pat_regs >= -1 && pat_regs <= 1);   // chunked 2: also the VAL* / plain kernels
+   // chunked 2: also the VAL* / plain kernels; pat_regs: bit 0 = the 40-register instantiation, bits 1-3 = grid of
+   // the pattern kernel in waves of resident blocks (0 leaves it)
+   ARG_CHECK(chunked >= -1 && chunked <= 2 && pat_regs >= -1 && pat_regs <= 9);
    if (chunked >= 0) { g_rows_chunked = chunked; }
-   if (pat_regs >= 0) { g_pat_regs = pat_regs; }
+   if (pat_regs >= 0)
+   {
+      g_pat_regs = pat_regs & 1;
+      if (pat_regs >> 1) { g_rows_waves = pat_regs >> 1; }
+   }
    return B200_OK;
 }
 
@@ -225,7 +232,7 @@ static bool pack_patterns(const HostCsr &h, const std::vector<int> *order, int n
       bytes[(size_t)s + 1] = lane_words;       // 32-lane-word groups of this slice
    }
    for (int s = 0; s < n_slices; s++) { bytes[(size_t)s + 1] += bytes[(size_t)s]; }
-   if (bytes[(size_t)n_slices] >= (1LL << 24)) { return false; }     // the group offset has 24 bits in word 0
+   if (bytes[(size_t)n_slices] >= (1LL << 22)) { return false; }     // the group offset has 22 bits in word 0
    int nw_max = 0;
    for (int s = 0; s < n_slices; s++) { nw_max = std::max(nw_max, w4[(size_t)s] / 4); }
    const int stride16 = (4 + 4 * nw_max + 15) / 16;                   // 16-byte units per slice header
@@ -239,7 +246,9 @@ static bool pack_patterns(const HostCsr &h, const std::vector<int> *order, int n
       const int nw = w4[(size_t)s] / 4;
       unsigned *w0 = reinterpret_cast<unsigned *>(P->pat.data() + (size_t)s * 16 * (size_t)stride16);
       unsigned *lanew = P->pat_lanes.data() + (size_t)bytes[(size_t)s] * 32;
-      w0[0] = (unsigned)nw | ((unsigned)bytes[(size_t)s] << 8);
+      const int w_true = (int)((off_orig[(size_t)s + 1] - off_orig[(size_t)s]) / 32);      // entries of the longest row
+      const int last_cnt = nw > 0 ? w_true - 4 * (nw - 1) : 1;
+      w0[0] = (unsigned)nw | ((unsigned)(last_cnt - 1) << 8) | ((unsigned)bytes[(size_t)s] << 10);
       for (int i = 0; i < nw; i++)
       {
          unsigned hw = 0, mixed_any = 0;
@@ -593,7 +602,8 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
             const unsigned *w0 = reinterpret_cast<const unsigned *>(P.pat.data() + (size_t)slice * 16 * (size_t)P.pat_stride);
             const unsigned nw = w0[0] & 0xFFu;
             if (4 + 4 * (int)nw > 16 * P.pat_stride) { b200_set_error("pattern header wider than its stride"); return B200_ERR_ARG; }
-            const unsigned *lp = P.pat_lanes.data() + (size_t)(w0[0] >> 8) * 32 + lane;
+            const unsigned *lp = P.pat_lanes.data() + (size_t)(w0[0] >> 10) * 32 + lane;
+            const int last_cnt = (int)((w0[0] >> 8) & 3u) + 1;
             const int rowc = row < n ? row : n - 1;
             for (unsigned i = 0; i < nw; i++)
             {
@@ -604,7 +614,7 @@ int packed_matvec_host(const PackedDMat &P, const HostCsr &h, const double *x, d
                   if (lp >= P.pat_lanes.data() + P.pat_lanes.size()) { b200_set_error("pattern stream overrun"); return B200_ERR_ARG; }
                   hw = (*lp & m) | (hw & ~m); lp += 32;
                }
-               for (int j = 0; j < 4; j++)
+               for (int j = 0; j < (i + 1 == nw ? last_cnt : 4); j++)
                {
                   const unsigned cd = (hw >> (8 * j)) & 0xFFu;
                   if (2 * (size_t)cd + 1 >= P.dict.size()) { b200_set_error("pattern code out of range"); return B200_ERR_ARG; }

@@ -2,6 +2,7 @@
 #pragma once
 #include "spmv.cuh"
 #include <cstring>
+#include <algorithm>
 
 static inline RedCtx make_redctx(b200_ctx *ctx, double *out, int accumulate)
 {
@@ -13,10 +14,11 @@ static inline RedCtx make_redctx(b200_ctx *ctx, double *out, int accumulate)
 
 // grid for `work` row-groups of which `per_block` fit a block: whole waves of the
 // 148 SMs x 8 resident 256-thread blocks, folded by the kernels' stride loops
-static inline int rows_grid(long long work, int per_block)
+extern int g_rows_waves;
+static inline int rows_grid(long long work, int per_block, int waves = 4)
 {
    long long g = (work + per_block - 1) / per_block;
-   const long long cap = (long long)B200_NUM_SMS * 8 * 4;   // 4736 <= B200_MAX_PARTIALS
+   const long long cap = (long long)B200_NUM_SMS * 8 * waves;   // 4736 <= B200_MAX_PARTIALS
    if (g > cap) { g = cap; }
    if (g < 1) { g = 1; }
    return (int)g;
@@ -25,6 +27,15 @@ static inline int rows_grid(long long work, int per_block)
 // launch options of the thread-per-row kernels (pack.cu; environment B200_CHUNKED, B200_PAT_REGS,
 // b200_set_kernel_options): slice-to-block mapping and the PAT8 instantiation
 extern int g_rows_chunked, g_pat_regs;
+
+// the pattern dictionary of a CFMT_PAT8 block as a kernel parameter (host copy kept in the DMat)
+static inline PatTab pat_tab_of(const DMat &D)
+{
+   PatTab t;
+   memset(&t, 0, sizeof(t));
+   memcpy(t.e, D.h_dict.data(), std::min(sizeof(t.e), D.h_dict.size() * sizeof(double)));
+   return t;
+}
 
 static inline HaloArgs no_halo()
 {
@@ -49,17 +60,20 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    //  and the reduction publishes the zero)
    if (D.layout >= 1 || D.n_rows == 0)
    {
-      int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32);
+      // the pattern kernel runs as ONE wave of resident blocks, each walking a long contiguous run of slices
+      int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32, D.cfmt == CFMT_PAT8 ? g_rows_waves : 4);
       HaloArgs hh = h;
       hh.chunked = D.cfmt == CFMT_PAT8 ? g_rows_chunked : (g_rows_chunked > 1);
       const int variant = D.cfmt == CFMT_PAT8 ? (g_pat_regs ? 1 : 0) : (D.zpad ? 1 : 0);
       switch (D.cfmt ? D.cfmt + 8 * variant : 0)
       {
-#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
-         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_C(CFMT_PAT8)
-         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_C(CFMT_PAT8 + 8)
+#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, NoTab()); break;
+#define CASE_P(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, pat_tab_of(D)); break;
+         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_P(CFMT_PAT8)
+         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_P(CFMT_PAT8 + 8)
 #undef CASE_C
-         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
+#undef CASE_P
+         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, NoTab()); break;
       }
    }
    else
@@ -69,7 +83,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
 #define CASE_T(TT)                                                                            \
    case TT: {                                                                                 \
       int grid = rows_grid(D.n_rows, ROWK_BLOCK / TT);                                        \
-      LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);       \
+      LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc, NoTab());   \
    } break;
          CASE_T(1) CASE_T(2) CASE_T(4) CASE_T(8) CASE_T(16) CASE_T(32)
 #undef CASE_T

@@ -188,8 +188,8 @@ def _compression_matrices(H, hier):
 
 # (mode, no_padding_markers, chunked, pat_regs): every storage format in both padding forms, the pattern kernel in
 # both instantiations, both slice-to-block mappings
-_FORMATS = [(-1, 0, 1, 0), (0, 0, 1, 0), (1, 0, 1, 0), (2, 0, 1, 0), (3, 0, 1, 0), (4, 0, 1, 0), (4, 0, 0, 1), (4, 0, 1, 1),
-            (-1, 1, 1, 0), (1, 1, 0, 0), (2, 1, 1, 0), (3, 1, 1, 0), (1, 0, 0, 0)]
+_FORMATS = [(-1, 0, 1, 2), (0, 0, 1, 2), (1, 0, 1, 2), (2, 0, 1, 2), (3, 0, 1, 2), (4, 0, 1, 2), (4, 0, 0, 9), (4, 0, 1, 3),
+            (-1, 1, 1, 8), (1, 1, 0, 2), (2, 1, 1, 2), (3, 1, 1, 2), (1, 0, 2, 2)]
 
 
 @pytest.mark.parametrize("layout", [1, 2])
@@ -245,13 +245,13 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, zpad, chunke
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 1)
-        L.b200_set_kernel_options(1, 0)
+        L.b200_set_kernel_options(1, 2)
 
 
 _BITS = {}      # SpMV result of the first format run on (matrix, layout): the others must reproduce it bit for bit
 
 
-@pytest.mark.parametrize("mode,zpad,chunked,pat_regs", [(-1, 0, 1, 0), (4, 0, 0, 1), (1, 0, 1, 0), (1, 1, 1, 0), (2, 1, 0, 0), (3, 0, 1, 0), (3, 1, 1, 0)])
+@pytest.mark.parametrize("mode,zpad,chunked,pat_regs", [(-1, 0, 1, 2), (4, 0, 0, 9), (1, 0, 1, 2), (1, 1, 1, 2), (2, 1, 0, 2), (3, 0, 1, 2), (3, 1, 1, 2)])
 def test_smoothers_on_compressed_storage(H, ctx, hier, mode, zpad, chunked, pat_regs):
     """every fused epilogue on the compressed thread-per-row kernels against the oracle"""
     L = capi.lib()
@@ -289,7 +289,7 @@ def test_smoothers_on_compressed_storage(H, ctx, hier, mode, zpad, chunked, pat_
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 1)
-        L.b200_set_kernel_options(1, 0)
+        L.b200_set_kernel_options(1, 2)
 
 
 def vec_err_max(a, b):
