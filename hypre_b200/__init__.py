@@ -27,6 +27,7 @@ LIB_BRIDGE = os.path.join(LIB_DIR, "libhypre_bridge.so")            # struct acc
 LIB_BRIDGE_MP = os.path.join(LIB_DIR, "libhypre_bridge_mp.so")
 MPIRUN_SHIM = os.path.join(LIB_DIR, "mpirun_shim")                  # launcher of the native multi-rank mode
 LIB_HYPRE_REF = os.path.join(REF_DIR, "libHYPRE_ref.so")            # the oracle's separately built reference (checker)
+LIB_REF_BRIDGE = os.path.join(REF_DIR, "libref_bridge.so")          # the same accessors, the checker's own build
 LIB_ORACLE = os.path.join(REF_DIR, "liboracle.so")
 IJ_B200 = os.path.join(LIB_DIR, "ij_b200")
 IJ_REF = os.path.join(REF_DIR, "ij_ref")

@@ -290,7 +290,7 @@ static int coarse_dense_solve(b200_amg *a, const double *f, double *u)
    return op_dense_matvec(c, n_local, a->coarse_n, a->d_Ainv, f, u);
 }
 
-static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const double *f)
+static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const double *f, const FusedDot *fd = nullptr)
 {
    AmgLevel &L = a->L[l];
    const int zg = s.zero[l] ? 1 : 0;
@@ -300,7 +300,7 @@ static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const d
          if (zg) { B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, nullptr, U_cur(s, l), 1)); }
          else
          {
-            B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, U_cur(s, l), U_other(s, l), 0));
+            B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, U_cur(s, l), U_other(s, l), 0, fd));
             s.cur[l] = 1 - s.cur[l];
          }
          break;
@@ -308,10 +308,10 @@ static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const d
          // hypre_ParCSRRelax_Cheby_Solve(A, f, ds, coefs, order, scale, variant, u, Vtemp, Ztemp, Ptemp, Rtemp)
          // (par_cycle.c:529-538)
          B200_TRY(op_cheby(L.A, f, L.d_ds, L.coefs.data(), L.cheby_order, L.cheby_scale, U_cur(s, l),
-                           a->Vtemp, a->Ztemp, a->Rtemp, zg));
+                           a->Vtemp, a->Ztemp, a->Rtemp, zg, fd));
          break;
       case 11: case 12:
-         B200_TRY(op_gs2(L.A, f, L.relax_weight, relax_type == 11 ? 1 : 2, U_cur(s, l), a->Vtemp, a->Ztemp, zg));
+         B200_TRY(op_gs2(L.A, f, L.relax_weight, relax_type == 11 ? 1 : 2, U_cur(s, l), a->Vtemp, a->Ztemp, zg, fd));
          break;
       case 9:
          B200_TRY(coarse_dense_solve(a, f, U_cur(s, l)));
@@ -326,7 +326,10 @@ static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const d
 
 // One cycle; the level-counter state machine is the reference's (par_cycle.c:209-223,647-779).
 // u_alt0: second level-0 buffer.  On return *u_result points at the buffer holding U[0].
-static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result)
+// fd (optional): <fd->with, U[0]> is reduced inside the cycle's last smoothing launch on level 0 where the
+// smoother supports it (*fd->done tells); the caller (PCG: gamma = <r, C r>) falls back to its own pass otherwise.
+static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result,
+                          const FusedDot *fd = nullptr)
 {
    const int nl = a->num_levels;
    CycleState s;
@@ -362,7 +365,12 @@ static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_gues
       int relax_type, num_sweep;
       if (nl > 1) { relax_type = a->relax_type[cycle_param]; num_sweep = a->num_sweeps[cycle_param]; }
       else        { relax_type = a->relax_type[0];           num_sweep = a->num_sweeps[0]; }
-      for (int j = 0; j < num_sweep; j++) { B200_TRY(relax_once(a, s, level, relax_type, F[level])); }
+      // level 0 is visited twice (lev_counter 1 -> 0 -> -1): its last sweep of the second visit ends the cycle
+      const bool final_visit = level == 0 && (nl == 1 || lev_counter[0] == 0);
+      for (int j = 0; j < num_sweep; j++)
+      {
+         B200_TRY(relax_once(a, s, level, relax_type, F[level], final_visit && j == num_sweep - 1 ? fd : nullptr));
+      }
 
       --lev_counter[level];
       if (lev_counter[level] >= 0 && level != nl - 1)
@@ -427,13 +435,13 @@ double *amg_level0_alt(b200_amg *a) { return a->L[0].Ualt; }
 // BoomerAMG as a preconditioner: z = B r.  hypre_BoomerAMGSolve with tol 0 and max_iter k (ij -precon_cycles k)
 // runs k cycles without looking at the residual (src/parcsr_ls/par_amg_solve.c:257-336); the Krylov solver cleared
 // u before the call, so the first cycle starts from a zero guess and the others continue on its result.
-int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result)
+int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result, const FusedDot *fd)
 {
-   B200_TRY(amg_cycle_core(a, f, u, 1, u_result));
+   B200_TRY(amg_cycle_core(a, f, u, 1, u_result, a->precond_cycles == 1 ? fd : nullptr));
    for (int k = 1; k < a->precond_cycles; k++)
    {
       if (*u_result != u) { B200_TRY(b200_vec_copy(a->ctx, a->L[0].n, *u_result, u)); }
-      B200_TRY(amg_cycle_core(a, f, u, 0, u_result));
+      B200_TRY(amg_cycle_core(a, f, u, 0, u_result, k == a->precond_cycles - 1 ? fd : nullptr));
    }
    return B200_OK;
 }

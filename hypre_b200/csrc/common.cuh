@@ -105,7 +105,7 @@ struct b200_ctx {
    size_t       h_kry_n = 0;
 };
 
-enum { WS_PCG_P = 0, WS_PCG_S, WS_PCG_R, WS_HOST_B, WS_HOST_X, WS_HOST_Y, WS_AMG_R, WS_KRYLOV };
+enum { WS_PCG_P = 0, WS_PCG_S, WS_PCG_R, WS_HOST_B, WS_HOST_X, WS_HOST_Y, WS_AMG_R, WS_KRYLOV, WS_PCG_P2, WS_PCG_Z };
 // device work vector `slot` with at least n doubles
 int ctx_workspace(b200_ctx *c, int slot, size_t n, double **out);
 
@@ -163,7 +163,6 @@ struct DMat {
    int             n_dict = 0;
    long long       stored_bytes = 0;     // bytes one pass over the block reads from the matrix arrays
    int             zpad = 0;             // compressed storage without CFMT_PAD lanes (padding = valid column x value 0)
-   std::vector<double> h_dict;           // CFMT_PAT8: host copy of the (value, delta) dictionary (kernel parameter)
    int             pat_stride = 0;       // CFMT_PAT8: 16-byte units per slice header (headers in c_code, lane words in c_idx)
 };
 

@@ -14,7 +14,7 @@
 #include "p2p.cuh"
 #include "krylov_core.hpp"
 
-int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result);
+int amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result, const FusedDot *fd = nullptr);
 
 // z = r ./ d   (HYPRE_ParCSRDiagScale, src/parcsr_ls/HYPRE_parcsr_pcg.c:267-277)
 struct FDiagScale {

@@ -86,7 +86,6 @@ int dmat_upload(b200_ctx *ctx, const HostCsr &h, DMat *m, int allow_sell)
       m->c_idx = reinterpret_cast<unsigned short *>(d_lanes);      // lane words live in the c_idx slot
       m->n_dict = (int)(P.dict.size() / 2);
       m->pat_stride = P.pat_stride;
-      m->h_dict = P.dict;
    }
    else { B200_TRY(dev_upload(&d_code, P.code.data(), P.code.size())); }
    m->c_code = d_code;

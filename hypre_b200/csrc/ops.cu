@@ -27,14 +27,44 @@ struct EpiMatvecDot {
       red[0] = fma(t, x[r], red[0]);
    }
 };
-// u_out = u_in + (w*(f - t)) / l1     hypre_BoomerAMGRelax7Jacobi (src/parcsr_ls/par_relax.c:1177-1254)
-struct EpiJacobi {
-   static constexpr int NRED = 0;
-   EPI_PLAIN_X
-   double w; const double *f; const double *l1; const double *u_in; double *u_out;
-   __device__ void operator()(int r, double t, double *) const
+// PCG: the direction update p = z + beta p (src/krylov/pcg.c:960-971: ScaleVector(beta, p); Axpy(1, s, p)) fused
+// into the next s = A p and <s, p> (pcg.c:577-580): the gathered operand is formed on the fly from z and the OLD p,
+// the epilogue writes the new p into the other of two buffers (other rows still gather the old one) -- p is streamed
+// once per iteration instead of three times and the pass of its own disappears.  beta and the parity of the
+// iteration (which buffer is old) are device-resident: the launch is identical from one iteration to the next.
+struct EpiMatvecDotDir {
+   static constexpr int NRED = 1;
+   const double *scal_beta; const int *iter; const double *z; double *pbuf0; double *pbuf1; double *s;
+   double beta; const double *p_old; double *p_new;       // set by init()
+   __device__ void init()
    {
-      u_out[r] = u_in[r] + (w * (f[r] - t)) / l1[r];
+      beta = *scal_beta;
+      const int odd = *iter & 1;
+      p_old = odd ? pbuf1 : pbuf0;
+      p_new = odd ? pbuf0 : pbuf1;
+   }
+   __device__ __forceinline__ double xval(const double *__restrict__, int j) const { return fma(beta, __ldg(p_old + j), __ldg(z + j)); }
+   __device__ void operator()(int r, double t, double *red) const
+   {
+      const double pn = fma(beta, p_old[r], z[r]);
+      p_new[r] = pn;
+      s[r] = t;
+      red[0] = fma(t, pn, red[0]);
+   }
+};
+// u_out = u_in + (w*(f - t)) / l1     hypre_BoomerAMGRelax7Jacobi (src/parcsr_ls/par_relax.c:1177-1254)
+// DOT: the sweep is the last operation of a preconditioner application z = C r inside PCG, so gamma = <r, z>
+// (src/krylov/pcg.c:737) is reduced here, while z_i is in a register, instead of in a pass of its own.
+template <bool DOT>
+struct EpiJacobiT {
+   static constexpr int NRED = DOT ? 1 : 0;
+   EPI_PLAIN_X
+   double w; const double *f; const double *l1; const double *u_in; double *u_out; const double *dw;
+   __device__ void operator()(int r, double t, double *red) const
+   {
+      const double un = u_in[r] + (w * (f[r] - t)) / l1[r];
+      u_out[r] = un;
+      if (DOT) { red[0] = fma(dw[r], un, red[0]); }
    }
 };
 // Chebyshev first step (src/parcsr_ls/par_cheby.c:275-283,318-341):
@@ -54,15 +84,21 @@ struct EpiChebyFirst {
 };
 // Chebyshev inner step (par_cheby.c:284-297,344-371): u_i = c_i*r + ds.*t ; then either
 //   out = ds.*u_i (next SpMV input)   or   u += ds.*u_i (last step)
-struct EpiChebyStep {
-   static constexpr int NRED = 0;
+template <bool DOT>
+struct EpiChebyStepT {
+   static constexpr int NRED = DOT ? 1 : 0;
    EPI_PLAIN_X
-   int scale; int last; double c; const double *ds; const double *rv; double *out; double *u;
-   __device__ void operator()(int r, double t, double *) const
+   int scale; int last; double c; const double *ds; const double *rv; double *out; double *u; const double *dw;
+   __device__ void operator()(int r, double t, double *red) const
    {
       double ui = scale ? c * rv[r] + ds[r] * t : c * rv[r] + t;
       double su = scale ? ds[r] * ui : ui;
-      if (last) { u[r] = u[r] + su; }
+      if (last)
+      {
+         const double un = u[r] + su;
+         u[r] = un;
+         if (DOT) { red[0] = fma(dw[r], un, red[0]); }      // last step of the last sweep: <r, z> of PCG
+      }
       else      { out[r] = su; }
    }
 };
@@ -102,17 +138,20 @@ struct EpiGsFirst {
 };
 // inner stage over the strict lower triangle (par_relax.c:1562-1585): z' = t/d ; u += mult*z'
 // (first inner stage also applies the pending u += z0)
-struct EpiGsInner {
-   static constexpr int NRED = 0;
+template <bool DOT>
+struct EpiGsInnerT {
+   static constexpr int NRED = DOT ? 1 : 0;
    EPI_PLAIN_X
-   int first; double mult; const double *d; const double *z_in; double *z_out; double *u;
-   __device__ void operator()(int r, double t, double *) const
+   int first; double mult; const double *d; const double *z_in; double *z_out; double *u; const double *dw;
+   __device__ void operator()(int r, double t, double *red) const
    {
       double zn = t / d[r];
       double uu = u[r];
       if (first) { uu = uu + z_in[r]; }
-      u[r] = uu + mult * zn;
+      const double un = uu + mult * zn;
+      u[r] = un;
       z_out[r] = zn;
+      if (DOT) { red[0] = fma(dw[r], un, red[0]); }
    }
 };
 
@@ -154,6 +193,19 @@ int op_matvec_dot(b200_parcsr *A, const double *x, double *y, double *d_out)
    return run_rows(A, A->diag, A->offd, true, x, e, d_out);
 }
 
+bool op_can_fuse_gather(const b200_parcsr *A)
+{
+   // (the NCCL baseline path packs the raw vector with its own kernel: no composite operands there)
+   return (A->num_sends + A->num_recvs) == 0 || A->ch_fwd != nullptr;
+}
+
+int op_matvec_dot_direction(b200_parcsr *A, const double *d_beta, const int *d_iter, const double *z,
+                            double *pbuf0, double *pbuf1, double *s, double *d_out)
+{
+   EpiMatvecDotDir e{d_beta, d_iter, z, pbuf0, pbuf1, s, 0.0, nullptr, nullptr};
+   return run_rows(A, A->diag, A->offd, true, z, e, d_out);
+}
+
 struct FScaleInPlace { static constexpr int NRED = 0; __device__ void init() {} double beta; double *y;
    __device__ void operator()(int i, double *) const { y[i] = beta * y[i]; } };
 
@@ -183,7 +235,7 @@ int op_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, doubl
 }
 
 int op_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
-                const double *u_in, double *u_out, int zero_guess)
+                const double *u_in, double *u_out, int zero_guess, const FusedDot *fd)
 {
    if (zero_guess)
    {
@@ -191,12 +243,18 @@ int op_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
       FZero fz{w, f, l1, u_out};
       return run_ewise(A->ctx, A->n_rows, fz, nullptr);
    }
-   EpiJacobi e{w, f, l1, u_in, u_out};
+   if (fd && fd->with)
+   {
+      EpiJacobiT<true> e{w, f, l1, u_in, u_out, fd->with};
+      *fd->done = true;
+      return run_rows(A, A->diag, A->offd, true, u_in, e, fd->out);
+   }
+   EpiJacobiT<false> e{w, f, l1, u_in, u_out, nullptr};
    return run_rows(A, A->diag, A->offd, true, u_in, e, nullptr);
 }
 
 int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *coefs_h, int order,
-             int scale, double *u, double *v, double *r, double *tmp, int zero_guess)
+             int scale, double *u, double *v, double *r, double *tmp, int zero_guess, const FusedDot *fd)
 {
    if (order > 4) { order = 4; }
    if (order < 1) { order = 1; }
@@ -205,8 +263,7 @@ int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *co
    const int n = A->n_rows;
    int i_first = k - 1;
    double *in = tmp, *out = v;
-   // (the NCCL baseline path packs the raw vector with its own kernel, so it keeps the unfused form)
-   const bool can_fuse = (A->num_sends + A->num_recvs) == 0 || A->ch_fwd != nullptr;
+   const bool can_fuse = op_can_fuse_gather(A);
    if (zero_guess && k >= 1 && can_fuse)
    {
       // first elementwise step fused into the first polynomial SpMV (see EpiChebyZero)
@@ -234,20 +291,29 @@ int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *co
    }
    for (int i = i_first; i >= 0; i--)
    {
-      EpiChebyStep e{scale, i == 0 ? 1 : 0, coefs_h[i], ds, r, out, u};
       if (i == 0 && zero_guess)
       {
          // u == 0: write instead of accumulate (same value: 0 + x == x)
          B200_TRY(vec_fill(c, n, 0.0, u));
       }
-      B200_TRY(run_rows(A, A->diag, A->offd, true, in, e, nullptr));
+      if (i == 0 && fd && fd->with)
+      {
+         EpiChebyStepT<true> e{scale, 1, coefs_h[i], ds, r, out, u, fd->with};
+         *fd->done = true;
+         B200_TRY(run_rows(A, A->diag, A->offd, true, in, e, fd->out));
+      }
+      else
+      {
+         EpiChebyStepT<false> e{scale, i == 0 ? 1 : 0, coefs_h[i], ds, r, out, u, nullptr};
+         B200_TRY(run_rows(A, A->diag, A->offd, true, in, e, nullptr));
+      }
       double *t = in; in = out; out = t;
    }
    return B200_OK;
 }
 
 int op_gs2(b200_parcsr *A, const double *f, double w, int inner, double *u, double *z, double *tmp,
-           int zero_guess)
+           int zero_guess, const FusedDot *fd)
 {
    B200_TRY(parcsr_ensure_L(A));
    if (A->zero_diagonal)
@@ -274,8 +340,17 @@ int op_gs2(b200_parcsr *A, const double *f, double w, int inner, double *u, doub
    double *zin = z, *zout = tmp;
    for (int k = 0; k < inner; k++)
    {
-      EpiGsInner e{k == 0 ? 1 : 0, mult, d, zin, zout, u};
-      B200_TRY(run_rows(A, A->lower, A->lower, false, zin, e, nullptr));
+      if (k == inner - 1 && fd && fd->with)
+      {
+         EpiGsInnerT<true> e{k == 0 ? 1 : 0, mult, d, zin, zout, u, fd->with};
+         *fd->done = true;
+         B200_TRY(run_rows(A, A->lower, A->lower, false, zin, e, fd->out));
+      }
+      else
+      {
+         EpiGsInnerT<false> e{k == 0 ? 1 : 0, mult, d, zin, zout, u, nullptr};
+         B200_TRY(run_rows(A, A->lower, A->lower, false, zin, e, nullptr));
+      }
       mult = -mult;
       double *t = zin; zin = zout; zout = t;
    }
@@ -326,8 +401,8 @@ extern "C" int b200_relax_l1jacobi(b200_parcsr *A, const double *f, const double
                                    double *u, double *tmp, int zero_guess)
 {
    ARG_CHECK(A != nullptr && f != nullptr && l1 != nullptr && u != nullptr && tmp != nullptr);
-   if (zero_guess) { return op_l1jacobi(A, f, l1, w, u, u, 1); }
-   B200_TRY(op_l1jacobi(A, f, l1, w, u, tmp, 0));
+   if (zero_guess) { return op_l1jacobi(A, f, l1, w, u, u, 1, nullptr); }
+   B200_TRY(op_l1jacobi(A, f, l1, w, u, tmp, 0, nullptr));
    return b200_vec_copy(A->ctx, A->n_rows, tmp, u);
 }
 
@@ -338,14 +413,14 @@ extern "C" int b200_relax_cheby(b200_parcsr *A, const double *f, const double *d
    ARG_CHECK(A != nullptr && f != nullptr && coefs_h != nullptr && u != nullptr && v != nullptr &&
              r != nullptr && tmp != nullptr);
    ARG_CHECK(!scale || ds != nullptr);
-   return op_cheby(A, f, ds, coefs_h, order, scale, u, v, r, tmp, zero_guess);
+   return op_cheby(A, f, ds, coefs_h, order, scale, u, v, r, tmp, zero_guess, nullptr);
 }
 
 extern "C" int b200_relax_2stage_gs(b200_parcsr *A, const double *f, double w, int inner,
                                     double *u, double *z, double *tmp, int zero_guess)
 {
    ARG_CHECK(A != nullptr && f != nullptr && u != nullptr && z != nullptr && tmp != nullptr && inner >= 1);
-   return op_gs2(A, f, w, inner, u, z, tmp, zero_guess);
+   return op_gs2(A, f, w, inner, u, z, tmp, zero_guess, nullptr);
 }
 
 // host-vector SpMV: what HYPRE_ParCSRMatrixMatvec costs end to end for host-resident

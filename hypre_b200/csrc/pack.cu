@@ -27,7 +27,7 @@ static int g_zpad = env_int("B200_ZPAD", 1) != 0;
 // launch options of the thread-per-row kernels (rowlaunch.cuh)
 int g_rows_chunked = env_int("B200_CHUNKED", 1);
 int g_pat_regs = env_int("B200_PAT_REGS", 0) != 0;
-int g_rows_waves = std::min(4, std::max(1, env_int("B200_PAT_WAVES", 1)));    // grid of the pattern kernel in waves of 148 x 8 blocks
+int g_rows_waves = std::min(4, std::max(1, env_int("B200_PAT_WAVES", 4)));    // grid of the pattern kernel in waves of 148 x 8 blocks
 
 extern "C" int b200_set_compression(int mode, int no_padding_markers)
 {

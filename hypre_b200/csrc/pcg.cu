@@ -9,7 +9,7 @@
 #include <cmath>
 #include <cfloat>
 
-int     amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result);
+int     amg_precond_ptr(b200_amg *a, const double *f, double *u, double **u_result, const FusedDot *fd = nullptr);
 int     amg_precond_cycles(const b200_amg *a);
 
 // scalar slots in ctx->d_scalars
@@ -33,8 +33,10 @@ struct FPcgUpdate {
    static constexpr int NRED = 1;
    int skip_break; const double *scal; const double *p; const double *s; double *x; double *r;
    double alpha; bool stop;      // set by init(), once per thread
+   const int *iter; const double *p_alt;     // fused-direction mode: p is the buffer EpiMatvecDotDir just wrote
    __device__ void init()
    {
+      if (iter != nullptr && (*iter & 1)) { p = p_alt; }
       const double sdotp = scal[S_SDOTP];
       alpha = scal[S_GAMMA] / sdotp;
       stop = (sdotp == 0.0);
@@ -135,17 +137,23 @@ static int dot_to(b200_ctx *c, int n, const double *x, const double *y, int slot
 }
 
 // z = C r.  Returns in *z_out the buffer that holds the result (z or the AMG's level-0 alternate).
+// dot_slot >= 0: <r, z> is wanted in that scalar slot; *dot_done tells whether the preconditioner's last launch
+// reduced it (the caller runs a dot kernel otherwise).
 static int apply_precond(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_pcg_params *prm,
-                         const double *r, double *z, double **z_out)
+                         const double *r, double *z, double **z_out, int dot_slot = -1, bool *dot_done = nullptr)
 {
    const int n = A->n_rows;
    *z_out = z;
-   if (amg) { return amg_precond_ptr(amg, r, z, z_out); }
+   bool done_local = false;
+   FusedDot fd{r, dot_slot >= 0 ? c->d_scalars + dot_slot : nullptr, dot_done ? dot_done : &done_local};
+   if (dot_done) { *dot_done = false; }
+   if (amg) { return amg_precond_ptr(amg, r, z, z_out, dot_slot >= 0 ? &fd : nullptr); }
    if (prm->diag_scale)
    {
       B200_TRY(parcsr_ensure_L(A));
       FDiagScaleDot f{A->d_diagonal, r, z};
-      return run_ewise(c, n, f, c->d_scalars + S_TMP);
+      if (dot_slot >= 0) { *fd.done = true; }
+      return run_ewise(c, n, f, c->d_scalars + (dot_slot >= 0 ? dot_slot : S_TMP));
    }
    return b200_vec_copy(c, n, r, z);   // identity: hypre_ParKrylovIdentity
 }
@@ -154,10 +162,42 @@ static int apply_precond(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_
 struct PcgIter {
    b200_ctx *c; b200_parcsr *A; b200_amg *amg; const b200_pcg_params *prm;
    int n; double *p, *s, *r, *x; long long epoch;
+   // fused mode (single rank or peer-memory halo): the direction update lives inside s = A p (two p buffers
+   // alternate with the parity of the device's iteration counter), <r, z> inside the preconditioner's last launch
+   bool fused; double *p2, *zbuf; double *z;     // z: where z = C r of the PREVIOUS step lives
 };
+
+// One iteration in fused form: 3 launches around the preconditioner instead of 5 (no stand-alone dot, no direction
+// pass): [s = A (z + beta p), p' = z + beta p, <s,p'>] [x += alpha p', r -= alpha s, <r,r>] [z = C r with <r,z>] [check]
+static int pcg_enqueue_iteration_fused(const PcgIter &it)
+{
+   b200_ctx *c = it.c;
+   B200_TRY(op_matvec_dot_direction(it.A, c->d_scalars + S_BETA, c->d_iter, it.z, it.p, it.p2, it.s, c->d_scalars + S_SDOTP));
+   B200_TRY(scalars_allreduce(c, c->d_scalars + S_SDOTP, 1));
+   {
+      // even count of finished iterations: the new p is p2 (EpiMatvecDotDir::init)
+      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p2, it.s, it.x, it.r, 0.0, false, c->d_iter, it.p};
+      B200_TRY(run_ewise(c, it.n, f, c->d_scalars + S_IPROD));
+   }
+   double *z = nullptr;
+   bool dot_done = false;
+   B200_TRY(apply_precond(c, it.A, it.amg, it.prm, it.r, it.zbuf, &z, S_GAMMA_NEW, &dot_done));
+   if (z != it.z)
+   {
+      b200_set_error("PCG: the preconditioner's result moved between applications");
+      return B200_ERR_ARG;
+   }
+   if (!dot_done) { B200_TRY(vec_dot(c, it.n, it.r, z, c->d_scalars + S_GAMMA_NEW)); }
+   B200_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 2));
+   LAUNCH(c, pcg_check_kernel, 1, 1, 0, c->d_scalars, c->d_stop, c->d_iter, (PcgRecord *)c->d_ring,
+          it.prm->two_norm, it.prm->skip_break, it.prm->max_iter);
+   CHECK_LAUNCH();
+   return B200_OK;
+}
 
 static int pcg_enqueue_iteration(const PcgIter &it)
 {
+   if (it.fused) { return pcg_enqueue_iteration_fused(it); }
    b200_ctx *c = it.c;
    double *z = nullptr;
    // s = A p ; sdotp = <s,p>
@@ -165,7 +205,7 @@ static int pcg_enqueue_iteration(const PcgIter &it)
    B200_TRY(scalars_allreduce(c, c->d_scalars + S_SDOTP, 1));
    // x += alpha p ; r -= alpha s ; <r,r>
    {
-      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r, 0.0, false};
+      FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r, 0.0, false, nullptr, nullptr};
       B200_TRY(run_ewise(c, it.n, f, c->d_scalars + S_IPROD));
    }
    // s = C r ; gamma = <r,s>
@@ -206,7 +246,7 @@ static int pcg_launch_iteration(const PcgIter &it, int i)
    if (!pcg_graph_enabled(c) || i < 2) { return pcg_enqueue_iteration(it); }
    const void *key[8] = {it.A, it.amg, it.x, it.p, it.s, it.r,
                          (const void *)(size_t)(it.prm->two_norm * 64 + it.prm->skip_break * 8 + it.prm->diag_scale +
-                                                (it.amg ? 4096 * amg_precond_cycles(it.amg) : 0)),
+                                                (it.fused ? 128 : 0) + (it.amg ? 4096 * amg_precond_cycles(it.amg) : 0)),
                          (const void *)(size_t)it.prm->max_iter};
    if (c->pcg_graph == nullptr || memcmp(key, c->pcg_graph_key, sizeof(key)) != 0)
    {
@@ -266,16 +306,23 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
    double *h = c->h_scalars;
    memset(res, 0, sizeof(*res));
 
-   double *p = nullptr, *s = nullptr, *r = nullptr;
+   double *p = nullptr, *s = nullptr, *r = nullptr, *p2 = nullptr, *zbuf = nullptr;
    B200_TRY(ctx_workspace(c, WS_PCG_P, n, &p));
    B200_TRY(ctx_workspace(c, WS_PCG_S, n, &s));
    B200_TRY(ctx_workspace(c, WS_PCG_R, n, &r));
+   static const int fuse_env = []() { const char *e = getenv("B200_PCG_FUSE"); return e ? atoi(e) : 1; }();
+   const bool fused = fuse_env != 0 && op_can_fuse_gather(A);
+   if (fused)
+   {
+      B200_TRY(ctx_workspace(c, WS_PCG_P2, n, &p2));
+      B200_TRY(ctx_workspace(c, WS_PCG_Z, n, &zbuf));
+   }
    int status = B200_OK;
    int i = 0, queued = 0;
    double bi_prod = 0.0, i_prod = 0.0, i_prod_0 = 0.0, gamma = 0.0, eps = 0.0;
    double *z = nullptr;
    const long long epoch = ++c->pcg_epoch;
-   PcgIter it{c, A, amg, prm, n, p, s, r, x, epoch};
+   PcgIter it{c, A, amg, prm, n, p, s, r, x, epoch, fused, p2, zbuf, nullptr};
    constexpr int LOOKAHEAD = 1;     // iterations queued beyond the one the host is waiting for
 
 #define PCG_TRY(expr) do { status = (expr); if (status != B200_OK) goto done; } while (0)
@@ -317,9 +364,21 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
 
    // r = b - A x ; p = C r ; gamma = <r,p>
    PCG_TRY(op_matvec(A, -1.0, x, 1.0, b, r));
-   PCG_TRY(apply_precond(c, A, amg, prm, r, p, &z));
-   if (z != p) { PCG_TRY(b200_vec_copy(c, n, z, p)); }
-   PCG_TRY(dot_to(c, n, r, p, S_GAMMA));
+   if (fused)
+   {
+      // z = C r stays where the preconditioner leaves it; the first fused SpMV forms p = z + 0 * 0
+      PCG_TRY(apply_precond(c, A, amg, prm, r, zbuf, &z));
+      it.z = z;
+      PCG_TRY(vec_fill(c, n, 0.0, p));
+      CUDA_TRY(cudaMemsetAsync(c->d_scalars + S_BETA, 0, sizeof(double), c->stream));
+      PCG_TRY(dot_to(c, n, r, z, S_GAMMA));
+   }
+   else
+   {
+      PCG_TRY(apply_precond(c, A, amg, prm, r, p, &z));
+      if (z != p) { PCG_TRY(b200_vec_copy(c, n, z, p)); }
+      PCG_TRY(dot_to(c, n, r, p, S_GAMMA));
+   }
    PCG_TRY(dot_to(c, n, r, r, S_IPROD));
    // S_IPROD (9) and S_GAMMA (11) are not adjacent: reduce the span 9..11 (S_GAMMA_NEW is scratch here)
    PCG_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 3));

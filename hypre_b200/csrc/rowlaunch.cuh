@@ -28,15 +28,6 @@ static inline int rows_grid(long long work, int per_block, int waves = 4)
 // b200_set_kernel_options): slice-to-block mapping and the PAT8 instantiation
 extern int g_rows_chunked, g_pat_regs;
 
-// the pattern dictionary of a CFMT_PAT8 block as a kernel parameter (host copy kept in the DMat)
-static inline PatTab pat_tab_of(const DMat &D)
-{
-   PatTab t;
-   memset(&t, 0, sizeof(t));
-   memcpy(t.e, D.h_dict.data(), std::min(sizeof(t.e), D.h_dict.size() * sizeof(double)));
-   return t;
-}
-
 static inline HaloArgs no_halo()
 {
    HaloArgs h;
@@ -60,20 +51,17 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
    //  and the reduction publishes the zero)
    if (D.layout >= 1 || D.n_rows == 0)
    {
-      // the pattern kernel runs as ONE wave of resident blocks, each walking a long contiguous run of slices
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32, D.cfmt == CFMT_PAT8 ? g_rows_waves : 4);
       HaloArgs hh = h;
       hh.chunked = D.cfmt == CFMT_PAT8 ? g_rows_chunked : (g_rows_chunked > 1);
       const int variant = D.cfmt == CFMT_PAT8 ? (g_pat_regs ? 1 : 0) : (D.zpad ? 1 : 0);
       switch (D.cfmt ? D.cfmt + 8 * variant : 0)
       {
-#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, NoTab()); break;
-#define CASE_P(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, pat_tab_of(D)); break;
-         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_P(CFMT_PAT8)
-         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_P(CFMT_PAT8 + 8)
+#define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
+         CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_C(CFMT_PAT8)
+         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_C(CFMT_PAT8 + 8)
 #undef CASE_C
-#undef CASE_P
-         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc, NoTab()); break;
+         default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
       }
    }
    else
@@ -83,7 +71,7 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
 #define CASE_T(TT)                                                                            \
    case TT: {                                                                                 \
       int grid = rows_grid(D.n_rows, ROWK_BLOCK / TT);                                        \
-      LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc, NoTab());   \
+      LAUNCH(ctx, (rows_kernel<TT, HALO, Epi>), grid, ROWK_BLOCK, 0, V, h, x, epi, rc);       \
    } break;
          CASE_T(1) CASE_T(2) CASE_T(4) CASE_T(8) CASE_T(16) CASE_T(32)
 #undef CASE_T

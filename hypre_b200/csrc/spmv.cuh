@@ -7,7 +7,6 @@
 #pragma once
 #include "common.cuh"
 #include "p2p.cuh"
-#include <type_traits>
 
 constexpr int ROWK_BLOCK = 256;
 
@@ -101,6 +100,10 @@ __device__ __forceinline__ void grid_reduce(double (&red)[NRED > 0 ? NRED : 1], 
 // The gathered operand x_j is obtained through the epilogue functor: xval(x, j).  Plain operators
 // read x[j]; a fused operator may compute it from other vectors on the fly (Chebyshev with a zero
 // initial guess: x_j = ds_j * (c * (ds_j * f_j)), so the vectors r and tmp are never materialised).
+// An epilogue may carry per-thread state prepared once at kernel start (device-resident scalars read into
+// registers): optional member init(), called on the kernel's own copy of the functor.
+template <class E> __device__ __forceinline__ auto epi_init(E &e, int) -> decltype(e.init(), void()) { e.init(); }
+template <class E> __device__ __forceinline__ void epi_init(E &, long) {}
 #define EPI_PLAIN_X __device__ __forceinline__ double xval(const double *__restrict__ x, int j) const { return __ldg(x + j); }
 struct XPlain { EPI_PLAIN_X };
 // sliced-ELL, one thread per row (lane = row within the 32-row slice).
@@ -263,73 +266,45 @@ __device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off
 // Padding entries are patterns (delta of the row's own last entry, 0.0): no predicate anywhere.  Level 0 of a
 // stencil problem then streams little more than x and y.
 constexpr unsigned PAT_LANE = 0xFFu;
-constexpr int PAT_MAX = 254;
-// The pattern dictionary travels as a KERNEL PARAMETER (constant bank): header codes are warp-uniform, so
-// their (value, delta) come through LDC -- no load/store-unit traffic at all (ncu on the first version:
-// the shared-memory lookups were 18 of the 33 LSU wavefronts per slice).  Lane words (codes that differ
-// between lanes) are looked up in the shared-memory copy, where divergent addresses cost nothing extra.
-struct PatTab { double2 e[PAT_MAX]; };
-struct NoTab { };
 
-// one header word = up to 4 entries; cnt < 4 only in a slice's last word (warp-uniform)
+// one header word = 4 entries (entries past the longest row of the slice are padding patterns like any other)
 template <class XF>
-__device__ __forceinline__ double pat_word(unsigned h, int cnt, const unsigned *&lp, int row, double t,
-                                           const double *__restrict__ x, const XF &xf, const PatTab &tab,
-                                           const double2 *s_pat)
+__device__ __forceinline__ double pat_word(unsigned h, const unsigned *&lp, int row, double t,
+                                           const double *__restrict__ x, const XF &xf, const double2 *s_pat)
 {
    const unsigned m = __vcmpeq4(h, 0xFFFFFFFFu);          // 0xFF in the bytes marked PAT_LANE (warp-uniform)
-   double xv[4];
-   if (m == 0u)
+   if (m) { const unsigned lw = ld_stream_u32(lp); lp += 32; h = (lw & m) | (h & ~m); }
+   double v[4], xv[4];
+#pragma unroll
+   for (int j = 0; j < 4; j++)
    {
-      // uniform codes: deltas first (gathers in flight), values at the fma -- the constant bank costs no registers
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         if (j < cnt) { xv[j] = xf.xval(x, row + __double2loint(tab.e[(h >> (8 * j)) & 0xFFu].y)); }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; j++) { if (j < cnt) { t = fma(tab.e[(h >> (8 * j)) & 0xFFu].x, xv[j], t); } }
+      const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
+      v[j] = pd.x;
+      xv[j] = xf.xval(x, row + __double2loint(pd.y));
    }
-   else
-   {
-      const unsigned lw = ld_stream_u32(lp);
-      lp += 32;
-      h = (lw & m) | (h & ~m);
-      double v[4];
 #pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         if (j < cnt)
-         {
-            const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
-            v[j] = pd.x;
-            xv[j] = xf.xval(x, row + __double2loint(pd.y));
-         }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; j++) { if (j < cnt) { t = fma(v[j], xv[j], t); } }
-   }
+   for (int j = 0; j < 4; j++) { t = fma(v[j], xv[j], t); }
    return t;
 }
 
 // h0 = the first 16 bytes of the slice header (already in registers), hdr = the header in memory.
-// word 0: bits 0-7 header words, 8-9 entries of the last word - 1, 10-31 first lane-word group.
+// word 0: bits 0-7 header words, 8-9 entries of the last word - 1 (the host decoder stops there; the padding
+// entries behind them multiply 0.0 with a column of the row itself), 10-31 first lane-word group.
+// (Measured and dropped, profiles/r02_fmt_probe_*.jsonl: the dictionary as a kernel parameter read through
+// indexed LDC -- twice as slow as the shared-memory lookups; a grid of one wave of resident blocks -- 1.5x slower
+// than four waves; 40 / 48 registers per thread -- slower than 32.)
 template <class XF>
 __device__ __forceinline__ double rowsum_pat(const MatView &D, const uint4 &h0, const uint4 *hdr, int lane, int row,
-                                             const double *__restrict__ x, const XF &xf, const PatTab &tab,
-                                             const double2 *s_pat)
+                                             const double *__restrict__ x, const XF &xf, const double2 *s_pat)
 {
    const unsigned nw = h0.x & 0xFFu;
-   const int last_cnt = (int)((h0.x >> 8) & 3u) + 1;
    const unsigned *lp = reinterpret_cast<const unsigned *>(D.c_idx) + (size_t)(h0.x >> 10) * 32 + lane;
-   const unsigned *hw = reinterpret_cast<const unsigned *>(hdr) + 1;
    double t = 0.0;
-#pragma unroll 1
-   for (unsigned i = 0; i < nw; i++)
-   {
-      const unsigned h = i == 0 ? h0.y : i == 1 ? h0.z : i == 2 ? h0.w : __ldg(hw + i);
-      t = pat_word(h, i + 1 == nw ? last_cnt : 4, lp, row, t, x, xf, tab, s_pat);
-   }
+   if (nw > 0) { t = pat_word(h0.y, lp, row, t, x, xf, s_pat); }
+   if (nw > 1) { t = pat_word(h0.z, lp, row, t, x, xf, s_pat); }
+   if (nw > 2) { t = pat_word(h0.w, lp, row, t, x, xf, s_pat); }
+   const unsigned *hw = reinterpret_cast<const unsigned *>(hdr) + 1;
+   for (unsigned i = 3; i < nw; i++) { t = pat_word(__ldg(hw + i), lp, row, t, x, xf, s_pat); }
    return t;
 }
 
@@ -472,10 +447,10 @@ __device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const
 // Thread-per-row mapping: h.chunked != 0 gives every block ONE contiguous run of slices (its warps walk it
 // 8 slices at a time), so that the gathers of neighbouring rows -- the +-nx lines of a stencil -- meet in the
 // SM's L1 instead of each costing an L2 read; 0 = grid stride.
-template <int T, int HALO, class Epi, class Tab>
+template <int T, int HALO, class Epi>
 __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
                                            const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
-                                           int vblock, const Tab &tab, const double2 *s_tab)
+                                           int vblock, const double2 *s_tab = nullptr)
 {
    // vblock: the block's position in this range's grid (a permutation of blockIdx.x), so that
    // short ranges do not all land on the low-numbered blocks, which also carry the put phase
@@ -500,12 +475,9 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          s_end = g_end;
          step = gridDim.x * wpb;
       }
-      // PAT8, second instantiation (more registers): the header of the warp's next slice is requested while
-      // this one is processed
-      constexpr bool PREFETCH = T < 0 && FMT == CFMT_PAT8 && ((-T) >> 3) == 1;
       const uint4 *hdr = reinterpret_cast<const uint4 *>(D.c_code);
       uint4 h_cur = make_uint4(0u, 0u, 0u, 0u);
-      if (PREFETCH && slice < s_end) { h_cur = __ldg(hdr + (size_t)slice * D.aux); }
+      if (FMT == CFMT_PAT8 && slice < s_end) { h_cur = __ldg(hdr + (size_t)slice * D.aux); }
       for (; slice < s_end; slice += step)
       {
          int row = (slice << 5) + lane;
@@ -515,20 +487,11 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          if (T == 0) { t = rowsum_sell(D, slice, lane, x, epi); }
          else if (FMT == CFMT_PAT8)
          {
-            if (PREFETCH)
-            {
-               uint4 h_next = make_uint4(0u, 0u, 0u, 0u);
-               if (slice + step < s_end) { h_next = __ldg(hdr + (size_t)(slice + step) * D.aux); }
-               t = rowsum_pat(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi,
-                              reinterpret_cast<const PatTab &>(tab), s_tab);
-               h_cur = h_next;
-            }
-            else
-            {
-               const uint4 *hs = hdr + (size_t)slice * D.aux;
-               t = rowsum_pat(D, __ldg(hs), hs, lane, live ? row : D.n_rows - 1, x, epi,
-                              reinterpret_cast<const PatTab &>(tab), s_tab);
-            }
+            // the header of the warp's next slice travels while this one is processed
+            uint4 h_next = make_uint4(0u, 0u, 0u, 0u);
+            if (slice + step < s_end) { h_next = __ldg(hdr + (size_t)(slice + step) * D.aux); }
+            t = rowsum_pat(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi, s_tab);
+            h_cur = h_next;
          }
          else
          {
@@ -600,16 +563,17 @@ template <int T> struct RowsKernelCfg {
    static constexpr int VAR = T < 0 ? ((-T) >> 3) : 0;
    static constexpr bool PAT = FMT == CFMT_PAT8;
    static constexpr bool SMEM_TAB = PAT || (VAR == 1 && FMT == CFMT_VAL8);
-   static constexpr int MIN_BLOCKS = PAT ? (VAR == 1 ? 5 : 6) : 8;
-   typedef typename std::conditional<PAT, PatTab, NoTab>::type Tab;     // pattern dictionary as a kernel parameter
+   static constexpr int MIN_BLOCKS = (PAT && VAR == 1) ? 6 : 8;
 };
 
 // All rows of the diag block.
 template <int T, int HALO, class Epi>
 __global__ void __launch_bounds__(ROWK_BLOCK, RowsKernelCfg<T>::MIN_BLOCKS)
-rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx rc, typename RowsKernelCfg<T>::Tab tab)
+rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi_arg, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
+   Epi epi = epi_arg;
+   epi_init(epi, 0);
    double red[Epi::NRED > 0 ? Epi::NRED : 1];
 #pragma unroll
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
@@ -626,7 +590,7 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
    }
    const int n_groups = (D.n_rows + 31) >> 5;
    const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
-   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, tab, s_tab); }
+   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, s_tab); }
    else
    {
       if (h.ch.n_out > 0)
@@ -641,9 +605,9 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
       // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
       // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
       const int G = gridDim.x, b = blockIdx.x;
-      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, tab, s_tab);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, tab, s_tab);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, tab, s_tab);
+      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, s_tab);
    }
    grid_reduce<Epi::NRED>(red, rc);
    if (P2P && h.ch.n_in > 0 && !(h.dbg & 4)) { p2p_consumer_done(h.ch); }
@@ -653,9 +617,11 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi, RedCtx
 template <class Epi>
 __global__ void __launch_bounds__(ROWK_BLOCK)
 rowlist_kernel(MatView D, MatView O, const int *__restrict__ rows, int n_list,
-               const double *__restrict__ x, const double *__restrict__ xg, Epi epi, RedCtx rc)
+               const double *__restrict__ x, const double *__restrict__ xg, Epi epi_arg, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
+   Epi epi = epi_arg;
+   epi_init(epi, 0);
    double red[Epi::NRED > 0 ? Epi::NRED : 1];
 #pragma unroll
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }

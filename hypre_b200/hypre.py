@@ -12,7 +12,7 @@ import os
 
 import numpy as np
 
-from . import LIB_BRIDGE, LIB_BRIDGE_MP, LIB_HYPRE_B200, LIB_HYPRE_B200_MP, LIB_HYPRE_REF, capi
+from . import LIB_BRIDGE, LIB_BRIDGE_MP, LIB_HYPRE_B200, LIB_HYPRE_B200_MP, LIB_HYPRE_REF, LIB_REF_BRIDGE, capi
 
 _lib = None
 # Reference-only mode (bench.py --impl reference, the cpu_baseline leg): this process loads the oracle's separately
@@ -57,7 +57,7 @@ def lib():
     if not os.path.exists(path):
         raise capi.B200Error("%s is missing (built from hypre_b200/host or oracle/ with the reference sources)" % path)
     main = C.CDLL(path, mode=C.RTLD_GLOBAL)
-    bridge_path = LIB_BRIDGE_MP if NATIVE else LIB_BRIDGE
+    bridge_path = LIB_REF_BRIDGE if REFERENCE_ONLY else LIB_BRIDGE_MP if NATIVE else LIB_BRIDGE
     if not os.path.exists(bridge_path):
         raise capi.B200Error("%s is missing (built from hypre_b200/host)" % bridge_path)
     L = _Libs(main, C.CDLL(bridge_path, mode=C.RTLD_GLOBAL))

@@ -21,7 +21,7 @@ from hypre_b200 import capi, hypre as H   # noqa: E402
 # name: (compression mode, no_padding_markers, [(chunked, pat_regs), ...] launch options timed on that upload)
 CONFIGS = {
     # pat_regs: bit 0 = instantiation with header prefetch (48 registers), bits 1-3 = waves of resident blocks in the grid
-    "pat8": (-1, 1, [(1, 2), (1, 8), (1, 3), (1, 9), (0, 2)]),
+    "pat8": (-1, 1, [(1, 8), (1, 9)]),
     "val_markers": (1, 0, [(1, 0), (0, 0)]),
     "val_zpad": (1, 1, [(1, 0), (0, 0)]),
     "plain": (0, 0, [(1, 0), (0, 0)]),
@@ -106,7 +106,7 @@ def main():
         for v in [vx, vf, vl1] + w:
             v.free()
     capi.check(L.b200_set_compression(-1, 1))
-    capi.check(L.b200_set_kernel_options(1, 2))
+    capi.check(L.b200_set_kernel_options(1, 8))
 
 
 if __name__ == "__main__":

@@ -245,7 +245,7 @@ def test_compressed_storage_is_lossless(H, ctx, hier, layout, mode, zpad, chunke
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 1)
-        L.b200_set_kernel_options(1, 2)
+        L.b200_set_kernel_options(1, 8)
 
 
 _BITS = {}      # SpMV result of the first format run on (matrix, layout): the others must reproduce it bit for bit
@@ -289,7 +289,7 @@ def test_smoothers_on_compressed_storage(H, ctx, hier, mode, zpad, chunked, pat_
     finally:
         L.b200_set_layout_override(-1, -1)
         L.b200_set_compression(-1, 1)
-        L.b200_set_kernel_options(1, 2)
+        L.b200_set_kernel_options(1, 8)
 
 
 def vec_err_max(a, b):
