@@ -132,6 +132,8 @@ def lib():
         "b200_cycle_sweep_counts": (i, [i, i, i, vp, vp]),
         "b200_cycle_exchange_counts": (i, [i, i, i, vp, vp, i, i, vp, vp, vp]),
         "b200_parcsr_halo_info": (i, [vp, c_int_p, c_int_p, c_int_p, c_int_p]),
+        "b200_set_tail_limit": (i, [ll]),
+        "b200_amg_tail_level": (i, [vp, c_int_p]),
         "b200_amg_level_matrix": (i, [vp, i, c_void_pp]),
         "b200_amg_level_interp": (i, [vp, i, c_void_pp]),
         "b200_amg_level_info": (i, [vp, i, c_int_p, C.POINTER(ll), C.POINTER(ll)]),

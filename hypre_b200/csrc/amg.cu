@@ -2,7 +2,9 @@
 #include "ops.cuh"
 #include "vecops.cuh"
 #include "p2p.cuh"
+#include "tail.cuh"
 #include <cmath>
+#include <climits>
 
 struct AmgLevel {
    b200_parcsr *A = nullptr, *P = nullptr;
@@ -34,6 +36,9 @@ struct b200_amg {
    // a vector all-reduce, prolongation from it is local.
    int  repl_level = 1 << 30;
    int  precond_cycles = 1;    // cycles per preconditioner application (hypre_ParAMGDataMaxIter with tol 0)
+   // levels >= tail_level run inside ONE persistent kernel per visit (tail.cuh): small CSR-vector levels without
+   // communication (all of them on one rank, the replicated ones on several); INT_MAX = none
+   int  tail_level = INT_MAX;
    bool finalized = false;
 };
 
@@ -51,6 +56,8 @@ extern "C" int b200_amg_destroy(b200_amg *a)
    if (!a) { return B200_OK; }
    cudaSetDevice(a->ctx->device);
    cudaStreamSynchronize(a->ctx->stream);
+   tail_drop_programs(a->ctx);       // recorded programs point into this hierarchy
+   a->ctx->generation++;
    for (auto &l : a->L)
    {
       b200_parcsr_destroy(l.A); b200_parcsr_destroy(l.P);
@@ -83,6 +90,7 @@ extern "C" int b200_amg_set_cycle(b200_amg *a, const int relax_type[4], const in
    ARG_CHECK(a != nullptr && relax_type != nullptr && num_sweeps != nullptr && cycle_type >= 1);
    for (int k = 0; k < 4; k++) { a->relax_type[k] = relax_type[k]; a->num_sweeps[k] = num_sweeps[k]; }
    a->cycle_type = cycle_type; a->fcycle = fcycle;
+   a->ctx->generation++;
    return B200_OK;
 }
 
@@ -90,6 +98,7 @@ extern "C" int b200_amg_set_level_relax(b200_amg *a, int level, double relax_wei
 {
    ARG_CHECK(a != nullptr && level >= 0 && level < a->num_levels && a->L[level].A != nullptr);
    AmgLevel &l = a->L[level];
+   a->ctx->generation++;
    l.relax_weight = relax_weight;
    cudaFree(l.d_l1); l.d_l1 = nullptr;
    if (l1_h) { B200_TRY(dev_upload(&l.d_l1, l1_h, (size_t)l.n)); }
@@ -102,6 +111,7 @@ extern "C" int b200_amg_set_level_cheby(b200_amg *a, int level, const double *ds
    ARG_CHECK(a != nullptr && level >= 0 && level < a->num_levels && a->L[level].A != nullptr);
    ARG_CHECK(coefs_h != nullptr && order >= 1);
    AmgLevel &l = a->L[level];
+   a->ctx->generation++;
    cudaFree(l.d_ds); l.d_ds = nullptr;
    if (ds_h) { B200_TRY(dev_upload(&l.d_ds, ds_h, (size_t)l.n)); }
    ARG_CHECK(!scale || ds_h != nullptr);
@@ -189,6 +199,15 @@ extern "C" int b200_amg_set_coarse_dense(b200_amg *a, int n_global, const double
    return B200_OK;
 }
 
+// largest level (in nonzeros of A) that joins the persistent coarse-level kernel; 0 switches the kernel off
+static long long g_tail_nnz = []() { const char *e = getenv("B200_TAIL_NNZ"); return e ? atoll(e) : 4000000LL; }();
+extern "C" int b200_set_tail_limit(long long max_nnz)
+{
+   ARG_CHECK(max_nnz >= 0);
+   g_tail_nnz = max_nnz;
+   return B200_OK;
+}
+
 static bool relax_supported(int t) { return t == 18 || t == 7 || t == 16 || t == 11 || t == 12 || t == 9; }
 
 extern "C" int b200_amg_finalize(b200_amg *a)
@@ -248,6 +267,25 @@ extern "C" int b200_amg_finalize(b200_amg *a)
    B200_TRY(b200_dev_alloc(c, maxn, &a->Ztemp));
    B200_TRY(b200_dev_alloc(c, maxn, &a->Ptemp));
    B200_TRY(b200_dev_alloc(c, maxn, &a->Rtemp));
+   // persistent coarse-level kernel: the deepest run of levels whose operators are CSR-vector blocks without
+   // communication and small enough that launch latency, not bandwidth, is what they cost
+   {
+      const long long tail_nnz = g_tail_nnz;
+      const int nl = a->num_levels;
+      a->tail_level = INT_MAX;
+      bool coarse_ok = c->nranks == 1 || a->repl_level <= nl - 1;       // no gather of the coarse right-hand side
+      auto quiet = [](const b200_parcsr *M) { return M->num_sends + M->num_recvs == 0; };
+      for (int l = nl - 1; l >= 1 && coarse_ok && tail_nnz > 0; l--)
+      {
+         const AmgLevel &L = a->L[l];
+         bool ok = L.A->diag.layout == 0 && quiet(L.A) && L.A->diag.nnz <= tail_nnz && (!L.A->hasL || L.A->lower.layout == 0);
+         if (l < nl - 1) { ok = ok && L.P->diag.layout == 0 && L.P->diagT.layout == 0 && quiet(L.P); }
+         if (!ok) { break; }
+         a->tail_level = l;
+      }
+      // a tail of one level (the dense solve alone) gains nothing
+      if (a->tail_level >= nl - 1) { a->tail_level = INT_MAX; }
+   }
    a->finalized = true;
    return B200_OK;
 }
@@ -328,8 +366,19 @@ static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const d
 // u_alt0: second level-0 buffer.  On return *u_result points at the buffer holding U[0].
 // fd (optional): <fd->with, U[0]> is reduced inside the cycle's last smoothing launch on level 0 where the
 // smoother supports it (*fd->done tells); the caller (PCG: gamma = <r, C r>) falls back to its own pass otherwise.
+static int amg_cycle_body(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result,
+                          const FusedDot *fd);
+
 static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result,
                           const FusedDot *fd = nullptr)
+{
+   const int st = amg_cycle_body(a, f, u, zero_guess, u_result, fd);
+   if (st != B200_OK && tail_recording(a->ctx)) { tail_drop_programs(a->ctx); }     // leave the recorder clean
+   return st;
+}
+
+static int amg_cycle_body(b200_amg *a, const double *f, double *u, int zero_guess, double **u_result,
+                          const FusedDot *fd)
 {
    const int nl = a->num_levels;
    CycleState s;
@@ -360,8 +409,11 @@ static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_gues
    int level = 0, cycle_param = 1;
    bool not_finished = true;
 
+   const int Lt = a->tail_level;
    while (not_finished)
    {
+      // levels >= Lt: operators are recorded, the whole visit runs as one persistent kernel (tail.cuh)
+      if (level >= Lt && !tail_recording(a->ctx)) { B200_TRY(tail_begin(a->ctx)); }
       int relax_type, num_sweep;
       if (nl > 1) { relax_type = a->relax_type[cycle_param]; num_sweep = a->num_sweeps[cycle_param]; }
       else        { relax_type = a->relax_type[0];           num_sweep = a->num_sweeps[0]; }
@@ -401,6 +453,7 @@ static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_gues
          // interpolation (par_cycle.c:751-757): U[fine] += P U[coarse]
          const int fine = level - 1, coarse = level;
          AmgLevel &L = a->L[fine];
+         if (fine < Lt && tail_recording(a->ctx)) { B200_TRY(tail_flush(a->ctx)); }      // leaving the tail
          B200_TRY(materialize_zero(a, s, coarse));
          if (s.zero[fine])
          {
@@ -421,6 +474,7 @@ static int amg_cycle_core(b200_amg *a, const double *f, double *u, int zero_gues
       }
       else { not_finished = false; }
    }
+   if (tail_recording(a->ctx)) { B200_TRY(tail_flush(a->ctx)); }
    B200_TRY(materialize_zero(a, s, 0));
    *u_result = U_cur(s, 0);
    return B200_OK;
@@ -451,6 +505,7 @@ extern "C" int b200_amg_set_precond_cycles(b200_amg *a, int cycles)
 {
    ARG_CHECK(a != nullptr && cycles >= 1);
    a->precond_cycles = cycles;
+   a->ctx->generation++;
    return B200_OK;
 }
 
@@ -460,6 +515,14 @@ extern "C" int b200_amg_cycle(b200_amg *a, const double *f, double *u, int zero_
    double *res = nullptr;
    B200_TRY(amg_cycle_core(a, f, u, zero_guess, &res));
    if (res != u) { B200_TRY(b200_vec_copy(a->ctx, a->L[0].n, res, u)); }
+   return B200_OK;
+}
+
+// first level of the persistent coarse-level kernel (-1: none)
+extern "C" int b200_amg_tail_level(const b200_amg *a, int *level)
+{
+   ARG_CHECK(a != nullptr && level != nullptr);
+   *level = a->tail_level == INT_MAX ? -1 : a->tail_level;
    return B200_OK;
 }
 

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <vector>
 #include <string>
+#include <type_traits>
 #include "../../include/b200amg.h"
 
 // ---------------------------------------------------------------- errors
@@ -62,6 +63,8 @@ struct b200_ctx {
    ncclComm_t   hcomm    = nullptr;   // halo point-to-point on `cstream` (own communicator: the two
                                       // streams run concurrently and must not share one)
    long long    launches = 0;
+   void        *tail = nullptr;      // recorder / program cache of the persistent cycle kernel (tail.cuh)
+   long long    generation = 0;      // bumped whenever device objects baked into a captured graph go away or change
    // peer-memory exchange (p2p.cuh): this rank's arena, the IPC-mapped arenas of all ranks
    int          use_p2p = 0;
    int          p2p_debug = 0;       // B200_P2P_DEBUG (timing experiments)

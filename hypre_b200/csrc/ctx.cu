@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "vecops.cuh"
 #include "p2p.cuh"
+#include "tail.cuh"
 #include <cstdarg>
 
 static thread_local char g_err[1024] = "";
@@ -141,6 +142,7 @@ extern "C" int b200_ctx_destroy(b200_ctx *c)
    cudaSetDevice(c->device);
    cudaDeviceSynchronize();
    p2p_shutdown(c);
+   tail_release(c);
    if (c->h_err) { cudaFreeHost(c->h_err); }
    if (c->hcomm) { ncclCommDestroy(c->hcomm); }
    if (c->comm) { ncclCommDestroy(c->comm); }
@@ -277,6 +279,13 @@ extern "C" int b200_vec_copy(b200_ctx *c, int n, const double *x, double *y)
 {
    ARG_CHECK(c != nullptr && n >= 0);
    if (n == 0 || x == y) { return B200_OK; }
+   if (tail_recording(c))
+   {
+      TailOp op;
+      memset(&op, 0, sizeof(op));
+      op.kind = TK_COPY; op.n = n; op.x = x; op.y = y;
+      return tail_append(c, op);
+   }
    CUDA_TRY(cudaMemcpyAsync(y, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
    return B200_OK;
 }

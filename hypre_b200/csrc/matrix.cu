@@ -228,6 +228,7 @@ extern "C" int b200_parcsr_create(b200_ctx *ctx, int n_rows, int n_cols_diag,
 extern "C" int b200_parcsr_destroy(b200_parcsr *A)
 {
    if (!A) { return B200_OK; }
+   if (A->ctx) { A->ctx->generation++; }
    if (A->ctx) { cudaSetDevice(A->ctx->device); cudaStreamSynchronize(A->ctx->stream); cudaStreamSynchronize(A->ctx->cstream); }
    p2p_chan_destroy(A->ch_fwd); p2p_chan_destroy(A->ch_rev);
    dmat_free(&A->diag); dmat_free(&A->offd);

@@ -43,7 +43,10 @@ struct EpiMatvecDotDir {
       p_old = odd ? pbuf1 : pbuf0;
       p_new = odd ? pbuf0 : pbuf1;
    }
-   __device__ __forceinline__ double xval(const double *__restrict__, int j) const { return fma(beta, __ldg(p_old + j), __ldg(z + j)); }
+   template <bool COH> __device__ __forceinline__ double xval(const double *__restrict__, int j) const
+   {
+      return fma(beta, ld_gather<COH>(p_old + j), ld_gather<COH>(z + j));
+   }
    __device__ void operator()(int r, double t, double *red) const
    {
       const double pn = fma(beta, p_old[r], z[r]);
@@ -111,12 +114,12 @@ struct EpiChebyZero {
    static constexpr int NRED = 0;
    int scale; int last; int write_r; double ck; double ci; const double *f; const double *ds; double *rv;
    double *out; double *u;
-   __device__ __forceinline__ double xval(const double *__restrict__, int j) const
+   template <bool COH> __device__ __forceinline__ double xval(const double *__restrict__, int j) const
    {
-      double res = __ldg(f + j);
-      if (scale) { res = __ldg(ds + j) * res; }
+      double res = ld_gather<COH>(f + j);
+      if (scale) { res = ld_gather<COH>(ds + j) * res; }
       const double u1 = res * ck;
-      return scale ? __ldg(ds + j) * u1 : u1;
+      return scale ? ld_gather<COH>(ds + j) * u1 : u1;
    }
    __device__ void operator()(int r, double t, double *) const
    {
@@ -172,6 +175,276 @@ struct FChebyFirst0 { static constexpr int NRED = 0; __device__ void init() {} i
    } };
 struct FGsFirst0 { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *d; double *z;
    __device__ void operator()(int i, double *) const { z[i] = (w * f[i]) / d[i]; } };
+
+// ---------------------------------------------------------------- persistent cycle kernel (tail.cuh)
+template <> struct TailKind<EpiMatvec>            { static constexpr int value = TK_MATVEC; };
+template <> struct TailKind<EpiJacobiT<false>>    { static constexpr int value = TK_JACOBI; };
+template <> struct TailKind<EpiChebyFirst>        { static constexpr int value = TK_CHEBY_FIRST; };
+template <> struct TailKind<EpiChebyStepT<false>> { static constexpr int value = TK_CHEBY_STEP; };
+template <> struct TailKind<EpiChebyZero>         { static constexpr int value = TK_CHEBY_ZERO; };
+template <> struct TailKind<EpiGsFirst>           { static constexpr int value = TK_GS_FIRST; };
+template <> struct TailKind<EpiGsInnerT<false>>   { static constexpr int value = TK_GS_INNER; };
+template <> struct TailKind<FScaleCopy>           { static constexpr int value = TK_E_SCALECOPY; };
+template <> struct TailKind<FZero>                { static constexpr int value = TK_E_ZERO; };
+template <> struct TailKind<FChebyFirst0>         { static constexpr int value = TK_E_CHEBY_FIRST0; };
+template <> struct TailKind<FGsFirst0>            { static constexpr int value = TK_E_GS_FIRST0; };
+
+constexpr int TAIL_BLOCK = 256;
+constexpr int TAIL_BLOCKS_PER_SM = 4;
+constexpr long long TAIL_SPIN_LIMIT = 4000000000LL;     // ~2 s: a barrier that cannot complete reports instead of hanging
+
+// rows of a CSR block with `lanes` lanes per row (a power of two, runtime), grid-strided over the whole grid.
+// Loop order and shuffle tree are those of rowsum_csr<T>: bit-identical to the stand-alone launch.
+template <class Epi>
+__device__ __forceinline__ void tail_rows(const TailOp &op)
+{
+   Epi e;
+   memcpy(&e, op.fn, sizeof(Epi));
+   epi_init(e, 0);
+   const int T = op.lanes;
+   const int sub = threadIdx.x & (T - 1);
+   const int rpb = TAIL_BLOCK / T;
+   const int rpw = 32 / T;
+   const int n_pad = (op.n + rpw - 1) / rpw * rpw;          // whole warps take part in the shuffles
+   double red[1] = {0.0};
+   for (int row = blockIdx.x * rpb + threadIdx.x / T; row < n_pad; row += gridDim.x * rpb)
+   {
+      const bool live = row < op.n;
+      const int r = live ? row : op.n - 1;
+      const int beg = op.rp[r], end = op.rp[r + 1];
+      double t = 0.0;
+      int k = beg + sub;
+      for (; k + T < end; k += 2 * T)
+      {
+         const int c0 = ld_stream(op.ci + k), c1 = ld_stream(op.ci + k + T);
+         const double v0 = ld_stream(op.va + k), v1 = ld_stream(op.va + k + T);
+         const double x0 = e.template xval<true>(op.x, c0), x1 = e.template xval<true>(op.x, c1);
+         t = fma(v0, x0, t); t = fma(v1, x1, t);
+      }
+      if (k < end)
+      {
+         const int c0 = ld_stream(op.ci + k);
+         t = fma(ld_stream(op.va + k), e.template xval<true>(op.x, c0), t);
+      }
+      for (int o = T >> 1; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o, T); }
+      if (live && sub == 0) { e(row, t, red); }
+   }
+}
+
+template <class F>
+__device__ __forceinline__ void tail_ewise(const TailOp &op)
+{
+   F f;
+   memcpy(&f, op.fn, sizeof(F));
+   f.init();
+   double red[1] = {0.0};
+   for (int i = blockIdx.x * TAIL_BLOCK + threadIdx.x; i < op.n; i += gridDim.x * TAIL_BLOCK) { f(i, red); }
+}
+
+// grid-wide barrier: arrival counter + generation word; the last block to arrive re-arms the counter and bumps the
+// generation.  Every block reads the generation before its first arrival, so it cannot miss a bump.
+__device__ __forceinline__ void tail_barrier(unsigned *bar, unsigned &gen)
+{
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      __threadfence();
+      if (atomicAdd(bar, 1u) == gridDim.x - 1)
+      {
+         bar[0] = 0u;
+         __threadfence();
+         atomicAdd(bar + 1, 1u);
+      }
+      else
+      {
+         const long long t0 = clock64();
+         while (*(volatile unsigned *)(bar + 1) == gen)
+         {
+            if (clock64() - t0 > TAIL_SPIN_LIMIT) { atomicExch(bar + 2, 1u); break; }
+         }
+      }
+      __threadfence();       // acquire side: also drops this SM's L1 lines (vectors rewritten by other SMs)
+   }
+   gen++;
+   __syncthreads();
+}
+
+__global__ void __launch_bounds__(TAIL_BLOCK, TAIL_BLOCKS_PER_SM)
+tail_kernel(const TailOp *__restrict__ ops, int n_ops, unsigned *bar, const int *stop)
+{
+   if (stop != nullptr && *stop != 0) { return; }
+   __shared__ TailOp s_op;
+   unsigned gen = *(volatile unsigned *)(bar + 1);
+   for (int k = 0; k < n_ops; k++)
+   {
+      // (the previous barrier's trailing __syncthreads keeps s_op stable until every thread is done with it)
+      for (int w = threadIdx.x; w < (int)(sizeof(TailOp) / 4); w += TAIL_BLOCK)
+      {
+         reinterpret_cast<unsigned *>(&s_op)[w] = reinterpret_cast<const unsigned *>(ops + k)[w];
+      }
+      __syncthreads();
+      const TailOp &op = s_op;
+      switch (op.kind)
+      {
+         case TK_MATVEC:         tail_rows<EpiMatvec>(op); break;
+         case TK_JACOBI:         tail_rows<EpiJacobiT<false>>(op); break;
+         case TK_CHEBY_FIRST:    tail_rows<EpiChebyFirst>(op); break;
+         case TK_CHEBY_STEP:     tail_rows<EpiChebyStepT<false>>(op); break;
+         case TK_CHEBY_ZERO:     tail_rows<EpiChebyZero>(op); break;
+         case TK_GS_FIRST:       tail_rows<EpiGsFirst>(op); break;
+         case TK_GS_INNER:       tail_rows<EpiGsInnerT<false>>(op); break;
+         case TK_E_SCALECOPY:    tail_ewise<FScaleCopy>(op); break;
+         case TK_E_ZERO:         tail_ewise<FZero>(op); break;
+         case TK_E_CHEBY_FIRST0: tail_ewise<FChebyFirst0>(op); break;
+         case TK_E_GS_FIRST0:    tail_ewise<FGsFirst0>(op); break;
+         case TK_FILL:  for (int i = blockIdx.x * TAIL_BLOCK + threadIdx.x; i < op.n; i += gridDim.x * TAIL_BLOCK) { op.y[i] = op.a; } break;
+         case TK_COPY:  for (int i = blockIdx.x * TAIL_BLOCK + threadIdx.x; i < op.n; i += gridDim.x * TAIL_BLOCK) { op.y[i] = __ldcg(op.x + i); } break;
+         case TK_AXPY:  for (int i = blockIdx.x * TAIL_BLOCK + threadIdx.x; i < op.n; i += gridDim.x * TAIL_BLOCK) { op.y[i] = fma(op.a, __ldcg(op.x + i), op.y[i]); } break;
+         case TK_SCALE: for (int i = blockIdx.x * TAIL_BLOCK + threadIdx.x; i < op.n; i += gridDim.x * TAIL_BLOCK) { op.y[i] *= op.a; } break;
+         case TK_DENSE:
+         {
+            // u[i] = sum_j M[i][j] f[j]; one warp per row (dense_matvec_kernel's loop and shuffle tree)
+            const int lane = threadIdx.x & 31;
+            for (int row = blockIdx.x * (TAIL_BLOCK >> 5) + (threadIdx.x >> 5); row < op.n; row += gridDim.x * (TAIL_BLOCK >> 5))
+            {
+               double t = 0.0;
+               for (int j = lane; j < op.n_cols; j += 32) { t = fma(op.va[(size_t)row * op.n_cols + j], __ldcg(op.x + j), t); }
+#pragma unroll
+               for (int o = 16; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o); }
+               if (lane == 0) { op.y[row] = t; }
+            }
+            break;
+         }
+         default: break;
+      }
+      if (k + 1 < n_ops) { tail_barrier(bar, gen); }
+   }
+}
+
+struct TailProgram { std::vector<TailOp> ops; TailOp *d_ops = nullptr; };
+struct TailRec {
+   bool recording = false;
+   std::vector<TailOp> cur;
+   std::vector<TailProgram> cache;
+   unsigned *d_bar = nullptr;         // [0] arrivals, [1] generation, [2] barrier timed out
+   int grid = 0;
+   int coop = 1;
+};
+
+static TailRec *tail_of(b200_ctx *c)
+{
+   if (!c->tail) { c->tail = new TailRec(); }
+   return static_cast<TailRec *>(c->tail);
+}
+
+bool tail_recording(const b200_ctx *c) { return c->tail != nullptr && static_cast<const TailRec *>(c->tail)->recording; }
+
+int tail_begin(b200_ctx *c)
+{
+   TailRec *t = tail_of(c);
+   t->cur.clear();
+   t->recording = true;
+   return B200_OK;
+}
+
+int tail_append(b200_ctx *c, const TailOp &op)
+{
+   tail_of(c)->cur.push_back(op);
+   return B200_OK;
+}
+
+void tail_drop_programs(b200_ctx *c)
+{
+   if (!c->tail) { return; }
+   TailRec *t = static_cast<TailRec *>(c->tail);
+   for (auto &p : t->cache) { cudaFree(p.d_ops); }
+   t->cache.clear();
+   t->recording = false;
+   t->cur.clear();
+}
+
+void tail_release(b200_ctx *c)
+{
+   if (!c->tail) { return; }
+   tail_drop_programs(c);
+   TailRec *t = static_cast<TailRec *>(c->tail);
+   cudaFree(t->d_bar);
+   delete t;
+   c->tail = nullptr;
+}
+
+int tail_flush(b200_ctx *c)
+{
+   TailRec *t = tail_of(c);
+   t->recording = false;
+   if (t->cur.empty()) { return B200_OK; }
+   if (t->d_bar == nullptr)
+   {
+      CUDA_TRY(cudaMalloc((void **)&t->d_bar, 4 * sizeof(unsigned)));
+      CUDA_TRY(cudaMemset(t->d_bar, 0, 4 * sizeof(unsigned)));
+      int per_sm = 0;
+      CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tail_kernel, TAIL_BLOCK, 0));
+      if (per_sm < 1) { b200_set_error("persistent cycle kernel does not fit an SM"); return B200_ERR_CUDA; }
+      if (per_sm > TAIL_BLOCKS_PER_SM) { per_sm = TAIL_BLOCKS_PER_SM; }
+      int sms = B200_NUM_SMS;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+      t->grid = sms * per_sm;
+      const char *e = getenv("B200_TAIL_COOP");
+      t->coop = e ? atoi(e) : 1;
+   }
+   // the program of a cycle is the same every time: upload once, find it again by content
+   TailProgram *prog = nullptr;
+   for (auto &p : t->cache)
+   {
+      if (p.ops.size() == t->cur.size() && memcmp(p.ops.data(), t->cur.data(), sizeof(TailOp) * t->cur.size()) == 0) { prog = &p; break; }
+   }
+   if (prog == nullptr)
+   {
+      if (c->capturing)
+      {
+         b200_set_error("persistent cycle kernel: new program during graph capture");
+         return B200_ERR_CUDA;
+      }
+      if (t->cache.size() >= 64) { tail_drop_programs(c); }
+      TailProgram p;
+      p.ops = t->cur;
+      CUDA_TRY(cudaMalloc((void **)&p.d_ops, sizeof(TailOp) * p.ops.size()));
+      CUDA_TRY(cudaMemcpyAsync(p.d_ops, p.ops.data(), sizeof(TailOp) * p.ops.size(), cudaMemcpyHostToDevice, c->stream));
+      CUDA_TRY(cudaStreamSynchronize(c->stream));      // (first cycle only; the host vector is about to move)
+      t->cache.push_back(std::move(p));
+      prog = &t->cache.back();
+   }
+   const TailOp *d_ops = prog->d_ops;
+   int n_ops = (int)prog->ops.size();
+   unsigned *bar = t->d_bar;
+   const int *stop = c->d_stop;
+   if (c->prof) { prof_begin(c, "tail_kernel (persistent coarse-level cycle)"); }
+   if (t->coop)
+   {
+      void *args[] = {(void *)&d_ops, (void *)&n_ops, (void *)&bar, (void *)&stop};
+      CUDA_TRY(cudaLaunchCooperativeKernel((const void *)tail_kernel, dim3(t->grid), dim3(TAIL_BLOCK), args, 0, c->stream));
+   }
+   else
+   {
+      tail_kernel<<<t->grid, TAIL_BLOCK, 0, c->stream>>>(d_ops, n_ops, bar, stop);
+   }
+   if (c->prof) { prof_end(c); }
+   c->launches++;
+   CHECK_LAUNCH();
+   t->cur.clear();
+   return B200_OK;
+}
+
+// 0 = fine, 1 = a grid barrier of the persistent cycle kernel timed out (results invalid)
+int tail_error(b200_ctx *c)
+{
+   if (!c->tail) { return 0; }
+   TailRec *t = static_cast<TailRec *>(c->tail);
+   if (!t->d_bar) { return 0; }
+   unsigned e = 0;
+   if (cudaMemcpy(&e, t->d_bar + 2, sizeof(unsigned), cudaMemcpyDeviceToHost) != cudaSuccess) { return 1; }
+   return e != 0;
+}
 
 // ---------------------------------------------------------------- operators
 int op_matvec(b200_parcsr *A, double alpha, const double *x, double beta, const double *b, double *y)
@@ -375,6 +648,13 @@ __global__ void dense_matvec_kernel(int n_rows, int n_cols, const double *__rest
 int op_dense_matvec(b200_ctx *ctx, int n_rows, int n_cols, const double *M, const double *f_all, double *u)
 {
    if (n_rows == 0) { return B200_OK; }
+   if (tail_recording(ctx))
+   {
+      TailOp op;
+      memset(&op, 0, sizeof(op));
+      op.kind = TK_DENSE; op.n = n_rows; op.n_cols = n_cols; op.va = M; op.x = f_all; op.y = u;
+      return tail_append(ctx, op);
+   }
    int grid = (n_rows + 7) / 8;
    LAUNCH(ctx, dense_matvec_kernel, grid, 256, 0, n_rows, n_cols, M, f_all, u);
    CHECK_LAUNCH();

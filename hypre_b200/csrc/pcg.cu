@@ -6,6 +6,7 @@
 #include "ops.cuh"
 #include "vecops.cuh"
 #include "p2p.cuh"
+#include "tail.cuh"
 #include <cmath>
 #include <cfloat>
 
@@ -158,6 +159,8 @@ static int apply_precond(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const b200_
    return b200_vec_copy(c, n, r, z);   // identity: hypre_ParKrylovIdentity
 }
 
+static const int g_pcg_fuse = []() { const char *e = getenv("B200_PCG_FUSE"); return e ? atoi(e) : 1; }();
+
 // ---- one iteration, enqueued on the compute stream without any host synchronisation
 struct PcgIter {
    b200_ctx *c; b200_parcsr *A; b200_amg *amg; const b200_pcg_params *prm;
@@ -208,14 +211,20 @@ static int pcg_enqueue_iteration(const PcgIter &it)
       FPcgUpdate f{it.prm->skip_break, c->d_scalars, it.p, it.s, it.x, it.r, 0.0, false, nullptr, nullptr};
       B200_TRY(run_ewise(c, it.n, f, c->d_scalars + S_IPROD));
    }
-   // s = C r ; gamma = <r,s>
-   B200_TRY(apply_precond(c, it.A, it.amg, it.prm, it.r, it.s, &z));
-   if (!it.amg && it.prm->diag_scale)
+   // s = C r ; gamma = <r,s> (reduced inside the preconditioner's last launch where it can be)
+   bool dot_done = false;
+   if (g_pcg_fuse & 1) { B200_TRY(apply_precond(c, it.A, it.amg, it.prm, it.r, it.s, &z, S_GAMMA_NEW, &dot_done)); }
+   else
    {
-      CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_GAMMA_NEW, c->d_scalars + S_TMP, sizeof(double),
-                               cudaMemcpyDeviceToDevice, c->stream));
+      B200_TRY(apply_precond(c, it.A, it.amg, it.prm, it.r, it.s, &z));
+      if (!it.amg && it.prm->diag_scale)
+      {
+         CUDA_TRY(cudaMemcpyAsync(c->d_scalars + S_GAMMA_NEW, c->d_scalars + S_TMP, sizeof(double),
+                                  cudaMemcpyDeviceToDevice, c->stream));
+         dot_done = true;
+      }
    }
-   else { B200_TRY(dot_to(c, it.n, it.r, z, S_GAMMA_NEW)); }
+   if (!dot_done) { B200_TRY(dot_to(c, it.n, it.r, z, S_GAMMA_NEW)); }
    B200_TRY(scalars_allreduce(c, c->d_scalars + S_IPROD, 2));
    // scalar logic + record for the host
    LAUNCH(c, pcg_check_kernel, 1, 1, 0, c->d_scalars, c->d_stop, c->d_iter, (PcgRecord *)c->d_ring,
@@ -247,14 +256,16 @@ static int pcg_launch_iteration(const PcgIter &it, int i)
    const void *key[8] = {it.A, it.amg, it.x, it.p, it.s, it.r,
                          (const void *)(size_t)(it.prm->two_norm * 64 + it.prm->skip_break * 8 + it.prm->diag_scale +
                                                 (it.fused ? 128 : 0) + (it.amg ? 4096 * amg_precond_cycles(it.amg) : 0)),
-                         (const void *)(size_t)it.prm->max_iter};
+                         (const void *)(size_t)((long long)it.prm->max_iter + (c->generation << 20))};
    if (c->pcg_graph == nullptr || memcmp(key, c->pcg_graph_key, sizeof(key)) != 0)
    {
       if (c->pcg_graph) { cudaGraphExecDestroy(c->pcg_graph); c->pcg_graph = nullptr; }
       cudaGraph_t g = nullptr;
       const long long l0 = c->launches;
       CUDA_TRY(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      c->capturing = true;
       int st = pcg_enqueue_iteration(it);
+      c->capturing = false;
       cudaError_t e = cudaStreamEndCapture(c->stream, &g);
       c->pcg_graph_launches = c->launches - l0;
       c->launches = l0;
@@ -310,8 +321,9 @@ extern "C" int b200_pcg_solve(b200_ctx *c, b200_parcsr *A, b200_amg *amg, const 
    B200_TRY(ctx_workspace(c, WS_PCG_P, n, &p));
    B200_TRY(ctx_workspace(c, WS_PCG_S, n, &s));
    B200_TRY(ctx_workspace(c, WS_PCG_R, n, &r));
-   static const int fuse_env = []() { const char *e = getenv("B200_PCG_FUSE"); return e ? atoi(e) : 1; }();
-   const bool fused = fuse_env != 0 && op_can_fuse_gather(A);
+   // B200_PCG_FUSE: bit 0 = <r,z> inside the preconditioner's last launch (default), bit 1 = direction update inside
+   // s = A p (measured slower on the pattern kernel, which is bound by gathers, not by bytes: off by default)
+   const bool fused = (g_pcg_fuse & 2) != 0 && op_can_fuse_gather(A);
    if (fused)
    {
       B200_TRY(ctx_workspace(c, WS_PCG_P2, n, &p2));
@@ -420,6 +432,11 @@ done:
    cudaMemsetAsync(c->d_stop, 0, sizeof(int), c->stream);
    cudaStreamSynchronize(c->stream);
    if (status == B200_OK && c->use_p2p && c->h_err && *c->h_err) { status = B200_ERR_NCCL; }
+   if (status == B200_OK && tail_error(c))
+   {
+      b200_set_error("a grid barrier of the persistent coarse-level kernel timed out");
+      status = B200_ERR_CUDA;
+   }
    return status;
 }
 

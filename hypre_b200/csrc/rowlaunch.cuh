@@ -1,6 +1,7 @@
 // rowlaunch.cuh -- host-side dispatch of the fused row kernels.
 #pragma once
 #include "spmv.cuh"
+#include "tail.cuh"
 #include <cstring>
 #include <algorithm>
 
@@ -41,6 +42,20 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
 {
    MatView V = view_of(D);
    constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
+   if (tail_recording(ctx))
+   {
+      // persistent cycle kernel: record instead of launching (CSR-vector blocks without communication only)
+      if (HALO != HALO_NONE || D.layout != 0)
+      {
+         b200_set_error("operator with communication or a thread-per-row layout inside the persistent cycle kernel");
+         return B200_ERR_UNSUPPORTED;
+      }
+      if (D.n_rows == 0) { return B200_OK; }
+      TailOp op;
+      memset(&op, 0, sizeof(op));
+      op.n = D.n_rows; op.lanes = D.lanes; op.rp = D.rp; op.ci = D.ci; op.va = D.va; op.x = x;
+      return tail_record_fn(ctx, op, epi);
+   }
    if (D.n_rows == 0 && !P2P)
    {
       // reductions still have to publish a zero
@@ -97,6 +112,11 @@ static int run_rows(b200_parcsr *A, const DMat &D, const DMat &O, bool use_halo,
    b200_ctx *ctx = A->ctx;
    if (use_halo && (A->num_sends + A->num_recvs) > 0)
    {
+      if (tail_recording(ctx))
+      {
+         b200_set_error("operator with a halo exchange inside the persistent cycle kernel");
+         return B200_ERR_UNSUPPORTED;
+      }
       HaloArgs h = no_halo();
       h.O = view_of(O);
       if (A->ch_fwd)

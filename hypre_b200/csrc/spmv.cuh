@@ -104,7 +104,10 @@ __device__ __forceinline__ void grid_reduce(double (&red)[NRED > 0 ? NRED : 1], 
 // registers): optional member init(), called on the kernel's own copy of the functor.
 template <class E> __device__ __forceinline__ auto epi_init(E &e, int) -> decltype(e.init(), void()) { e.init(); }
 template <class E> __device__ __forceinline__ void epi_init(E &, long) {}
-#define EPI_PLAIN_X __device__ __forceinline__ double xval(const double *__restrict__ x, int j) const { return __ldg(x + j); }
+// COH = true (the persistent cycle kernel, tail.cuh): the vector may have been written earlier in the SAME kernel by
+// another SM, so it is read from L2 instead of through the non-coherent read-only path.
+template <bool COH> __device__ __forceinline__ double ld_gather(const double *p) { return COH ? __ldcg(p) : __ldg(p); }
+#define EPI_PLAIN_X template <bool COH> __device__ __forceinline__ double xval(const double *__restrict__ x, int j) const { return ld_gather<COH>(x + j); }
 struct XPlain { EPI_PLAIN_X };
 // sliced-ELL, one thread per row (lane = row within the 32-row slice).
 // Memory latency bounds this loop (ncu: >90 % of the stall samples are long-scoreboard) and
@@ -131,7 +134,7 @@ __device__ __forceinline__ double rowsum_sell(const MatView &D, int slice, int l
 #pragma unroll
       for (int j = 0; j < 4; j++) { v[j] = (j < m) ? ld_stream(va + (k0 + j) * 32) : 0.0; }
 #pragma unroll
-      for (int j = 0; j < 4; j++) { xv[j] = (j < m) ? xf.xval(x, c[j]) : 0.0; }
+      for (int j = 0; j < 4; j++) { xv[j] = (j < m) ? xf.template xval<false>(x, c[j]) : 0.0; }
 #pragma unroll
       for (int j = 0; j < 4; j++) { if (j < m) { t = fma(v[j], xv[j], t); } }
    }
@@ -201,7 +204,7 @@ __device__ __forceinline__ double rowsum_sellc(const MatView &D, long long off, 
          else { v[j] = live[j] ? ld_stream(D.sl_va + off + (c * 4 + j) * 32 + lane) : 0.0; }
       }
 #pragma unroll
-      for (int j = 0; j < 4; j++) { xv[j] = live[j] ? xf.xval(x, col[j]) : 0.0; }
+      for (int j = 0; j < 4; j++) { xv[j] = live[j] ? xf.template xval<false>(x, col[j]) : 0.0; }
 #pragma unroll
       for (int j = 0; j < 4; j++) { if (live[j]) { t = fma(v[j], xv[j], t); } }
    }
@@ -241,7 +244,7 @@ __device__ __forceinline__ double rowsum_sellc_z(const MatView &D, long long off
          if (b4.w < 0) { col[3] = ld_stream(e + 96); }
       }
 #pragma unroll
-      for (int j = 0; j < 4; j++) { xv[j] = xf.xval(x, col[j]); }
+      for (int j = 0; j < 4; j++) { xv[j] = xf.template xval<false>(x, col[j]); }
 #pragma unroll
       for (int j = 0; j < 4; j++)
       {
@@ -280,7 +283,7 @@ __device__ __forceinline__ double pat_word(unsigned h, const unsigned *&lp, int 
    {
       const double2 pd = s_pat[(h >> (8 * j)) & 0xFFu];
       v[j] = pd.x;
-      xv[j] = xf.xval(x, row + __double2loint(pd.y));
+      xv[j] = xf.template xval<false>(x, row + __double2loint(pd.y));
    }
 #pragma unroll
    for (int j = 0; j < 4; j++) { t = fma(v[j], xv[j], t); }
@@ -325,13 +328,13 @@ __device__ __forceinline__ double rowsum_csr(const int *__restrict__ rp, const i
    {
       int    c0 = ld_stream(ci + k), c1 = ld_stream(ci + k + T);
       double v0 = ld_stream(va + k), v1 = ld_stream(va + k + T);
-      double x0 = CG ? __ldcg(x + c0) : xf.xval(x, c0), x1 = CG ? __ldcg(x + c1) : xf.xval(x, c1);
+      double x0 = CG ? __ldcg(x + c0) : xf.template xval<false>(x, c0), x1 = CG ? __ldcg(x + c1) : xf.template xval<false>(x, c1);
       t = fma(v0, x0, t); t = fma(v1, x1, t);
    }
    if (k < end)
    {
       const int c0 = ld_stream(ci + k);
-      t = fma(ld_stream(va + k), CG ? __ldcg(x + c0) : xf.xval(x, c0), t);
+      t = fma(ld_stream(va + k), CG ? __ldcg(x + c0) : xf.template xval<false>(x, c0), t);
    }
 #pragma unroll
    for (int o = T >> 1; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o, T); }
@@ -391,7 +394,7 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
    {
       while (i >= ch.out_starts[seg + 1]) { seg++; }
       double v;
-      if (HALO == HALO_FWD) { v = xf.xval(x, h.map[i]); }   // pack: x_buf[i] = x_local[send_map_elmts[i]]
+      if (HALO == HALO_FWD) { v = xf.template xval<false>(x, h.map[i]); }   // pack: x_buf[i] = x_local[send_map_elmts[i]]
       else
       {
          // row i of offd^T: contribution of my rows to ghost column i

@@ -11,20 +11,31 @@ struct FAxpy  { static constexpr int NRED = 0; __device__ void init() {} double 
 struct FDot   { static constexpr int NRED = 1; __device__ void init() {} const double *x; const double *y;
    __device__ void operator()(int i, double *red) const { red[0] = fma(x[i], y[i], red[0]); } };
 
+static int tail_blas1(b200_ctx *c, int kind, int n, double a, const double *x, double *y)
+{
+   TailOp op;
+   memset(&op, 0, sizeof(op));
+   op.kind = kind; op.n = n; op.a = a; op.x = x; op.y = y;
+   return tail_append(c, op);
+}
+
 int vec_fill(b200_ctx *c, int n, double a, double *y)
 {
    if (n == 0) { return B200_OK; }
+   if (tail_recording(c)) { return tail_blas1(c, TK_FILL, n, a, nullptr, y); }
    if (a == 0.0) { CUDA_TRY(cudaMemsetAsync(y, 0, sizeof(double) * (size_t)n, c->stream)); return B200_OK; }
    FFill f{a, y};
    return run_ewise(c, n, f, nullptr);
 }
 int vec_scale(b200_ctx *c, int n, double a, double *y)
 {
+   if (tail_recording(c)) { return n > 0 ? tail_blas1(c, TK_SCALE, n, a, nullptr, y) : B200_OK; }
    FScale f{a, y};
    return run_ewise(c, n, f, nullptr);
 }
 int vec_axpy(b200_ctx *c, int n, double a, const double *x, double *y)
 {
+   if (tail_recording(c)) { return n > 0 ? tail_blas1(c, TK_AXPY, n, a, x, y) : B200_OK; }
    FAxpy f{a, x, y};
    return run_ewise(c, n, f, nullptr);
 }

@@ -26,6 +26,14 @@ __global__ void __launch_bounds__(ROWK_BLOCK) ewise_kernel(int n, F f, RedCtx rc
 template <class F>
 static int run_ewise(b200_ctx *ctx, int n, const F &f, double *red_out)
 {
+   if (tail_recording(ctx))
+   {
+      if (n == 0) { return B200_OK; }
+      TailOp op;
+      memset(&op, 0, sizeof(op));
+      op.n = n;
+      return tail_record_fn(ctx, op, f);
+   }
    RedCtx rc = make_redctx(ctx, red_out, 0);
    if (n == 0)
    {

@@ -236,6 +236,14 @@ int b200_amg_cycle_bytes(const b200_amg *amg, double *bytes);
 /* the same model with the bytes the device layouts actually store (b200_parcsr_storage) */
 int b200_amg_cycle_bytes_stored(const b200_amg *amg, double *bytes);
 /* borrowed handle to A_array[level] / P_array[level] (owned by amg) */
+/* Persistent coarse-level kernel: the deepest run of levels whose operators are small CSR blocks without
+ * communication (every level below ~4e6 nonzeros on one rank; the replicated levels on several) is executed as ONE
+ * cooperative kernel per visit -- the operators of hypre_BoomerAMGCycle (par_cycle.c:209-779) on those levels in
+ * order, a grid-wide barrier between them -- instead of one launch each.  Same arithmetic, bit-identical results.
+ * b200_set_tail_limit: largest level (nonzeros of A_l) that joins, 0 = off (applies to hierarchies finalized
+ * afterwards; environment B200_TAIL_NNZ); b200_amg_tail_level: first level inside the kernel, -1 = none. */
+int b200_set_tail_limit(long long max_nnz);
+int b200_amg_tail_level(const b200_amg *amg, int *level);
 int b200_amg_level_matrix(const b200_amg *amg, int level, b200_parcsr **A);
 int b200_amg_level_interp(const b200_amg *amg, int level, b200_parcsr **P);
 int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *nnz_A,

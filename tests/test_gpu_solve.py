@@ -422,3 +422,43 @@ def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
     it_r, fin_r = run(ij_ref)
     assert it_d == it_r, (it_d, it_r)
     assert abs(fin_d - fin_r) <= 2e-6 * fin_r, (fin_d, fin_r)
+
+
+@pytest.mark.parametrize("name", ["lap7_32_rlx18", "lap7_24_rlx16", "lap27_20_rlx11", "lap7_24_rlx18_W", "lap7_24_rlx16_F"])
+def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, name):
+    """levels below the fine one run as ONE cooperative kernel per visit (tail.cuh: the operators of the cycle
+    recorded and replayed with grid barriers): same epilogues, same lane counts, same summation order -> the cycle
+    and the whole PCG solve must equal the launch-per-operator path bit for bit (V, W and F cycles; l1-Jacobi,
+    Chebyshev, two-stage GS; dense coarse solve)"""
+    L = capi.lib()
+    H.set_device_path(True)
+    out = {}
+    for limit in (0, 4000000):
+        capi.check(L.b200_set_tail_limit(limit))
+        try:
+            A, b, x, amg, pcg = O.build_case(H, name)
+            damg = amg.device_mirror()
+            lvl = C.c_int()
+            capi.check(L.b200_amg_tail_level(damg, C.byref(lvl)))
+            assert (lvl.value == -1) if limit == 0 else (lvl.value == 1), (limit, lvl.value)
+            n = A.global_rows
+            rng = np.random.default_rng(31)
+            f, u0 = rng.standard_normal(n), rng.standard_normal(n)
+            res = []
+            for zg in (1, 0):
+                df, du = dvec(ctx, f), dvec(ctx, np.zeros(n) if zg else u0)
+                capi.check(L.b200_amg_cycle(damg, df.ptr, du.ptr, zg))
+                capi.check(L.b200_amg_cycle(damg, df.ptr, du.ptr, 0))      # second cycle: program found in the cache
+                res.append(du.get())
+                df.free(); du.free()
+            H.clear_errors()
+            pcg.Solve(A, b, x)              # graph replay with the persistent kernel inside
+            assert H.error_flag() == 0
+            res += [pcg.rel_norms().copy(), x.numpy().copy(), pcg.num_iterations]
+            out[limit] = res
+            for o in (pcg, amg, A):
+                o.destroy()
+        finally:
+            L.b200_set_tail_limit(4000000)
+    for a, b_ in zip(out[0], out[4000000]):
+        assert np.array_equal(a, b_), name
