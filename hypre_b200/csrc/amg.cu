@@ -200,7 +200,7 @@ extern "C" int b200_amg_set_coarse_dense(b200_amg *a, int n_global, const double
 }
 
 // largest level (in nonzeros of A) that joins the persistent coarse-level kernel; 0 switches the kernel off
-static long long g_tail_nnz = []() { const char *e = getenv("B200_TAIL_NNZ"); return e ? atoll(e) : 4000000LL; }();
+static long long g_tail_nnz = []() { const char *e = getenv("B200_TAIL_NNZ"); return e ? atoll(e) : 0LL; }();
 extern "C" int b200_set_tail_limit(long long max_nnz)
 {
    ARG_CHECK(max_nnz >= 0);

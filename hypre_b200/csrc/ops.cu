@@ -4,6 +4,13 @@
 #include "vecops.cuh"
 
 // ---------------------------------------------------------------- epilogues
+// Arithmetic of the epilogues is pinned with __dmul_rn / __dadd_rn: separately rounded products and sums, as the
+// reference's host code (gcc -O2, x86-64 baseline: no fused multiply-add) evaluates the same expressions, and
+// independent of how nvcc would contract a*b+c in one inlining context or another (the stand-alone launch and the
+// persistent coarse-level kernel must agree bit for bit).  The row sums themselves are explicit fma chains.
+#define MUL(a, b) __dmul_rn((a), (b))
+#define ADD(a, b) __dadd_rn((a), (b))
+#define SUB(a, b) __dsub_rn((a), (b))
 // y = alpha*t + beta*b           hypre_CSRMatrixMatvecOutOfPlaceHost (src/seq_mv/csr_matvec.c:683-847)
 struct EpiMatvec {
    static constexpr int NRED = 0;
@@ -11,8 +18,8 @@ struct EpiMatvec {
    double alpha, beta; const double *b; double *y;
    __device__ void operator()(int r, double t, double *) const
    {
-      double v = alpha * t;
-      if (beta != 0.0) { v = fma(beta, b[r], v); }
+      double v = MUL(alpha, t);
+      if (beta != 0.0) { v = ADD(v, MUL(beta, b[r])); }      // y = alpha*(A x) + beta*b, two rounded products (csr_matvec.c)
       y[r] = v;
    }
 };
@@ -65,7 +72,7 @@ struct EpiJacobiT {
    double w; const double *f; const double *l1; const double *u_in; double *u_out; const double *dw;
    __device__ void operator()(int r, double t, double *red) const
    {
-      const double un = u_in[r] + (w * (f[r] - t)) / l1[r];
+      const double un = ADD(u_in[r], __ddiv_rn(MUL(w, SUB(f[r], t)), l1[r]));
       u_out[r] = un;
       if (DOT) { red[0] = fma(dw[r], un, red[0]); }
    }
@@ -78,11 +85,11 @@ struct EpiChebyFirst {
    int scale; double c; const double *f; const double *ds; double *rv; double *tmp;
    __device__ void operator()(int r, double t, double *) const
    {
-      double res = f[r] - t;
-      if (scale) { res = ds[r] * res; }
+      double res = SUB(f[r], t);
+      if (scale) { res = MUL(ds[r], res); }
       rv[r] = res;
-      double u1 = res * c;
-      tmp[r] = scale ? ds[r] * u1 : u1;
+      double u1 = MUL(res, c);
+      tmp[r] = scale ? MUL(ds[r], u1) : u1;
    }
 };
 // Chebyshev inner step (par_cheby.c:284-297,344-371): u_i = c_i*r + ds.*t ; then either
@@ -94,11 +101,11 @@ struct EpiChebyStepT {
    int scale; int last; double c; const double *ds; const double *rv; double *out; double *u; const double *dw;
    __device__ void operator()(int r, double t, double *red) const
    {
-      double ui = scale ? c * rv[r] + ds[r] * t : c * rv[r] + t;
-      double su = scale ? ds[r] * ui : ui;
+      double ui = scale ? ADD(MUL(c, rv[r]), MUL(ds[r], t)) : ADD(MUL(c, rv[r]), t);
+      double su = scale ? MUL(ds[r], ui) : ui;
       if (last)
       {
-         const double un = u[r] + su;
+         const double un = ADD(u[r], su);
          u[r] = un;
          if (DOT) { red[0] = fma(dw[r], un, red[0]); }      // last step of the last sweep: <r, z> of PCG
       }
@@ -117,17 +124,17 @@ struct EpiChebyZero {
    template <bool COH> __device__ __forceinline__ double xval(const double *__restrict__, int j) const
    {
       double res = ld_gather<COH>(f + j);
-      if (scale) { res = ld_gather<COH>(ds + j) * res; }
-      const double u1 = res * ck;
-      return scale ? ld_gather<COH>(ds + j) * u1 : u1;
+      if (scale) { res = MUL(ld_gather<COH>(ds + j), res); }
+      const double u1 = MUL(res, ck);
+      return scale ? MUL(ld_gather<COH>(ds + j), u1) : u1;
    }
    __device__ void operator()(int r, double t, double *) const
    {
       double res = f[r];
-      if (scale) { res = ds[r] * res; }
+      if (scale) { res = MUL(ds[r], res); }
       if (write_r) { rv[r] = res; }
-      double ui = scale ? ci * res + ds[r] * t : ci * res + t;
-      double su = scale ? ds[r] * ui : ui;
+      double ui = scale ? ADD(MUL(ci, res), MUL(ds[r], t)) : ADD(MUL(ci, res), t);
+      double su = scale ? MUL(ds[r], ui) : ui;
       if (last) { u[r] = su; }      // u == 0: 0 + su
       else      { out[r] = su; }
    }
@@ -137,7 +144,7 @@ struct EpiGsFirst {
    static constexpr int NRED = 0;
    EPI_PLAIN_X
    double w; const double *f; const double *d; double *z;
-   __device__ void operator()(int r, double t, double *) const { z[r] = (w * (f[r] - t)) / d[r]; }
+   __device__ void operator()(int r, double t, double *) const { z[r] = __ddiv_rn(MUL(w, SUB(f[r], t)), d[r]); }
 };
 // inner stage over the strict lower triangle (par_relax.c:1562-1585): z' = t/d ; u += mult*z'
 // (first inner stage also applies the pending u += z0)
@@ -148,10 +155,10 @@ struct EpiGsInnerT {
    int first; double mult; const double *d; const double *z_in; double *z_out; double *u; const double *dw;
    __device__ void operator()(int r, double t, double *red) const
    {
-      double zn = t / d[r];
+      double zn = __ddiv_rn(t, d[r]);
       double uu = u[r];
-      if (first) { uu = uu + z_in[r]; }
-      const double un = uu + mult * zn;
+      if (first) { uu = ADD(uu, z_in[r]); }
+      const double un = ADD(uu, MUL(mult, zn));
       u[r] = un;
       z_out[r] = zn;
       if (DOT) { red[0] = fma(dw[r], un, red[0]); }
@@ -160,21 +167,21 @@ struct EpiGsInnerT {
 
 // zero-initial-guess / alpha == 0 elementwise variants (A*0 == 0: same arithmetic, no SpMV)
 struct FScaleCopy { static constexpr int NRED = 0; __device__ void init() {} double beta; const double *b; double *y;
-   __device__ void operator()(int i, double *) const { y[i] = beta * b[i]; } };
+   __device__ void operator()(int i, double *) const { y[i] = MUL(beta, b[i]); } };
 struct FZero { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *l1; double *u;
-   __device__ void operator()(int i, double *) const { u[i] = (w * f[i]) / l1[i]; } };
+   __device__ void operator()(int i, double *) const { u[i] = __ddiv_rn(MUL(w, f[i]), l1[i]); } };
 struct FChebyFirst0 { static constexpr int NRED = 0; __device__ void init() {} int scale; double c; const double *f; const double *ds;
    double *rv; double *tmp;
    __device__ void operator()(int i, double *) const
    {
       double res = f[i];
-      if (scale) { res = ds[i] * res; }
+      if (scale) { res = MUL(ds[i], res); }
       rv[i] = res;
-      double u1 = res * c;
-      tmp[i] = scale ? ds[i] * u1 : u1;
+      double u1 = MUL(res, c);
+      tmp[i] = scale ? MUL(ds[i], u1) : u1;
    } };
 struct FGsFirst0 { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *d; double *z;
-   __device__ void operator()(int i, double *) const { z[i] = (w * f[i]) / d[i]; } };
+   __device__ void operator()(int i, double *) const { z[i] = __ddiv_rn(MUL(w, f[i]), d[i]); } };
 
 // ---------------------------------------------------------------- persistent cycle kernel (tail.cuh)
 template <> struct TailKind<EpiMatvec>            { static constexpr int value = TK_MATVEC; };

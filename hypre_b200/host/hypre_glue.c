@@ -31,6 +31,7 @@
 #include "_hypre_parcsr_ls.h"
 #include "_hypre_parcsr_mv.h"
 #include "_hypre_utilities.h"
+#include "_hypre_IJ_mv.h"
 #include "krylov.h"
 #include "b200amg.h"
 
@@ -60,9 +61,44 @@ typedef struct mirror_s {
    int              first_row, first_col;   /* this rank's offset into the global host vectors */
    int             *starts;   /* distributed mode: (levels) x (nranks+1) row starts; NULL otherwise */
    int              num_levels, repl_level;
+   /* the host matrix the mirror was uploaded from (level 0 of a hierarchy) and its stamp at upload time: an
+    * application that changes values in place (IJ SetValues / AddToValues + Assemble between time steps, or a
+    * lagged preconditioner on a changed A) must not keep solving with the old device copy */
+   hypre_ParCSRMatrix *src;
+   unsigned long long  stamp;
    struct mirror_s *next;
 } mirror_t;
 static mirror_t *g_mirrors = NULL;
+
+/* Cheap version stamp of a ParCSR matrix: array addresses, sizes and ~4096 sampled values of the diag / offd
+ * blocks (FNV-1a).  Checked at every solve / SpMV entry (microseconds); an in-place update of the coefficients
+ * changes it and the mirror is uploaded again.  An application that changes only entries the sample misses calls
+ * hypre_b200_matrix_changed(A); HYPRE_IJMatrixAssemble does it by itself. */
+static unsigned long long fnv_mix(unsigned long long h, const void *p, size_t n)
+{
+   const unsigned char *b = (const unsigned char *) p;
+   size_t k;
+   for (k = 0; k < n; k++) { h ^= b[k]; h *= 1099511628211ULL; }
+   return h;
+}
+static unsigned long long matrix_stamp(hypre_ParCSRMatrix *A)
+{
+   unsigned long long h = 1469598103934665603ULL;
+   int blk;
+   for (blk = 0; blk < 2; blk++)
+   {
+      hypre_CSRMatrix *M = blk == 0 ? hypre_ParCSRMatrixDiag(A) : hypre_ParCSRMatrixOffd(A);
+      const HYPRE_Real *a = hypre_CSRMatrixData(M);
+      const HYPRE_Int  *ia = hypre_CSRMatrixI(M);
+      HYPRE_Int n = hypre_CSRMatrixNumRows(M);
+      HYPRE_Int nnz = (ia && n > 0) ? ia[n] : 0;
+      HYPRE_Int step = nnz / 2048 + 1, k;
+      h = fnv_mix(h, &a, sizeof(a)); h = fnv_mix(h, &ia, sizeof(ia)); h = fnv_mix(h, &nnz, sizeof(nnz));
+      for (k = 0; a && k < nnz; k += step) { h = fnv_mix(h, a + k, sizeof(HYPRE_Real)); }
+      if (a && nnz > 0) { h = fnv_mix(h, a + nnz - 1, sizeof(HYPRE_Real)); }
+   }
+   return h;
+}
 
 static int verbose(void)
 {
@@ -597,9 +633,54 @@ HYPRE_Int hypre_ParCSRMatrixDestroy(hypre_ParCSRMatrix *A)
    return next(A);
 }
 
+/* the coefficients of a host matrix changed: drop every device copy made from it (the next solve uploads again;
+ * a hierarchy is re-uploaded from the host hierarchy as it is -- new A on level 0, lagged coarse levels -- which
+ * is what the reference's CPU solve would use) */
+void hypre_b200_matrix_changed(void *parcsr)
+{
+   int again = 1;
+   while (again)
+   {
+      mirror_t *m;
+      again = 0;
+      for (m = g_mirrors; m; m = m->next)
+      {
+         if (m->src == (hypre_ParCSRMatrix *) parcsr) { mirror_drop(m->key); again = 1; break; }
+      }
+   }
+}
+
+static mirror_t *mirror_current(void *key)
+{
+   mirror_t *m = mirror_find(key);
+   if (m && m->src && m->stamp != matrix_stamp(m->src))
+   {
+      if (verbose()) { fprintf(stderr, "hypre_b200: coefficients of matrix %p changed, device copy dropped\n", (void *) m->src); }
+      mirror_drop(key);
+      m = NULL;
+   }
+   return m;
+}
+
+/* HYPRE_IJMatrixAssemble (src/IJ_mv/HYPRE_IJMatrix.c) closes a round of SetValues / AddToValues: whatever was
+ * uploaded from that matrix is stale */
+HYPRE_Int HYPRE_IJMatrixAssemble(HYPRE_IJMatrix matrix)
+{
+   typedef HYPRE_Int (*ij_assemble_fn)(HYPRE_IJMatrix);
+   static ij_assemble_fn next = NULL;
+   HYPRE_Int ierr;
+   if (!next) { next = (ij_assemble_fn) next_sym("HYPRE_IJMatrixAssemble"); }
+   ierr = next(matrix);
+   if (matrix && hypre_IJMatrixObjectType((hypre_IJMatrix *) matrix) == HYPRE_PARCSR && hypre_IJMatrixObject((hypre_IJMatrix *) matrix))
+   {
+      hypre_b200_matrix_changed(hypre_IJMatrixObject((hypre_IJMatrix *) matrix));
+   }
+   return ierr;
+}
+
 static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
 {
-   mirror_t *m = mirror_find(amg_data);
+   mirror_t *m = mirror_current(amg_data);
    if (m) { return m; }
    {
       int *starts = NULL, repl = 1 << 30;
@@ -607,6 +688,7 @@ static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
       if (!amg) { free(starts); return NULL; }
       m = (mirror_t *) calloc(1, sizeof(mirror_t));
       m->key = amg_data; m->amg = amg;
+      m->src = hypre_ParAMGDataAArray(amg_data)[0]; m->stamp = matrix_stamp(m->src);
       m->starts = starts; m->repl_level = repl; m->num_levels = (int) hypre_ParAMGDataNumLevels(amg_data);
       b200_amg_level_matrix(amg, 0, &m->A);
       if (g_nranks > 1 && !g_native)
@@ -623,7 +705,7 @@ static mirror_t *mirror_for_amg(hypre_ParAMGData *amg_data)
 
 static mirror_t *mirror_for_matrix(hypre_ParCSRMatrix *A)
 {
-   mirror_t *m = mirror_find(A);
+   mirror_t *m = mirror_current(A);
    if (m) { return m; }
    {
       b200_parcsr *dA = NULL;
@@ -642,6 +724,7 @@ static mirror_t *mirror_for_matrix(hypre_ParCSRMatrix *A)
       if (!dA) { return NULL; }
       m = (mirror_t *) calloc(1, sizeof(mirror_t));
       m->key = A; m->A = dA; m->first_row = first_row; m->first_col = first_col;
+      m->src = A; m->stamp = matrix_stamp(A);
       m->next = g_mirrors; g_mirrors = m;
    }
    return m;

@@ -1,0 +1,42 @@
+"""the reference's own regression jobs as a gate for the B200 backend.
+
+Every `mpirun -np N ./ij ...` line of src/test/TEST_ij/{smoother,solvers,default,coarsening,interp}.jobs whose
+options the device path accepts is run with the reference's UNCHANGED driver on N ranks / N GPUs
+(hypre_b200/lib/ij_b200_mp over hypre_b200/lib/mpirun_shim: hypre's own distributed setup, the solve on the
+devices) and compared with the reference's recorded values (<suite>.saved, tests/golden/ref_saved_goldens.json:
+iteration counts exactly, residual norms / factors / complexities to the printed digits) -- what
+src/test/runtest.sh:400-428 does for the reference.  Options without a device implementation must be REJECTED
+loudly (status "rejected"), never answered by the CPU.  Needs one GPU per rank: jobs with more ranks than GPUs
+are skipped, the whole test below 2 GPUs.  Table of the last full run: profiles/r02_saved_jobs_b200_*.json."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = [pytest.mark.gpu]
+
+
+def _gpus():
+    try:
+        r = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=30)
+        return sum(1 for l in r.stdout.splitlines() if l.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+def test_reference_saved_jobs_gate_the_device_backend(built):
+    n = _gpus()
+    if n < 2:
+        pytest.skip("needs one GPU per rank (the reference's jobs use 2-8 ranks)")
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "run_saved_jobs_b200.py"), "--max-ranks", str(min(n, 8))],
+                       capture_output=True, text=True, timeout=3000)
+    open(os.path.join(out, "saved_jobs_b200_%dgpu.json" % n), "w").write(p.stdout)
+    rep = json.loads(p.stdout)
+    bad = [j for j in rep["jobs"] if j["status"] in ("mismatch", "failed")]
+    assert not bad, bad[:5]
+    assert rep["counts"]["pass"] > 0, rep["counts"]

@@ -459,6 +459,55 @@ def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, 
             for o in (pcg, amg, A):
                 o.destroy()
         finally:
-            L.b200_set_tail_limit(4000000)
+            L.b200_set_tail_limit(0)
     for a, b_ in zip(out[0], out[4000000]):
         assert np.array_equal(a, b_), name
+
+
+def _values_view(H, A):
+    """writable views of hypre's own coefficient arrays (diag block) of a ParCSR matrix"""
+    L = H.lib()
+    n, nc, no = C.c_int(), C.c_int(), C.c_int()
+    di, dj, oi, oj = (C.POINTER(C.c_int)() for _ in range(4))
+    da, oa = C.POINTER(C.c_double)(), C.POINTER(C.c_double)()
+    L.hb_matrix_blocks(A.h, C.byref(n), C.byref(nc), C.byref(di), C.byref(dj), C.byref(da),
+                       C.byref(no), C.byref(oi), C.byref(oj), C.byref(oa))
+    nnz = np.ctypeslib.as_array(di, (n.value + 1,))[-1]
+    return np.ctypeslib.as_array(da, (int(nnz),))
+
+
+def test_in_place_coefficient_update_reaches_the_device(H, ctx):
+    """an application that changes the coefficients of the SAME hypre_ParCSRMatrix between solves (time stepping;
+    a lagged preconditioner on a changed A) must not keep solving the old system: the binding stamps the host
+    matrix at upload time, notices the change and uploads again (AMG-PCG: new A on level 0, lagged coarse levels,
+    as the reference's CPU solve)"""
+    H.set_device_path(True)
+    A, b, x, amg, pcg = O.build_case(H, "lap7_24_rlx16")
+    H.clear_errors()
+    pcg.Solve(A, b, x)
+    x1, it1 = x.numpy().copy(), pcg.num_iterations
+    vals = _values_view(H, A)
+    vals *= 2.0                                  # 2A x = b  ->  x/2; the hierarchy keeps the old coarse levels
+    x.numpy()[:] = 0.0
+    H.clear_errors()
+    pcg.Solve(A, b, x)
+    x2 = x.numpy().copy()
+    H.set_device_path(False)
+    try:
+        x.numpy()[:] = 0.0
+        H.clear_errors()
+        pcg.Solve(A, b, x)                       # the reference on the same (changed) objects
+        xr, itr = x.numpy().copy(), pcg.num_iterations
+    finally:
+        H.set_device_path(True)
+    assert np.allclose(x2, 0.5 * x1, rtol=1e-6, atol=1e-10)
+    np.testing.assert_allclose(x2, xr, rtol=1e-8, atol=1e-11)
+    # SpMV through the public API sees the new coefficients, too
+    y = A.vector(0.0)
+    xx = A.vector(1.0)
+    H.lib().HYPRE_ParCSRMatrixMatvec(1.0, A.h, xx.h, 0.0, y.h)
+    vals *= 3.0
+    y2 = A.vector(0.0)
+    H.lib().HYPRE_ParCSRMatrixMatvec(1.0, A.h, xx.h, 0.0, y2.h)
+    np.testing.assert_allclose(y2.numpy(), 3.0 * y.numpy(), rtol=1e-14)
+    H.clear_errors()
