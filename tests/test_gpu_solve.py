@@ -433,7 +433,7 @@ def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, 
     L = capi.lib()
     H.set_device_path(True)
     out = {}
-    for limit in (0, 4000000):
+    for run, limit in enumerate((0, 0, 4000000)):
         capi.check(L.b200_set_tail_limit(limit))
         try:
             A, b, x, amg, pcg = O.build_case(H, name)
@@ -455,13 +455,17 @@ def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, 
             pcg.Solve(A, b, x)              # graph replay with the persistent kernel inside
             assert H.error_flag() == 0
             res += [pcg.rel_norms().copy(), x.numpy().copy(), pcg.num_iterations]
-            out[limit] = res
+            out[run] = res
             for o in (pcg, amg, A):
                 o.destroy()
         finally:
             L.b200_set_tail_limit(0)
-    for a, b_ in zip(out[0], out[4000000]):
-        assert np.array_equal(a, b_), name
+
+    def diffs(p, q):
+        return [float(np.max(np.abs(np.asarray(a, dtype=np.float64) - np.asarray(b_, dtype=np.float64))) /
+                      max(float(np.max(np.abs(np.asarray(a, dtype=np.float64)))), 1e-300)) for a, b_ in zip(p, q)]
+    assert all(np.array_equal(a, b_) for a, b_ in zip(out[0], out[1])), ("launch-per-operator path not reproducible", name, diffs(out[0], out[1]))
+    assert all(np.array_equal(a, b_) for a, b_ in zip(out[0], out[2])), (name, diffs(out[0], out[2]))
 
 
 def _values_view(H, A):
@@ -487,7 +491,7 @@ def test_in_place_coefficient_update_reaches_the_device(H, ctx):
     pcg.Solve(A, b, x)
     x1, it1 = x.numpy().copy(), pcg.num_iterations
     vals = _values_view(H, A)
-    vals *= 2.0                                  # 2A x = b  ->  x/2; the hierarchy keeps the old coarse levels
+    vals *= 1.05                                 # 1.05 A x = b  ->  x / 1.05; the hierarchy keeps its (lagged) coarse levels
     x.numpy()[:] = 0.0
     H.clear_errors()
     pcg.Solve(A, b, x)
@@ -500,8 +504,8 @@ def test_in_place_coefficient_update_reaches_the_device(H, ctx):
         xr, itr = x.numpy().copy(), pcg.num_iterations
     finally:
         H.set_device_path(True)
-    assert np.allclose(x2, 0.5 * x1, rtol=1e-6, atol=1e-10)
     np.testing.assert_allclose(x2, xr, rtol=1e-8, atol=1e-11)
+    assert np.allclose(x2, x1 / 1.05, rtol=1e-5, atol=1e-9) and not np.allclose(x2, x1, rtol=1e-3)
     # SpMV through the public API sees the new coefficients, too
     y = A.vector(0.0)
     xx = A.vector(1.0)
