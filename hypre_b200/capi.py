@@ -97,6 +97,7 @@ def lib():
         "b200_vec_dot": (i, [vp, i, vp, vp, c_dbl_p]),
         "b200_parcsr_create": (i, [vp, i, i, vp, vp, vp, i, vp, vp, vp, i, vp, vp, vp, i, vp, vp, c_void_pp]),
         "b200_parcsr_destroy": (i, [vp]),
+        "b200_parcsr_set_gs_blocks": (i, [vp, i, vp]),
         "b200_parcsr_info": (i, [vp, c_int_p, c_int_p, C.POINTER(ll), c_int_p, c_int_p]),
         "b200_set_layout_override": (i, [i, i]),
         "b200_set_compression": (i, [i, i]),

@@ -225,6 +225,7 @@ struct b200_parcsr {
    DMat lower;
    double *d_diagonal = nullptr;
    bool zero_diagonal = false;
+   std::vector<int> gs_block_of;     // gathered level: owner block of every row (two-stage GS stays block-local)
    // host copies kept for derived operators
    HostCsr h_diag, h_offd;
    // halo plan (hypre_ParCSRCommPkg)

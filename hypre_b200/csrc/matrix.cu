@@ -302,6 +302,19 @@ int parcsr_ensure_T(b200_parcsr *A)
    return B200_OK;
 }
 
+// Owner blocks of a gathered (replicated) level: the strict lower triangle used by two-stage Gauss-Seidel is then
+// that of the owners' diagonal blocks, as in the reference's distributed sweep (par_relax.c:1505-1588 works on the
+// rank's diag block only; couplings to other ranks' rows are treated Jacobi-like).  rows_per_block[b] = rows of block b.
+extern "C" int b200_parcsr_set_gs_blocks(b200_parcsr *A, int n_blocks, const int *rows_per_block)
+{
+   ARG_CHECK(A != nullptr && n_blocks >= 1 && rows_per_block != nullptr && !A->hasL);
+   A->gs_block_of.assign((size_t)A->n_rows, 0);
+   int r = 0;
+   for (int b = 0; b < n_blocks; b++) { for (int k = 0; k < rows_per_block[b] && r < A->n_rows; k++) { A->gs_block_of[(size_t)r++] = b; } }
+   ARG_CHECK(r == A->n_rows);
+   return B200_OK;
+}
+
 // strict lower triangle of the diag block (local column < row) and the diagonal
 // (first entry of each diag row by hypre's convention; we search for it so that a
 // missing diagonal is detected) for the two-stage Gauss-Seidel smoother
@@ -323,7 +336,8 @@ int parcsr_ensure_L(b200_parcsr *A)
       if (dv == 0.0) { A->zero_diagonal = true; }
       for (int k = h.i[r]; k < h.i[r + 1]; k++)
       {
-         if (h.j[k] < r) { L.j.push_back(h.j[k]); L.a.push_back(h.a[k]); }
+         const bool same_block = A->gs_block_of.empty() || (h.j[k] < h.n_rows && A->gs_block_of[(size_t)h.j[k]] == A->gs_block_of[(size_t)r]);
+         if (h.j[k] < r && same_block) { L.j.push_back(h.j[k]); L.a.push_back(h.a[k]); }
       }
       L.i[r + 1] = (int)L.j.size();
    }

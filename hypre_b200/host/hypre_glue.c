@@ -362,6 +362,94 @@ static b200_parcsr *upload_parcsr_row_slab(hypre_ParCSRMatrix *A, int r0, int r1
 }
 
 /* hypre_ParAMGData (after the reference's host setup) -> b200_amg */
+/* ---- native mode, replicated coarse levels: a small level is gathered on every rank and runs without communication
+ * (the reference's answer to idle ranks on coarse grids is seq_threshold / hypre_seqAMGCycle, par_cycle.c:362-369;
+ * hypre_ParCSRMatrixToCSRMatrixAll leaves out the ranks that own no rows, so the gather is done here). */
+#ifndef HYPRE_SEQUENTIAL
+/* this rank's rows of A with GLOBAL column indices, diag entries first (the diagonal stays the first entry) */
+static void local_rows_global_cols(hypre_ParCSRMatrix *A, int **ri, int **rj, double **ra)
+{
+   hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A), *o = hypre_ParCSRMatrixOffd(A);
+   const HYPRE_Int *di = hypre_CSRMatrixI(d), *dj = hypre_CSRMatrixJ(d), *oi = hypre_CSRMatrixI(o), *oj = hypre_CSRMatrixJ(o);
+   const HYPRE_Real *da = hypre_CSRMatrixData(d), *oa = hypre_CSRMatrixData(o);
+   const HYPRE_BigInt *cmap = hypre_ParCSRMatrixColMapOffd(A);
+   const HYPRE_BigInt c0 = hypre_ParCSRMatrixFirstColDiag(A);
+   const HYPRE_Int n = hypre_CSRMatrixNumRows(d), no = hypre_CSRMatrixNumCols(o);
+   HYPRE_Int r, k, nnz = (n > 0 ? di[n] : 0) + ((n > 0 && no > 0) ? oi[n] : 0), p = 0;
+   *ri = (int *) calloc((size_t) n + 1, sizeof(int));
+   *rj = (int *) malloc(sizeof(int) * (size_t) (nnz > 0 ? nnz : 1));
+   *ra = (double *) malloc(sizeof(double) * (size_t) (nnz > 0 ? nnz : 1));
+   for (r = 0; r < n; r++)
+   {
+      for (k = di[r]; k < di[r + 1]; k++) { (*rj)[p] = (int) (c0 + dj[k]); (*ra)[p++] = da[k]; }
+      if (no > 0) { for (k = oi[r]; k < oi[r + 1]; k++) { (*rj)[p] = (int) cmap[oj[k]]; (*ra)[p++] = oa[k]; } }
+      (*ri)[r + 1] = p;
+   }
+}
+
+/* the whole matrix on every rank: rows in global order; rows_of[r] = rows owned by rank r (returned for the vectors) */
+static b200_parcsr *upload_parcsr_gathered(hypre_ParCSRMatrix *A, int *rows_of)
+{
+   MPI_Comm comm = hypre_ParCSRMatrixComm(A);
+   int *li, *lj, *cnt, *dsp, *ncnt, *ndsp, *gi, *gj, *glen, r, n_loc, nnz_loc, n_all = 0, nnz_all = 0;
+   double *la, *ga;
+   b200_parcsr *dA = NULL;
+   local_rows_global_cols(A, &li, &lj, &la);
+   n_loc = (int) hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(A));
+   nnz_loc = li[n_loc];
+   cnt = (int *) calloc((size_t) g_nranks, sizeof(int)); dsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+   ncnt = (int *) calloc((size_t) g_nranks, sizeof(int)); ndsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+   hypre_MPI_Allgather(&n_loc, 1, HYPRE_MPI_INT, cnt, 1, HYPRE_MPI_INT, comm);
+   hypre_MPI_Allgather(&nnz_loc, 1, HYPRE_MPI_INT, ncnt, 1, HYPRE_MPI_INT, comm);
+   for (r = 0; r < g_nranks; r++) { dsp[r + 1] = dsp[r] + cnt[r]; ndsp[r + 1] = ndsp[r] + ncnt[r]; if (rows_of) { rows_of[r] = cnt[r]; } }
+   n_all = dsp[g_nranks]; nnz_all = ndsp[g_nranks];
+   glen = (int *) calloc((size_t) n_all + 1, sizeof(int));
+   gi = (int *) calloc((size_t) n_all + 1, sizeof(int));
+   gj = (int *) malloc(sizeof(int) * (size_t) (nnz_all > 0 ? nnz_all : 1));
+   ga = (double *) malloc(sizeof(double) * (size_t) (nnz_all > 0 ? nnz_all : 1));
+   {
+      int *llen = (int *) calloc((size_t) n_loc + 1, sizeof(int));
+      for (r = 0; r < n_loc; r++) { llen[r] = li[r + 1] - li[r]; }
+      hypre_MPI_Allgatherv(llen, n_loc, HYPRE_MPI_INT, glen, cnt, dsp, HYPRE_MPI_INT, comm);
+      free(llen);
+   }
+   hypre_MPI_Allgatherv(lj, nnz_loc, HYPRE_MPI_INT, gj, ncnt, ndsp, HYPRE_MPI_INT, comm);
+   hypre_MPI_Allgatherv(la, nnz_loc, HYPRE_MPI_REAL, ga, ncnt, ndsp, HYPRE_MPI_REAL, comm);
+   for (r = 0; r < n_all; r++) { gi[r + 1] = gi[r] + glen[r]; }
+   if (b200_parcsr_create(glue_ctx(), n_all, (int) hypre_ParCSRMatrixGlobalNumCols(A), gi, gj, ga, 0, NULL, NULL, NULL,
+                          0, NULL, NULL, NULL, 0, NULL, NULL, &dA) != B200_OK) { dA = NULL; }
+   free(li); free(lj); free(la); free(cnt); free(dsp); free(ncnt); free(ndsp); free(glen); free(gi); free(gj); free(ga);
+   return dA;
+}
+
+/* this rank's rows of P with global (replicated) coarse columns: restriction onto the first replicated level ends with
+ * a sum over ranks, prolongation from it is local */
+static b200_parcsr *upload_parcsr_local_slab(hypre_ParCSRMatrix *P)
+{
+   int *li, *lj;
+   double *la;
+   b200_parcsr *dP = NULL;
+   local_rows_global_cols(P, &li, &lj, &la);
+   if (b200_parcsr_create(glue_ctx(), (int) hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(P)),
+                          (int) hypre_ParCSRMatrixGlobalNumCols(P), li, lj, la, 0, NULL, NULL, NULL,
+                          0, NULL, NULL, NULL, 0, NULL, NULL, &dP) != B200_OK) { dP = NULL; }
+   free(li); free(lj); free(la);
+   return dP;
+}
+
+/* a level vector (l1 norms, Chebyshev scaling) of a replicated level: every rank's part, in rank order */
+static double *gather_level_vector(MPI_Comm comm, const double *local, const int *rows_of)
+{
+   int r, *dsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+   double *all, dummy = 0.0;
+   for (r = 0; r < g_nranks; r++) { dsp[r + 1] = dsp[r] + rows_of[r]; }
+   all = (double *) calloc((size_t) (dsp[g_nranks] > 0 ? dsp[g_nranks] : 1), sizeof(double));
+   hypre_MPI_Allgatherv((void *) (local ? local : &dummy), rows_of[g_rank], HYPRE_MPI_REAL, all, (HYPRE_Int *) rows_of, dsp, HYPRE_MPI_REAL, comm);
+   free(dsp);
+   return all;
+}
+#endif
+
 static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *repl_out)
 {
    b200_ctx  *ctx = glue_ctx();
@@ -377,6 +465,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    int relax_type[4], num_sweeps[4], l, k, uses_cheby = 0, uses_jac0 = 0;
    int repl = 1 << 30;   /* distributed mode: first level replicated on every rank */
    int *starts = NULL;   /* distributed mode: (nl+1) x (g_nranks+1) row starts per level */
+   int *rows_of = NULL;  /* native mode: (nl) x (g_nranks) rows owned by every rank on the replicated levels */
 #define STARTS(l) (starts + (size_t)(l) * (g_nranks + 1))
 
    if (!ctx) { return NULL; }
@@ -460,15 +549,49 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          }
       }
    }
-   if (b200_amg_create(ctx, nl, &amg) != B200_OK) { free(starts); return NULL; }
+#ifndef HYPRE_SEQUENTIAL
+   if (g_nranks > 1 && g_native)
+   {
+      /* same rule as the replicated-setup mode, on the GLOBAL size of the level */
+      const char *e = getenv("B200_REPL_NNZ");
+      double limit = e ? atof(e) : 8.0e6;
+      for (l = 1; l < nl && limit > 0.0; l++)
+      {
+         hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]), *o = hypre_ParCSRMatrixOffd(A_array[l]);
+         HYPRE_Real loc = (HYPRE_Real) hypre_CSRMatrixNumNonzeros(d) + (HYPRE_Real) hypre_CSRMatrixNumNonzeros(o), all = 0.0;
+         hypre_MPI_Allreduce(&loc, &all, 1, HYPRE_MPI_REAL, hypre_MPI_SUM, hypre_ParCSRMatrixComm(A_array[l]));
+         if (all <= limit && hypre_ParCSRMatrixGlobalNumRows(A_array[l]) <= (1 << 18)) { repl = l; break; }
+      }
+      rows_of = (int *) calloc((size_t) nl * g_nranks + 1, sizeof(int));
+   }
+#endif
+   if (b200_amg_create(ctx, nl, &amg) != B200_OK) { free(starts); free(rows_of); return NULL; }
    for (l = 0; l < nl; l++)
    {
       b200_parcsr *dA, *dP;
       if (g_native)
       {
-         /* hypre's own distributed objects: what this rank owns, with the CommPkg hypre negotiated */
-         dA = upload_parcsr(A_array[l]);
-         dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+#ifndef HYPRE_SEQUENTIAL
+         if (l >= repl)
+         {
+            /* replicated level: gathered on every rank; two-stage GS keeps the owners' blocks (the reference's
+             * lower triangles are those of the ranks' diag blocks, par_relax.c:1505-1588) */
+            dA = upload_parcsr_gathered(A_array[l], rows_of + (size_t) l * g_nranks);
+            if (dA) { b200_parcsr_set_gs_blocks(dA, g_nranks, rows_of + (size_t) l * g_nranks); }
+            dP = (l < nl - 1) ? upload_parcsr_gathered(P_array[l], NULL) : NULL;
+         }
+         else if (l + 1 == repl)
+         {
+            dA = upload_parcsr(A_array[l]);
+            dP = upload_parcsr_local_slab(P_array[l]);
+         }
+         else
+#endif
+         {
+            /* hypre's own distributed objects: what this rank owns, with the CommPkg hypre negotiated */
+            dA = upload_parcsr(A_array[l]);
+            dP = (l < nl - 1) ? upload_parcsr(P_array[l]) : NULL;
+         }
       }
       else if (g_nranks > 1 && l >= repl)
       {
@@ -493,7 +616,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          if (dA) { b200_parcsr_destroy(dA); }
          if (dP) { b200_parcsr_destroy(dP); }
          b200_amg_destroy(amg);
-         free(starts);
+         free(starts); free(rows_of);
          return NULL;
       }
    }
@@ -505,8 +628,10 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    {
       const int off = (starts && l < repl) ? STARTS(l)[g_rank] : 0;   /* this rank's slice of the level vectors */
       const double *l1d = (l1 && l1[l]) ? hypre_VectorData(l1[l]) + off : NULL;
-      double *diag0 = NULL;
+      double *diag0 = NULL, *l1_all = NULL, *ds_all = NULL;
       int status;
+      const int gathered = g_native && rows_of != NULL && l >= repl;
+      (void) gathered;
       if (uses_jac0)
       {
          /* the diagonal of this level (first entry of each row of the diag block) in the place of the l1 norms */
@@ -519,8 +644,15 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          }
          l1d = diag0 + off;
       }
+#ifndef HYPRE_SEQUENTIAL
+      if (gathered && (l1d != NULL || uses_jac0))
+      {
+         l1_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), l1d, rows_of + (size_t) l * g_nranks);
+         l1d = l1_all;
+      }
+#endif
       status = b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d);
-      free(diag0);
+      free(diag0); free(l1_all);
       if (status != B200_OK)
       {
          b200_amg_destroy(amg); free(starts); return NULL;
@@ -528,8 +660,17 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       if (uses_cheby && coefs && coefs[l])
       {
          const double *dsd = (ds && ds[l]) ? hypre_VectorData(ds[l]) + off : NULL;
-         if (b200_amg_set_level_cheby(amg, l, dsd, coefs[l], hypre_ParAMGDataChebyOrder(amg_data),
-                                      hypre_ParAMGDataChebyScale(amg_data)) != B200_OK)
+#ifndef HYPRE_SEQUENTIAL
+         if (gathered && ds && ds[l])
+         {
+            ds_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), dsd, rows_of + (size_t) l * g_nranks);
+            dsd = ds_all;
+         }
+#endif
+         status = b200_amg_set_level_cheby(amg, l, dsd, coefs[l], hypre_ParAMGDataChebyOrder(amg_data),
+                                           hypre_ParAMGDataChebyScale(amg_data));
+         free(ds_all);
+         if (status != B200_OK)
          {
             b200_amg_destroy(amg); free(starts); return NULL;
          }
@@ -543,6 +684,28 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       int status;
       if (!hypre_ParAMGDataGSSetup(amg_data)) { hypre_GaussElimSetup(amg_data, nl - 1, grt[3]); }
       hypre_MPI_Comm_size(hypre_ParCSRMatrixComm(Ac), &np);
+#ifndef HYPRE_SEQUENTIAL
+      if (g_native && repl < nl)
+      {
+         /* the coarsest level is replicated: every rank holds the whole dense matrix (gathered from the owners' rows)
+          * and solves locally -- no gather of the right-hand side per cycle */
+         MPI_Comm comm = hypre_ParCSRMatrixComm(Ac);
+         int *li, *lj, r, k, mine = (int) hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(Ac));
+         double *la, *dense_loc = (double *) calloc((size_t) (mine > 0 ? mine : 1) * (size_t) N, sizeof(double));
+         double *dense = (double *) calloc((size_t) N * (size_t) N, sizeof(double));
+         int *cnt = (int *) calloc((size_t) g_nranks, sizeof(int)), *dsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int));
+         int *rows = (int *) calloc((size_t) g_nranks, sizeof(int));
+         int sz = mine * (int) N;
+         local_rows_global_cols(Ac, &li, &lj, &la);
+         for (r = 0; r < mine; r++) { for (k = li[r]; k < li[r + 1]; k++) { dense_loc[(size_t) r * N + lj[k]] = la[k]; } }
+         hypre_MPI_Allgather(&sz, 1, HYPRE_MPI_INT, cnt, 1, HYPRE_MPI_INT, comm);
+         for (r = 0; r < g_nranks; r++) { dsp[r + 1] = dsp[r] + cnt[r]; rows[r] = (int) N; }
+         hypre_MPI_Allgatherv(dense_loc, sz, HYPRE_MPI_REAL, dense, cnt, dsp, HYPRE_MPI_REAL, comm);
+         status = b200_amg_set_coarse_dense(amg, N, dense, 0, rows);
+         free(li); free(lj); free(la); free(dense_loc); free(dense); free(cnt); free(dsp); free(rows);
+      }
+      else
+#endif
       if (g_native)
       {
          /* rows of the coarsest level per WORLD rank (hypre's comm_info is indexed by the ranks of the
@@ -572,7 +735,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    }
    if (starts_out) { *starts_out = starts; starts = NULL; }
    if (repl_out) { *repl_out = repl; }
-   free(starts);
+   free(starts); free(rows_of);
 #undef STARTS
    if (b200_amg_finalize(amg) != B200_OK) { b200_amg_destroy(amg); return NULL; }
    if (verbose())

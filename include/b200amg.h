@@ -94,6 +94,10 @@ int b200_parcsr_create(b200_ctx *ctx,
                        const int *send_map_elmts,
                        int num_recvs, const int *recv_procs, const int *recv_vec_starts,
                        b200_parcsr **A);
+/* A level gathered on every rank (replicated coarse level of a multi-rank hierarchy): rows_per_block[b] = rows owned
+ * by rank b.  Two-stage Gauss-Seidel then uses the strict lower triangle of the owners' diagonal blocks only, as the
+ * reference's distributed sweep does (hypre_BoomerAMGRelaxTwoStageGaussSeidelHost, par_relax.c:1505-1588). */
+int b200_parcsr_set_gs_blocks(b200_parcsr *A, int n_blocks, const int *rows_per_block);
 int b200_parcsr_destroy(b200_parcsr *A);
 int b200_parcsr_info(const b200_parcsr *A, int *n_rows, int *n_cols, long long *nnz,
                      int *layout /* 0 = CSR-vector, 1 = sliced-ELL, 2 = sliced-ELL with rows sorted in 256-row windows */, int *lanes_per_row);

@@ -433,10 +433,11 @@ def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, 
     L = capi.lib()
     H.set_device_path(True)
     out = {}
-    for run, limit in enumerate((0, 0, 4000000)):
-        capi.check(L.b200_set_tail_limit(limit))
-        try:
-            A, b, x, amg, pcg = O.build_case(H, name)
+    A, b, x, amg, pcg = O.build_case(H, name)      # ONE host setup (the reference's threaded setup is not bit-reproducible)
+    try:
+        for run, limit in enumerate((0, 0, 4000000)):
+            capi.check(L.b200_set_tail_limit(limit))
+            H.lib().hypre_b200_matrix_changed(A.h)        # drop the device copy: the next use uploads with the new setting
             damg = amg.device_mirror()
             lvl = C.c_int()
             capi.check(L.b200_amg_tail_level(damg, C.byref(lvl)))
@@ -451,15 +452,16 @@ def test_persistent_coarse_kernel_is_bit_identical_to_separate_launches(H, ctx, 
                 capi.check(L.b200_amg_cycle(damg, df.ptr, du.ptr, 0))      # second cycle: program found in the cache
                 res.append(du.get())
                 df.free(); du.free()
+            x.numpy()[:] = 0.0
             H.clear_errors()
             pcg.Solve(A, b, x)              # graph replay with the persistent kernel inside
             assert H.error_flag() == 0
             res += [pcg.rel_norms().copy(), x.numpy().copy(), pcg.num_iterations]
             out[run] = res
-            for o in (pcg, amg, A):
-                o.destroy()
-        finally:
-            L.b200_set_tail_limit(0)
+    finally:
+        L.b200_set_tail_limit(0)
+        for o in (pcg, amg, A):
+            o.destroy()
 
     def diffs(p, q):
         return [float(np.max(np.abs(np.asarray(a, dtype=np.float64) - np.asarray(b_, dtype=np.float64))) /
@@ -513,5 +515,5 @@ def test_in_place_coefficient_update_reaches_the_device(H, ctx):
     vals *= 3.0
     y2 = A.vector(0.0)
     H.lib().HYPRE_ParCSRMatrixMatvec(1.0, A.h, xx.h, 0.0, y2.h)
-    np.testing.assert_allclose(y2.numpy(), 3.0 * y.numpy(), rtol=1e-14)
+    np.testing.assert_allclose(y2.numpy(), 3.0 * y.numpy(), rtol=1e-14, atol=1e-13)
     H.clear_errors()
