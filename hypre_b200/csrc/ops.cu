@@ -183,6 +183,9 @@ struct FChebyFirst0 { static constexpr int NRED = 0; __device__ void init() {} i
 struct FGsFirst0 { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *d; double *z;
    __device__ void operator()(int i, double *) const { z[i] = __ddiv_rn(MUL(w, f[i]), d[i]); } };
 
+template <> struct EpiHeavy<EpiChebyZero>    { static constexpr bool value = true; };
+template <> struct EpiHeavy<EpiMatvecDotDir> { static constexpr bool value = true; };
+
 // ---------------------------------------------------------------- persistent cycle kernel (tail.cuh)
 template <> struct TailKind<EpiMatvec>            { static constexpr int value = TK_MATVEC; };
 template <> struct TailKind<EpiJacobiT<false>>    { static constexpr int value = TK_JACOBI; };

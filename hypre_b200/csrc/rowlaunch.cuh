@@ -69,12 +69,12 @@ static int launch_rows_layout(b200_ctx *ctx, const DMat &D, const HaloArgs &h, c
       int grid = rows_grid(D.n_slices, ROWK_BLOCK / 32, D.cfmt == CFMT_PAT8 ? g_rows_waves : 4);
       HaloArgs hh = h;
       hh.chunked = D.cfmt == CFMT_PAT8 ? g_rows_chunked : (g_rows_chunked > 1);
-      const int variant = D.cfmt == CFMT_PAT8 ? (g_pat_regs ? 1 : 0) : (D.zpad ? 1 : 0);
+      const int variant = D.cfmt == CFMT_PAT8 ? 0 : (D.zpad ? 1 : 0);
       switch (D.cfmt ? D.cfmt + 8 * variant : 0)
       {
 #define CASE_C(TT) case TT: LAUNCH(ctx, (rows_kernel<-(TT), HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
          CASE_C(CFMT_VAL8) CASE_C(CFMT_VAL16) CASE_C(CFMT_VAL64) CASE_C(CFMT_PAT8)
-         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8) CASE_C(CFMT_PAT8 + 8)
+         CASE_C(CFMT_VAL8 + 8) CASE_C(CFMT_VAL16 + 8) CASE_C(CFMT_VAL64 + 8)
 #undef CASE_C
          default: LAUNCH(ctx, (rows_kernel<0, HALO, Epi>), grid, ROWK_BLOCK, 0, V, hh, x, epi, rc); break;
       }

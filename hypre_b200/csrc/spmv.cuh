@@ -295,7 +295,8 @@ __device__ __forceinline__ double pat_word(unsigned h, const unsigned *&lp, int 
 // entries behind them multiply 0.0 with a column of the row itself), 10-31 first lane-word group.
 // (Measured and dropped, profiles/r02_fmt_probe_*.jsonl: the dictionary as a kernel parameter read through
 // indexed LDC -- twice as slow as the shared-memory lookups; a grid of one wave of resident blocks -- 1.5x slower
-// than four waves; 40 / 48 registers per thread -- slower than 32.)
+// than four waves; 40 / 48 registers per thread -- slower than 32; the decoded header of lane-uniform slices cached
+// in registers from one slice to the next at 64 registers / 4 blocks per SM -- 1.8x slower.)
 template <class XF>
 __device__ __forceinline__ double rowsum_pat(const MatView &D, const uint4 &h0, const uint4 *hdr, int lane, int row,
                                              const double *__restrict__ x, const XF &xf, const double2 *s_pat)
@@ -308,56 +309,6 @@ __device__ __forceinline__ double rowsum_pat(const MatView &D, const uint4 &h0, 
    if (nw > 2) { t = pat_word(h0.w, lp, row, t, x, xf, s_pat); }
    const unsigned *hw = reinterpret_cast<const unsigned *>(hdr) + 1;
    for (unsigned i = 3; i < nw; i++) { t = pat_word(__ldg(hw + i), lp, row, t, x, xf, s_pat); }
-   return t;
-}
-
-// Second instantiation of the pattern kernel (variant 1, 64 registers / 4 blocks per SM): slices whose header is
-// lane-uniform and at most 8 entries wide (the interior of a 7-pt / 5-pt stencil) keep the DECODED header -- the
-// (value, delta) of every entry -- in registers from one slice to the next.  A warp walks consecutive slices of
-// neighbouring grid lines, whose headers are identical, so the dictionary lookups (18 of the 33 load/store-unit
-// wavefronts per slice in the ncu profile of variant 0, and a third of its instructions) disappear, and all
-// gathers of a row are issued back to back before the first fma.  Same products, same order.
-struct PatCache {
-   unsigned hy, hz;           // header words the registers below were decoded from
-   double   v[8];
-   int      d[8];
-};
-
-template <class XF>
-__device__ __forceinline__ double rowsum_pat_cached(const MatView &D, const uint4 &h0, const uint4 *hdr, int lane, int row,
-                                                    const double *__restrict__ x, const XF &xf, const double2 *s_pat,
-                                                    PatCache &pc)
-{
-   const unsigned nw = h0.x & 0xFFu;
-   const unsigned hz = nw > 1 ? h0.z : 0xFEFEFEFEu;                     // 0xFE is no pattern code (PAT_CAP = 254)
-   const bool uni = nw >= 1 && nw <= 2 && __vcmpeq4(h0.y, 0xFFFFFFFFu) == 0u && __vcmpeq4(hz, 0xFFFFFFFFu) == 0u;
-   if (!uni) { return rowsum_pat(D, h0, hdr, lane, row, x, xf, s_pat); }
-   if (h0.y != pc.hy || hz != pc.hz)
-   {
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-      {
-         const double2 pd = s_pat[(h0.y >> (8 * j)) & 0xFFu];
-         pc.v[j] = pd.x; pc.d[j] = __double2loint(pd.y);
-      }
-      if (nw > 1)
-      {
-#pragma unroll
-         for (int j = 0; j < 4; j++)
-         {
-            const double2 pd = s_pat[(hz >> (8 * j)) & 0xFFu];
-            pc.v[4 + j] = pd.x; pc.d[4 + j] = __double2loint(pd.y);
-         }
-      }
-      pc.hy = h0.y; pc.hz = hz;
-   }
-   const int n_ent = 4 * ((int)nw - 1) + (int)((h0.x >> 8) & 3u) + 1;      // entries of the longest row (warp-uniform)
-   double xv[8];
-#pragma unroll
-   for (int j = 0; j < 8; j++) { if (j < n_ent) { xv[j] = xf.template xval<false>(x, row + pc.d[j]); } }
-   double t = 0.0;
-#pragma unroll
-   for (int j = 0; j < 8; j++) { if (j < n_ent) { t = fma(pc.v[j], xv[j], t); } }
    return t;
 }
 
@@ -528,12 +479,9 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          s_end = g_end;
          step = gridDim.x * wpb;
       }
-      constexpr bool PAT_CACHED = T < 0 && FMT == CFMT_PAT8 && ((-T) >> 3) == 1;
       const uint4 *hdr = reinterpret_cast<const uint4 *>(D.c_code);
       uint4 h_cur = make_uint4(0u, 0u, 0u, 0u);
       if (FMT == CFMT_PAT8 && slice < s_end) { h_cur = __ldg(hdr + (size_t)slice * D.aux); }
-      PatCache pc;
-      pc.hy = 0xFFFFFFFFu; pc.hz = 0xFFFFFFFFu;        // matches no lane-uniform header
       for (; slice < s_end; slice += step)
       {
          int row = (slice << 5) + lane;
@@ -546,8 +494,7 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
             // the header of the warp's next slice travels while this one is processed
             uint4 h_next = make_uint4(0u, 0u, 0u, 0u);
             if (slice + step < s_end) { h_next = __ldg(hdr + (size_t)(slice + step) * D.aux); }
-            if (PAT_CACHED) { t = rowsum_pat_cached(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi, s_tab, pc); }
-            else { t = rowsum_pat(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi, s_tab); }
+            t = rowsum_pat(D, h_cur, hdr + (size_t)slice * D.aux, lane, live ? row : D.n_rows - 1, x, epi, s_tab);
             h_cur = h_next;
          }
          else
@@ -615,17 +562,21 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
 
 // resident blocks per SM: 8 x 256 threads at 32 registers hide the DRAM latency of the streaming kernels;
 // the second PAT8 instantiation trades occupancy for registers (the four gathers of a header word in flight)
-template <int T> struct RowsKernelCfg {
+// Epilogues whose gathered operand is composite (two vectors read per entry: EpiChebyZero, EpiMatvecDotDir) spill at
+// 32 (and 40) registers on the thread-per-row kernels; they run at 48 registers / 5 blocks per SM (specialised in ops.cu).
+template <class Epi> struct EpiHeavy { static constexpr bool value = false; };
+
+template <int T, class Epi> struct RowsKernelCfg {
    static constexpr int FMT = T < 0 ? ((-T) & 7) : 0;
    static constexpr int VAR = T < 0 ? ((-T) >> 3) : 0;
    static constexpr bool PAT = FMT == CFMT_PAT8;
    static constexpr bool SMEM_TAB = PAT || (VAR == 1 && FMT == CFMT_VAL8);
-   static constexpr int MIN_BLOCKS = (PAT && VAR == 1) ? 4 : 8;
+   static constexpr int MIN_BLOCKS = (T <= 0 && EpiHeavy<Epi>::value) ? 5 : 8;
 };
 
 // All rows of the diag block.
 template <int T, int HALO, class Epi>
-__global__ void __launch_bounds__(ROWK_BLOCK, RowsKernelCfg<T>::MIN_BLOCKS)
+__global__ void __launch_bounds__(ROWK_BLOCK, RowsKernelCfg<T, Epi>::MIN_BLOCKS)
 rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi_arg, RedCtx rc)
 {
    RETURN_IF_STOPPED(rc);
@@ -636,7 +587,7 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi_arg, Re
    for (int k = 0; k < (Epi::NRED > 0 ? Epi::NRED : 1); k++) { red[k] = 0.0; }
 
    constexpr bool P2P = (HALO == HALO_FWD || HALO == HALO_REV);
-   using Cfg = RowsKernelCfg<T>;
+   using Cfg = RowsKernelCfg<T, Epi>;
    // pattern dictionary (value, delta) / u8 value dictionary, staged once per block
    __shared__ double2 s_tab[Cfg::SMEM_TAB ? 256 : 1];
    if (Cfg::SMEM_TAB)
