@@ -95,6 +95,7 @@ def lib():
         "b200_vec_scale": (i, [vp, i, d, vp]),
         "b200_vec_axpy": (i, [vp, i, d, vp, vp]),
         "b200_vec_dot": (i, [vp, i, vp, vp, c_dbl_p]),
+        "b200_vec_dot_noalloc": (i, [vp, i, vp, vp, vp]),
         "b200_parcsr_create": (i, [vp, i, i, vp, vp, vp, i, vp, vp, vp, i, vp, vp, vp, i, vp, vp, c_void_pp]),
         "b200_parcsr_destroy": (i, [vp]),
         "b200_parcsr_set_gs_blocks": (i, [vp, i, vp]),

@@ -77,6 +77,18 @@ int b200_vec_copy(b200_ctx *ctx, int n, const double *x, double *y);
 int b200_vec_scale(b200_ctx *ctx, int n, double a, double *y);
 int b200_vec_axpy(b200_ctx *ctx, int n, double a, const double *x, double *y);
 int b200_vec_dot(b200_ctx *ctx, int n, const double *x, const double *y, double *result_h);
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The local inner
+ * product <x, y> of device vectors, written to the device word d_result on the context's stream; no host
+ * synchronisation, no all-reduce, and NO allocation of any kind (no cudaMalloc / cudaFree, neither here nor in any
+ * set-up this call needs): the block partials of the reduction live in a file-scope static device array of
+ * B200_NOALLOC_DOT_MAX_BLOCKS doubles (128 KB, held by every GPU that loads the library until the process exits).
+ * n > B200_NOALLOC_DOT_MAX_N is rejected with B200_ERR_ARG.  All calls share that array: calls that overlap on one
+ * GPU (two streams, two contexts) race on it and must be serialised by the caller.  Deterministic for a given n;
+ * the summation order differs from b200_vec_dot's (same tolerance against the exact sum). */
+#define B200_NOALLOC_DOT_MAX_BLOCKS 16384
+#define B200_NOALLOC_DOT_MAX_N      67108864      /* 16384 blocks x 4096 elements */
+int b200_vec_dot_noalloc(b200_ctx *ctx, int n, const double *x, const double *y, double *d_result);
 
 /* ------------------------------------------------------------------ ParCSR
  * Device mirror of hypre_ParCSRMatrix (src/parcsr_mv/par_csr_matrix.h:27-84):
