@@ -126,6 +126,8 @@ def lib():
         "b200_amg_set_level_relax": (i, [vp, i, d, vp]),
         "b200_amg_set_level_cheby": (i, [vp, i, vp, vp, i, i]),
         "b200_amg_set_coarse_dense": (i, [vp, i, vp, i, vp]),
+        "b200_amg_set_relax_order": (i, [vp, i]),
+        "b200_amg_set_level_cf_marker": (i, [vp, i, vp]),
         "b200_amg_finalize": (i, [vp]),
         "b200_amg_set_precond_cycles": (i, [vp, i]),
         "b200_amg_cycle": (i, [vp, vp, vp, i]),

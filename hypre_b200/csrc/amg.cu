@@ -12,6 +12,7 @@ struct AmgLevel {
    double  relax_weight = 1.0;
    double *d_l1 = nullptr;
    double *d_ds = nullptr;
+   int    *d_cf = nullptr;      // CF_marker_array[level] (relax_order 1), nullptr on the coarsest level
    std::vector<double> coefs;
    int     cheby_order = 2, cheby_scale = 1;
    double *F = nullptr, *U = nullptr, *Ualt = nullptr;   // F/U owned for level > 0, Ualt for all
@@ -36,6 +37,7 @@ struct b200_amg {
    // a vector all-reduce, prolongation from it is local.
    int  repl_level = 1 << 30;
    int  precond_cycles = 1;    // cycles per preconditioner application (hypre_ParAMGDataMaxIter with tol 0)
+   int  relax_order = 0;       // hypre_ParAMGDataRelaxOrder: 1 = C then F points on the way down, F then C on the way up
    // levels >= tail_level run inside ONE persistent kernel per visit (tail.cuh): small CSR-vector levels without
    // communication (all of them on one rank, the replicated ones on several); INT_MAX = none
    int  tail_level = INT_MAX;
@@ -61,7 +63,7 @@ extern "C" int b200_amg_destroy(b200_amg *a)
    for (auto &l : a->L)
    {
       b200_parcsr_destroy(l.A); b200_parcsr_destroy(l.P);
-      cudaFree(l.d_l1); cudaFree(l.d_ds); cudaFree(l.F); cudaFree(l.U); cudaFree(l.Ualt);
+      cudaFree(l.d_l1); cudaFree(l.d_ds); cudaFree(l.d_cf); cudaFree(l.F); cudaFree(l.U); cudaFree(l.Ualt);
    }
    cudaFree(a->Vtemp); cudaFree(a->Ztemp); cudaFree(a->Ptemp); cudaFree(a->Rtemp);
    cudaFree(a->d_Ainv); cudaFree(a->d_fall);
@@ -117,6 +119,28 @@ extern "C" int b200_amg_set_level_cheby(b200_amg *a, int level, const double *ds
    ARG_CHECK(!scale || ds_h != nullptr);
    l.coefs.assign(coefs_h, coefs_h + (order > 4 ? 4 : order) + 1);
    l.cheby_order = order; l.cheby_scale = scale;
+   return B200_OK;
+}
+
+// CF-ordered relaxation (hypre_BoomerAMGRelaxIF, src/parcsr_ls/par_relax_interface.c:20-64; ij -CF 1): with
+// relax_order 1 every sweep on a non-coarsest level is two calls of the smoother, on the C points then the F points
+// on the way down and F then C on the way up (Jacobi types 0 / 7 / 18: hypre_ParVectorElmdivpyMarked on CF_marker;
+// the two-stage Gauss-Seidel sweeps ignore the marker and simply run twice; Chebyshev does not go through RelaxIF).
+extern "C" int b200_amg_set_relax_order(b200_amg *a, int relax_order)
+{
+   ARG_CHECK(a != nullptr && (relax_order == 0 || relax_order == 1));
+   a->relax_order = relax_order;
+   a->ctx->generation++;
+   return B200_OK;
+}
+
+extern "C" int b200_amg_set_level_cf_marker(b200_amg *a, int level, const int *cf_marker_h)
+{
+   ARG_CHECK(a != nullptr && level >= 0 && level < a->num_levels && a->L[level].A != nullptr);
+   AmgLevel &l = a->L[level];
+   a->ctx->generation++;
+   cudaFree(l.d_cf); l.d_cf = nullptr;
+   if (cf_marker_h) { B200_TRY(dev_upload(&l.d_cf, cf_marker_h, (size_t)l.n)); }
    return B200_OK;
 }
 
@@ -255,6 +279,11 @@ extern "C" int b200_amg_finalize(b200_amg *a)
          if ((t == 18 || t == 7) && L.d_l1 == nullptr) { b200_set_error("level %d: l1 norms missing", l); return B200_ERR_ARG; }
          if (t == 16 && L.coefs.empty()) { b200_set_error("level %d: Chebyshev data missing", l); return B200_ERR_ARG; }
          if (t == 11 || t == 12) { B200_TRY(parcsr_ensure_L(L.A)); }
+         if (a->relax_order == 1 && cp != 3 && a->num_levels > 1 && (t == 18 || t == 7) && L.d_cf == nullptr)
+         {
+            b200_set_error("level %d: relax_order 1 needs the CF marker (b200_amg_set_level_cf_marker)", l);
+            return B200_ERR_ARG;
+         }
       }
       if (l > 0)
       {
@@ -328,17 +357,18 @@ static int coarse_dense_solve(b200_amg *a, const double *f, double *u)
    return op_dense_matvec(c, n_local, a->coarse_n, a->d_Ainv, f, u);
 }
 
-static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const double *f, const FusedDot *fd = nullptr)
+static int relax_once(b200_amg *a, CycleState &s, int l, int relax_type, const double *f, const FusedDot *fd = nullptr,
+                      int points = 0)
 {
    AmgLevel &L = a->L[l];
    const int zg = s.zero[l] ? 1 : 0;
    switch (relax_type)
    {
       case 18: case 7:
-         if (zg) { B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, nullptr, U_cur(s, l), 1)); }
+         if (zg) { B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, nullptr, U_cur(s, l), 1, nullptr, L.d_cf, points)); }
          else
          {
-            B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, U_cur(s, l), U_other(s, l), 0, fd));
+            B200_TRY(op_l1jacobi(L.A, f, L.d_l1, L.relax_weight, U_cur(s, l), U_other(s, l), 0, fd, L.d_cf, points));
             s.cur[l] = 1 - s.cur[l];
          }
          break;
@@ -397,8 +427,9 @@ static int amg_cycle_body(b200_amg *a, const double *f, double *u, int zero_gues
       // first write may go to either buffer, so start where an odd number of swaps ends in `u`
       auto jac = [](int t) { return t == 18 || t == 7; };
       int swaps = 0; bool z = true;
-      for (int j = 0; j < a->num_sweeps[1]; j++) { if (jac(a->relax_type[1]) && !z) { swaps++; } z = false; }
-      for (int j = 0; j < a->num_sweeps[2]; j++) { if (jac(a->relax_type[2])) { swaps++; } }
+      const int calls = a->relax_order == 1 ? 2 : 1;       // CF ordering: two calls per sweep
+      for (int j = 0; j < a->num_sweeps[1] * calls; j++) { if (jac(a->relax_type[1]) && !z) { swaps++; } z = false; }
+      for (int j = 0; j < a->num_sweeps[2] * calls; j++) { if (jac(a->relax_type[2])) { swaps++; } }
       if (swaps & 1) { s.cur[0] = 1; }
    }
 
@@ -419,9 +450,16 @@ static int amg_cycle_body(b200_amg *a, const double *f, double *u, int zero_gues
       else        { relax_type = a->relax_type[0];           num_sweep = a->num_sweeps[0]; }
       // level 0 is visited twice (lev_counter 1 -> 0 -> -1): its last sweep of the second visit ends the cycle
       const bool final_visit = level == 0 && (nl == 1 || lev_counter[0] == 0);
+      // hypre_BoomerAMGRelaxIF: relax_order 1 splits a sweep into two calls (C, F down; F, C up)
+      const bool cf_order = a->relax_order == 1 && cycle_param < 3 && nl > 1 && relax_type != 16 && relax_type != 9;
       for (int j = 0; j < num_sweep; j++)
       {
-         B200_TRY(relax_once(a, s, level, relax_type, F[level], final_visit && j == num_sweep - 1 ? fd : nullptr));
+         for (int pass = 0; pass < (cf_order ? 2 : 1); pass++)
+         {
+            const int points = !cf_order ? 0 : (((cycle_param < 2) == (pass == 0)) ? 1 : -1);
+            const bool last_call = final_visit && j == num_sweep - 1 && pass == (cf_order ? 1 : 0);
+            B200_TRY(relax_once(a, s, level, relax_type, F[level], last_call ? fd : nullptr, points));
+         }
       }
 
       --lev_counter[level];
@@ -599,11 +637,13 @@ static int cycle_bytes(const b200_amg *a, bool stored, double *bytes)
          const double passPT = (L.P->hasT ? dmat_pass_bytes(L.P->diagT, stored)
                                           : 12.0 * (double)L.P->diag.nnz + 4.0 * nc) + 12.0 * (double)L.P->offd.nnz;
          // V-cycle: pre sweeps (first one with zero guess), residual, restriction, prolongation, post sweeps
-         for (int j = 0; j < a->num_sweeps[1]; j++) { tot += sweep_bytes(a->relax_type[1], j == 0); }
+         const int calls = (a->relax_order == 1 && a->relax_type[1] != 16) ? 2 : 1;
+         const int calls2 = (a->relax_order == 1 && a->relax_type[2] != 16) ? 2 : 1;
+         for (int j = 0; j < a->num_sweeps[1] * calls; j++) { tot += sweep_bytes(a->relax_type[1], j == 0); }
          tot += spmv + 24.0 * n;                          // residual: u,f in; r out
          tot += passPT + 8.0 * n + 8.0 * nc;                    // restriction
          tot += passP + 8.0 * nc + 16.0 * n;                    // prolongation
-         for (int j = 0; j < a->num_sweeps[2]; j++) { tot += sweep_bytes(a->relax_type[2], false); }
+         for (int j = 0; j < a->num_sweeps[2] * calls2; j++) { tot += sweep_bytes(a->relax_type[2], false); }
       }
       else if (a->relax_type[3] == 9) { tot += 8.0 * (double)a->coarse_n * a->coarse_n; }
       else { for (int j = 0; j < a->num_sweeps[3]; j++) { tot += sweep_bytes(a->relax_type[3], j == 0); } }

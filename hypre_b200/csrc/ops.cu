@@ -70,9 +70,12 @@ struct EpiJacobiT {
    static constexpr int NRED = DOT ? 1 : 0;
    EPI_PLAIN_X
    double w; const double *f; const double *l1; const double *u_in; double *u_out; const double *dw;
+   const int *marker; int points;     // CF-ordered sweep (relax_order 1): only rows with marker == points move
    __device__ void operator()(int r, double t, double *red) const
    {
-      const double un = ADD(u_in[r], __ddiv_rn(MUL(w, SUB(f[r], t)), l1[r]));
+      // hypre_ParVectorElmdivpyMarked (seq_mv/vector.c:823-870): u_i += Vtemp_i / l1_i where marker_i == points
+      const bool on = marker == nullptr || marker[r] == points;
+      const double un = on ? ADD(u_in[r], __ddiv_rn(MUL(w, SUB(f[r], t)), l1[r])) : u_in[r];
       u_out[r] = un;
       if (DOT) { red[0] = fma(dw[r], un, red[0]); }
    }
@@ -169,7 +172,11 @@ struct EpiGsInnerT {
 struct FScaleCopy { static constexpr int NRED = 0; __device__ void init() {} double beta; const double *b; double *y;
    __device__ void operator()(int i, double *) const { y[i] = MUL(beta, b[i]); } };
 struct FZero { static constexpr int NRED = 0; __device__ void init() {} double w; const double *f; const double *l1; double *u;
-   __device__ void operator()(int i, double *) const { u[i] = __ddiv_rn(MUL(w, f[i]), l1[i]); } };
+   const int *marker; int points;
+   __device__ void operator()(int i, double *) const
+   {
+      u[i] = (marker == nullptr || marker[i] == points) ? __ddiv_rn(MUL(w, f[i]), l1[i]) : 0.0;     // the others keep their zero
+   } };
 struct FChebyFirst0 { static constexpr int NRED = 0; __device__ void init() {} int scale; double c; const double *f; const double *ds;
    double *rv; double *tmp;
    __device__ void operator()(int i, double *) const
@@ -518,21 +525,22 @@ int op_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, doubl
 }
 
 int op_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
-                const double *u_in, double *u_out, int zero_guess, const FusedDot *fd)
+                const double *u_in, double *u_out, int zero_guess, const FusedDot *fd, const int *marker, int points)
 {
+   if (points == 0) { marker = nullptr; }
    if (zero_guess)
    {
       // Vtemp = w*f ; u = 0 + Vtemp./l1 (par_relax.c:1221-1228,1238-1246)
-      FZero fz{w, f, l1, u_out};
+      FZero fz{w, f, l1, u_out, marker, points};
       return run_ewise(A->ctx, A->n_rows, fz, nullptr);
    }
    if (fd && fd->with)
    {
-      EpiJacobiT<true> e{w, f, l1, u_in, u_out, fd->with};
+      EpiJacobiT<true> e{w, f, l1, u_in, u_out, fd->with, marker, points};
       *fd->done = true;
       return run_rows(A, A->diag, A->offd, true, u_in, e, fd->out);
    }
-   EpiJacobiT<false> e{w, f, l1, u_in, u_out, nullptr};
+   EpiJacobiT<false> e{w, f, l1, u_in, u_out, nullptr, marker, points};
    return run_rows(A, A->diag, A->offd, true, u_in, e, nullptr);
 }
 
@@ -691,8 +699,8 @@ extern "C" int b200_relax_l1jacobi(b200_parcsr *A, const double *f, const double
                                    double *u, double *tmp, int zero_guess)
 {
    ARG_CHECK(A != nullptr && f != nullptr && l1 != nullptr && u != nullptr && tmp != nullptr);
-   if (zero_guess) { return op_l1jacobi(A, f, l1, w, u, u, 1, nullptr); }
-   B200_TRY(op_l1jacobi(A, f, l1, w, u, tmp, 0, nullptr));
+   if (zero_guess) { return op_l1jacobi(A, f, l1, w, u, u, 1, nullptr, nullptr, 0); }
+   B200_TRY(op_l1jacobi(A, f, l1, w, u, tmp, 0, nullptr, nullptr, 0));
    return b200_vec_copy(A->ctx, A->n_rows, tmp, u);
 }
 

@@ -24,7 +24,8 @@ int op_matvec_dot_direction(b200_parcsr *A, const double *d_beta, const int *d_i
 int op_matvecT(b200_parcsr *A, double alpha, const double *x, double beta, double *y);
 // u_out = u_in + w*(f - A u_in)./l1          (zero_guess: u_out = w*f./l1, u_in unused)
 int op_l1jacobi(b200_parcsr *A, const double *f, const double *l1, double w,
-                const double *u_in, double *u_out, int zero_guess, const FusedDot *fd = nullptr);
+                const double *u_in, double *u_out, int zero_guess, const FusedDot *fd = nullptr,
+                const int *marker = nullptr, int points = 0);   // marker / points: CF-ordered sweep, rows with marker != points keep u
 // Chebyshev, in place on u; v, r, tmp are work vectors
 int op_cheby(b200_parcsr *A, const double *f, const double *ds, const double *coefs_h, int order,
              int scale, double *u, double *v, double *r, double *tmp, int zero_guess, const FusedDot *fd = nullptr);

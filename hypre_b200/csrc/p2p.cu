@@ -78,11 +78,9 @@ int p2p_bootstrap(b200_ctx *c)
       fprintf(stderr, "b200: peer-memory halo path unavailable, using NCCL send/recv\n");
       return B200_OK;
    }
-   // all-reduce slots: vals[2][nranks][AR_MAX] doubles, flag[nranks] u64, then a local seq word
-   B200_TRY(arena_alloc(c, sizeof(double) * 2 * (size_t)c->nranks * AR_MAX, &c->ar_vals_off));
-   B200_TRY(arena_alloc(c, sizeof(u64) * (size_t)c->nranks, &c->ar_flag_off));
-   B200_TRY(arena_alloc(c, sizeof(double) * 2 * (size_t)c->nranks * AR_BIG_MAX, &c->arb_vals_off));
-   B200_TRY(arena_alloc(c, sizeof(u64) * (size_t)c->nranks, &c->arb_flag_off));
+   // all-reduce slots: vals[2][nranks][AR_MAX] values with their sequence numbers (LLVal)
+   B200_TRY(arena_alloc(c, sizeof(LLVal) * 2 * (size_t)c->nranks * AR_MAX, &c->ar_vals_off));
+   B200_TRY(arena_alloc(c, sizeof(LLVal) * 2 * (size_t)c->nranks * AR_BIG_MAX, &c->arb_vals_off));
    CUDA_TRY(cudaMalloc((void **)&c->d_ar_seq, 4 * sizeof(u64)));     // [0] small seq, [1] big seq, [2..3] big tickets
    CUDA_TRY(cudaMemset(c->d_ar_seq, 0, 4 * sizeof(u64)));
    B200_TRY(dev_upload(&c->d_peer_arena, c->peer_arena.data(), c->peer_arena.size()));
@@ -108,9 +106,9 @@ struct b200_p2p_chan {
    b200_ctx *ctx = nullptr;
    P2PChan   v;
    int      *d_out_starts = nullptr;
-   double  **d_out_dst[2] = {nullptr, nullptr};
-   u64     **d_out_flag = nullptr;
+   LLVal   **d_out_dst[2] = {nullptr, nullptr};
    u64     **d_in_ack = nullptr;
+   int      *d_out_wait_ack = nullptr, *d_in_send_ack = nullptr;
    u64      *d_seq = nullptr;       // [2] seq_put, seq_wait
    unsigned *d_ticket = nullptr;    // [2]
 };
@@ -121,7 +119,7 @@ void p2p_chan_destroy(b200_p2p_chan *ch)
 {
    if (!ch) { return; }
    cudaFree(ch->d_out_starts); cudaFree(ch->d_out_dst[0]); cudaFree(ch->d_out_dst[1]);
-   cudaFree(ch->d_out_flag); cudaFree(ch->d_in_ack); cudaFree(ch->d_seq); cudaFree(ch->d_ticket);
+   cudaFree(ch->d_out_wait_ack); cudaFree(ch->d_in_send_ack); cudaFree(ch->d_in_ack); cudaFree(ch->d_seq); cudaFree(ch->d_ticket);
    delete ch;
 }
 
@@ -152,21 +150,20 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
    b200_p2p_chan *ch = new b200_p2p_chan();
    ch->ctx = c;
    const int in_total = n_in > 0 ? in_starts[n_in] : 0;
-   size_t off_buf[2] = {0, 0}, off_flag = 0, off_ack = 0;
+   size_t off_buf[2] = {0, 0}, off_ack = 0;
    int s = B200_OK;
-   for (int p = 0; p < 2 && s == B200_OK; p++) { s = arena_alloc(c, sizeof(double) * (size_t)(in_total + 1), &off_buf[p]); }
-   if (s == B200_OK) { s = arena_alloc(c, sizeof(u64) * (size_t)(n_in + 1), &off_flag); }
+   for (int p = 0; p < 2 && s == B200_OK; p++) { s = arena_alloc(c, sizeof(LLVal) * (size_t)(in_total + 1), &off_buf[p]); }
    if (s == B200_OK) { s = arena_alloc(c, sizeof(u64) * (size_t)(n_out + 1), &off_ack); }
    if (s != B200_OK) { delete ch; return s; }
 
-   // tell every sender where its segment lands in my arena (3 words), and every receiver
+   // tell every sender where its segment lands in my arena (2 words + 1 spare), and every receiver
    // where its acknowledgement lands (1 word)
    std::vector<long long> to_in((size_t)n_in * 3 + 1), from_out((size_t)n_out * 3 + 1);
    for (int j = 0; j < n_in; j++)
    {
-      to_in[(size_t)j * 3 + 0] = (long long)(off_buf[0] + sizeof(double) * (size_t)in_starts[j]);
-      to_in[(size_t)j * 3 + 1] = (long long)(off_buf[1] + sizeof(double) * (size_t)in_starts[j]);
-      to_in[(size_t)j * 3 + 2] = (long long)(off_flag + sizeof(u64) * (size_t)j);
+      to_in[(size_t)j * 3 + 0] = (long long)(off_buf[0] + sizeof(LLVal) * (size_t)in_starts[j]);
+      to_in[(size_t)j * 3 + 1] = (long long)(off_buf[1] + sizeof(LLVal) * (size_t)in_starts[j]);
+      to_in[(size_t)j * 3 + 2] = 0;
    }
    s = exchange_words(c, 3, n_in, in_procs, to_in.data(), n_out, out_procs, from_out.data());
    std::vector<long long> to_out((size_t)n_out + 1), from_in((size_t)n_in + 1);
@@ -174,21 +171,30 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
    if (s == B200_OK) { s = exchange_words(c, 1, n_out, out_procs, to_out.data(), n_in, in_procs, from_in.data()); }
    if (s != B200_OK) { delete ch; return s; }
 
-   std::vector<double *> dst0((size_t)n_out + 1), dst1((size_t)n_out + 1);
-   std::vector<u64 *> oflag((size_t)n_out + 1), iack((size_t)n_in + 1);
+   std::vector<LLVal *> dst0((size_t)n_out + 1), dst1((size_t)n_out + 1);
+   std::vector<u64 *> iack((size_t)n_in + 1);
+   // per pair: a receiver I do not receive from must acknowledge (see p2p.cuh, flow control)
+   std::vector<int> wait_ack((size_t)n_out + 1, 0), send_ack((size_t)n_in + 1, 0);
+   int n_ack_in = 0;
    for (int i = 0; i < n_out; i++)
    {
       char *base = c->peer_arena[(size_t)out_procs[i]];
-      dst0[(size_t)i]  = (double *)(base + from_out[(size_t)i * 3 + 0]);
-      dst1[(size_t)i]  = (double *)(base + from_out[(size_t)i * 3 + 1]);
-      oflag[(size_t)i] = (u64 *)(base + from_out[(size_t)i * 3 + 2]);
+      dst0[(size_t)i]  = (LLVal *)(base + from_out[(size_t)i * 3 + 0]);
+      dst1[(size_t)i]  = (LLVal *)(base + from_out[(size_t)i * 3 + 1]);
+      wait_ack[(size_t)i] = std::find(in_procs, in_procs + n_in, out_procs[i]) == in_procs + n_in ? 1 : 0;
+   }
+   for (int j = 0; j < n_in; j++)
+   {
+      send_ack[(size_t)j] = std::find(out_procs, out_procs + n_out, in_procs[j]) == out_procs + n_out ? 1 : 0;
+      n_ack_in += send_ack[(size_t)j];
    }
    for (int j = 0; j < n_in; j++) { iack[(size_t)j] = (u64 *)(c->peer_arena[(size_t)in_procs[j]] + from_in[(size_t)j]); }
    std::vector<int> zero_starts(1, 0);
    s = dev_upload(&ch->d_out_starts, n_out > 0 ? out_starts : zero_starts.data(), (size_t)n_out + 1);
    if (s == B200_OK) { s = dev_upload(&ch->d_out_dst[0], dst0.data(), dst0.size()); }
    if (s == B200_OK) { s = dev_upload(&ch->d_out_dst[1], dst1.data(), dst1.size()); }
-   if (s == B200_OK) { s = dev_upload(&ch->d_out_flag, oflag.data(), oflag.size()); }
+   if (s == B200_OK) { s = dev_upload(&ch->d_out_wait_ack, wait_ack.data(), wait_ack.size()); }
+   if (s == B200_OK) { s = dev_upload(&ch->d_in_send_ack, send_ack.data(), send_ack.size()); }
    if (s == B200_OK) { s = dev_upload(&ch->d_in_ack, iack.data(), iack.size()); }
    if (s == B200_OK && cudaMalloc((void **)&ch->d_seq, 2 * sizeof(u64)) != cudaSuccess) { s = B200_ERR_CUDA; }
    if (s == B200_OK && cudaMalloc((void **)&ch->d_ticket, 2 * sizeof(unsigned)) != cudaSuccess) { s = B200_ERR_CUDA; }
@@ -201,11 +207,12 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
    v.n_out_total = n_out > 0 ? out_starts[n_out] : 0;
    v.out_starts = ch->d_out_starts;
    v.out_dst[0] = ch->d_out_dst[0]; v.out_dst[1] = ch->d_out_dst[1];
-   v.out_flag = ch->d_out_flag;
    v.out_ack = (u64 *)(c->arena + off_ack);
-   v.in_buf[0] = (double *)(c->arena + off_buf[0]); v.in_buf[1] = (double *)(c->arena + off_buf[1]);
-   v.in_flag = (u64 *)(c->arena + off_flag);
+   v.out_wait_ack = ch->d_out_wait_ack;
+   v.in_buf[0] = (LLVal *)(c->arena + off_buf[0]); v.in_buf[1] = (LLVal *)(c->arena + off_buf[1]);
    v.in_ack = ch->d_in_ack;
+   v.in_send_ack = ch->d_in_send_ack;
+   v.n_ack_in = n_ack_in;
    v.seq_put = ch->d_seq; v.seq_wait = ch->d_seq + 1;
    v.ticket = ch->d_ticket;
    v.err = c->d_err;
@@ -214,31 +221,32 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
 }
 
 // ---------------------------------------------------------------- all-reduce
-// Every rank stores its contribution into slot [parity][rank] of every peer's arena, publishes
-// the sequence number, waits for all peers and sums the slots in rank order: deterministic and
-// bit-identical on all ranks.  One launch, no library call.
-__global__ void __launch_bounds__(256) p2p_allreduce_kernel(char *const *__restrict__ peer, size_t vals_off, size_t flag_off,
+// Every rank stores its contribution into slot [parity][rank] of every peer's arena -- each value with the sequence
+// number of this reduction (flag-in-data, p2p.cuh) -- and sums the slots of its own arena in rank order as they
+// arrive: deterministic and bit-identical on all ranks, one launch, no fence, no library call.  Double buffered by
+// the parity of the sequence number; a rank can start reduction s + 2 only after it finished s + 1, for which every
+// peer had to have finished reading s.
+__global__ void __launch_bounds__(256) p2p_allreduce_kernel(char *const *__restrict__ peer, size_t vals_off,
                                                             int rank, int nranks, u64 *seq_p, double *d, int cnt, int *err,
                                                             const int *stop)
 {
    if (*stop != 0) { return; }      // identical on all ranks (derived from all-reduced scalars)
    const u64 seq = ld_relaxed_gpu(seq_p) + 1;
+   const unsigned flag = (unsigned)seq;
    const int par = (int)(seq & 1);
-   for (int t = 0; t < nranks; t++)
+   for (int k = threadIdx.x; k < cnt; k += blockDim.x)
    {
-      double *slot = (double *)(peer[t] + vals_off) + ((size_t)par * nranks + rank) * AR_MAX;
-      for (int k = threadIdx.x; k < cnt; k += blockDim.x) { slot[k] = d[k]; }
+      const double v = d[k];
+      for (int t = 0; t < nranks; t++)
+      {
+         ll_store((LLVal *)(peer[t] + vals_off) + ((size_t)par * nranks + rank) * AR_MAX + k, v, flag);
+      }
    }
-   __threadfence_system();
-   __syncthreads();
-   if (threadIdx.x < nranks) { st_release_sys((u64 *)(peer[threadIdx.x] + flag_off) + rank, seq); }
-   if (threadIdx.x < nranks) { p2p_spin_ge((const u64 *)(peer[rank] + flag_off) + threadIdx.x, seq, err); }
-   __syncthreads();
-   const double *mine = (const double *)(peer[rank] + vals_off) + (size_t)par * nranks * AR_MAX;
+   const LLVal *mine = (const LLVal *)(peer[rank] + vals_off) + (size_t)par * nranks * AR_MAX;
    for (int k = threadIdx.x; k < cnt; k += blockDim.x)
    {
       double s = 0.0;
-      for (int t = 0; t < nranks; t++) { s += __ldcg(mine + (size_t)t * AR_MAX + k); }
+      for (int t = 0; t < nranks; t++) { s += ll_read(mine + (size_t)t * AR_MAX + k, flag, err); }
       d[k] = s;
    }
    __syncthreads();
@@ -248,50 +256,43 @@ __global__ void __launch_bounds__(256) p2p_allreduce_kernel(char *const *__restr
 int p2p_allreduce(b200_ctx *c, double *d, int cnt)
 {
    if (cnt > AR_MAX) { b200_set_error("p2p_allreduce: %d > %d values", cnt, AR_MAX); return B200_ERR_ARG; }
-   LAUNCH(c, p2p_allreduce_kernel, 1, 256, 0, c->d_peer_arena, c->ar_vals_off, c->ar_flag_off, c->rank, c->nranks,
+   LAUNCH(c, p2p_allreduce_kernel, 1, 256, 0, c->d_peer_arena, c->ar_vals_off, c->rank, c->nranks,
           c->d_ar_seq, d, cnt, c->d_err, c->d_stop);
    CHECK_LAUNCH();
    return B200_OK;
 }
 
 // Vector all-reduce (n <= AR_BIG_MAX): same protocol with several blocks.  Block b owns the elements
-// k = b*256 + tid (grid stride) in both phases; the last block to finish its stores publishes the
-// sequence number, every block then waits for all ranks and sums its elements in rank order.
-__global__ void __launch_bounds__(256) p2p_allreduce_big_kernel(char *const *__restrict__ peer, size_t vals_off, size_t flag_off,
+// k = b*256 + tid (grid stride) in both phases; the last block to finish advances the sequence counter.
+__global__ void __launch_bounds__(256) p2p_allreduce_big_kernel(char *const *__restrict__ peer, size_t vals_off,
                                                                 int rank, int nranks, u64 *seq_p, unsigned *tickets,
                                                                 double *d, int n, int *err, const int *stop)
 {
    if (*stop != 0) { return; }
-   __shared__ bool s_last;
    const u64 seq = ld_relaxed_gpu(seq_p) + 1;
+   const unsigned flag = (unsigned)seq;
    const int par = (int)(seq & 1);
-   for (int t = 0; t < nranks; t++)
+   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
    {
-      double *slot = (double *)(peer[t] + vals_off) + ((size_t)par * nranks + rank) * AR_BIG_MAX;
-      for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) { slot[k] = d[k]; }
+      const double v = d[k];
+      for (int t = 0; t < nranks; t++)
+      {
+         ll_store((LLVal *)(peer[t] + vals_off) + ((size_t)par * nranks + rank) * AR_BIG_MAX + k, v, flag);
+      }
    }
-   __syncthreads();
-   if (threadIdx.x == 0)
-   {
-      __threadfence_system();
-      s_last = (atomicAdd(tickets, 1u) == gridDim.x - 1);
-   }
-   __syncthreads();
-   if (s_last && threadIdx.x < nranks) { st_release_sys((u64 *)(peer[threadIdx.x] + flag_off) + rank, seq); }
-   if (threadIdx.x < nranks) { p2p_spin_ge((const u64 *)(peer[rank] + flag_off) + threadIdx.x, seq, err); }
-   __syncthreads();
-   const double *mine = (const double *)(peer[rank] + vals_off) + (size_t)par * nranks * AR_BIG_MAX;
+   const LLVal *mine = (const LLVal *)(peer[rank] + vals_off) + (size_t)par * nranks * AR_BIG_MAX;
    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
    {
       double s = 0.0;
-      for (int t = 0; t < nranks; t++) { s += __ldcg(mine + (size_t)t * AR_BIG_MAX + k); }
+      for (int t = 0; t < nranks; t++) { s += ll_read(mine + (size_t)t * AR_BIG_MAX + k, flag, err); }
       d[k] = s;
    }
    __syncthreads();
    if (threadIdx.x == 0)
    {
-      // second ticket: the last block to finish advances the sequence and re-arms the tickets
-      if (atomicAdd(tickets + 1, 1u) == gridDim.x - 1) { *seq_p = seq; tickets[0] = 0u; tickets[1] = 0u; __threadfence(); }
+      // every block read the counter before it took its ticket: the last one advances it
+      __threadfence();
+      if (atomicAdd(tickets + 1, 1u) == gridDim.x - 1) { *seq_p = seq; tickets[1] = 0u; __threadfence(); }
    }
 }
 
@@ -303,7 +304,7 @@ int p2p_allreduce_vec(b200_ctx *c, double *d, int n)
    if (n <= 0) { return B200_OK; }
    int grid = (n + 255) / 256;
    if (grid > AR_BIG_GRID) { grid = AR_BIG_GRID; }
-   LAUNCH(c, p2p_allreduce_big_kernel, grid, 256, 0, c->d_peer_arena, c->arb_vals_off, c->arb_flag_off, c->rank, c->nranks,
+   LAUNCH(c, p2p_allreduce_big_kernel, grid, 256, 0, c->d_peer_arena, c->arb_vals_off, c->rank, c->nranks,
           c->d_ar_seq + 1, (unsigned *)(c->d_ar_seq + 2), d, n, c->d_err, c->d_stop);
    CHECK_LAUNCH();
    return B200_OK;

@@ -372,7 +372,8 @@ struct HaloArgs {
    int         chunked;  // thread-per-row layouts: contiguous run of slices per block instead of a grid stride
 };
 
-// sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks)
+// sender part of HALO_FWD / HALO_REV, executed by blocks [0, n_put_blocks): values go straight into the receivers'
+// buffers, each with the sequence number of this exchange (p2p.cuh: flag-in-data) -- no fence, no flag
 template <int HALO, class XF>
 __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *__restrict__ x, int n_put_blocks,
                                                const XF &xf)
@@ -383,13 +384,17 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
    if (threadIdx.x == 0)
    {
       const u64 seq = ld_relaxed_gpu(ch.seq_put) + 1;
-      // flow control: buffer (seq & 1) was used by exchange seq-2; wait until it was consumed
-      if (seq > 2 && !(h.dbg & 4)) { for (int i = 0; i < ch.n_out; i++) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
+      // flow control: buffer (seq & 1) was used by exchange seq-2; receivers that do not send to me acknowledge
+      if (seq > 2 && !(h.dbg & 4))
+      {
+         for (int i = 0; i < ch.n_out; i++) { if (ch.out_wait_ack[i]) { p2p_spin_ge(ch.out_ack + i, seq - 2, ch.err); } }
+      }
       s_seq = seq;
    }
    __syncthreads();
    const u64 seq = s_seq;
-   double *const *dst = ch.out_dst[(int)(seq & 1)];
+   const unsigned flag = (unsigned)seq;
+   LLVal *const *dst = ch.out_dst[(int)(seq & 1)];
    int seg = 0;
    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ch.n_out_total; i += n_put_blocks * blockDim.x)
    {
@@ -402,45 +407,43 @@ __device__ __forceinline__ void halo_put_phase(const HaloArgs &h, const double *
          v = 0.0;
          for (int k = h.O.rp[i]; k < h.O.rp[i + 1]; k++) { v = fma(h.O.va[k], x[h.O.ci[k]], v); }
       }
-      dst[seg][i - ch.out_starts[seg]] = v;
+      ll_store(dst[seg] + (i - ch.out_starts[seg]), v, flag);
    }
-   // publish: the block barrier orders the block's stores before thread 0; with one put block its
-   // release store (fence.sys + store, cumulative) is the only system-scope fence on the critical path,
-   // with several blocks each block's thread 0 fences once before taking its ticket
+   // the last put block advances the local sequence counter (every put block has read it by then)
    __syncthreads();
    if (n_put_blocks == 1) { s_last_p = true; }
    else
    {
-      if (threadIdx.x == 0)
-      {
-         if (!(h.dbg & 8)) { __threadfence_system(); }
-         s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u);
-      }
+      if (threadIdx.x == 0) { s_last_p = (atomicAdd(ch.ticket, 1u) == (unsigned)n_put_blocks - 1u); }
       __syncthreads();
    }
-   if (s_last_p)
-   {
-      for (int i = threadIdx.x; i < ch.n_out; i += blockDim.x)
-      {
-         if (h.dbg & 8) { st_relaxed_sys(ch.out_flag[i], seq); } else { st_release_sys(ch.out_flag[i], seq); }
-      }
-      if (threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; }
-   }
+   if (s_last_p && threadIdx.x == 0) { *ch.seq_put = seq; ch.ticket[0] = 0u; }
 }
 
-// receiver part: called by a converged warp when one of its rows needs remote data; waits once per warp
-__device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const double *cur, int dbg)
+// receiver part: called by a converged warp when one of its rows needs remote data; fixes the buffer and the
+// sequence number this exchange's values carry (once per warp).  The waiting itself is per element (ll_read).
+__device__ __forceinline__ const LLVal *halo_warp_wait(const P2PChan &ch, const LLVal *cur, unsigned &flag)
 {
    if (cur != nullptr) { return cur; }
-   int par = 0;
-   if ((threadIdx.x & 31) == 0)
-   {
-      const u64 seq = ld_relaxed_gpu(ch.seq_wait) + 1;
-      if (!(dbg & 2)) { for (int j = 0; j < ch.n_in; j++) { p2p_spin_ge(ch.in_flag + j, seq, ch.err); } }
-      par = (int)(seq & 1);
-   }
-   par = __shfl_sync(0xffffffffu, par, 0);
-   return ch.in_buf[par];
+   unsigned f = 0;
+   if ((threadIdx.x & 31) == 0) { f = (unsigned)(ld_relaxed_gpu(ch.seq_wait) + 1); }
+   f = __shfl_sync(0xffffffffu, f, 0);
+   flag = f;
+   return ch.in_buf[(int)(f & 1u)];
+}
+
+// CSR rows of the offd block over the receive buffer (T lanes per row, all lanes of the warp take part)
+template <int T>
+__device__ __forceinline__ double rowsum_csr_ll(const int *__restrict__ rp, const int *__restrict__ ci,
+                                                const double *__restrict__ va, int row, int sub,
+                                                const LLVal *xg, unsigned flag, int *err)
+{
+   const int beg = rp[row], end = rp[row + 1];
+   double t = 0.0;
+   for (int k = beg + sub; k < end; k += T) { t = fma(ld_stream(va + k), ll_read(xg + ld_stream(ci + k), flag, err), t); }
+#pragma unroll
+   for (int o = T >> 1; o > 0; o >>= 1) { t += __shfl_down_sync(0xffffffffu, t, o, T); }
+   return t;
 }
 
 // Row groups [g_begin, g_end) (a group = 32 consecutive rows = one slice of the sliced-ELL layouts) of the
@@ -453,8 +456,8 @@ __device__ __forceinline__ const double *halo_warp_wait(const P2PChan &ch, const
 // SM's L1 instead of each costing an L2 read; 0 = grid stride.
 template <int T, int HALO, class Epi>
 __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, const double *__restrict__ x,
-                                           const Epi &epi, double *red, int g_begin, int g_end, const double *&xg,
-                                           int vblock, const double2 *s_tab = nullptr)
+                                           const Epi &epi, double *red, int g_begin, int g_end, const LLVal *&xg,
+                                           unsigned &xflag, int vblock, const double2 *s_tab = nullptr)
 {
    // vblock: the block's position in this range's grid (a permutation of blockIdx.x), so that
    // short ranges do not all land on the low-numbered blocks, which also carry the put phase
@@ -509,15 +512,15 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          if (HALO == HALO_FWD && h.grp[slice])
          {
             const int ob = live ? h.O.rp[row] : 0, oe = live ? h.O.rp[row + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg, h.dbg);
-            for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], __ldcg(xg + h.O.ci[k]), t); }
+            xg = halo_warp_wait(h.ch, xg, xflag);
+            for (int k = ob; k < oe; k++) { t = fma(h.O.va[k], ll_read(xg + h.O.ci[k], xflag, h.ch.err), t); }
          }
          if (HALO == HALO_REV && h.grp[slice])
          {
             const int ub = live ? h.urp[row] : 0, ue = live ? h.urp[row + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg, h.dbg);
+            xg = halo_warp_wait(h.ch, xg, xflag);
             double e = 0.0;
-            for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+            for (int k = ub; k < ue; k++) { e += ll_read(xg + h.upos[k], xflag, h.ch.err); }
             t += e;
          }
          if (live && !skip) { epi(row, t, red); }
@@ -540,18 +543,18 @@ __device__ __forceinline__ void rows_range(const MatView &D, const HaloArgs &h, 
          if (HALO == HALO_SKIP) { skip = h.O.rp[r + 1] != h.O.rp[r]; }
          if (HALO == HALO_FWD && h.grp[row >> 5])
          {
-            xg = halo_warp_wait(h.ch, xg, h.dbg);
+            xg = halo_warp_wait(h.ch, xg, xflag);
             // all lanes take part (rows without offd entries have an empty range)
-            t += rowsum_csr<TT, true>(h.O.rp, h.O.ci, h.O.va, r, sub, xg, epi);
+            t += rowsum_csr_ll<TT>(h.O.rp, h.O.ci, h.O.va, r, sub, xg, xflag, h.ch.err);
          }
          if (HALO == HALO_REV && h.grp[row >> 5])
          {
             const int ub = live ? h.urp[r] : 0, ue = live ? h.urp[r + 1] : 0;
-            xg = halo_warp_wait(h.ch, xg, h.dbg);
+            xg = halo_warp_wait(h.ch, xg, xflag);
             if (sub == 0)
             {
                double e = 0.0;
-               for (int k = ub; k < ue; k++) { e += __ldcg(xg + h.upos[k]); }
+               for (int k = ub; k < ue; k++) { e += ll_read(xg + h.upos[k], xflag, h.ch.err); }
                t += e;
             }
          }
@@ -597,8 +600,9 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi_arg, Re
       __syncthreads();
    }
    const int n_groups = (D.n_rows + 31) >> 5;
-   const double *xg = nullptr;    // ghost vector / receive buffer once this warp has waited for it
-   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, blockIdx.x, s_tab); }
+   const LLVal *xg = nullptr;     // receive buffer of this exchange once this warp has looked it up
+   unsigned xflag = 0;            // sequence number its values carry
+   if (!P2P) { rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, n_groups, xg, xflag, blockIdx.x, s_tab); }
    else
    {
       if (h.ch.n_out > 0)
@@ -613,9 +617,9 @@ rows_kernel(MatView D, HaloArgs h, const double *__restrict__ x, Epi epi_arg, Re
       // interior groups [int_begin, int_end) first, with exactly the single-rank code; the groups that
       // need remote data (both ends of a 1-D block partition) last, when the halo has long arrived
       const int G = gridDim.x, b = blockIdx.x;
-      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, b, s_tab);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, G - 1 - b, s_tab);
-      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, (b + G / 2) % G, s_tab);
+      rows_range<T, HALO_NONE, Epi>(D, h, x, epi, red, h.int_begin, h.int_end, xg, xflag, b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, 0, h.int_begin, xg, xflag, G - 1 - b, s_tab);
+      rows_range<T, HALO, Epi>(D, h, x, epi, red, h.int_end, n_groups, xg, xflag, (b + G / 2) % G, s_tab);
    }
    grid_reduce<Epi::NRED>(red, rc);
    if (P2P && h.ch.n_in > 0 && !(h.dbg & 4)) { p2p_consumer_done(h.ch); }

@@ -73,6 +73,12 @@ double *hb_amg_cheby_coefs(void *amg, int l)
    HYPRE_Real **c = hypre_ParAMGDataChebyCoefs((hypre_ParAMGData *) amg);
    return (c && c[l]) ? c[l] : NULL;
 }
+/* CF_marker_array[l] of the setup (1 = C point, -1 = F point; NULL on the coarsest level) */
+int *hb_amg_cf_marker(void *amg, int l)
+{
+   hypre_IntArray **m = hypre_ParAMGDataCFMarkerArray((hypre_ParAMGData *) amg);
+   return (m && l < hypre_ParAMGDataNumLevels((hypre_ParAMGData *) amg) - 1 && m[l]) ? hypre_IntArrayData(m[l]) : NULL;
+}
 double hb_amg_relax_weight(void *amg, int l) { return hypre_ParAMGDataRelaxWeight((hypre_ParAMGData *) amg)[l]; }
 double hb_amg_omega(void *amg, int l) { return hypre_ParAMGDataOmega((hypre_ParAMGData *) amg)[l]; }
 /* out[0..3] grid_relax_type, out[4..7] num_grid_sweeps, out[8] cycle_type, out[9] fcycle,

@@ -473,12 +473,13 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    if (hypre_ParAMGDataBlockMode(amg_data) || hypre_ParAMGDataSmoothNumLevels(amg_data) > 0 ||
        hypre_ParAMGDataAdditive(amg_data) >= 0 || hypre_ParAMGDataMultAdditive(amg_data) >= 0 ||
        hypre_ParAMGDataSimple(amg_data) >= 0 || hypre_ParAMGDataRestriction(amg_data) ||
-       hypre_ParAMGDataRelaxOrder(amg_data) != 0 || hypre_ParAMGDataGridRelaxPoints(amg_data) != NULL ||
+       (hypre_ParAMGDataRelaxOrder(amg_data) != 0 && hypre_ParAMGDataRelaxOrder(amg_data) != 1) ||
+       hypre_ParAMGDataGridRelaxPoints(amg_data) != NULL ||
        hypre_ParAMGDataParticipate(amg_data) || hypre_ParAMGDataPartialCycleCoarsestLevel(amg_data) >= 0)
    {
       b200_ctx_sync(ctx);
       fprintf(stderr, "hypre_b200: BoomerAMG option outside the device path (block mode, complex "
-              "smoothers, additive cycles, AIR restriction, CF relaxation order, sequential coarse solve)\n");
+              "smoothers, additive cycles, AIR restriction, user-defined relax points, sequential coarse solve)\n");
       return NULL;
    }
    for (k = 0; k < 4; k++) { relax_type[k] = grt[k]; num_sweeps[k] = ngs[k]; }
@@ -623,6 +624,37 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    if (b200_amg_set_cycle(amg, relax_type, num_sweeps, hypre_ParAMGDataCycleType(amg_data),
                           hypre_ParAMGDataFCycle(amg_data)) != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
    if (repl < nl && b200_amg_set_replicated_from(amg, repl) != B200_OK) { b200_amg_destroy(amg); free(starts); return NULL; }
+   /* CF-ordered relaxation (HYPRE_BoomerAMGSetRelaxOrder(1), ij -CF 1): the CF markers of the setup, this rank's rows */
+   if (hypre_ParAMGDataRelaxOrder(amg_data) == 1 && nl > 1)
+   {
+      hypre_IntArray **cfm = hypre_ParAMGDataCFMarkerArray(amg_data);
+      int st = b200_amg_set_relax_order(amg, 1);
+      for (l = 0; l < nl - 1 && st == B200_OK; l++)
+      {
+         const int off = (starts && l < repl) ? STARTS(l)[g_rank] : 0;
+         if (!cfm || !cfm[l]) { st = B200_ERR_ARG; break; }
+         if (g_native && rows_of != NULL && l >= repl)
+         {
+#ifndef HYPRE_SEQUENTIAL
+            /* gathered level: every rank's markers, in rank order */
+            const int *ro = rows_of + (size_t) l * g_nranks;
+            int r, *dsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int)), *all;
+            for (r = 0; r < g_nranks; r++) { dsp[r + 1] = dsp[r] + ro[r]; }
+            all = (int *) calloc((size_t) (dsp[g_nranks] > 0 ? dsp[g_nranks] : 1), sizeof(int));
+            hypre_MPI_Allgatherv(hypre_IntArrayData(cfm[l]), ro[g_rank], HYPRE_MPI_INT, all, (HYPRE_Int *) ro, dsp, HYPRE_MPI_INT,
+                                 hypre_ParCSRMatrixComm(A_array[l]));
+            st = b200_amg_set_level_cf_marker(amg, l, all);
+            free(dsp); free(all);
+#endif
+         }
+         else { st = b200_amg_set_level_cf_marker(amg, l, hypre_IntArrayData(cfm[l]) + off); }
+      }
+      if (st != B200_OK)
+      {
+         fprintf(stderr, "hypre_b200: relax_order 1 without CF markers on every level\n");
+         b200_amg_destroy(amg); free(starts); free(rows_of); return NULL;
+      }
+   }
    for (k = 0; k < 4; k++) { if (relax_type[k] == 16) { uses_cheby = 1; } }
    for (l = 0; l < nl; l++)
    {
@@ -659,9 +691,11 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       }
       if (uses_cheby && coefs && coefs[l])
       {
-         const double *dsd = (ds && ds[l]) ? hypre_VectorData(ds[l]) + off : NULL;
+         /* unscaled Chebyshev (cheby_scale 0) has no scaling vector: the setup leaves ds[l] without data */
+         const double *dsd = (hypre_ParAMGDataChebyScale(amg_data) && ds && ds[l] && hypre_VectorData(ds[l]))
+                             ? hypre_VectorData(ds[l]) + off : NULL;
 #ifndef HYPRE_SEQUENTIAL
-         if (gathered && ds && ds[l])
+         if (gathered && dsd != NULL)
          {
             ds_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), dsd, rows_of + (size_t) l * g_nranks);
             dsd = ds_all;

@@ -73,6 +73,8 @@ def lib():
                  "hb_amg_coarse_dense", "hb_pcg_norms", "hb_pcg_rel_norms", "hb_gmres_norms", "hb_cogmres_norms", "hb_flexgmres_norms", "hb_lgmres_norms", "hb_bicgstab_norms"):
         getattr(L, name).restype = C.POINTER(d)
     L.hb_amg_relax_weight.restype = d
+    L.hb_amg_cf_marker.restype = C.POINTER(C.c_int)
+    L.hb_amg_cf_marker.argtypes = [vp, i]
     L.hb_amg_omega.restype = d
     L.hb_matrix_global_rows.restype = C.c_longlong
     L.GenerateLaplacian.argtypes = [i, i, i, i, i, i, i, i, i, i, vp]
@@ -367,6 +369,11 @@ class BoomerAMG(_Solver):
     def level_array(self, which, level, n):
         p = getattr(lib(), "hb_amg_" + which)(self.h, level)
         return np.ctypeslib.as_array(p, (n,)).copy() if p else None
+
+    def cf_marker(self, level, n):
+        """CF_marker_array[level] (1 = C point, -1 = F point), None on the coarsest level"""
+        p = lib().hb_amg_cf_marker(self.h, level)
+        return np.ctypeslib.as_array(p, (n,)).copy().astype(np.int32) if p else None
 
     def relax_weight(self, level):
         return lib().hb_amg_relax_weight(self.h, level)

@@ -243,6 +243,14 @@ int b200_amg_set_coarse_dense(b200_amg *amg, int n_global, const double *A_mat_h
  * without residual norms (src/parcsr_ls/par_amg_solve.c:257-336; ij -precon_cycles).  Default 1. */
 int b200_amg_set_precond_cycles(b200_amg *amg, int cycles);
 /* finalise: allocates F/U/work vectors, builds transposes and the launch plan */
+/* CF-ordered relaxation (hypre_BoomerAMGRelaxIF, src/parcsr_ls/par_relax_interface.c:20-64; hypre_ParAMGDataRelaxOrder,
+ * ij -CF 1): with relax_order 1 a sweep on a non-coarsest level is two calls of the smoother -- C points then F
+ * points on the way down, F then C on the way up (relax types 0 / 7 / 18 through hypre_ParVectorElmdivpyMarked,
+ * seq_mv/vector.c:823-870; two-stage Gauss-Seidel ignores the marker and runs twice; Chebyshev is not affected).
+ * cf_marker_h: CF_marker_array[level] of the setup (this rank's rows; 1 = C point), required on every
+ * non-coarsest level for the Jacobi types.  Both before b200_amg_finalize. */
+int b200_amg_set_relax_order(b200_amg *amg, int relax_order);
+int b200_amg_set_level_cf_marker(b200_amg *amg, int level, const int *cf_marker_h);
 int b200_amg_finalize(b200_amg *amg);
 /* one multigrid cycle u <- u + B(f - A u)   (dev pointers, level-0 size)
  * hypre_BoomerAMGCycle (src/parcsr_ls/par_cycle.c:22-803).  zero_guess as above. */

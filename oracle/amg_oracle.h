@@ -35,6 +35,8 @@ void orc_amg_set_level(orc_amg *h, int level, int n, const int *Ai, const int *A
                        const double *l1, const double *ds, const double *coefs, double relax_weight);
 void orc_amg_set_cycle(orc_amg *h, const int relax_type[4], const int num_sweeps[4], int cycle_type,
                        int fcycle, int cheby_order, int cheby_scale);
+void orc_amg_set_level_cf(orc_amg *h, int level, const int *cf_marker);   /* CF_marker_array[level], borrowed */
+void orc_amg_set_relax_order(orc_amg *h, int relax_order);                  /* hypre_ParAMGDataRelaxOrder */
 void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat);
 /* N-rank row partition of a level (nblocks+1 starts, copied): only two-stage GS depends on it */
 void orc_amg_set_level_blocks(orc_amg *h, int level, int nblocks, const int *starts);

@@ -14,6 +14,7 @@ typedef struct {
    double *F, *U;          /* owned for level > 0 */
    int all_zeros;          /* hypre_ParVectorAllZeros(U) */
    int nblocks; int *starts;   /* N-rank row partition (two-stage GS only); NULL = one rank */
+   const int *cf;          /* CF_marker_array[level] (borrowed), NULL on the coarsest level */
 } orc_level;
 
 struct orc_amg {
@@ -22,6 +23,7 @@ struct orc_amg {
    int relax_type[4], num_sweeps[4], cycle_type, fcycle, cheby_order, cheby_scale;
    int coarse_n;
    int precond_cycles;     /* hypre_ParAMGDataMaxIter of a preconditioner (ij -precon_cycles), default 1 */
+   int relax_order;        /* hypre_ParAMGDataRelaxOrder: 1 = C points then F points (down), F then C (up) */
    double *A_mat, *A_work, *b_vec;
    double *Vtemp, *Ztemp, *Ptemp, *Rtemp;
    int maxn;
@@ -108,14 +110,29 @@ void orc_amg_set_coarse_dense(orc_amg *h, int n, const double *A_mat)
    memcpy(h->A_mat, A_mat, sizeof(double) * (size_t) n * n);
 }
 
-/* one relaxation sweep on `level` (par_cycle.c:395-612 dispatch) */
-static int orc_relax(orc_amg *h, int level, int relax_type, const double *f, double *u)
+void orc_amg_set_level_cf(orc_amg *h, int level, const int *cf_marker) { h->L[level].cf = cf_marker; }
+void orc_amg_set_relax_order(orc_amg *h, int relax_order) { h->relax_order = relax_order; }
+
+/* one call of hypre_BoomerAMGRelax on `level` (par_relax.c:23-175; par_cycle.c:395-612 dispatch).
+ * points: 0 all rows, 1 / -1 only the rows whose CF marker has that value (relax types 0, 7, 18; the two-stage
+ * Gauss-Seidel sweeps ignore it, par_relax.c:1597-1607) */
+static int orc_relax(orc_amg *h, int level, int relax_type, int points, const double *f, double *u)
 {
    orc_level *L = &h->L[level];
    int err = 0;
    switch (relax_type)
    {
       case 18: case 7:
+         if (points && L->cf)
+         {
+            /* hypre_BoomerAMGRelax7Jacobi (par_relax.c:1177-1254): the whole Vtemp = w (f - A u), then
+             * hypre_ParVectorElmdivpyMarked (seq_mv/vector.c:823-870): u_i += Vtemp_i / l1_i where marker_i == points */
+            int i;
+            if (L->all_zeros) { for (i = 0; i < L->n; i++) { h->Vtemp[i] = L->relax_weight * f[i]; } }
+            else { orc_csr_matvec(L->n, L->Ai, L->Aj, L->Aa, -L->relax_weight, u, L->relax_weight, f, h->Vtemp); }
+            for (i = 0; i < L->n; i++) { if (L->cf[i] == points) { u[i] += h->Vtemp[i] / L->l1[i]; } }
+            break;
+         }
          orc_relax_l1jacobi(L->n, L->Ai, L->Aj, L->Aa, f, L->l1, L->relax_weight, u, h->Vtemp, L->all_zeros);
          break;
       case 0:
@@ -129,7 +146,7 @@ static int orc_relax(orc_amg *h, int level, int relax_type, const double *f, dou
          for (i = 0; i < L->n; i++)
          {
             const double di = L->Aa[L->Ai[i]];
-            if (di != 0.0)
+            if ((points == 0 || L->cf == NULL || L->cf[i] == points) && di != 0.0)
             {
                double res = f[i];
                for (jj = L->Ai[i] + 1; jj < L->Ai[i + 1]; jj++) { res -= L->Aa[jj] * h->Vtemp[L->Aj[jj]]; }
@@ -179,9 +196,18 @@ int orc_amg_cycle(orc_amg *h, const double *f, double *u, int all_zeros)
       int num_sweep = nl > 1 ? h->num_sweeps[cycle_param] : h->num_sweeps[0];
       for (j = 0; j < num_sweep; j++)
       {
-         int e = orc_relax(h, level, relax_type, F, U);
-         if (e < 0) { free(lev_counter); return e; }
-         err |= e;
+         /* hypre_BoomerAMGRelaxIF (par_relax_interface.c:20-64): with relax_order 1 a sweep on a non-coarsest level is
+          * two calls, C then F points on the way down, F then C on the way up; Chebyshev (16) and Gaussian
+          * elimination (9) do not go through it (par_cycle.c:495-540) */
+         const int cf_order = h->relax_order == 1 && cycle_param < 3 && nl > 1 && relax_type != 16 && relax_type != 9;
+         int pass;
+         for (pass = 0; pass < (cf_order ? 2 : 1); pass++)
+         {
+            const int points = !cf_order ? 0 : ((cycle_param < 2) == (pass == 0) ? 1 : -1);
+            int e = orc_relax(h, level, relax_type, points, F, U);
+            if (e < 0) { free(lev_counter); return e; }
+            err |= e;
+         }
       }
       --lev_counter[level];
       if (lev_counter[level] >= 0 && level != nl - 1)

@@ -37,7 +37,7 @@ def relevant(job):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-ranks", type=int, default=4)
-    ap.add_argument("--timeout", type=int, default=120)
+    ap.add_argument("--timeout", type=int, default=400)
     ap.add_argument("--all", action="store_true", help="also the jobs of solvers the binding does not interpose (expected: rejected or reference path)")
     ap.add_argument("--match", default="", help="only jobs whose output name contains this")
     a = ap.parse_args()

@@ -34,6 +34,8 @@ def lib():
         L.orc_amg_cycle.argtypes = [vp, vp, vp, i]
         L.orc_pcg.argtypes = [vp, vp, vp, d, i, i, vp, vp, vp]
         L.orc_amg_set_precond_cycles.argtypes = [vp, i]
+        L.orc_amg_set_level_cf.argtypes = [vp, i, vp]
+        L.orc_amg_set_relax_order.argtypes = [vp, i]
         L.orc_gmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_cogmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_flexgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
@@ -120,15 +122,19 @@ class OracleAMG:
             l1 = amg.level_array("l1", l, n)
             ds = amg.level_array("cheby_ds", l, n)
             coefs = amg.level_array("cheby_coefs", l, prm["cheby_order"] + 1) if 16 in prm["relax_type"] else None
-            self.keep.append((Ai, Aj, Aa, Pi, Pj, Pa, l1, ds, coefs))
+            cf = amg.cf_marker(l, n) if prm["relax_order"] == 1 else None
+            self.keep.append((Ai, Aj, Aa, Pi, Pj, Pa, l1, ds, coefs, cf))
             L.orc_amg_set_level(self.h, l, n, p(Ai), p(Aj), p(Aa), nc, p(Pi), p(Pj), p(Pa), p(l1), p(ds), p(coefs),
                                 amg.relax_weight(l))
+            if cf is not None:
+                L.orc_amg_set_level_cf(self.h, l, p(cf))
         rt = np.array(prm["relax_type"], dtype=np.int32)
         if rt[3] == 19:
             rt[3] = 9
         ns = np.array(prm["num_sweeps"], dtype=np.int32)
         L.orc_amg_set_cycle(self.h, p(rt), p(ns), prm["cycle_type"], prm["fcycle"], prm["cheby_order"],
                             prm["cheby_scale"])
+        L.orc_amg_set_relax_order(self.h, prm["relax_order"])
         dense = amg.coarse_dense()
         if dense is not None:
             dense = np.ascontiguousarray(dense)
@@ -275,6 +281,13 @@ CASES = {
     "lap7_24_rlx16_F": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"FCycle": 1}),
     "lap27_20_rlx18_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=18, opts={"NumSweeps": 2}),
     "lap7_24_rlx7_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxWt": 0.8}),
+    # CF-ordered relaxation (ij -CF 1 = HYPRE_BoomerAMGSetRelaxOrder(1)): C points then F points on the way down,
+    # F then C on the way up (par_relax_interface.c:20-64)
+    "lap7_24_rlx18_CF": dict(gen="laplacian", dims=(24, 24, 24), rlx=18, opts={"RelaxOrder": 1}),
+    "lap27_20_rlx0_CF_w07": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=0, opts={"RelaxOrder": 1, "RelaxWt": 0.7}),
+    "lap7_24_rlx7_CF_W": dict(gen="laplacian", dims=(24, 24, 24), rlx=7, opts={"RelaxOrder": 1, "CycleType": 2, "RelaxWt": 0.9}),
+    "lap27_20_rlx11_CF": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=11, opts={"RelaxOrder": 1}),
+    "lap7_24_rlx16_CF": dict(gen="laplacian", dims=(24, 24, 24), rlx=16, opts={"RelaxOrder": 1}),
     # relax_type 0: weighted point Jacobi (par_relax.c:320-335), five jobs of the reference's TEST_ij suites
     "lap7_24_rlx0_w08": dict(gen="laplacian", dims=(24, 24, 24), rlx=0, opts={"RelaxWt": 0.8}),
     "lap27_20_rlx0_w07_ns2": dict(gen="laplacian_27pt", dims=(20, 20, 20), rlx=0, opts={"RelaxWt": 0.7, "NumSweeps": 2}),

@@ -233,7 +233,9 @@ def test_pcg_matches_oracle_and_golden(H, ctx, cases, name):
     assert vec_err(x.numpy(), xo) < 1e-8
 
 
-@pytest.mark.parametrize("name", ["lap7_24_rlx18_W", "lap7_24_rlx16_F", "lap27_20_rlx18_ns2", "lap7_24_rlx7_w08"])
+@pytest.mark.parametrize("name", ["lap7_24_rlx18_W", "lap7_24_rlx16_F", "lap27_20_rlx18_ns2", "lap7_24_rlx7_w08",
+                                  "lap7_24_rlx18_CF", "lap27_20_rlx0_CF_w07", "lap7_24_rlx7_CF_W", "lap27_20_rlx11_CF",
+                                  "lap7_24_rlx16_CF"])
 def test_pcg_cycle_variants_match_oracle_and_reference(H, ctx, cases, name):
     """W-cycle, F-cycle, two sweeps per level, weighted Jacobi (relax_type 7): device vs oracle vs the
     reference's own hypre_PCGSolve in-process on the same hierarchy"""
@@ -394,7 +396,9 @@ def _gpu_count():
 
 
 @pytest.mark.parametrize("args", ["-n 40 40 40 -P 2 1 1 -solver 1 -rlx 18", "-n 40 40 40 -P 2 1 1 -solver 1 -rlx 16",
-                                  "-27pt -n 24 24 24 -P 1 2 1 -solver 1 -rlx 11"])
+                                  "-27pt -n 24 24 24 -P 1 2 1 -solver 1 -rlx 11",
+                                  "-solver 1 -rlx 16 -cheby_eig_est 0 -cheby_scale 0 -n 40 40 20 -P 2 1 1",
+                                  "-n 30 30 30 -P 1 1 2 -solver 1 -rlx 18 -CF 1", "-27pt -n 24 24 24 -P 2 1 1 -solver 1 -rlx 0 -w 0.7 -CF 1"])
 def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
     """The reference's unchanged src/test/ij.c on 2 ranks, hypre's own DISTRIBUTED host setup (MPI build of the
     reference over oracle/mpishim), solve on 2 GPUs (hypre_b200/lib/ij_b200_mp) -- against the same command on

@@ -186,7 +186,9 @@ def test_gs2_block_partitioned_restatement(ref_off, inner):
 
 @pytest.mark.parametrize("name", ["lap7_24_rlx18_W", "lap7_24_rlx16_F", "lap27_20_rlx18_ns2", "lap7_24_rlx7_w08",
                                   "lap7_24_rlx16_var1", "lap7_24_rlx16_o4", "lap7_24_rlx16_o3_noscale",
-                                  "lap7_24_rlx18_pc3", "lap7_24_rlx16_pc2", "lap7_24_rlx0_w08", "lap27_20_rlx0_w07_ns2"])
+                                  "lap7_24_rlx18_pc3", "lap7_24_rlx16_pc2", "lap7_24_rlx0_w08", "lap27_20_rlx0_w07_ns2",
+                                  "lap7_24_rlx18_CF", "lap27_20_rlx0_CF_w07", "lap7_24_rlx7_CF_W", "lap27_20_rlx11_CF",
+                                  "lap7_24_rlx16_CF"])
 def test_oracle_pcg_option_cases_match_reference(ref_off, name):
     """cycle and smoother options without a golden (W / F cycle, two sweeps, weighted Jacobi, Chebyshev variant 1,
     orders 3 / 4, unscaled): the oracle against hypre_PCGSolve in-process on the same hierarchy"""
