@@ -614,7 +614,12 @@ def finish_multi(args, R, P, m):
             "roofline": {"bound": "hbm", "kernel": "whole PCG iteration, all ranks (per-kernel roofline is reported at N=1)",
                          "achieved": iter_gbs, "peak": peak * R.world, "unit": "GB/s", "frac": iter_gbs / (peak * R.world),
                          "traffic": None, "peak_source": peak_src + " x n_gpus", "pcg_iteration_bytes": iter_bytes},
-            "cpu_baseline": None, "parity": parity_block(m["rel"], m["iters"], golden_history(args.workload, args.n)),
+            # (native mode: hypre's distributed setup builds another hierarchy than the single-rank golden's; its parity
+            #  is checked against the reference on the same process grid by tests/test_gpu_solve.py, not here)
+            "cpu_baseline": None,
+            "parity": parity_block(m["rel"], m["iters"], golden_history(args.workload, args.n)) if not P.get("native") else
+                      {"checked": False, "why": "distributed setup: hierarchy differs from the single-rank golden; see "
+                                                "tests/test_gpu_solve.py::test_unchanged_ij_on_two_ranks_with_distributed_setup"},
             "clocks": m["clocks"], "setup_s": P["setup_s"], "upload_s": m["upload_s"],
             "halo": halo,
         }
