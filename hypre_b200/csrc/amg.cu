@@ -279,7 +279,7 @@ extern "C" int b200_amg_finalize(b200_amg *a)
          if ((t == 18 || t == 7) && L.d_l1 == nullptr) { b200_set_error("level %d: l1 norms missing", l); return B200_ERR_ARG; }
          if (t == 16 && L.coefs.empty()) { b200_set_error("level %d: Chebyshev data missing", l); return B200_ERR_ARG; }
          if (t == 11 || t == 12) { B200_TRY(parcsr_ensure_L(L.A)); }
-         if (a->relax_order == 1 && cp != 3 && a->num_levels > 1 && (t == 18 || t == 7) && L.d_cf == nullptr)
+         if (a->relax_order == 1 && cp != 3 && a->num_levels > 1 && (t == 18 || t == 7) && L.d_cf == nullptr && L.n > 0)
          {
             b200_set_error("level %d: relax_order 1 needs the CF marker (b200_amg_set_level_cf_marker)", l);
             return B200_ERR_ARG;

@@ -632,7 +632,9 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
       for (l = 0; l < nl - 1 && st == B200_OK; l++)
       {
          const int off = (starts && l < repl) ? STARTS(l)[g_rank] : 0;
-         if (!cfm || !cfm[l]) { st = B200_ERR_ARG; break; }
+         const HYPRE_Int n_here = hypre_CSRMatrixNumRows(hypre_ParCSRMatrixDiag(A_array[l]));
+         const int *cf_here = (cfm && cfm[l]) ? hypre_IntArrayData(cfm[l]) : NULL;
+         if (cf_here == NULL && n_here > 0) { st = B200_ERR_ARG; break; }       /* (a rank without rows holds no marker) */
          if (g_native && rows_of != NULL && l >= repl)
          {
 #ifndef HYPRE_SEQUENTIAL
@@ -641,13 +643,14 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
             int r, *dsp = (int *) calloc((size_t) g_nranks + 1, sizeof(int)), *all;
             for (r = 0; r < g_nranks; r++) { dsp[r + 1] = dsp[r] + ro[r]; }
             all = (int *) calloc((size_t) (dsp[g_nranks] > 0 ? dsp[g_nranks] : 1), sizeof(int));
-            hypre_MPI_Allgatherv(hypre_IntArrayData(cfm[l]), ro[g_rank], HYPRE_MPI_INT, all, (HYPRE_Int *) ro, dsp, HYPRE_MPI_INT,
+            int dummy = 0;
+            hypre_MPI_Allgatherv((void *) (cf_here ? cf_here : &dummy), ro[g_rank], HYPRE_MPI_INT, all, (HYPRE_Int *) ro, dsp, HYPRE_MPI_INT,
                                  hypre_ParCSRMatrixComm(A_array[l]));
             st = b200_amg_set_level_cf_marker(amg, l, all);
             free(dsp); free(all);
 #endif
          }
-         else { st = b200_amg_set_level_cf_marker(amg, l, hypre_IntArrayData(cfm[l]) + off); }
+         else { st = b200_amg_set_level_cf_marker(amg, l, cf_here ? cf_here + off : NULL); }
       }
       if (st != B200_OK)
       {
@@ -677,10 +680,17 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          l1d = diag0 + off;
       }
 #ifndef HYPRE_SEQUENTIAL
-      if (gathered && (l1d != NULL || uses_jac0))
+      if (gathered)
       {
-         l1_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), l1d, rows_of + (size_t) l * g_nranks);
-         l1d = l1_all;
+         /* collective: the decision must not depend on this rank's data (a rank without rows on this level holds no
+          * l1 norms at all) */
+         HYPRE_Int have = (l1d != NULL || uses_jac0) ? 1 : 0, any = 0;
+         hypre_MPI_Allreduce(&have, &any, 1, HYPRE_MPI_INT, hypre_MPI_MAX, hypre_ParCSRMatrixComm(A_array[l]));
+         if (any)
+         {
+            l1_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), l1d, rows_of + (size_t) l * g_nranks);
+            l1d = l1_all;
+         }
       }
 #endif
       status = b200_amg_set_level_relax(amg, l, hypre_ParAMGDataRelaxWeight(amg_data)[l], l1d);
@@ -695,7 +705,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          const double *dsd = (hypre_ParAMGDataChebyScale(amg_data) && ds && ds[l] && hypre_VectorData(ds[l]))
                              ? hypre_VectorData(ds[l]) + off : NULL;
 #ifndef HYPRE_SEQUENTIAL
-         if (gathered && dsd != NULL)
+         if (gathered && hypre_ParAMGDataChebyScale(amg_data))       /* (same decision on every rank) */
          {
             ds_all = gather_level_vector(hypre_ParCSRMatrixComm(A_array[l]), dsd, rows_of + (size_t) l * g_nranks);
             dsd = ds_all;
