@@ -296,7 +296,9 @@ __device__ __forceinline__ double pat_word(unsigned h, const unsigned *&lp, int 
 // (Measured and dropped, profiles/r02_fmt_probe_*.jsonl: the dictionary as a kernel parameter read through
 // indexed LDC -- twice as slow as the shared-memory lookups; a grid of one wave of resident blocks -- 1.5x slower
 // than four waves; 40 / 48 registers per thread -- slower than 32; the decoded header of lane-uniform slices cached
-// in registers from one slice to the next at 64 registers / 4 blocks per SM -- 1.8x slower.)
+// in registers from one slice to the next at 64 registers / 4 blocks per SM -- 1.8x slower; two header words per trip
+// with all eight gathers issued before the first fma at 40 registers / 6 blocks -- 12 % slower.  The loop is bound by
+// load latency and occupancy is what hides it: every variant that trades resident warps for work per warp lost.)
 template <class XF>
 __device__ __forceinline__ double rowsum_pat(const MatView &D, const uint4 &h0, const uint4 *hdr, int lane, int row,
                                              const double *__restrict__ x, const XF &xf, const double2 *s_pat)

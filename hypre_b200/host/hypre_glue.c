@@ -536,13 +536,13 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
          }
          if (!ok) { even_starts(nc, g_nranks, STARTS(l + 1)); }
       }
-      /* Small levels are latency-bound: below B200_REPL_NNZ nonzeros (default 8e6 = one ~16 us pass at
-       * HBM speed) every rank keeps the whole level and runs it without communication -- the
+      /* Small levels are latency-bound: below B200_REPL_NNZ nonzeros (default 2e6; measured at 8 GPUs:
+       * 15.2 ms per 256^3 solve against 16.5 ms with 8e6, profiles/r02_bench_c3_8gpu*.json) every rank keeps the whole level and runs it without communication -- the
        * reference's own answer to idle ranks on coarse grids is seq_threshold / hypre_seqAMGCycle
        * (par_cycle.c:362-369).  Results do not depend on this choice for Jacobi / Chebyshev. */
       {
          const char *e = getenv("B200_REPL_NNZ");
-         double limit = e ? atof(e) : 8.0e6;
+         double limit = e ? atof(e) : 2.0e6;
          for (l = 1; l < nl; l++)
          {
             hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]);
@@ -555,7 +555,7 @@ static b200_amg *upload_amg(hypre_ParAMGData *amg_data, int **starts_out, int *r
    {
       /* same rule as the replicated-setup mode, on the GLOBAL size of the level */
       const char *e = getenv("B200_REPL_NNZ");
-      double limit = e ? atof(e) : 8.0e6;
+      double limit = e ? atof(e) : 2.0e6;
       for (l = 1; l < nl && limit > 0.0; l++)
       {
          hypre_CSRMatrix *d = hypre_ParCSRMatrixDiag(A_array[l]), *o = hypre_ParCSRMatrixOffd(A_array[l]);

@@ -21,6 +21,7 @@ from hypre_b200 import capi, hypre as H   # noqa: E402
 # name: (compression mode, no_padding_markers, [(chunked, pat_regs), ...] launch options timed on that upload)
 CONFIGS = {
     # pat_regs: bits 1-3 = waves of resident blocks in the grid of the pattern kernel (8 = four waves, the default)
+    # pat_regs: bits 1-3 = waves of resident blocks in the grid of the pattern kernel (8 = four waves, the default)
     "pat8": (-1, 1, [(1, 8), (0, 8), (1, 2)]),
     "val_markers": (1, 0, [(1, 0), (0, 0)]),
     "val_zpad": (1, 1, [(1, 0), (0, 0)]),

@@ -398,7 +398,10 @@ def _gpu_count():
 @pytest.mark.parametrize("args", ["-n 40 40 40 -P 2 1 1 -solver 1 -rlx 18", "-n 40 40 40 -P 2 1 1 -solver 1 -rlx 16",
                                   "-27pt -n 24 24 24 -P 1 2 1 -solver 1 -rlx 11",
                                   "-solver 1 -rlx 16 -cheby_eig_est 0 -cheby_scale 0 -n 40 40 20 -P 2 1 1",
-                                  "-n 30 30 30 -P 1 1 2 -solver 1 -rlx 18 -CF 1", "-27pt -n 24 24 24 -P 2 1 1 -solver 1 -rlx 0 -w 0.7 -CF 1"])
+                                  "-n 30 30 30 -P 1 1 2 -solver 1 -rlx 18 -CF 1",
+                                  # small enough that one rank owns no row of the coarsest levels (gathered levels)
+                                  "-n 10 10 10 -P 2 1 1 -solver 1 -rlx 11", "-n 12 12 12 -P 2 1 1 -solver 1 -rlx 18 -CF 1",
+                                  "-n 12 12 12 -P 1 1 2 -solver 1 -rlx 16", "-27pt -n 24 24 24 -P 2 1 1 -solver 1 -rlx 0 -w 0.7 -CF 1"])
 def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
     """The reference's unchanged src/test/ij.c on 2 ranks, hypre's own DISTRIBUTED host setup (MPI build of the
     reference over oracle/mpishim), solve on 2 GPUs (hypre_b200/lib/ij_b200_mp) -- against the same command on
