@@ -3,8 +3,10 @@
 report of scripts/prof_ops.py and write the committed summary that bench.py quotes as roofline.traffic.
 usage: ncu_traffic.py gpurun_out/prof_rows.ncu-rep profiles/r01_ncu_traffic.json [rows nnz value_format]"""
 import csv
+import hashlib
 import io
 import json
+import os
 import subprocess
 import sys
 
@@ -39,9 +41,13 @@ for r in rows[2:]:
     })
 spmv = [l for l in launches if "EpiMatvec>" in l["kernel"] or "EpiMatvec," in l["kernel"] or "9EpiMatvec" in l["kernel"]]
 first = (spmv or launches)[0]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 summary = {
+    # bench.py quotes the traffic only while the kernel source is the one that was profiled
+    "spmv_cuh_sha16": hashlib.sha256(open(os.path.join(ROOT, "hypre_b200", "csrc", "spmv.cuh"), "rb").read()).hexdigest()[:16],
+    "commit": subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip(),
     "source": "ncu --set full --clock-control none -k regex:rows_kernel -s 3 -c 4 python scripts/prof_ops.py --reps 2",
-    "matrix": {"rows": rows_n, "nnz": nnz, "value_format": vfmt, "what": "7-pt Laplacian 256^3, level-0 diag block, sliced ELL"},
+    "matrix": {"rows": rows_n, "nnz": nnz, "value_format": vfmt, "what": "7-pt Laplacian 256^3, level-0 diag block, thread-per-row layout"},
     "spmv_level0": {"traffic_bytes_per_launch": first["dram_read_bytes"] + first["dram_write_bytes"],
                     "algorithmic_bytes_per_launch": 12.0 * nnz + 4.0 * (rows_n + 1) + 16.0 * rows_n, **first},
     "launches": launches,
