@@ -60,10 +60,6 @@ int  orc_gmres(orc_amg *h, int precond_kind, const double *b, double *x, double 
 int  orc_flexgmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                    int min_iter, int max_iter, int skip_real_r_check, double *norms, double *rel_resid,
                    int *converged);
-/* hypre_CGNRSolve (krylov/cgnr.c) with diagonal scaling (1) or no preconditioner (2): iteration count, -101 for
- * Inf/NaN input */
-int  orc_cgnr(orc_amg *h, int precond_kind, const double *b, double *x, double tol, int stop_crit, int max_iter,
-              double *norms, double *rel_resid);
 /* hypre_LGMRESSolve (krylov/lgmres.c): GMRES augmented with aug_dim error approximations */
 int  orc_lgmres(orc_amg *h, int precond_kind, const double *b, double *x, double tol, double a_tol, int k_dim,
                 int aug_dim, int approx_constant, int min_iter, int max_iter, double *norms, double *rel_resid,

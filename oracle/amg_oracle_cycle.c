@@ -783,71 +783,3 @@ done:
    free(p); free(av); free(aav); free(aug_order); free(hh); free(r); free(w); free(rs); free(c); free(s);
    return iter;
 }
-
-/* hypre_CGNRSolve (krylov/cgnr.c:209-...; ij -solver 6 with diagonal scaling): conjugate gradients on the normal
- * equations of the right-preconditioned system.  precond_kind 1 (diagonal scaling, symmetric: precondT == precond)
- * or 2 (identity); the AMG form needs the transposed cycle (HYPRE_BoomerAMGSolveT) and is not restated.
- * Returns the iteration count, or -101 for Inf/NaN input (the reference returns ierr = 101). */
-int orc_cgnr(orc_amg *h, int precond_kind, const double *b, double *x, double tol, int stop_crit, int max_iter,
-             double *norms, double *rel_resid)
-{
-   orc_level *L0 = &h->L[0];
-   const int n = L0->n;
-   const size_t nb = sizeof(double) * (size_t) n;
-   double *p = (double *) calloc((size_t) n, sizeof(double));
-   double *q = (double *) calloc((size_t) n, sizeof(double));
-   double *r = (double *) calloc((size_t) n, sizeof(double));
-   double *t = (double *) calloc((size_t) n, sizeof(double));
-   double alpha, beta, gamma, gamma_old, bi_prod, i_prod = 0.0, eps, last_norm;
-   int i = 0, k, x_not_set = 1, ret;
-   if (precond_kind == 0) { ret = -1; goto done; }
-   bi_prod = orc_dot(n, b, b);
-   if (bi_prod != 0.0 && !(bi_prod / bi_prod == bi_prod / bi_prod)) { ret = -101; goto done; }
-   eps = stop_crit ? tol * tol : (tol * tol) * bi_prod;
-   if (bi_prod == 0.0) { memcpy(x, b, nb); if (norms) { norms[0] = 0.0; } if (rel_resid) { *rel_resid = 0.0; } ret = 0; goto done; }
-   orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, x, 1.0, b, r);
-   last_norm = sqrt(orc_dot(n, r, r));
-   if (norms) { norms[0] = last_norm; }
-   if (last_norm != 0.0 && !(last_norm / last_norm == last_norm / last_norm)) { ret = -101; goto done; }
-   orc_csr_matvecT(n, n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, q);
-   orc_precond(h, precond_kind, q, t);
-   memcpy(p, r, nb);
-   gamma = orc_dot(n, t, t);
-   if (gamma != 0.0 && !(gamma / gamma == gamma / gamma)) { ret = -101; goto done; }
-   while ((i + 1) <= max_iter)
-   {
-      i++;
-      orc_precond(h, precond_kind, p, t);
-      orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, 1.0, t, 0.0, NULL, q);
-      alpha = gamma / orc_dot(n, q, q);
-      gamma_old = gamma;
-      for (k = 0; k < n; k++) { x[k] += alpha * p[k]; }
-      for (k = 0; k < n; k++) { r[k] += -alpha * q[k]; }
-      orc_csr_matvecT(n, n, L0->Ai, L0->Aj, L0->Aa, 1.0, r, 0.0, q);
-      orc_precond(h, precond_kind, q, t);
-      gamma = orc_dot(n, t, t);
-      i_prod = orc_dot(n, r, r);
-      last_norm = sqrt(i_prod);
-      if (norms) { norms[i] = last_norm; }
-      if (i_prod < eps)
-      {
-         orc_precond(h, precond_kind, x, q);
-         orc_csr_matvec(n, L0->Ai, L0->Aj, L0->Aa, -1.0, q, 1.0, b, r);
-         i_prod = orc_dot(n, r, r);
-         if (i_prod < eps) { memcpy(x, q, nb); x_not_set = 0; break; }
-      }
-      beta = gamma / gamma_old;
-      for (k = 0; k < n; k++) { p[k] *= beta; }
-      for (k = 0; k < n; k++) { p[k] += t[k]; }
-   }
-   if (x_not_set)
-   {
-      memcpy(q, x, nb);
-      orc_precond(h, precond_kind, q, x);
-   }
-   if (rel_resid) { *rel_resid = last_norm / sqrt(bi_prod); }
-   ret = i;
-done:
-   free(p); free(q); free(r); free(t);
-   return ret;
-}

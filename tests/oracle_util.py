@@ -41,7 +41,6 @@ def lib():
         L.orc_flexgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, vp, vp, vp]
         L.orc_lgmres.argtypes = [vp, i, vp, vp, d, d, i, i, i, i, i, vp, vp, vp]
         L.orc_krylov_set_options.argtypes = [d, i]
-        L.orc_cgnr.argtypes = [vp, i, vp, vp, d, i, i, vp, vp]
         L.orc_bicgstab.argtypes = [vp, i, vp, vp, d, d, i, i, vp, vp, vp]
         _lib = L
     return _lib
@@ -205,15 +204,6 @@ class OracleAMG:
         it = lib().orc_lgmres(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, a_tol, k_dim, aug_dim,
                               approx_constant, min_iter, max_iter, p(norms), C.byref(rel), C.byref(conv))
         return x, it, norms[:it + 1].copy(), rel.value, conv.value
-
-    def cgnr(self, b, x0, precond=1, tol=1e-8, stop_crit=0, max_iter=100):
-        """orc_cgnr: (x, iterations, norms[0..iterations], final relative residual)"""
-        x = np.array(x0, dtype=np.float64, copy=True)
-        norms = np.zeros(max_iter + 1)
-        rel = C.c_double()
-        it = lib().orc_cgnr(self.h, precond, p(np.ascontiguousarray(b)), p(x), tol, stop_crit, max_iter, p(norms),
-                            C.byref(rel))
-        return x, it, norms[:max(it, 0) + 1].copy(), rel.value
 
     def flexgmres(self, b, x0, **kw):
         """orc_flexgmres (preconditioned basis kept): same arguments and results as gmres"""
