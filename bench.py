@@ -338,7 +338,7 @@ def run_b200(args, rank, world):
     HL = H.lib()
     native = bool(args.native and world > 1)
     if native:
-        # hypre's own distributed setup on `world` ranks (MPI build of the reference over oracle/mpishim, ranks
+        # hypre's own distributed setup on `world` ranks (MPI build of the reference over hypre_b200/host/mpishim, ranks
         # met through SHIM_DIR in main()); the binding bootstraps NCCL through hypre's MPI layer at first use
         assert H.NATIVE and H.world() == (rank, world), (H.NATIVE, H.world(), rank, world)
     elif world > 1:
@@ -509,6 +509,7 @@ def run_b200(args, rank, world):
                 "iterations_per_step": e2e_iters, "ms_per_step": 1e3 * e2e_s / args.steps,
                 "final_rel_residual": float(api_rel[-1]) if len(api_rel) else None},
         "gpu_launches": int(launches),
+        "launches_per_iteration": launches / float(args.steps * (iters + 1)),
         "roofline": {"bound": "hbm", "kernel": "rows_kernel (level-0 SpMV y=A*x, %.1f MB algorithmic)" % (spmv_bytes / 1e6),
                      "achieved": spmv_gbs, "peak": peak, "unit": "GB/s", "frac": spmv_gbs / peak,
                      "traffic": ncu_traffic(n, nnz0, vfmt.value), "algorithmic_bytes": spmv_bytes,
@@ -598,7 +599,7 @@ def finish_multi(args, R, P, m):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": P["cmd"], "dof": m["n_global"], "iterations_per_step": m["iters"],
                        "levels": m["levels"],
-                       "setup": ("hypre's distributed setup on %d ranks (MPI build over oracle/mpishim)" % R.world)
+                       "setup": ("hypre's distributed setup on %d ranks (MPI build over hypre_b200/host/mpishim)" % R.world)
                        if P.get("native") else "single-rank host setup replicated on every process",
                        "partition": "%s, %d ranks, halo = %s" % (
                            "hypre's box partition and CommPkg" if P.get("native") else "1-D row blocks",
@@ -611,6 +612,7 @@ def finish_multi(args, R, P, m):
                     "ms_per_step": 1e3 * m["e2e_s"] / args.steps,
                     "final_rel_residual": float(m["api_rel"][-1]) if len(m["api_rel"]) else None},
             "gpu_launches": int(launches),
+            "launches_per_iteration_per_rank": launches / float(R.world * args.steps * (m["iters"] + 1)),
             "roofline": {"bound": "hbm", "kernel": "whole PCG iteration, all ranks (per-kernel roofline is reported at N=1)",
                          "achieved": iter_gbs, "peak": peak * R.world, "unit": "GB/s", "frac": iter_gbs / (peak * R.world),
                          "traffic": None, "peak_source": peak_src + " x n_gpus", "pcg_iteration_bytes": iter_bytes},

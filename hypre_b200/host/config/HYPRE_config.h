@@ -1,10 +1,10 @@
-/* oracle/ref_config/HYPRE_config.h
+/* hypre_b200/host/config/HYPRE_config.h
  *
- * TEST INFRASTRUCTURE (oracle build) -- hand-written configuration header used
- * when oracle/Makefile compiles the reference's host sources where they lie
- * under /root/reference/src.  It stands in for the header that the reference's
- * own configure step would generate (template: src/config/HYPRE_config.h.in)
- * for a `--without-MPI --with-openmp` host-only build:
+ * Hand-written configuration header used when the reference's host sources are compiled
+ * where they lie under /root/reference/src (hypre_b200/host/Makefile for the product's
+ * libHYPRE_host.so; oracle/Makefile for the checker's separately built libHYPRE_ref.so).
+ * It stands in for the header that the reference's own configure step would generate
+ * (template: src/config/HYPRE_config.h.in) for a `--without-MPI --with-openmp` host-only build:
  *   - HYPRE_SEQUENTIAL      : hypre_MPI_* resolve to the single-rank stubs in
  *                             src/utilities/mpistubs.c
  *   - HYPRE_USING_OPENMP    : OpenMP row loops (src/seq_mv/csr_matvec.c:673-848)

@@ -1,12 +1,11 @@
-/* oracle/ref_config_mp/HYPRE_config.h
+/* hypre_b200/host/config_mp/HYPRE_config.h
  *
- * TEST INFRASTRUCTURE (oracle build) -- hand-written configuration header used
- * when oracle/Makefile compiles the reference's host sources where they lie
- * under /root/reference/src.  It stands in for the header that the reference's
- * own configure step would generate (template: src/config/HYPRE_config.h.in)
- * for a `--with-MPI --with-openmp` host-only build, the MPI being oracle/mpishim
- * (mpi.h there; N processes on one machine).  Used for ONE thing: reproducing the
- * reference's multi-rank goldens (src/test/TEST_ij, .saved files) with oracle/_ref/ij_ref_mp.
+ * Hand-written configuration header used when the reference's host sources are compiled
+ * where they lie under /root/reference/src (hypre_b200/host/Makefile for the product's
+ * libHYPRE_host_mp.so; oracle/Makefile for the checker's separately built libHYPRE_ref_mp.so).
+ * It stands in for the header that the reference's own configure step would generate
+ * (template: src/config/HYPRE_config.h.in) for a `--with-MPI --with-openmp` host-only build,
+ * the MPI being hypre_b200/host/mpishim (mpi.h there; N processes on one machine).
  *   - HYPRE_HAVE_MPI        : hypre_MPI_* call MPI_* (src/utilities/mpistubs.c:919-1530)
  *   - HYPRE_USING_OPENMP    : OpenMP row loops (src/seq_mv/csr_matvec.c:673-848)
  *   - HYPRE_USING_HOST_MEMORY: every object lives in host memory

@@ -1,13 +1,14 @@
-/* oracle/mpishim/mpi.h -- TEST INFRASTRUCTURE.
+/* hypre_b200/host/mpishim/mpi.h -- the MPI stand-in of the native multi-rank mode (our own code).
  *
  * A small message-passing library with the MPI-1/2 subset the reference calls through its
  * hypre_MPI_* wrappers (src/utilities/mpistubs.c:919-1530), so that the reference's host code can
- * run on N ranks (N processes on one machine) on boxes that have no MPI installation.  It exists
- * to reproduce the reference's multi-rank golden results (src/test/TEST_ij, the .saved files, all
- * recorded with mpirun -np 2..4) with the reference library compiled by oracle/Makefile, and to
- * host the ranks of the multi-GPU demonstration of the binding (hypre_b200/lib/ij_b200_mp; with a
- * real MPI installation that binary links the real library instead).
- * Ranks are processes started by oracle/_ref/mpirun_shim, connected pairwise by Unix stream
+ * run on N ranks (N processes on one machine) on boxes that have no MPI installation.  Two builds
+ * use this source: the product's (hypre_b200/host/Makefile -> hypre_b200/lib/libmpishim.so: the ranks
+ * of hypre's own distributed setup, one per GPU, ij_b200_mp / bench.py --native; with a real MPI
+ * installation those binaries link the real library instead), and the checker's own (oracle/Makefile
+ * -> oracle/_ref/libmpishim.so: reproduces the reference's multi-rank golden results, src/test/TEST_ij
+ * .saved files, all recorded with mpirun -np 2..4).
+ * Ranks are processes started by mpirun_shim (or by torchrun, see mpishim.c), connected pairwise by Unix stream
  * sockets; sends are buffered (eager), receives match on (communicator, source, tag) in arrival
  * order, collectives are linear algorithms over point-to-point messages with a fixed
  * combination order (rank 0, 1, 2, ...), hence deterministic.

@@ -1,4 +1,4 @@
-/* oracle/mpishim/mpirun_shim.c -- TEST INFRASTRUCTURE: launcher for oracle/mpishim.
+/* hypre_b200/host/mpishim/mpirun_shim.c -- launcher for the message-passing shim in this directory.
  *
  *    mpirun_shim -np N program [args...]
  *

@@ -1,5 +1,5 @@
-/* oracle/mpishim/mpishim.c -- TEST INFRASTRUCTURE: the message-passing library behind
- * oracle/mpishim/mpi.h (see there for scope).  One process per rank, started by mpirun_shim,
+/* hypre_b200/host/mpishim/mpishim.c -- the message-passing library behind mpi.h in this
+ * directory (see there for scope and for who builds it).  One process per rank, started by mpirun_shim,
  * which hands every rank one connected Unix stream socket per peer (environment SHIM_RANK,
  * SHIM_SIZE, SHIM_FDS).  Ranks started by something else (torchrun, a job script) meet through
  * Unix sockets in a directory instead: SHIM_DIR=<dir> with SHIM_RANK/SHIM_SIZE or torchrun's

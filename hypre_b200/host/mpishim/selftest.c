@@ -1,4 +1,4 @@
-/* oracle/mpishim/selftest.c -- TEST INFRASTRUCTURE: exercises the message-passing shim itself
+/* hypre_b200/host/mpishim/selftest.c -- TEST INFRASTRUCTURE (built by oracle/Makefile only): exercises the message-passing shim itself
  * (run by tests/test_mpishim.py under mpirun_shim with 1, 2, 3 and 5 ranks). Prints "SHIM_OK". */
 #include "mpi.h"
 #include <stdio.h>

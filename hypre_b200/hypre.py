@@ -36,10 +36,10 @@ class _Libs:
         setattr(self, name, f)
         return f
 
-COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h) and of oracle/mpishim
+COMM_WORLD = 0   # hypre_MPI_COMM_WORLD of the sequential stubs (src/utilities/mpistubs.h) and of hypre_b200/host/mpishim
 # Native multi-rank mode: this process is one of N ranks (one per GPU), the
-# reference is its MPI build over oracle/mpishim and hypre's own distributed setup runs.  Ranks started by
-# torchrun meet through SHIM_DIR (oracle/mpishim/mpishim.c); under mpirun_shim nothing else is needed.
+# reference is its MPI build over hypre_b200/host/mpishim and hypre's own distributed setup runs.  Ranks started by
+# torchrun meet through SHIM_DIR (hypre_b200/host/mpishim/mpishim.c); under mpirun_shim nothing else is needed.
 NATIVE = os.environ.get("HYPRE_B200_NATIVE", "0") == "1"
 
 

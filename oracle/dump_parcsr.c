@@ -1,6 +1,6 @@
-/* oracle/mpishim/dump_parcsr.c -- TEST INFRASTRUCTURE.
+/* oracle/dump_parcsr.c -- TEST INFRASTRUCTURE.
  *
- * Runs the reference on N ranks (oracle/mpishim) and writes what every rank holds of the operators of a
+ * Runs the reference on N ranks (hypre_b200/host/mpishim) and writes what every rank holds of the operators of a
  * BoomerAMG hierarchy: the ParCSR pieces (diag, offd, col_map_offd, row/column starts) and the matvec
  * communication package the reference negotiated with its real exchange
  * (hypre_MatvecCommPkgCreate, src/parcsr_mv/par_csr_communication.c:1163; assumed-partition

@@ -7,7 +7,7 @@ and <suite>.saved (what the reference's regression harness src/test/runtest.sh c
 iteration counts, final relative residual norms, average convergence factors, complexities).
 Jobs that read matrix files shipped with the reference's test data are left out (the files do not
 travel).  tests/test_ref_multirank.py replays the jobs on N ranks with the reference compiled by
-oracle/Makefile against oracle/mpishim and checks every number.
+oracle/Makefile against hypre_b200/host/mpishim and checks every number.
 
     python tests/golden/gen_saved_goldens.py [suite ...]
 """

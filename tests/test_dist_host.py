@@ -1,7 +1,7 @@
 """CPU tests of the N>1 host logic: b200_rowpart (row partition + halo plan, the counterpart of
 GenerateDiagAndOffd / hypre_MatvecCommPkgCreate) in a single-process emulation over several rank
 counts, a real 2-process gloo run of tests/dist_worker.py, and a comparison with what N real ranks of
-the reference (oracle/_ref/dump_parcsr over oracle/mpishim) build and negotiate for a whole hierarchy."""
+the reference (oracle/_ref/dump_parcsr over hypre_b200/host/mpishim) build and negotiate for a whole hierarchy."""
 import os
 import subprocess
 import sys
@@ -125,7 +125,7 @@ HAVE_MP = all(os.path.exists(os.path.join(REF_BIN, f)) for f in ("mpirun_shim", 
 
 
 def read_dump(path):
-    """one rank's file written by oracle/mpishim/dump_parcsr.c"""
+    """one rank's file written by oracle/dump_parcsr.c"""
     raw = np.fromfile(path, dtype=np.int32)
     h = raw[:12]
     (grows, gcols, first_row, n, first_col, ncd, nco, nnzd, nnzo, ns, nse, nr) = [int(v) for v in h]

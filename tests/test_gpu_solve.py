@@ -404,7 +404,7 @@ def _gpu_count():
                                   "-n 12 12 12 -P 1 1 2 -solver 1 -rlx 16", "-27pt -n 24 24 24 -P 2 1 1 -solver 1 -rlx 0 -w 0.7 -CF 1"])
 def test_unchanged_ij_on_two_ranks_with_distributed_setup(built, args):
     """The reference's unchanged src/test/ij.c on 2 ranks, hypre's own DISTRIBUTED host setup (MPI build of the
-    reference over oracle/mpishim), solve on 2 GPUs (hypre_b200/lib/ij_b200_mp) -- against the same command on
+    reference over hypre_b200/host/mpishim), solve on 2 GPUs (hypre_b200/lib/ij_b200_mp) -- against the same command on
     the reference's CPU path (oracle/_ref/ij_ref_mp): identical iteration count, final residual to 1e-6
     relative (the printed digits).  Measured in round 1 (profiles/r01_ij_b200_mp_2gpu_*.log): 13 iterations /
     3.629277e-09 and 8 / 6.133724e-10, both identical to the reference."""

@@ -1,5 +1,5 @@
 """CPU tests of the native multi-rank mode as bench.py uses it: ranks that were NOT started by mpirun_shim
-(torchrun starts them) meet through a directory (SHIM_DIR, oracle/mpishim/mpishim.c: rendezvous) and
+(torchrun starts them) meet through a directory (SHIM_DIR, hypre_b200/host/mpishim/mpishim.c: rendezvous) and
 hypre_b200/hypre.py drives the MPI build of the reference on them.  With the device path off the result must
 be what the reference's own ij driver prints on the same process grid."""
 import os

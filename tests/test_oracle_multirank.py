@@ -1,6 +1,6 @@
 """The plain-C oracle against the reference running on N real ranks.
 
-oracle/_ref/dump_parcsr (our driver over the reference's MPI build + oracle/mpishim) does what
+oracle/_ref/dump_parcsr (our driver over the reference's MPI build + hypre_b200/host/mpishim) does what
 `mpirun -np N ij -solver 1 -rlx <type> [-rhsrand] -n .. -P ..` does and writes the distributed hierarchy,
 the smoother data, the right-hand side and PCG's logged norms.  The test gathers the hierarchy into global
 matrices (the reference's numbering), hands them to the serial oracle restatement (oracle/amg_oracle*.c;

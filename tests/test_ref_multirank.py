@@ -1,7 +1,7 @@
 """The reference on N ranks against ITS OWN golden results.
 
 oracle/Makefile compiles the reference's unmodified host sources a second time WITH MPI
-(oracle/ref_config_mp) against oracle/mpishim -- our small message-passing library, ranks = processes
+(hypre_b200/host/config_mp) against hypre_b200/host/mpishim -- our small message-passing library, ranks = processes
 on this machine -- into oracle/_ref/ij_ref_mp.  These tests replay the `mpirun -np N ./ij ...` lines of
 the reference's regression suite src/test/TEST_ij/{smoother,solvers,default,coarsening,interp}.jobs and
 compare with the numbers its harness checks (<suite>.saved; collected by tests/golden/gen_saved_goldens.py
