@@ -154,22 +154,44 @@ int p2p_chan_create(b200_ctx *c, int n_out, const int *out_procs, const int *out
    int s = B200_OK;
    for (int p = 0; p < 2 && s == B200_OK; p++) { s = arena_alloc(c, sizeof(LLVal) * (size_t)(in_total + 1), &off_buf[p]); }
    if (s == B200_OK) { s = arena_alloc(c, sizeof(u64) * (size_t)(n_out + 1), &off_ack); }
-   if (s != B200_OK) { delete ch; return s; }
+   // A rank whose arena is exhausted still takes part in the two exchanges below -- its neighbours are already
+   // inside them -- and sends offsets of -1, so that every neighbour reports the failure instead of waiting for it.
+   const int  arena_status = s;
+   const bool arena_ok = (s == B200_OK);
 
    // tell every sender where its segment lands in my arena (2 words + 1 spare), and every receiver
    // where its acknowledgement lands (1 word)
    std::vector<long long> to_in((size_t)n_in * 3 + 1), from_out((size_t)n_out * 3 + 1);
    for (int j = 0; j < n_in; j++)
    {
-      to_in[(size_t)j * 3 + 0] = (long long)(off_buf[0] + sizeof(LLVal) * (size_t)in_starts[j]);
-      to_in[(size_t)j * 3 + 1] = (long long)(off_buf[1] + sizeof(LLVal) * (size_t)in_starts[j]);
+      to_in[(size_t)j * 3 + 0] = arena_ok ? (long long)(off_buf[0] + sizeof(LLVal) * (size_t)in_starts[j]) : -1LL;
+      to_in[(size_t)j * 3 + 1] = arena_ok ? (long long)(off_buf[1] + sizeof(LLVal) * (size_t)in_starts[j]) : -1LL;
       to_in[(size_t)j * 3 + 2] = 0;
    }
    s = exchange_words(c, 3, n_in, in_procs, to_in.data(), n_out, out_procs, from_out.data());
    std::vector<long long> to_out((size_t)n_out + 1), from_in((size_t)n_in + 1);
-   for (int i = 0; i < n_out; i++) { to_out[(size_t)i] = (long long)(off_ack + sizeof(u64) * (size_t)i); }
+   for (int i = 0; i < n_out; i++) { to_out[(size_t)i] = arena_ok ? (long long)(off_ack + sizeof(u64) * (size_t)i) : -1LL; }
    if (s == B200_OK) { s = exchange_words(c, 1, n_out, out_procs, to_out.data(), n_in, in_procs, from_in.data()); }
+   if (!arena_ok) { delete ch; return arena_status; }
    if (s != B200_OK) { delete ch; return s; }
+   for (int i = 0; i < n_out; i++)
+   {
+      if (from_out[(size_t)i * 3 + 0] < 0 || from_out[(size_t)i * 3 + 1] < 0)
+      {
+         b200_set_error("peer arena exhausted on rank %d (B200_ARENA_MB sizes it)", out_procs[i]);
+         delete ch;
+         return B200_ERR_CUDA;
+      }
+   }
+   for (int j = 0; j < n_in; j++)
+   {
+      if (from_in[(size_t)j] < 0)
+      {
+         b200_set_error("peer arena exhausted on rank %d (B200_ARENA_MB sizes it)", in_procs[j]);
+         delete ch;
+         return B200_ERR_CUDA;
+      }
+   }
 
    std::vector<LLVal *> dst0((size_t)n_out + 1), dst1((size_t)n_out + 1);
    std::vector<u64 *> iack((size_t)n_in + 1);

@@ -1,5 +1,5 @@
 /* hypre_b200/host/mpishim/selftest.c -- TEST INFRASTRUCTURE (built by oracle/Makefile only): exercises the message-passing shim itself
- * (run by tests/test_mpishim.py under mpirun_shim with 1, 2, 3 and 5 ranks). Prints "SHIM_OK". */
+ * (run by tests/test_ref_multirank.py under mpirun_shim and by tests/test_native_host.py through SHIM_DIR). Prints "SHIM_OK". */
 #include "mpi.h"
 #include <stdio.h>
 #include <stdlib.h>
