@@ -40,8 +40,8 @@ extern "C" int b200_set_compression(int mode, int no_padding_markers)
 
 extern "C" int b200_set_kernel_options(int chunked, int pat_regs)
 {
-   // chunked 2: also the VAL* / plain kernels; pat_regs: bit 0 = the 40-register instantiation, bits 1-3 = grid of
-   // the pattern kernel in waves of resident blocks (0 leaves it)
+   // chunked 2: also the VAL* / plain kernels; pat_regs: bit 0 = ignored (selected register-heavier instantiations
+   // that were measured slower and removed), bits 1-3 = grid of the pattern kernel in waves of resident blocks (0 leaves it)
    ARG_CHECK(chunked >= -1 && chunked <= 2 && pat_regs >= -1 && pat_regs <= 9);
    if (chunked >= 0) { g_rows_chunked = chunked; }
    if (pat_regs >= 0)

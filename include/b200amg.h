@@ -132,8 +132,10 @@ int b200_parcsr_storage(const b200_parcsr *A, int *value_format, long long *stor
  * (environment B200_ZPAD). */
 int b200_set_compression(int mode, int no_padding_markers);
 /* launch options of the thread-per-row kernels (A/B measurements): chunked 1 = every block walks one
- * contiguous run of 32-row slices (default; neighbouring rows meet in L1), 0 = grid stride; pat_regs 1 =
- * the pattern kernel instantiated at 48 registers / 5 blocks per SM instead of 32 / 8; -1 leaves a value. */
+ * contiguous run of 32-row slices (default; neighbouring rows meet in L1), 0 = grid stride, 2 = also the
+ * value-dictionary / plain kernels; pat_regs: bits 1-3 = grid of the pattern kernel in waves of resident blocks
+ * (8 = four waves, the default; 0 leaves it), bit 0 is ignored (it selected register-heavier instantiations of the
+ * pattern kernel, which were measured slower on the B200 and removed); -1 leaves a value. */
 int b200_set_kernel_options(int chunked, int pat_regs);
 /* Test hook for the storage formats (host only, no device needed, never on a solve path): packs the CSR
  * block with the current layout / compression settings exactly as b200_parcsr_create would and computes
@@ -242,7 +244,6 @@ int b200_amg_set_coarse_dense(b200_amg *amg, int n_global, const double *A_mat_h
  * b200_bicgstab_solve): hypre_ParAMGDataMaxIter with tol 0 -- hypre_BoomerAMGSolve then runs that many cycles
  * without residual norms (src/parcsr_ls/par_amg_solve.c:257-336; ij -precon_cycles).  Default 1. */
 int b200_amg_set_precond_cycles(b200_amg *amg, int cycles);
-/* finalise: allocates F/U/work vectors, builds transposes and the launch plan */
 /* CF-ordered relaxation (hypre_BoomerAMGRelaxIF, src/parcsr_ls/par_relax_interface.c:20-64; hypre_ParAMGDataRelaxOrder,
  * ij -CF 1): with relax_order 1 a sweep on a non-coarsest level is two calls of the smoother -- C points then F
  * points on the way down, F then C on the way up (relax types 0 / 7 / 18 through hypre_ParVectorElmdivpyMarked,
@@ -251,6 +252,7 @@ int b200_amg_set_precond_cycles(b200_amg *amg, int cycles);
  * non-coarsest level for the Jacobi types.  Both before b200_amg_finalize. */
 int b200_amg_set_relax_order(b200_amg *amg, int relax_order);
 int b200_amg_set_level_cf_marker(b200_amg *amg, int level, const int *cf_marker_h);
+/* finalise: allocates F/U/work vectors, builds transposes and the launch plan */
 int b200_amg_finalize(b200_amg *amg);
 /* one multigrid cycle u <- u + B(f - A u)   (dev pointers, level-0 size)
  * hypre_BoomerAMGCycle (src/parcsr_ls/par_cycle.c:22-803).  zero_guess as above. */
@@ -259,15 +261,16 @@ int b200_amg_cycle(b200_amg *amg, const double *f, double *u, int zero_guess);
 int b200_amg_cycle_bytes(const b200_amg *amg, double *bytes);
 /* the same model with the bytes the device layouts actually store (b200_parcsr_storage) */
 int b200_amg_cycle_bytes_stored(const b200_amg *amg, double *bytes);
-/* borrowed handle to A_array[level] / P_array[level] (owned by amg) */
 /* Persistent coarse-level kernel: the deepest run of levels whose operators are small CSR blocks without
  * communication (every level below ~4e6 nonzeros on one rank; the replicated levels on several) is executed as ONE
  * cooperative kernel per visit -- the operators of hypre_BoomerAMGCycle (par_cycle.c:209-779) on those levels in
  * order, a grid-wide barrier between them -- instead of one launch each.  Same arithmetic, bit-identical results.
  * b200_set_tail_limit: largest level (nonzeros of A_l) that joins, 0 = off (applies to hierarchies finalized
- * afterwards; environment B200_TAIL_NNZ); b200_amg_tail_level: first level inside the kernel, -1 = none. */
+ * afterwards; environment B200_TAIL_NNZ); b200_amg_tail_level: first level inside the kernel, -1 = none.
+ * Off by default: measured on the B200 it is slower than the graph-replayed launches. */
 int b200_set_tail_limit(long long max_nnz);
 int b200_amg_tail_level(const b200_amg *amg, int *level);
+/* borrowed handle to A_array[level] / P_array[level] (owned by amg) */
 int b200_amg_level_matrix(const b200_amg *amg, int level, b200_parcsr **A);
 int b200_amg_level_interp(const b200_amg *amg, int level, b200_parcsr **P);
 int b200_amg_level_info(const b200_amg *amg, int level, int *n_rows, long long *nnz_A,
