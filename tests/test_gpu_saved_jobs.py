@@ -7,7 +7,7 @@ devices) and compared with the reference's recorded values (<suite>.saved, tests
 iteration counts exactly, residual norms / factors / complexities to the printed digits) -- what
 src/test/runtest.sh:400-428 does for the reference.  Options without a device implementation must be REJECTED
 loudly (status "rejected"), never answered by the CPU.  Needs one GPU per rank: jobs with more ranks than GPUs
-are skipped, the whole test below 2 GPUs.  Table of the last full run: profiles/r02_saved_jobs_b200_*.json."""
+are skipped, the whole test below 2 GPUs; jobs with more than 4 ranks only with B200_SAVED_JOBS_MAX_RANKS=8.  Table of the last full run: profiles/r02_saved_jobs_b200_*.json."""
 import json
 import os
 import subprocess
@@ -33,7 +33,10 @@ def test_reference_saved_jobs_gate_the_device_backend(built):
         pytest.skip("needs one GPU per rank (the reference's jobs use 2-8 ranks)")
     out = os.path.join(ROOT, "gpurun_out")
     os.makedirs(out, exist_ok=True)
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "run_saved_jobs_b200.py"), "--max-ranks", str(min(n, 8))],
+    # jobs with up to 4 ranks are what has been run on hardware (profiles/r02_saved_jobs_b200_4gpu.json); the 5-8-rank
+    # jobs join only on request
+    cap = int(os.environ.get("B200_SAVED_JOBS_MAX_RANKS", "4"))
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "run_saved_jobs_b200.py"), "--max-ranks", str(min(n, cap))],
                        capture_output=True, text=True, timeout=3000)
     open(os.path.join(out, "saved_jobs_b200_%dgpu.json" % n), "w").write(p.stdout)
     rep = json.loads(p.stdout)
