@@ -1,4 +1,4 @@
-"""GPU tests, collected last (first GPU run pending -- written in a session without GPU minutes): GMRES(k),
+"""GPU tests, collected late: GMRES(k),
 COGMRES(k), FlexGMRES(k) and BiCGSTAB on the device (hypre_b200/csrc/krylov.cu) behind hypre_GMRESSolve / hypre_BiCGSTABSolve
 (src/krylov/gmres.c:274-930, bicgstab.c:226-640).
 
@@ -263,7 +263,7 @@ def test_device_bound_vectors_solve_in_place(H, ctx, kind):
 @pytest.mark.parametrize("name", ["lap7_24_rlx16_var1", "lap7_24_rlx16_o4", "lap7_24_rlx16_o3_noscale", "lap7_24_rlx18_pc3",
                                   "lap7_24_rlx16_pc2", "lap7_24_rlx0_w08", "lap27_20_rlx0_w07_ns2"])
 def test_pcg_option_cases_match_oracle_and_reference(H, ctx, name):
-    """AMG-PCG with the options added after the last GPU run of round 1 -- Chebyshev variant 1 / orders 3, 4 /
+    """AMG-PCG with further options -- Chebyshev variant 1 / orders 3, 4 /
     unscaled, several cycles per preconditioner application, weighted point Jacobi (relax 0) -- device vs oracle vs
     the reference's hypre_PCGSolve in-process (the form of test_gpu_solve.py's cycle-variant test; kept in this
     file so that a first-run failure cannot disturb the verified tests)"""
