@@ -123,3 +123,22 @@ def test_parity_block_against_the_reference_run(bench, histories):
 def test_parity_block_without_anything_to_compare_is_not_ok(bench):
     p = bench.parity_block(np.array([1.0, 0.1, 0.01]), 2, None, None)
     assert p["ok"] is False and p["ref_iterations"] is None and p["max_rel_norm_diff"] is None
+
+
+def test_committed_ncu_traffic_belongs_to_the_kernel_source_in_the_tree(bench):
+    """roofline.traffic is quoted from profiles/r02_ncu_traffic_pat8.json only while spmv.cuh is the file it was
+    measured on: the committed pair must match, and a different matrix / format must be refused"""
+    t = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic_pat8.json")))
+    assert t["spmv_cuh_sha16"] == bench._sha(os.path.join(ROOT, "hypre_b200", "csrc", "spmv.cuh"))
+    m = t["matrix"]
+    assert bench.ncu_traffic(m["rows"], m["nnz"], m["value_format"]) == t["spmv_level0"]["traffic_bytes_per_launch"]
+    assert bench.ncu_traffic(m["rows"], m["nnz"], 1) is None
+    assert bench.ncu_traffic(m["rows"] + 1, m["nnz"], m["value_format"]) is None
+
+
+def test_launch_summary_is_what_the_script_makes_of_the_committed_launch_list():
+    import subprocess
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "summarize_launches.py"),
+                          os.path.join(ROOT, "profiles", "r02_launches_lap7_256_cheby.csv")],
+                         capture_output=True, text=True, check=True).stdout
+    assert out == open(os.path.join(ROOT, "profiles", "r02_launches_lap7_256_cheby_summary.txt")).read()
